@@ -1,0 +1,156 @@
+/* kge_abi.h — C-ABI of libkge_b200.so: the B200-native batch hot path of
+ * melissakou/knowledge-graph-embedding (training step + filtered ranking).
+ *
+ * The reference has no FFI: its "operator API" is the Python protocol of
+ * KGE/models/base_model/BaseModel.py.  Each entry point below names the reference
+ * interface it replaces; INTEGRATION.md shows the ctypes binding a maintainer adds.
+ *
+ * Conventions
+ *  - plain C, no CUDA / torch types: device pointers are void* / float*, the stream
+ *    is a cudaStream_t passed as void*.
+ *  - the caller owns every buffer (tables, workspace, outputs); the library never
+ *    allocates, frees or retains device memory across calls.
+ *  - every call enqueues on the given stream and returns; no host sync.
+ *  - return 0 on success, a negative kge_status otherwise; kge_last_error() gives the
+ *    thread-local message.  There is no CPU fallback: without a CUDA device the
+ *    compute calls return KGE_ECUDA.
+ *  - all floating point is fp32 (every reference table is np.float32, TransE.py:96).
+ *  - table rows are `cols` logical floats at a stride of `ld` floats; ld % 4 == 0 and
+ *    16-byte aligned bases are required (128-bit row access); padding must be zero.
+ */
+#ifndef KGE_ABI_H
+#define KGE_ABI_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KGE_ABI_VERSION 1
+#define KGE_MAX_TABLES 4
+
+typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
+               KGE_EWORKSPACE = -4 } kge_status;
+
+/* KGE/models/{translating_based,semantic_based}/ *.py */
+typedef enum { KGE_UM = 0, KGE_SE = 1, KGE_TRANSE = 2, KGE_TRANSH = 3, KGE_TRANSR = 4,
+               KGE_TRANSD = 5, KGE_ROTATE = 6, KGE_DISTMULT = 7, KGE_RESCAL = 8 } kge_model;
+/* KGE/score.py:49 LpDistance, :65 LpDistancePow, :78 Dot */
+typedef enum { KGE_SCORE_LP = 0, KGE_SCORE_LP_POW = 1, KGE_SCORE_DOT = 2 } kge_score_kind;
+/* KGE/loss.py:49,84,115,145,184 */
+typedef enum { KGE_LOSS_HINGE = 0, KGE_LOSS_LOGISTIC = 1, KGE_LOSS_BCE = 2,
+               KGE_LOSS_SELF_ADV = 3, KGE_LOSS_SQUARE = 4 } kge_loss_kind;
+/* BaseModel.py:49 corrupt_side */
+typedef enum { KGE_SIDE_H = 0, KGE_SIDE_T = 1, KGE_SIDE_HT = 2 } kge_side;
+/* KGE/ns_strategy.py:23 UniformStrategy, :67 TypedStrategy */
+typedef enum { KGE_NS_UNIFORM = 0, KGE_NS_TYPED = 1 } kge_sampler_kind;
+
+/* Table slots (model_weights keys):
+ *   0 ent_emb (RotatE: cols = 2*d, re/im interleaved, RotatE.py:96)
+ *   1 ent_proj (TransD)
+ *   2 rel_emb (TransE/H/R/D, RotatE) | rel_inter (DistMult; RESCAL d*d) | rel_proj_h (SE d*d)
+ *   3 rel_hyper (TransH) | rel_proj (TransR d_e*d_r row-major; TransD d_r) | rel_proj_t (SE) */
+enum { KGE_T_ENT = 0, KGE_T_ENT_PROJ = 1, KGE_T_REL_A = 2, KGE_T_REL_B = 3 };
+
+typedef struct kge_table {
+  float* w;          /* weights                                   */
+  float* m;          /* Adam first moment  (NULL for score/rank)   */
+  float* v;          /* Adam second moment (NULL for score/rank)   */
+  int64_t rows;
+  int32_t cols;      /* logical floats per row                     */
+  int32_t ld;        /* row stride in floats, multiple of 4        */
+} kge_table;
+
+typedef struct kge_tables {
+  kge_table t[KGE_MAX_TABLES];   /* unused slots: w == NULL */
+} kge_tables;
+
+typedef struct kge_cfg {
+  int32_t abi_version;           /* KGE_ABI_VERSION */
+  int32_t model;                 /* kge_model */
+  int32_t score;                 /* kge_score_kind (ignored by DistMult / RESCAL) */
+  int32_t loss;                  /* kge_loss_kind */
+  int32_t sampler;               /* kge_sampler_kind */
+  int32_t corrupt_side;          /* kge_side */
+  int32_t negative_ratio;        /* as given by the user; 'h+t' uses negative_ratio/2 per side */
+  int32_t constraint;            /* model's constraint flag */
+  int32_t id_dtype;              /* 0 = int32 triples, 1 = int64 (test_data_utils.py:82,90) */
+  int32_t d_ent, d_rel;          /* embedding sizes (RotatE: complex dimension) */
+  int32_t reserved;
+  float score_p;                 /* LpDistance.p; INFINITY allowed (score.py:60) */
+  float margin, temperature;     /* loss.py:77, 171-172 */
+  float constraint_weight;       /* TransH.py:66, DistMult.py:40, RESCAL.py:39 */
+  float lr, beta1, beta2, eps;   /* tf.optimizers.Adam(): 1e-3, .9, .999, 1e-7 */
+  float clip_norm;               /* 5.0, BaseModel.py:327 */
+  float rotate_scale;            /* pi / limit, RotatE.py:160 */
+  int64_t n_ent, n_rel;
+} kge_cfg;
+
+/* Negative-sampler data (device pointers).  Uniform: pool == NULL means arange(n_ent)
+ * (BaseModel.py:257).  Typed: CSR of metadata["type2inds"] (BaseModel.py:259-263). */
+typedef struct kge_sampler {
+  const int64_t* pool;  int64_t pool_len;
+  const int64_t* ent_type;      /* [n_ent] type id of each entity                 */
+  const int64_t* type_off;      /* [n_types+1]                                    */
+  const int64_t* type_members;  /* members, grouped by type                       */
+  const int64_t* ent_pos;       /* [n_ent] position inside own type pool, or -1   */
+  int64_t n_types;
+} kge_sampler;
+
+/* Known-positive filter for ranking, CSR per query (replaces the two scans of
+ * positive_X per query at BaseModel.py:646-650): ids[off[q] .. off[q+1]) are the
+ * candidate entities to exclude for query q.  off == NULL means unfiltered. */
+typedef struct kge_filter {
+  const int64_t* off;  const int64_t* ids;
+} kge_filter;
+
+typedef struct kge_ctx kge_ctx;
+
+int kge_abi_version(void);
+const char* kge_last_error(void);
+int kge_ctx_create(int device, kge_ctx** out);
+int kge_ctx_destroy(kge_ctx* ctx);
+
+/* Bytes of workspace kge_train_step (batch B) / kge_rank (Q queries) need. */
+int kge_workspace_bytes(const kge_cfg* cfg, int64_t B, int64_t Q, size_t* out);
+
+/* Replaces NegativeSampler.__call__ + __corrupt_h/__corrupt_t (ns_strategy.py:39,94;
+ * BaseModel.py:332-408).  neg_out: int64[B*k_eff] entity ids in the reference's row
+ * order (row i*k_eff+c belongs to positive i; 'h+t': even c = head corruption).
+ * Stream = counter-based Philox4x32-10, see oracle/philox.py for the spec. */
+int kge_sample_negatives(kge_ctx*, const kge_cfg*, const kge_sampler*, const void* triples,
+                         int64_t B, uint64_t seed, uint64_t step, int64_t* neg_out, void* stream);
+
+/* Replaces model.score_hrt(h, r, t) on id vectors (BaseModel.py:410 + each model). */
+int kge_score(kge_ctx*, const kge_cfg*, const kge_tables*, const void* h, const void* r,
+              const void* t, int64_t n, float* out, void* stream);
+
+/* Start-of-batch constraint of _constraint_loss (e.g. TransE.py:171-172) on its own;
+ * kge_train_step runs it itself.  Exposed for init-time normalisation
+ * (TransE.py:108-109, RESCAL.py:109-115): op 0 = normalise L2 rows to 1, 1 = clip L2
+ * rows to <= 1, applied to table slot `slot`. */
+int kge_constrain_table(kge_ctx*, const kge_tables*, int slot, int op, void* stream);
+
+/* Replaces KGEModel.__run_single_batch (BaseModel.py:293-330): constraint, negative
+ * sampling (or neg_override: int64[B*k_eff] ids as above), scores, loss, and when
+ * is_train: analytic backward, per-variable clip_by_norm, TF-semantics Adam step
+ * number adam_t (1-based).  loss_out: device float.  neg_out (nullable) receives
+ * the negatives used. */
+int kge_train_step(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*,
+                   const void* triples, int64_t B, uint64_t seed, uint64_t step,
+                   uint64_t adam_t, const int64_t* neg_override, int is_train,
+                   float* loss_out, int64_t* neg_out, void* ws, size_t ws_bytes, void* stream);
+
+/* Replaces the evaluate()/get_rank() loop (BaseModel.py:602-604, 620-654) for Q
+ * queries at once: count_out[q] += #{e in [ent_lo, ent_hi) : score(e) > pos_score(q),
+ * e not filtered}; rank = 1 + count (summed over entity shards).  count_out must be
+ * zeroed by the caller.  side = KGE_SIDE_H or KGE_SIDE_T. */
+int kge_rank(kge_ctx*, const kge_cfg*, const kge_tables*, const void* queries, int64_t Q,
+             int side, const kge_filter* filter, int64_t ent_lo, int64_t ent_hi,
+             int32_t* count_out, void* ws, size_t ws_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KGE_ABI_H */

@@ -1,0 +1,185 @@
+// common.cuh — shared device helpers for the sm_100a KGE kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+#include "kge_abi.h"
+
+namespace kge {
+
+constexpr int WARP = 32;
+constexpr unsigned FULL = 0xffffffffu;
+
+// ---- error plumbing (abi.cu owns the thread-local string) -----------------------
+void set_error(const char* fmt, ...);
+#define KGE_CUDA_OK(expr)                                                          \
+  do {                                                                             \
+    cudaError_t _e = (expr);                                                       \
+    if (_e != cudaSuccess) {                                                       \
+      kge::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),       \
+                     __FILE__, __LINE__);                                          \
+      return KGE_ECUDA;                                                            \
+    }                                                                              \
+  } while (0)
+#define KGE_REQUIRE(cond, code, ...)                                               \
+  do {                                                                             \
+    if (!(cond)) { kge::set_error(__VA_ARGS__); return (code); }                   \
+  } while (0)
+
+struct kge_ctx_impl {
+  int device;
+  int sm_count;
+  int smem_optin;
+};
+
+// ---- warp reductions (fixed butterfly order: deterministic) ---------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(FULL, v, o));
+  return v;
+}
+__device__ __forceinline__ void warp_sum2(float& a, float& b) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(FULL, a, o);
+    b += __shfl_xor_sync(FULL, b, o);
+  }
+}
+
+// ---- ids -------------------------------------------------------------------------
+__device__ __forceinline__ int64_t load_id(const void* p, int64_t i, int id64) {
+  return id64 ? reinterpret_cast<const int64_t*>(p)[i]
+              : (int64_t) reinterpret_cast<const int32_t*>(p)[i];
+}
+
+// ---- float4 helpers ---------------------------------------------------------------
+__device__ __forceinline__ float4 f4(float a, float b, float c, float d) { return make_float4(a, b, c, d); }
+__device__ __forceinline__ float4 f4zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+__device__ __forceinline__ float4 operator+(float4 a, float4 b) { return f4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+__device__ __forceinline__ float4 operator-(float4 a, float4 b) { return f4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
+__device__ __forceinline__ float4 operator*(float4 a, float4 b) { return f4(a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w); }
+__device__ __forceinline__ float4 operator*(float s, float4 a) { return f4(s * a.x, s * a.y, s * a.z, s * a.w); }
+__device__ __forceinline__ float4 operator-(float4 a) { return f4(-a.x, -a.y, -a.z, -a.w); }
+__device__ __forceinline__ void operator+=(float4& a, float4 b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+__device__ __forceinline__ float hsum(float4 a) { return (a.x + a.y) + (a.z + a.w); }
+__device__ __forceinline__ float dot4(float4 a, float4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
+__device__ __forceinline__ float sgn(float x) { return (x > 0.f) ? 1.f : ((x < 0.f) ? -1.f : 0.f); }
+
+// A table row spread over a warp: lane l owns 16-byte chunks l, l+32, ... (NV of them).
+template <int NV>
+struct Row {
+  float4 v[NV];
+  __device__ __forceinline__ void zero() {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = f4zero();
+  }
+};
+
+template <int NV>
+__device__ __forceinline__ void load_row(Row<NV>& r, const float* __restrict__ base, int64_t row,
+                                         int ld, int cols, int lane) {
+  const float4* p = reinterpret_cast<const float4*>(base + row * (int64_t) ld);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    int c = lane + i * WARP;
+    r.v[i] = (4 * c < cols) ? __ldg(p + c) : f4zero();
+  }
+}
+template <int NV>
+__device__ __forceinline__ void store_row(const Row<NV>& r, float* __restrict__ base, int64_t row,
+                                          int ld, int cols, int lane) {
+  float4* p = reinterpret_cast<float4*>(base + row * (int64_t) ld);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    int c = lane + i * WARP;
+    if (4 * c < cols) p[c] = r.v[i];
+  }
+}
+template <int NV>
+__device__ __forceinline__ float row_dot_partial(const Row<NV>& a, const Row<NV>& b) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) s += dot4(a.v[i], b.v[i]);
+  return s;
+}
+template <int NV>
+__device__ __forceinline__ void row_axpy(Row<NV>& y, float a, const Row<NV>& x) {  // y += a*x
+#pragma unroll
+  for (int i = 0; i < NV; ++i) y.v[i] += a * x.v[i];
+}
+template <int NV>
+__device__ __forceinline__ void row_add(Row<NV>& y, const Row<NV>& x) {
+#pragma unroll
+  for (int i = 0; i < NV; ++i) y.v[i] += x.v[i];
+}
+// mask elements with index >= cols (used where padding could leak: Linf ties, trunc)
+template <int NV>
+__device__ __forceinline__ void row_mask(Row<NV>& r, int cols, int lane) {
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    int e = 4 * (lane + i * WARP);
+    if (e + 0 >= cols) r.v[i].x = 0.f;
+    if (e + 1 >= cols) r.v[i].y = 0.f;
+    if (e + 2 >= cols) r.v[i].z = 0.f;
+    if (e + 3 >= cols) r.v[i].w = 0.f;
+  }
+}
+
+// ---- Philox4x32-10 (Salmon et al. SC'11; spec in oracle/philox.py) ----------------
+__device__ __forceinline__ uint32_t philox_word0(uint64_t seed, uint64_t step,
+                                                          uint32_t side_bit, uint64_t n) {
+  uint32_t c0 = (uint32_t) n, c1 = (uint32_t)(n >> 32), c2 = (uint32_t) step,
+           c3 = (uint32_t)(((step >> 32) << 1) | side_bit);
+  uint32_t k0 = (uint32_t) seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    if (r) { k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+    uint64_t p0 = (uint64_t) 0xD2511F53u * c0;
+    uint64_t p1 = (uint64_t) 0xCD9E8D57u * c2;
+    uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t) p1;
+    uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t) p0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+  }
+  return c0;
+}
+
+// Negative entity for positive i, slot c of its k_eff negatives (reference row order).
+// Returns the entity id; *is_head tells which side was corrupted.
+struct SamplerDev {
+  int kind;                 // kge_sampler_kind
+  int side_mode;            // kge_side
+  int k_eff, k_side;
+  uint64_t seed, step;
+  int64_t n_ent;
+  kge_sampler s;
+};
+__device__ __forceinline__ bool neg_is_head(const SamplerDev& sd, int c) {
+  return sd.side_mode == KGE_SIDE_H || (sd.side_mode == KGE_SIDE_HT && (c & 1) == 0);
+}
+__device__ __forceinline__ int64_t sample_negative(const SamplerDev& sd, int64_t i, int c,
+                                                   int64_t h, int64_t t) {
+  bool head = neg_is_head(sd, c);
+  int jj = (sd.side_mode == KGE_SIDE_HT) ? (c >> 1) : c;
+  uint64_t n = (uint64_t) i * (uint64_t) sd.k_side + (uint64_t) jj;
+  uint64_t u = philox_word0(sd.seed, sd.step, head ? 0u : 1u, n);
+  if (sd.kind == KGE_NS_UNIFORM) {
+    if (sd.s.pool == nullptr) return (int64_t)(u % (uint64_t) sd.n_ent);
+    return sd.s.pool[u % (uint64_t) sd.s.pool_len];
+  }
+  int64_t x = head ? h : t;
+  int64_t ty = sd.s.ent_type[x];
+  int64_t lo = sd.s.type_off[ty], len = sd.s.type_off[ty + 1] - lo;
+  int64_t q = sd.s.ent_pos[x];
+  int64_t eff = (q >= 0) ? len - 1 : len;
+  if (eff <= 0) return x;   // host rejects singleton pools before launch
+  int64_t j = (int64_t)(u % (uint64_t) eff);
+  if (q >= 0 && j >= q) ++j;
+  return sd.s.type_members[lo + j];
+}
+
+}  // namespace kge

@@ -1,0 +1,9 @@
+// model_rotate.cu — kernel instantiations for MRotatE (step_kernels.cuh, rank_kernels.cuh);
+// one translation unit per model so they compile in parallel.
+#include "step_launch.cuh"
+#include "rank_kernels.cuh"
+namespace kge {
+int launch_step_rotate(const StepParams& p, const StepLaunch& L) { return launch_step_model<MRotatE>(p, L); }
+int launch_score_rotate(const ScoreParams& p, const AuxLaunch& L) { return launch_score_model<MRotatE>(p, L); }
+int launch_rank_rotate(const RankParams& p, const AuxLaunch& L) { return launch_rank_model<MRotatE>(p, L); }
+}  // namespace kge

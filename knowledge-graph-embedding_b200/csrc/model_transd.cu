@@ -1,0 +1,9 @@
+// model_transd.cu — kernel instantiations for MTransD (step_kernels.cuh, rank_kernels.cuh);
+// one translation unit per model so they compile in parallel.
+#include "step_launch.cuh"
+#include "rank_kernels.cuh"
+namespace kge {
+int launch_step_transd(const StepParams& p, const StepLaunch& L) { return launch_step_model<MTransD>(p, L); }
+int launch_score_transd(const ScoreParams& p, const AuxLaunch& L) { return launch_score_model<MTransD>(p, L); }
+int launch_rank_transd(const RankParams& p, const AuxLaunch& L) { return launch_rank_model<MTransD>(p, L); }
+}  // namespace kge

@@ -1,0 +1,9 @@
+// model_transh.cu — kernel instantiations for MTransH (step_kernels.cuh, rank_kernels.cuh);
+// one translation unit per model so they compile in parallel.
+#include "step_launch.cuh"
+#include "rank_kernels.cuh"
+namespace kge {
+int launch_step_transh(const StepParams& p, const StepLaunch& L) { return launch_step_model<MTransH>(p, L); }
+int launch_score_transh(const ScoreParams& p, const AuxLaunch& L) { return launch_score_model<MTransH>(p, L); }
+int launch_rank_transh(const RankParams& p, const AuxLaunch& L) { return launch_rank_model<MTransH>(p, L); }
+}  // namespace kge

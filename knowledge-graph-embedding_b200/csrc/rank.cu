@@ -1,0 +1,90 @@
+// rank.cu — host side of kge_score and kge_rank.
+#include "host_common.cuh"
+#include "rank_kernels.cuh"
+
+namespace kge {
+size_t rank_workspace_bytes(const kge_cfg*, int64_t) { return 256; }
+}  // namespace kge
+using namespace kge;
+
+extern "C" int kge_score(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tables, const void* h, const void* r,
+                         const void* t, int64_t n, float* out, void* stream) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
+  if (int rc = check_cfg(cfg)) return rc;
+  if (int rc = check_tables(cfg, tables, false)) return rc;
+  KGE_REQUIRE(h && r && t && out && n > 0, KGE_EINVAL, "h / r / t / out / n invalid");
+  KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED, "matrix-relation models (SE/TransR/RESCAL) not built yet");
+  ScoreParams p;
+  fill_model_dev(cfg, tables, p.md);
+  p.h = h; p.r = r; p.t = t; p.id64 = cfg->id_dtype; p.n = n; p.out = out;
+  AuxLaunch L;
+  L.nv = pick_nv(cfg);
+  int64_t blocks = (n + 7) / 8;
+  if (blocks > (int64_t) ctx->sm_count * 16) blocks = (int64_t) ctx->sm_count * 16;
+  L.grid = dim3((unsigned) blocks);
+  L.stream = (cudaStream_t) stream;
+  switch (cfg->model) {
+    case KGE_UM: return launch_score_um(p, L);
+    case KGE_TRANSE: return launch_score_transe(p, L);
+    case KGE_TRANSH: return launch_score_transh(p, L);
+    case KGE_TRANSD: return launch_score_transd(p, L);
+    case KGE_ROTATE: return launch_score_rotate(p, L);
+    case KGE_DISTMULT: return launch_score_distmult(p, L);
+  }
+  set_error("model %d has no score kernel", cfg->model);
+  return KGE_EUNSUPPORTED;
+}
+
+extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tables, const void* queries, int64_t Q,
+                        int side, const kge_filter* filter, int64_t ent_lo, int64_t ent_hi, int32_t* count_out,
+                        void* ws, size_t ws_bytes, void* stream) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
+  if (int rc = check_cfg(cfg)) return rc;
+  if (int rc = check_tables(cfg, tables, false)) return rc;
+  KGE_REQUIRE(queries && count_out && Q > 0, KGE_EINVAL, "queries / count_out / Q invalid");
+  KGE_REQUIRE(side == KGE_SIDE_H || side == KGE_SIDE_T, KGE_EINVAL, "side must be 'h' or 't' (BaseModel.py:639-644)");
+  KGE_REQUIRE(0 <= ent_lo && ent_lo < ent_hi && ent_hi <= cfg->n_ent, KGE_EINVAL, "bad entity shard [%lld, %lld)",
+              (long long) ent_lo, (long long) ent_hi);
+  KGE_REQUIRE(!filter || !filter->off || filter->ids, KGE_EINVAL, "filter.off given without filter.ids");
+  KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED, "matrix-relation models (SE/TransR/RESCAL) not built yet");
+  (void) ws; (void) ws_bytes;
+  RankParams p;
+  fill_model_dev(cfg, tables, p.md);
+  p.queries = queries; p.id64 = cfg->id_dtype; p.Q = Q; p.side = side;
+  p.f_off = filter ? filter->off : nullptr;
+  p.f_ids = filter ? filter->ids : nullptr;
+  p.ent_lo = ent_lo; p.ent_hi = ent_hi;
+  p.count = count_out;
+  AuxLaunch L;
+  L.nv = pick_nv(cfg);
+  L.stream = (cudaStream_t) stream;
+  const int64_t span = ent_hi - ent_lo;
+  // enough CTAs per query to fill the machine, at least 64 candidates per warp pass
+  int chunk = 2048;
+  while (chunk > 256 && Q * ((span + chunk - 1) / chunk) < (int64_t) ctx->sm_count * 8) chunk >>= 1;
+  p.chunk = chunk;
+  const int64_t QMAX = 65535;    // gridDim.y limit
+  for (int64_t q0 = 0; q0 < Q; q0 += QMAX) {
+    const int64_t qn = (Q - q0 < QMAX) ? Q - q0 : QMAX;
+    RankParams pp = p;
+    pp.queries = (const char*) queries + (size_t) q0 * 3 * (cfg->id_dtype ? 8 : 4);
+    pp.count = count_out + q0;
+    if (pp.f_off) pp.f_off = p.f_off + q0;
+    pp.Q = qn;
+    L.grid = dim3((unsigned) ((span + chunk - 1) / chunk), (unsigned) qn);
+    int rc;
+    switch (cfg->model) {
+      case KGE_UM: rc = launch_rank_um(pp, L); break;
+      case KGE_TRANSE: rc = launch_rank_transe(pp, L); break;
+      case KGE_TRANSH: rc = launch_rank_transh(pp, L); break;
+      case KGE_TRANSD: rc = launch_rank_transd(pp, L); break;
+      case KGE_ROTATE: rc = launch_rank_rotate(pp, L); break;
+      case KGE_DISTMULT: rc = launch_rank_distmult(pp, L); break;
+      default: set_error("model %d has no rank kernel", cfg->model); rc = KGE_EUNSUPPORTED;
+    }
+    if (rc) return rc;
+  }
+  return KGE_OK;
+}

@@ -1,0 +1,241 @@
+// step_kernels.cuh — the fused per-batch training kernels (vector-family models).
+//
+//   k_step   : one warp group per positive: Philox corruption, gather of h/r/t rows
+//              (128-bit loads, rows in registers), model projection, score, loss,
+//              analytic backward.  Emits gradient *records* (one row per negative
+//              entity, plus per-positive pre-reduced rows for the shared h, t and
+//              relation rows), sort keys, and per-positive loss / norm^2 partials.
+//   k_reduce : fixed-order reduction of the partials -> loss, per-table clip scales.
+//   k_update : one warp per table row: sum the row's records in sorted (stable)
+//              order, apply clip scale and the TF-semantics Adam update (dense
+//              decay of m, v and move of w for every row).
+// No atomics anywhere: results are bitwise reproducible run to run.
+#pragma once
+#include "models.cuh"
+#include "loss.cuh"
+
+namespace kge {
+
+constexpr int STEP_THREADS = 256;
+constexpr int STEP_WARPS = STEP_THREADS / WARP;
+constexpr int N_PART = 1 + KGE_MAX_TABLES;   // loss + norm^2 per table
+
+struct StepParams {
+  ModelDev md;
+  LossDev loss;
+  SamplerDev sd;
+  const void* triples;
+  int id64;
+  int64_t B;
+  int k_eff;
+  int wpp;                       // warps per positive: 1, 2, 4 or 8
+  const int64_t* neg_override;   // nullable
+  int64_t* neg_ids;              // [B*k_eff] negatives used (always written)
+  float* rec[KGE_MAX_TABLES];    // gradient records per table slot
+  uint32_t* keys;                // [2B + B*k_eff + B]
+  uint32_t* vals;                // iota over the same range
+  float* part;                   // [N_PART][B]
+};
+
+__device__ __forceinline__ void group_barrier(int grp, int wpp) {
+  if (wpp == 1) { __syncwarp(); return; }
+  asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(wpp * WARP) : "memory");
+}
+
+template <class M, int NV, bool TRAIN>
+__global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
+  using Ent = typename M::template Ent<NV>;
+  using Rel = typename M::template Rel<NV>;
+  extern __shared__ float4 smem4[];
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wpp = p.wpp, ppc = STEP_WARPS / wpp;
+  const int grp = warp / wpp, wig = warp % wpp;
+  const int64_t i = (int64_t) blockIdx.x * ppc + grp;
+  if (i >= p.B) return;                       // whole group leaves together
+  const ModelDev& md = p.md;
+  const int k = p.k_eff;
+
+  // shared memory carve-up (per CTA): scores [ppc][k], scalars [8][8], accumulators
+  constexpr int ACC_F4 = (2 * Ent::NROWS + Rel::NROWS) * NV;   // float4 per lane
+  float* s_neg = reinterpret_cast<float*>(smem4) + (size_t) grp * k;
+  float* s_red = reinterpret_cast<float*>(smem4) + (((size_t) ppc * k + 3) & ~(size_t) 3) + warp * 8;
+  float4* s_acc = smem4 + (((size_t) ppc * k + 3) / 4) + (STEP_WARPS * 8) / 4 + (size_t) warp * ACC_F4 * WARP;
+
+  const int64_t h = load_id(p.triples, 3 * i + 0, p.id64);
+  const int64_t r = load_id(p.triples, 3 * i + 1, p.id64);
+  const int64_t t = load_id(p.triples, 3 * i + 2, p.id64);
+  Ent H, T;
+  Rel R;
+  H.load(md, h, lane);
+  T.load(md, t, lane);
+  R.load(md, r, lane);
+
+  Row<NV> x, y;
+  FwdSaved<NV> sv;
+  const float sp = M::template forward<NV>(md, H, R, T, lane, x, y, sv);
+
+  // self-adversarial weights need all k scores of this positive first (loss.py:176-177)
+  float sm_max = 0.f, sm_inv = 1.f;
+  const bool softmax = (p.loss.kind == KGE_LOSS_SELF_ADV);
+  if (softmax) {
+    for (int c = wig; c < k; c += wpp) {
+      const bool head = neg_is_head(p.sd, c);
+      const int64_t e = p.neg_override ? p.neg_override[i * k + c] : sample_negative(p.sd, i, c, h, t);
+      Ent N;
+      N.load(md, e, lane);
+      const float sn = M::template forward<NV>(md, head ? N : H, R, head ? T : N, lane, x, y, sv);
+      if (lane == 0) s_neg[c] = sn;
+    }
+    group_barrier(grp, wpp);
+    float m = -INFINITY;
+    for (int c = lane; c < k; c += WARP) m = fmaxf(m, p.loss.temperature * s_neg[c]);
+    m = warp_max(m);
+    float z = 0.f;
+    for (int c = lane; c < k; c += WARP) z += expf(p.loss.temperature * s_neg[c] - m);
+    z = warp_sum(z);
+    sm_max = m;
+    sm_inv = 1.0f / z;
+  }
+
+  Ent GH, GT;
+  Rel GR;
+  GH.zero(); GT.zero(); GR.zero();
+  float nrm[KGE_MAX_TABLES] = {0.f, 0.f, 0.f, 0.f};
+  float lsum = 0.f, gpos = 0.f;
+  const int64_t nE = 2 * p.B + p.B * (int64_t) k;
+
+  for (int c = wig; c < k; c += wpp) {
+    const bool head = neg_is_head(p.sd, c);
+    const int64_t slot = i * k + c;
+    const int64_t e = p.neg_override ? p.neg_override[slot] : sample_negative(p.sd, i, c, h, t);
+    Ent N;
+    N.load(md, e, lane);
+    if (lane == 0) {
+      p.neg_ids[slot] = e;
+      if (TRAIN) { p.keys[2 * p.B + slot] = (uint32_t) e; p.vals[2 * p.B + slot] = (uint32_t)(2 * p.B + slot); }
+    }
+    const Ent& A = head ? N : H;
+    const Ent& Bq = head ? T : N;
+    const float sn = M::template forward<NV>(md, A, R, Bq, lane, x, y, sv);
+    const float w = softmax ? expf(p.loss.temperature * sn - sm_max) * sm_inv : 1.f;
+    float term, dneg, dpp;
+    loss_neg(p.loss, sp, sn, w, term, dneg, dpp);
+    lsum += term;
+    gpos += dpp;
+    if (TRAIN) {
+      Ent gA, gB;
+      Rel gR;
+      M::template backward<NV>(md, A, R, Bq, x, y, sv, dneg, lane, gA, gR, gB);
+      gA.sumsq(nrm); gB.sumsq(nrm); gR.sumsq(nrm);   // each lookup row is one IndexedSlices occurrence
+      if (head) { gA.store(md, p.rec, 2 * p.B + slot, lane); GT.add(gB); }
+      else      { gB.store(md, p.rec, 2 * p.B + slot, lane); GH.add(gA); }
+      GR.add(gR);
+    }
+  }
+
+  // d loss / d pos needs every warp's share
+  if (lane == 0) s_red[0] = gpos;
+  group_barrier(grp, wpp);
+  if (wig == 0) {
+    float gp = 0.f;
+    for (int w2 = 0; w2 < wpp; ++w2) gp += (s_red - warp * 8 + (grp * wpp + w2) * 8)[0];
+    float term, dpos;
+    loss_pos(p.loss, sp, term, dpos);
+    lsum += term;
+    gp += dpos;
+    if constexpr (M::KIND == KGE_DISTMULT) {
+      if (md.constraint) {
+        // DistMult.py:164-165: cw * mean_i sum(rel_inter[r_i]^2) — its own lookup occurrence
+        const float rr = warp_sum(row_dot_partial(R.a, R.a));
+        lsum += md.cw * rr * p.loss.inv_n;
+        if (TRAIN) {
+          Rel gReg;
+          gReg.zero();
+          row_axpy(gReg.a, 2.0f * md.cw * p.loss.inv_n, R.a);
+          gReg.sumsq(nrm);
+          GR.add(gReg);
+        }
+      }
+    }
+    if (TRAIN) {
+      M::template forward<NV>(md, H, R, T, lane, x, y, sv);
+      Ent gA, gB;
+      Rel gR;
+      M::template backward<NV>(md, H, R, T, x, y, sv, gp, lane, gA, gR, gB);
+      gA.sumsq(nrm); gB.sumsq(nrm); gR.sumsq(nrm);
+      GH.add(gA); GT.add(gB); GR.add(gR);
+    }
+  }
+
+  // ---- cross-warp reduction of the per-positive rows and partials (fixed order) ----
+  float red[N_PART];
+  red[0] = lsum;
+#pragma unroll
+  for (int q = 0; q < KGE_MAX_TABLES; ++q) red[1 + q] = TRAIN ? warp_sum(nrm[q]) : 0.f;
+  if (wpp > 1) {
+    group_barrier(grp, wpp);                // s_red[0] reads are done
+    if (lane == 0) {
+#pragma unroll
+      for (int q = 0; q < N_PART; ++q) s_red[q] = red[q];
+    }
+    if (TRAIN) {
+      GH.each([&](Row<NV>& rw, int q) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) s_acc[((q) * NV + v) * WARP + lane] = rw.v[v];
+      });
+      GT.each([&](Row<NV>& rw, int q) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) s_acc[((Ent::NROWS + q) * NV + v) * WARP + lane] = rw.v[v];
+      });
+      GR.each([&](Row<NV>& rw, int q) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) s_acc[((2 * Ent::NROWS + q) * NV + v) * WARP + lane] = rw.v[v];
+      });
+    }
+    group_barrier(grp, wpp);
+    if (wig != 0) return;
+#pragma unroll
+    for (int q = 0; q < N_PART; ++q) red[q] = 0.f;
+    for (int w2 = 0; w2 < wpp; ++w2) {
+      const float* sr = s_red + w2 * 8;
+#pragma unroll
+      for (int q = 0; q < N_PART; ++q) red[q] += sr[q];
+    }
+    if (TRAIN) {
+      GH.zero(); GT.zero(); GR.zero();
+      for (int w2 = 0; w2 < wpp; ++w2) {
+        const float4* sa = s_acc + (size_t) w2 * ACC_F4 * WARP;
+        GH.each([&](Row<NV>& rw, int q) {
+#pragma unroll
+          for (int v = 0; v < NV; ++v) rw.v[v] += sa[((q) * NV + v) * WARP + lane];
+        });
+        GT.each([&](Row<NV>& rw, int q) {
+#pragma unroll
+          for (int v = 0; v < NV; ++v) rw.v[v] += sa[((Ent::NROWS + q) * NV + v) * WARP + lane];
+        });
+        GR.each([&](Row<NV>& rw, int q) {
+#pragma unroll
+          for (int v = 0; v < NV; ++v) rw.v[v] += sa[((2 * Ent::NROWS + q) * NV + v) * WARP + lane];
+        });
+      }
+    }
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int q = 0; q < N_PART; ++q) p.part[(size_t) q * p.B + i] = red[q];
+  }
+  if (TRAIN) {
+    GH.store(md, p.rec, i, lane);
+    GT.store(md, p.rec, p.B + i, lane);
+    GR.store(md, p.rec, i, lane);
+    if (lane == 0) {
+      p.keys[i] = (uint32_t) h;           p.vals[i] = (uint32_t) i;
+      p.keys[p.B + i] = (uint32_t) t;     p.vals[p.B + i] = (uint32_t)(p.B + i);
+      p.keys[nE + i] = (uint32_t)(md.t[KGE_T_ENT].rows + r);
+      p.vals[nE + i] = (uint32_t)(nE + i);
+    }
+  }
+}
+
+}  // namespace kge

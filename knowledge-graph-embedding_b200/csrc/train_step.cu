@@ -1,0 +1,282 @@
+// train_step.cu — host side of kge_train_step / kge_sample_negatives /
+// kge_constrain_table: validation, workspace carve-up, kernel sequencing.
+// Replaces KGEModel.__run_single_batch (BaseModel.py:293-330).
+#include <cub/device/device_radix_sort.cuh>
+#include "host_common.cuh"
+#include "step_launch.cuh"
+#include "update_kernels.cuh"
+
+namespace kge {
+
+struct StepWs {
+  size_t off_part, off_scal, off_neg, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub,
+      off_rec[KGE_MAX_TABLES];
+  size_t cub_bytes, total;
+  int64_t n_ent_rec, n_keys;
+  int rld[KGE_MAX_TABLES];
+};
+
+static int sort_bits(const kge_cfg* c) {
+  uint64_t mx = (uint64_t) c->n_ent + (uint64_t) c->n_rel;
+  int b = 1;
+  while ((1ull << b) < mx && b < 32) ++b;
+  return b;
+}
+
+int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
+  const int k = k_eff_of(c);
+  int cols[KGE_MAX_TABLES];
+  expected_cols(c, cols);
+  L.n_ent_rec = 2 * B + B * (int64_t) k;
+  L.n_keys = L.n_ent_rec + B;
+  KGE_REQUIRE(L.n_keys < 0x7fffffffll, KGE_EUNSUPPORTED, "batch too large: %lld gradient records", (long long) L.n_keys);
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t at = o; o += align_up(bytes); return at; };
+  L.off_part = take(sizeof(float) * N_PART * (size_t) B);
+  L.off_scal = take(sizeof(float) * 16);
+  L.off_neg = take(sizeof(int64_t) * (size_t) B * (k > 0 ? k : 1));
+  L.off_keys_in = take(sizeof(uint32_t) * (size_t) L.n_keys);
+  L.off_keys_out = take(sizeof(uint32_t) * (size_t) L.n_keys);
+  L.off_vals_in = take(sizeof(uint32_t) * (size_t) L.n_keys);
+  L.off_vals_out = take(sizeof(uint32_t) * (size_t) L.n_keys);
+  L.cub_bytes = 0;
+  cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, L.cub_bytes, (const uint32_t*) nullptr, (uint32_t*) nullptr,
+                                                  (const uint32_t*) nullptr, (uint32_t*) nullptr, (int) L.n_keys, 0,
+                                                  sort_bits(c), (cudaStream_t) 0);
+  KGE_REQUIRE(e == cudaSuccess, KGE_ECUDA, "cub temp-size query failed: %s", cudaGetErrorString(e));
+  L.off_cub = take(L.cub_bytes);
+  for (int s = 0; s < KGE_MAX_TABLES; ++s) {
+    L.rld[s] = (cols[s] + 3) / 4 * 4;
+    const int64_t nrec = (s < 2) ? L.n_ent_rec : B;
+    L.off_rec[s] = cols[s] ? take(sizeof(float) * (size_t) nrec * L.rld[s]) : 0;
+  }
+  L.total = o;
+  return KGE_OK;
+}
+
+// constraint jobs of _constraint_loss per model
+static int constraint_jobs(const kge_cfg* c, const kge_tables* t, ConstrainParams& cp) {
+  cp.n_jobs = 0;
+  cp.total_rows = 0;
+  if (!c->constraint) return 0;
+  auto add = [&](int slot, int op) {
+    ConstrainJob& J = cp.job[cp.n_jobs++];
+    J.w = t->t[slot].w; J.rows = t->t[slot].rows; J.cols = t->t[slot].cols; J.ld = t->t[slot].ld; J.op = op;
+    cp.total_rows += J.rows;
+  };
+  switch (c->model) {
+    case KGE_UM: case KGE_SE: case KGE_TRANSE: case KGE_DISTMULT: add(KGE_T_ENT, CON_NORMALIZE); break;
+    case KGE_TRANSH: add(KGE_T_REL_B, CON_NORMALIZE); break;
+    case KGE_TRANSR: case KGE_TRANSD: add(KGE_T_ENT, CON_CLIP); add(KGE_T_REL_A, CON_CLIP); break;
+    default: break;
+  }
+  return cp.n_jobs;
+}
+
+static int launch_constrain(const kge_ctx_impl* ctx, const ConstrainParams& cp, cudaStream_t st) {
+  if (cp.n_jobs == 0) return KGE_OK;
+  int64_t blocks = (cp.total_rows + 7) / 8;
+  const int64_t cap = (int64_t) ctx->sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  k_constrain<<<(unsigned) blocks, 256, 0, st>>>(cp);
+  KGE_CUDA_OK(cudaGetLastError());
+  return KGE_OK;
+}
+
+__global__ void k_sample(SamplerDev sd, const void* triples, int id64, int64_t B, int64_t* out) {
+  const int64_t n = (int64_t) B * sd.k_eff;
+  for (int64_t s = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (int64_t) gridDim.x * blockDim.x) {
+    const int64_t i = s / sd.k_eff;
+    const int c = (int) (s - i * sd.k_eff);
+    out[s] = sample_negative(sd, i, c, load_id(triples, 3 * i, id64), load_id(triples, 3 * i + 2, id64));
+  }
+}
+
+}  // namespace kge
+
+using namespace kge;
+
+extern "C" int kge_sample_negatives(kge_ctx* ctx_, const kge_cfg* cfg, const kge_sampler* smp, const void* triples,
+                                    int64_t B, uint64_t seed, uint64_t step, int64_t* neg_out, void* stream) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
+  if (int rc = check_cfg(cfg)) return rc;
+  if (int rc = check_sampler(cfg, smp)) return rc;
+  KGE_REQUIRE(triples && neg_out && B > 0, KGE_EINVAL, "triples / neg_out / B invalid");
+  SamplerDev sd;
+  fill_sampler_dev(cfg, smp, seed, step, sd);
+  if (sd.k_eff == 0) return KGE_OK;
+  const int64_t n = B * sd.k_eff;
+  int64_t blocks = (n + 255) / 256;
+  if (blocks > (int64_t) ctx->sm_count * 16) blocks = (int64_t) ctx->sm_count * 16;
+  k_sample<<<(unsigned) blocks, 256, 0, (cudaStream_t) stream>>>(sd, triples, cfg->id_dtype, B, neg_out);
+  KGE_CUDA_OK(cudaGetLastError());
+  return KGE_OK;
+}
+
+extern "C" int kge_constrain_table(kge_ctx* ctx_, const kge_tables* t, int slot, int op, void* stream) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  KGE_REQUIRE(ctx && t, KGE_EINVAL, "ctx / tables is NULL");
+  KGE_REQUIRE(slot >= 0 && slot < KGE_MAX_TABLES && t->t[slot].w, KGE_EINVAL, "bad table slot %d", slot);
+  KGE_REQUIRE(op == CON_NORMALIZE || op == CON_CLIP, KGE_EINVAL, "bad constraint op %d", op);
+  KGE_REQUIRE(t->t[slot].ld % 4 == 0 && ((uintptr_t) t->t[slot].w & 15) == 0, KGE_EINVAL, "table not 16-byte strided");
+  ConstrainParams cp;
+  cp.n_jobs = 1;
+  cp.job[0] = ConstrainJob{t->t[slot].w, t->t[slot].rows, t->t[slot].cols, t->t[slot].ld, op};
+  cp.total_rows = t->t[slot].rows;
+  return launch_constrain(ctx, cp, (cudaStream_t) stream);
+}
+
+namespace kge {
+size_t rank_workspace_bytes(const kge_cfg* cfg, int64_t Q);   // rank.cu
+
+static int pick_wpp(int k) { return k >= 48 ? 8 : (k >= 12 ? 4 : (k >= 3 ? 2 : 1)); }
+}  // namespace kge
+
+extern "C" int kge_workspace_bytes(const kge_cfg* cfg, int64_t B, int64_t Q, size_t* out) {
+  if (int rc = check_cfg(cfg)) return rc;
+  KGE_REQUIRE(out, KGE_EINVAL, "out is NULL");
+  size_t need = 256;
+  if (B > 0) {
+    StepWs L;
+    if (int rc = layout_step_ws(cfg, B, L)) return rc;
+    need = L.total > need ? L.total : need;
+  }
+  if (Q > 0) {
+    size_t r = rank_workspace_bytes(cfg, Q);
+    need = r > need ? r : need;
+  }
+  *out = need;
+  return KGE_OK;
+}
+
+extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                              const void* triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
+                              const int64_t* neg_override, int is_train, float* loss_out, int64_t* neg_out,
+                              void* ws, size_t ws_bytes, void* stream) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  cudaStream_t st = (cudaStream_t) stream;
+  KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
+  if (int rc = check_cfg(cfg)) return rc;
+  if (int rc = check_tables(cfg, tables, is_train != 0)) return rc;
+  if (!neg_override) { if (int rc = check_sampler(cfg, smp)) return rc; }
+  KGE_REQUIRE(triples && loss_out && ws && B > 0, KGE_EINVAL, "triples / loss_out / ws / B invalid");
+  KGE_REQUIRE(cfg->loss >= KGE_LOSS_HINGE && cfg->loss <= KGE_LOSS_SQUARE, KGE_EINVAL, "bad loss id %d", cfg->loss);
+  KGE_REQUIRE(cfg->corrupt_side >= KGE_SIDE_H && cfg->corrupt_side <= KGE_SIDE_HT, KGE_EINVAL, "bad corrupt_side");
+  const int k = k_eff_of(cfg);
+  KGE_REQUIRE(k > 0, KGE_EINVAL,
+              "zero negatives per positive (corrupt_side='h+t' uses negative_ratio//2 per side, BaseModel.py:354-355)");
+  KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED,
+              "training step for matrix-relation models (SE/TransR/RESCAL) is not built yet");
+  KGE_REQUIRE(!(cfg->model == KGE_TRANSH && cfg->constraint), KGE_EUNSUPPORTED,
+              "TransH constraint=True needs the dense-regulariser pass, not built yet");
+  KGE_REQUIRE(!is_train || adam_t >= 1, KGE_EINVAL, "adam_t is 1-based");
+  const int nv = pick_nv(cfg);
+  KGE_REQUIRE(nv > 0, KGE_EUNSUPPORTED, "row wider than 1024 floats");
+
+  StepWs L;
+  if (int rc = layout_step_ws(cfg, B, L)) return rc;
+  KGE_REQUIRE(ws_bytes >= L.total, KGE_EWORKSPACE, "workspace %zu < required %zu bytes", ws_bytes, L.total);
+  KGE_REQUIRE(((uintptr_t) ws & 255) == 0, KGE_EINVAL, "workspace must be 256-byte aligned");
+  char* wsb = reinterpret_cast<char*>(ws);
+
+  // 1. start-of-batch constraint (train AND validation batches, BaseModel.py:319)
+  ConstrainParams cp;
+  constraint_jobs(cfg, tables, cp);
+  if (int rc = launch_constrain(ctx, cp, st)) return rc;
+
+  // 2. fused sample + gather + score + loss + backward
+  StepParams p;
+  fill_model_dev(cfg, tables, p.md);
+  for (int s = 0; s < KGE_MAX_TABLES; ++s) {
+    p.md.rld[s] = L.rld[s];
+    p.rec[s] = L.off_rec[s] || s == 0 ? reinterpret_cast<float*>(wsb + L.off_rec[s]) : nullptr;
+  }
+  p.loss.kind = cfg->loss;
+  p.loss.margin = cfg->margin;
+  p.loss.temperature = cfg->temperature;
+  p.loss.inv_n = 1.0f / (float) B;
+  p.loss.inv_nk = 1.0f / ((float) B * (float) k);
+  fill_sampler_dev(cfg, smp, seed, step, p.sd);
+  p.triples = triples;
+  p.id64 = cfg->id_dtype;
+  p.B = B;
+  p.k_eff = k;
+  p.wpp = pick_wpp(k);
+  p.neg_override = neg_override;
+  p.neg_ids = reinterpret_cast<int64_t*>(wsb + L.off_neg);
+  p.keys = reinterpret_cast<uint32_t*>(wsb + L.off_keys_in);
+  p.vals = reinterpret_cast<uint32_t*>(wsb + L.off_vals_in);
+  p.part = reinterpret_cast<float*>(wsb + L.off_part);
+
+  int ent_rows = (cfg->model == KGE_TRANSD) ? 2 : 1;
+  int rel_rows = (cfg->model == KGE_UM) ? 0 : ((cfg->model == KGE_TRANSH || cfg->model == KGE_TRANSD) ? 2 : 1);
+  StepLaunch SL;
+  SL.nv = nv;
+  SL.train = is_train != 0;
+  const int ppc = STEP_WARPS / p.wpp;
+  SL.grid = (B + ppc - 1) / ppc;
+  SL.smem = step_smem_bytes(nv, p.wpp, k, ent_rows, rel_rows);
+  SL.stream = st;
+  KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step needs %zu B shared memory", SL.smem);
+  int rc;
+  switch (cfg->model) {
+    case KGE_UM: rc = launch_step_um(p, SL); break;
+    case KGE_TRANSE: rc = launch_step_transe(p, SL); break;
+    case KGE_TRANSH: rc = launch_step_transh(p, SL); break;
+    case KGE_TRANSD: rc = launch_step_transd(p, SL); break;
+    case KGE_ROTATE: rc = launch_step_rotate(p, SL); break;
+    case KGE_DISTMULT: rc = launch_step_distmult(p, SL); break;
+    default: set_error("model %d has no step kernel", cfg->model); rc = KGE_EUNSUPPORTED;
+  }
+  if (rc) return rc;
+
+  // 3. loss + per-table clip scales
+  ReduceParams rp;
+  rp.part = p.part;
+  rp.B = B;
+  rp.n_part = is_train ? N_PART : 1;
+  rp.clip_norm = cfg->clip_norm;
+  rp.scal = reinterpret_cast<float*>(wsb + L.off_scal);
+  rp.loss_out = loss_out;
+  k_reduce<<<1, 1024, 0, st>>>(rp);
+  KGE_CUDA_OK(cudaGetLastError());
+  if (neg_out)
+    KGE_CUDA_OK(cudaMemcpyAsync(neg_out, p.neg_ids, sizeof(int64_t) * (size_t) B * k, cudaMemcpyDeviceToDevice, st));
+  if (!is_train) return KGE_OK;
+
+  // 4. sort records by (table, row): stable LSD radix sort => occurrence order inside a row
+  uint32_t* keys_out = reinterpret_cast<uint32_t*>(wsb + L.off_keys_out);
+  uint32_t* vals_out = reinterpret_cast<uint32_t*>(wsb + L.off_vals_out);
+  size_t cub_bytes = L.cub_bytes;
+  KGE_CUDA_OK(cub::DeviceRadixSort::SortPairs(wsb + L.off_cub, cub_bytes, (const uint32_t*) p.keys, keys_out,
+                                              (const uint32_t*) p.vals, vals_out, (int) L.n_keys, 0, sort_bits(cfg), st));
+
+  // 5. per-row segmented sum + clip + Adam (every row of every table, TF semantics)
+  UpdateParams up;
+  up.n_tabs = 0;
+  up.total_rows = 0;
+  for (int s = 0; s < KGE_MAX_TABLES; ++s) {
+    if (!tables->t[s].w) continue;
+    UpdateTable& U = up.tab[up.n_tabs++];
+    U.w = tables->t[s].w; U.m = tables->t[s].m; U.v = tables->t[s].v;
+    U.rec = p.rec[s];
+    U.rows = tables->t[s].rows; U.cols = tables->t[s].cols; U.ld = tables->t[s].ld;
+    U.rec_ld = L.rld[s];
+    U.key_base = (s < 2) ? 0u : (uint32_t) cfg->n_ent;
+    U.rec_base = (s < 2) ? 0u : (uint32_t) L.n_ent_rec;
+    U.slot = s;
+    up.total_rows += U.rows;
+  }
+  up.keys = keys_out;
+  up.vals = vals_out;
+  up.n_keys = L.n_keys;
+  up.scal = rp.scal;
+  const float b1p = powf(cfg->beta1, (float) adam_t), b2p = powf(cfg->beta2, (float) adam_t);
+  up.lr_t = cfg->lr * sqrtf(1.0f - b2p) / (1.0f - b1p);
+  up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
+  const int64_t ublocks = (up.total_rows + 7) / 8;
+  k_update<<<(unsigned) ublocks, 256, 0, st>>>(up);
+  KGE_CUDA_OK(cudaGetLastError());
+  return KGE_OK;
+}

@@ -156,7 +156,7 @@ class TransH(RefModel):
     def constraint_loss(self, W, X):
         if not self.constraint:
             return 0.0
-            W.assign("rel_hyper", O.normalized_embeddings(W.value("rel_hyper"), 2, 1, 1))
+        W.assign("rel_hyper", O.normalized_embeddings(W.value("rel_hyper"), 2, 1, 1))
         scale = O.soft_constraint(W.dense("ent_emb"), 2, 1, -1)
         rh, re_ = W.dense("rel_hyper"), W.dense("rel_emb")
         orth = torch.sum(rh * re_, dim=-1)
@@ -286,7 +286,7 @@ class DistMult(RefModel):
     def constraint_loss(self, W, X):
         if not self.constraint:
             return 0.0
-            W.assign("ent_emb", O.normalized_embeddings(W.value("ent_emb"), 2, 1, 1))
+        W.assign("ent_emb", O.normalized_embeddings(W.value("ent_emb"), 2, 1, 1))
         ri = W.lookup("rel_inter", X[:, 1])
         return self.constraint_weight * torch.mean(O.Lp_regularization(ri, 2, -1))
 
