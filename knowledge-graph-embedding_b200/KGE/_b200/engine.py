@@ -1,0 +1,171 @@
+"""Device-side state of one model and the calls into libkge_b200.so.
+
+torch is plumbing only: it owns device memory (tables, Adam slots, workspace) and the
+stream; every computation on the hot path is a kernel of the library.
+"""
+import ctypes as C
+import math
+import numpy as np
+import torch
+from . import lib as L
+
+_CTX = {}
+
+
+def _ctx(device_index):
+    if device_index not in _CTX:
+        if not torch.cuda.is_available():
+            raise RuntimeError("KGE (B200 build) needs a CUDA device: there is no CPU fallback")
+        h = C.c_void_p()
+        L.check(L.load().kge_ctx_create(device_index, C.byref(h)))
+        _CTX[device_index] = h
+    return _CTX[device_index]
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+class PaddedTable:
+    """(rows, cols) fp32 table stored with a row stride that is a multiple of 4 floats
+    (16-byte rows for 128-bit access); `view` is the logical tensor."""
+
+    def __init__(self, value, device):
+        value = torch.as_tensor(np.asarray(value) if not torch.is_tensor(value) else value,
+                                dtype=torch.float32)
+        self.shape = tuple(value.shape)
+        rows = self.shape[0]
+        cols = int(np.prod(self.shape[1:]))
+        self.rows, self.cols, self.ld = rows, cols, (cols + 3) // 4 * 4
+        self.storage = torch.zeros((rows, self.ld), dtype=torch.float32, device=device)
+        self.storage[:, :cols] = value.reshape(rows, cols).to(device)
+        self.m = None
+        self.v = None
+
+    @property
+    def view(self):
+        return self.storage[:, :self.cols].reshape(self.shape)
+
+    def ensure_slots(self):
+        if self.m is None:
+            self.m = torch.zeros_like(self.storage)
+            self.v = torch.zeros_like(self.storage)
+
+
+class Engine:
+    def __init__(self, cfg_kwargs, tables, device="cuda:0"):
+        """cfg_kwargs: fields of kge_cfg; tables: {slot: array-like}."""
+        self.device = torch.device(device)
+        self.ctx = _ctx(self.device.index or 0)
+        self.cfg = L.Cfg(abi_version=L.KGE_ABI_VERSION, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-7,
+                         clip_norm=5.0, id_dtype=1, score_p=2.0, rotate_scale=1.0)
+        for k, v in cfg_kwargs.items():
+            setattr(self.cfg, k, v)
+        self.tab = {s: PaddedTable(v, self.device) for s, v in tables.items()}
+        self.sampler = L.Sampler()
+        self._sampler_keep = []
+        self._ws = None
+        self.adam_t = 0
+
+    # ---- struct packing -----------------------------------------------------------
+    def _tables(self, with_opt):
+        T = L.Tables()
+        for s, pt in self.tab.items():
+            if with_opt:
+                pt.ensure_slots()
+            T.t[s] = L.Table(w=pt.storage.data_ptr(), m=pt.m.data_ptr() if pt.m is not None else None,
+                             v=pt.v.data_ptr() if pt.v is not None else None,
+                             rows=pt.rows, cols=pt.cols, ld=pt.ld)
+        return T
+
+    def set_uniform_pool(self, pool=None):
+        self.cfg.sampler = L.NS_UNIFORM
+        self.sampler = L.Sampler()
+        if pool is not None:
+            p = torch.as_tensor(np.asarray(pool), dtype=torch.int64).to(self.device)
+            self._sampler_keep = [p]
+            self.sampler.pool = p.data_ptr()
+            self.sampler.pool_len = p.numel()
+
+    def set_typed_pools(self, ent_type, type_off, type_members, ent_pos):
+        self.cfg.sampler = L.NS_TYPED
+        ts = [torch.as_tensor(np.asarray(a), dtype=torch.int64).to(self.device)
+              for a in (ent_type, type_off, type_members, ent_pos)]
+        self._sampler_keep = ts
+        self.sampler = L.Sampler(ent_type=ts[0].data_ptr(), type_off=ts[1].data_ptr(),
+                                 type_members=ts[2].data_ptr(), ent_pos=ts[3].data_ptr(),
+                                 n_types=ts[1].numel() - 1)
+
+    def _workspace(self, B, Q):
+        need = C.c_size_t()
+        L.check(L.load().kge_workspace_bytes(C.byref(self.cfg), B, Q, C.byref(need)))
+        if self._ws is None or self._ws.numel() < need.value:
+            self._ws = torch.empty(need.value, dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def k_eff(self):
+        k = self.cfg.negative_ratio
+        return 2 * (k // 2) if self.cfg.corrupt_side == L.SIDE_HT else k
+
+    def _ids(self, x):
+        dt = torch.int64 if self.cfg.id_dtype == 1 else torch.int32
+        if torch.is_tensor(x):
+            return x.to(device=self.device, dtype=dt).contiguous()
+        return torch.as_tensor(np.ascontiguousarray(x), dtype=dt).to(self.device)
+
+    # ---- calls ----------------------------------------------------------------------
+    def sample_negatives(self, triples, seed, step):
+        X = self._ids(triples)
+        out = torch.empty(X.shape[0] * self.k_eff(), dtype=torch.int64, device=self.device)
+        L.check(L.load().kge_sample_negatives(self.ctx, C.byref(self.cfg), C.byref(self.sampler), _ptr(X),
+                                              X.shape[0], seed, step, _ptr(out), _stream()))
+        return out
+
+    def train_step(self, triples, seed, step, is_train=True, neg_override=None, loss_out=None,
+                   want_negatives=False):
+        X = self._ids(triples)
+        B = X.shape[0]
+        ws = self._workspace(B, 0)
+        if loss_out is None:
+            loss_out = torch.empty(1, dtype=torch.float32, device=self.device)
+        neg = None
+        if neg_override is not None:
+            neg = torch.as_tensor(neg_override, dtype=torch.int64).to(self.device).contiguous()
+        neg_out = torch.empty(B * self.k_eff(), dtype=torch.int64, device=self.device) if want_negatives else None
+        if is_train:
+            self.adam_t += 1
+        T = self._tables(with_opt=bool(is_train))
+        L.check(L.load().kge_train_step(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler), _ptr(X), B,
+                                        seed, step, max(self.adam_t, 1), _ptr(neg), int(bool(is_train)),
+                                        _ptr(loss_out), _ptr(neg_out), _ptr(ws), ws.numel(), _stream()))
+        return (loss_out, neg_out) if want_negatives else loss_out
+
+    def score(self, h, r, t):
+        h, r, t = self._ids(h), self._ids(r), self._ids(t)
+        out = torch.empty(h.numel(), dtype=torch.float32, device=self.device)
+        T = self._tables(False)
+        L.check(L.load().kge_score(self.ctx, C.byref(self.cfg), C.byref(T), _ptr(h), _ptr(r), _ptr(t),
+                                   h.numel(), _ptr(out), _stream()))
+        return out
+
+    def constrain_table(self, slot, op):
+        T = self._tables(False)
+        L.check(L.load().kge_constrain_table(self.ctx, C.byref(T), slot, op, _stream()))
+
+    def rank_counts(self, queries, side, f_off=None, f_ids=None, ent_lo=0, ent_hi=None):
+        Qx = self._ids(queries)
+        Q = Qx.shape[0]
+        cnt = torch.zeros(Q, dtype=torch.int32, device=self.device)
+        ws = self._workspace(0, Q)
+        flt = L.Filter()
+        if f_off is not None:
+            flt.off, flt.ids = f_off.data_ptr(), f_ids.data_ptr()
+        T = self._tables(False)
+        L.check(L.load().kge_rank(self.ctx, C.byref(self.cfg), C.byref(T), _ptr(Qx), Q, side, C.byref(flt),
+                                  ent_lo, self.cfg.n_ent if ent_hi is None else ent_hi, _ptr(cnt), _ptr(ws),
+                                  ws.numel(), _stream()))
+        return cnt

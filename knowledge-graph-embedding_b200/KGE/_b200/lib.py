@@ -1,0 +1,95 @@
+"""ctypes binding of libkge_b200.so (include/kge_abi.h).  No CPU fallback: a missing
+library or a failing call raises."""
+import ctypes as C
+import os
+
+KGE_ABI_VERSION = 1
+KGE_MAX_TABLES = 4
+(UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
+SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
+LOSS_HINGE, LOSS_LOGISTIC, LOSS_BCE, LOSS_SELF_ADV, LOSS_SQUARE = range(5)
+SIDE_H, SIDE_T, SIDE_HT = 0, 1, 2
+NS_UNIFORM, NS_TYPED = 0, 1
+T_ENT, T_ENT_PROJ, T_REL_A, T_REL_B = range(4)
+CON_NORMALIZE, CON_CLIP = 0, 1
+
+
+class Table(C.Structure):
+    _fields_ = [("w", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p),
+                ("rows", C.c_int64), ("cols", C.c_int32), ("ld", C.c_int32)]
+
+
+class Tables(C.Structure):
+    _fields_ = [("t", Table * KGE_MAX_TABLES)]
+
+
+class Cfg(C.Structure):
+    _fields_ = [("abi_version", C.c_int32), ("model", C.c_int32), ("score", C.c_int32),
+                ("loss", C.c_int32), ("sampler", C.c_int32), ("corrupt_side", C.c_int32),
+                ("negative_ratio", C.c_int32), ("constraint", C.c_int32), ("id_dtype", C.c_int32),
+                ("d_ent", C.c_int32), ("d_rel", C.c_int32), ("reserved", C.c_int32),
+                ("score_p", C.c_float), ("margin", C.c_float), ("temperature", C.c_float),
+                ("constraint_weight", C.c_float), ("lr", C.c_float), ("beta1", C.c_float),
+                ("beta2", C.c_float), ("eps", C.c_float), ("clip_norm", C.c_float),
+                ("rotate_scale", C.c_float), ("n_ent", C.c_int64), ("n_rel", C.c_int64)]
+
+
+class Sampler(C.Structure):
+    _fields_ = [("pool", C.c_void_p), ("pool_len", C.c_int64), ("ent_type", C.c_void_p),
+                ("type_off", C.c_void_p), ("type_members", C.c_void_p), ("ent_pos", C.c_void_p),
+                ("n_types", C.c_int64)]
+
+
+class Filter(C.Structure):
+    _fields_ = [("off", C.c_void_p), ("ids", C.c_void_p)]
+
+
+SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destroy",
+           "kge_workspace_bytes", "kge_sample_negatives", "kge_score", "kge_constrain_table",
+           "kge_train_step", "kge_rank"]
+
+_LIB = None
+
+
+def lib_path():
+    here = os.path.dirname(os.path.abspath(__file__))
+    return os.environ.get("KGE_B200_LIB",
+                          os.path.normpath(os.path.join(here, "..", "..", "lib", "libkge_b200.so")))
+
+
+def load():
+    """dlopen the library and declare prototypes. Raises if it is missing."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = lib_path()
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} not found: build it with __graft_entry__.build() "
+                           "(KGE has no CPU fallback)")
+    L = C.CDLL(path)
+    vp, i64, u64, i32 = C.c_void_p, C.c_int64, C.c_uint64, C.c_int
+    L.kge_abi_version.restype = i32
+    L.kge_last_error.restype = C.c_char_p
+    L.kge_ctx_create.argtypes = [i32, C.POINTER(vp)]
+    L.kge_ctx_destroy.argtypes = [vp]
+    L.kge_workspace_bytes.argtypes = [C.POINTER(Cfg), i64, i64, C.POINTER(C.c_size_t)]
+    L.kge_sample_negatives.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Sampler), vp, i64, u64, u64, vp, vp]
+    L.kge_score.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp, vp, vp, i64, vp, vp]
+    L.kge_constrain_table.argtypes = [vp, C.POINTER(Tables), i32, i32, vp]
+    L.kge_train_step.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), vp, i64,
+                                 u64, u64, u64, vp, i32, vp, vp, vp, C.c_size_t, vp]
+    L.kge_rank.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp, i64, i32, C.POINTER(Filter),
+                           i64, i64, vp, vp, C.c_size_t, vp]
+    for s in SYMBOLS:
+        getattr(L, s)
+        if s not in ("kge_last_error",):
+            getattr(L, s).restype = i32
+    if L.kge_abi_version() != KGE_ABI_VERSION:
+        raise RuntimeError("libkge_b200 ABI version mismatch")
+    _LIB = L
+    return L
+
+
+def check(rc):
+    if rc != 0:
+        raise RuntimeError("libkge_b200: " + load().kge_last_error().decode() + f" (code {rc})")

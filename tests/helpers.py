@@ -1,0 +1,32 @@
+"""Shared builders for parity tests: the same model/score/loss spec instantiated as the
+CPU oracle and as the CUDA engine."""
+import numpy as np
+import torch
+from oracle import ref_ops as O, ref_models as RM, ref_step as RS, philox
+
+
+def make_pair(model, N, R, d, d_rel=None, score=None, loss=None, k=2, side="h+t", constraint=True,
+              cw=1.0, seed=7):
+    from KGE._b200 import engine as E, spec
+    cls = RM.MODELS[model]
+    ref = cls(N, R, d, d_rel, score_fn=score, loss_fn=loss, constraint=constraint, constraint_weight=cw)
+    W = ref.init_weights(seed)
+    cfg = spec.make_cfg(model, N, R, d, d_rel, score_fn=score, loss_fn=loss, negative_ratio=k,
+                        corrupt_side=side, constraint=constraint, constraint_weight=cw,
+                        rotate_limit=ref.limit)
+    eng = E.Engine(cfg, {spec.SLOTS[model][kk]: v for kk, v in W.data.items()})
+    return ref, W, eng
+
+
+def tables_of(eng, model):
+    from KGE._b200 import spec
+    return {k: eng.tab[s].view.detach().cpu() for k, s in spec.SLOTS[model].items()}
+
+
+def rand_triples(rng, n, N, R):
+    return np.stack([rng.integers(0, N, n), rng.integers(0, R, n), rng.integers(0, N, n)], 1).astype(np.int64)
+
+
+def rel_err(a, b):
+    a, b = torch.as_tensor(a).double(), torch.as_tensor(b).double()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-12))
