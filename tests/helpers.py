@@ -30,3 +30,15 @@ def rand_triples(rng, n, N, R):
 def rel_err(a, b):
     a, b = torch.as_tensor(a).double(), torch.as_tensor(b).double()
     return float((a - b).abs().max() / (b.abs().max() + 1e-12))
+
+
+def assert_weights_close(got, want, lr, steps, where=""):
+    """Adam divides by sqrt(v): where a summed gradient cancels to ~1e-6 the update
+    lr*g/(|g|+eps') amplifies 1e-7 summation-order noise to a fraction of lr.  So: all
+    elements within steps*lr (Adam's per-step bound), and all but 1% within 1e-4 relative."""
+    got, want = torch.as_tensor(got).double(), torch.as_tensor(want).double()
+    diff = (got - want).abs()
+    scale = float(want.abs().max()) + 1e-12
+    assert float(diff.max()) <= steps * lr * 1.01 + 1e-6 * scale, (where, float(diff.max()))
+    frac = float((diff > 1e-4 * scale).double().mean())
+    assert frac < 0.01, (where, frac, float(diff.max()))

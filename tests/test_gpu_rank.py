@@ -1,0 +1,70 @@
+"""GPU parity of filtered ranking (kge_rank) against the oracle's get_rank
+(BaseModel.py:620-654).  Ranks must match exactly, except where the oracle's own
+candidate score is within 1e-5 relative of the true triple's score (documented ties)."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import make_pair, rand_triples
+from oracle import ref_ops as O, ref_step as RS
+from test_gpu_step import SCORES, LOSSES, VECTOR_MODELS, _score_for
+
+pytestmark = pytest.mark.gpu
+N, R = 257, 9
+
+
+def _check(model, score, side, filtered, d=50, d_rel=None, Q=40):
+    from KGE._b200.filter import build_filter
+    rng = np.random.default_rng(2)
+    ref, W, eng = make_pair(model, N, R, d, d_rel, score=_score_for(model, score), loss=LOSSES["hinge"])
+    pos = rand_triples(rng, 4000, N, R)
+    Xq = pos[:Q].copy()
+    Xq[::3] = rand_triples(rng, len(Xq[::3]), N, R)        # some queries not in positive_X
+    off = ids = None
+    if filtered:
+        off, ids = build_filter(pos, Xq, side, N, eng.device)
+    cnt = eng.rank_counts(Xq, 0 if side == "h" else 1, off, ids).cpu().numpy()
+    for q, x in enumerate(Xq):
+        want = RS.get_rank(ref, W, x, pos if filtered else None, side)
+        if cnt[q] + 1 != want:
+            s = RS.get_scores_all(ref, W, x, side)
+            with torch.no_grad():
+                one = lambda v: torch.tensor([int(v)])
+                p = float(ref.score_hrt(W, one(x[0]), one(x[1]), one(x[2]))[0])
+            near = int(((s - p).abs() <= 1e-5 * max(1.0, abs(p))).sum())
+            assert abs(int(cnt[q]) + 1 - want) <= near, (model, q, int(cnt[q]) + 1, want, near)
+
+
+@pytest.mark.parametrize("model", VECTOR_MODELS)
+@pytest.mark.parametrize("side", ["h", "t"])
+@pytest.mark.parametrize("filtered", [False, True])
+def test_rank_matches_oracle(model, side, filtered):
+    score = {"UM": "l2pow", "TransE": "l1", "TransH": "l2pow", "TransD": "l2pow", "RotatE": "l1",
+             "DistMult": "dot"}[model]
+    _check(model, score, side, filtered, d=50 if model != "RotatE" else 21)
+
+
+@pytest.mark.parametrize("score", ["l2", "linf", "dot"])
+def test_rank_transe_scores(score):
+    _check("TransE", score, "t", True, d=33)
+
+
+def test_filtered_rank_not_worse_than_raw():
+    """tests/test_model.py:46-49 invariant."""
+    from KGE._b200.filter import build_filter
+    rng = np.random.default_rng(4)
+    ref, W, eng = make_pair("TransE", N, R, 16, score=SCORES["l2"], loss=LOSSES["hinge"])
+    pos = rand_triples(rng, 3000, N, R)
+    off, ids = build_filter(pos, pos[:64], "h", N, eng.device)
+    raw = eng.rank_counts(pos[:64], 0).cpu().numpy()
+    flt = eng.rank_counts(pos[:64], 0, off, ids).cpu().numpy()
+    assert (flt <= raw).all() and (flt >= 0).all()
+
+
+def test_entity_shards_sum_to_full():
+    rng = np.random.default_rng(6)
+    ref, W, eng = make_pair("DistMult", N, R, 40, loss=LOSSES["bce"])
+    Xq = rand_triples(rng, 33, N, R)
+    full = eng.rank_counts(Xq, 1).cpu()
+    parts = sum(eng.rank_counts(Xq, 1, ent_lo=lo, ent_hi=hi).cpu() for lo, hi in [(0, 100), (100, 101), (101, N)])
+    assert torch.equal(full, parts)
