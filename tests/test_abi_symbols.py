@@ -1,0 +1,53 @@
+"""The C-ABI library loads on a CPU-only box and exports every symbol include/kge_abi.h
+declares; compute entry points fail loudly (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "kge_abi.h")).read()
+    return sorted(set(re.findall(r"^(?:int|const char\*) (kge_[a-z_]+)\(", src, re.M)))
+
+
+def test_library_exports_every_declared_symbol():
+    from KGE._b200 import lib
+    L = lib.load()
+    names = _declared()
+    assert set(names) == set(lib.SYMBOLS)
+    for n in names:
+        assert getattr(L, n) is not None
+    assert L.kge_abi_version() == lib.KGE_ABI_VERSION
+
+
+def test_struct_sizes_match_header():
+    from KGE._b200 import lib
+    assert C.sizeof(lib.Table) == 40 and C.sizeof(lib.Tables) == 160
+    assert C.sizeof(lib.Cfg) == 12 * 4 + 10 * 4 + 2 * 8
+    assert C.sizeof(lib.Sampler) == 56 and C.sizeof(lib.Filter) == 16
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from KGE._b200 import lib
+    L = lib.load()
+    h = C.c_void_p()
+    rc = L.kge_ctx_create(0, C.byref(h))
+    assert rc == -3 and b"no CPU fallback" in L.kge_last_error()
+    from KGE._b200 import engine
+    with pytest.raises(RuntimeError):
+        engine.Engine({"model": 2, "n_ent": 4, "n_rel": 2, "d_ent": 4, "d_rel": 4}, {})
+
+
+def test_bad_cfg_is_rejected_without_gpu():
+    from KGE._b200 import lib
+    L = lib.load()
+    cfg = lib.Cfg(abi_version=99)
+    n = C.c_size_t()
+    assert L.kge_workspace_bytes(C.byref(cfg), 1, 0, C.byref(n)) == -1
+    assert b"abi_version" in L.kge_last_error()
