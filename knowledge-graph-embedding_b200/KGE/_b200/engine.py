@@ -169,3 +169,13 @@ class Engine:
                                   ent_lo, self.cfg.n_ent if ent_hi is None else ent_hi, _ptr(cnt), _ptr(ws),
                                   ws.numel(), _stream()))
         return cnt
+
+    def profile_begin(self, max_calls):
+        L.check(L.load().kge_profile_begin(self.ctx, max_calls))
+
+    def profile_end(self):
+        """-> ({phase: summed ms}, n_calls)"""
+        ms = (C.c_float * L.N_PHASES)()
+        n = C.c_int()
+        L.check(L.load().kge_profile_end(self.ctx, ms, C.byref(n)))
+        return {L.PHASES[i]: float(ms[i]) for i in range(L.N_PHASES)}, n.value

@@ -37,7 +37,44 @@ extern "C" int kge_ctx_create(int device, kge_ctx** out) {
   *out = reinterpret_cast<kge_ctx*>(c);
   return KGE_OK;
 }
+static void free_events(kge_ctx_impl* c) {
+  if (c->ev) {
+    for (int i = 0; i < c->prof_cap * 2 * KGE_N_PHASES; ++i) cudaEventDestroy(c->ev[i]);
+    delete[] c->ev; delete[] c->ev_mask;
+    c->ev = nullptr; c->ev_mask = nullptr; c->prof_cap = c->prof_n = 0;
+  }
+}
 extern "C" int kge_ctx_destroy(kge_ctx* ctx) {
-  delete reinterpret_cast<kge_ctx_impl*>(ctx);
+  auto* c = reinterpret_cast<kge_ctx_impl*>(ctx);
+  if (c) free_events(c);
+  delete c;
+  return KGE_OK;
+}
+extern "C" int kge_profile_begin(kge_ctx* ctx, int max_calls) {
+  auto* c = reinterpret_cast<kge_ctx_impl*>(ctx);
+  KGE_REQUIRE(c && max_calls > 0 && max_calls <= (1 << 16), KGE_EINVAL, "bad profile_begin arguments");
+  free_events(c);
+  c->ev = new cudaEvent_t[(size_t) max_calls * 2 * KGE_N_PHASES];
+  c->ev_mask = new unsigned[max_calls];
+  for (int i = 0; i < max_calls * 2 * KGE_N_PHASES; ++i) KGE_CUDA_OK(cudaEventCreate(&c->ev[i]));
+  c->prof_cap = max_calls;
+  c->prof_n = 0;
+  return KGE_OK;
+}
+extern "C" int kge_profile_end(kge_ctx* ctx, float* phase_ms, int* n_calls) {
+  auto* c = reinterpret_cast<kge_ctx_impl*>(ctx);
+  KGE_REQUIRE(c && phase_ms && n_calls, KGE_EINVAL, "bad profile_end arguments");
+  KGE_REQUIRE(c->ev, KGE_EINVAL, "kge_profile_begin was not called");
+  KGE_CUDA_OK(cudaDeviceSynchronize());
+  for (int p = 0; p < KGE_N_PHASES; ++p) phase_ms[p] = 0.f;
+  for (int s = 0; s < c->prof_n; ++s)
+    for (int p = 0; p < KGE_N_PHASES; ++p)
+      if (c->ev_mask[s] & (1u << p)) {
+        float ms = 0.f;
+        KGE_CUDA_OK(cudaEventElapsedTime(&ms, c->ev[s * 2 * KGE_N_PHASES + 2 * p], c->ev[s * 2 * KGE_N_PHASES + 2 * p + 1]));
+        phase_ms[p] += ms;
+      }
+  *n_calls = c->prof_n;
+  free_events(c);
   return KGE_OK;
 }

@@ -30,6 +30,21 @@ struct kge_ctx_impl {
   int device;
   int sm_count;
   int smem_optin;
+  // optional per-phase timing: ev[call][0..KGE_N_PHASES] boundaries, mask of phases hit
+  cudaEvent_t* ev = nullptr;
+  unsigned* ev_mask = nullptr;
+  int prof_cap = 0, prof_n = 0;
+};
+// RAII marker: records the boundary events of one call when profiling is on
+struct PhaseTimer {
+  kge_ctx_impl* c; cudaStream_t st; int slot;
+  PhaseTimer(kge_ctx_impl* c_, cudaStream_t s) : c(c_), st(s), slot(-1) {
+    if (c->ev && c->prof_n < c->prof_cap) { slot = c->prof_n++; c->ev_mask[slot] = 0; }
+  }
+  void begin(int phase) { if (slot >= 0) cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + 2 * phase], st); }
+  void end(int phase) {
+    if (slot >= 0) { cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + 2 * phase + 1], st); c->ev_mask[slot] |= 1u << phase; }
+  }
 };
 
 // ---- warp reductions (fixed butterfly order: deterministic) ---------------------

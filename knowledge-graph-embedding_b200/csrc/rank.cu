@@ -65,6 +65,8 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
   int chunk = 2048;
   while (chunk > 256 && Q * ((span + chunk - 1) / chunk) < (int64_t) ctx->sm_count * 8) chunk >>= 1;
   p.chunk = chunk;
+  PhaseTimer pt(ctx, (cudaStream_t) stream);
+  pt.begin(5);
   const int64_t QMAX = 65535;    // gridDim.y limit
   for (int64_t q0 = 0; q0 < Q; q0 += QMAX) {
     const int64_t qn = (Q - q0 < QMAX) ? Q - q0 : QMAX;
@@ -86,5 +88,6 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
     }
     if (rc) return rc;
   }
+  pt.end(5);
   return KGE_OK;
 }

@@ -181,9 +181,12 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   char* wsb = reinterpret_cast<char*>(ws);
 
   // 1. start-of-batch constraint (train AND validation batches, BaseModel.py:319)
+  PhaseTimer pt(ctx, st);
   ConstrainParams cp;
   constraint_jobs(cfg, tables, cp);
+  pt.begin(0);
   if (int rc = launch_constrain(ctx, cp, st)) return rc;
+  pt.end(0);
 
   // 2. fused sample + gather + score + loss + backward
   StepParams p;
@@ -220,6 +223,7 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   SL.stream = st;
   KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step needs %zu B shared memory", SL.smem);
   int rc;
+  pt.begin(1);
   switch (cfg->model) {
     case KGE_UM: rc = launch_step_um(p, SL); break;
     case KGE_TRANSE: rc = launch_step_transe(p, SL); break;
@@ -230,6 +234,7 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
     default: set_error("model %d has no step kernel", cfg->model); rc = KGE_EUNSUPPORTED;
   }
   if (rc) return rc;
+  pt.end(1);
 
   // 3. loss + per-table clip scales
   ReduceParams rp;
@@ -239,8 +244,10 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   rp.clip_norm = cfg->clip_norm;
   rp.scal = reinterpret_cast<float*>(wsb + L.off_scal);
   rp.loss_out = loss_out;
+  pt.begin(2);
   k_reduce<<<1, 1024, 0, st>>>(rp);
   KGE_CUDA_OK(cudaGetLastError());
+  pt.end(2);
   if (neg_out)
     KGE_CUDA_OK(cudaMemcpyAsync(neg_out, p.neg_ids, sizeof(int64_t) * (size_t) B * k, cudaMemcpyDeviceToDevice, st));
   if (!is_train) return KGE_OK;
@@ -249,8 +256,10 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   uint32_t* keys_out = reinterpret_cast<uint32_t*>(wsb + L.off_keys_out);
   uint32_t* vals_out = reinterpret_cast<uint32_t*>(wsb + L.off_vals_out);
   size_t cub_bytes = L.cub_bytes;
+  pt.begin(3);
   KGE_CUDA_OK(cub::DeviceRadixSort::SortPairs(wsb + L.off_cub, cub_bytes, (const uint32_t*) p.keys, keys_out,
                                               (const uint32_t*) p.vals, vals_out, (int) L.n_keys, 0, sort_bits(cfg), st));
+  pt.end(3);
 
   // 5. per-row segmented sum + clip + Adam (every row of every table, TF semantics)
   UpdateParams up;
@@ -276,7 +285,9 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   up.lr_t = cfg->lr * sqrtf(1.0f - b2p) / (1.0f - b1p);
   up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
   const int64_t ublocks = (up.total_rows + 7) / 8;
+  pt.begin(4);
   k_update<<<(unsigned) ublocks, 256, 0, st>>>(up);
   KGE_CUDA_OK(cudaGetLastError());
+  pt.end(4);
   return KGE_OK;
 }
