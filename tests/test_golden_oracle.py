@@ -1,0 +1,193 @@
+"""Pins the CPU oracle to the golden vectors produced by the reference's own source
+(tests/golden/make_golden.py: /root/reference/KGE executed over oracle/tf_shim).
+CPU-only; the GPU twin is tests/test_gpu_golden.py."""
+import glob
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_ops as O, ref_models as RM, ref_step as RS, philox
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CASES = sorted(os.path.basename(p)[5:-4] for p in glob.glob(os.path.join(GOLD, "case_*.npz")))
+TOL = 1e-4          # north_star: scores and losses within 1e-4 relative in fp32
+
+
+def close(a, b, tol=TOL):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    np.testing.assert_allclose(a, b, rtol=tol, atol=tol * max(1.0, float(np.abs(b).max()) if b.size else 1.0))
+
+
+def T(a):
+    return torch.as_tensor(np.asarray(a))
+
+
+SCORES = {"l1": lambda: O.LpDistance(1), "l2": lambda: O.LpDistance(2), "linf": lambda: O.LpDistance(math.inf),
+          "l2pow": lambda: O.LpDistancePow(2), "dot": lambda: O.Dot(), "None": lambda: None}
+LOSSES = {"hinge": lambda: O.PairwiseHingeLoss(1.0), "logistic": lambda: O.PairwiseLogisticLoss(),
+          "bce": lambda: O.BinaryCrossEntropyLoss(),
+          "selfadv": lambda: O.SelfAdversarialNegativeSamplingLoss(3.0, 1.0), "square": lambda: O.SquareErrorLoss()}
+
+
+def test_golden_files_present():
+    assert len(CASES) >= 17 and os.path.exists(os.path.join(GOLD, "ops.npz"))
+
+
+def test_scores_losses_constraints():
+    g = np.load(os.path.join(GOLD, "ops.npz"))
+    x, y, xi, yi = T(g["x"]), T(g["y"]), T(g["xi"]), T(g["yi"])
+    fns = {"lp1": O.LpDistance(1), "lp2": O.LpDistance(2), "lp3": O.LpDistance(3), "lpinf": O.LpDistance(math.inf),
+           "lppow2": O.LpDistancePow(2), "lppow1": O.LpDistancePow(1), "dot": O.Dot()}
+    for name, fn in fns.items():
+        close(fn(x, y), g["score_" + name])
+        if name != "dot":
+            close(fn((x, xi), (y, yi)), g["cscore_" + name])
+    pos, neg = T(g["pos"]), T(g["neg"])
+    for name, fn in {"hinge": O.PairwiseHingeLoss(1.0), "hinge3": O.PairwiseHingeLoss(3.0),
+                     "logistic": O.PairwiseLogisticLoss(), "bce": O.BinaryCrossEntropyLoss(),
+                     "selfadv": O.SelfAdversarialNegativeSamplingLoss(3.0, 1.0),
+                     "selfadv2": O.SelfAdversarialNegativeSamplingLoss(1.5, 0.5),
+                     "square": O.SquareErrorLoss()}.items():
+        close(fn(pos, neg), g["loss_" + name])
+    X = T(g["X"])
+    for p, tag in [(1, "1"), (2, "2"), (math.inf, "inf")]:
+        close(O.normalized_embeddings(X, p, 1.0, -1), g["norm_p" + tag], 1e-6)
+        close(O.clip_constraint(X, p, 1.0, -1), g["clip_p" + tag], 1e-6)
+    close(O.soft_constraint(X, 2, 1.0, -1), g["soft_p2"])
+    close(O.Lp_regularization(X, 2, -1), g["lpreg_p2"])
+    close(O.Lp_regularization(X, 3, -1), g["lpreg_p3"])
+
+
+def load_case(name):
+    g = np.load(os.path.join(GOLD, "case_%s.npz" % name))
+    model, sc, ls, k, side, con, cw, d, dr = [str(v) for v in g["spec"]]
+    spec = dict(model=model, score=sc, loss=ls, k=int(k), side=side, constraint=(con == "True"), cw=float(cw),
+                d=int(d), dr=int(dr))
+    return g, spec
+
+
+def oracle_model(spec, n_ent=40, n_rel=5):
+    return RM.MODELS[spec["model"]](n_ent, n_rel, spec["d"], spec["dr"], score_fn=SCORES[spec["score"]](),
+                                    loss_fn=LOSSES[spec["loss"]](), constraint=spec["constraint"],
+                                    constraint_weight=spec["cw"])
+
+
+def weights(g, prefix):
+    return {k[len(prefix):]: T(g[k]).float() for k in g.files if k.startswith(prefix)}
+
+
+def neg_ids_from_triples(X, neg, side):
+    """reference (B*k_eff, 3) negative triples -> entity ids + layout check (BaseModel.py:332-408)."""
+    B = len(X)
+    k_eff = len(neg) // B
+    c = np.arange(len(neg)) % k_eff
+    is_h = np.ones_like(c, bool) if side == "h" else (np.zeros_like(c, bool) if side == "t" else c % 2 == 0)
+    rep = np.repeat(X, k_eff, axis=0)
+    assert np.array_equal(neg[:, 1], rep[:, 1])
+    assert np.array_equal(neg[~is_h, 0], rep[~is_h, 0]) and np.array_equal(neg[is_h, 2], rep[is_h, 2])
+    return np.where(is_h, neg[:, 0], neg[:, 2]), k_eff
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_score_hrt(name):
+    g, spec = load_case(name)
+    m = oracle_model(spec)
+    m.limit = getattr(m, "limit", None)
+    W = RM.Weights(weights(g, "w0_"))
+    X = T(g["score_X"])
+    with torch.no_grad():
+        close(m.score_hrt(W, X[:, 0], X[:, 1], X[:, 2]), g["score_batch"])
+    close(RS.get_scores_all(m, W, g["score_X"][0], "h"), g["score_all_h"])
+    close(RS.get_scores_all(m, W, g["score_X"][0], "t"), g["score_all_t"])
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_run_single_batch_sequence(name):
+    g, spec = load_case(name)
+    m = oracle_model(spec)
+    W = RM.Weights(weights(g, "w0_"))
+    opt = RS.TFAdam()
+    for step in range(len(g["step_X"])):
+        X, neg = g["step_X"][step], g["step_neg"][step]
+        ids, k_eff = neg_ids_from_triples(X, neg, spec["side"])
+        # the stored negatives are the shared Philox stream (bit-exact)
+        want_ids, ke2 = philox.negatives(4242, step, X, spec["k"], spec["side"], 40)
+        assert ke2 == k_eff and np.array_equal(ids, want_ids)
+        loss, _ = RS.run_single_batch(m, W, opt, X, ids, k_eff, spec["side"], bool(g["step_is_train"][step]))
+        assert abs(loss - g["step_loss"][step]) <= TOL * max(1.0, abs(g["step_loss"][step])), (step, loss)
+        if step == 0:
+            for k, v in weights(g, "w1_").items():
+                close(W.data[k], v)
+    for k, v in weights(g, "wT_").items():
+        close(W.data[k], v)
+
+
+def near_ties(m, W, x, side):
+    """candidates whose score is within 1e-5 relative of the true triple's: the documented
+    tie band (north_star; SURVEY.md C.6 — the reference scores the true triple on a separate
+    scalar path, so an ulp can move the count)."""
+    sc = RS.get_scores_all(m, W, x, side)
+    p = float(sc[int(x[0 if side == "h" else 2])])
+    return int(((sc - p).abs() <= 1e-5 * max(1.0, abs(p))).sum())
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_ranks_and_metrics(name):
+    g, spec = load_case(name)
+    m = oracle_model(spec)
+    W = RM.Weights(weights(g, "wT_"))
+    pos, ev = g["rank_pos"], g["rank_X"]
+    for s in ("h", "t"):
+        for tag, P in (("raw", None), ("flt", pos)):
+            for q, x in enumerate(ev):
+                got, want = RS.get_rank(m, W, x, P, s), int(g["rank_%s_%s" % (tag, s)][q])
+                assert abs(got - want) <= near_ties(m, W, x, s), (tag, s, q, got, want)
+        assert (g["rank_flt_" + s] <= g["rank_raw_" + s]).all()          # tests/test_model.py:46-49
+    res, ranks = RS.evaluate(m, W, ev, "t", pos)
+    assert list(res.keys()) == [str(k) for k in g["eval_keys"]]
+    if ranks == list(g["rank_flt_t"]):
+        close(list(res.values()), g["eval_vals"], 1e-9)
+    close(list(RS.metrics(g["rank_flt_t"]).values()), g["eval_vals"], 1e-9)      # KGE/metrics.py on the same ranks
+
+
+def test_typed_sampler_invariants():
+    """tests/test_ns_strategy.py:52-53,61-62 on the reference's output and on our stream."""
+    g = np.load(os.path.join(GOLD, "typed.npz"))
+    ind2type, X = g["ind2type"], g["X"]
+    pools = philox.TypedPools(ind2type=list(ind2type))
+    for side, col in (("h", 0), ("t", 2)):
+        ref_neg = g["neg_" + side].reshape(len(X), 5)
+        ours = philox.sample_typed(11, 0, side, X, 5, pools).reshape(len(X), 5)
+        for arr in (ref_neg, ours):
+            assert (ind2type[arr] == ind2type[X[:, col]][:, None]).all()
+            assert (arr != X[:, col][:, None]).all()
+    # same support: over many draws our sampler reaches exactly pool-minus-self
+    x = int(X[0, 0])
+    want = set(np.flatnonzero(ind2type == ind2type[x])) - {x}
+    got = set()
+    for step in range(40):
+        got |= set(philox.sample_typed(3, step, "h", X[:1], 8, pools).tolist())
+    assert got == want
+
+
+def test_full_train_loop_matches_reference():
+    """train() (2 epochs incl. validation batches) + evaluate(): BaseModel.py:58-190, 578-618."""
+    g = np.load(os.path.join(GOLD, "train_loop_transh.npz"))
+    d, k, bs, epochs, seed = [int(v) for v in g["cfg"]]
+    m = RM.TransH(40, 5, d, d, score_fn=O.LpDistancePow(2), loss_fn=O.PairwiseHingeLoss(1.0), constraint=False)
+    W = RM.Weights(weights(g, "w0_"))
+    opt = RS.TFAdam()
+    n_train_batches = math.ceil(len(g["train"]) / bs)
+    assert int(g["is_train"].sum()) == epochs * n_train_batches
+    for step, X in enumerate(g["batches"]):
+        ids, k_eff = philox.negatives(seed, step, X, k, "h+t", 40)
+        loss, _ = RS.run_single_batch(m, W, opt, X, ids, k_eff, "h+t", bool(g["is_train"][step]))
+        assert abs(loss - g["loss"][step]) <= TOL * max(1.0, abs(g["loss"][step])), step
+    for kk, v in weights(g, "wT_").items():
+        close(W.data[kk], v)
+    res, _ = RS.evaluate(m, W, g["val"], "h", np.concatenate([g["train"], g["val"]]))
+    close(list(res.values()), g["eval_vals"], 1e-9)
