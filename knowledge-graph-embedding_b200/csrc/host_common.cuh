@@ -104,6 +104,12 @@ inline int pick_nv(const kge_cfg* c) {
   return 0;
 }
 
+// strided layout of the matrix models: 128 floats per NV
+inline int pick_nv_strided(const kge_cfg* c) {
+  const int mx = c->d_ent > c->d_rel ? c->d_ent : c->d_rel;
+  return mx <= 128 ? 1 : (mx <= 256 ? 2 : 0);
+}
+
 inline int k_eff_of(const kge_cfg* c) {
   return c->corrupt_side == KGE_SIDE_HT ? 2 * (c->negative_ratio / 2) : c->negative_ratio;
 }

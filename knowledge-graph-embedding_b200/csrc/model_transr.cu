@@ -1,0 +1,12 @@
+// model_transr.cu — kernel instantiations for MTransR (step_mat_kernels.cuh, rank_mat_kernels.cuh).
+#include "step_mat_launch.cuh"
+#include "rank_mat_kernels.cuh"
+namespace kge {
+int launch_step_transr(const MatStepParams& q, const StepLaunch& L) { return launch_step_mat_model<MTransR>(q, L); }
+int launch_score_transr(const ScoreParams& p, const AuxLaunch& L, const MatAux& a, size_t smem) {
+  return launch_score_mat_model<MTransR>(p, L, a, smem);
+}
+int launch_rank_transr(const RankParams& p, const AuxLaunch& L, const MatAux& a, size_t smem) {
+  return launch_rank_mat_model<MTransR>(p, L, a, smem);
+}
+}  // namespace kge

@@ -1,6 +1,7 @@
 // rank.cu — host side of kge_score and kge_rank.
 #include "host_common.cuh"
 #include "rank_kernels.cuh"
+#include "rank_mat_kernels.cuh"
 
 namespace kge {
 size_t rank_workspace_bytes(const kge_cfg*, int64_t) { return 256; }
@@ -14,16 +15,27 @@ extern "C" int kge_score(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* ta
   if (int rc = check_cfg(cfg)) return rc;
   if (int rc = check_tables(cfg, tables, false)) return rc;
   KGE_REQUIRE(h && r && t && out && n > 0, KGE_EINVAL, "h / r / t / out / n invalid");
-  KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED, "matrix-relation models (SE/TransR/RESCAL) not built yet");
   ScoreParams p;
   fill_model_dev(cfg, tables, p.md);
   p.h = h; p.r = r; p.t = t; p.id64 = cfg->id_dtype; p.n = n; p.out = out;
   AuxLaunch L;
-  L.nv = pick_nv(cfg);
+  const bool mat = is_matrix_model(cfg->model);
+  L.nv = mat ? pick_nv_strided(cfg) : pick_nv(cfg);
   int64_t blocks = (n + 7) / 8;
   if (blocks > (int64_t) ctx->sm_count * 16) blocks = (int64_t) ctx->sm_count * 16;
   L.grid = dim3((unsigned) blocks);
   L.stream = (cudaStream_t) stream;
+  if (mat) {
+    KGE_REQUIRE(L.nv > 0, KGE_EUNSUPPORTED, "matrix models support embedding sizes up to 256");
+    MatAux a;
+    a.dpad = 128 * L.nv; a.stage = 0;
+    const size_t smem = sizeof(float) * 8 * (size_t) a.dpad;
+    switch (cfg->model) {
+      case KGE_SE: return launch_score_se(p, L, a, smem);
+      case KGE_TRANSR: return launch_score_transr(p, L, a, smem);
+      default: return launch_score_rescal(p, L, a, smem);
+    }
+  }
   switch (cfg->model) {
     case KGE_UM: return launch_score_um(p, L);
     case KGE_TRANSE: return launch_score_transe(p, L);
@@ -48,8 +60,8 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
   KGE_REQUIRE(0 <= ent_lo && ent_lo < ent_hi && ent_hi <= cfg->n_ent, KGE_EINVAL, "bad entity shard [%lld, %lld)",
               (long long) ent_lo, (long long) ent_hi);
   KGE_REQUIRE(!filter || !filter->off || filter->ids, KGE_EINVAL, "filter.off given without filter.ids");
-  KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED, "matrix-relation models (SE/TransR/RESCAL) not built yet");
   (void) ws; (void) ws_bytes;
+  const bool mat = is_matrix_model(cfg->model);
   RankParams p;
   fill_model_dev(cfg, tables, p.md);
   p.queries = queries; p.id64 = cfg->id_dtype; p.Q = Q; p.side = side;
@@ -58,8 +70,19 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
   p.ent_lo = ent_lo; p.ent_hi = ent_hi;
   p.count = count_out;
   AuxLaunch L;
-  L.nv = pick_nv(cfg);
+  L.nv = mat ? pick_nv_strided(cfg) : pick_nv(cfg);
+  KGE_REQUIRE(L.nv > 0, KGE_EUNSUPPORTED, "embedding size too large for the rank kernel");
   L.stream = (cudaStream_t) stream;
+  MatAux ma;
+  size_t msmem = 0;
+  if (mat) {
+    ma.dpad = 128 * L.nv;
+    const int mr = cfg->d_ent, mc = cfg->model == KGE_TRANSR ? cfg->d_rel : cfg->d_ent;
+    const size_t base = sizeof(float) * RANK_WARPS * (size_t) ma.dpad;
+    const size_t staged = base + sizeof(float) * (size_t) (cfg->model == KGE_SE ? 2 : 1) * mr * (mc | 1);
+    ma.stage = staged <= (size_t) ctx->smem_optin;
+    msmem = ma.stage ? staged : base;
+  }
   const int64_t span = ent_hi - ent_lo;
   // enough CTAs per query to fill the machine, at least 64 candidates per warp pass
   int chunk = 2048;
@@ -78,6 +101,9 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
     L.grid = dim3((unsigned) ((span + chunk - 1) / chunk), (unsigned) qn);
     int rc;
     switch (cfg->model) {
+      case KGE_SE: rc = launch_rank_se(pp, L, ma, msmem); break;
+      case KGE_TRANSR: rc = launch_rank_transr(pp, L, ma, msmem); break;
+      case KGE_RESCAL: rc = launch_rank_rescal(pp, L, ma, msmem); break;
       case KGE_UM: rc = launch_rank_um(pp, L); break;
       case KGE_TRANSE: rc = launch_rank_transe(pp, L); break;
       case KGE_TRANSH: rc = launch_rank_transh(pp, L); break;

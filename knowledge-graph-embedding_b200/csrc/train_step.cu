@@ -5,15 +5,18 @@
 #include "host_common.cuh"
 #include "step_launch.cuh"
 #include "update_kernels.cuh"
+#include "update_mat_kernels.cuh"
+#include "step_mat_launch.cuh"
 
 namespace kge {
 
 struct StepWs {
   size_t off_part, off_scal, off_neg, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub,
-      off_rec[KGE_MAX_TABLES];
+      off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart;
   size_t cub_bytes, total;
-  int64_t n_ent_rec, n_keys;
+  int64_t n_ent_rec, n_keys, total_rows, n_mat_cta;
   int rld[KGE_MAX_TABLES];
+  int ldp;
 };
 
 static int sort_bits(const kge_cfg* c) {
@@ -21,6 +24,25 @@ static int sort_bits(const kge_cfg* c) {
   int b = 1;
   while ((1ull << b) < mx && b < 32) ++b;
   return b;
+}
+
+// which table slots hold per-relation matrices (updated by k_update_mat, not k_update)
+static bool is_matrix_slot(const kge_cfg* c, int s) {
+  switch (c->model) {
+    case KGE_SE: return s == KGE_T_REL_A || s == KGE_T_REL_B;
+    case KGE_TRANSR: return s == KGE_T_REL_B;
+    case KGE_RESCAL: return s == KGE_T_REL_A;
+    default: return false;
+  }
+}
+// dense regulariser on every row: TransH.py:204-211, RESCAL.py:191-198
+static bool has_dense_reg(const kge_cfg* c) {
+  return c->constraint && (c->model == KGE_TRANSH || c->model == KGE_RESCAL);
+}
+static int mat_rows(const kge_cfg* c) { return c->d_ent; }
+static int mat_cols(const kge_cfg* c) { return c->model == KGE_TRANSR ? c->d_rel : c->d_ent; }
+static int mat_tiles(const kge_cfg* c) {
+  return ((mat_rows(c) + MU_TILE - 1) / MU_TILE) * ((mat_cols(c) + MU_TILE - 1) / MU_TILE);
 }
 
 int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
@@ -45,10 +67,29 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
                                                   sort_bits(c), (cudaStream_t) 0);
   KGE_REQUIRE(e == cudaSuccess, KGE_ECUDA, "cub temp-size query failed: %s", cudaGetErrorString(e));
   L.off_cub = take(L.cub_bytes);
+  L.total_rows = 0;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     L.rld[s] = (cols[s] + 3) / 4 * 4;
     const int64_t nrec = (s < 2) ? L.n_ent_rec : B;
-    L.off_rec[s] = cols[s] ? take(sizeof(float) * (size_t) nrec * L.rld[s]) : 0;
+    const bool vec = cols[s] && !is_matrix_slot(c, s);
+    L.off_rec[s] = vec ? take(sizeof(float) * (size_t) nrec * L.rld[s]) : 0;
+    if (vec) L.total_rows += (s < 2) ? c->n_ent : c->n_rel;
+  }
+  L.ldp = 0; L.off_recP = 0; L.n_mat_cta = 0;
+  if (is_matrix_model(c->model)) {
+    L.ldp = (mat_cols(c) > mat_rows(c) ? mat_cols(c) : mat_rows(c));
+    L.ldp = (L.ldp + 3) / 4 * 4;
+    L.off_recP = take(sizeof(float) * (size_t) L.n_ent_rec * L.ldp);
+    L.n_mat_cta = (int64_t) mat_tiles(c) * c->n_rel * (c->model == KGE_SE ? 2 : 1);
+  }
+  L.off_snap[0] = L.off_snap[1] = L.off_rowpart = L.off_matpart = 0;
+  if (has_dense_reg(c)) {
+    if (c->model == KGE_TRANSH) {
+      L.off_snap[0] = take(sizeof(float) * (size_t) c->n_rel * L.rld[KGE_T_REL_A]);
+      L.off_snap[1] = take(sizeof(float) * (size_t) c->n_rel * L.rld[KGE_T_REL_B]);
+    }
+    L.off_rowpart = take(sizeof(float) * 2 * (size_t) L.total_rows);
+    if (L.n_mat_cta) L.off_matpart = take(sizeof(float) * 2 * (size_t) L.n_mat_cta);
   }
   L.total = o;
   return KGE_OK;
@@ -166,19 +207,18 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   const int k = k_eff_of(cfg);
   KGE_REQUIRE(k > 0, KGE_EINVAL,
               "zero negatives per positive (corrupt_side='h+t' uses negative_ratio//2 per side, BaseModel.py:354-355)");
-  KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED,
-              "training step for matrix-relation models (SE/TransR/RESCAL) is not built yet");
-  KGE_REQUIRE(!(cfg->model == KGE_TRANSH && cfg->constraint), KGE_EUNSUPPORTED,
-              "TransH constraint=True needs the dense-regulariser pass, not built yet");
   KGE_REQUIRE(!is_train || adam_t >= 1, KGE_EINVAL, "adam_t is 1-based");
-  const int nv = pick_nv(cfg);
-  KGE_REQUIRE(nv > 0, KGE_EUNSUPPORTED, "row wider than 1024 floats");
+  const bool mat = is_matrix_model(cfg->model);
+  const int nv = mat ? pick_nv_strided(cfg) : pick_nv(cfg);
+  KGE_REQUIRE(nv > 0, KGE_EUNSUPPORTED, mat ? "matrix models support embedding sizes up to 256" : "row wider than 1024 floats");
 
   StepWs L;
   if (int rc = layout_step_ws(cfg, B, L)) return rc;
   KGE_REQUIRE(ws_bytes >= L.total, KGE_EWORKSPACE, "workspace %zu < required %zu bytes", ws_bytes, L.total);
   KGE_REQUIRE(((uintptr_t) ws & 255) == 0, KGE_EINVAL, "workspace must be 256-byte aligned");
   char* wsb = reinterpret_cast<char*>(ws);
+  int cols[KGE_MAX_TABLES];
+  expected_cols(cfg, cols);
 
   // 1. start-of-batch constraint (train AND validation batches, BaseModel.py:319)
   PhaseTimer pt(ctx, st);
@@ -189,11 +229,12 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   pt.end(0);
 
   // 2. fused sample + gather + score + loss + backward
-  StepParams p;
+  MatStepParams mq;
+  StepParams& p = mq.s;
   fill_model_dev(cfg, tables, p.md);
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     p.md.rld[s] = L.rld[s];
-    p.rec[s] = L.off_rec[s] || s == 0 ? reinterpret_cast<float*>(wsb + L.off_rec[s]) : nullptr;
+    p.rec[s] = (cols[s] && !is_matrix_slot(cfg, s)) ? reinterpret_cast<float*>(wsb + L.off_rec[s]) : nullptr;
   }
   p.loss.kind = cfg->loss;
   p.loss.margin = cfg->margin;
@@ -205,38 +246,56 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   p.id64 = cfg->id_dtype;
   p.B = B;
   p.k_eff = k;
-  p.wpp = pick_wpp(k);
+  p.wpp = mat ? STEP_WARPS : pick_wpp(k);
   p.neg_override = neg_override;
   p.neg_ids = reinterpret_cast<int64_t*>(wsb + L.off_neg);
   p.keys = reinterpret_cast<uint32_t*>(wsb + L.off_keys_in);
   p.vals = reinterpret_cast<uint32_t*>(wsb + L.off_vals_in);
   p.part = reinterpret_cast<float*>(wsb + L.off_part);
 
-  int ent_rows = (cfg->model == KGE_TRANSD) ? 2 : 1;
-  int rel_rows = (cfg->model == KGE_UM) ? 0 : ((cfg->model == KGE_TRANSH || cfg->model == KGE_TRANSD) ? 2 : 1);
   StepLaunch SL;
   SL.nv = nv;
   SL.train = is_train != 0;
-  const int ppc = STEP_WARPS / p.wpp;
-  SL.grid = (B + ppc - 1) / ppc;
-  SL.smem = step_smem_bytes(nv, p.wpp, k, ent_rows, rel_rows);
   SL.stream = st;
-  KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step needs %zu B shared memory", SL.smem);
   int rc;
-  pt.begin(1);
-  switch (cfg->model) {
-    case KGE_UM: rc = launch_step_um(p, SL); break;
-    case KGE_TRANSE: rc = launch_step_transe(p, SL); break;
-    case KGE_TRANSH: rc = launch_step_transh(p, SL); break;
-    case KGE_TRANSD: rc = launch_step_transd(p, SL); break;
-    case KGE_ROTATE: rc = launch_step_rotate(p, SL); break;
-    case KGE_DISTMULT: rc = launch_step_distmult(p, SL); break;
-    default: set_error("model %d has no step kernel", cfg->model); rc = KGE_EUNSUPPORTED;
+  if (!mat) {
+    int ent_rows = (cfg->model == KGE_TRANSD) ? 2 : 1;
+    int rel_rows = (cfg->model == KGE_UM) ? 0 : ((cfg->model == KGE_TRANSH || cfg->model == KGE_TRANSD) ? 2 : 1);
+    const int ppc = STEP_WARPS / p.wpp;
+    SL.grid = (B + ppc - 1) / ppc;
+    SL.smem = step_smem_bytes(nv, p.wpp, k, ent_rows, rel_rows);
+    KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step needs %zu B shared memory", SL.smem);
+    pt.begin(1);
+    switch (cfg->model) {
+      case KGE_UM: rc = launch_step_um(p, SL); break;
+      case KGE_TRANSE: rc = launch_step_transe(p, SL); break;
+      case KGE_TRANSH: rc = launch_step_transh(p, SL); break;
+      case KGE_TRANSD: rc = launch_step_transd(p, SL); break;
+      case KGE_ROTATE: rc = launch_step_rotate(p, SL); break;
+      case KGE_DISTMULT: rc = launch_step_distmult(p, SL); break;
+      default: set_error("model %d has no step kernel", cfg->model); rc = KGE_EUNSUPPORTED;
+    }
+  } else {
+    mq.recP = reinterpret_cast<float*>(wsb + L.off_recP);
+    mq.ldp = L.ldp;
+    mq.dpad = 128 * nv;
+    const int n_mats = cfg->model == KGE_SE ? 2 : 1;
+    SL.grid = B;
+    SL.smem = step_mat_smem_bytes(nv, k, mq.dpad, SL.train, true, n_mats, mat_rows(cfg), mat_cols(cfg));
+    mq.stage = SL.smem <= (size_t) ctx->smem_optin;
+    if (!mq.stage) SL.smem = step_mat_smem_bytes(nv, k, mq.dpad, SL.train, false, n_mats, mat_rows(cfg), mat_cols(cfg));
+    KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step_mat needs %zu B shared memory", SL.smem);
+    pt.begin(1);
+    switch (cfg->model) {
+      case KGE_SE: rc = launch_step_se(mq, SL); break;
+      case KGE_TRANSR: rc = launch_step_transr(mq, SL); break;
+      default: rc = launch_step_rescal(mq, SL);
+    }
   }
   if (rc) return rc;
   pt.end(1);
 
-  // 3. loss + per-table clip scales
+  // 3. loss + per-table clip scales (sparse-gradient tables)
   ReduceParams rp;
   rp.part = p.part;
   rp.B = B;
@@ -250,24 +309,29 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   pt.end(2);
   if (neg_out)
     KGE_CUDA_OK(cudaMemcpyAsync(neg_out, p.neg_ids, sizeof(int64_t) * (size_t) B * k, cudaMemcpyDeviceToDevice, st));
-  if (!is_train) return KGE_OK;
+  const bool dense = has_dense_reg(cfg);
+  if (!is_train && !dense) return KGE_OK;
 
   // 4. sort records by (table, row): stable LSD radix sort => occurrence order inside a row
   uint32_t* keys_out = reinterpret_cast<uint32_t*>(wsb + L.off_keys_out);
   uint32_t* vals_out = reinterpret_cast<uint32_t*>(wsb + L.off_vals_out);
-  size_t cub_bytes = L.cub_bytes;
-  pt.begin(3);
-  KGE_CUDA_OK(cub::DeviceRadixSort::SortPairs(wsb + L.off_cub, cub_bytes, (const uint32_t*) p.keys, keys_out,
-                                              (const uint32_t*) p.vals, vals_out, (int) L.n_keys, 0, sort_bits(cfg), st));
-  pt.end(3);
+  if (is_train) {
+    size_t cub_bytes = L.cub_bytes;
+    pt.begin(3);
+    KGE_CUDA_OK(cub::DeviceRadixSort::SortPairs(wsb + L.off_cub, cub_bytes, (const uint32_t*) p.keys, keys_out,
+                                                (const uint32_t*) p.vals, vals_out, (int) L.n_keys, 0, sort_bits(cfg), st));
+    pt.end(3);
+  }
 
   // 5. per-row segmented sum + clip + Adam (every row of every table, TF semantics)
   UpdateParams up;
   up.n_tabs = 0;
   up.total_rows = 0;
+  ReduceDenseParams rd;
+  rd.row_begin[0] = 0;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
-    if (!tables->t[s].w) continue;
-    UpdateTable& U = up.tab[up.n_tabs++];
+    if (!cols[s] || is_matrix_slot(cfg, s)) continue;
+    UpdateTable& U = up.tab[up.n_tabs];
     U.w = tables->t[s].w; U.m = tables->t[s].m; U.v = tables->t[s].v;
     U.rec = p.rec[s];
     U.rows = tables->t[s].rows; U.cols = tables->t[s].cols; U.ld = tables->t[s].ld;
@@ -275,18 +339,90 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
     U.key_base = (s < 2) ? 0u : (uint32_t) cfg->n_ent;
     U.rec_base = (s < 2) ? 0u : (uint32_t) L.n_ent_rec;
     U.slot = s;
+    U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
+    if (dense) {
+      if (cfg->model == KGE_RESCAL) U.dense_kind = DK_RESCAL_ENT;
+      else if (s == KGE_T_ENT) U.dense_kind = DK_TRANSH_ENT;
+      else {
+        U.dense_kind = (s == KGE_T_REL_A) ? DK_TRANSH_REL : DK_TRANSH_HYPER;
+        U.other_w = reinterpret_cast<const float*>(wsb + L.off_snap[s == KGE_T_REL_A ? 1 : 0]);
+        U.other_ld = L.rld[s == KGE_T_REL_A ? KGE_T_REL_B : KGE_T_REL_A];
+      }
+    }
+    rd.slot[up.n_tabs] = s;
+    rd.is_dense[up.n_tabs] = U.dense_kind != DK_NONE;
     up.total_rows += U.rows;
+    rd.row_begin[++up.n_tabs] = up.total_rows;
   }
   up.keys = keys_out;
   up.vals = vals_out;
-  up.n_keys = L.n_keys;
+  up.n_keys = is_train ? L.n_keys : 0;
   up.scal = rp.scal;
   const float b1p = powf(cfg->beta1, (float) adam_t), b2p = powf(cfg->beta2, (float) adam_t);
   up.lr_t = cfg->lr * sqrtf(1.0f - b2p) / (1.0f - b1p);
   up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
+  up.cw = cfg->constraint_weight;
+  up.rowpart = dense ? reinterpret_cast<float*>(wsb + L.off_rowpart) : nullptr;
   const int64_t ublocks = (up.total_rows + 7) / 8;
+
+  MatUpdParams mu;
+  dim3 mgrid(1, 1, 1);
+  if (mat) {
+    mu.n_tabs = 0;
+    auto add = [&](int slot, int sh, int st_, int neg_mode, int er_sh, int er_st, int er_neg) {
+      MatUpdTable& T = mu.tab[mu.n_tabs++];
+      T.w = tables->t[slot].w; T.m = tables->t[slot].m; T.v = tables->t[slot].v;
+      T.rows_m = mat_rows(cfg); T.cols_m = mat_cols(cfg); T.ld = tables->t[slot].ld; T.slot = slot;
+      T.use_sh = sh; T.use_st = st_; T.neg_mode = neg_mode;
+      T.ent_row_sh = er_sh; T.ent_row_st = er_st; T.ent_row_neg = er_neg;
+    };
+    if (cfg->model == KGE_TRANSR) add(KGE_T_REL_B, 1, 1, 1, 1, 1, 1);          // G += ent (x) P
+    else if (cfg->model == KGE_SE) { add(KGE_T_REL_A, 1, 0, 2, 0, 0, 0); add(KGE_T_REL_B, 0, 1, 3, 0, 0, 0); }   // G += P (x) ent
+    else add(KGE_T_REL_A, 1, 1, 0, 1, 0, 0);                                    // h (x) P  +  P (x) t
+    mu.n_rel = cfg->n_rel;
+    mu.ent_w = tables->t[KGE_T_ENT].w; mu.ent_ld = tables->t[KGE_T_ENT].ld; mu.d_ent = cfg->d_ent;
+    mu.recP = mq.recP; mu.ldp = L.ldp; mu.dp = mat_cols(cfg);
+    mu.triples = triples; mu.id64 = cfg->id_dtype; mu.neg_ids = p.neg_ids;
+    mu.B = B; mu.k = k; mu.side_mode = cfg->corrupt_side;
+    mu.keys = keys_out; mu.vals = vals_out; mu.n_keys = is_train ? L.n_keys : 0;
+    mu.key_base = (uint32_t) cfg->n_ent; mu.rec_base = (uint32_t) L.n_ent_rec;
+    mu.scal = rp.scal; mu.lr_t = up.lr_t; mu.beta1 = cfg->beta1; mu.beta2 = cfg->beta2; mu.eps = cfg->eps;
+    mu.reg_coef = (dense && cfg->model == KGE_RESCAL) ? 2.0f * cfg->constraint_weight / (float) cfg->n_rel : 0.f;
+    mu.part = dense ? reinterpret_cast<float*>(wsb + L.off_matpart) : nullptr;
+    mgrid = dim3((unsigned) mat_tiles(cfg), (unsigned) cfg->n_rel, (unsigned) mu.n_tabs);
+    KGE_REQUIRE(cfg->n_rel <= 65535, KGE_EUNSUPPORTED, "matrix models: n_rel must be <= 65535");
+  }
+
   pt.begin(4);
-  k_update<<<(unsigned) ublocks, 256, 0, st>>>(up);
+  if (dense) {
+    // densified gradients: norm pass, reduce, then apply  (tf.clip_by_norm on a dense tensor)
+    if (cfg->model == KGE_TRANSH)
+      for (int j = 0; j < 2; ++j) {
+        const kge_table& S = tables->t[j == 0 ? KGE_T_REL_A : KGE_T_REL_B];
+        KGE_CUDA_OK(cudaMemcpy2DAsync(wsb + L.off_snap[j], sizeof(float) * L.rld[j == 0 ? KGE_T_REL_A : KGE_T_REL_B], S.w,
+                                      sizeof(float) * S.ld, sizeof(float) * L.rld[j == 0 ? KGE_T_REL_A : KGE_T_REL_B],
+                                      (size_t) S.rows, cudaMemcpyDeviceToDevice, st));
+      }
+    k_update<1><<<(unsigned) ublocks, 256, 0, st>>>(up);
+    KGE_CUDA_OK(cudaGetLastError());
+    rd.rowpart = up.rowpart; rd.total_rows = up.total_rows; rd.n_tabs = up.n_tabs;
+    rd.matpart = nullptr; rd.n_mat = 0; rd.mat_slot = KGE_T_REL_A; rd.mat_loss_coef = 0.f;
+    if (mat) {
+      k_update_mat<1><<<mgrid, MU_THREADS, 0, st>>>(mu);
+      KGE_CUDA_OK(cudaGetLastError());
+      rd.matpart = mu.part; rd.n_mat = L.n_mat_cta; rd.mat_loss_coef = cfg->constraint_weight / (float) cfg->n_rel;
+    }
+    rd.clip_norm = cfg->clip_norm; rd.write_scales = is_train != 0; rd.scal = rp.scal; rd.loss_out = loss_out;
+    k_reduce_dense<<<1, 1024, 0, st>>>(rd);
+    KGE_CUDA_OK(cudaGetLastError());
+    if (!is_train) { pt.end(4); return KGE_OK; }
+  }
+  if (mat) {      // reads the pre-update entity rows: must precede k_update
+    k_update_mat<0><<<mgrid, MU_THREADS, 0, st>>>(mu);
+    KGE_CUDA_OK(cudaGetLastError());
+  }
+  if (dense) k_update<2><<<(unsigned) ublocks, 256, 0, st>>>(up);
+  else k_update<0><<<(unsigned) ublocks, 256, 0, st>>>(up);
   KGE_CUDA_OK(cudaGetLastError());
   pt.end(4);
   return KGE_OK;

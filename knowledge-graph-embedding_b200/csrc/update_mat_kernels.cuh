@@ -1,0 +1,164 @@
+// update_mat_kernels.cuh — per-relation matrix gradient + TF-semantics Adam for the
+// matrix tables of SE / TransR / RESCAL.
+//
+// grid = (tiles, n_rel, n_tables); a CTA owns one 64x64 tile of one relation's matrix:
+//   G_tile = sum over the relation's positives (sorted, stable => occurrence order) and
+//            their pair slots of  rowvec (x) colvec           (grouped small GEMM, K = #pairs)
+//   then   g = clip_scale * (G + dense_reg);  m,v,w <- Adam     (EVERY relation: Keras Adam
+//   decays/moves all rows).
+// MODE 1 (norm pass, only for dense-regulariser models) writes sum((G + reg)^2) and the
+// regulariser's loss term per CTA instead of updating.  No atomics: deterministic.
+#pragma once
+#include "update_kernels.cuh"
+
+namespace kge {
+
+constexpr int MU_TILE = 64, MU_KC = 8, MU_THREADS = 256;
+
+struct MatUpdTable {
+  float *w, *m, *v;
+  int rows_m, cols_m;      // matrix dims (row-major inside the table row)
+  int ld;                  // table row stride (floats)
+  int slot;                // kge table slot (index into scal)
+  int use_sh, use_st;      // shared-h / shared-t pair slots feed this table
+  int neg_mode;            // per-negative pair slots: 0 none, 1 all, 2 head-corrupted, 3 tail-corrupted
+  int ent_row_sh, ent_row_st, ent_row_neg;   // 1: entity row indexes matrix rows (P indexes columns)
+};
+
+struct MatUpdParams {
+  MatUpdTable tab[2];
+  int n_tabs;
+  int64_t n_rel;
+  const float* ent_w; int ent_ld, d_ent;
+  const float* recP; int ldp, dp;
+  const void* triples; int id64;
+  const int64_t* neg_ids;
+  int64_t B; int k, side_mode;
+  const uint32_t* keys; const uint32_t* vals; int64_t n_keys;
+  uint32_t key_base, rec_base;      // relation keys are key_base + r; vals - rec_base = positive index
+  const float* scal;
+  float lr_t, beta1, beta2, eps;
+  float reg_coef;                   // dense regulariser: g += reg_coef * w   (RESCAL.py:191-198), 0 = none
+  float* part;                      // MODE 1: [2][n_tabs * n_rel * tiles] (norm^2, sum w^2)
+};
+
+// number of per-negative slots of table T for one positive, and the c of the j-th
+__device__ __forceinline__ int mu_neg_count(int neg_mode, int side_mode, int k) {
+  if (neg_mode == 0) return 0;
+  if (neg_mode == 1) return k;
+  const bool want_head = (neg_mode == 2);
+  if (side_mode == KGE_SIDE_HT) return k / 2;
+  return ((side_mode == KGE_SIDE_H) == want_head) ? k : 0;
+}
+__device__ __forceinline__ int mu_neg_c(int neg_mode, int side_mode, int j) {
+  if (neg_mode == 1 || side_mode != KGE_SIDE_HT) return j;
+  return 2 * j + (neg_mode == 2 ? 0 : 1);       // 'h+t': even c = head corruption
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p) {
+  __shared__ float s_row[MU_KC][MU_TILE];
+  __shared__ float s_col[MU_KC][MU_TILE];
+  __shared__ float s_red[2][MU_THREADS / 32];
+  const MatUpdTable& T = p.tab[blockIdx.z];
+  const int64_t r = blockIdx.y;
+  const int tiles_c = (T.cols_m + MU_TILE - 1) / MU_TILE;
+  const int tr = blockIdx.x / tiles_c, tc = blockIdx.x % tiles_c;
+  if (tr * MU_TILE >= T.rows_m) return;
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+  const int row0 = tr * MU_TILE, col0 = tc * MU_TILE;
+
+  const uint32_t key = p.key_base + (uint32_t) r;
+  const int64_t lo = lower_bound_u32(p.keys, p.n_keys, key);
+  const int64_t hi = lower_bound_u32(p.keys, p.n_keys, key + 1);
+  const int n_neg = mu_neg_count(T.neg_mode, p.side_mode, p.k);
+  const int S = T.use_sh + T.use_st + n_neg;
+  const int64_t n_pairs = (hi - lo) * S;
+
+  float acc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+
+  for (int64_t u0 = 0; u0 < n_pairs; u0 += MU_KC) {
+    // stage MU_KC pairs: 2 * MU_KC * 64 floats by 256 threads
+    for (int e = threadIdx.x; e < 2 * MU_KC * MU_TILE; e += MU_THREADS) {
+      const int which = e / (MU_KC * MU_TILE);            // 0 row vectors, 1 column vectors
+      const int kk = (e / MU_TILE) % MU_KC, off = e % MU_TILE;
+      const int64_t u = u0 + kk;
+      float val = 0.f;
+      if (u < n_pairs) {
+        const int64_t pos = (int64_t) (__ldg(p.vals + lo + u / S) - p.rec_base);
+        int s = (int) (u % S);
+        int64_t rec, ent; int ent_row;
+        if (T.use_sh && s == 0) { rec = pos; ent = load_id(p.triples, 3 * pos, p.id64); ent_row = T.ent_row_sh; }
+        else if (T.use_st && s == T.use_sh) { rec = p.B + pos; ent = load_id(p.triples, 3 * pos + 2, p.id64); ent_row = T.ent_row_st; }
+        else {
+          const int c = mu_neg_c(T.neg_mode, p.side_mode, s - T.use_sh - T.use_st);
+          rec = 2 * p.B + pos * p.k + c; ent = __ldg(p.neg_ids + pos * p.k + c); ent_row = T.ent_row_neg;
+        }
+        const bool from_ent = (which == 0) == (ent_row != 0);
+        const int idx = (which == 0 ? row0 : col0) + off;
+        const int lim = which == 0 ? T.rows_m : T.cols_m;
+        if (idx < lim)
+          val = from_ent ? __ldg(p.ent_w + ent * (int64_t) p.ent_ld + idx) : __ldg(p.recP + rec * (int64_t) p.ldp + idx);
+      }
+      (which == 0 ? s_row : s_col)[kk][off] = val;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < MU_KC; ++kk) {
+      float a4[4], b4[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) { a4[a] = s_row[kk][ty * 4 + a]; b4[a] = s_col[kk][tx * 4 + a]; }
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(a4[a], b4[b], acc[a][b]);
+    }
+    __syncthreads();
+  }
+
+  float* wr = T.w + r * (int64_t) T.ld;
+  float* mr = T.m + r * (int64_t) T.ld;
+  float* vr = T.v + r * (int64_t) T.ld;
+  const float scale = (MODE == 0) ? p.scal[T.slot] : 1.f;
+  float n2 = 0.f, w2 = 0.f;
+#pragma unroll
+  for (int a = 0; a < 4; ++a) {
+    const int ra = row0 + ty * 4 + a;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int cb = col0 + tx * 4 + b;
+      if (ra < T.rows_m && cb < T.cols_m) {
+        const int64_t o = (int64_t) ra * T.cols_m + cb;
+        float w = wr[o];
+        float g = acc[a][b] + p.reg_coef * w;
+        if (MODE == 1) { n2 += g * g; w2 += w * w; }
+        else {
+          g *= scale;
+          float m = p.beta1 * mr[o] + (1.f - p.beta1) * g;
+          float v = p.beta2 * vr[o] + (1.f - p.beta2) * g * g;
+          mr[o] = m; vr[o] = v;
+          wr[o] = w - p.lr_t * m / (sqrtf(v) + p.eps);
+        }
+      }
+    }
+  }
+  if (MODE == 1) {
+    warp_sum2(n2, w2);
+    if ((threadIdx.x & 31) == 0) { s_red[0][threadIdx.x >> 5] = n2; s_red[1][threadIdx.x >> 5] = w2; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float a = 0.f, b = 0.f;
+      for (int w2i = 0; w2i < MU_THREADS / 32; ++w2i) { a += s_red[0][w2i]; b += s_red[1][w2i]; }
+      const int64_t n_cta = (int64_t) gridDim.x * gridDim.y * gridDim.z;
+      const int64_t me = ((int64_t) blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+      p.part[me] = a;
+      p.part[n_cta + me] = b;
+    }
+  }
+}
+
+}  // namespace kge
