@@ -11,6 +11,13 @@ def make_pair(model, N, R, d, d_rel=None, score=None, loss=None, k=2, side="h+t"
     cls = RM.MODELS[model]
     ref = cls(N, R, d, d_rel, score_fn=score, loss_fn=loss, constraint=constraint, constraint_weight=cw)
     W = ref.init_weights(seed)
+    if model == "TransR":
+        # The reference initialises rel_proj to the identity (TransR.py:125-128).  With start-of-batch
+        # clipping ||e|| == 1 +- 1 ulp, so ||e I|| sits exactly ON the clip threshold of TransR.py:187-189
+        # and which branch is taken is decided by rounding: the reference function itself is
+        # discontinuous there.  Parity is tested away from that knife edge.
+        g = torch.Generator().manual_seed(seed + 1)
+        W.data["rel_proj"] = W.data["rel_proj"] + (torch.rand(W.data["rel_proj"].shape, generator=g) - 0.5) * 0.2
     cfg = spec.make_cfg(model, N, R, d, d_rel, score_fn=score, loss_fn=loss, negative_ratio=k,
                         corrupt_side=side, constraint=constraint, constraint_weight=cw,
                         rotate_limit=ref.limit)

@@ -68,3 +68,10 @@ def test_entity_shards_sum_to_full():
     full = eng.rank_counts(Xq, 1).cpu()
     parts = sum(eng.rank_counts(Xq, 1, ent_lo=lo, ent_hi=hi).cpu() for lo, hi in [(0, 100), (100, 101), (101, N)])
     assert torch.equal(full, parts)
+
+
+@pytest.mark.parametrize("model,score,d,dr", [("SE", "l1", 24, 24), ("TransR", "l2pow", 40, 24), ("RESCAL", "dot", 32, 32),
+                                              ("TransR", "l2pow", 160, 160)])
+@pytest.mark.parametrize("side", ["h", "t"])
+def test_rank_matrix_models(model, score, d, dr, side):
+    _check(model, score if model != "RESCAL" else "dot", side, True, d=d, d_rel=dr, Q=16)

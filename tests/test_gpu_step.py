@@ -23,7 +23,7 @@ VECTOR_MODELS = ["UM", "TransE", "TransH", "TransD", "RotatE", "DistMult"]
 
 
 def _score_for(model, name):
-    return None if model == "DistMult" else SCORES[name]
+    return None if model in ("DistMult", "RESCAL") else SCORES[name]
 
 
 @pytest.mark.parametrize("model", VECTOR_MODELS)
@@ -128,3 +128,103 @@ def test_negatives_override_is_used():
     l_gpu, neg = eng.train_step(X, 0, 0, neg_override=ids, want_negatives=True)
     assert np.array_equal(neg.cpu().numpy(), ids)
     assert abs(float(l_gpu.item()) - l_ref) <= 1e-4 * max(1.0, abs(l_ref))
+
+
+# ---- matrix-relation models and dense regularisers ----------------
+MATRIX_DEFAULTS = {"SE": ("l1", "hinge"), "TransR": ("l2pow", "hinge"), "RESCAL": ("dot", "square")}
+
+
+def _score_mat(model, name):
+    return None if model == "RESCAL" else SCORES[name]
+
+
+@pytest.mark.parametrize("model", list(MATRIX_DEFAULTS))
+@pytest.mark.parametrize("constraint", [True, False])
+def test_matrix_models_default_config(model, constraint):
+    score, loss = MATRIX_DEFAULTS[model]
+    rng = np.random.default_rng(13)
+    ref, W, eng = make_pair(model, N, R, 24, 24, score=_score_mat(model, score), loss=LOSSES[loss], k=4, side="h+t",
+                            constraint=constraint)
+    opt = RS.TFAdam()
+    for step in range(3):
+        X = rand_triples(rng, 48, N, R)
+        ids, k_eff = RS.sample_negatives(5, step, X, 4, "h+t", N)
+        l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, "h+t", True)
+        l_gpu = eng.train_step(X, 5, step)
+        assert abs(float(l_gpu.item()) - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, float(l_gpu.item()), l_ref)
+        got = tables_of(eng, model)
+        for kk, v in W.data.items():
+            assert_weights_close(got[kk], v, 1e-3, step + 1, (step, kk))
+
+
+@pytest.mark.parametrize("model,d,dr,k,side,loss", [
+    ("TransR", 100, 100, 10, "h+t", "hinge"),      # C4 shape
+    ("TransR", 40, 70, 3, "h", "logistic"),        # rectangular, clip active, unnormalised loss (clip_by_norm active)
+    ("TransR", 70, 40, 5, "t", "selfadv"),
+    ("SE", 50, 50, 6, "h+t", "bce"),
+    ("SE", 33, 33, 2, "t", "hinge"),
+    ("RESCAL", 64, 64, 8, "h+t", "square"),
+    ("RESCAL", 30, 30, 3, "h", "logistic"),
+    ("TransR", 200, 200, 2, "h+t", "hinge"),       # matrix too large to stage with Adam accumulators: global path
+])
+def test_matrix_models_shapes(model, d, dr, k, side, loss):
+    score = {"TransR": "l2pow", "SE": "l1", "RESCAL": "dot"}[model]
+    rng = np.random.default_rng(17)
+    ref, W, eng = make_pair(model, N, R, d, dr, score=_score_mat(model, score), loss=LOSSES[loss], k=k, side=side)
+    opt = RS.TFAdam()
+    for step in range(2):
+        X = rand_triples(rng, 40, N, R)
+        ids, k_eff = RS.sample_negatives(21, step, X, k, side, N)
+        l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, side, True)
+        l_gpu, neg = eng.train_step(X, 21, step, want_negatives=True)
+        assert np.array_equal(neg.cpu().numpy(), ids)
+        assert abs(float(l_gpu.item()) - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, float(l_gpu.item()), l_ref)
+        got = tables_of(eng, model)
+        for kk, v in W.data.items():
+            assert_weights_close(got[kk], v, 1e-3, step + 1, (step, kk))
+
+
+@pytest.mark.parametrize("model", list(MATRIX_DEFAULTS))
+def test_matrix_score_hrt(model):
+    score, loss = MATRIX_DEFAULTS[model]
+    rng = np.random.default_rng(2)
+    ref, W, eng = make_pair(model, N, R, 50, 30 if model == "TransR" else 50, score=_score_mat(model, score),
+                            loss=LOSSES[loss])
+    X = rand_triples(rng, 129, N, R)
+    got = eng.score(X[:, 0], X[:, 1], X[:, 2]).cpu()
+    Xt = torch.as_tensor(X)
+    with torch.no_grad():
+        want = ref.score_hrt(W, Xt[:, 0], Xt[:, 1], Xt[:, 2])
+    assert rel_err(got, want) < 1e-4
+
+
+@pytest.mark.parametrize("cw", [1.0, 0.25])
+def test_transh_dense_regulariser(cw):
+    """TransH constraint=True: soft constraints give dense gradients on all three tables and
+    tf.clip_by_norm sees the densified tensors (TransH.py:202-211)."""
+    rng = np.random.default_rng(23)
+    ref, W, eng = make_pair("TransH", N, R, 50, score=SCORES["l2pow"], loss=LOSSES["hinge"], k=4, side="h+t",
+                            constraint=True, cw=cw)
+    opt = RS.TFAdam()
+    for step in range(3):
+        X = rand_triples(rng, 64, N, R)
+        ids, k_eff = RS.sample_negatives(8, step, X, 4, "h+t", N)
+        is_train = step != 1
+        l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, "h+t", is_train)
+        l_gpu = eng.train_step(X, 8, step, is_train=is_train)
+        assert abs(float(l_gpu.item()) - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, float(l_gpu.item()), l_ref)
+        got = tables_of(eng, "TransH")
+        for kk, v in W.data.items():
+            assert_weights_close(got[kk], v, 1e-3, step + 1, (step, kk))
+
+
+def test_matrix_step_is_bitwise_deterministic():
+    outs = []
+    for _ in range(2):
+        rng = np.random.default_rng(3)
+        ref, W, eng = make_pair("TransR", N, R, 48, 32, score=SCORES["l2pow"], loss=LOSSES["hinge"], k=6, side="h+t")
+        for step in range(3):
+            eng.train_step(rand_triples(rng, 96, N, R), 5, step)
+        outs.append(tables_of(eng, "TransR"))
+    for kk in outs[0]:
+        assert torch.equal(outs[0][kk], outs[1][kk])
