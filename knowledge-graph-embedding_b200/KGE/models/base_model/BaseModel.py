@@ -1,0 +1,409 @@
+"""KGEModel — drop-in for KGE/models/base_model/BaseModel.py of the reference.
+
+Same public surface (constructor arguments :29-56, `train` :58-61, `evaluate` :578,
+`get_rank` :620, `score_hrt` :410, `restore_model_weights` :656, attribute
+`model_weights`), but the two hot loops are library calls:
+
+  * one `kge_train_step` per batch replaces `__run_single_batch` (:293-330): constraint,
+    Philox negative sampling, gather, projection, score, loss, analytic backward,
+    per-variable clip_by_norm and the Keras-semantics Adam update all run in the CUDA
+    kernels of libkge_b200.so; the loss stays on the device and is read once per epoch.
+  * one `kge_rank` per query block replaces the per-triple `get_rank` loop (:602-604,
+    :620-654): integer "better-scoring candidate" counts with a known-positive filter.
+
+Host control flow (epochs, early stopping, checkpoints, logging) is ordinary Python.
+There is no TensorFlow and no CPU fallback: without the CUDA library every compute
+entry point raises.
+"""
+import datetime
+import logging
+import math
+import os
+
+import numpy as np
+import torch
+
+from ... import metrics as _metrics
+from ...data_utils import DeviceBatchStream, calculate_data_size, load_triples
+from ...ns_strategy import TypedStrategy, UniformStrategy, _type_csr, check_typed_pools
+from ...optimizers import adam_fields
+from ..._b200 import engine as _engine, filter as _filter, lib as _lib, spec as _spec
+
+logging.getLogger().setLevel(logging.INFO)
+
+
+def _now():
+    return str(datetime.datetime.now())
+
+
+class WeightView:
+    """One entry of `model_weights`: a window on a device table that keeps the handful of
+    tf.Variable conveniences callers use (`.numpy()`, `.shape`, `.assign()`)."""
+
+    def __init__(self, name, table):
+        self.name, self._table = name, table
+
+    @property
+    def tensor(self):
+        return self._table.view
+
+    @property
+    def shape(self):
+        return tuple(self._table.shape)
+
+    def numpy(self):
+        return self._table.view.detach().cpu().numpy()
+
+    def __array__(self, dtype=None, copy=None):
+        a = self.numpy()
+        return a.astype(dtype) if dtype is not None else a
+
+    def assign(self, value):
+        v = value.tensor if isinstance(value, WeightView) else value
+        v = torch.as_tensor(np.asarray(v) if not torch.is_tensor(v) else v, dtype=torch.float32)
+        if tuple(v.shape) != self.shape:
+            raise ValueError(f"{self.name}: shape {tuple(v.shape)} != {self.shape}")
+        self._table.view.copy_(v.to(self._table.storage.device))
+        return self
+
+    def __repr__(self):
+        return f"WeightView({self.name}, shape={self.shape})"
+
+
+class KGEModel:
+    """Base of all models.  Subclasses declare `MODEL` (kernel family name) and
+    `_tables(n_ent, n_rel)` -> {key: (shape, init)} with init = limit | "eye"."""
+
+    MODEL = None
+    HAS_SCORE_FN = True
+
+    def __init__(self, embedding_params, negative_ratio, corrupt_side, loss_fn, ns_strategy, n_workers):
+        assert corrupt_side in ["h+t", "h", "t"], "Invalid corrupt_side, valid options: 'h+t', 'h', 't'"
+        self.embedding_params = embedding_params
+        self.negative_ratio = negative_ratio
+        self.corrupt_side = corrupt_side
+        self.loss_fn = loss_fn
+        self.ns_strategy = ns_strategy
+        self._n_workers = n_workers          # kept for signature parity; sampling is a kernel
+        self.device = os.environ.get("KGE_DEVICE", "cuda:0")
+        self.metadata = None
+        self._model_weights_initial = None
+        self._engine = None
+        self._optimizer = "Adam"
+        self.seed = None
+
+    # ---- subclass hooks ---------------------------------------------------------------
+    def _dims(self):
+        """(d_ent, d_rel)"""
+        d = self.embedding_params.get("embedding_size")
+        assert d is not None, "'embedding_size' should be given in embedding_params when using %s" % self.MODEL
+        return d, d
+
+    def _tables(self, n_ent, n_rel):
+        raise NotImplementedError("subclass of KGEModel should implement _tables()")
+
+    def _post_init(self):
+        """init-time constraints (TransE.py:108-109, RESCAL.py:109-115)."""
+
+    def _constraint_flag(self):
+        return bool(getattr(self, "constraint", False))
+
+    def _rotate_limit(self):
+        return None
+
+    # ---- weights ----------------------------------------------------------------------
+    def _sizes(self):
+        return len(self.metadata["ind2ent"]), len(self.metadata["ind2rel"])
+
+    def _check_model_weights(self, model_weights):
+        n_ent, n_rel = self._sizes()
+        for key, (shape, _) in self._tables(n_ent, n_rel).items():
+            assert model_weights.get(key) is not None, "'%s' should be given in model_weights" % key
+            assert list(np.shape(_plain(model_weights[key]))) == list(shape), \
+                "shape of '%s' should be %s" % (key, tuple(shape))
+
+    def _init_embeddings(self, seed):
+        """Uniform(+-limit) tables or `model_weights_initial`; builds the engine.
+        Every table has its own stream of the seeded generator: the reference's quirk of
+        identical same-shaped tables under a seed is not replicated."""
+        n_ent, n_rel = self._sizes()
+        spec = self._tables(n_ent, n_rel)
+        values = {}
+        if self._model_weights_initial is None:
+            gen = torch.Generator()
+            if seed is None:
+                gen.seed()
+            else:
+                gen.manual_seed(int(seed))
+            for key, (shape, init) in spec.items():
+                if init == "eye":
+                    values[key] = torch.eye(shape[1], shape[2]).repeat(shape[0], 1, 1)
+                else:
+                    values[key] = (torch.rand(shape, generator=gen, dtype=torch.float32) * 2 - 1) * float(init)
+        else:
+            self._check_model_weights(self._model_weights_initial)
+            values = {k: torch.as_tensor(_plain(self._model_weights_initial[k]), dtype=torch.float32) for k in spec}
+        self._build_engine(values)
+        self._post_init()
+
+    def _build_engine(self, values):
+        n_ent, n_rel = self._sizes()
+        d_ent, d_rel = self._dims()
+        cfg = _spec.make_cfg(self.MODEL, n_ent, n_rel, d_ent, d_rel,
+                             score_fn=getattr(self, "score_fn", None) if self.HAS_SCORE_FN else None,
+                             loss_fn=self.loss_fn, negative_ratio=self.negative_ratio,
+                             corrupt_side=self.corrupt_side, constraint=self._constraint_flag(),
+                             constraint_weight=getattr(self, "constraint_weight", 1.0),
+                             rotate_limit=self._rotate_limit())
+        cfg.update(adam_fields(self._optimizer))
+        slots = _spec.SLOTS[self.MODEL]
+        self._engine = _engine.Engine(cfg, {slots[k]: v for k, v in values.items()}, device=self.device)
+        self.model_weights = {k: WeightView(k, self._engine.tab[slots[k]]) for k in values}
+
+    def restore_model_weights(self, model_weights):
+        self._check_model_weights(model_weights)
+        if self._engine is None:
+            self._model_weights_initial = model_weights
+            self._init_embeddings(self.seed)
+            return
+        for k, view in self.model_weights.items():
+            view.assign(_plain(model_weights[k]))
+
+    def _require_engine(self):
+        if self._engine is None:
+            raise RuntimeError("model has no weights yet: call train() or _init_embeddings() first")
+        return self._engine
+
+    # ---- sampler ----------------------------------------------------------------------
+    def _setup_sampler(self):
+        eng, n_ent = self._require_engine(), self._sizes()[0]
+        ns = self.ns_strategy
+        if ns is UniformStrategy:
+            self.ns_strategy = ns = UniformStrategy(sample_pool=np.arange(n_ent))
+        elif ns is TypedStrategy:
+            labels = self.metadata["ind2type"]
+            self.metadata["type2inds"] = {t: np.array([i for i, ti in enumerate(labels) if ti == t])
+                                          for t in np.unique(labels)}
+            self.ns_strategy = ns = TypedStrategy(pool=None, metadata={"type2inds": self.metadata["type2inds"],
+                                                                       "ind2type": labels})
+        if isinstance(ns, UniformStrategy):
+            pool = ns.pool_array()
+            eng.set_uniform_pool(None if np.array_equal(pool, np.arange(n_ent)) else pool)
+        elif isinstance(ns, TypedStrategy):
+            ent_type, off, members, pos = ns.csr()
+            check_typed_pools(ent_type, off, pos)
+            eng.set_typed_pools(ent_type, off, members, pos)
+        else:
+            raise NotImplementedError("ns_strategy must be UniformStrategy or TypedStrategy (class or instance): "
+                                      "negatives are drawn inside the CUDA step kernel")
+
+    # ---- training ---------------------------------------------------------------------
+    def train(self, train_X, val_X, metadata, epochs, batch_size, early_stopping_rounds=None,
+              model_weights_initial=None, restore_best_weight=True, optimizer="Adam", seed=None,
+              log_path="./logs", log_projector=False):
+        """Same arguments as the reference (BaseModel.py:58-61).  `seed` additionally seeds the
+        Philox negative-sampling stream (the reference leaves that stream unseeded)."""
+        self.metadata = metadata
+        self.batch_size = batch_size
+        self._model_weights_initial = model_weights_initial
+        self._optimizer = optimizer
+        self.seed = seed
+        self.log_path = log_path
+        os.makedirs(log_path, exist_ok=True)
+        writers = _Writers(log_path, val_X is not None)
+
+        logging.info("[%s] Preparing for training..." % _now())
+        n_train = calculate_data_size(train_X)
+        n_batches = int(np.ceil(n_train / batch_size))
+        n_val_batches = int(np.ceil(calculate_data_size(val_X) / batch_size)) if val_X is not None else 0
+        train_iter = DeviceBatchStream(train_X, batch_size, shuffle=True, seed=seed, device=self.device)
+        val_iter = DeviceBatchStream(val_X, batch_size, shuffle=False, device=self.device) if val_X is not None else None
+        self._init_embeddings(seed=seed)
+        self._setup_sampler()
+        eng = self._engine
+        ns_seed = int(seed) if seed is not None else int.from_bytes(os.urandom(7), "little")
+        step = 0
+        self.train_loss_history, self.val_loss_history = [], []
+        self.best_step, patience = None, 0
+
+        logging.info("[%s] Start Training..." % _now())
+        for epoch in range(epochs):
+            t_loss = torch.zeros(n_batches, dtype=torch.float32, device=eng.device)
+            v_loss = torch.zeros(max(n_val_batches, 1), dtype=torch.float32, device=eng.device)
+            for b in range(n_batches):
+                eng.train_step(next(train_iter), ns_seed, step, is_train=True, loss_out=t_loss[b:b + 1])
+                step += 1
+                if val_iter is not None and b < n_val_batches:
+                    # validation batches draw negatives and apply the constraint too
+                    eng.train_step(next(val_iter), ns_seed, step, is_train=False, loss_out=v_loss[b:b + 1])
+                    step += 1
+            self.train_loss_history.append(float(t_loss.sum().item()) / n_batches)       # one sync per epoch
+            writers.scalar("train", self.train_loss_history[-1], epoch)
+            if val_iter is not None:
+                self.val_loss_history.append(float(v_loss.sum().item()) / n_val_batches)
+                writers.scalar("validation", self.val_loss_history[-1], epoch)
+                logging.info("epoch: %i, train loss: %f, valid loss: %f"
+                             % (epoch, self.train_loss_history[-1], self.val_loss_history[-1]))
+            else:
+                logging.info("epoch: %i, train loss: %f" % (epoch, self.train_loss_history[-1]))
+            writers.histograms(self.model_weights, epoch)
+
+            if early_stopping_rounds is not None:
+                assert val_X is not None, "val_X should be given if want to check early stopping."
+                stop, patience = self._check_early_stopping(self.val_loss_history, patience, early_stopping_rounds,
+                                                            epoch, restore_best_weight)
+                if stop:
+                    logging.info("[%s] Val loss does not improve within %i iterations, trigger early stopping."
+                                 % (_now(), early_stopping_rounds))
+                    break
+            else:
+                self._save_checkpoint()
+        if log_projector:
+            writers.projector(self.model_weights, self.metadata)
+        writers.close()
+        logging.info("[%s] Finished training!" % _now())
+
+    fit = train      # alias used by BASELINE.json's prose (the reference method is train())
+
+    def _check_early_stopping(self, history, patience, patience_max, step, restore_best_weight):
+        if step == 0 or self.best_step is None:
+            self._save_checkpoint()
+            self.best_step = step
+            return False, patience
+        if history[step] >= history[self.best_step]:
+            patience += 1
+        else:
+            patience, self.best_step = 0, step
+            self._save_checkpoint()
+        if patience == patience_max:
+            if restore_best_weight:
+                logging.info("[%s] Restore best weight from %i to %i step." % (_now(), step, self.best_step))
+                self._load_checkpoint()
+            return True, patience
+        return False, patience
+
+    def _ckpt_path(self):
+        return os.path.join(self.log_path, "ckpt.pt")
+
+    def _save_checkpoint(self):
+        """max_to_keep=1 like the reference's CheckpointManager (BaseModel.py:253); unlike the
+        reference the Adam slots and step are saved too."""
+        eng = self._engine
+        torch.save({"weights": {k: v.tensor.detach().cpu() for k, v in self.model_weights.items()},
+                    "adam_m": {s: t.m.cpu() for s, t in eng.tab.items() if t.m is not None},
+                    "adam_v": {s: t.v.cpu() for s, t in eng.tab.items() if t.v is not None},
+                    "adam_t": eng.adam_t}, self._ckpt_path())
+
+    def _load_checkpoint(self):
+        state = torch.load(self._ckpt_path())
+        for k, v in state["weights"].items():
+            self.model_weights[k].assign(v)
+
+    # ---- scoring / ranking ------------------------------------------------------------
+    def score_hrt(self, h, r, t):
+        """Scores of triples given as id vectors; `h=None` or `t=None` scores every entity on
+        that side against scalar ids (BaseModel.py:410-430).  Returns a torch tensor on the device."""
+        assert not (h is None and t is None), "h and t should not be None simultaneously"
+        eng, n_ent = self._require_engine(), self._sizes()[0]
+
+        def ids(x):
+            return np.atleast_1d(np.asarray(_plain(x))).astype(np.int64)
+        if h is None or t is None:
+            r_, o_ = ids(r), ids(t if h is None else h)
+            assert r_.size == 1 and o_.size == 1, "r and the given entity must be scalars when one side is None"
+            every = np.arange(n_ent, dtype=np.int64)
+            rep_r, rep_o = np.full(n_ent, r_[0]), np.full(n_ent, o_[0])
+            return eng.score(every, rep_r, rep_o) if h is None else eng.score(rep_o, rep_r, every)
+        return eng.score(ids(h), ids(r), ids(t))
+
+    def _rank_block(self, X, corrupt_side, positive_X):
+        eng, n_ent = self._require_engine(), self._sizes()[0]
+        assert corrupt_side in ("h", "t"), "corrupt_side can be 'h' or 't'"
+        X = np.asarray(_plain(X)).reshape(-1, 3).astype(np.int64)
+        side = _lib.SIDE_H if corrupt_side == "h" else _lib.SIDE_T
+        pos = None if positive_X is None else torch.as_tensor(np.asarray(_plain(positive_X))).to(eng.device)
+        ranks = []
+        for lo in range(0, len(X), 16384):
+            blk = X[lo:lo + 16384]
+            off = ids = None
+            if pos is not None:
+                off, ids = _filter.build_filter(pos, blk, corrupt_side, n_ent, eng.device)
+            ranks.append(eng.rank_counts(blk, side, off, ids).cpu().numpy().astype(np.int64) + 1)
+        return np.concatenate(ranks)
+
+    def get_rank(self, x, positive_X, corrupt_side):
+        """rank = 1 + #{candidates scoring strictly higher}, known positives excluded
+        (BaseModel.py:620-654).  The count is 32-bit, not the reference's int16."""
+        return np.int_(self._rank_block(x, corrupt_side, positive_X)[0])
+
+    def evaluate(self, eval_X, corrupt_side, positive_X=None):
+        ranks = self._rank_block(load_triples(eval_X), corrupt_side, positive_X)
+        self.last_ranks = ranks
+        return {
+            "mean_rank": _metrics.mean_rank(ranks),
+            "mean_reciprocal_rank": _metrics.mean_reciprocal_rank(ranks),
+            "median_rank": _metrics.median_rank(ranks),
+            "geometric_mean_rank": _metrics.geometric_mean_rank(ranks),
+            "harmonic_mean_rank": _metrics.harmonic_mean_rank(ranks),
+            "std_rank": _metrics.std_rank(ranks),
+            "hit@1": _metrics.hits_at_k(ranks, k=1),
+            "hit@3": _metrics.hits_at_k(ranks, k=3),
+            "hit@10": _metrics.hits_at_k(ranks, k=10),
+        }
+
+
+def _plain(x):
+    """WeightView / torch tensor / tf-like object -> numpy-compatible."""
+    if isinstance(x, WeightView):
+        return x.numpy()
+    if torch.is_tensor(x):
+        return x.detach().cpu().numpy()
+    if hasattr(x, "numpy") and not isinstance(x, np.ndarray):
+        return x.numpy()
+    return x
+
+
+class _Writers:
+    """Per-epoch scalars / histograms (BaseModel.py:444-483) and the projector export
+    (:542-576) through torch.utils.tensorboard when tensorboard is importable; otherwise
+    silently off — observability only, never on the hot path."""
+
+    def __init__(self, log_path, with_val):
+        self.log_path, self.w = log_path, {}
+        try:
+            from torch.utils.tensorboard import SummaryWriter
+            self.w["root"] = SummaryWriter(log_path)
+            self.w["train"] = SummaryWriter(os.path.join(log_path, "scalar", "train"))
+            if with_val:
+                self.w["validation"] = SummaryWriter(os.path.join(log_path, "scalar", "validation"))
+        except Exception:
+            self.w = {}
+
+    def scalar(self, which, value, step):
+        if which in self.w:
+            self.w[which].add_scalar("loss", value, step)
+
+    def histograms(self, weights, step):
+        if "root" in self.w:
+            for k, v in weights.items():
+                if v.tensor.numel() <= (1 << 22):
+                    self.w["root"].add_histogram(k, v.numpy(), step)
+
+    def projector(self, weights, metadata):
+        """metadata + embedding tsv files and a projector_config.pbtxt in log_path."""
+        blocks = []
+        for key, names in (("ent_emb", metadata.get("ind2ent")), ("rel_emb", metadata.get("ind2rel"))):
+            if key not in weights or names is None:
+                continue
+            mat = weights[key].numpy().reshape(len(names), -1)
+            np.savetxt(os.path.join(self.log_path, key + ".tsv"), mat, delimiter="\t", fmt="%.6g")
+            with open(os.path.join(self.log_path, key + "_metadata.tsv"), "w") as fh:
+                fh.write("\n".join(str(n) for n in names) + "\n")
+            blocks.append('embeddings {\n  tensor_name: "%s"\n  tensor_path: "%s.tsv"\n  metadata_path: "%s_metadata.tsv"\n}\n'
+                          % (key, key, key))
+        with open(os.path.join(self.log_path, "projector_config.pbtxt"), "w") as fh:
+            fh.write("".join(blocks))
+
+    def close(self):
+        for w in self.w.values():
+            w.close()

@@ -1,0 +1,203 @@
+"""The drop-in KGE Python API on the GPU: mirrors the reference's tests/test_model.py,
+tests/test_ns_strategy.py and tests/test_integration.py (same invariants, same combination
+matrix), plus golden parity of the API path itself (model classes -> C-ABI)."""
+import itertools
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from KGE import score, loss, ns_strategy, optimizers
+from KGE.models.translating_based.UM import UM
+from KGE.models.translating_based.SE import SE
+from KGE.models.translating_based.TransE import TransE
+from KGE.models.translating_based.TransH import TransH
+from KGE.models.translating_based.TransR import TransR
+from KGE.models.translating_based.TransD import TransD
+from KGE.models.translating_based.RotatE import RotatE
+from KGE.models.semantic_based.DistMult import DistMult
+from KGE.models.semantic_based.RESCAL import RESCAL
+from toy_kg import train, val, metadata
+from test_golden_oracle import load_case, weights, close, TOL
+
+pytestmark = pytest.mark.gpu
+
+TRANSLATING = {"UM": UM, "SE": SE, "TransE": TransE, "TransH": TransH, "TransR": TransR, "TransD": TransD,
+               "RotatE": RotatE}
+SEMANTIC = {"DistMult": DistMult, "RESCAL": RESCAL}
+ALL = dict(TRANSLATING, **SEMANTIC)
+
+
+def emb(name, d=16):
+    return {"ent_embedding_size": d, "rel_embedding_size": d} if name in ("TransR", "TransD") else {"embedding_size": d}
+
+
+def typed_metadata():
+    md = dict(metadata)
+    n = len(md["ind2ent"])
+    md["ind2type"] = ["A"] * (n // 2) + ["B"] * (n - n // 2)
+    md["type2inds"] = {t: np.array([i for i, ti in enumerate(md["ind2type"]) if ti == t]) for t in ("A", "B")}
+    return md
+
+
+# ---- tests/test_model.py -----------------------------------------------------------------
+class TestBaseModel:
+    def setup_method(self):
+        self.model = TransE(embedding_params={"embedding_size": 16}, negative_ratio=2, corrupt_side="h+t")
+        self.model._model_weights_initial = None
+        self.model.metadata = metadata
+        self.model._init_embeddings(seed=None)
+
+    def test_train(self, tmp_path):
+        self.model.train(train_X=train, val_X=val, metadata=metadata, epochs=1, batch_size=2, log_path=str(tmp_path))
+        assert len(self.model.train_loss_history) == 1 and math.isfinite(self.model.train_loss_history[0])
+
+    def test_get_rank(self):
+        x = val[:1]
+        rank = self.model.get_rank(x=x, positive_X=None, corrupt_side="h")
+        rank_filter = self.model.get_rank(x=x, positive_X=np.concatenate((train, val), axis=0), corrupt_side="h")
+        assert isinstance(rank, np.int_) and isinstance(rank_filter, np.int_)
+        assert rank >= 1 and rank_filter >= 1 and rank_filter <= rank
+
+    def test_evaluate(self):
+        raw = self.model.evaluate(eval_X=val, corrupt_side="h", positive_X=None)
+        flt = self.model.evaluate(eval_X=val, corrupt_side="h", positive_X=np.concatenate((train, val), axis=0))
+        for m in ["mean_rank", "median_rank", "geometric_mean_rank", "harmonic_mean_rank"]:
+            assert flt[m] <= raw[m]
+        for m in ["mean_reciprocal_rank", "hit@1", "hit@3", "hit@10"]:
+            assert flt[m] >= raw[m]
+        assert list(raw.keys()) == ["mean_rank", "mean_reciprocal_rank", "median_rank", "geometric_mean_rank",
+                                    "harmonic_mean_rank", "std_rank", "hit@1", "hit@3", "hit@10"]
+
+
+@pytest.mark.parametrize("name", list(ALL))
+def test_init_and_score_hrt(name):
+    kw = dict(embedding_params=emb(name), negative_ratio=2, corrupt_side="h+t")
+    model = ALL[name](**kw)
+    model._model_weights_initial = None
+    model.metadata = metadata
+    model._init_embeddings(seed=None)
+    n_ent, n_rel = len(metadata["ind2ent"]), len(metadata["ind2rel"])
+    assert set(model.model_weights) == set(model._tables(n_ent, n_rel))
+    for k, (shape, _) in model._tables(n_ent, n_rel).items():
+        assert model.model_weights[k].shape == tuple(shape) and model.model_weights[k].numpy().dtype == np.float32
+    s = model.score_hrt(h=val[:, 0], r=val[:, 1], t=val[:, 2])
+    assert len(s) == len(val) and bool(torch.isfinite(s).all())
+    assert len(model.score_hrt(h=None, r=val[0, 1], t=val[0, 2])) == n_ent
+    assert len(model.score_hrt(h=val[0, 0], r=val[0, 1], t=None)) == n_ent
+    with pytest.raises(AssertionError):
+        model.score_hrt(h=None, r=val[0, 1], t=None)              # the reference's guard never fires
+
+
+# ---- tests/test_ns_strategy.py ---------------------------------------------------------
+def test_uniform_strategy_shape_dtype():
+    n_ent = len(metadata["ind2ent"])
+    strat = ns_strategy.UniformStrategy(sample_pool=np.arange(n_ent))
+    for side in ("h", "t"):
+        out = strat(torch.as_tensor(val), negative_ratio=2, side=side)
+        assert tuple(out.shape) == (len(val) * 2,) and out.dtype == torch.int64
+        assert int(out.min()) >= 0 and int(out.max()) < n_ent
+    out32 = strat(torch.as_tensor(val.astype(np.int32)), negative_ratio=2, side="h")
+    assert out32.dtype == torch.int32
+    sub = ns_strategy.UniformStrategy(sample_pool=np.array([3, 5, 7]))
+    assert set(sub(val, negative_ratio=50, side="t").cpu().tolist()) <= {3, 5, 7}
+
+
+def test_typed_strategy_preserves_type():
+    md = typed_metadata()
+    strat = ns_strategy.TypedStrategy(pool=None, metadata=md)
+    types = np.asarray(md["ind2type"])
+    for side, col in (("h", 0), ("t", 2)):
+        out = strat(torch.as_tensor(val), negative_ratio=2, side=side)
+        assert tuple(out.shape) == (len(val) * 2,) and out.dtype == torch.int64
+        ref = np.repeat(val[:, col], 2)
+        got = out.cpu().numpy()
+        assert (types[got] == types[ref]).all() and (got != ref).all()
+    lonely = dict(md, ind2type=["Z"] + ["A"] * (len(types) - 1))
+    lonely.pop("type2inds")
+    with pytest.raises(ValueError):
+        ns_strategy.TypedStrategy(pool=None, metadata=lonely)(val, negative_ratio=1, side="h")
+
+
+# ---- tests/test_integration.py: every model x score x loss x sampler ----------------------
+ALL_SCORES = [score.LpDistance(p=2), score.LpDistancePow(p=2), score.Dot()]
+ALL_LOSSES = [loss.PairwiseHingeLoss(margin=1.0), loss.PairwiseLogisticLoss(), loss.BinaryCrossEntropyLoss(),
+              loss.SquareErrorLoss(), loss.SelfAdversarialNegativeSamplingLoss(margin=1.0, temperature=1.0)]
+
+
+@pytest.mark.parametrize("name", list(ALL))
+def test_integration_matrix(name, tmp_path):
+    md = typed_metadata()
+    samplers = [ns_strategy.UniformStrategy(np.arange(len(md["ind2ent"]))), ns_strategy.TypedStrategy(pool=None, metadata=md)]
+    scores = [None] if name in SEMANTIC else (ALL_SCORES[:2] if name == "RotatE" else ALL_SCORES)
+    for sc, ls, smp in itertools.product(scores, ALL_LOSSES, samplers):
+        kw = dict(embedding_params=emb(name), negative_ratio=2, corrupt_side="h+t", loss_fn=ls, ns_strategy=smp)
+        if sc is not None:
+            kw["score_fn"] = sc
+        model = ALL[name](**kw)
+        model.train(train_X=train, val_X=val, metadata=md, epochs=1, batch_size=4, early_stopping_rounds=None,
+                    restore_best_weight=False, optimizer=optimizers.Adam(), seed=12345, log_path=str(tmp_path),
+                    log_projector=True)
+        res = model.evaluate(eval_X=val, corrupt_side="h")
+        assert math.isfinite(model.train_loss_history[-1]) and res["mean_rank"] >= 1
+
+
+def test_sampler_class_and_early_stopping(tmp_path):
+    md = typed_metadata()
+    for cls in (ns_strategy.UniformStrategy, ns_strategy.TypedStrategy):
+        m = TransE(embedding_params={"embedding_size": 8}, negative_ratio=2, corrupt_side="t", ns_strategy=cls)
+        m.train(train, val, md, epochs=6, batch_size=4, early_stopping_rounds=2, seed=1, log_path=str(tmp_path))
+        assert 1 <= len(m.val_loss_history) <= 6 and m.best_step is not None
+    m2 = TransE(embedding_params={"embedding_size": 8}, negative_ratio=1, corrupt_side="h+t")
+    with pytest.raises(RuntimeError):          # 'h+t' with negative_ratio=1 -> zero negatives
+        m2.train(train, None, md, epochs=1, batch_size=4, log_path=str(tmp_path))
+
+
+def test_train_without_validation_and_restore(tmp_path):
+    m = DistMult(embedding_params={"embedding_size": 8}, negative_ratio=4, corrupt_side="h+t")
+    m.train(train, None, metadata, epochs=2, batch_size=4, seed=3, log_path=str(tmp_path))   # reference crashes (C.1)
+    saved = {k: v.numpy().copy() for k, v in m.model_weights.items()}
+    m.train(train, None, metadata, epochs=1, batch_size=4, seed=4, log_path=str(tmp_path))
+    m.restore_model_weights(saved)                                                           # reference: TypeError (C.12)
+    for k, v in saved.items():
+        assert np.array_equal(m.model_weights[k].numpy(), v)
+    same = DistMult(embedding_params={"embedding_size": 8}, negative_ratio=4, corrupt_side="h+t")
+    same.train(train, None, metadata, epochs=2, batch_size=4, seed=3, log_path=str(tmp_path))
+    same2 = {k: v.numpy() for k, v in same.model_weights.items()}
+    m.train(train, None, metadata, epochs=2, batch_size=4, seed=3, log_path=str(tmp_path))
+    for k in same2:                                    # seeded runs are bitwise reproducible end to end
+        assert np.array_equal(m.model_weights[k].numpy(), same2[k])
+
+
+# ---- the API path against the reference's own train()/evaluate() run (golden) -------------
+def test_api_step_sequence_matches_reference_golden():
+    """model class -> spec -> C-ABI: same losses as the reference's __run_single_batch sequence."""
+    for name in ("transe", "distmult", "transr", "rotate", "rescal", "transh"):
+        g, spec = load_case(name)
+        cls = ALL[spec["model"]]
+        sc = {"l1": score.LpDistance(1), "l2": score.LpDistance(2), "l2pow": score.LpDistancePow(2), "dot": score.Dot(),
+              "None": None}[spec["score"]]
+        ls = {"hinge": loss.PairwiseHingeLoss(1.0), "bce": loss.BinaryCrossEntropyLoss(), "square": loss.SquareErrorLoss(),
+              "selfadv": loss.SelfAdversarialNegativeSamplingLoss(3.0, 1.0)}[spec["loss"]]
+        kw = dict(embedding_params=emb(spec["model"], spec["d"]), negative_ratio=spec["k"], corrupt_side=spec["side"], loss_fn=ls)
+        if spec["model"] in ("TransR", "TransD"):
+            kw["embedding_params"] = {"ent_embedding_size": spec["d"], "rel_embedding_size": spec["dr"]}
+        if sc is not None:
+            kw["score_fn"] = sc
+        if spec["model"] != "RotatE":
+            kw["constraint"] = spec["constraint"]
+        if spec["model"] in ("TransH", "DistMult", "RESCAL"):
+            kw["constraint_weight"] = spec["cw"]
+        m = cls(**kw)
+        m.metadata = {"ind2ent": list(range(40)), "ind2rel": list(range(5))}
+        m._model_weights_initial = {k: v.numpy() for k, v in weights(g, "w0_").items()}
+        # w0 is the reference's post-init state: skip our init-time constraint by building the engine directly
+        m._build_engine({k: torch.as_tensor(v) for k, v in m._model_weights_initial.items()})
+        m._setup_sampler()
+        for step in range(len(g["step_X"])):
+            l = m._engine.train_step(g["step_X"][step], 4242, step, is_train=bool(g["step_is_train"][step]))
+            want = float(g["step_loss"][step])
+            assert abs(float(l.item()) - want) <= TOL * max(1.0, abs(want)), (name, step)
+        sc_all = m.score_hrt(h=None, r=g["score_X"][0][1], t=g["score_X"][0][2])
+        assert len(sc_all) == 40
