@@ -11,6 +11,7 @@ def build_filter(positive_X, queries, side, n_ent, device):
     Returns (off[Q+1], ids[total]) int64 device tensors, ids[off[q]:off[q+1]] = entities to
     exclude for query q (the query's own true entity included when it is in positive_X)."""
     P = torch.as_tensor(positive_X).to(device=device, dtype=torch.int64)
+    P = torch.unique(P, dim=0)          # duplicate triples would be subtracted twice by the CSR-subtraction kernels
     Qx = torch.as_tensor(queries).to(device=device, dtype=torch.int64)
     fs, cs = (2, 0) if side == "h" else (0, 2)
     pkey = P[:, 1] * n_ent + P[:, fs]

@@ -2,9 +2,22 @@
 #include "host_common.cuh"
 #include "rank_kernels.cuh"
 #include "rank_mat_kernels.cuh"
+#include "rank_dot_host.cuh"
+#include <stdlib.h>
 
 namespace kge {
-size_t rank_workspace_bytes(const kge_cfg*, int64_t) { return 256; }
+static bool force_generic_rank() {
+  const char* e = getenv("KGE_RANK_GENERIC");     // A/B switch for tests and profiling
+  return e && e[0] == '1';
+}
+size_t rank_workspace_bytes(const kge_cfg* cfg, int64_t Q) {
+  if (rank_dot_eligible(cfg)) {
+    DotWs L;
+    layout_dot_ws(cfg, Q, cfg->n_ent, L);         // sized for the full entity range (largest shard)
+    return L.total;
+  }
+  return 256;
+}
 }  // namespace kge
 using namespace kge;
 
@@ -60,7 +73,14 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
   KGE_REQUIRE(0 <= ent_lo && ent_lo < ent_hi && ent_hi <= cfg->n_ent, KGE_EINVAL, "bad entity shard [%lld, %lld)",
               (long long) ent_lo, (long long) ent_hi);
   KGE_REQUIRE(!filter || !filter->off || filter->ids, KGE_EINVAL, "filter.off given without filter.ids");
-  (void) ws; (void) ws_bytes;
+  if (rank_dot_eligible(cfg) && !force_generic_rank()) {
+    PhaseTimer ptd(ctx, (cudaStream_t) stream);
+    ptd.begin(5);
+    if (int rc = rank_dot_tensor(ctx, cfg, tables, queries, Q, side, filter, ent_lo, ent_hi, count_out, ws, ws_bytes,
+                                 (cudaStream_t) stream)) return rc;
+    ptd.end(5);
+    return KGE_OK;
+  }
   const bool mat = is_matrix_model(cfg->model);
   RankParams p;
   fill_model_dev(cfg, tables, p.md);

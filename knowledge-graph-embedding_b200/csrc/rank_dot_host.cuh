@@ -1,0 +1,140 @@
+// rank_dot_host.cuh — host side of the tensor-core ranking path (included by rank.cu).
+#pragma once
+#include <cudaTypedefs.h>
+#include "host_common.cuh"
+#include "rank_dot_tc.cuh"
+
+namespace kge {
+
+// Dot-family with a plain entity row on the candidate side
+inline bool rank_dot_eligible(const kge_cfg* c) {
+  if (c->model == KGE_DISTMULT || c->model == KGE_RESCAL) return true;
+  return c->score == KGE_SCORE_DOT && (c->model == KGE_UM || c->model == KGE_TRANSE);
+}
+
+struct DotWs {
+  int kpad, words_per_q, n_etiles;
+  int64_t qblk;                    // queries per launch (multiple of 128)
+  size_t off_qm, off_pos, off_bias, off_hi, off_lo, off_maxn, off_mask, total;
+};
+inline void layout_dot_ws(const kge_cfg* c, int64_t Q, int64_t span, DotWs& L) {
+  L.kpad = (c->d_ent + TC_BK - 1) / TC_BK * TC_BK;
+  L.n_etiles = (int) ((span + TC_BN - 1) / TC_BN);
+  L.words_per_q = L.n_etiles * (TC_BN / 32);
+  int64_t cap = ((int64_t) 256 << 20) / ((int64_t) L.words_per_q * 4);
+  cap = cap / TC_BM * TC_BM;
+  if (cap < TC_BM) cap = TC_BM;
+  if (cap > 16384) cap = 16384;
+  const int64_t qpad = (Q + TC_BM - 1) / TC_BM * TC_BM;
+  L.qblk = qpad < cap ? qpad : cap;
+  size_t o = 0;
+  auto take = [&](size_t b) { size_t at = o; o += align_up(b); return at; };
+  L.off_maxn = take(256);
+  L.off_qm = take(sizeof(float) * (size_t) L.qblk * L.kpad);
+  L.off_pos = take(sizeof(float) * (size_t) L.qblk);
+  L.off_bias = take(sizeof(float) * (size_t) L.qblk);
+  L.off_hi = take(sizeof(float) * (size_t) L.qblk);
+  L.off_lo = take(sizeof(float) * (size_t) L.qblk);
+  L.off_mask = take(sizeof(uint32_t) * (size_t) L.qblk * L.words_per_q);
+  L.total = o;
+}
+
+inline PFN_cuTensorMapEncodeTiled_v12000 tensor_map_encoder() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  }
+  return fn;
+}
+// fp32 row-major [rows x cols] at a stride of ld floats; box = 32 floats x box_rows, 128B swizzle, OOB -> 0
+inline int make_map_2d(CUtensorMap* m, const float* base, uint64_t cols, uint64_t rows, uint64_t ld, uint32_t box_rows) {
+  auto enc = tensor_map_encoder();
+  KGE_REQUIRE(enc, KGE_ECUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * sizeof(float)};
+  cuuint32_t box[2] = {(cuuint32_t) TC_BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  KGE_REQUIRE(r == CUDA_SUCCESS, KGE_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int) r);
+  return KGE_OK;
+}
+
+// count_out[q] += #{e in [ent_lo, ent_hi): score(e) > pos(q), e not filtered}
+inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tables* tables, const void* queries,
+                           int64_t Q, int side, const kge_filter* filter, int64_t ent_lo, int64_t ent_hi,
+                           int32_t* count_out, void* ws, size_t ws_bytes, cudaStream_t st) {
+  DotWs L;
+  layout_dot_ws(cfg, Q, ent_hi - ent_lo, L);
+  KGE_REQUIRE(ws && ws_bytes >= L.total, KGE_EWORKSPACE, "rank workspace %zu < required %zu bytes", ws_bytes, L.total);
+  KGE_REQUIRE(((uintptr_t) ws & 255) == 0, KGE_EINVAL, "workspace must be 256-byte aligned");
+  char* wsb = reinterpret_cast<char*>(ws);
+  const kge_table& E = tables->t[KGE_T_ENT];
+  static bool attr_set = false;
+  if (!attr_set) {
+    KGE_CUDA_OK(cudaFuncSetAttribute(k_rank_dot_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+    attr_set = true;
+  }
+  unsigned* maxn = reinterpret_cast<unsigned*>(wsb + L.off_maxn);
+  KGE_CUDA_OK(cudaMemsetAsync(maxn, 0, 256, st));
+  {
+    int64_t blocks = (ent_hi - ent_lo + 7) / 8;
+    if (blocks > (int64_t) ctx->sm_count * 16) blocks = (int64_t) ctx->sm_count * 16;
+    k_rank_maxnorm<<<(unsigned) blocks, 256, 0, st>>>(E.w, E.ld, E.cols, ent_lo, ent_hi, maxn);
+    KGE_CUDA_OK(cudaGetLastError());
+  }
+  CUtensorMap map_a, map_b;
+  float* Qm = reinterpret_cast<float*>(wsb + L.off_qm);
+  if (int rc = make_map_2d(&map_a, Qm, (uint64_t) L.kpad, (uint64_t) L.qblk, (uint64_t) L.kpad, TC_BM)) return rc;
+  if (int rc = make_map_2d(&map_b, E.w, (uint64_t) E.cols, (uint64_t) ent_hi, (uint64_t) E.ld, TC_BN)) return rc;
+  const size_t idb = cfg->id_dtype ? 8 : 4;
+  for (int64_t q0 = 0; q0 < Q; q0 += L.qblk) {
+    const int64_t qn = (Q - q0 < L.qblk) ? Q - q0 : L.qblk;
+    KGE_CUDA_OK(cudaMemsetAsync(Qm, 0, sizeof(float) * (size_t) L.qblk * L.kpad, st));
+    DotPrepParams pp;
+    fill_model_dev(cfg, tables, pp.md);
+    pp.queries = (const char*) queries + (size_t) q0 * 3 * idb; pp.id64 = cfg->id_dtype; pp.Q = qn; pp.side = side;
+    pp.Qm = Qm; pp.kpad = L.kpad;
+    pp.pos = reinterpret_cast<float*>(wsb + L.off_pos); pp.bias = reinterpret_cast<float*>(wsb + L.off_bias);
+    pp.thr_hi = reinterpret_cast<float*>(wsb + L.off_hi); pp.thr_lo = reinterpret_cast<float*>(wsb + L.off_lo);
+    pp.maxnorm_bits = maxn;
+    pp.eps = 2.0e-3f + 2.5e-7f * (float) L.kpad;      // 2^-9 (two TF32 truncations) + fp32 accumulation slack
+    k_rank_dot_prep<<<(unsigned) ((qn + 7) / 8), 256, 0, st>>>(pp);
+    KGE_CUDA_OK(cudaGetLastError());
+
+    DotTcParams tp;
+    tp.n_kc = L.kpad / TC_BK; tp.Q = qn; tp.n_qblocks = (int) ((qn + TC_BM - 1) / TC_BM);
+    tp.ent_lo = ent_lo; tp.ent_hi = ent_hi; tp.n_etiles = L.n_etiles;
+    int split = 1;
+    while (tp.n_qblocks * split < 2 * ctx->sm_count && split * 2 <= L.n_etiles) split *= 2;
+    tp.n_split = split;
+    tp.thr_hi = pp.thr_hi; tp.thr_lo = pp.thr_lo; tp.count = count_out + q0;
+    tp.mask = reinterpret_cast<uint32_t*>(wsb + L.off_mask); tp.words_per_q = L.words_per_q;
+    int grid = tp.n_qblocks * split;
+    if (grid > ctx->sm_count) grid = ctx->sm_count;
+    k_rank_dot_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(map_a, map_b, tp);
+    KGE_CUDA_OK(cudaGetLastError());
+
+    DotFixParams fp;
+    fp.Qm = Qm; fp.kpad = L.kpad; fp.E = E.w; fp.ldE = E.ld; fp.cols = E.cols;
+    fp.pos = pp.pos; fp.bias = pp.bias; fp.mask = tp.mask; fp.words_per_q = L.words_per_q;
+    fp.Q = qn; fp.ent_lo = ent_lo; fp.ent_hi = ent_hi; fp.count = count_out + q0;
+    fp.f_off = (filter && filter->off) ? filter->off + q0 : nullptr;
+    fp.f_ids = filter ? filter->ids : nullptr;
+    const int64_t fix_warps = qn * ((L.words_per_q + 31) / 32);
+    k_rank_dot_fix<<<(unsigned) ((fix_warps + 7) / 8), 256, 0, st>>>(fp);
+    KGE_CUDA_OK(cudaGetLastError());
+    if (fp.f_off) {
+      k_rank_dot_filter<<<(unsigned) ((qn + 7) / 8), 256, 0, st>>>(fp);
+      KGE_CUDA_OK(cudaGetLastError());
+    }
+  }
+  return KGE_OK;
+}
+
+}  // namespace kge

@@ -1,3 +1,3 @@
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -q "$@" 2>&1 | tail -60 > gpurun_out/pytest_gpu.log
+timeout 600 python -m pytest tests -m gpu -q "$@" 2>&1 | tail -60 > gpurun_out/pytest_gpu.log
 tail -5 gpurun_out/pytest_gpu.log

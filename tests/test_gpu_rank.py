@@ -75,3 +75,37 @@ def test_entity_shards_sum_to_full():
 @pytest.mark.parametrize("side", ["h", "t"])
 def test_rank_matrix_models(model, score, d, dr, side):
     _check(model, score if model != "RESCAL" else "dot", side, True, d=d, d_rel=dr, Q=16)
+
+
+# ---- tensor-core (tcgen05) ranking path vs the generic CUDA-core path -------------------
+@pytest.mark.parametrize("model,score,d,n_ent", [("DistMult", "dot", 200, 5000), ("DistMult", "dot", 50, 777),
+                                                 ("RESCAL", "dot", 64, 3000), ("TransE", "dot", 100, 4097),
+                                                 ("UM", "dot", 33, 1500), ("DistMult", "dot", 500, 2100)])
+@pytest.mark.parametrize("side", ["h", "t"])
+def test_tensor_core_rank_equals_generic(model, score, d, n_ent, side):
+    import os
+    from KGE._b200.filter import build_filter
+    rng = np.random.default_rng(12)
+    ref, W, eng = make_pair(model, n_ent, R, d, None, score=_score_for(model, score), loss=LOSSES["hinge"])
+    pos = rand_triples(rng, 20000, n_ent, R)
+    Xq = pos[:700].copy()
+    Xq[::4] = rand_triples(rng, len(Xq[::4]), n_ent, R)
+    off, ids = build_filter(pos, Xq, side, n_ent, eng.device)
+    s = 0 if side == "h" else 1
+    tc_raw = eng.rank_counts(Xq, s).cpu().numpy()
+    tc_flt = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+    os.environ["KGE_RANK_GENERIC"] = "1"
+    try:
+        g_raw = eng.rank_counts(Xq, s).cpu().numpy()
+        g_flt = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+    finally:
+        os.environ.pop("KGE_RANK_GENERIC")
+    for a, b in ((tc_raw, g_raw), (tc_flt, g_flt)):
+        diff = np.abs(a.astype(np.int64) - b)
+        # both are exact-fp32 rankings with different summation orders: only near-ties may move
+        assert diff.max() <= 2 and (diff > 0).mean() <= 0.01, (diff.max(), (diff > 0).mean())
+    assert (tc_flt <= tc_raw).all()
+    # shards add up exactly
+    parts = sum(eng.rank_counts(Xq, s, off, ids, ent_lo=lo, ent_hi=hi).cpu().numpy()
+                for lo, hi in [(0, n_ent // 3), (n_ent // 3, n_ent // 3 + 77), (n_ent // 3 + 77, n_ent)])
+    assert np.array_equal(parts, tc_flt)
