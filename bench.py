@@ -31,7 +31,7 @@ import torch
 
 WORKLOAD = {"workload": "C2 DistMult d=200 BCE uniform h+t k=64 B=1024 FB15k-shape (N=14951,R=1345)",
             "model": "DistMult", "n_ent": 14951, "n_rel": 1345, "d": 200, "B": 1024, "k": 64,
-            "side": "h+t", "n_train": 483142, "eval_Q": 4096}
+            "side": "h+t", "n_train": 483142, "eval_Q": 16384}
 METRIC = "train triples/sec (pos+neg)"
 
 
@@ -204,7 +204,8 @@ def run_ours(args, rank, world, device):
 
 def run_eval(eng, train, rank, world, device, reps=3):
     """Filtered ranking, both sides, Q queries per side; queries sharded over ranks (tables
-    are replicated for this config, so no collective on the data path)."""
+    are replicated for this config, so no collective on the data path).  DistMult scores are
+    dot products: kge_rank runs the tcgen05 GEMM path (csrc/rank_dot_tc.cuh)."""
     from KGE._b200.filter import build_filter
     W = WORKLOAD
     Q = W["eval_Q"]
@@ -213,25 +214,53 @@ def run_eval(eng, train, rank, world, device, reps=3):
     mine = q_all[rank::world]
     filt = {s: build_filter(train, mine, s, W["n_ent"], device) for s in ("h", "t")}
     qd = torch.from_numpy(mine).to(device)
+    cnts = {}
     for s in ("h", "t"):
-        eng.rank_counts(qd, 0 if s == "h" else 1, *filt[s])
+        cnts[s] = eng.rank_counts(qd, 0 if s == "h" else 1, *filt[s])
     torch.cuda.synchronize()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     eng.profile_begin(2 * reps)
     a.record()
     for _ in range(reps):
         for s in ("h", "t"):
-            cnt = eng.rank_counts(qd, 0 if s == "h" else 1, *filt[s])
+            eng.rank_counts(qd, 0 if s == "h" else 1, *filt[s])
     b.record()
     torch.cuda.synchronize()
-    phases, _ = eng.profile_end()
+    phases, n_calls = eng.profile_end()
     t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=device)
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     ms = float(t.item())
-    ranks = (cnt.cpu().numpy() + 1).astype(np.float64)
-    return {"queries": 2 * Q * reps, "ms": ms, "kernel_ms": phases["rank"],
-            "mrr_t": float(np.mean(1 / ranks)), "hits10_t": float(np.mean(ranks <= 10))}
+    ranks = {s: (c.cpu().numpy() + 1).astype(np.float64) for s, c in cnts.items()}
+    both = np.concatenate([ranks["h"], ranks["t"]])
+    gemm_ms = phases["rank_gemm"] / max(n_calls, 1)
+    flops = 2.0 * W["n_ent"] * W["d"] * len(mine)            # algorithmic: 2*N*d per query
+    return {"queries": 2 * len(mine) * reps * world, "ms": ms, "kernel_ms": phases["rank"], "gemm_ms": gemm_ms,
+            "fix_ms": phases["rank_fix"] / max(n_calls, 1), "gemm_tflops": flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms else None,
+            "mrr": float(np.mean(1 / both)), "hits10": float(np.mean(both <= 10)), "ranks": ranks, "queries_used": mine}
+
+
+def cpu_oracle_eval(eng, train, ev, n_queries, threads):
+    """The reference's get_rank loop (BaseModel.py:602-654: per query, two scans of positive_X, score all
+    entities) on host cores, on the first n_queries of the GPU's query set; also returns whether the GPU
+    ranks of those queries match (ties within 1e-5 excepted by construction of the oracle test)."""
+    from oracle import ref_ops as O, ref_models as RM, ref_step as RS
+    from KGE._b200 import spec
+    W = WORKLOAD
+    torch.set_num_threads(threads)
+    ref = RM.DistMult(W["n_ent"], W["n_rel"], W["d"], loss_fn=O.BinaryCrossEntropyLoss())
+    Wt = RM.Weights({k: eng.tab[s].view.detach().cpu() for k, s in spec.SLOTS["DistMult"].items()})
+    qs = ev["queries_used"][:n_queries]
+    t0 = time.perf_counter()
+    r_cpu = {s: np.array([RS.get_rank(ref, Wt, x, train, s) for x in qs], dtype=np.float64) for s in ("h", "t")}
+    dt = time.perf_counter() - t0
+    cpu_all = np.concatenate([r_cpu["h"], r_cpu["t"]])
+    gpu_all = np.concatenate([ev["ranks"]["h"][:n_queries], ev["ranks"]["t"][:n_queries]])
+    return {"value": 2 * len(qs) / dt, "unit": "queries/s", "cores": threads, "kind": "port",
+            "sample": f"{2 * len(qs)} queries (both sides of the first {len(qs)} eval triples), filter = train set",
+            "mrr_cpu": float(np.mean(1 / cpu_all)), "mrr_gpu_same_queries": float(np.mean(1 / gpu_all)),
+            "hits10_cpu": float(np.mean(cpu_all <= 10)), "hits10_gpu_same_queries": float(np.mean(gpu_all <= 10)),
+            "ranks_identical": int((cpu_all == gpu_all).sum()), "ranks_compared": int(len(cpu_all))}
 
 
 def cpu_oracle_steps(n_steps, threads):
@@ -263,6 +292,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-steps", type=int, default=30)
+    ap.add_argument("--cpu-queries", type=int, default=64)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -309,6 +339,7 @@ def main():
     achieved = fwd_bytes / (step_ms * 1e-3) / 1e9
     share = {k: round(v / max(sum(r["phases"].values()), 1e-9), 4) for k, v in r["phases"].items() if v > 0}
     cpu_tps, cpu_s = cpu_oracle_steps(args.cpu_steps, cores)
+    cpu_ev = cpu_oracle_eval(r["eng"], r["train"], ev, args.cpu_queries, cores)
     out = {
         "metric": METRIC, "value": r["triples"] / (r["ms_cold"] * 1e-3), "unit": "triples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_cold"] / args.steps,
@@ -326,8 +357,14 @@ def main():
                          "sample": f"{args.cpu_steps} full steps of the same workload on the host (oracle port; "
                                    "TensorFlow reference not installable)"},
         "eval": {"metric": "filtered-eval queries/sec", "value": ev["queries"] / (ev["ms"] * 1e-3), "unit": "queries/s",
-                 "queries": ev["queries"], "kernel": "k_rank_generic", "kernel_ms": ev["kernel_ms"],
-                 "mrr_tail": ev["mrr_t"], "hits10_tail": ev["hits10_t"]},
+                 "queries": ev["queries"], "kernel": "k_rank_dot_tc (tcgen05 kind::tf32) + k_rank_dot_fix/filter",
+                 "mrr": ev["mrr"], "hits10": ev["hits10"],
+                 "roofline": {"bound": "tensor", "achieved": ev["gemm_tflops"], "peak": pk["bf16_tflops"] / 2,
+                              "unit": "TFLOP/s", "frac": (ev["gemm_tflops"] or 0) / (pk["bf16_tflops"] / 2),
+                              "peak_note": "tf32 dense = measured bf16 cuBLAS burst / 2 (MEASURED_PEAKS.json has no tf32 entry)",
+                              "algorithmic_flops_per_launch": 2.0 * W["n_ent"] * W["d"] * W["eval_Q"] / world,
+                              "avg_launch_ms": ev["gemm_ms"], "fixup_filter_ms": ev["fix_ms"], "traffic": None},
+                 "cpu_baseline": cpu_ev},
         "final_loss": r["loss"],
     }
     print(json.dumps(out))

@@ -153,8 +153,9 @@ int kge_rank(kge_ctx*, const kge_cfg*, const kge_tables*, const void* queries, i
 /* Per-phase device timing (CUDA events recorded on the call's stream, read back only at
  * kge_profile_end: no sync inside the timed region).  Phases: 0 constraint, 1 fused
  * sample+gather+score+loss+backward, 2 partial reduction, 3 record sort, 4 row update,
- * 5 ranking.  phase_ms[p] = summed milliseconds over the n_calls recorded calls. */
-#define KGE_N_PHASES 6
+ * 5 ranking (whole call), 6 ranking: tensor-core GEMM kernel alone, 7 ranking: exact fix-up +
+ * filter kernels.  phase_ms[p] = summed milliseconds over the n_calls recorded calls. */
+#define KGE_N_PHASES 8
 int kge_profile_begin(kge_ctx*, int max_calls);
 int kge_profile_end(kge_ctx*, float* phase_ms /* [KGE_N_PHASES] */, int* n_calls);
 

@@ -12,8 +12,8 @@ SIDE_H, SIDE_T, SIDE_HT = 0, 1, 2
 NS_UNIFORM, NS_TYPED = 0, 1
 T_ENT, T_ENT_PROJ, T_REL_A, T_REL_B = range(4)
 CON_NORMALIZE, CON_CLIP = 0, 1
-N_PHASES = 6
-PHASES = ["constraint", "step", "reduce", "sort", "update", "rank"]
+N_PHASES = 8
+PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm", "rank_fix"]
 
 
 class Table(C.Structure):

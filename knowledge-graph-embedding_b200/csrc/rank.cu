@@ -77,7 +77,7 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
     PhaseTimer ptd(ctx, (cudaStream_t) stream);
     ptd.begin(5);
     if (int rc = rank_dot_tensor(ctx, cfg, tables, queries, Q, side, filter, ent_lo, ent_hi, count_out, ws, ws_bytes,
-                                 (cudaStream_t) stream)) return rc;
+                                 (cudaStream_t) stream, &ptd)) return rc;
     ptd.end(5);
     return KGE_OK;
   }

@@ -15,7 +15,8 @@ inline bool rank_dot_eligible(const kge_cfg* c) {
 struct DotWs {
   int kpad, words_per_q, n_etiles;
   int64_t qblk;                    // queries per launch (multiple of 128)
-  size_t off_qm, off_pos, off_bias, off_hi, off_lo, off_maxn, off_mask, total;
+  size_t off_qm, off_qhi, off_qlo, off_ehi, off_elo, off_pos, off_bias, off_hi, off_lo, off_maxn, off_mask, off_filt, total;
+  int ldE;
 };
 inline void layout_dot_ws(const kge_cfg* c, int64_t Q, int64_t span, DotWs& L) {
   L.kpad = (c->d_ent + TC_BK - 1) / TC_BK * TC_BK;
@@ -31,11 +32,17 @@ inline void layout_dot_ws(const kge_cfg* c, int64_t Q, int64_t span, DotWs& L) {
   auto take = [&](size_t b) { size_t at = o; o += align_up(b); return at; };
   L.off_maxn = take(256);
   L.off_qm = take(sizeof(float) * (size_t) L.qblk * L.kpad);
+  L.off_qhi = take(sizeof(float) * (size_t) L.qblk * L.kpad);
+  L.off_qlo = take(sizeof(float) * (size_t) L.qblk * L.kpad);
+  L.ldE = (c->d_ent + 3) / 4 * 4;
+  L.off_ehi = take(sizeof(float) * (size_t) span * L.ldE);
+  L.off_elo = take(sizeof(float) * (size_t) span * L.ldE);
   L.off_pos = take(sizeof(float) * (size_t) L.qblk);
   L.off_bias = take(sizeof(float) * (size_t) L.qblk);
   L.off_hi = take(sizeof(float) * (size_t) L.qblk);
   L.off_lo = take(sizeof(float) * (size_t) L.qblk);
   L.off_mask = take(sizeof(uint32_t) * (size_t) L.qblk * L.words_per_q);
+  L.off_filt = take(sizeof(uint32_t) * (size_t) L.qblk * L.words_per_q);
   L.total = o;
 }
 
@@ -68,7 +75,7 @@ inline int make_map_2d(CUtensorMap* m, const float* base, uint64_t cols, uint64_
 // count_out[q] += #{e in [ent_lo, ent_hi): score(e) > pos(q), e not filtered}
 inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tables* tables, const void* queries,
                            int64_t Q, int side, const kge_filter* filter, int64_t ent_lo, int64_t ent_hi,
-                           int32_t* count_out, void* ws, size_t ws_bytes, cudaStream_t st) {
+                           int32_t* count_out, void* ws, size_t ws_bytes, cudaStream_t st, PhaseTimer* pt) {
   DotWs L;
   layout_dot_ws(cfg, Q, ent_hi - ent_lo, L);
   KGE_REQUIRE(ws && ws_bytes >= L.total, KGE_EWORKSPACE, "rank workspace %zu < required %zu bytes", ws_bytes, L.total);
@@ -88,24 +95,49 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
     k_rank_maxnorm<<<(unsigned) blocks, 256, 0, st>>>(E.w, E.ld, E.cols, ent_lo, ent_hi, maxn);
     KGE_CUDA_OK(cudaGetLastError());
   }
-  CUtensorMap map_a, map_b;
+  // exact TF32 split of the candidate shard (E = E_hi + E_lo)
+  const int64_t span = ent_hi - ent_lo;
+  float* Ehi = reinterpret_cast<float*>(wsb + L.off_ehi);
+  float* Elo = reinterpret_cast<float*>(wsb + L.off_elo);
+  KGE_REQUIRE(E.ld == L.ldE, KGE_EUNSUPPORTED, "tensor-core ranking needs ld == round4(cols) (got %d)", E.ld);
+  {
+    int64_t blocks = (span * (E.ld / 4) + 255) / 256;
+    if (blocks > (int64_t) ctx->sm_count * 32) blocks = (int64_t) ctx->sm_count * 32;
+    k_rank_split_table<<<(unsigned) blocks, 256, 0, st>>>(E.w, E.ld, E.cols, ent_lo, ent_hi, Ehi, Elo);
+    KGE_CUDA_OK(cudaGetLastError());
+  }
+  CUtensorMap map_ah, map_al, map_bh, map_bl;
   float* Qm = reinterpret_cast<float*>(wsb + L.off_qm);
-  if (int rc = make_map_2d(&map_a, Qm, (uint64_t) L.kpad, (uint64_t) L.qblk, (uint64_t) L.kpad, TC_BM)) return rc;
-  if (int rc = make_map_2d(&map_b, E.w, (uint64_t) E.cols, (uint64_t) ent_hi, (uint64_t) E.ld, TC_BN)) return rc;
+  float* Qhi = reinterpret_cast<float*>(wsb + L.off_qhi);
+  float* Qlo = reinterpret_cast<float*>(wsb + L.off_qlo);
+  if (int rc = make_map_2d(&map_ah, Qhi, (uint64_t) L.kpad, (uint64_t) L.qblk, (uint64_t) L.kpad, TC_BM)) return rc;
+  if (int rc = make_map_2d(&map_al, Qlo, (uint64_t) L.kpad, (uint64_t) L.qblk, (uint64_t) L.kpad, TC_BM)) return rc;
+  if (int rc = make_map_2d(&map_bh, Ehi, (uint64_t) E.cols, (uint64_t) span, (uint64_t) E.ld, TC_BN)) return rc;
+  if (int rc = make_map_2d(&map_bl, Elo, (uint64_t) E.cols, (uint64_t) span, (uint64_t) E.ld, TC_BN)) return rc;
   const size_t idb = cfg->id_dtype ? 8 : 4;
+  const bool filtered = filter && filter->off;
   for (int64_t q0 = 0; q0 < Q; q0 += L.qblk) {
     const int64_t qn = (Q - q0 < L.qblk) ? Q - q0 : L.qblk;
-    KGE_CUDA_OK(cudaMemsetAsync(Qm, 0, sizeof(float) * (size_t) L.qblk * L.kpad, st));
+    KGE_CUDA_OK(cudaMemsetAsync(wsb + L.off_qm, 0, 3 * align_up(sizeof(float) * (size_t) L.qblk * L.kpad), st));
     DotPrepParams pp;
     fill_model_dev(cfg, tables, pp.md);
     pp.queries = (const char*) queries + (size_t) q0 * 3 * idb; pp.id64 = cfg->id_dtype; pp.Q = qn; pp.side = side;
-    pp.Qm = Qm; pp.kpad = L.kpad;
+    pp.Qm = Qm; pp.Qhi = Qhi; pp.Qlo = Qlo; pp.kpad = L.kpad;
     pp.pos = reinterpret_cast<float*>(wsb + L.off_pos); pp.bias = reinterpret_cast<float*>(wsb + L.off_bias);
     pp.thr_hi = reinterpret_cast<float*>(wsb + L.off_hi); pp.thr_lo = reinterpret_cast<float*>(wsb + L.off_lo);
     pp.maxnorm_bits = maxn;
-    pp.eps = 2.0e-3f + 2.5e-7f * (float) L.kpad;      // 2^-9 (two TF32 truncations) + fp32 accumulation slack
+    // dropped q_lo.e_lo (2^-20) + truncation of the lo parts (2 * 2^-21) + fp32 accumulation of 3*kpad terms
+    pp.eps = 4.0e-6f + 3.6e-7f * (float) L.kpad;
     k_rank_dot_prep<<<(unsigned) ((qn + 7) / 8), 256, 0, st>>>(pp);
     KGE_CUDA_OK(cudaGetLastError());
+    uint32_t* filt = nullptr;
+    if (filtered) {
+      filt = reinterpret_cast<uint32_t*>(wsb + L.off_filt);
+      KGE_CUDA_OK(cudaMemsetAsync(filt, 0, sizeof(uint32_t) * (size_t) qn * L.words_per_q, st));
+      k_rank_filter_bits<<<(unsigned) ((qn + 7) / 8), 256, 0, st>>>(filter->off + q0, filter->ids, qn, ent_lo, ent_hi,
+                                                                    filt, L.words_per_q);
+      KGE_CUDA_OK(cudaGetLastError());
+    }
 
     DotTcParams tp;
     tp.n_kc = L.kpad / TC_BK; tp.Q = qn; tp.n_qblocks = (int) ((qn + TC_BM - 1) / TC_BM);
@@ -115,24 +147,23 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
     tp.n_split = split;
     tp.thr_hi = pp.thr_hi; tp.thr_lo = pp.thr_lo; tp.count = count_out + q0;
     tp.mask = reinterpret_cast<uint32_t*>(wsb + L.off_mask); tp.words_per_q = L.words_per_q;
+    tp.filt = filt;
     int grid = tp.n_qblocks * split;
     if (grid > ctx->sm_count) grid = ctx->sm_count;
-    k_rank_dot_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(map_a, map_b, tp);
+    const bool timed = (q0 == 0);           // phase slots hold one interval per call: time the first query block
+    if (timed) pt->begin(6);
+    k_rank_dot_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(map_ah, map_al, map_bh, map_bl, tp);
     KGE_CUDA_OK(cudaGetLastError());
+    if (timed) { pt->end(6); pt->begin(7); }
 
     DotFixParams fp;
     fp.Qm = Qm; fp.kpad = L.kpad; fp.E = E.w; fp.ldE = E.ld; fp.cols = E.cols;
     fp.pos = pp.pos; fp.bias = pp.bias; fp.mask = tp.mask; fp.words_per_q = L.words_per_q;
-    fp.Q = qn; fp.ent_lo = ent_lo; fp.ent_hi = ent_hi; fp.count = count_out + q0;
-    fp.f_off = (filter && filter->off) ? filter->off + q0 : nullptr;
-    fp.f_ids = filter ? filter->ids : nullptr;
+    fp.Q = qn; fp.ent_lo = ent_lo; fp.count = count_out + q0;
     const int64_t fix_warps = qn * ((L.words_per_q + 31) / 32);
     k_rank_dot_fix<<<(unsigned) ((fix_warps + 7) / 8), 256, 0, st>>>(fp);
     KGE_CUDA_OK(cudaGetLastError());
-    if (fp.f_off) {
-      k_rank_dot_filter<<<(unsigned) ((qn + 7) / 8), 256, 0, st>>>(fp);
-      KGE_CUDA_OK(cudaGetLastError());
-    }
+    if (timed) pt->end(7);
   }
   return KGE_OK;
 }

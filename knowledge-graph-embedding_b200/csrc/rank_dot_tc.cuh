@@ -3,31 +3,38 @@
 //
 //   scores[Q x N] = Qm[Q x d] . E^T[d x N]  (+ bias_q),    rank count = #{e : score > pos_q}
 //
-// The score matrix is never written.  Tensor cores run kind::tf32 straight off the fp32
-// tables (TMA -> 128B-swizzled shared memory -> tcgen05.mma -> TMEM); TF32 drops 13 mantissa
-// bits, so the GEMM only DECIDES candidates that are clear of the true score by more than a
-// rigorous error bound delta_q = eps * ||q|| * max||e||:
+// The score matrix is never written.  Tensor cores run kind::tf32 (TMA -> 128B-swizzled
+// shared memory -> tcgen05.mma -> TMEM).  TF32 keeps 11 significant bits, so both operands are
+// split exactly, x = x_hi + x_lo with x_hi TF32-representable, and three MMAs per K step
+// accumulate q_hi.e_hi + q_lo.e_hi + q_hi.e_lo ("3xTF32").  What is dropped (q_lo.e_lo, the
+// truncation of the lo parts, fp32 accumulation) is bounded rigorously and the GEMM only
+// DECIDES candidates clear of the true score by more than delta_q = eps * ||q|| * max||e||:
 //      s_tc >  pos + delta            -> counted by the epilogue            (definite win)
 //      s_tc <  pos - delta            -> dropped                            (definite loss)
 //      otherwise                      -> one bit in an "uncertain" mask
-// and k_rank_fix re-scores the uncertain candidates in fp32 with the very function that
-// produced pos_q (warp_dot_exact), so the final integer counts equal an all-fp32 ranking
-// (SURVEY.md H3).  Known positives are then subtracted by k_rank_filter (CSR subtraction,
-// SURVEY.md App. F).  All counters are integers: results do not depend on scheduling.
+// and k_rank_dot_fix re-scores the (few) uncertain candidates in fp32 with the very function
+// that produced pos_q (warp_dot_exact), so the final integer counts equal an all-fp32 ranking
+// (SURVEY.md H3).  Known positives are a per-query bitmask over the candidate shard
+// (k_rank_filter_bits, built from the CSR filter) that the epilogue ANDs out of both the win
+// and the uncertain masks.  All counters are integers: results do not depend on scheduling.
 //
 // Kernel roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
-// warps 2-5 = epilogue (one TMEM lane quarter each).  4-stage smem ring (A 128x32 + B 256x32
-// fp32 per stage), two 256-column TMEM accumulators so the epilogue of tile i overlaps the
-// MMAs of tile i+1.
+// warps 2-5 = epilogue (one TMEM lane quarter each).  2-stage smem ring (A_hi, A_lo 128x32 and
+// B_hi, B_lo 256x32 fp32 per stage = 96 KB), two 256-column TMEM accumulators so the epilogue
+// of tile i overlaps the MMAs of tile i+1.
 #pragma once
 #include "tc_ptx.cuh"
 #include "rank_kernels.cuh"
 
 namespace kge {
 
-constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 32, TC_STAGES = 4, TC_THREADS = 192;
+constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 32, TC_STAGES = 2, TC_THREADS = 192;
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 4, TC_B_BYTES = TC_BN * TC_BK * 4;
-constexpr int TC_SMEM_BYTES = TC_STAGES * (TC_A_BYTES + TC_B_BYTES) + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int TC_STAGE_BYTES = 2 * TC_A_BYTES + 2 * TC_B_BYTES;          // hi and lo of both operands
+constexpr int TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+
+// exact split x = hi + lo with hi representable in TF32 (low 13 mantissa bits clear)
+__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 
 // fp32 dot of two rows with a fixed evaluation order: THE reference arithmetic of this path
 // (pos_q, the re-scored uncertain candidates and the filtered candidates all come from it).
@@ -45,6 +52,7 @@ struct DotPrepParams {
   ModelDev md;
   const void* queries; int id64; int64_t Q; int side;
   float* Qm; int kpad;            // [Qpad x kpad], zero padded
+  float* Qhi; float* Qlo;         // exact TF32 split of Qm
   float* pos;                     // exact score of the true triple
   float* bias;                    // per-query additive term (TransE head side: r . t)
   float* thr_hi; float* thr_lo;   // thresholds on the raw tensor-core dot
@@ -104,6 +112,11 @@ __global__ void __launch_bounds__(256) k_rank_dot_prep(const DotPrepParams p) {
     bias = warp_sum(bpart);
   }
   __syncwarp();
+  for (int j = lane; j < d; j += WARP) {
+    const float v = qm[j], hi = tf32_hi(v);
+    p.Qhi[q * (int64_t) p.kpad + j] = hi;
+    p.Qlo[q * (int64_t) p.kpad + j] = v - hi;
+  }
   const int nch = (d + 3) >> 2;
   const float nq = sqrtf(warp_dot_exact(qm, qm, nch, lane));
   const float pos = warp_dot_exact(qm, truth, nch, lane) + bias;
@@ -115,6 +128,31 @@ __global__ void __launch_bounds__(256) k_rank_dot_prep(const DotPrepParams p) {
   }
 }
 
+// E_hi / E_lo of the candidate shard (row e - lo of the outputs)
+__global__ void __launch_bounds__(256) k_rank_split_table(const float* w, int ld, int cols, int64_t lo, int64_t hi,
+                                                           float* out_hi, float* out_lo) {
+  const int nch = ld >> 2;
+  const int64_t total = (hi - lo) * nch;
+  for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(w + lo * (int64_t) ld) + i);
+    const float4 h = f4(tf32_hi(v.x), tf32_hi(v.y), tf32_hi(v.z), tf32_hi(v.w));
+    reinterpret_cast<float4*>(out_hi)[i] = h;
+    reinterpret_cast<float4*>(out_lo)[i] = v - h;
+  }
+}
+
+// CSR filter -> per-query bitmask over the candidate shard (bit = excluded)
+__global__ void __launch_bounds__(256) k_rank_filter_bits(const int64_t* f_off, const int64_t* f_ids, int64_t Q,
+                                                          int64_t ent_lo, int64_t ent_hi, uint32_t* bits, int words_per_q) {
+  const int lane = threadIdx.x & 31;
+  const int64_t q = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (q >= Q) return;
+  for (int64_t f = f_off[q] + lane; f < f_off[q + 1]; f += WARP) {
+    const int64_t e = f_ids[f];
+    if (e >= ent_lo && e < ent_hi) atomicOr(bits + q * (int64_t) words_per_q + ((e - ent_lo) >> 5), 1u << ((e - ent_lo) & 31));
+  }
+}
+
 struct DotTcParams {
   int n_kc;                       // K chunks of 32
   int64_t Q; int n_qblocks;
@@ -123,22 +161,24 @@ struct DotTcParams {
   const float* thr_hi; const float* thr_lo;
   int32_t* count;
   uint32_t* mask; int words_per_q;
+  const uint32_t* filt;           // nullable: excluded-candidate bits, same indexing as mask
 };
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
-k_rank_dot_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const DotTcParams p) {
+k_rank_dot_tc(const __grid_constant__ CUtensorMap map_ah, const __grid_constant__ CUtensorMap map_al,
+              const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl, const DotTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
-  uint8_t* sA = smem;
-  uint8_t* sB = smem + TC_STAGES * TC_A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TC_STAGES * (TC_A_BYTES + TC_B_BYTES));
+  // stage s: [A_hi | A_lo | B_hi | B_lo], every tile 1024-byte aligned
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TC_STAGES * TC_STAGE_BYTES);
   uint64_t* full = bars; uint64_t* empty = bars + TC_STAGES;
   uint64_t* tfull = bars + 2 * TC_STAGES; uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) {
-    tc::tma_prefetch_desc(&map_a); tc::tma_prefetch_desc(&map_b);
+    tc::tma_prefetch_desc(&map_ah); tc::tma_prefetch_desc(&map_al);
+    tc::tma_prefetch_desc(&map_bh); tc::tma_prefetch_desc(&map_bl);
     for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); }
     for (int a = 0; a < 2; ++a) { tc::mbar_init(tfull + a, 1); tc::mbar_init(tempty + a, 4); }
     tc::mbar_fence_init();
@@ -162,9 +202,12 @@ k_rank_dot_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
           for (int kc = 0; kc < p.n_kc; ++kc, ++it) {
             const int s = it % TC_STAGES; const uint32_t ph = (it / TC_STAGES) & 1;
             tc::mbar_wait(empty + s, ph ^ 1);
-            tc::mbar_expect_tx(full + s, TC_A_BYTES + TC_B_BYTES);
-            tc::tma_load_2d(sA + s * TC_A_BYTES, &map_a, kc * TC_BK, qb * TC_BM, full + s);
-            tc::tma_load_2d(sB + s * TC_B_BYTES, &map_b, kc * TC_BK, (int) (p.ent_lo + (int64_t) et * TC_BN), full + s);
+            uint8_t* st = smem + s * TC_STAGE_BYTES;
+            tc::mbar_expect_tx(full + s, TC_STAGE_BYTES);
+            tc::tma_load_2d(st, &map_ah, kc * TC_BK, qb * TC_BM, full + s);
+            tc::tma_load_2d(st + TC_A_BYTES, &map_al, kc * TC_BK, qb * TC_BM, full + s);
+            tc::tma_load_2d(st + 2 * TC_A_BYTES, &map_bh, kc * TC_BK, et * TC_BN, full + s);        // shard-relative rows
+            tc::tma_load_2d(st + 2 * TC_A_BYTES + TC_B_BYTES, &map_bl, kc * TC_BK, et * TC_BN, full + s);
           }
       }
     }
@@ -183,11 +226,17 @@ k_rank_dot_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
             const int s = it % TC_STAGES; const uint32_t ph = (it / TC_STAGES) & 1;
             tc::mbar_wait(full + s, ph);
             tc::tc_fence_after();
-            const uint64_t da = tc::smem_desc_k_sw128(tc::smem_u32(sA + s * TC_A_BYTES));
-            const uint64_t db = tc::smem_desc_k_sw128(tc::smem_u32(sB + s * TC_B_BYTES));
+            const uint32_t sbase = tc::smem_u32(smem + s * TC_STAGE_BYTES);
+            const uint64_t dah = tc::smem_desc_k_sw128(sbase), dal = tc::smem_desc_k_sw128(sbase + TC_A_BYTES);
+            const uint64_t dbh = tc::smem_desc_k_sw128(sbase + 2 * TC_A_BYTES);
+            const uint64_t dbl = tc::smem_desc_k_sw128(sbase + 2 * TC_A_BYTES + TC_B_BYTES);
+            const uint32_t td = tmem_base + acc * TC_BN;
 #pragma unroll
-            for (int k = 0; k < TC_BK / 8; ++k)      // UMMA K = 8 tf32 = 32 bytes = 2 descriptor units
-              tc::mma_tf32(tmem_base + acc * TC_BN, da + 2 * k, db + 2 * k, idesc, (kc | k) ? 1u : 0u);
+            for (int k = 0; k < TC_BK / 8; ++k) {    // UMMA K = 8 tf32 = 32 bytes = 2 descriptor units
+              tc::mma_tf32(td, dah + 2 * k, dbh + 2 * k, idesc, (kc | k) ? 1u : 0u);     // q_hi . e_hi
+              tc::mma_tf32(td, dal + 2 * k, dbh + 2 * k, idesc, 1u);                     // q_lo . e_hi
+              tc::mma_tf32(td, dah + 2 * k, dbl + 2 * k, idesc, 1u);                     // q_hi . e_lo
+            }
             tc::mma_commit(empty + s);               // frees the smem stage when these MMAs retire
           }
           tc::mma_commit(tfull + acc);
@@ -214,15 +263,20 @@ k_rank_dot_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
           tc::tmem_ld_32x32(tmem_base + ((uint32_t) (quarter * 32) << 16) + acc * TC_BN + c * 32, v);
           tc::tmem_ld_wait();
           const int64_t e0 = p.ent_lo + (int64_t) et * TC_BN + c * 32;
-          uint32_t m = 0;
+          uint32_t win = 0, unc = 0;
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const float s = __uint_as_float(v[j]);
-            const bool valid = e0 + j < p.ent_hi;
-            cnt += (valid && s > hi) ? 1 : 0;
-            m |= (valid && !(s > hi) && s >= lo) ? (1u << j) : 0u;
+            win |= (s > hi) ? (1u << j) : 0u;
+            unc |= (s >= lo) ? (1u << j) : 0u;
           }
-          if (live) p.mask[q * (int64_t) p.words_per_q + et * (TC_BN / 32) + c] = m;
+          const int64_t left = p.ent_hi - e0;                      // candidates left in the shard
+          uint32_t ok = left >= 32 ? 0xFFFFFFFFu : (left > 0 ? ((1u << left) - 1u) : 0u);
+          const int64_t widx = q * (int64_t) p.words_per_q + et * (TC_BN / 32) + c;
+          if (live && p.filt) ok &= ~__ldg(p.filt + widx);         // known positives never count
+          win &= ok;
+          cnt += __popc(win);
+          if (live) p.mask[widx] = unc & ~win & ok;
         }
         tc::tc_fence_before();
         __syncwarp();
@@ -243,8 +297,6 @@ struct DotFixParams {
   const uint32_t* mask; int words_per_q;
   int64_t Q, ent_lo;
   int32_t* count;
-  const int64_t* f_off; const int64_t* f_ids;     // filter (nullable), ids unique per query
-  int64_t ent_hi;
 };
 
 // uncertain candidates -> exact fp32 score; one warp per (query, 32 mask words)
@@ -276,24 +328,6 @@ __global__ void __launch_bounds__(256) k_rank_dot_fix(const DotFixParams p) {
     }
   }
   if (lane == 0 && cnt) atomicAdd(p.count + q, cnt);
-}
-
-// known positives: subtract those that out-score the true triple (they were counted above)
-__global__ void __launch_bounds__(256) k_rank_dot_filter(const DotFixParams p) {
-  const int lane = threadIdx.x & 31;
-  const int64_t q = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (q >= p.Q) return;
-  const float* qm = p.Qm + q * (int64_t) p.kpad;
-  const float pos = p.pos[q], bias = p.bias[q];
-  const int nch = (p.cols + 3) >> 2;
-  int cnt = 0;
-  for (int64_t f = p.f_off[q]; f < p.f_off[q + 1]; ++f) {
-    const int64_t e = p.f_ids[f];
-    if (e < p.ent_lo || e >= p.ent_hi) continue;
-    const float s = warp_dot_exact(qm, p.E + e * (int64_t) p.ldE, nch, lane) + bias;
-    cnt += (s > pos) ? 1 : 0;
-  }
-  if (lane == 0 && cnt) atomicSub(p.count + q, cnt);
 }
 
 }  // namespace kge
