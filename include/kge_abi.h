@@ -8,8 +8,11 @@
  * Conventions
  *  - plain C, no CUDA / torch types: device pointers are void* / float*, the stream
  *    is a cudaStream_t passed as void*.
- *  - the caller owns every buffer (tables, workspace, outputs); the library never
- *    allocates, frees or retains device memory across calls.
+ *  - the caller owns every buffer (tables, workspace, outputs); compute calls never
+ *    allocate, free or retain device memory.  The context itself owns a 256-byte
+ *    device counter block and one side stream (kge_train_step forks the key sort onto
+ *    it and joins before returning control of the caller's stream), so one context
+ *    serves one call at a time.
  *  - every call enqueues on the given stream and returns; no host sync.
  *  - return 0 on success, a negative kge_status otherwise; kge_last_error() gives the
  *    thread-local message.  There is no CPU fallback: without a CUDA device the

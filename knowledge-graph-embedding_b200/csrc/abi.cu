@@ -34,6 +34,13 @@ extern "C" int kge_ctx_create(int device, kge_ctx** out) {
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
   c->smem_optin = (int) prop.sharedMemPerBlockOptin;
+  int prio_least = 0, prio_greatest = 0;     // side stream first: its small kernels fill SMs the step kernel frees
+  KGE_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+  KGE_CUDA_OK(cudaStreamCreateWithPriority(&c->aux, cudaStreamNonBlocking, prio_greatest));
+  KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+  KGE_CUDA_OK(cudaMalloc(&c->ticket, 64 * sizeof(unsigned)));
+  KGE_CUDA_OK(cudaMemset(c->ticket, 0, 64 * sizeof(unsigned)));
   *out = reinterpret_cast<kge_ctx*>(c);
   return KGE_OK;
 }
@@ -46,7 +53,13 @@ static void free_events(kge_ctx_impl* c) {
 }
 extern "C" int kge_ctx_destroy(kge_ctx* ctx) {
   auto* c = reinterpret_cast<kge_ctx_impl*>(ctx);
-  if (c) free_events(c);
+  if (c) {
+    free_events(c);
+    if (c->aux) { cudaStreamSynchronize(c->aux); cudaStreamDestroy(c->aux); }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->ticket) cudaFree(c->ticket);
+  }
   delete c;
   return KGE_OK;
 }

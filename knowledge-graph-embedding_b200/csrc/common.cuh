@@ -34,6 +34,11 @@ struct kge_ctx_impl {
   cudaEvent_t* ev = nullptr;
   unsigned* ev_mask = nullptr;
   int prof_cap = 0, prof_n = 0;
+  // side stream of kge_train_step (sort keys are independent of the weights, so key generation,
+  // the radix sort and the segment table overlap the step kernel) + its fork / join events
+  cudaStream_t aux = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  unsigned* ticket = nullptr;     // device, 64 words, zero between calls (self-resetting counters)
 };
 // RAII marker: records the boundary events of one call when profiling is on
 struct PhaseTimer {
@@ -41,9 +46,11 @@ struct PhaseTimer {
   PhaseTimer(kge_ctx_impl* c_, cudaStream_t s) : c(c_), st(s), slot(-1) {
     if (c->ev && c->prof_n < c->prof_cap) { slot = c->prof_n++; c->ev_mask[slot] = 0; }
   }
-  void begin(int phase) { if (slot >= 0) cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + 2 * phase], st); }
-  void end(int phase) {
-    if (slot >= 0) { cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + 2 * phase + 1], st); c->ev_mask[slot] |= 1u << phase; }
+  void begin(int phase) { begin(phase, st); }
+  void end(int phase) { end(phase, st); }
+  void begin(int phase, cudaStream_t s) { if (slot >= 0) cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + 2 * phase], s); }
+  void end(int phase, cudaStream_t s) {
+    if (slot >= 0) { cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + 2 * phase + 1], s); c->ev_mask[slot] |= 1u << phase; }
   }
 };
 
@@ -181,10 +188,10 @@ __device__ __forceinline__ int64_t sample_negative(const SamplerDev& sd, int64_t
   bool head = neg_is_head(sd, c);
   int jj = (sd.side_mode == KGE_SIDE_HT) ? (c >> 1) : c;
   uint64_t n = (uint64_t) i * (uint64_t) sd.k_side + (uint64_t) jj;
-  uint64_t u = philox_word0(sd.seed, sd.step, head ? 0u : 1u, n);
-  if (sd.kind == KGE_NS_UNIFORM) {
-    if (sd.s.pool == nullptr) return (int64_t)(u % (uint64_t) sd.n_ent);
-    return sd.s.pool[u % (uint64_t) sd.s.pool_len];
+  const uint32_t u = philox_word0(sd.seed, sd.step, head ? 0u : 1u, n);
+  if (sd.kind == KGE_NS_UNIFORM) {      // 32-bit modulo: n_ent < 2^32 is checked on the host
+    if (sd.s.pool == nullptr) return (int64_t) ((uint32_t) u % (uint32_t) sd.n_ent);
+    return sd.s.pool[(uint32_t) u % (uint32_t) sd.s.pool_len];
   }
   int64_t x = head ? h : t;
   int64_t ty = sd.s.ent_type[x];
@@ -192,7 +199,7 @@ __device__ __forceinline__ int64_t sample_negative(const SamplerDev& sd, int64_t
   int64_t q = sd.s.ent_pos[x];
   int64_t eff = (q >= 0) ? len - 1 : len;
   if (eff <= 0) return x;   // host rejects singleton pools before launch
-  int64_t j = (int64_t)(u % (uint64_t) eff);
+  int64_t j = (int64_t) ((uint32_t) u % (uint32_t) eff);
   if (q >= 0 && j >= q) ++j;
   return sd.s.type_members[lo + j];
 }

@@ -132,6 +132,7 @@ inline int check_sampler(const kge_cfg* c, const kge_sampler* s) {
   } else {
     KGE_REQUIRE(c->sampler == KGE_NS_UNIFORM, KGE_EINVAL, "bad sampler id %d", c->sampler);
     KGE_REQUIRE(!(s && s->pool) || s->pool_len > 0, KGE_EINVAL, "uniform sampler pool is empty");
+    KGE_REQUIRE(!(s && s->pool) || (uint64_t) s->pool_len < 0xffffffffull, KGE_EUNSUPPORTED, "uniform sampler pool too long");
   }
   return KGE_OK;
 }

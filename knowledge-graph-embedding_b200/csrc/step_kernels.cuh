@@ -13,6 +13,7 @@
 #pragma once
 #include "models.cuh"
 #include "loss.cuh"
+#include "reduce_tail.cuh"
 
 namespace kge {
 
@@ -35,7 +36,23 @@ struct StepParams {
   uint32_t* keys;                // [2B + B*k_eff + B]
   uint32_t* vals;                // iota over the same range
   float* part;                   // [N_PART][B]
+  int write_keys;                // 0: sort keys / negatives are produced by k_keys on the side stream
+  int tail;                      // 1: the last warp to finish reduces the partials (no k_reduce launch)
+  unsigned* done;                // ticket counter for the tail reduction (self-resetting)
+  ReduceParams rp;
 };
+
+// ticket handshake: the caller's stores are fenced; returns true in the last warp to arrive
+__device__ __forceinline__ bool last_warp_done(unsigned* done, unsigned total, int lane) {
+  __threadfence();
+  unsigned t = 0;
+  if (lane == 0) t = atomicAdd(done, 1u);
+  t = __shfl_sync(FULL, t, 0);
+  if (t != total - 1) return false;
+  if (lane == 0) *done = 0u;
+  __threadfence();
+  return true;
+}
 
 __device__ __forceinline__ void group_barrier(int grp, int wpp) {
   if (wpp == 1) { __syncwarp(); return; }
@@ -105,13 +122,33 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
   float lsum = 0.f, gpos = 0.f;
   const int64_t nE = 2 * p.B + p.B * (int64_t) k;
 
-  for (int c = wig; c < k; c += wpp) {
+  // Negative ids: lane l draws the id of this warp's (it0 + l)-th negative, so the ~100
+  // instruction Philox runs once per 32 negatives per lane instead of once per negative per
+  // warp; the next negative's rows are requested before the current one is processed.
+  const int n_it = (k - wig + wpp - 1) / wpp;
+  int64_t my_e = 0;
+  auto draw = [&](int it0) {
+    const int c = wig + (it0 + lane) * wpp;
+    if (c < k) my_e = p.neg_override ? p.neg_override[i * k + c] : sample_negative(p.sd, i, c, h, t);
+  };
+  constexpr bool PREFETCH = (NV <= 2);       // wider rows: the second row in flight would spill
+  Ent Nnext;
+  if (n_it > 0) {
+    draw(0);
+    if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, 0), lane);
+  }
+  for (int it = 0; it < n_it; ++it) {
+    const int c = wig + it * wpp;
     const bool head = neg_is_head(p.sd, c);
     const int64_t slot = i * k + c;
-    const int64_t e = p.neg_override ? p.neg_override[slot] : sample_negative(p.sd, i, c, h, t);
+    const int64_t e = __shfl_sync(FULL, my_e, it & 31);
     Ent N;
-    N.load(md, e, lane);
-    if (lane == 0) {
+    if (PREFETCH) N = Nnext; else N.load(md, e, lane);
+    if (it + 1 < n_it) {
+      if (((it + 1) & 31) == 0) draw(it + 1);
+      if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, (it + 1) & 31), lane);
+    }
+    if (lane == 0 && p.write_keys) {
       p.neg_ids[slot] = e;
       if (TRAIN) { p.keys[2 * p.B + slot] = (uint32_t) e; p.vals[2 * p.B + slot] = (uint32_t)(2 * p.B + slot); }
     }
@@ -225,11 +262,12 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
 #pragma unroll
     for (int q = 0; q < N_PART; ++q) p.part[(size_t) q * p.B + i] = red[q];
   }
+  if (p.tail && last_warp_done(p.done, (unsigned) p.B, lane)) tail_reduce_warp(p.rp, lane);
   if (TRAIN) {
     GH.store(md, p.rec, i, lane);
     GT.store(md, p.rec, p.B + i, lane);
     GR.store(md, p.rec, i, lane);
-    if (lane == 0) {
+    if (lane == 0 && p.write_keys) {
       p.keys[i] = (uint32_t) h;           p.vals[i] = (uint32_t) i;
       p.keys[p.B + i] = (uint32_t) t;     p.vals[p.B + i] = (uint32_t)(p.B + i);
       p.keys[nE + i] = (uint32_t)(md.t[KGE_T_ENT].rows + r);

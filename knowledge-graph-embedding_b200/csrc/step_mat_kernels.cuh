@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_mat(const MatStepParams q
     const int64_t e = p.neg_override ? p.neg_override[slot] : sample_negative(p.sd, i, c, h, t);
     Row<NV> N, CN; float nN;
     sload(N, md.t[KGE_T_ENT].w + e * (int64_t) md.t[KGE_T_ENT].ld, din, lane);
-    if (lane == 0) {
+    if (lane == 0 && p.write_keys) {
       p.neg_ids[slot] = e;
       if (TRAIN) { p.keys[2 * p.B + slot] = (uint32_t) e; p.vals[2 * p.B + slot] = (uint32_t)(2 * p.B + slot); }
     }
@@ -256,10 +256,13 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_mat(const MatStepParams q
       for (int u = 0; u < NV; ++u) mine[(a * NV + u) * WARP + lane] = rows[a]->v[u];
   }
   __syncthreads();
-  if (warp == 0 && lane < N_PART) {
-    float a = 0.f;
-    for (int w2 = 0; w2 < STEP_WARPS; ++w2) a += s_red[w2 * 8 + lane];
-    p.part[(size_t) lane * p.B + i] = a;
+  if (warp == 0) {
+    if (lane < N_PART) {
+      float a = 0.f;
+      for (int w2 = 0; w2 < STEP_WARPS; ++w2) a += s_red[w2 * 8 + lane];
+      p.part[(size_t) lane * p.B + i] = a;
+    }
+    if (p.tail && last_warp_done(p.done, (unsigned) p.B, lane)) tail_reduce_warp(p.rp, lane);
   }
   if (TRAIN && warp < MAT_ACC_ROWS) {
     Row<NV> acc;
@@ -277,7 +280,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_mat(const MatStepParams q
       default: sstore(acc, q.recP + (p.B + i) * (int64_t) q.ldp, dout, lane);
     }
   }
-  if (TRAIN && threadIdx.x == 0) {
+  if (TRAIN && threadIdx.x == 0 && p.write_keys) {
     p.keys[i] = (uint32_t) h;           p.vals[i] = (uint32_t) i;
     p.keys[p.B + i] = (uint32_t) t;     p.vals[p.B + i] = (uint32_t)(p.B + i);
     p.keys[nE + i] = (uint32_t)(md.t[KGE_T_ENT].rows + r);

@@ -12,8 +12,8 @@ namespace kge {
 
 struct StepWs {
   size_t off_part, off_scal, off_neg, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub,
-      off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart;
-  size_t cub_bytes, total;
+      off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart, off_seg;
+  size_t cub_bytes, total, n_seg;
   int64_t n_ent_rec, n_keys, total_rows, n_mat_cta;
   int rld[KGE_MAX_TABLES];
   int ldp;
@@ -67,6 +67,8 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
                                                   sort_bits(c), (cudaStream_t) 0);
   KGE_REQUIRE(e == cudaSuccess, KGE_ECUDA, "cub temp-size query failed: %s", cudaGetErrorString(e));
   L.off_cub = take(L.cub_bytes);
+  L.n_seg = (size_t) c->n_ent + (size_t) c->n_rel;
+  L.off_seg = take(sizeof(uint32_t) * 2 * L.n_seg);         // seg_lo | seg_hi
   L.total_rows = 0;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     L.rld[s] = (cols[s] + 3) / 4 * 4;
@@ -122,6 +124,27 @@ static int launch_constrain(const kge_ctx_impl* ctx, const ConstrainParams& cp, 
   k_constrain<<<(unsigned) blocks, 256, 0, st>>>(cp);
   KGE_CUDA_OK(cudaGetLastError());
   return KGE_OK;
+}
+
+// sort keys, record ids and the negatives used, one thread per record slot; runs on the side
+// stream concurrently with k_step (the keys depend on the ids only, not on any weight)
+__global__ void __launch_bounds__(256) k_keys(const StepParams p) {
+  const int64_t nneg = p.B * (int64_t) p.k_eff, nE = 2 * p.B + nneg;
+  for (int64_t s = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; s < nE + p.B; s += (int64_t) gridDim.x * blockDim.x) {
+    uint32_t key;
+    if (s < 2 * p.B) key = (uint32_t) load_id(p.triples, 3 * (s % p.B) + (s < p.B ? 0 : 2), p.id64);
+    else if (s < nE) {
+      const int64_t slot = s - 2 * p.B, i = slot / p.k_eff;
+      const int c = (int) (slot - i * p.k_eff);
+      const int64_t e = p.neg_override ? p.neg_override[slot]
+                                       : sample_negative(p.sd, i, c, load_id(p.triples, 3 * i, p.id64),
+                                                         load_id(p.triples, 3 * i + 2, p.id64));
+      p.neg_ids[slot] = e;
+      key = (uint32_t) e;
+    } else key = (uint32_t) (p.md.t[KGE_T_ENT].rows + load_id(p.triples, 3 * (s - nE) + 1, p.id64));
+    p.keys[s] = key;
+    p.vals[s] = (uint32_t) s;
+  }
 }
 
 __global__ void k_sample(SamplerDev sd, const void* triples, int id64, int64_t B, int64_t* out) {
@@ -220,13 +243,11 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   int cols[KGE_MAX_TABLES];
   expected_cols(cfg, cols);
 
-  // 1. start-of-batch constraint (train AND validation batches, BaseModel.py:319)
+  // 1. start-of-batch constraint (train AND validation batches, BaseModel.py:319): enqueued by
+  //    fork_side() below, once every argument check has passed
   PhaseTimer pt(ctx, st);
   ConstrainParams cp;
   constraint_jobs(cfg, tables, cp);
-  pt.begin(0);
-  if (int rc = launch_constrain(ctx, cp, st)) return rc;
-  pt.end(0);
 
   // 2. fused sample + gather + score + loss + backward
   MatStepParams mq;
@@ -252,6 +273,51 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   p.keys = reinterpret_cast<uint32_t*>(wsb + L.off_keys_in);
   p.vals = reinterpret_cast<uint32_t*>(wsb + L.off_vals_in);
   p.part = reinterpret_cast<float*>(wsb + L.off_part);
+  // training: keys / record ids / negatives come from k_keys on the side stream
+  p.write_keys = is_train ? 0 : 1;
+  p.tail = (B <= TAIL_REDUCE_MAX_B) ? 1 : 0;
+  p.done = ctx->ticket;
+  p.rp.part = p.part;
+  p.rp.B = B;
+  p.rp.n_part = is_train ? N_PART : 1;
+  p.rp.clip_norm = cfg->clip_norm;
+  p.rp.scal = reinterpret_cast<float*>(wsb + L.off_scal);
+  p.rp.loss_out = loss_out;
+
+  // side stream: sort keys depend on ids only, so key generation, the stable radix sort and the
+  // segment table run concurrently with the step kernel and join before the update kernels
+  uint32_t* keys_out = reinterpret_cast<uint32_t*>(wsb + L.off_keys_out);
+  uint32_t* vals_out = reinterpret_cast<uint32_t*>(wsb + L.off_vals_out);
+  uint32_t* seg_lo = reinterpret_cast<uint32_t*>(wsb + L.off_seg);
+  uint32_t* seg_hi = seg_lo + L.n_seg;
+  auto fork_side = [&]() -> int {
+    if (!is_train) {
+      pt.begin(0);
+      if (int rc2 = launch_constrain(ctx, cp, st)) return rc2;
+      pt.end(0);
+      return KGE_OK;
+    }
+    cudaStream_t ax = ctx->aux;
+    KGE_CUDA_OK(cudaEventRecord(ctx->ev_fork, st));
+    KGE_CUDA_OK(cudaStreamWaitEvent(ax, ctx->ev_fork, 0));
+    pt.begin(3, ax);
+    int64_t kb = (L.n_keys + 255) / 256;
+    if (kb > (int64_t) ctx->sm_count * 8) kb = (int64_t) ctx->sm_count * 8;
+    k_keys<<<(unsigned) kb, 256, 0, ax>>>(p);
+    KGE_CUDA_OK(cudaGetLastError());
+    KGE_CUDA_OK(cudaMemsetAsync(seg_lo, 0, sizeof(uint32_t) * 2 * L.n_seg, ax));
+    size_t cub_bytes = L.cub_bytes;
+    KGE_CUDA_OK(cub::DeviceRadixSort::SortPairs(wsb + L.off_cub, cub_bytes, (const uint32_t*) p.keys, keys_out,
+                                                (const uint32_t*) p.vals, vals_out, (int) L.n_keys, 0, sort_bits(cfg), ax));
+    k_segments<<<(unsigned) ((L.n_keys + 255) / 256), 256, 0, ax>>>(keys_out, L.n_keys, seg_lo, seg_hi);
+    KGE_CUDA_OK(cudaGetLastError());
+    pt.end(3, ax);
+    KGE_CUDA_OK(cudaEventRecord(ctx->ev_join, ax));
+    pt.begin(0);
+    if (int rc2 = launch_constrain(ctx, cp, st)) return rc2;
+    pt.end(0);
+    return KGE_OK;
+  };
 
   StepLaunch SL;
   SL.nv = nv;
@@ -265,6 +331,7 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
     SL.grid = (B + ppc - 1) / ppc;
     SL.smem = step_smem_bytes(nv, p.wpp, k, ent_rows, rel_rows);
     KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step needs %zu B shared memory", SL.smem);
+    if (int rc2 = fork_side()) return rc2;      // after the last argument check
     pt.begin(1);
     switch (cfg->model) {
       case KGE_UM: rc = launch_step_um(p, SL); break;
@@ -285,6 +352,7 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
     mq.stage = SL.smem <= (size_t) ctx->smem_optin;
     if (!mq.stage) SL.smem = step_mat_smem_bytes(nv, k, mq.dpad, SL.train, false, n_mats, mat_rows(cfg), mat_cols(cfg));
     KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step_mat needs %zu B shared memory", SL.smem);
+    if (int rc2 = fork_side()) return rc2;      // after the last argument check
     pt.begin(1);
     switch (cfg->model) {
       case KGE_SE: rc = launch_step_se(mq, SL); break;
@@ -292,37 +360,25 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
       default: rc = launch_step_rescal(mq, SL);
     }
   }
-  if (rc) return rc;
+  if (rc) { if (is_train) cudaStreamWaitEvent(st, ctx->ev_join, 0); return rc; }
   pt.end(1);
 
   // 3. loss + per-table clip scales (sparse-gradient tables)
-  ReduceParams rp;
-  rp.part = p.part;
-  rp.B = B;
-  rp.n_part = is_train ? N_PART : 1;
-  rp.clip_norm = cfg->clip_norm;
-  rp.scal = reinterpret_cast<float*>(wsb + L.off_scal);
-  rp.loss_out = loss_out;
-  pt.begin(2);
-  k_reduce<<<1, 1024, 0, st>>>(rp);
-  KGE_CUDA_OK(cudaGetLastError());
-  pt.end(2);
+  const ReduceParams& rp = p.rp;
+  if (!p.tail) {
+    pt.begin(2);
+    k_reduce<<<1, 1024, 0, st>>>(rp);
+    KGE_CUDA_OK(cudaGetLastError());
+    pt.end(2);
+  }
+  if (is_train) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));     // join the side stream
   if (neg_out)
     KGE_CUDA_OK(cudaMemcpyAsync(neg_out, p.neg_ids, sizeof(int64_t) * (size_t) B * k, cudaMemcpyDeviceToDevice, st));
   const bool dense = has_dense_reg(cfg);
   if (!is_train && !dense) return KGE_OK;
 
-  // 4. sort records by (table, row): stable LSD radix sort => occurrence order inside a row
-  uint32_t* keys_out = reinterpret_cast<uint32_t*>(wsb + L.off_keys_out);
-  uint32_t* vals_out = reinterpret_cast<uint32_t*>(wsb + L.off_vals_out);
-  if (is_train) {
-    size_t cub_bytes = L.cub_bytes;
-    pt.begin(3);
-    KGE_CUDA_OK(cub::DeviceRadixSort::SortPairs(wsb + L.off_cub, cub_bytes, (const uint32_t*) p.keys, keys_out,
-                                                (const uint32_t*) p.vals, vals_out, (int) L.n_keys, 0, sort_bits(cfg), st));
-    pt.end(3);
-  }
-
+  // 4. (side stream, above) records sorted by (table, row): stable LSD radix sort => occurrence
+  //    order inside a row
   // 5. per-row segmented sum + clip + Adam (every row of every table, TF semantics)
   UpdateParams up;
   up.n_tabs = 0;
@@ -357,6 +413,7 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   up.keys = keys_out;
   up.vals = vals_out;
   up.n_keys = is_train ? L.n_keys : 0;
+  up.seg_lo = seg_lo; up.seg_hi = seg_hi;
   up.scal = rp.scal;
   const float b1p = powf(cfg->beta1, (float) adam_t), b2p = powf(cfg->beta2, (float) adam_t);
   up.lr_t = cfg->lr * sqrtf(1.0f - b2p) / (1.0f - b1p);
@@ -364,6 +421,9 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   up.cw = cfg->constraint_weight;
   up.rowpart = dense ? reinterpret_cast<float*>(wsb + L.off_rowpart) : nullptr;
   const int64_t ublocks = (up.total_rows + 7) / 8;
+  int max_ch = 1;
+  for (int j = 0; j < up.n_tabs; ++j) max_ch = ((up.tab[j].cols + 3) / 4 > max_ch) ? (up.tab[j].cols + 3) / 4 : max_ch;
+  const int cpl = max_ch <= 32 ? 1 : (max_ch <= 64 ? 2 : (max_ch <= 128 ? 4 : 8));
 
   MatUpdParams mu;
   dim3 mgrid(1, 1, 1);
@@ -385,6 +445,7 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
     mu.triples = triples; mu.id64 = cfg->id_dtype; mu.neg_ids = p.neg_ids;
     mu.B = B; mu.k = k; mu.side_mode = cfg->corrupt_side;
     mu.keys = keys_out; mu.vals = vals_out; mu.n_keys = is_train ? L.n_keys : 0;
+    mu.seg_lo = seg_lo; mu.seg_hi = seg_hi;
     mu.key_base = (uint32_t) cfg->n_ent; mu.rec_base = (uint32_t) L.n_ent_rec;
     mu.scal = rp.scal; mu.lr_t = up.lr_t; mu.beta1 = cfg->beta1; mu.beta2 = cfg->beta2; mu.eps = cfg->eps;
     mu.reg_coef = (dense && cfg->model == KGE_RESCAL) ? 2.0f * cfg->constraint_weight / (float) cfg->n_rel : 0.f;
@@ -403,8 +464,7 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
                                       sizeof(float) * S.ld, sizeof(float) * L.rld[j == 0 ? KGE_T_REL_A : KGE_T_REL_B],
                                       (size_t) S.rows, cudaMemcpyDeviceToDevice, st));
       }
-    k_update<1><<<(unsigned) ublocks, 256, 0, st>>>(up);
-    KGE_CUDA_OK(cudaGetLastError());
+    if (int rc2 = launch_update<1>(up, cpl, ublocks, st)) return rc2;
     rd.rowpart = up.rowpart; rd.total_rows = up.total_rows; rd.n_tabs = up.n_tabs;
     rd.matpart = nullptr; rd.n_mat = 0; rd.mat_slot = KGE_T_REL_A; rd.mat_loss_coef = 0.f;
     if (mat) {
@@ -421,9 +481,7 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
     k_update_mat<0><<<mgrid, MU_THREADS, 0, st>>>(mu);
     KGE_CUDA_OK(cudaGetLastError());
   }
-  if (dense) k_update<2><<<(unsigned) ublocks, 256, 0, st>>>(up);
-  else k_update<0><<<(unsigned) ublocks, 256, 0, st>>>(up);
-  KGE_CUDA_OK(cudaGetLastError());
+  if (int rc2 = dense ? launch_update<2>(up, cpl, ublocks, st) : launch_update<0>(up, cpl, ublocks, st)) return rc2;
   pt.end(4);
   return KGE_OK;
 }

@@ -2,6 +2,7 @@
 // All are model independent: they see tables, records and sorted keys only.
 #pragma once
 #include "common.cuh"
+#include "reduce_tail.cuh"
 
 namespace kge {
 
@@ -42,17 +43,6 @@ __global__ void __launch_bounds__(256) k_constrain(const ConstrainParams p) {
     }
   }
 }
-
-// ---- fixed-order reduction of per-positive partials ---------------------------------
-// scal[0..3] = clip scale per table, scal[4..7] = norm^2 per table, scal[8] = loss.
-struct ReduceParams {
-  const float* part;     // [n_part][B]
-  int64_t B;
-  int n_part;
-  float clip_norm;
-  float* scal;
-  float* loss_out;
-};
 
 __global__ void __launch_bounds__(1024) k_reduce(const ReduceParams p) {
   __shared__ float sm[32];
@@ -107,6 +97,8 @@ struct UpdateParams {
   const uint32_t* keys;  // sorted
   const uint32_t* vals;  // record ids, stable within equal keys
   int64_t n_keys;
+  const uint32_t* seg_lo;  // per key: first sorted position, one past the last (k_segments)
+  const uint32_t* seg_hi;
   const float* scal;
   float lr_t, beta1, beta2, eps;
   float cw;              // constraint_weight
@@ -122,50 +114,105 @@ __device__ __forceinline__ int64_t lower_bound_u32(const uint32_t* a, int64_t n,
   return lo;
 }
 
-// sum of the row's records for float4 chunk c, in sorted (stable) order; record ids are
-// fetched 32 at a time and the row loads are independent, so several are in flight
-// (all 32 lanes must call; lanes whose chunk c is past the row clamp it and discard)
-__device__ __forceinline__ float4 sum_records(const UpdateParams& p, const UpdateTable& T, int64_t lo, int64_t hi,
-                                              int c, int lane) {
-  float4 g = f4zero();
-  for (int64_t q0 = lo; q0 < hi; q0 += WARP) {
-    const int n = (int) ((hi - q0 < WARP) ? hi - q0 : WARP);
-    const uint32_t mine = (lane < n) ? __ldg(p.vals + q0 + lane) - T.rec_base : 0u;
-    int j = 0;
-    for (; j + 4 <= n; j += 4) {
-      const uint32_t r0 = __shfl_sync(FULL, mine, j), r1 = __shfl_sync(FULL, mine, j + 1),
-                     r2 = __shfl_sync(FULL, mine, j + 2), r3 = __shfl_sync(FULL, mine, j + 3);
-      const float4 a0 = __ldg(reinterpret_cast<const float4*>(T.rec + (int64_t) r0 * T.rec_ld) + c);
-      const float4 a1 = __ldg(reinterpret_cast<const float4*>(T.rec + (int64_t) r1 * T.rec_ld) + c);
-      const float4 a2 = __ldg(reinterpret_cast<const float4*>(T.rec + (int64_t) r2 * T.rec_ld) + c);
-      const float4 a3 = __ldg(reinterpret_cast<const float4*>(T.rec + (int64_t) r3 * T.rec_ld) + c);
-      g += a0; g += a1; g += a2; g += a3;
-    }
-    for (; j < n; ++j) {
-      const uint32_t r0 = __shfl_sync(FULL, mine, j);
-      g += __ldg(reinterpret_cast<const float4*>(T.rec + (int64_t) r0 * T.rec_ld) + c);
-    }
-  }
-  return g;
+// ---- segment table: first / one-past-last sorted position of every key -----------------
+// (replaces two binary searches per row; both arrays are zeroed first, absent keys keep lo == hi)
+__global__ void __launch_bounds__(256) k_segments(const uint32_t* __restrict__ keys, int64_t n, uint32_t* seg_lo,
+                                                  uint32_t* seg_hi) {
+  const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t k = keys[i];
+  if (i == 0 || keys[i - 1] != k) seg_lo[k] = (uint32_t) i;
+  if (i == n - 1 || keys[i + 1] != k) seg_hi[k] = (uint32_t) (i + 1);
 }
 
-template <int DENSE>
+// Sum of the records at sorted positions [lo, hi) into the lane's chunks c = lane + 32 u, in
+// sorted (stable) order.  Record ids are fetched 32 at a time; the row loads of 4 records x CPL
+// chunks are independent, so many are in flight.  All 32 lanes must call.
+template <int CPL>
+__device__ __forceinline__ void sum_records(const uint32_t* __restrict__ vals, const float* __restrict__ rec, int rec_ld,
+                                            uint32_t rec_base, int64_t lo, int64_t hi, int nch, int lane,
+                                            float4 (&g)[CPL]) {
+  for (int64_t q0 = lo; q0 < hi; q0 += WARP) {
+    const int n = (int) ((hi - q0 < WARP) ? hi - q0 : WARP);
+    const uint32_t mine = (lane < n) ? __ldg(vals + q0 + lane) - rec_base : 0u;
+    constexpr int J = CPL <= 2 ? 4 : (CPL == 4 ? 2 : 1);       // records in flight (register budget)
+    int j = 0;
+    for (; j + J <= n; j += J) {
+      const float4* r[J];
+#pragma unroll
+      for (int x = 0; x < J; ++x) r[x] = reinterpret_cast<const float4*>(rec + (int64_t) __shfl_sync(FULL, mine, j + x) * rec_ld);
+      float4 a[CPL][J];
+#pragma unroll
+      for (int u = 0; u < CPL; ++u) {
+        const int c = lane + 32 * u;
+#pragma unroll
+        for (int x = 0; x < J; ++x) a[u][x] = (c < nch) ? __ldg(r[x] + c) : f4zero();
+      }
+#pragma unroll
+      for (int u = 0; u < CPL; ++u)
+#pragma unroll
+        for (int x = 0; x < J; ++x) g[u] += a[u][x];
+    }
+    for (; j < n; ++j) {
+      const float4* r0 = reinterpret_cast<const float4*>(rec + (int64_t) __shfl_sync(FULL, mine, j) * rec_ld);
+#pragma unroll
+      for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) g[u] += __ldg(r0 + c); }
+    }
+  }
+}
+
+constexpr int UPD_HEAVY = 48;     // rows with more records are summed by the whole CTA
+
+// One warp per table row (8 rows per CTA); CPL = float4 chunks per lane (row width <= 128*CPL floats).
+template <int DENSE, int CPL>
 __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
-  const int lane = threadIdx.x & 31;
-  const int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (gw >= p.total_rows) return;
-  int64_t row = gw;
+  __shared__ float4 s_part[8][CPL * WARP];
+  __shared__ int s_lo[8], s_hi[8], s_tab[8], s_heavy[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t gw = (int64_t) blockIdx.x * 8 + warp;
+  const bool valid = gw < p.total_rows;
+  int64_t row = valid ? gw : 0;
   int j = 0;
   while (j < p.n_tabs - 1 && row >= p.tab[j].rows) { row -= p.tab[j].rows; ++j; }
   const UpdateTable& T = p.tab[j];
-  const uint32_t key = T.key_base + (uint32_t) row;
-  int64_t lo = 0, hi = 0;
-  if (T.rec != nullptr && p.n_keys > 0) {
-    lo = lower_bound_u32(p.keys, p.n_keys, key);
-    hi = lower_bound_u32(p.keys, p.n_keys, key + 1);
+  uint32_t lo = 0, hi = 0;
+  if (valid && T.rec != nullptr && p.n_keys > 0) {
+    const uint32_t key = T.key_base + (uint32_t) row;
+    lo = __ldg(p.seg_lo + key);
+    hi = __ldg(p.seg_hi + key);
   }
-  const float b1 = p.beta1, b2 = p.beta2;
   const int nch = (T.cols + 3) >> 2;
+  const bool heavy = (hi - lo) > (uint32_t) UPD_HEAVY;
+  if (lane == 0) { s_lo[warp] = (int) lo; s_hi[warp] = (int) hi; s_tab[warp] = j; s_heavy[warp] = heavy; }
+  __syncthreads();
+
+  float4 g[CPL];
+#pragma unroll
+  for (int u = 0; u < CPL; ++u) g[u] = f4zero();
+  if (!heavy) sum_records<CPL>(p.vals, T.rec, T.rec_ld, T.rec_base, lo, hi, nch, lane, g);
+  for (int w2 = 0; w2 < 8; ++w2) {                     // CTA-uniform loop
+    if (!s_heavy[w2]) continue;
+    const UpdateTable& H = p.tab[s_tab[w2]];
+    const int hn = (H.cols + 3) >> 2;
+    const int64_t L = s_hi[w2] - s_lo[w2];
+    float4 part[CPL];
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) part[u] = f4zero();
+    sum_records<CPL>(p.vals, H.rec, H.rec_ld, H.rec_base, s_lo[w2] + L * warp / 8, s_lo[w2] + L * (warp + 1) / 8, hn,
+                     lane, part);
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) s_part[warp][u * WARP + lane] = part[u];
+    __syncthreads();
+    if (warp == w2) {
+      for (int w3 = 0; w3 < 8; ++w3)                   // fixed order: slices are contiguous in sorted order
+#pragma unroll
+        for (int u = 0; u < CPL; ++u) g[u] += s_part[w3][u * WARP + lane];
+    }
+    __syncthreads();
+  }
+  if (!valid) return;
+
+  const float b1 = p.beta1, b2 = p.beta2;
   float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
 
   // dense-regulariser coefficients of this row:  g += ca * w + cb * other
@@ -208,13 +255,15 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
   if (DENSE == 1) {
     float n2 = 0.f;
     if (T.dense_kind != DK_NONE) {
-      for (int c0 = 0; c0 < nch; c0 += WARP) {
-        const bool act = c0 + lane < nch;
-        const int c = act ? c0 + lane : nch - 1;
-        float4 g = sum_records(p, T, lo, hi, c, lane);
-        g += ca * w4[c];
-        if (o4) g += cb * o4[c];
-        if (act) n2 += dot4(g, g);
+#pragma unroll
+      for (int u = 0; u < CPL; ++u) {
+        const int c = lane + 32 * u;
+        if (c < nch) {
+          float4 gg = g[u];
+          gg += ca * w4[c];
+          if (o4) gg += cb * o4[c];
+          n2 += dot4(gg, gg);
+        }
       }
       n2 = warp_sum(n2);
     }
@@ -225,24 +274,24 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
   const float scale = p.scal[T.slot];
   float4* m4 = reinterpret_cast<float4*>(T.m + row * (int64_t) T.ld);
   float4* v4 = reinterpret_cast<float4*>(T.v + row * (int64_t) T.ld);
-  for (int c0 = 0; c0 < nch; c0 += WARP) {
-    const bool act = c0 + lane < nch;
-    const int c = act ? c0 + lane : nch - 1;
-    float4 g = sum_records(p, T, lo, hi, c, lane);
-    if (!act) continue;
+#pragma unroll
+  for (int u = 0; u < CPL; ++u) {
+    const int c = lane + 32 * u;
+    if (c >= nch) continue;
+    float4 gg = g[u];
     float4 w = w4[c];
     if (DENSE == 2 && T.dense_kind != DK_NONE) {
-      g += ca * w;
-      if (o4) g += cb * o4[c];
+      gg += ca * w;
+      if (o4) gg += cb * o4[c];
     }
-    g = scale * g;
+    gg = scale * gg;
     float4 m = m4[c], v = v4[c];
     // Keras Adam, sparse path: m = b1*m (+ (1-b1) g on touched rows), likewise v; then
     // w -= lr_t * m / (sqrt(v) + eps) for EVERY row.
-    m = f4(b1 * m.x + (1.f - b1) * g.x, b1 * m.y + (1.f - b1) * g.y,
-           b1 * m.z + (1.f - b1) * g.z, b1 * m.w + (1.f - b1) * g.w);
-    v = f4(b2 * v.x + (1.f - b2) * g.x * g.x, b2 * v.y + (1.f - b2) * g.y * g.y,
-           b2 * v.z + (1.f - b2) * g.z * g.z, b2 * v.w + (1.f - b2) * g.w * g.w);
+    m = f4(b1 * m.x + (1.f - b1) * gg.x, b1 * m.y + (1.f - b1) * gg.y,
+           b1 * m.z + (1.f - b1) * gg.z, b1 * m.w + (1.f - b1) * gg.w);
+    v = f4(b2 * v.x + (1.f - b2) * gg.x * gg.x, b2 * v.y + (1.f - b2) * gg.y * gg.y,
+           b2 * v.z + (1.f - b2) * gg.z * gg.z, b2 * v.w + (1.f - b2) * gg.w * gg.w);
     w = f4(w.x - p.lr_t * m.x / (sqrtf(v.x) + p.eps), w.y - p.lr_t * m.y / (sqrtf(v.y) + p.eps),
            w.z - p.lr_t * m.z / (sqrtf(v.z) + p.eps), w.w - p.lr_t * m.w / (sqrtf(v.w) + p.eps));
     // keep the zero-padding invariant on the ragged last chunk
@@ -252,6 +301,19 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
     if (e0 + 3 >= T.cols) { w.w = 0.f; m.w = 0.f; v.w = 0.f; }
     m4[c] = m; v4[c] = v; w4[c] = w;
   }
+}
+
+template <int DENSE>
+inline int launch_update(const UpdateParams& up, int cpl, int64_t blocks, cudaStream_t st) {
+  switch (cpl) {
+    case 1: k_update<DENSE, 1><<<(unsigned) blocks, 256, 0, st>>>(up); break;
+    case 2: k_update<DENSE, 2><<<(unsigned) blocks, 256, 0, st>>>(up); break;
+    case 4: k_update<DENSE, 4><<<(unsigned) blocks, 256, 0, st>>>(up); break;
+    default: k_update<DENSE, 8><<<(unsigned) blocks, 256, 0, st>>>(up); break;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("k_update launch failed: %s", cudaGetErrorString(e)); return KGE_ECUDA; }
+  return KGE_OK;
 }
 
 // ---- reduction of the dense pass: per-table norm^2 -> clip scale, regulariser -> loss ----

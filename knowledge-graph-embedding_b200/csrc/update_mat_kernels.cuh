@@ -35,6 +35,7 @@ struct MatUpdParams {
   const int64_t* neg_ids;
   int64_t B; int k, side_mode;
   const uint32_t* keys; const uint32_t* vals; int64_t n_keys;
+  const uint32_t* seg_lo; const uint32_t* seg_hi;      // k_segments
   uint32_t key_base, rec_base;      // relation keys are key_base + r; vals - rec_base = positive index
   const float* scal;
   float lr_t, beta1, beta2, eps;
@@ -69,8 +70,8 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
   const int row0 = tr * MU_TILE, col0 = tc * MU_TILE;
 
   const uint32_t key = p.key_base + (uint32_t) r;
-  const int64_t lo = lower_bound_u32(p.keys, p.n_keys, key);
-  const int64_t hi = lower_bound_u32(p.keys, p.n_keys, key + 1);
+  const int64_t lo = p.n_keys > 0 ? (int64_t) __ldg(p.seg_lo + key) : 0;
+  const int64_t hi = p.n_keys > 0 ? (int64_t) __ldg(p.seg_hi + key) : 0;
   const int n_neg = mu_neg_count(T.neg_mode, p.side_mode, p.k);
   const int S = T.use_sh + T.use_st + n_neg;
   const int64_t n_pairs = (hi - lo) * S;
