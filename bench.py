@@ -133,9 +133,13 @@ def run_ours(args, rank, world, device):
     B, k_eff = W["B"], 2 * (W["k"] // 2)
     eng = make_engine(device)
     train = zipf_triples(W["n_train"], W["n_ent"], W["n_rel"], 12345)
-    rng = np.random.default_rng(100 + rank)
+    # data-parallel (world > 1): one GLOBAL batch of world*B positives per step, identical on every
+    # rank; rank r owns positives [r*B, (r+1)*B) (weak scaling: per-GPU batch fixed).  Gradients are
+    # summed with one NCCL all-reduce per step inside Engine.train_step_dp.
+    rng = np.random.default_rng(100)
     n_batches = 64
-    host_batches = [torch.from_numpy(train[rng.integers(0, len(train), B)]).pin_memory() for _ in range(n_batches)]
+    host_batches = [torch.from_numpy(train[rng.integers(0, len(train), B * world)][rank * B:(rank + 1) * B].copy())
+                    .pin_memory() for _ in range(n_batches)]
     dev_batches = [b.to(device) for b in host_batches]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)      # > 126 MB L2
     loss_dev = torch.zeros(1, dtype=torch.float32, device=device)
@@ -143,7 +147,10 @@ def run_ours(args, rank, world, device):
     step_no = [0]
 
     def one_step(batch):
-        eng.train_step(batch, seed, step_no[0], is_train=True, loss_out=loss_dev)
+        if world > 1:
+            eng.train_step_dp(batch, seed, step_no[0], B * world, rank * B, loss_out=loss_dev)
+        else:
+            eng.train_step(batch, seed, step_no[0], is_train=True, loss_out=loss_dev)
         step_no[0] += 1
 
     def barrier():

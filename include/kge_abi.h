@@ -145,6 +145,36 @@ int kge_train_step(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*,
                    uint64_t adam_t, const int64_t* neg_override, int is_train,
                    float* loss_out, int64_t* neg_out, void* ws, size_t ws_bytes, void* stream);
 
+/* Data-parallel form of kge_train_step (the reference is single-device): every
+ * rank holds all tables and B of the step's B_global positives, [i_base, i_base + B).
+ *   kge_train_grad  : constraint, sampling on the GLOBAL Philox counters (the negatives equal a
+ *                     one-GPU step on the whole batch), scores, loss terms normalised by
+ *                     B_global, backward, per-row segmented sum -> this rank's summed gradient
+ *                     per table and scal_out[0] = loss share, scal_out[1+s] = sum of squared
+ *                     norms of slot s over this rank's lookup occurrences.  Tables untouched.
+ *   (caller)        : sum `grads` and scal over ranks (NCCL all-reduce; any order-fixed reduction
+ *                     keeps replicas bit-identical).
+ *   kge_train_apply : per-variable clip_by_norm from the summed norms, dense regularisers,
+ *                     TF-semantics Adam on every row; loss_out = summed loss (+ regulariser).
+ * grads.dense[s]: [rows x ld] fp32 with the table's own ld (every row is written by _grad).
+ * Row-sparse lists (ent_rows / ent_vals) are reserved: must be NULL / 0 in ABI version 1. */
+typedef struct kge_dp {
+  int32_t world, rank;
+  int64_t B_global;              /* positives of the whole step */
+  int64_t i_base;                /* global index of this rank's first positive */
+} kge_dp;
+typedef struct kge_grads {
+  float* dense[KGE_MAX_TABLES];
+  int64_t* ent_rows;  float* ent_vals[2];  int64_t cap;  int32_t lists, reserved;
+} kge_grads;
+int kge_train_grad(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const kge_dp*,
+                   const void* triples, int64_t B, uint64_t seed, uint64_t step,
+                   const int64_t* neg_override, kge_grads* out, float* scal_out /* [8] device */,
+                   int64_t* neg_out, void* ws, size_t ws_bytes, void* stream);
+int kge_train_apply(kge_ctx*, const kge_cfg*, kge_tables*, const kge_grads* summed,
+                    const float* scal_summed /* [8] device */, int64_t B, uint64_t adam_t,
+                    float* loss_out, void* ws, size_t ws_bytes, void* stream);
+
 /* Replaces the evaluate()/get_rank() loop (BaseModel.py:602-604, 620-654) for Q
  * queries at once: count_out[q] += #{e in [ent_lo, ent_hi) : score(e) > pos_score(q),
  * e not filtered}; rank = 1 + count (summed over entity shards).  count_out must be

@@ -144,6 +144,57 @@ class Engine:
                                         _ptr(loss_out), _ptr(neg_out), _ptr(ws), ws.numel(), _stream()))
         return (loss_out, neg_out) if want_negatives else loss_out
 
+    # ---- data-parallel step: grad -> one all-reduce -> apply ---------------
+    def grad_buffer(self):
+        from . import dp as _dp
+        return _dp.GradBuffer({s: (pt.rows, pt.ld) for s, pt in self.tab.items()}, self.device)
+
+    def _grads_struct(self, gb):
+        G = L.Grads()
+        for s in self.tab:
+            G.dense[s] = gb.view(s).data_ptr()
+        return G
+
+    def train_grad(self, gb, triples_local, seed, step, B_global, i_base, rank=0, world_size=1,
+                   neg_override=None, want_negatives=False):
+        """kge_train_grad: this rank's summed gradients and [norm^2 x4, loss] into `gb`."""
+        X = self._ids(triples_local)
+        B = X.shape[0]
+        ws = self._workspace(B, 0)
+        dpd = L.Dp(world=world_size, rank=rank, B_global=B_global, i_base=i_base)
+        neg = None
+        if neg_override is not None:
+            neg = torch.as_tensor(neg_override, dtype=torch.int64).to(self.device).contiguous()
+        neg_out = torch.empty(B * self.k_eff(), dtype=torch.int64, device=self.device) if want_negatives else None
+        T = self._tables(with_opt=False)
+        G = self._grads_struct(gb)
+        L.check(L.load().kge_train_grad(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler),
+                                        C.byref(dpd), _ptr(X), B, seed, step, _ptr(neg), C.byref(G), _ptr(gb.scal),
+                                        _ptr(neg_out), _ptr(ws), ws.numel(), _stream()))
+        return neg_out
+
+    def train_apply(self, gb, B, loss_out=None):
+        """kge_train_apply with the (rank-summed) buffer `gb`; B = the local batch the workspace was sized for."""
+        ws = self._workspace(B, 0)
+        if loss_out is None:
+            loss_out = torch.empty(1, dtype=torch.float32, device=self.device)
+        self.adam_t += 1
+        T = self._tables(with_opt=True)
+        G = self._grads_struct(gb)
+        L.check(L.load().kge_train_apply(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(G), _ptr(gb.scal), B,
+                                         self.adam_t, _ptr(loss_out), _ptr(ws), ws.numel(), _stream()))
+        return loss_out
+
+    def train_step_dp(self, triples_local, seed, step, B_global, i_base, loss_out=None, neg_override=None, group=None):
+        """One data-parallel step; every rank of the process group must call it."""
+        from . import dp as _dp
+        rank, world_size = _dp.world()
+        if getattr(self, "_gbuf", None) is None:
+            self._gbuf = self.grad_buffer()
+        self.train_grad(self._gbuf, triples_local, seed, step, B_global, i_base, rank, world_size, neg_override)
+        self._gbuf.allreduce(group)                       # the step's single collective
+        return self.train_apply(self._gbuf, len(triples_local), loss_out)
+
     def score(self, h, r, t):
         h, r, t = self._ids(h), self._ids(r), self._ids(t)
         out = torch.empty(h.numel(), dtype=torch.float32, device=self.device)

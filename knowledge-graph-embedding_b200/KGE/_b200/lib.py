@@ -46,9 +46,18 @@ class Filter(C.Structure):
     _fields_ = [("off", C.c_void_p), ("ids", C.c_void_p)]
 
 
+class Dp(C.Structure):
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("B_global", C.c_int64), ("i_base", C.c_int64)]
+
+
+class Grads(C.Structure):
+    _fields_ = [("dense", C.c_void_p * KGE_MAX_TABLES), ("ent_rows", C.c_void_p),
+                ("ent_vals", C.c_void_p * 2), ("cap", C.c_int64), ("lists", C.c_int32), ("reserved", C.c_int32)]
+
+
 SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destroy",
            "kge_workspace_bytes", "kge_sample_negatives", "kge_score", "kge_constrain_table",
-           "kge_train_step", "kge_rank", "kge_profile_begin", "kge_profile_end"]
+           "kge_train_step", "kge_train_grad", "kge_train_apply", "kge_rank", "kge_profile_begin", "kge_profile_end"]
 
 _LIB = None
 
@@ -80,6 +89,10 @@ def load():
     L.kge_constrain_table.argtypes = [vp, C.POINTER(Tables), i32, i32, vp]
     L.kge_train_step.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), vp, i64,
                                  u64, u64, u64, vp, i32, vp, vp, vp, C.c_size_t, vp]
+    L.kge_train_grad.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Dp), vp, i64,
+                                 u64, u64, vp, C.POINTER(Grads), vp, vp, vp, C.c_size_t, vp]
+    L.kge_train_apply.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Grads), vp, i64, u64, vp, vp,
+                                  C.c_size_t, vp]
     L.kge_rank.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp, i64, i32, C.POINTER(Filter),
                            i64, i64, vp, vp, C.c_size_t, vp]
     L.kge_profile_begin.argtypes = [vp, i32]

@@ -27,7 +27,7 @@ from ... import metrics as _metrics
 from ...data_utils import DeviceBatchStream, calculate_data_size, load_triples
 from ...ns_strategy import TypedStrategy, UniformStrategy, _type_csr, check_typed_pools
 from ...optimizers import adam_fields
-from ..._b200 import engine as _engine, filter as _filter, lib as _lib, spec as _spec
+from ..._b200 import dp as _dp, engine as _engine, filter as _filter, lib as _lib, spec as _spec
 
 logging.getLogger().setLevel(logging.INFO)
 
@@ -85,7 +85,8 @@ class KGEModel:
         self.loss_fn = loss_fn
         self.ns_strategy = ns_strategy
         self._n_workers = n_workers          # kept for signature parity; sampling is a kernel
-        self.device = os.environ.get("KGE_DEVICE", "cuda:0")
+        # one process per GPU under torchrun: LOCAL_RANK picks the device
+        self.device = os.environ.get("KGE_DEVICE", "cuda:%d" % int(os.environ.get("LOCAL_RANK", "0")))
         self.metadata = None
         self._model_weights_initial = None
         self._engine = None
@@ -210,7 +211,7 @@ class KGEModel:
         self.seed = seed
         self.log_path = log_path
         os.makedirs(log_path, exist_ok=True)
-        writers = _Writers(log_path, val_X is not None)
+        writers = _Writers(log_path, val_X is not None, enabled=_dp.world()[0] == 0)
 
         logging.info("[%s] Preparing for training..." % _now())
         n_train = calculate_data_size(train_X)
@@ -222,6 +223,14 @@ class KGEModel:
         self._setup_sampler()
         eng = self._engine
         ns_seed = int(seed) if seed is not None else int.from_bytes(os.urandom(7), "little")
+        # multi-GPU (torch.distributed initialised by the launcher): every rank walks the same
+        # seeded batch sequence and owns a contiguous share of each batch; gradients are summed
+        # with one all-reduce per step, replicas stay identical.  Matrix models (SE / TransR /
+        # RESCAL) have no split step yet: their ranks repeat the whole batch (identical replicas).
+        rank, world_size = _dp.world()
+        split = world_size > 1 and self.MODEL not in ("SE", "TransR", "RESCAL")
+        if world_size > 1:
+            assert seed is not None, "multi-GPU training needs a seed: every rank must walk the same batch sequence"
         step = 0
         self.train_loss_history, self.val_loss_history = [], []
         self.best_step, patience = None, 0
@@ -231,7 +240,12 @@ class KGEModel:
             t_loss = torch.zeros(n_batches, dtype=torch.float32, device=eng.device)
             v_loss = torch.zeros(max(n_val_batches, 1), dtype=torch.float32, device=eng.device)
             for b in range(n_batches):
-                eng.train_step(next(train_iter), ns_seed, step, is_train=True, loss_out=t_loss[b:b + 1])
+                batch = next(train_iter)
+                if split:
+                    lo, hi = _dp.batch_shard(len(batch))
+                    eng.train_step_dp(batch[lo:hi], ns_seed, step, len(batch), lo, loss_out=t_loss[b:b + 1])
+                else:
+                    eng.train_step(batch, ns_seed, step, is_train=True, loss_out=t_loss[b:b + 1])
                 step += 1
                 if val_iter is not None and b < n_val_batches:
                     # validation batches draw negatives and apply the constraint too
@@ -289,12 +303,16 @@ class KGEModel:
         """max_to_keep=1 like the reference's CheckpointManager (BaseModel.py:253); unlike the
         reference the Adam slots and step are saved too."""
         eng = self._engine
+        if _dp.world()[0] != 0:      # replicas are identical: rank 0 writes, everyone can read
+            return
         torch.save({"weights": {k: v.tensor.detach().cpu() for k, v in self.model_weights.items()},
                     "adam_m": {s: t.m.cpu() for s, t in eng.tab.items() if t.m is not None},
                     "adam_v": {s: t.v.cpu() for s, t in eng.tab.items() if t.v is not None},
                     "adam_t": eng.adam_t}, self._ckpt_path())
 
     def _load_checkpoint(self):
+        if _dp.world()[1] > 1:
+            torch.distributed.barrier()
         state = torch.load(self._ckpt_path())
         for k, v in state["weights"].items():
             self.model_weights[k].assign(v)
@@ -323,12 +341,15 @@ class KGEModel:
         side = _lib.SIDE_H if corrupt_side == "h" else _lib.SIDE_T
         pos = None if positive_X is None else torch.as_tensor(np.asarray(_plain(positive_X))).to(eng.device)
         ranks = []
+        # multi-GPU: each rank counts over its slice of the entity table, counts are summed
+        e_lo, e_hi = _dp.entity_shard(n_ent)
         for lo in range(0, len(X), 16384):
             blk = X[lo:lo + 16384]
             off = ids = None
             if pos is not None:
                 off, ids = _filter.build_filter(pos, blk, corrupt_side, n_ent, eng.device)
-            ranks.append(eng.rank_counts(blk, side, off, ids).cpu().numpy().astype(np.int64) + 1)
+            cnt = _dp.allreduce_counts(eng.rank_counts(blk, side, off, ids, ent_lo=e_lo, ent_hi=e_hi))
+            ranks.append(cnt.cpu().numpy().astype(np.int64) + 1)
         return np.concatenate(ranks)
 
     def get_rank(self, x, positive_X, corrupt_side):
@@ -368,8 +389,10 @@ class _Writers:
     (:542-576) through torch.utils.tensorboard when tensorboard is importable; otherwise
     silently off — observability only, never on the hot path."""
 
-    def __init__(self, log_path, with_val):
+    def __init__(self, log_path, with_val, enabled=True):
         self.log_path, self.w = log_path, {}
+        if not enabled:          # only rank 0 writes event files
+            return
         try:
             from torch.utils.tensorboard import SummaryWriter
             self.w["root"] = SummaryWriter(log_path)

@@ -178,6 +178,7 @@ struct SamplerDev {
   int k_eff, k_side;
   uint64_t seed, step;
   int64_t n_ent;
+  int64_t i_base;           // global index of this call's first positive (data-parallel ranks)
   kge_sampler s;
 };
 __device__ __forceinline__ bool neg_is_head(const SamplerDev& sd, int c) {
@@ -187,7 +188,7 @@ __device__ __forceinline__ int64_t sample_negative(const SamplerDev& sd, int64_t
                                                    int64_t h, int64_t t) {
   bool head = neg_is_head(sd, c);
   int jj = (sd.side_mode == KGE_SIDE_HT) ? (c >> 1) : c;
-  uint64_t n = (uint64_t) i * (uint64_t) sd.k_side + (uint64_t) jj;
+  uint64_t n = (uint64_t) (i + sd.i_base) * (uint64_t) sd.k_side + (uint64_t) jj;
   const uint32_t u = philox_word0(sd.seed, sd.step, head ? 0u : 1u, n);
   if (sd.kind == KGE_NS_UNIFORM) {      // 32-bit modulo: n_ent < 2^32 is checked on the host
     if (sd.s.pool == nullptr) return (int64_t) ((uint32_t) u % (uint32_t) sd.n_ent);

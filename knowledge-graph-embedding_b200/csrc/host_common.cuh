@@ -122,6 +122,7 @@ inline void fill_sampler_dev(const kge_cfg* c, const kge_sampler* s, uint64_t se
   sd.seed = seed;
   sd.step = step;
   sd.n_ent = c->n_ent;
+  sd.i_base = 0;
   if (s) sd.s = *s; else { sd.s = kge_sampler{}; }
 }
 

@@ -214,17 +214,19 @@ extern "C" int kge_workspace_bytes(const kge_cfg* cfg, int64_t B, int64_t Q, siz
   return KGE_OK;
 }
 
-extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
-                              const void* triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
-                              const int64_t* neg_override, int is_train, float* loss_out, int64_t* neg_out,
-                              void* ws, size_t ws_bytes, void* stream) {
+// dp / grads_out / scal_out non-NULL = the gradient half of a data-parallel step (kge_train_grad)
+static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                      const kge_dp* dp, const void* triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
+                      const int64_t* neg_override, int is_train, kge_grads* grads_out, float* scal_out,
+                      float* loss_out, int64_t* neg_out, void* ws, size_t ws_bytes, void* stream) {
   auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
   cudaStream_t st = (cudaStream_t) stream;
+  const bool grad_only = dp != nullptr;
   KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
   if (int rc = check_cfg(cfg)) return rc;
-  if (int rc = check_tables(cfg, tables, is_train != 0)) return rc;
+  if (int rc = check_tables(cfg, tables, is_train != 0 && dp == nullptr)) return rc;
   if (!neg_override) { if (int rc = check_sampler(cfg, smp)) return rc; }
-  KGE_REQUIRE(triples && loss_out && ws && B > 0, KGE_EINVAL, "triples / loss_out / ws / B invalid");
+  KGE_REQUIRE(triples && (loss_out || grad_only) && ws && B > 0, KGE_EINVAL, "triples / loss_out / ws / B invalid");
   KGE_REQUIRE(cfg->loss >= KGE_LOSS_HINGE && cfg->loss <= KGE_LOSS_SQUARE, KGE_EINVAL, "bad loss id %d", cfg->loss);
   KGE_REQUIRE(cfg->corrupt_side >= KGE_SIDE_H && cfg->corrupt_side <= KGE_SIDE_HT, KGE_EINVAL, "bad corrupt_side");
   const int k = k_eff_of(cfg);
@@ -232,6 +234,22 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
               "zero negatives per positive (corrupt_side='h+t' uses negative_ratio//2 per side, BaseModel.py:354-355)");
   KGE_REQUIRE(!is_train || adam_t >= 1, KGE_EINVAL, "adam_t is 1-based");
   const bool mat = is_matrix_model(cfg->model);
+  int64_t B_global = B;
+  if (grad_only) {
+    KGE_REQUIRE(grads_out && scal_out, KGE_EINVAL, "grads / scal_out is NULL");
+    KGE_REQUIRE(dp->world >= 1 && dp->rank >= 0 && dp->rank < dp->world && dp->i_base >= 0 &&
+                    dp->B_global >= dp->i_base + B, KGE_EINVAL, "bad kge_dp (world %d rank %d B_global %lld i_base %lld)",
+                dp->world, dp->rank, (long long) dp->B_global, (long long) dp->i_base);
+    KGE_REQUIRE(!mat, KGE_EUNSUPPORTED, "data-parallel steps cover the vector models; SE / TransR / RESCAL are single-GPU");
+    KGE_REQUIRE(!grads_out->ent_rows && !grads_out->ent_vals[0] && !grads_out->ent_vals[1], KGE_EUNSUPPORTED,
+                "row-sparse gradient lists are reserved in ABI version 1");
+    int gcols[KGE_MAX_TABLES];
+    expected_cols(cfg, gcols);
+    for (int s = 0; s < KGE_MAX_TABLES; ++s)
+      KGE_REQUIRE(!gcols[s] || (grads_out->dense[s] && ((uintptr_t) grads_out->dense[s] & 15) == 0), KGE_EINVAL,
+                  "grads.dense[%d] missing or not 16-byte aligned", s);
+    B_global = dp->B_global;
+  }
   const int nv = mat ? pick_nv_strided(cfg) : pick_nv(cfg);
   KGE_REQUIRE(nv > 0, KGE_EUNSUPPORTED, mat ? "matrix models support embedding sizes up to 256" : "row wider than 1024 floats");
 
@@ -260,9 +278,10 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   p.loss.kind = cfg->loss;
   p.loss.margin = cfg->margin;
   p.loss.temperature = cfg->temperature;
-  p.loss.inv_n = 1.0f / (float) B;
-  p.loss.inv_nk = 1.0f / ((float) B * (float) k);
+  p.loss.inv_n = 1.0f / (float) B_global;                 // loss normalisations use the whole step's batch
+  p.loss.inv_nk = 1.0f / ((float) B_global * (float) k);
   fill_sampler_dev(cfg, smp, seed, step, p.sd);
+  if (grad_only) p.sd.i_base = dp->i_base;
   p.triples = triples;
   p.id64 = cfg->id_dtype;
   p.B = B;
@@ -282,7 +301,7 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   p.rp.n_part = is_train ? N_PART : 1;
   p.rp.clip_norm = cfg->clip_norm;
   p.rp.scal = reinterpret_cast<float*>(wsb + L.off_scal);
-  p.rp.loss_out = loss_out;
+  p.rp.loss_out = grad_only ? p.rp.scal + 9 : loss_out;
 
   // side stream: sort keys depend on ids only, so key generation, the stable radix sort and the
   // segment table run concurrently with the step kernel and join before the update kernels
@@ -374,7 +393,9 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   if (is_train) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));     // join the side stream
   if (neg_out)
     KGE_CUDA_OK(cudaMemcpyAsync(neg_out, p.neg_ids, sizeof(int64_t) * (size_t) B * k, cudaMemcpyDeviceToDevice, st));
-  const bool dense = has_dense_reg(cfg);
+  if (grad_only)      // scal[4..8] = norm^2 per slot, loss share
+    KGE_CUDA_OK(cudaMemcpyAsync(scal_out, rp.scal + 4, sizeof(float) * 5, cudaMemcpyDeviceToDevice, st));
+  const bool dense = has_dense_reg(cfg) && !grad_only;    // regularisers are added once, by kge_train_apply
   if (!is_train && !dense) return KGE_OK;
 
   // 4. (side stream, above) records sorted by (table, row): stable LSD radix sort => occurrence
@@ -396,6 +417,7 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
     U.rec_base = (s < 2) ? 0u : (uint32_t) L.n_ent_rec;
     U.slot = s;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
+    U.gsum = nullptr; U.gout = grad_only ? grads_out->dense[s] : nullptr;
     if (dense) {
       if (cfg->model == KGE_RESCAL) U.dense_kind = DK_RESCAL_ENT;
       else if (s == KGE_T_ENT) U.dense_kind = DK_TRANSH_ENT;
@@ -455,6 +477,11 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   }
 
   pt.begin(4);
+  if (grad_only) {
+    if (int rc2 = launch_update<3>(up, cpl, ublocks, st)) return rc2;
+    pt.end(4);
+    return KGE_OK;
+  }
   if (dense) {
     // densified gradients: norm pass, reduce, then apply  (tf.clip_by_norm on a dense tensor)
     if (cfg->model == KGE_TRANSH)
@@ -482,6 +509,112 @@ extern "C" int kge_train_step(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
     KGE_CUDA_OK(cudaGetLastError());
   }
   if (int rc2 = dense ? launch_update<2>(up, cpl, ublocks, st) : launch_update<0>(up, cpl, ublocks, st)) return rc2;
+  pt.end(4);
+  return KGE_OK;
+}
+
+extern "C" int kge_train_step(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                              const void* triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
+                              const int64_t* neg_override, int is_train, float* loss_out, int64_t* neg_out,
+                              void* ws, size_t ws_bytes, void* stream) {
+  return train_impl(ctx, cfg, tables, smp, nullptr, triples, B, seed, step, adam_t, neg_override, is_train, nullptr,
+                    nullptr, loss_out, neg_out, ws, ws_bytes, stream);
+}
+
+extern "C" int kge_train_grad(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                              const kge_dp* dp, const void* triples, int64_t B, uint64_t seed, uint64_t step,
+                              const int64_t* neg_override, kge_grads* out, float* scal_out, int64_t* neg_out, void* ws,
+                              size_t ws_bytes, void* stream) {
+  KGE_REQUIRE(dp, KGE_EINVAL, "dp is NULL");
+  return train_impl(ctx, cfg, tables, smp, dp, triples, B, seed, step, 1, neg_override, 1, out, scal_out, nullptr,
+                    neg_out, ws, ws_bytes, stream);
+}
+
+// Second half of a data-parallel step: the rank-summed gradients replace the record sums.
+extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, const kge_grads* g,
+                               const float* scal_summed, int64_t B, uint64_t adam_t, float* loss_out, void* ws,
+                               size_t ws_bytes, void* stream) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  cudaStream_t st = (cudaStream_t) stream;
+  KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
+  if (int rc = check_cfg(cfg)) return rc;
+  if (int rc = check_tables(cfg, tables, true)) return rc;
+  KGE_REQUIRE(g && scal_summed && loss_out && ws && B > 0 && adam_t >= 1, KGE_EINVAL, "bad kge_train_apply arguments");
+  KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED,
+              "data-parallel steps cover the vector models; SE / TransR / RESCAL are single-GPU");
+  KGE_REQUIRE(!g->ent_rows && !g->ent_vals[0] && !g->ent_vals[1], KGE_EUNSUPPORTED,
+              "row-sparse gradient lists are reserved in ABI version 1");
+  StepWs L;
+  if (int rc = layout_step_ws(cfg, B, L)) return rc;
+  KGE_REQUIRE(ws_bytes >= L.total, KGE_EWORKSPACE, "workspace %zu < required %zu bytes", ws_bytes, L.total);
+  KGE_REQUIRE(((uintptr_t) ws & 255) == 0, KGE_EINVAL, "workspace must be 256-byte aligned");
+  char* wsb = reinterpret_cast<char*>(ws);
+  int cols[KGE_MAX_TABLES];
+  expected_cols(cfg, cols);
+  float* scal = reinterpret_cast<float*>(wsb + L.off_scal);
+  PhaseTimer pt(ctx, st);
+  pt.begin(4);
+  k_dp_scales<<<1, 32, 0, st>>>(scal_summed, cfg->clip_norm, scal, loss_out);
+  KGE_CUDA_OK(cudaGetLastError());
+
+  const bool dense = has_dense_reg(cfg);
+  UpdateParams up;
+  up.n_tabs = 0;
+  up.total_rows = 0;
+  ReduceDenseParams rd;
+  rd.row_begin[0] = 0;
+  int max_ch = 1;
+  for (int s = 0; s < KGE_MAX_TABLES; ++s) {
+    if (!cols[s]) continue;
+    KGE_REQUIRE(g->dense[s] && ((uintptr_t) g->dense[s] & 15) == 0, KGE_EINVAL, "grads.dense[%d] missing or not 16-byte aligned", s);
+    UpdateTable& U = up.tab[up.n_tabs];
+    U.w = tables->t[s].w; U.m = tables->t[s].m; U.v = tables->t[s].v;
+    U.rec = nullptr;
+    U.rows = tables->t[s].rows; U.cols = tables->t[s].cols; U.ld = tables->t[s].ld;
+    U.rec_ld = 0; U.key_base = 0; U.rec_base = 0;
+    U.slot = s;
+    U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
+    U.gsum = g->dense[s]; U.gout = nullptr;
+    if (dense) {            // TransH only (RESCAL is a matrix model)
+      if (s == KGE_T_ENT) U.dense_kind = DK_TRANSH_ENT;
+      else {
+        U.dense_kind = (s == KGE_T_REL_A) ? DK_TRANSH_REL : DK_TRANSH_HYPER;
+        U.other_w = reinterpret_cast<const float*>(wsb + L.off_snap[s == KGE_T_REL_A ? 1 : 0]);
+        U.other_ld = L.rld[s == KGE_T_REL_A ? KGE_T_REL_B : KGE_T_REL_A];
+      }
+    }
+    rd.slot[up.n_tabs] = s;
+    rd.is_dense[up.n_tabs] = U.dense_kind != DK_NONE;
+    up.total_rows += U.rows;
+    rd.row_begin[++up.n_tabs] = up.total_rows;
+    max_ch = ((U.cols + 3) / 4 > max_ch) ? (U.cols + 3) / 4 : max_ch;
+  }
+  up.keys = nullptr; up.vals = nullptr; up.n_keys = 0; up.seg_lo = nullptr; up.seg_hi = nullptr;
+  up.scal = scal;
+  const float b1p = powf(cfg->beta1, (float) adam_t), b2p = powf(cfg->beta2, (float) adam_t);
+  up.lr_t = cfg->lr * sqrtf(1.0f - b2p) / (1.0f - b1p);
+  up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
+  up.cw = cfg->constraint_weight;
+  up.rowpart = dense ? reinterpret_cast<float*>(wsb + L.off_rowpart) : nullptr;
+  const int64_t ublocks = (up.total_rows + 7) / 8;
+  const int cpl = max_ch <= 32 ? 1 : (max_ch <= 64 ? 2 : (max_ch <= 128 ? 4 : 8));
+  if (dense) {
+    for (int j = 0; j < 2; ++j) {
+      const int sl = j == 0 ? KGE_T_REL_A : KGE_T_REL_B;
+      const kge_table& S = tables->t[sl];
+      KGE_CUDA_OK(cudaMemcpy2DAsync(wsb + L.off_snap[j], sizeof(float) * L.rld[sl], S.w, sizeof(float) * S.ld,
+                                    sizeof(float) * L.rld[sl], (size_t) S.rows, cudaMemcpyDeviceToDevice, st));
+    }
+    if (int rc = launch_update<1>(up, cpl, ublocks, st)) return rc;
+    rd.rowpart = up.rowpart; rd.total_rows = up.total_rows; rd.n_tabs = up.n_tabs;
+    rd.matpart = nullptr; rd.n_mat = 0; rd.mat_slot = KGE_T_REL_A; rd.mat_loss_coef = 0.f;
+    rd.clip_norm = cfg->clip_norm; rd.write_scales = 1; rd.scal = scal; rd.loss_out = loss_out;
+    k_reduce_dense<<<1, 1024, 0, st>>>(rd);
+    KGE_CUDA_OK(cudaGetLastError());
+    if (int rc = launch_update<2>(up, cpl, ublocks, st)) return rc;
+  } else {
+    if (int rc = launch_update<0>(up, cpl, ublocks, st)) return rc;
+  }
   pt.end(4);
   return KGE_OK;
 }

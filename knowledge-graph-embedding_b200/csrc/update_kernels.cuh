@@ -89,6 +89,8 @@ struct UpdateTable {
   int dense_kind;        // DK_*
   const float* other_w;  // TransH: the paired relation table (rel_hyper for rel_emb and vice versa)
   int other_ld;
+  const float* gsum;     // data-parallel apply: summed gradient [rows x ld] added to the record sum (or NULL)
+  float* gout;           // DENSE=3 (data-parallel grad): where the row's summed gradient goes, [rows x ld]
 };
 struct UpdateParams {
   UpdateTable tab[KGE_MAX_TABLES];
@@ -212,6 +214,18 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
   }
   if (!valid) return;
 
+  if (DENSE == 3) {            // gradient only: every row is written (zeros where nothing was looked up)
+    float4* o = reinterpret_cast<float4*>(T.gout + row * (int64_t) T.ld);
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) o[c] = g[u]; }
+    return;
+  }
+  if (T.gsum != nullptr) {
+    const float4* gs = reinterpret_cast<const float4*>(T.gsum + row * (int64_t) T.ld);
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) g[u] += __ldg(gs + c); }
+  }
+
   const float b1 = p.beta1, b2 = p.beta2;
   float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
 
@@ -314,6 +328,16 @@ inline int launch_update(const UpdateParams& up, int cpl, int64_t blocks, cudaSt
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("k_update launch failed: %s", cudaGetErrorString(e)); return KGE_ECUDA; }
   return KGE_OK;
+}
+
+// data-parallel apply: clip scales and loss from the rank-summed [norm^2 x4, loss]
+__global__ void k_dp_scales(const float* __restrict__ summed, float clip_norm, float* scal, float* loss_out) {
+  const int t = threadIdx.x;
+  if (t < KGE_MAX_TABLES) {
+    const float n2 = summed[t];
+    scal[4 + t] = n2;
+    scal[t] = clip_norm / fmaxf(sqrtf(n2), clip_norm);
+  } else if (t == KGE_MAX_TABLES) { scal[8] = summed[KGE_MAX_TABLES]; *loss_out = summed[KGE_MAX_TABLES]; }
 }
 
 // ---- reduction of the dense pass: per-table norm^2 -> clip scale, regulariser -> loss ----

@@ -1,0 +1,73 @@
+"""Data-parallel training step on ONE GPU: G emulated ranks each run
+kge_train_grad on their share of the batch, the buffers are summed the way the all-reduce
+would, kge_train_apply updates — and the result must equal the oracle's step on the WHOLE
+batch (same Philox negatives as a one-GPU step, same losses 1e-4, same weights)."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import make_pair, tables_of, rand_triples, assert_weights_close
+from oracle import ref_ops as O, ref_step as RS
+from KGE._b200 import dp
+
+pytestmark = pytest.mark.gpu
+N, R = 300, 11
+
+CASES = [
+    ("TransE", O.LpDistance(1), O.PairwiseHingeLoss(1.0), 4, "h+t", 50, True),
+    ("DistMult", None, O.BinaryCrossEntropyLoss(), 6, "h+t", 40, True),
+    ("RotatE", O.LpDistance(1), O.SelfAdversarialNegativeSamplingLoss(3.0, 1.0), 8, "t", 24, True),
+    ("TransH", O.LpDistancePow(2), O.PairwiseHingeLoss(1.0), 4, "h", 32, True),     # dense regulariser
+    ("TransD", O.LpDistancePow(2), O.PairwiseLogisticLoss(), 2, "h+t", 20, True),
+    ("UM", O.LpDistancePow(2), O.SquareErrorLoss(), 3, "t", 16, False),
+]
+
+
+@pytest.mark.parametrize("G", [1, 2, 3])
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_emulated_ranks_match_full_batch_oracle(case, G):
+    model, score, loss, k, side, d, constraint = case
+    rng = np.random.default_rng(5)
+    ref, W, eng = make_pair(model, N, R, d, score=score, loss=loss, k=k, side=side, constraint=constraint)
+    opt = RS.TFAdam()
+    B, seed = 50, 21
+    bufs = [eng.grad_buffer() for _ in range(G)]
+    for step in range(3):
+        X = rand_triples(rng, B, N, R)
+        ids, k_eff = RS.sample_negatives(seed, step, X, k, side, N)
+        l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, side, True)
+        negs = []
+        for g in range(G):
+            lo, hi = dp.split_even(B, G, g)
+            negs.append(eng.train_grad(bufs[g], X[lo:hi], seed, step, B, lo, g, G, want_negatives=True))
+        assert np.array_equal(torch.cat(negs).cpu().numpy(), ids), "ranks must draw the one-GPU negatives"
+        for g in range(1, G):                         # what the all-reduce does
+            bufs[0].flat += bufs[g].flat
+        l_gpu = eng.train_apply(bufs[0], hi - lo)
+        assert abs(float(l_gpu.item()) - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, float(l_gpu.item()), l_ref)
+        got = tables_of(eng, model)
+        for kk, v in W.data.items():
+            assert_weights_close(got[kk], v, 1e-3, step + 1, (step, kk))
+
+
+def test_one_rank_equals_fused_step_bitwise():
+    """world = 1: grad + apply is the fused kge_train_step split in two (same record sums, same
+    update arithmetic) — weights must be bit-identical."""
+    rng = np.random.default_rng(9)
+    _, _, a = make_pair("DistMult", N, R, 40, loss=O.BinaryCrossEntropyLoss(), k=6)
+    _, _, b = make_pair("DistMult", N, R, 40, loss=O.BinaryCrossEntropyLoss(), k=6)
+    gb = b.grad_buffer()
+    for step in range(3):
+        X = rand_triples(rng, 64, N, R)
+        la = a.train_step(X, 3, step)
+        b.train_grad(gb, X, 3, step, 64, 0)
+        lb = b.train_apply(gb, 64)
+        assert float(la.item()) == float(lb.item())
+    for s in a.tab:
+        assert torch.equal(a.tab[s].storage, b.tab[s].storage)
+
+
+def test_matrix_models_are_refused():
+    _, _, eng = make_pair("TransR", N, R, 12, 10, score=O.LpDistancePow(2), loss=O.PairwiseHingeLoss(1.0))
+    with pytest.raises(RuntimeError, match="single-GPU"):
+        eng.train_grad(eng.grad_buffer(), rand_triples(np.random.default_rng(0), 8, N, R), 1, 0, 8, 0)
