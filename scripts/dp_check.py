@@ -1,0 +1,66 @@
+"""Run under torchrun on >= 2 GPUs: python -m torch.distributed.run --nproc-per-node 2 scripts/dp_check.py
+Checks on real NCCL what tests/test_gpu_dp.py emulates on one device:
+  * replicas stay bit-identical over data-parallel steps,
+  * the weights equal a one-GPU run over the same global batches (tolerance of the parity tests),
+  * entity-sharded evaluate() returns the one-GPU ranks exactly."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "knowledge-graph-embedding_b200"), os.path.join(ROOT, "tests")]
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    from KGE._b200 import dp, engine as E, spec, filter as F
+    from oracle import ref_ops as O
+    N, R, d, B, k = 2000, 37, 64, 96 * world, 8
+    rng = np.random.default_rng(1)
+    g = torch.Generator().manual_seed(4)
+    W = {"ent_emb": (torch.rand((N, d), generator=g) - 0.5) * 0.6, "rel_emb": (torch.rand((R, d), generator=g) - 0.5) * 0.6}
+    cfg = spec.make_cfg("TransE", N, R, d, score_fn=O.LpDistance(1), loss_fn=O.PairwiseHingeLoss(1.0), negative_ratio=k,
+                        corrupt_side="h+t", constraint=True)
+    slots = spec.SLOTS["TransE"]
+    multi = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)
+    single = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)
+    ok = True
+    for step in range(5):
+        X = np.stack([rng.integers(0, N, B), rng.integers(0, R, B), rng.integers(0, N, B)], 1)
+        lo, hi = dp.batch_shard(B)
+        lm = multi.train_step_dp(X[lo:hi], 11, step, B, lo)
+        ls = single.train_step(X, 11, step)
+        ok &= abs(float(lm.item()) - float(ls.item())) <= 1e-4 * max(1.0, abs(float(ls.item())))
+    for s in multi.tab:
+        mine = multi.tab[s].storage
+        ref = single.tab[s].storage
+        ok &= float((mine - ref).abs().max()) <= 5 * 1e-3 * 1.01
+        ok &= float(((mine - ref).abs() > 1e-4 * float(ref.abs().max())).double().mean()) < 0.01
+        gathered = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(gathered, mine)
+        ok &= all(torch.equal(gathered[0], t) for t in gathered)            # replicas bit-identical
+    # sharded evaluation: counts over this rank's entity slice, summed == one-GPU counts
+    Q = np.stack([rng.integers(0, N, 300), rng.integers(0, R, 300), rng.integers(0, N, 300)], 1)
+    posX = np.concatenate([Q, np.stack([rng.integers(0, N, 4000), rng.integers(0, R, 4000), rng.integers(0, N, 4000)], 1)])
+    for side, sid in (("h", 0), ("t", 1)):
+        off, ids = F.build_filter(torch.as_tensor(posX).to(dev), Q, side, N, dev)
+        e_lo, e_hi = dp.entity_shard(N)
+        part = dp.allreduce_counts(multi.rank_counts(Q, sid, off, ids, ent_lo=e_lo, ent_hi=e_hi))
+        full = multi.rank_counts(Q, sid, off, ids)
+        ok &= bool(torch.equal(part, full))
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("DP_CHECK", "PASS" if int(flag.item()) == 1 else "FAIL", "world", world)
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag.item()) == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()

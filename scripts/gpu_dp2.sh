@@ -1,0 +1,4 @@
+mkdir -p gpurun_out
+N=${1:-2}
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 scripts/dp_check.py > gpurun_out/dp_check.log 2>&1; tail -3 gpurun_out/dp_check.log
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $N --steps 100 --warmup 5 --cpu-steps 2 --cpu-queries 4 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; tail -c 300 gpurun_out/bench_n$N.err; cut -c1-700 gpurun_out/bench_n$N.json
