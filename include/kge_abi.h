@@ -183,6 +183,12 @@ int kge_rank(kge_ctx*, const kge_cfg*, const kge_tables*, const void* queries, i
              int side, const kge_filter* filter, int64_t ent_lo, int64_t ent_hi,
              int32_t* count_out, void* ws, size_t ws_bytes, void* stream);
 
+/* Implementation switches (testing / A-B measurement; results are identical either way).
+ * KGE_OPT_RADIX_SORT: 1 = group the step's gradient records with cub's stable radix sort
+ * instead of the counting sort of csrc/group_kernels.cuh (default 0). */
+enum { KGE_OPT_RADIX_SORT = 1 };
+int kge_set_option(kge_ctx*, int option, int value);
+
 /* Per-phase device timing (CUDA events recorded on the call's stream, read back only at
  * kge_profile_end: no sync inside the timed region).  Phases: 0 constraint, 1 fused
  * sample+gather+score+loss+backward, 2 partial reduction, 3 record sort, 4 row update,

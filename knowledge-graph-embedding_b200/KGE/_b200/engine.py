@@ -221,6 +221,10 @@ class Engine:
                                   ws.numel(), _stream()))
         return cnt
 
+    def set_option(self, option, value):
+        """Implementation switch of the context (shared by every engine on the device)."""
+        L.check(L.load().kge_set_option(self.ctx, option, int(value)))
+
     def profile_begin(self, max_calls):
         L.check(L.load().kge_profile_begin(self.ctx, max_calls))
 

@@ -12,6 +12,7 @@ SIDE_H, SIDE_T, SIDE_HT = 0, 1, 2
 NS_UNIFORM, NS_TYPED = 0, 1
 T_ENT, T_ENT_PROJ, T_REL_A, T_REL_B = range(4)
 CON_NORMALIZE, CON_CLIP = 0, 1
+OPT_RADIX_SORT = 1
 N_PHASES = 8
 PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm", "rank_fix"]
 
@@ -57,7 +58,8 @@ class Grads(C.Structure):
 
 SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destroy",
            "kge_workspace_bytes", "kge_sample_negatives", "kge_score", "kge_constrain_table",
-           "kge_train_step", "kge_train_grad", "kge_train_apply", "kge_rank", "kge_profile_begin", "kge_profile_end"]
+           "kge_train_step", "kge_train_grad", "kge_train_apply", "kge_rank", "kge_profile_begin", "kge_profile_end",
+           "kge_set_option"]
 
 _LIB = None
 
@@ -95,6 +97,7 @@ def load():
                                   C.c_size_t, vp]
     L.kge_rank.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp, i64, i32, C.POINTER(Filter),
                            i64, i64, vp, vp, C.c_size_t, vp]
+    L.kge_set_option.argtypes = [vp, i32, i32]
     L.kge_profile_begin.argtypes = [vp, i32]
     L.kge_profile_end.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
     for s in SYMBOLS:

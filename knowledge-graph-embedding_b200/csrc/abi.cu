@@ -63,6 +63,14 @@ extern "C" int kge_ctx_destroy(kge_ctx* ctx) {
   delete c;
   return KGE_OK;
 }
+extern "C" int kge_set_option(kge_ctx* ctx, int option, int value) {
+  auto* c = reinterpret_cast<kge_ctx_impl*>(ctx);
+  KGE_REQUIRE(c, KGE_EINVAL, "ctx is NULL");
+  switch (option) {
+    case KGE_OPT_RADIX_SORT: c->opt_radix_sort = value; return KGE_OK;
+    default: set_error("unknown option %d", option); return KGE_EINVAL;
+  }
+}
 extern "C" int kge_profile_begin(kge_ctx* ctx, int max_calls) {
   auto* c = reinterpret_cast<kge_ctx_impl*>(ctx);
   KGE_REQUIRE(c && max_calls > 0 && max_calls <= (1 << 16), KGE_EINVAL, "bad profile_begin arguments");

@@ -38,6 +38,7 @@ struct kge_ctx_impl {
   // the radix sort and the segment table overlap the step kernel) + its fork / join events
   cudaStream_t aux = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  int opt_radix_sort = 0;         // kge_set_option(KGE_OPT_RADIX_SORT)
   unsigned* ticket = nullptr;     // device, 64 words, zero between calls (self-resetting counters)
 };
 // RAII marker: records the boundary events of one call when profiling is on

@@ -2,9 +2,11 @@
 // kge_constrain_table: validation, workspace carve-up, kernel sequencing.
 // Replaces KGEModel.__run_single_batch (BaseModel.py:293-330).
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include "host_common.cuh"
 #include "step_launch.cuh"
 #include "update_kernels.cuh"
+#include "group_kernels.cuh"
 #include "update_mat_kernels.cuh"
 #include "step_mat_launch.cuh"
 
@@ -68,7 +70,16 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   KGE_REQUIRE(e == cudaSuccess, KGE_ECUDA, "cub temp-size query failed: %s", cudaGetErrorString(e));
   L.off_cub = take(L.cub_bytes);
   L.n_seg = (size_t) c->n_ent + (size_t) c->n_rel;
-  L.off_seg = take(sizeof(uint32_t) * 2 * L.n_seg);         // seg_lo | seg_hi
+  L.off_seg = take(sizeof(uint32_t) * (2 * L.n_seg + 1));   // cnt[K] | off[K+1]   (radix path: seg_lo | seg_hi)
+  size_t scan_bytes = 0;
+  if ((int64_t) L.n_seg > SCAN_SMALL_MAX) {
+    e = cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (const uint32_t*) nullptr, (uint32_t*) nullptr, (int64_t) L.n_seg,
+                                      (cudaStream_t) 0);
+    KGE_REQUIRE(e == cudaSuccess, KGE_ECUDA, "cub scan temp-size query failed: %s", cudaGetErrorString(e));
+    if (scan_bytes > L.cub_bytes) { /* the scan reuses the radix sort's temp region */
+      KGE_REQUIRE(false, KGE_EUNSUPPORTED, "scan temp storage exceeds the sort's (%zu > %zu)", scan_bytes, L.cub_bytes);
+    }
+  }
   L.total_rows = 0;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     L.rld[s] = (cols[s] + 3) / 4 * 4;
@@ -128,7 +139,7 @@ static int launch_constrain(const kge_ctx_impl* ctx, const ConstrainParams& cp, 
 
 // sort keys, record ids and the negatives used, one thread per record slot; runs on the side
 // stream concurrently with k_step (the keys depend on the ids only, not on any weight)
-__global__ void __launch_bounds__(256) k_keys(const StepParams p) {
+__global__ void __launch_bounds__(256) k_keys(const StepParams p, uint32_t* cnt) {
   const int64_t nneg = p.B * (int64_t) p.k_eff, nE = 2 * p.B + nneg;
   for (int64_t s = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; s < nE + p.B; s += (int64_t) gridDim.x * blockDim.x) {
     uint32_t key;
@@ -144,8 +155,10 @@ __global__ void __launch_bounds__(256) k_keys(const StepParams p) {
     } else key = (uint32_t) (p.md.t[KGE_T_ENT].rows + load_id(p.triples, 3 * (s - nE) + 1, p.id64));
     p.keys[s] = key;
     p.vals[s] = (uint32_t) s;
+    if (cnt) atomicAdd(cnt + key, 1u);          // histogram of the counting sort (group_kernels.cuh)
   }
 }
+
 
 __global__ void k_sample(SamplerDev sd, const void* triples, int id64, int64_t B, int64_t* out) {
   const int64_t n = (int64_t) B * sd.k_eff;
@@ -309,6 +322,10 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   uint32_t* vals_out = reinterpret_cast<uint32_t*>(wsb + L.off_vals_out);
   uint32_t* seg_lo = reinterpret_cast<uint32_t*>(wsb + L.off_seg);
   uint32_t* seg_hi = seg_lo + L.n_seg;
+  // what the update kernels read: radix path = the two tables of k_segments; counting sort =
+  // the scan itself (first position of key = off[key], one past the last = off[key + 1])
+  const uint32_t* use_lo = (ctx->opt_radix_sort != 0) ? seg_lo : seg_lo + L.n_seg;
+  const uint32_t* use_hi = (ctx->opt_radix_sort != 0) ? seg_hi : seg_lo + L.n_seg + 1;
   auto fork_side = [&]() -> int {
     if (!is_train) {
       pt.begin(0);
@@ -322,14 +339,36 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     pt.begin(3, ax);
     int64_t kb = (L.n_keys + 255) / 256;
     if (kb > (int64_t) ctx->sm_count * 8) kb = (int64_t) ctx->sm_count * 8;
-    k_keys<<<(unsigned) kb, 256, 0, ax>>>(p);
-    KGE_CUDA_OK(cudaGetLastError());
-    KGE_CUDA_OK(cudaMemsetAsync(seg_lo, 0, sizeof(uint32_t) * 2 * L.n_seg, ax));
-    size_t cub_bytes = L.cub_bytes;
-    KGE_CUDA_OK(cub::DeviceRadixSort::SortPairs(wsb + L.off_cub, cub_bytes, (const uint32_t*) p.keys, keys_out,
-                                                (const uint32_t*) p.vals, vals_out, (int) L.n_keys, 0, sort_bits(cfg), ax));
-    k_segments<<<(unsigned) ((L.n_keys + 255) / 256), 256, 0, ax>>>(keys_out, L.n_keys, seg_lo, seg_hi);
-    KGE_CUDA_OK(cudaGetLastError());
+    KGE_CUDA_OK(cudaMemsetAsync(seg_lo, 0, sizeof(uint32_t) * (2 * L.n_seg + 1), ax));
+    if ((ctx->opt_radix_sort != 0)) {
+      k_keys<<<(unsigned) kb, 256, 0, ax>>>(p, nullptr);
+      KGE_CUDA_OK(cudaGetLastError());
+      size_t cub_bytes = L.cub_bytes;
+      KGE_CUDA_OK(cub::DeviceRadixSort::SortPairs(wsb + L.off_cub, cub_bytes, (const uint32_t*) p.keys, keys_out,
+                                                  (const uint32_t*) p.vals, vals_out, (int) L.n_keys, 0, sort_bits(cfg), ax));
+      k_segments<<<(unsigned) ((L.n_keys + 255) / 256), 256, 0, ax>>>(keys_out, L.n_keys, seg_lo, seg_hi);
+      KGE_CUDA_OK(cudaGetLastError());
+    } else {
+      // counting sort: histogram (in k_keys) -> scan -> scatter -> canonical order inside each segment
+      uint32_t* cnt = seg_lo;
+      uint32_t* off = seg_lo + L.n_seg;
+      const int64_t K = (int64_t) L.n_seg;
+      k_keys<<<(unsigned) kb, 256, 0, ax>>>(p, cnt);
+      KGE_CUDA_OK(cudaGetLastError());
+      if (K <= SCAN_SMALL_MAX) k_scan<<<1, SCAN_THREADS, 0, ax>>>(cnt, off, K);
+      else {
+        size_t scan_bytes = L.cub_bytes;
+        KGE_CUDA_OK(cub::DeviceScan::ExclusiveSum(wsb + L.off_cub, scan_bytes, (const uint32_t*) cnt, off, K, ax));
+        k_scan_close<<<1, 1, 0, ax>>>(cnt, off, K);
+      }
+      KGE_CUDA_OK(cudaGetLastError());
+      k_scatter<<<(unsigned) kb, 256, 0, ax>>>(p.keys, L.n_keys, off, cnt, p.vals);
+      KGE_CUDA_OK(cudaGetLastError());
+      int64_t cb = (K + CANON_WARPS - 1) / CANON_WARPS;
+      if (cb > (int64_t) ctx->sm_count * 16) cb = (int64_t) ctx->sm_count * 16;
+      k_canon<<<(unsigned) cb, CANON_WARPS * 32, 0, ax>>>(off, K, p.vals, vals_out);
+      KGE_CUDA_OK(cudaGetLastError());
+    }
     pt.end(3, ax);
     KGE_CUDA_OK(cudaEventRecord(ctx->ev_join, ax));
     pt.begin(0);
@@ -435,7 +474,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   up.keys = keys_out;
   up.vals = vals_out;
   up.n_keys = is_train ? L.n_keys : 0;
-  up.seg_lo = seg_lo; up.seg_hi = seg_hi;
+  up.seg_lo = use_lo; up.seg_hi = use_hi;
   up.scal = rp.scal;
   const float b1p = powf(cfg->beta1, (float) adam_t), b2p = powf(cfg->beta2, (float) adam_t);
   up.lr_t = cfg->lr * sqrtf(1.0f - b2p) / (1.0f - b1p);
@@ -467,7 +506,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     mu.triples = triples; mu.id64 = cfg->id_dtype; mu.neg_ids = p.neg_ids;
     mu.B = B; mu.k = k; mu.side_mode = cfg->corrupt_side;
     mu.keys = keys_out; mu.vals = vals_out; mu.n_keys = is_train ? L.n_keys : 0;
-    mu.seg_lo = seg_lo; mu.seg_hi = seg_hi;
+    mu.seg_lo = use_lo; mu.seg_hi = use_hi;
     mu.key_base = (uint32_t) cfg->n_ent; mu.rec_base = (uint32_t) L.n_ent_rec;
     mu.scal = rp.scal; mu.lr_t = up.lr_t; mu.beta1 = cfg->beta1; mu.beta2 = cfg->beta2; mu.eps = cfg->eps;
     mu.reg_coef = (dense && cfg->model == KGE_RESCAL) ? 2.0f * cfg->constraint_weight / (float) cfg->n_rel : 0.f;

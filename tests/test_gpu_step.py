@@ -228,3 +228,32 @@ def test_matrix_step_is_bitwise_deterministic():
         outs.append(tables_of(eng, "TransR"))
     for kk in outs[0]:
         assert torch.equal(outs[0][kk], outs[1][kk])
+
+
+@pytest.mark.parametrize("model,B,k,n_rel", [
+    ("DistMult", 512, 64, 11),        # long relation segments (> 32 ids): bitmap windows
+    ("TransE", 2048, 40, 3),          # segments longer than one 32768-id window span
+    ("TransD", 64, 2, 11),            # short segments only: warp bitonic network
+    ("TransR", 96, 6, 4),             # matrix gradients read the relation segments in order
+])
+def test_grouping_equals_stable_radix_sort(model, B, k, n_rel):
+    """The counting sort (csrc/group_kernels.cuh) must hand the update kernels exactly the record
+    order of cub's stable radix sort: weights after several steps are bit-identical."""
+    from KGE._b200 import lib as L
+    rng = np.random.default_rng(17)
+    score = None if model == "DistMult" else SCORES["l2pow"]
+    d, dr = (24, 20) if model == "TransR" else (40, None)
+    outs = []
+    for radix in (1, 0):
+        _, _, eng = make_pair(model, 120, n_rel, d, dr, score=score, loss=LOSSES["hinge"], k=k, side="h+t")
+        eng.set_option(L.OPT_RADIX_SORT, radix)
+        r2 = np.random.default_rng(17)
+        try:
+            for step in range(3):
+                eng.train_step(rand_triples(r2, B, 120, n_rel), 5, step)
+            torch.cuda.synchronize()
+        finally:
+            eng.set_option(L.OPT_RADIX_SORT, 0)
+        outs.append({s: t.storage.clone() for s, t in eng.tab.items()})
+    for s in outs[0]:
+        assert torch.equal(outs[0][s], outs[1][s]), f"slot {s}"
