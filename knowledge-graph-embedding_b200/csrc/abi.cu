@@ -39,6 +39,8 @@ extern "C" int kge_ctx_create(int device, kge_ctx** out) {
   KGE_CUDA_OK(cudaStreamCreateWithPriority(&c->aux, cudaStreamNonBlocking, prio_greatest));
   KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+  KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_mid, cudaEventDisableTiming));
+  KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_heavy, cudaEventDisableTiming));
   KGE_CUDA_OK(cudaMalloc(&c->ticket, 64 * sizeof(unsigned)));
   KGE_CUDA_OK(cudaMemset(c->ticket, 0, 64 * sizeof(unsigned)));
   *out = reinterpret_cast<kge_ctx*>(c);
@@ -58,6 +60,8 @@ extern "C" int kge_ctx_destroy(kge_ctx* ctx) {
     if (c->aux) { cudaStreamSynchronize(c->aux); cudaStreamDestroy(c->aux); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->ev_mid) cudaEventDestroy(c->ev_mid);
+    if (c->ev_heavy) cudaEventDestroy(c->ev_heavy);
     if (c->ticket) cudaFree(c->ticket);
   }
   delete c;

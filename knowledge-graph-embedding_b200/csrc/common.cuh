@@ -9,6 +9,7 @@ namespace kge {
 
 constexpr int WARP = 32;
 constexpr unsigned FULL = 0xffffffffu;
+constexpr int UPD_HEAVY = 48;     // table rows with more gradient records are summed by a whole CTA
 
 // ---- error plumbing (abi.cu owns the thread-local string) -----------------------
 void set_error(const char* fmt, ...);
@@ -37,7 +38,7 @@ struct kge_ctx_impl {
   // side stream of kge_train_step (sort keys are independent of the weights, so key generation,
   // the radix sort and the segment table overlap the step kernel) + its fork / join events
   cudaStream_t aux = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_mid = nullptr, ev_heavy = nullptr;
   int opt_radix_sort = 0;         // kge_set_option(KGE_OPT_RADIX_SORT)
   unsigned* ticket = nullptr;     // device, 64 words, zero between calls (self-resetting counters)
 };

@@ -90,18 +90,26 @@ constexpr int CANON_WARPS = 8;
 
 // one warp per key
 __global__ void __launch_bounds__(CANON_WARPS * 32) k_canon(const uint32_t* __restrict__ off, int64_t K,
-                                                            const uint32_t* __restrict__ vals_tmp, uint32_t* __restrict__ vals) {
+                                                            const uint32_t* __restrict__ vals_tmp, uint32_t* __restrict__ vals,
+                                                            uint32_t* __restrict__ hdr, uint32_t* __restrict__ heavy_keys,
+                                                            uint32_t* n_heavy) {
   __shared__ uint32_t s_bits[CANON_WARPS][CANON_WORDS];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int64_t key = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
   for (; key < K; key += nw) {
     const uint32_t lo = off[key], hi = off[key + 1], L = hi - lo;
+    // header of the key for k_update_fast: [count, first position, first six ids, ascending]
+    if (lane == 0) {
+      hdr[key * 8] = L; hdr[key * 8 + 1] = lo;
+      if (L > (uint32_t) UPD_HEAVY) heavy_keys[atomicAdd(n_heavy, 1u)] = (uint32_t) key;   // list order is irrelevant
+    }
     if (L == 0) continue;
     if (L <= 32) {
       uint32_t v = (lane < L) ? vals_tmp[lo + lane] : 0xffffffffu;
       if (L > 1) v = warp_bitonic_sort(v, lane);
       if (lane < L) vals[lo + lane] = v;
+      if (lane < 6 && lane < L) hdr[key * 8 + 2 + lane] = v;
       continue;
     }
     // long segment: min / max id, then bitmap windows
@@ -138,6 +146,7 @@ __global__ void __launch_bounds__(CANON_WARPS * 32) k_canon(const uint32_t* __re
       written += __shfl_sync(FULL, inc, 31);
       __syncwarp();
     }
+    if (lane < 6) hdr[key * 8 + 2 + lane] = vals[lo + lane];       // written by this warp, ordered by __syncwarp
   }
 }
 

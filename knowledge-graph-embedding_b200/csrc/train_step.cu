@@ -14,7 +14,7 @@ namespace kge {
 
 struct StepWs {
   size_t off_part, off_scal, off_neg, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub,
-      off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart, off_seg;
+      off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart, off_seg, off_hdr, off_heavy;
   size_t cub_bytes, total, n_seg;
   int64_t n_ent_rec, n_keys, total_rows, n_mat_cta;
   int rld[KGE_MAX_TABLES];
@@ -70,7 +70,9 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   KGE_REQUIRE(e == cudaSuccess, KGE_ECUDA, "cub temp-size query failed: %s", cudaGetErrorString(e));
   L.off_cub = take(L.cub_bytes);
   L.n_seg = (size_t) c->n_ent + (size_t) c->n_rel;
-  L.off_seg = take(sizeof(uint32_t) * (2 * L.n_seg + 1));   // cnt[K] | off[K+1]   (radix path: seg_lo | seg_hi)
+  L.off_seg = take(sizeof(uint32_t) * (2 * L.n_seg + 2));   // cnt[K] | off[K+1] | n_heavy   (radix path: seg_lo | seg_hi)
+  L.off_hdr = take(sizeof(uint32_t) * 8 * L.n_seg);         // k_canon's per-key headers
+  L.off_heavy = take(sizeof(uint32_t) * (size_t) (L.n_keys / UPD_HEAVY + 1));
   size_t scan_bytes = 0;
   if ((int64_t) L.n_seg > SCAN_SMALL_MAX) {
     e = cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (const uint32_t*) nullptr, (uint32_t*) nullptr, (int64_t) L.n_seg,
@@ -339,7 +341,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     pt.begin(3, ax);
     int64_t kb = (L.n_keys + 255) / 256;
     if (kb > (int64_t) ctx->sm_count * 8) kb = (int64_t) ctx->sm_count * 8;
-    KGE_CUDA_OK(cudaMemsetAsync(seg_lo, 0, sizeof(uint32_t) * (2 * L.n_seg + 1), ax));
+    KGE_CUDA_OK(cudaMemsetAsync(seg_lo, 0, sizeof(uint32_t) * (2 * L.n_seg + 2), ax));
     if ((ctx->opt_radix_sort != 0)) {
       k_keys<<<(unsigned) kb, 256, 0, ax>>>(p, nullptr);
       KGE_CUDA_OK(cudaGetLastError());
@@ -366,7 +368,10 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
       KGE_CUDA_OK(cudaGetLastError());
       int64_t cb = (K + CANON_WARPS - 1) / CANON_WARPS;
       if (cb > (int64_t) ctx->sm_count * 16) cb = (int64_t) ctx->sm_count * 16;
-      k_canon<<<(unsigned) cb, CANON_WARPS * 32, 0, ax>>>(off, K, p.vals, vals_out);
+      k_canon<<<(unsigned) cb, CANON_WARPS * 32, 0, ax>>>(off, K, p.vals, vals_out,
+                                                          reinterpret_cast<uint32_t*>(wsb + L.off_hdr),
+                                                          reinterpret_cast<uint32_t*>(wsb + L.off_heavy),
+                                                          seg_lo + 2 * L.n_seg + 1);
       KGE_CUDA_OK(cudaGetLastError());
     }
     pt.end(3, ax);
@@ -475,6 +480,9 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   up.vals = vals_out;
   up.n_keys = is_train ? L.n_keys : 0;
   up.seg_lo = use_lo; up.seg_hi = use_hi;
+  up.hdr = reinterpret_cast<const uint32_t*>(wsb + L.off_hdr);
+  up.heavy_keys = reinterpret_cast<const uint32_t*>(wsb + L.off_heavy);
+  up.n_heavy = seg_lo + 2 * L.n_seg + 1;
   up.scal = rp.scal;
   const float b1p = powf(cfg->beta1, (float) adam_t), b2p = powf(cfg->beta2, (float) adam_t);
   up.lr_t = cfg->lr * sqrtf(1.0f - b2p) / (1.0f - b1p);
@@ -547,7 +555,20 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     k_update_mat<0><<<mgrid, MU_THREADS, 0, st>>>(mu);
     KGE_CUDA_OK(cudaGetLastError());
   }
-  if (int rc2 = dense ? launch_update<2>(up, cpl, ublocks, st) : launch_update<0>(up, cpl, ublocks, st)) return rc2;
+  if (dense) {
+    if (int rc2 = launch_update<2>(up, cpl, ublocks, st)) return rc2;
+  } else if (ctx->opt_radix_sort) {
+    if (int rc2 = launch_update<0>(up, cpl, ublocks, st)) return rc2;
+  } else {
+    // light rows: independent warps on the caller's stream; the few rows with many records are
+    // summed by whole CTAs on the side stream at the same time (disjoint rows)
+    KGE_CUDA_OK(cudaEventRecord(ctx->ev_mid, st));
+    KGE_CUDA_OK(cudaStreamWaitEvent(ctx->aux, ctx->ev_mid, 0));
+    if (int rc2 = launch_update_heavy(up, cpl, L.n_keys / UPD_HEAVY + 1, ctx->aux)) return rc2;
+    KGE_CUDA_OK(cudaEventRecord(ctx->ev_heavy, ctx->aux));
+    if (int rc2 = launch_update_fast(up, cpl, st)) return rc2;
+    KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_heavy, 0));
+  }
   pt.end(4);
   return KGE_OK;
 }
@@ -629,6 +650,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     max_ch = ((U.cols + 3) / 4 > max_ch) ? (U.cols + 3) / 4 : max_ch;
   }
   up.keys = nullptr; up.vals = nullptr; up.n_keys = 0; up.seg_lo = nullptr; up.seg_hi = nullptr;
+  up.hdr = nullptr; up.heavy_keys = nullptr; up.n_heavy = nullptr;
   up.scal = scal;
   const float b1p = powf(cfg->beta1, (float) adam_t), b2p = powf(cfg->beta2, (float) adam_t);
   up.lr_t = cfg->lr * sqrtf(1.0f - b2p) / (1.0f - b1p);

@@ -105,6 +105,9 @@ struct UpdateParams {
   float lr_t, beta1, beta2, eps;
   float cw;              // constraint_weight
   float* rowpart;        // DENSE=1: [2][total_rows]  (norm^2, loss term) per row
+  const uint32_t* hdr;   // k_update_fast: per key [count, first position, first 6 record ids] (k_canon)
+  const uint32_t* heavy_keys;  // keys with more than UPD_HEAVY records (k_canon): k_update_heavy's work list
+  const uint32_t* n_heavy;
 };
 
 __device__ __forceinline__ int64_t lower_bound_u32(const uint32_t* a, int64_t n, uint32_t key) {
@@ -127,9 +130,36 @@ __global__ void __launch_bounds__(256) k_segments(const uint32_t* __restrict__ k
   if (i == n - 1 || keys[i + 1] != k) seg_hi[k] = (uint32_t) (i + 1);
 }
 
-// Sum of the records at sorted positions [lo, hi) into the lane's chunks c = lane + 32 u, in
-// sorted (stable) order.  Record ids are fetched 32 at a time; the row loads of 4 records x CPL
-// chunks are independent, so many are in flight.  All 32 lanes must call.
+// Sum of n <= 32 records whose ids sit one per lane in `mine`, added to the lane's chunks
+// c = lane + 32 u strictly in lane (= sorted, stable) order.  The row loads of J records x CPL
+// chunks are independent, so many are in flight; the ragged last batch is predicated, not serial.
+// All 32 lanes must call.
+template <int CPL>
+__device__ __forceinline__ void sum_chunk(uint32_t mine, int n, const float* __restrict__ rec, int rec_ld, int nch, int lane,
+                                          float4 (&g)[CPL]) {
+  constexpr int J = CPL <= 2 ? 4 : (CPL == 4 ? 2 : 1);       // records in flight (register budget)
+  for (int j = 0; j < n; j += J) {
+    const float4* r[J];
+#pragma unroll
+    for (int x = 0; x < J; ++x)
+      r[x] = reinterpret_cast<const float4*>(rec + (int64_t) __shfl_sync(FULL, mine, (j + x) & 31) * rec_ld);
+    float4 a[CPL][J];
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) {
+      const int c = lane + 32 * u;
+#pragma unroll
+      for (int x = 0; x < J; ++x) a[u][x] = (c < nch && j + x < n) ? __ldg(r[x] + c) : f4zero();
+    }
+#pragma unroll
+    for (int x = 0; x < J; ++x)
+      if (j + x < n) {
+#pragma unroll
+        for (int u = 0; u < CPL; ++u) g[u] += a[u][x];
+      }
+  }
+}
+
+// Records at sorted positions [lo, hi), ids fetched 32 at a time.
 template <int CPL>
 __device__ __forceinline__ void sum_records(const uint32_t* __restrict__ vals, const float* __restrict__ rec, int rec_ld,
                                             uint32_t rec_base, int64_t lo, int64_t hi, int nch, int lane,
@@ -137,33 +167,39 @@ __device__ __forceinline__ void sum_records(const uint32_t* __restrict__ vals, c
   for (int64_t q0 = lo; q0 < hi; q0 += WARP) {
     const int n = (int) ((hi - q0 < WARP) ? hi - q0 : WARP);
     const uint32_t mine = (lane < n) ? __ldg(vals + q0 + lane) - rec_base : 0u;
-    constexpr int J = CPL <= 2 ? 4 : (CPL == 4 ? 2 : 1);       // records in flight (register budget)
-    int j = 0;
-    for (; j + J <= n; j += J) {
-      const float4* r[J];
-#pragma unroll
-      for (int x = 0; x < J; ++x) r[x] = reinterpret_cast<const float4*>(rec + (int64_t) __shfl_sync(FULL, mine, j + x) * rec_ld);
-      float4 a[CPL][J];
-#pragma unroll
-      for (int u = 0; u < CPL; ++u) {
-        const int c = lane + 32 * u;
-#pragma unroll
-        for (int x = 0; x < J; ++x) a[u][x] = (c < nch) ? __ldg(r[x] + c) : f4zero();
-      }
-#pragma unroll
-      for (int u = 0; u < CPL; ++u)
-#pragma unroll
-        for (int x = 0; x < J; ++x) g[u] += a[u][x];
-    }
-    for (; j < n; ++j) {
-      const float4* r0 = reinterpret_cast<const float4*>(rec + (int64_t) __shfl_sync(FULL, mine, j) * rec_ld);
-#pragma unroll
-      for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) g[u] += __ldg(r0 + c); }
-    }
+    sum_chunk<CPL>(mine, n, rec, rec_ld, nch, lane, g);
   }
 }
 
-constexpr int UPD_HEAVY = 48;     // rows with more records are summed by the whole CTA
+// Keras Adam, sparse path: m = b1*m (+ (1-b1) g on touched rows), likewise v; then
+// w -= lr_t * m / (sqrt(v) + eps) for EVERY row.  One function for every
+// update kernel so the arithmetic (and its FMA contraction) is the same everywhere.
+__device__ __forceinline__ float adam1(float& w, float& m, float& v, float g, float b1, float b2, float lr_t, float eps) {
+  // explicit rounding of every operation: no context-dependent FMA contraction, so every kernel
+  // that updates a row produces the same bits
+  m = __fadd_rn(__fmul_rn(b1, m), __fmul_rn(1.f - b1, g));
+  v = __fadd_rn(__fmul_rn(b2, v), __fmul_rn(__fmul_rn(1.f - b2, g), g));
+  w = __fsub_rn(w, __fdiv_rn(__fmul_rn(lr_t, m), __fadd_rn(sqrtf(v), eps)));
+  return w;
+}
+__device__ __forceinline__ void adam_chunk(float4& w, float4& m, float4& v, const float4 gg, float b1, float b2, float lr_t,
+                                           float eps) {
+  adam1(w.x, m.x, v.x, gg.x, b1, b2, lr_t, eps);
+  adam1(w.y, m.y, v.y, gg.y, b1, b2, lr_t, eps);
+  adam1(w.z, m.z, v.z, gg.z, b1, b2, lr_t, eps);
+  adam1(w.w, m.w, v.w, gg.w, b1, b2, lr_t, eps);
+}
+__device__ __forceinline__ float4 scale4(float s, float4 a) {
+  return f4(__fmul_rn(s, a.x), __fmul_rn(s, a.y), __fmul_rn(s, a.z), __fmul_rn(s, a.w));
+}
+// keep the zero-padding invariant on the ragged last chunk
+__device__ __forceinline__ void mask_tail(float4& w, float4& m, float4& v, int c, int cols) {
+  const int e0 = 4 * c;
+  if (e0 + 1 >= cols) { w.y = 0.f; m.y = 0.f; v.y = 0.f; }
+  if (e0 + 2 >= cols) { w.z = 0.f; m.z = 0.f; v.z = 0.f; }
+  if (e0 + 3 >= cols) { w.w = 0.f; m.w = 0.f; v.w = 0.f; }
+}
+
 
 // One warp per table row (8 rows per CTA); CPL = float4 chunks per lane (row width <= 128*CPL floats).
 template <int DENSE, int CPL>
@@ -298,23 +334,135 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
       gg += ca * w;
       if (o4) gg += cb * o4[c];
     }
-    gg = scale * gg;
+    gg = scale4(scale, gg);
     float4 m = m4[c], v = v4[c];
-    // Keras Adam, sparse path: m = b1*m (+ (1-b1) g on touched rows), likewise v; then
-    // w -= lr_t * m / (sqrt(v) + eps) for EVERY row.
-    m = f4(b1 * m.x + (1.f - b1) * gg.x, b1 * m.y + (1.f - b1) * gg.y,
-           b1 * m.z + (1.f - b1) * gg.z, b1 * m.w + (1.f - b1) * gg.w);
-    v = f4(b2 * v.x + (1.f - b2) * gg.x * gg.x, b2 * v.y + (1.f - b2) * gg.y * gg.y,
-           b2 * v.z + (1.f - b2) * gg.z * gg.z, b2 * v.w + (1.f - b2) * gg.w * gg.w);
-    w = f4(w.x - p.lr_t * m.x / (sqrtf(v.x) + p.eps), w.y - p.lr_t * m.y / (sqrtf(v.y) + p.eps),
-           w.z - p.lr_t * m.z / (sqrtf(v.z) + p.eps), w.w - p.lr_t * m.w / (sqrtf(v.w) + p.eps));
-    // keep the zero-padding invariant on the ragged last chunk
-    const int e0 = 4 * c;
-    if (e0 + 1 >= T.cols) { w.y = 0.f; m.y = 0.f; v.y = 0.f; }
-    if (e0 + 2 >= T.cols) { w.z = 0.f; m.z = 0.f; v.z = 0.f; }
-    if (e0 + 3 >= T.cols) { w.w = 0.f; m.w = 0.f; v.w = 0.f; }
+    adam_chunk(w, m, v, gg, b1, b2, p.lr_t, p.eps);
+    mask_tail(w, m, v, c, T.cols);
     m4[c] = m; v4[c] = v; w4[c] = w;
   }
+}
+
+// The common training case (no dense regulariser): one warp per table row, warps fully
+// independent (no CTA barrier), dependent-load chain shortened to header -> records -> w/m/v:
+//   * the w / m / v lines are requested into L2 first (no registers held),
+//   * one 32-byte header per key gives the record count, the first sorted position and the first
+//     six record ids, so most rows never read the id array,
+//   * rows with more than UPD_HEAVY records are left to k_update_heavy (whole-CTA summation),
+//     which runs concurrently on the side stream.
+// Summation order and update arithmetic are those of k_update: results are bit-identical.
+template <int CPL>
+__global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t gw = (int64_t) blockIdx.x * 2 + (threadIdx.x >> 5);
+  if (gw >= p.total_rows) return;
+  int64_t row = gw;
+  int j = 0;
+  while (j < p.n_tabs - 1 && row >= p.tab[j].rows) { row -= p.tab[j].rows; ++j; }
+  const UpdateTable& T = p.tab[j];
+  const int nch = (T.cols + 3) >> 2;
+  float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
+  float4* m4 = reinterpret_cast<float4*>(T.m + row * (int64_t) T.ld);
+  float4* v4 = reinterpret_cast<float4*>(T.v + row * (int64_t) T.ld);
+#pragma unroll
+  for (int u = 0; u < CPL; ++u) {
+    const int c = lane + 32 * u;
+    if (c < nch && (c & 7) == 0) {                   // one request per 128-byte line
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(w4 + c));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(m4 + c));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(v4 + c));
+    }
+  }
+  uint32_t hv = 0;
+  if (T.rec != nullptr && lane < 8) hv = __ldg(p.hdr + ((int64_t) T.key_base + row) * 8 + lane);
+  const uint32_t L = __shfl_sync(FULL, hv, 0), lo = __shfl_sync(FULL, hv, 1);
+  if (L > (uint32_t) UPD_HEAVY) return;             // k_update_heavy's row
+  float4 g[CPL];
+#pragma unroll
+  for (int u = 0; u < CPL; ++u) g[u] = f4zero();
+  if (L > 0) {
+    const int n0 = (int) (L < 32u ? L : 32u);
+    uint32_t mine = __shfl_sync(FULL, hv, (lane + 2) & 31);           // lanes 0..5: ids from the header
+    if (lane >= 6 && lane < n0) mine = __ldg(p.vals + lo + lane);
+    mine = (lane < n0) ? mine - T.rec_base : 0u;
+    sum_chunk<CPL>(mine, n0, T.rec, T.rec_ld, nch, lane, g);
+    if (L > 32u) sum_records<CPL>(p.vals, T.rec, T.rec_ld, T.rec_base, (int64_t) lo + 32, (int64_t) lo + L, nch, lane, g);
+  }
+  const float scale = p.scal[T.slot];
+#pragma unroll
+  for (int u = 0; u < CPL; ++u) {
+    const int c = lane + 32 * u;
+    if (c >= nch) continue;
+    float4 w = w4[c], m = m4[c], v = v4[c];
+    const float4 gg = scale4(scale, g[u]);
+    adam_chunk(w, m, v, gg, p.beta1, p.beta2, p.lr_t, p.eps);
+    mask_tail(w, m, v, c, T.cols);
+    m4[c] = m; v4[c] = v; w4[c] = w;
+  }
+}
+
+// Rows with many records (hot entities / relations): one CTA per (heavy key, table), the eight
+// warps sum contiguous slices of the sorted record list, partials are combined in slice order —
+// the order k_update uses for its heavy rows, so the bits agree.
+template <int CPL>
+__global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
+  __shared__ float4 s_part[8][CPL * WARP];
+  if (blockIdx.x >= *p.n_heavy) return;
+  const uint32_t key = p.heavy_keys[blockIdx.x];
+  const UpdateTable& T = p.tab[blockIdx.y];
+  if (T.rec == nullptr || key < T.key_base || (int64_t) (key - T.key_base) >= T.rows) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t row = key - T.key_base;
+  const int nch = (T.cols + 3) >> 2;
+  const int64_t lo = __ldg(p.seg_lo + key), L = (int64_t) __ldg(p.seg_hi + key) - lo;
+  float4 part[CPL];
+#pragma unroll
+  for (int u = 0; u < CPL; ++u) part[u] = f4zero();
+  sum_records<CPL>(p.vals, T.rec, T.rec_ld, T.rec_base, lo + L * warp / 8, lo + L * (warp + 1) / 8, nch, lane, part);
+#pragma unroll
+  for (int u = 0; u < CPL; ++u) s_part[warp][u * WARP + lane] = part[u];
+  __syncthreads();
+  if (warp != 0) return;
+  float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
+  float4* m4 = reinterpret_cast<float4*>(T.m + row * (int64_t) T.ld);
+  float4* v4 = reinterpret_cast<float4*>(T.v + row * (int64_t) T.ld);
+  const float scale = p.scal[T.slot];
+#pragma unroll
+  for (int u = 0; u < CPL; ++u) {
+    const int c = lane + 32 * u;
+    if (c >= nch) continue;
+    float4 g = f4zero();
+    for (int w3 = 0; w3 < 8; ++w3) g += s_part[w3][u * WARP + lane];
+    float4 w = w4[c], m = m4[c], v = v4[c];
+    adam_chunk(w, m, v, scale4(scale, g), p.beta1, p.beta2, p.lr_t, p.eps);
+    mask_tail(w, m, v, c, T.cols);
+    m4[c] = m; v4[c] = v; w4[c] = w;
+  }
+}
+
+inline int launch_update_heavy(const UpdateParams& up, int cpl, int64_t max_heavy, cudaStream_t st) {
+  const dim3 grid((unsigned) max_heavy, (unsigned) up.n_tabs, 1);
+  switch (cpl) {
+    case 1: k_update_heavy<1><<<grid, 256, 0, st>>>(up); break;
+    case 2: k_update_heavy<2><<<grid, 256, 0, st>>>(up); break;
+    case 4: k_update_heavy<4><<<grid, 256, 0, st>>>(up); break;
+    default: k_update_heavy<8><<<grid, 256, 0, st>>>(up); break;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("k_update_heavy launch failed: %s", cudaGetErrorString(e)); return KGE_ECUDA; }
+  return KGE_OK;
+}
+
+inline int launch_update_fast(const UpdateParams& up, int cpl, cudaStream_t st) {
+  const unsigned blocks = (unsigned) ((up.total_rows + 1) / 2);
+  switch (cpl) {
+    case 1: k_update_fast<1><<<blocks, 64, 0, st>>>(up); break;
+    case 2: k_update_fast<2><<<blocks, 64, 0, st>>>(up); break;
+    case 4: k_update_fast<4><<<blocks, 64, 0, st>>>(up); break;
+    default: k_update_fast<8><<<blocks, 64, 0, st>>>(up); break;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("k_update_fast launch failed: %s", cudaGetErrorString(e)); return KGE_ECUDA; }
+  return KGE_OK;
 }
 
 template <int DENSE>
