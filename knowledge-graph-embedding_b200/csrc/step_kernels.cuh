@@ -137,7 +137,76 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
     draw(0);
     if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, 0), lane);
   }
-  for (int it = 0; it < n_it; ++it) {
+  // DistMult fast path.  s = sum(e_h * r * e_t) is linear in the corrupted entity, so with
+  // q = r*t (head corrupted) or h*r (tail corrupted) fixed per positive:  s_neg = N . q,
+  // d s/d N = q, and the shared rows' gradients are (sum_neg dneg * N) * {r, kept entity}: one
+  // accumulator A instead of three gradient rows per negative.  Per-occurrence norm^2 (what
+  // tf.clip_by_norm sums over the un-merged IndexedSlices) stays exact per negative:
+  // dneg^2 * (|q|^2 + sum N^2 r^2) for the entity table, dneg^2 * sum N^2 kept^2 for the relation.
+  // Needs the corrupted side to be fixed per warp: true unless 'h+t' meets an odd warp count.
+  bool fast_done = false;
+  if constexpr (M::KIND == KGE_DISTMULT) {
+    if (p.sd.side_mode != KGE_SIDE_HT || (wpp & 1) == 0) {
+      fast_done = true;
+      const bool head = neg_is_head(p.sd, wig);
+      Row<NV> q, r2, o2, A;
+      A.zero();
+#pragma unroll
+      for (int v = 0; v < NV; ++v) {
+        const float4 o = head ? T.e.v[v] : H.e.v[v];
+        q.v[v] = R.a.v[v] * o;
+        r2.v[v] = R.a.v[v] * R.a.v[v];
+        o2.v[v] = o * o;
+      }
+      const float q2 = row_dot_partial(q, q);
+      for (int it = 0; it < n_it; ++it) {
+        const int c = wig + it * wpp;
+        const int64_t slot = i * k + c;
+        const int64_t e = __shfl_sync(FULL, my_e, it & 31);
+        Ent N;
+        if (PREFETCH) N = Nnext; else N.load(md, e, lane);
+        if (it + 1 < n_it) {
+          if (((it + 1) & 31) == 0) draw(it + 1);
+          if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, (it + 1) & 31), lane);
+        }
+        if (lane == 0 && p.write_keys) {
+          p.neg_ids[slot] = e;
+          if (TRAIN) { p.keys[2 * p.B + slot] = (uint32_t) e; p.vals[2 * p.B + slot] = (uint32_t)(2 * p.B + slot); }
+        }
+        const float sn = warp_sum(row_dot_partial(N.e, q));
+        const float w = softmax ? expf(p.loss.temperature * sn - sm_max) * sm_inv : 1.f;
+        float term, dneg, dpp;
+        loss_neg(p.loss, sp, sn, w, term, dneg, dpp);
+        lsum += term;
+        gpos += dpp;
+        if (TRAIN) {
+          Row<NV> gN;
+          float pe = 0.f, pr = 0.f;
+#pragma unroll
+          for (int v = 0; v < NV; ++v) {
+            gN.v[v] = dneg * q.v[v];
+            A.v[v] += dneg * N.e.v[v];
+            const float4 n2 = N.e.v[v] * N.e.v[v];
+            pe += dot4(n2, r2.v[v]);
+            pr += dot4(n2, o2.v[v]);
+          }
+          const float d2 = dneg * dneg;
+          nrm[KGE_T_ENT] += d2 * (q2 + pe);
+          nrm[KGE_T_REL_A] += d2 * pr;
+          store_row(gN, p.rec[KGE_T_ENT], 2 * p.B + slot, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+        }
+      }
+      if (TRAIN) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+          const float4 ar = A.v[v] * R.a.v[v];
+          if (head) { GT.e.v[v] += ar; GR.a.v[v] += A.v[v] * T.e.v[v]; }
+          else      { GH.e.v[v] += ar; GR.a.v[v] += A.v[v] * H.e.v[v]; }
+        }
+      }
+    }
+  }
+  for (int it = 0; !fast_done && it < n_it; ++it) {
     const int c = wig + it * wpp;
     const bool head = neg_is_head(p.sd, c);
     const int64_t slot = i * k + c;

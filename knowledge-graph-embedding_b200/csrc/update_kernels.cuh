@@ -406,11 +406,13 @@ __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
 template <int CPL>
 __global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
   __shared__ float4 s_part[8][CPL * WARP];
-  if (blockIdx.x >= *p.n_heavy) return;
-  const uint32_t key = p.heavy_keys[blockIdx.x];
-  const UpdateTable& T = p.tab[blockIdx.y];
-  if (T.rec == nullptr || key < T.key_base || (int64_t) (key - T.key_base) >= T.rows) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const UpdateTable& T = p.tab[blockIdx.y];
+  const uint32_t n_queued = *p.n_heavy;
+  for (uint32_t item = blockIdx.x; item < n_queued; item += gridDim.x) {     // few CTAs, few items
+  __syncthreads();
+  const uint32_t key = p.heavy_keys[item];
+  if (T.rec == nullptr || key < T.key_base || (int64_t) (key - T.key_base) >= T.rows) continue;
   const int64_t row = key - T.key_base;
   const int nch = (T.cols + 3) >> 2;
   const int64_t lo = __ldg(p.seg_lo + key), L = (int64_t) __ldg(p.seg_hi + key) - lo;
@@ -421,7 +423,7 @@ __global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
 #pragma unroll
   for (int u = 0; u < CPL; ++u) s_part[warp][u * WARP + lane] = part[u];
   __syncthreads();
-  if (warp != 0) return;
+  if (warp != 0) continue;
   float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
   float4* m4 = reinterpret_cast<float4*>(T.m + row * (int64_t) T.ld);
   float4* v4 = reinterpret_cast<float4*>(T.v + row * (int64_t) T.ld);
@@ -437,10 +439,11 @@ __global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
     mask_tail(w, m, v, c, T.cols);
     m4[c] = m; v4[c] = v; w4[c] = w;
   }
+  }
 }
 
 inline int launch_update_heavy(const UpdateParams& up, int cpl, int64_t max_heavy, cudaStream_t st) {
-  const dim3 grid((unsigned) max_heavy, (unsigned) up.n_tabs, 1);
+  const dim3 grid((unsigned) (max_heavy < 148 ? max_heavy : 148), (unsigned) up.n_tabs, 1);
   switch (cpl) {
     case 1: k_update_heavy<1><<<grid, 256, 0, st>>>(up); break;
     case 2: k_update_heavy<2><<<grid, 256, 0, st>>>(up); break;
