@@ -3,6 +3,7 @@
 #include "rank_kernels.cuh"
 #include "rank_mat_kernels.cuh"
 #include "rank_dot_host.cuh"
+#include "rank_lp_tile.cuh"
 #include <stdlib.h>
 
 namespace kge {
@@ -14,6 +15,11 @@ size_t rank_workspace_bytes(const kge_cfg* cfg, int64_t Q) {
   if (rank_dot_eligible(cfg)) {
     DotWs L;
     layout_dot_ws(cfg, Q, cfg->n_ent, L);         // sized for the full entity range (largest shard)
+    return L.total;
+  }
+  if (rank_lp_eligible(cfg)) {
+    LpWs L;
+    layout_lp_ws(cfg, Q, L);
     return L.total;
   }
   return 256;
@@ -79,6 +85,14 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
     if (int rc = rank_dot_tensor(ctx, cfg, tables, queries, Q, side, filter, ent_lo, ent_hi, count_out, ws, ws_bytes,
                                  (cudaStream_t) stream, &ptd)) return rc;
     ptd.end(5);
+    return KGE_OK;
+  }
+  if (rank_lp_eligible(cfg) && !force_generic_rank()) {
+    PhaseTimer ptl(ctx, (cudaStream_t) stream);
+    ptl.begin(5);
+    if (int rc = rank_lp_tiled(cfg, tables, queries, Q, side, filter, ent_lo, ent_hi, count_out, ws, ws_bytes,
+                               (cudaStream_t) stream)) return rc;
+    ptl.end(5);
     return KGE_OK;
   }
   const bool mat = is_matrix_model(cfg->model);

@@ -109,3 +109,50 @@ def test_tensor_core_rank_equals_generic(model, score, d, n_ent, side):
     parts = sum(eng.rank_counts(Xq, s, off, ids, ent_lo=lo, ent_hi=hi).cpu().numpy()
                 for lo, hi in [(0, n_ent // 3), (n_ent // 3, n_ent // 3 + 77), (n_ent // 3 + 77, n_ent)])
     assert np.array_equal(parts, tc_flt)
+
+
+@pytest.mark.parametrize("model,score,d,n_ent,side", [
+    ("TransE", "l1", 50, 1500, "t"), ("TransE", "l1", 50, 1500, "h"),
+    ("TransE", "l2", 37, 700, "h"), ("TransE", "l2pow", 128, 333, "t"),
+    ("TransE", "linf", 20, 500, "t"), ("TransE", "l3", 24, 400, "h"),
+    ("UM", "l2pow", 64, 900, "t"), ("UM", "l1", 33, 900, "h"),
+])
+def test_lp_tile_rank_equals_generic(model, score, d, n_ent, side):
+    """CUDA-core tiled Lp ranking (csrc/rank_lp_tile.cuh) against the warp-per-candidate kernel:
+    both are exact fp32 rankings with different evaluation orders, so only candidates within
+    rounding of the true score may move; shards must add up exactly; filtered <= raw."""
+    import os
+    from KGE._b200.filter import build_filter
+    rng = np.random.default_rng(21)
+    ref, W, eng = make_pair(model, n_ent, R, d, None, score=_score_for(model, score), loss=LOSSES["hinge"])
+    pos = rand_triples(rng, 20000, n_ent, R)
+    Xq = pos[:700].copy()
+    Xq[::4] = rand_triples(rng, len(Xq[::4]), n_ent, R)
+    off, ids = build_filter(pos, Xq, side, n_ent, eng.device)
+    s = 0 if side == "h" else 1
+    t_raw = eng.rank_counts(Xq, s).cpu().numpy()
+    t_flt = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+    os.environ["KGE_RANK_GENERIC"] = "1"
+    try:
+        g_raw = eng.rank_counts(Xq, s).cpu().numpy()
+        g_flt = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+    finally:
+        os.environ.pop("KGE_RANK_GENERIC")
+    for a, b in ((t_raw, g_raw), (t_flt, g_flt)):
+        diff = np.abs(a.astype(np.int64) - b)
+        assert diff.max() <= 2 and (diff > 0).mean() <= 0.01, (diff.max(), (diff > 0).mean())
+    assert (t_flt <= t_raw).all() and (t_flt >= 0).all()
+    parts = sum(eng.rank_counts(Xq, s, off, ids, ent_lo=lo, ent_hi=hi).cpu().numpy()
+                for lo, hi in [(0, n_ent // 3), (n_ent // 3, n_ent // 3 + 77), (n_ent // 3 + 77, n_ent)])
+    assert np.array_equal(parts, t_flt)
+    # the oracle's ranks on a sample (ties within 1e-5 relative of the true score excepted)
+    for qi in range(40):
+        x = Xq[qi]
+        want = RS.get_rank(ref, W, x, pos, side)
+        if t_flt[qi] + 1 != want:
+            sc = RS.get_scores_all(ref, W, x, side)
+            with torch.no_grad():
+                one = lambda v: torch.tensor([int(v)])
+                pp = float(ref.score_hrt(W, one(x[0]), one(x[1]), one(x[2]))[0])
+            near = int(((sc - pp).abs() <= 1e-5 * max(1.0, abs(pp))).sum())
+            assert abs(int(t_flt[qi]) + 1 - want) <= near, (qi, int(t_flt[qi]) + 1, want, near)
