@@ -371,9 +371,11 @@ def main():
         "value_steady_state_l2_warm": r["triples"] / (r["ms_warm"] * 1e-3),
         "e2e": {"value": r["triples"] / (r["ms_e2e"] * 1e-3), "unit": "triples/s",
                 "h2d_bytes_per_step": W["B"] * 3 * 8, "d2h_bytes_per_step": 4},
-        "gpu_launches": args.steps * 5, "gpu_launches_note": "own kernels per step: k_constrain, k_step (loss/clip "
-        "reduction folded into its last warp), k_update on the caller's stream; k_keys, k_segments on the side stream "
-        "(+ CUB radix-sort kernels and one memset there)",
+        "gpu_launches": args.steps * (8 if world == 1 else 9),
+        "gpu_launches_note": "own kernels per step: k_constrain, k_step (loss/clip reduction folded into its last warp), "
+        "k_update_fast on the caller's stream; k_keys, k_scan, k_scatter, k_canon, k_update_heavy on the side stream "
+        "(+ one memset there); data-parallel runs add k_dp_scales and replace the update pair by k_update<3> / k_update<0> "
+        "around one NCCL all-reduce",
         "roofline": {"kernel": "k_step<MDistMult,2,true>", "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": ncu_traffic("k_step<MDistMult"),
                      "traffic_note": "ncu dram read+write per launch (cold caches); below the algorithmic bytes because "
