@@ -536,7 +536,16 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
 
   pt.begin(4);
   if (grad_only) {
-    if (int rc2 = launch_update<3>(up, cpl, ublocks, st)) return rc2;
+    if (ctx->opt_radix_sort) {
+      if (int rc2 = launch_update<3>(up, cpl, ublocks, st)) return rc2;
+    } else {
+      KGE_CUDA_OK(cudaEventRecord(ctx->ev_mid, st));
+      KGE_CUDA_OK(cudaStreamWaitEvent(ctx->aux, ctx->ev_mid, 0));
+      if (int rc2 = launch_update_heavy<3>(up, cpl, L.n_keys / UPD_HEAVY + 1, ctx->aux)) return rc2;
+      KGE_CUDA_OK(cudaEventRecord(ctx->ev_heavy, ctx->aux));
+      if (int rc2 = launch_update_fast<3>(up, cpl, st)) return rc2;
+      KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_heavy, 0));
+    }
     pt.end(4);
     return KGE_OK;
   }
@@ -575,9 +584,9 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     // summed by whole CTAs on the side stream at the same time (disjoint rows)
     KGE_CUDA_OK(cudaEventRecord(ctx->ev_mid, st));
     KGE_CUDA_OK(cudaStreamWaitEvent(ctx->aux, ctx->ev_mid, 0));
-    if (int rc2 = launch_update_heavy(up, cpl, L.n_keys / UPD_HEAVY + 1, ctx->aux)) return rc2;
+    if (int rc2 = launch_update_heavy<0>(up, cpl, L.n_keys / UPD_HEAVY + 1, ctx->aux)) return rc2;
     KGE_CUDA_OK(cudaEventRecord(ctx->ev_heavy, ctx->aux));
-    if (int rc2 = launch_update_fast(up, cpl, st)) return rc2;
+    if (int rc2 = launch_update_fast<0>(up, cpl, st)) return rc2;
     KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_heavy, 0));
   }
   pt.end(4);
@@ -685,7 +694,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     KGE_CUDA_OK(cudaGetLastError());
     if (int rc = launch_update<2>(up, cpl, ublocks, st)) return rc;
   } else {
-    if (int rc = launch_update<0>(up, cpl, ublocks, st)) return rc;
+    if (int rc = launch_update_fast<4>(up, cpl, st)) return rc;      // streaming pass: gradient = gsum row
   }
   pt.end(4);
   return KGE_OK;

@@ -350,7 +350,9 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
 //   * rows with more than UPD_HEAVY records are left to k_update_heavy (whole-CTA summation),
 //     which runs concurrently on the side stream.
 // Summation order and update arithmetic are those of k_update: results are bit-identical.
-template <int CPL>
+// MODE 0: fused step.  MODE 3: data-parallel gradient half (row sum -> T.gout, tables untouched).
+// MODE 4: data-parallel apply half (gradient = T.gsum row, no records).
+template <int CPL, int MODE>
 __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
   const int lane = threadIdx.x & 31;
   const int64_t gw = (int64_t) blockIdx.x * 2 + (threadIdx.x >> 5);
@@ -363,17 +365,19 @@ __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
   float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
   float4* m4 = reinterpret_cast<float4*>(T.m + row * (int64_t) T.ld);
   float4* v4 = reinterpret_cast<float4*>(T.v + row * (int64_t) T.ld);
+  if (MODE != 3) {
 #pragma unroll
-  for (int u = 0; u < CPL; ++u) {
-    const int c = lane + 32 * u;
-    if (c < nch && (c & 7) == 0) {                   // one request per 128-byte line
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(w4 + c));
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(m4 + c));
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(v4 + c));
+    for (int u = 0; u < CPL; ++u) {
+      const int c = lane + 32 * u;
+      if (c < nch && (c & 7) == 0) {                 // one request per 128-byte line
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(w4 + c));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(m4 + c));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(v4 + c));
+      }
     }
   }
   uint32_t hv = 0;
-  if (T.rec != nullptr && lane < 8) hv = __ldg(p.hdr + ((int64_t) T.key_base + row) * 8 + lane);
+  if (MODE != 4 && T.rec != nullptr && lane < 8) hv = __ldg(p.hdr + ((int64_t) T.key_base + row) * 8 + lane);
   const uint32_t L = __shfl_sync(FULL, hv, 0), lo = __shfl_sync(FULL, hv, 1);
   if (L > (uint32_t) UPD_HEAVY) return;             // k_update_heavy's row
   float4 g[CPL];
@@ -386,6 +390,17 @@ __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
     mine = (lane < n0) ? mine - T.rec_base : 0u;
     sum_chunk<CPL>(mine, n0, T.rec, T.rec_ld, nch, lane, g);
     if (L > 32u) sum_records<CPL>(p.vals, T.rec, T.rec_ld, T.rec_base, (int64_t) lo + 32, (int64_t) lo + L, nch, lane, g);
+  }
+  if (MODE == 3) {
+    float4* o = reinterpret_cast<float4*>(T.gout + row * (int64_t) T.ld);
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) o[c] = g[u]; }
+    return;
+  }
+  if (MODE == 4) {
+    const float4* gs = reinterpret_cast<const float4*>(T.gsum + row * (int64_t) T.ld);
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) g[u] += __ldg(gs + c); }
   }
   const float scale = p.scal[T.slot];
 #pragma unroll
@@ -403,7 +418,7 @@ __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
 // Rows with many records (hot entities / relations): one CTA per (heavy key, table), the eight
 // warps sum contiguous slices of the sorted record list, partials are combined in slice order —
 // the order k_update uses for its heavy rows, so the bits agree.
-template <int CPL>
+template <int CPL, int MODE>
 __global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
   __shared__ float4 s_part[8][CPL * WARP];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -434,6 +449,7 @@ __global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
     if (c >= nch) continue;
     float4 g = f4zero();
     for (int w3 = 0; w3 < 8; ++w3) g += s_part[w3][u * WARP + lane];
+    if (MODE == 3) { reinterpret_cast<float4*>(T.gout + row * (int64_t) T.ld)[c] = g; continue; }
     float4 w = w4[c], m = m4[c], v = v4[c];
     adam_chunk(w, m, v, scale4(scale, g), p.beta1, p.beta2, p.lr_t, p.eps);
     mask_tail(w, m, v, c, T.cols);
@@ -442,26 +458,28 @@ __global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
   }
 }
 
+template <int MODE>
 inline int launch_update_heavy(const UpdateParams& up, int cpl, int64_t max_heavy, cudaStream_t st) {
   const dim3 grid((unsigned) (max_heavy < 148 ? max_heavy : 148), (unsigned) up.n_tabs, 1);
   switch (cpl) {
-    case 1: k_update_heavy<1><<<grid, 256, 0, st>>>(up); break;
-    case 2: k_update_heavy<2><<<grid, 256, 0, st>>>(up); break;
-    case 4: k_update_heavy<4><<<grid, 256, 0, st>>>(up); break;
-    default: k_update_heavy<8><<<grid, 256, 0, st>>>(up); break;
+    case 1: k_update_heavy<1, MODE><<<grid, 256, 0, st>>>(up); break;
+    case 2: k_update_heavy<2, MODE><<<grid, 256, 0, st>>>(up); break;
+    case 4: k_update_heavy<4, MODE><<<grid, 256, 0, st>>>(up); break;
+    default: k_update_heavy<8, MODE><<<grid, 256, 0, st>>>(up); break;
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("k_update_heavy launch failed: %s", cudaGetErrorString(e)); return KGE_ECUDA; }
   return KGE_OK;
 }
 
+template <int MODE>
 inline int launch_update_fast(const UpdateParams& up, int cpl, cudaStream_t st) {
   const unsigned blocks = (unsigned) ((up.total_rows + 1) / 2);
   switch (cpl) {
-    case 1: k_update_fast<1><<<blocks, 64, 0, st>>>(up); break;
-    case 2: k_update_fast<2><<<blocks, 64, 0, st>>>(up); break;
-    case 4: k_update_fast<4><<<blocks, 64, 0, st>>>(up); break;
-    default: k_update_fast<8><<<blocks, 64, 0, st>>>(up); break;
+    case 1: k_update_fast<1, MODE><<<blocks, 64, 0, st>>>(up); break;
+    case 2: k_update_fast<2, MODE><<<blocks, 64, 0, st>>>(up); break;
+    case 4: k_update_fast<4, MODE><<<blocks, 64, 0, st>>>(up); break;
+    default: k_update_fast<8, MODE><<<blocks, 64, 0, st>>>(up); break;
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("k_update_fast launch failed: %s", cudaGetErrorString(e)); return KGE_ECUDA; }
