@@ -116,6 +116,8 @@ def test_tensor_core_rank_equals_generic(model, score, d, n_ent, side):
     ("TransE", "l2", 37, 700, "h"), ("TransE", "l2pow", 128, 333, "t"),
     ("TransE", "linf", 20, 500, "t"), ("TransE", "l3", 24, 400, "h"),
     ("UM", "l2pow", 64, 900, "t"), ("UM", "l1", 33, 900, "h"),
+    ("RotatE", "l1", 37, 600, "t"), ("RotatE", "l1", 64, 600, "h"), ("RotatE", "l2", 20, 300, "h"),
+    ("RotatE", "linf", 16, 300, "t"), ("RotatE", "l3", 12, 300, "t"),
 ])
 def test_lp_tile_rank_equals_generic(model, score, d, n_ent, side):
     """CUDA-core tiled Lp ranking (csrc/rank_lp_tile.cuh) against the warp-per-candidate kernel:
