@@ -73,13 +73,22 @@ class Engine:
 
     # ---- struct packing -----------------------------------------------------------
     def _tables(self, with_opt):
+        """kge_tables of the current storages, rebuilt only when a pointer changed (tables are
+        updated in place; Adam slots appear once)."""
+        if with_opt:
+            for pt in self.tab.values():
+                pt.ensure_slots()
+        key = (bool(with_opt),) + tuple((pt.storage.data_ptr(), 0 if pt.m is None else pt.m.data_ptr())
+                                        for pt in self.tab.values())
+        hit = getattr(self, "_tables_cache", None)
+        if hit is not None and hit[0] == key:
+            return hit[1]
         T = L.Tables()
         for s, pt in self.tab.items():
-            if with_opt:
-                pt.ensure_slots()
             T.t[s] = L.Table(w=pt.storage.data_ptr(), m=pt.m.data_ptr() if pt.m is not None else None,
                              v=pt.v.data_ptr() if pt.v is not None else None,
                              rows=pt.rows, cols=pt.cols, ld=pt.ld)
+        self._tables_cache = (key, T)
         return T
 
     def set_uniform_pool(self, pool=None):
@@ -101,8 +110,14 @@ class Engine:
                                  n_types=ts[1].numel() - 1)
 
     def _workspace(self, B, Q):
+        memo = getattr(self, "_ws_memo", None)
+        if memo is None:
+            memo = self._ws_memo = {}
+        if (B, Q) in memo and self._ws is not None and self._ws.numel() >= memo[(B, Q)]:
+            return self._ws
         need = C.c_size_t()
         L.check(L.load().kge_workspace_bytes(C.byref(self.cfg), B, Q, C.byref(need)))
+        memo[(B, Q)] = need.value
         if self._ws is None or self._ws.numel() < need.value:
             self._ws = torch.empty(need.value, dtype=torch.uint8, device=self.device)
         return self._ws
@@ -113,6 +128,8 @@ class Engine:
 
     def _ids(self, x):
         dt = torch.int64 if self.cfg.id_dtype == 1 else torch.int32
+        if torch.is_tensor(x) and x.dtype == dt and x.device == self.device and x.is_contiguous():
+            return x
         if torch.is_tensor(x):
             return x.to(device=self.device, dtype=dt).contiguous()
         return torch.as_tensor(np.ascontiguousarray(x), dtype=dt).to(self.device)

@@ -63,11 +63,20 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   L.off_keys_out = take(sizeof(uint32_t) * (size_t) L.n_keys);
   L.off_vals_in = take(sizeof(uint32_t) * (size_t) L.n_keys);
   L.off_vals_out = take(sizeof(uint32_t) * (size_t) L.n_keys);
-  L.cub_bytes = 0;
-  cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, L.cub_bytes, (const uint32_t*) nullptr, (uint32_t*) nullptr,
-                                                  (const uint32_t*) nullptr, (uint32_t*) nullptr, (int) L.n_keys, 0,
-                                                  sort_bits(c), (cudaStream_t) 0);
-  KGE_REQUIRE(e == cudaSuccess, KGE_ECUDA, "cub temp-size query failed: %s", cudaGetErrorString(e));
+  // temp size of the radix-sort mode: queried once per (n_keys, bits), this runs on every call
+  static thread_local int64_t memo_n = -1;
+  static thread_local int memo_bits = -1;
+  static thread_local size_t memo_bytes = 0;
+  cudaError_t e = cudaSuccess;
+  if (memo_n != L.n_keys || memo_bits != sort_bits(c)) {
+    size_t bytes = 0;
+    e = cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint32_t*) nullptr, (uint32_t*) nullptr,
+                                        (const uint32_t*) nullptr, (uint32_t*) nullptr, (int) L.n_keys, 0, sort_bits(c),
+                                        (cudaStream_t) 0);
+    KGE_REQUIRE(e == cudaSuccess, KGE_ECUDA, "cub temp-size query failed: %s", cudaGetErrorString(e));
+    memo_n = L.n_keys; memo_bits = sort_bits(c); memo_bytes = bytes;
+  }
+  L.cub_bytes = memo_bytes;
   L.off_cub = take(L.cub_bytes);
   L.n_seg = (size_t) c->n_ent + (size_t) c->n_rel;
   L.off_seg = take(sizeof(uint32_t) * (2 * L.n_seg + 2));   // cnt[K] | off[K+1] | n_heavy   (radix path: seg_lo | seg_hi)
@@ -339,15 +348,18 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   // the scan itself (first position of key = off[key], one past the last = off[key + 1])
   const uint32_t* use_lo = (ctx->opt_radix_sort != 0) ? seg_lo : seg_lo + L.n_seg;
   const uint32_t* use_hi = (ctx->opt_radix_sort != 0) ? seg_hi : seg_lo + L.n_seg + 1;
+  // Host enqueue order: the caller's stream first (fork point, constraint, step kernel), so the
+  // GPU starts on the critical path while the host is still enqueueing the side chain.
   auto fork_side = [&]() -> int {
-    if (!is_train) {
-      pt.begin(0);
-      if (int rc2 = launch_constrain(ctx, cp, st)) return rc2;
-      pt.end(0);
-      return KGE_OK;
-    }
+    if (is_train) KGE_CUDA_OK(cudaEventRecord(ctx->ev_fork, st));
+    pt.begin(0);
+    if (int rc2 = launch_constrain(ctx, cp, st)) return rc2;
+    pt.end(0);
+    return KGE_OK;
+  };
+  auto side_chain = [&]() -> int {
+    if (!is_train) return KGE_OK;
     cudaStream_t ax = ctx->aux;
-    KGE_CUDA_OK(cudaEventRecord(ctx->ev_fork, st));
     KGE_CUDA_OK(cudaStreamWaitEvent(ax, ctx->ev_fork, 0));
     pt.begin(3, ax);
     int64_t kb = (L.n_keys + 255) / 256;
@@ -387,9 +399,6 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     }
     pt.end(3, ax);
     KGE_CUDA_OK(cudaEventRecord(ctx->ev_join, ax));
-    pt.begin(0);
-    if (int rc2 = launch_constrain(ctx, cp, st)) return rc2;
-    pt.end(0);
     return KGE_OK;
   };
 
@@ -434,8 +443,9 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
       default: rc = launch_step_rescal(mq, SL);
     }
   }
-  if (rc) { if (is_train) cudaStreamWaitEvent(st, ctx->ev_join, 0); return rc; }
+  if (rc) return rc;
   pt.end(1);
+  if (int rc2 = side_chain()) return rc2;
 
   // 3. loss + per-table clip scales (sparse-gradient tables)
   const ReduceParams& rp = p.rp;
