@@ -215,9 +215,13 @@ def run_ours(args, rank, world, device):
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        stage.copy_(host_batches[i % n_batches], non_blocking=True)
-        one_step(stage)
-        loss_host.copy_(loss_dev, non_blocking=True)
+        if world > 1:
+            stage.copy_(host_batches[i % n_batches], non_blocking=True)
+            one_step(stage)
+            loss_host.copy_(loss_dev, non_blocking=True)
+        else:           # host buffers straight through the C-ABI: H2D + step + D2H enqueued by kge_train_step_host
+            eng.train_step_host(host_batches[i % n_batches], seed, step_no[0], loss_host)
+            step_no[0] += 1
         torch.cuda.current_stream().synchronize()      # the reference reads loss.numpy() per batch
     barrier()
     ms_e2e = (time.perf_counter() - t0) * 1e3

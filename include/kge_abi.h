@@ -145,6 +145,17 @@ int kge_train_step(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*,
                    uint64_t adam_t, const int64_t* neg_override, int is_train,
                    float* loss_out, int64_t* neg_out, void* ws, size_t ws_bytes, void* stream);
 
+/* kge_train_step for a caller whose batch and loss live in HOST memory (what the reference's
+ * loop does per batch, BaseModel.py:139-147: iterator -> step -> loss.numpy()): copies the
+ * (B, 3) ids from `host_triples` (pinned for a truly asynchronous copy) into the caller's device
+ * staging buffer `dev_triples`, runs the step, and copies the loss to `host_loss_out`; all three
+ * are enqueued on `stream`, no host sync — the loss is valid once the stream has been
+ * synchronised.  `dev_loss` is a device float the step writes first. */
+int kge_train_step_host(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*,
+                        const void* host_triples, void* dev_triples, int64_t B, uint64_t seed,
+                        uint64_t step, uint64_t adam_t, int is_train, float* dev_loss,
+                        float* host_loss_out, void* ws, size_t ws_bytes, void* stream);
+
 /* Data-parallel form of kge_train_step (the reference is single-device): every
  * rank holds all tables and B of the step's B_global positives, [i_base, i_base + B).
  *   kge_train_grad  : constraint, sampling on the GLOBAL Philox counters (the negatives equal a

@@ -161,6 +161,27 @@ class Engine:
                                         _ptr(loss_out), _ptr(neg_out), _ptr(ws), ws.numel(), _stream()))
         return (loss_out, neg_out) if want_negatives else loss_out
 
+    def train_step_host(self, host_triples, seed, step, host_loss, is_train=True):
+        """Batch and loss in (pinned) host memory: H2D copy, step and D2H of the loss are enqueued by
+        ONE library call (kge_train_step_host); the caller synchronises the stream to read the loss."""
+        B = host_triples.shape[0]
+        dt = torch.int64 if self.cfg.id_dtype == 1 else torch.int32
+        if host_triples.dtype != dt or not host_triples.is_contiguous():
+            raise ValueError(f"host_triples must be a contiguous {dt} tensor")
+        st = getattr(self, "_stage", None)
+        if st is None or st.shape[0] < B:
+            st = self._stage = torch.empty((B, 3), dtype=dt, device=self.device)
+            self._stage_loss = torch.zeros(1, dtype=torch.float32, device=self.device)
+        ws = self._workspace(B, 0)
+        if is_train:
+            self.adam_t += 1
+        T = self._tables(with_opt=bool(is_train))
+        L.check(L.load().kge_train_step_host(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler),
+                                             C.c_void_p(host_triples.data_ptr()), _ptr(st), B, seed, step,
+                                             max(self.adam_t, 1), int(bool(is_train)), _ptr(self._stage_loss),
+                                             C.c_void_p(host_loss.data_ptr()), _ptr(ws), ws.numel(), _stream()))
+        return host_loss
+
     # ---- data-parallel step (SURVEY.md 8e): grad -> one all-reduce -> apply ---------------
     def grad_buffer(self):
         from . import dp as _dp

@@ -58,7 +58,7 @@ class Grads(C.Structure):
 
 SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destroy",
            "kge_workspace_bytes", "kge_sample_negatives", "kge_score", "kge_constrain_table",
-           "kge_train_step", "kge_train_grad", "kge_train_apply", "kge_rank", "kge_profile_begin", "kge_profile_end",
+           "kge_train_step", "kge_train_step_host", "kge_train_grad", "kge_train_apply", "kge_rank", "kge_profile_begin", "kge_profile_end",
            "kge_set_option"]
 
 _LIB = None
@@ -91,6 +91,8 @@ def load():
     L.kge_constrain_table.argtypes = [vp, C.POINTER(Tables), i32, i32, vp]
     L.kge_train_step.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), vp, i64,
                                  u64, u64, u64, vp, i32, vp, vp, vp, C.c_size_t, vp]
+    L.kge_train_step_host.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), vp, vp, i64,
+                                      u64, u64, u64, i32, vp, vp, vp, C.c_size_t, vp]
     L.kge_train_grad.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Dp), vp, i64,
                                  u64, u64, vp, C.POINTER(Grads), vp, vp, vp, C.c_size_t, vp]
     L.kge_train_apply.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Grads), vp, i64, u64, vp, vp,

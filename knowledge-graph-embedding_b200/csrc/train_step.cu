@@ -611,6 +611,20 @@ extern "C" int kge_train_step(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tabl
                     nullptr, loss_out, neg_out, ws, ws_bytes, stream);
 }
 
+extern "C" int kge_train_step_host(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                                   const void* host_triples, void* dev_triples, int64_t B, uint64_t seed, uint64_t step,
+                                   uint64_t adam_t, int is_train, float* dev_loss, float* host_loss_out, void* ws,
+                                   size_t ws_bytes, void* stream) {
+  KGE_REQUIRE(cfg && host_triples && dev_triples && dev_loss && host_loss_out && B > 0, KGE_EINVAL,
+              "cfg / host_triples / dev_triples / dev_loss / host_loss_out / B invalid");
+  cudaStream_t st = (cudaStream_t) stream;
+  KGE_CUDA_OK(cudaMemcpyAsync(dev_triples, host_triples, (size_t) B * 3 * (cfg->id_dtype ? 8 : 4), cudaMemcpyHostToDevice, st));
+  if (int rc = train_impl(ctx, cfg, tables, smp, nullptr, dev_triples, B, seed, step, adam_t, nullptr, is_train, nullptr,
+                          nullptr, dev_loss, nullptr, ws, ws_bytes, stream)) return rc;
+  KGE_CUDA_OK(cudaMemcpyAsync(host_loss_out, dev_loss, sizeof(float), cudaMemcpyDeviceToHost, st));
+  return KGE_OK;
+}
+
 extern "C" int kge_train_grad(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
                               const kge_dp* dp, const void* triples, int64_t B, uint64_t seed, uint64_t step,
                               const int64_t* neg_override, kge_grads* out, float* scal_out, int64_t* neg_out, void* ws,

@@ -201,3 +201,25 @@ def test_api_step_sequence_matches_reference_golden():
             assert abs(float(l.item()) - want) <= TOL * max(1.0, abs(want)), (name, step)
         sc_all = m.score_hrt(h=None, r=g["score_X"][0][1], t=g["score_X"][0][2])
         assert len(sc_all) == 40
+
+
+@pytest.mark.gpu
+def test_train_step_host_equals_device_step():
+    """kge_train_step_host (pinned host batch in, host loss out) is the device step plus two
+    copies: same weights bit for bit, same loss."""
+    import numpy as np
+    import torch
+    from helpers import make_pair, rand_triples
+    from oracle import ref_ops as O
+    rng = np.random.default_rng(4)
+    _, _, a = make_pair("DistMult", 300, 11, 40, loss=O.BinaryCrossEntropyLoss(), k=6)
+    _, _, b = make_pair("DistMult", 300, 11, 40, loss=O.BinaryCrossEntropyLoss(), k=6)
+    host_loss = torch.zeros(1, dtype=torch.float32).pin_memory()
+    for step in range(3):
+        X = rand_triples(rng, 64, 300, 11)
+        la = a.train_step(X, 9, step)
+        b.train_step_host(torch.from_numpy(X).pin_memory(), 9, step, host_loss)
+        torch.cuda.synchronize()
+        assert float(la.item()) == float(host_loss.item())
+    for s in a.tab:
+        assert torch.equal(a.tab[s].storage, b.tab[s].storage)
