@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 1
+#define KGE_ABI_VERSION 2
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -60,13 +60,23 @@ typedef struct kge_table {
   float* w;          /* weights                                   */
   float* m;          /* Adam first moment  (NULL for score/rank)   */
   float* v;          /* Adam second moment (NULL for score/rank)   */
+  float* wn;         /* optional shadow: the row-normalised table the NEXT batch starts from, same
+                        layout as w (see kge_tables.wn_valid); NULL = none                        */
   int64_t rows;
   int32_t cols;      /* logical floats per row                     */
   int32_t ld;        /* row stride in floats, multiple of 4        */
 } kge_table;
 
+/* wn_valid[s] != 0: t[s].wn holds normalise(t[s].w) — what the start-of-batch constraint
+ * (TransE.py:171-172, DistMult.py:162, UM.py:153) would assign.  kge_train_step then skips the
+ * full-table constraint pass: rows are gathered from wn, and the row update (which has the new row
+ * in registers anyway) writes both the reference-visible w and the next batch's wn.  The library
+ * sets the flag after a training step that maintained wn; the CALLER clears it whenever it writes
+ * w itself (assign / restore / init-time constraint).  Entity table of UM / TransE / DistMult with
+ * constraint = True only; ignored elsewhere.  Results are bit-identical with and without wn. */
 typedef struct kge_tables {
   kge_table t[KGE_MAX_TABLES];   /* unused slots: w == NULL */
+  int32_t wn_valid[KGE_MAX_TABLES];
 } kge_tables;
 
 typedef struct kge_cfg {
@@ -196,8 +206,9 @@ int kge_rank(kge_ctx*, const kge_cfg*, const kge_tables*, const void* queries, i
 
 /* Implementation switches (testing / A-B measurement; results are identical either way).
  * KGE_OPT_RADIX_SORT: 1 = group the step's gradient records with cub's stable radix sort
- * instead of the counting sort of csrc/group_kernels.cuh (default 0). */
-enum { KGE_OPT_RADIX_SORT = 1 };
+ * instead of the counting sort of csrc/group_kernels.cuh (default 0).
+ * KGE_OPT_NO_SHADOW: 1 = ignore kge_table.wn and run the full-table constraint pass every batch. */
+enum { KGE_OPT_RADIX_SORT = 1, KGE_OPT_NO_SHADOW = 2 };
 int kge_set_option(kge_ctx*, int option, int value);
 
 /* Per-phase device timing (CUDA events recorded on the call's stream, read back only at

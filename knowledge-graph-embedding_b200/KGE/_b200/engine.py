@@ -45,6 +45,12 @@ class PaddedTable:
         self.storage[:, :cols] = value.reshape(rows, cols).to(device)
         self.m = None
         self.v = None
+        self.wn = None            # shadow: normalise(storage) maintained by the training step (kge_tables.wn_valid)
+        self.wn_valid = False
+
+    def touch(self):
+        """Call after writing `storage` / `view` from outside the library: the shadow is stale."""
+        self.wn_valid = False
 
     @property
     def view(self):
@@ -66,6 +72,8 @@ class Engine:
         for k, v in cfg_kwargs.items():
             setattr(self.cfg, k, v)
         self.tab = {s: PaddedTable(v, self.device) for s, v in tables.items()}
+        if self.cfg.constraint and self.cfg.model in (L.UM, L.TRANSE, L.DISTMULT):
+            self.tab[L.T_ENT].wn = torch.zeros_like(self.tab[L.T_ENT].storage)
         self.sampler = L.Sampler()
         self._sampler_keep = []
         self._ws = None
@@ -80,16 +88,30 @@ class Engine:
                 pt.ensure_slots()
         key = (bool(with_opt),) + tuple((pt.storage.data_ptr(), 0 if pt.m is None else pt.m.data_ptr())
                                         for pt in self.tab.values())
-        hit = getattr(self, "_tables_cache", None)
-        if hit is not None and hit[0] == key:
-            return hit[1]
+        cache = getattr(self, "_tables_cache", None)
+        if cache is None:
+            cache = self._tables_cache = {}
+        if key in cache:
+            T = cache[key]
+            for s, pt in self.tab.items():
+                T.wn_valid[s] = int(pt.wn_valid)
+            return T
         T = L.Tables()
         for s, pt in self.tab.items():
             T.t[s] = L.Table(w=pt.storage.data_ptr(), m=pt.m.data_ptr() if pt.m is not None else None,
                              v=pt.v.data_ptr() if pt.v is not None else None,
+                             wn=pt.wn.data_ptr() if pt.wn is not None else None,
                              rows=pt.rows, cols=pt.cols, ld=pt.ld)
-        self._tables_cache = (key, T)
+            T.wn_valid[s] = int(pt.wn_valid)
+        if len(cache) > 8:
+            cache.clear()
+        cache[key] = T
         return T
+
+    def _sync_shadow(self, T):
+        """The library updates kge_tables.wn_valid; mirror it on the tables."""
+        for s, pt in self.tab.items():
+            pt.wn_valid = bool(T.wn_valid[s])
 
     def set_uniform_pool(self, pool=None):
         self.cfg.sampler = L.NS_UNIFORM
@@ -159,6 +181,7 @@ class Engine:
         L.check(L.load().kge_train_step(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler), _ptr(X), B,
                                         seed, step, max(self.adam_t, 1), _ptr(neg), int(bool(is_train)),
                                         _ptr(loss_out), _ptr(neg_out), _ptr(ws), ws.numel(), _stream()))
+        self._sync_shadow(T)
         return (loss_out, neg_out) if want_negatives else loss_out
 
     def train_step_host(self, host_triples, seed, step, host_loss, is_train=True):
@@ -180,6 +203,7 @@ class Engine:
                                              C.c_void_p(host_triples.data_ptr()), _ptr(st), B, seed, step,
                                              max(self.adam_t, 1), int(bool(is_train)), _ptr(self._stage_loss),
                                              C.c_void_p(host_loss.data_ptr()), _ptr(ws), ws.numel(), _stream()))
+        self._sync_shadow(T)
         return host_loss
 
     # ---- data-parallel step: grad -> one all-reduce -> apply ---------------
@@ -221,6 +245,7 @@ class Engine:
         G = self._grads_struct(gb)
         L.check(L.load().kge_train_apply(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(G), _ptr(gb.scal), B,
                                          self.adam_t, _ptr(loss_out), _ptr(ws), ws.numel(), _stream()))
+        self._sync_shadow(T)
         return loss_out
 
     def train_step_dp(self, triples_local, seed, step, B_global, i_base, loss_out=None, neg_override=None, group=None):
@@ -244,6 +269,7 @@ class Engine:
     def constrain_table(self, slot, op):
         T = self._tables(False)
         L.check(L.load().kge_constrain_table(self.ctx, C.byref(T), slot, op, _stream()))
+        self.tab[slot].touch()
 
     def rank_counts(self, queries, side, f_off=None, f_ids=None, ent_lo=0, ent_hi=None):
         Qx = self._ids(queries)

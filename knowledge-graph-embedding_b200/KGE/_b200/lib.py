@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 1
+KGE_ABI_VERSION = 2
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -13,17 +13,18 @@ NS_UNIFORM, NS_TYPED = 0, 1
 T_ENT, T_ENT_PROJ, T_REL_A, T_REL_B = range(4)
 CON_NORMALIZE, CON_CLIP = 0, 1
 OPT_RADIX_SORT = 1
+OPT_NO_SHADOW = 2
 N_PHASES = 8
 PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm", "rank_fix"]
 
 
 class Table(C.Structure):
-    _fields_ = [("w", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p),
+    _fields_ = [("w", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("wn", C.c_void_p),
                 ("rows", C.c_int64), ("cols", C.c_int32), ("ld", C.c_int32)]
 
 
 class Tables(C.Structure):
-    _fields_ = [("t", Table * KGE_MAX_TABLES)]
+    _fields_ = [("t", Table * KGE_MAX_TABLES), ("wn_valid", C.c_int32 * KGE_MAX_TABLES)]
 
 
 class Cfg(C.Structure):

@@ -64,6 +64,7 @@ class WeightView:
         if tuple(v.shape) != self.shape:
             raise ValueError(f"{self.name}: shape {tuple(v.shape)} != {self.shape}")
         self._table.view.copy_(v.to(self._table.storage.device))
+        self._table.touch()          # the training step's shadow of this table is stale now
         return self
 
     def __repr__(self):

@@ -41,6 +41,12 @@ static bool is_matrix_slot(const kge_cfg* c, int s) {
 static bool has_dense_reg(const kge_cfg* c) {
   return c->constraint && (c->model == KGE_TRANSH || c->model == KGE_RESCAL);
 }
+// the shadow table of kge_tables.wn_valid: entity table of the models whose start-of-batch
+// constraint is "normalise every entity row" (UM.py:153, TransE.py:171, DistMult.py:162)
+static bool shadow_capable(const kge_ctx_impl* ctx, const kge_cfg* c, const kge_tables* t) {
+  return !ctx->opt_no_shadow && !ctx->opt_radix_sort && c->constraint && t->t[KGE_T_ENT].wn != nullptr &&
+         (c->model == KGE_UM || c->model == KGE_TRANSE || c->model == KGE_DISTMULT);
+}
 static int mat_rows(const kge_cfg* c) { return c->d_ent; }
 static int mat_cols(const kge_cfg* c) { return c->model == KGE_TRANSR ? c->d_rel : c->d_ent; }
 static int mat_tiles(const kge_cfg* c) {
@@ -140,11 +146,7 @@ static int constraint_jobs(const kge_cfg* c, const kge_tables* t, ConstrainParam
 
 static int launch_constrain(const kge_ctx_impl* ctx, const ConstrainParams& cp, cudaStream_t st) {
   if (cp.n_jobs == 0) return KGE_OK;
-  int64_t blocks = (cp.total_rows + 7) / 8;
-  const int64_t cap = (int64_t) ctx->sm_count * 8;
-  if (blocks > cap) blocks = cap;
-  k_constrain<<<(unsigned) blocks, 256, 0, st>>>(cp);
-  KGE_CUDA_OK(cudaGetLastError());
+  if (launch_constrain_kernel(cp, ctx->sm_count, st) != KGE_OK) { set_error("k_constrain launch failed"); return KGE_ECUDA; }
   return KGE_OK;
 }
 
@@ -301,11 +303,21 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   PhaseTimer pt(ctx, st);
   ConstrainParams cp;
   constraint_jobs(cfg, tables, cp);
+  KGE_REQUIRE(!tables->t[KGE_T_ENT].wn || ((uintptr_t) tables->t[KGE_T_ENT].wn & 15) == 0, KGE_EINVAL, "wn not 16-byte aligned");
+  const bool shadow_ok = shadow_capable(ctx, cfg, tables);
+  // valid shadow + training call: rows are gathered from wn and the full-table pass is skipped
+  // (a validation call still assigns the normalised rows to w, as the reference does)
+  const bool shadow_use = shadow_ok && tables->wn_valid[KGE_T_ENT] && is_train;
+  if (shadow_use) { cp.n_jobs = 0; cp.total_rows = 0; }
+  // a validation call rewrites w with its normalised rows: wn = normalise(old w) is then no longer
+  // normalise(w) bit for bit (normalising twice moves the last bits), so the shadow is dropped
+  if (!is_train && cp.n_jobs > 0) tables->wn_valid[KGE_T_ENT] = 0;
 
   // 2. fused sample + gather + score + loss + backward
   MatStepParams mq;
   StepParams& p = mq.s;
   fill_model_dev(cfg, tables, p.md);
+  if (shadow_use) p.md.t[KGE_T_ENT].w = tables->t[KGE_T_ENT].wn;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     p.md.rld[s] = L.rld[s];
     p.rec[s] = (cols[s] && !is_matrix_slot(cfg, s)) ? reinterpret_cast<float*>(wsb + L.off_rec[s]) : nullptr;
@@ -483,6 +495,8 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     U.slot = s;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
     U.gsum = nullptr; U.gout = grad_only ? grads_out->dense[s] : nullptr;
+    U.w_in = (shadow_use && s == KGE_T_ENT) ? tables->t[s].wn : tables->t[s].w;
+    U.wn_out = (shadow_ok && s == KGE_T_ENT && !dense) ? tables->t[s].wn : nullptr;
     if (dense) {
       if (cfg->model == KGE_RESCAL) U.dense_kind = DK_RESCAL_ENT;
       else if (s == KGE_T_ENT) U.dense_kind = DK_TRANSH_ENT;
@@ -587,8 +601,10 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   }
   if (dense) {
     if (int rc2 = launch_update<2>(up, cpl, ublocks, st)) return rc2;
+    tables->wn_valid[KGE_T_ENT] = 0;
   } else if (ctx->opt_radix_sort) {
     if (int rc2 = launch_update<0>(up, cpl, ublocks, st)) return rc2;
+    tables->wn_valid[KGE_T_ENT] = 0;
   } else {
     // light rows: independent warps on the caller's stream; the few rows with many records are
     // summed by whole CTAs on the side stream at the same time (disjoint rows)
@@ -598,6 +614,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     KGE_CUDA_OK(cudaEventRecord(ctx->ev_heavy, ctx->aux));
     if (int rc2 = launch_update_fast<0>(up, cpl, st)) return rc2;
     KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_heavy, 0));
+    tables->wn_valid[KGE_T_ENT] = shadow_ok ? 1 : 0;        // wn now holds normalise(new w)
   }
   pt.end(4);
   return KGE_OK;
@@ -662,6 +679,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   KGE_CUDA_OK(cudaGetLastError());
 
   const bool dense = has_dense_reg(cfg);
+  const bool shadow_ok = shadow_capable(ctx, cfg, tables);
   UpdateParams up;
   up.n_tabs = 0;
   up.total_rows = 0;
@@ -679,6 +697,8 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     U.slot = s;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
     U.gsum = g->dense[s]; U.gout = nullptr;
+    U.w_in = (shadow_ok && tables->wn_valid[KGE_T_ENT] && s == KGE_T_ENT) ? tables->t[s].wn : tables->t[s].w;
+    U.wn_out = (shadow_ok && s == KGE_T_ENT && !dense) ? tables->t[s].wn : nullptr;
     if (dense) {            // TransH only (RESCAL is a matrix model)
       if (s == KGE_T_ENT) U.dense_kind = DK_TRANSH_ENT;
       else {
@@ -720,6 +740,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   } else {
     if (int rc = launch_update_fast<4>(up, cpl, st)) return rc;      // streaming pass: gradient = gsum row
   }
+  tables->wn_valid[KGE_T_ENT] = (shadow_ok && !dense) ? 1 : 0;
   pt.end(4);
   return KGE_OK;
 }

@@ -20,28 +20,78 @@ struct ConstrainParams {
   int64_t total_rows;
 };
 
+// The constraint arithmetic, one row held by a warp as CPL chunks per lane: sum of squares in
+// chunk order with explicitly rounded operations (no context-dependent FMA contraction), so the
+// stand-alone constraint pass and the update kernels' shadow output agree bit for bit.
+template <int CPL>
+__device__ __forceinline__ float row_sumsq(const float4 (&v)[CPL]) {
+  float ss = 0.f;
+#pragma unroll
+  for (int u = 0; u < CPL; ++u) {
+    ss = __fmaf_rn(v[u].x, v[u].x, ss); ss = __fmaf_rn(v[u].y, v[u].y, ss);
+    ss = __fmaf_rn(v[u].z, v[u].z, ss); ss = __fmaf_rn(v[u].w, v[u].w, ss);
+  }
+  return warp_sum(ss);
+}
+__device__ __forceinline__ float4 div4(float4 a, float den) {
+  return f4(__fdiv_rn(a.x, den), __fdiv_rn(a.y, den), __fdiv_rn(a.z, den), __fdiv_rn(a.w, den));   // X / norm * 1
+}
+
+// CPL = float4 chunks per lane (row width <= 128 * CPL floats); a warp takes RB consecutive rows and
+// issues all their loads before the first reduction, so the DRAM latency is paid once per batch.
+template <int CPL>
 __global__ void __launch_bounds__(256) k_constrain(const ConstrainParams p) {
+  constexpr int RB = CPL <= 2 ? 4 : (CPL == 4 ? 2 : 1);
   const int lane = threadIdx.x & 31;
   int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
-  for (; gw < p.total_rows; gw += nw) {
-    int64_t row = gw;
-    int j = 0;
-    while (j < p.n_jobs - 1 && row >= p.job[j].rows) { row -= p.job[j].rows; ++j; }
-    const ConstrainJob& J = p.job[j];
-    float4* base = reinterpret_cast<float4*>(J.w + row * (int64_t) J.ld);
-    const int nch = (J.cols + 3) >> 2;
-    float ss = 0.f;
-    for (int c = lane; c < nch; c += WARP) { float4 v = base[c]; ss += dot4(v, v); }
-    ss = warp_sum(ss);
-    const float nrm = sqrtf(ss);                 // pow(sum(pow(|x|, 2)), 1/2)
-    if (J.op == CON_CLIP && nrm < 1.0f) continue;
-    const float den = (J.op == CON_CLIP) ? fmaxf(nrm, 1e-9f) : nrm;
-    for (int c = lane; c < nch; c += WARP) {
-      float4 v = base[c];
-      base[c] = f4(v.x / den, v.y / den, v.z / den, v.w / den);   // X / norm * 1
+  for (int64_t g0 = gw * RB; g0 < p.total_rows; g0 += nw * RB) {
+    float4 v[RB][CPL];
+    float4* base[RB];
+    int nch[RB], op[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {
+      int64_t row = g0 + r;
+      base[r] = nullptr; nch[r] = 0; op[r] = CON_NORMALIZE;
+      if (row < p.total_rows) {
+        int j = 0;
+        while (j < p.n_jobs - 1 && row >= p.job[j].rows) { row -= p.job[j].rows; ++j; }
+        const ConstrainJob& J = p.job[j];
+        base[r] = reinterpret_cast<float4*>(J.w + row * (int64_t) J.ld);
+        nch[r] = (J.cols + 3) >> 2;
+        op[r] = J.op;
+      }
+#pragma unroll
+      for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; v[r][u] = (c < nch[r]) ? base[r][c] : f4zero(); }
+    }
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {
+      const float nrm = sqrtf(row_sumsq<CPL>(v[r]));      // pow(sum(pow(|x|, 2)), 1/2)
+      if (base[r] == nullptr || (op[r] == CON_CLIP && nrm < 1.0f)) continue;
+      const float den = (op[r] == CON_CLIP) ? fmaxf(nrm, 1e-9f) : nrm;
+#pragma unroll
+      for (int u = 0; u < CPL; ++u) {
+        const int c = lane + 32 * u;
+        if (c < nch[r]) base[r][c] = div4(v[r][u], den);
+      }
     }
   }
+}
+inline int launch_constrain_kernel(const ConstrainParams& cp, int sm_count, cudaStream_t st) {
+  int max_ch = 1;
+  for (int j = 0; j < cp.n_jobs; ++j) max_ch = ((cp.job[j].cols + 3) / 4 > max_ch) ? (cp.job[j].cols + 3) / 4 : max_ch;
+  const int cpl = max_ch <= 32 ? 1 : (max_ch <= 64 ? 2 : (max_ch <= 128 ? 4 : 8));
+  const int rb = cpl <= 2 ? 4 : (cpl == 4 ? 2 : 1);
+  int64_t blocks = (cp.total_rows + 8 * rb - 1) / (8 * rb);
+  const int64_t cap = (int64_t) sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  switch (cpl) {
+    case 1: k_constrain<1><<<(unsigned) blocks, 256, 0, st>>>(cp); break;
+    case 2: k_constrain<2><<<(unsigned) blocks, 256, 0, st>>>(cp); break;
+    case 4: k_constrain<4><<<(unsigned) blocks, 256, 0, st>>>(cp); break;
+    default: k_constrain<8><<<(unsigned) blocks, 256, 0, st>>>(cp); break;
+  }
+  return cudaGetLastError() == cudaSuccess ? KGE_OK : KGE_ECUDA;
 }
 
 __global__ void __launch_bounds__(1024) k_reduce(const ReduceParams p) {
@@ -89,6 +139,8 @@ struct UpdateTable {
   int dense_kind;        // DK_*
   const float* other_w;  // TransH: the paired relation table (rel_hyper for rel_emb and vice versa)
   int other_ld;
+  const float* w_in;     // where the row's current weights are read: w, or the shadow wn when it is valid
+  float* wn_out;         // shadow output: normalise(new row) for the next batch's gathers (or NULL)
   const float* gsum;     // data-parallel apply: summed gradient [rows x ld] added to the record sum (or NULL)
   float* gout;           // DENSE=3 (data-parallel grad): where the row's summed gradient goes, [rows x ld]
 };
@@ -342,6 +394,36 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
   }
 }
 
+// Clip scale + Adam on one row held by a warp (g = summed, unscaled gradient); optionally also
+// writes normalise(new row) to the shadow table the next batch gathers from.
+template <int CPL>
+__device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTable& T, int64_t row, int nch, int lane,
+                                         const float4 (&g)[CPL]) {
+  const float4* wi = reinterpret_cast<const float4*>(T.w_in + row * (int64_t) T.ld);
+  float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
+  float4* m4 = reinterpret_cast<float4*>(T.m + row * (int64_t) T.ld);
+  float4* v4 = reinterpret_cast<float4*>(T.v + row * (int64_t) T.ld);
+  const float scale = p.scal[T.slot];
+  float4 wnew[CPL];
+#pragma unroll
+  for (int u = 0; u < CPL; ++u) {
+    const int c = lane + 32 * u;
+    wnew[u] = f4zero();
+    if (c >= nch) continue;
+    float4 w = wi[c], m = m4[c], v = v4[c];
+    adam_chunk(w, m, v, scale4(scale, g[u]), p.beta1, p.beta2, p.lr_t, p.eps);
+    mask_tail(w, m, v, c, T.cols);
+    m4[c] = m; v4[c] = v; w4[c] = w;
+    wnew[u] = w;
+  }
+  if (T.wn_out != nullptr) {                       // warp-uniform
+    const float nrm = sqrtf(row_sumsq<CPL>(wnew));
+    float4* o = reinterpret_cast<float4*>(T.wn_out + row * (int64_t) T.ld);
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) o[c] = div4(wnew[u], nrm); }
+  }
+}
+
 // The common training case (no dense regulariser): one warp per table row, warps fully
 // independent (no CTA barrier), dependent-load chain shortened to header -> records -> w/m/v:
 //   * the w / m / v lines are requested into L2 first (no registers held),
@@ -362,9 +444,9 @@ __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
   while (j < p.n_tabs - 1 && row >= p.tab[j].rows) { row -= p.tab[j].rows; ++j; }
   const UpdateTable& T = p.tab[j];
   const int nch = (T.cols + 3) >> 2;
-  float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
-  float4* m4 = reinterpret_cast<float4*>(T.m + row * (int64_t) T.ld);
-  float4* v4 = reinterpret_cast<float4*>(T.v + row * (int64_t) T.ld);
+  const float4* w4 = reinterpret_cast<const float4*>(T.w_in + row * (int64_t) T.ld);
+  const float4* m4 = reinterpret_cast<const float4*>(T.m + row * (int64_t) T.ld);
+  const float4* v4 = reinterpret_cast<const float4*>(T.v + row * (int64_t) T.ld);
   if (MODE != 3) {
 #pragma unroll
     for (int u = 0; u < CPL; ++u) {
@@ -402,17 +484,7 @@ __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
 #pragma unroll
     for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) g[u] += __ldg(gs + c); }
   }
-  const float scale = p.scal[T.slot];
-#pragma unroll
-  for (int u = 0; u < CPL; ++u) {
-    const int c = lane + 32 * u;
-    if (c >= nch) continue;
-    float4 w = w4[c], m = m4[c], v = v4[c];
-    const float4 gg = scale4(scale, g[u]);
-    adam_chunk(w, m, v, gg, p.beta1, p.beta2, p.lr_t, p.eps);
-    mask_tail(w, m, v, c, T.cols);
-    m4[c] = m; v4[c] = v; w4[c] = w;
-  }
+  adam_row<CPL>(p, T, row, nch, lane, g);
 }
 
 // Rows with many records (hot entities / relations): one CTA per (heavy key, table), the eight
@@ -439,22 +511,15 @@ __global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
   for (int u = 0; u < CPL; ++u) s_part[warp][u * WARP + lane] = part[u];
   __syncthreads();
   if (warp != 0) continue;
-  float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
-  float4* m4 = reinterpret_cast<float4*>(T.m + row * (int64_t) T.ld);
-  float4* v4 = reinterpret_cast<float4*>(T.v + row * (int64_t) T.ld);
-  const float scale = p.scal[T.slot];
+  float4 g[CPL];
 #pragma unroll
   for (int u = 0; u < CPL; ++u) {
+    g[u] = f4zero();
+    for (int w3 = 0; w3 < 8; ++w3) g[u] += s_part[w3][u * WARP + lane];
     const int c = lane + 32 * u;
-    if (c >= nch) continue;
-    float4 g = f4zero();
-    for (int w3 = 0; w3 < 8; ++w3) g += s_part[w3][u * WARP + lane];
-    if (MODE == 3) { reinterpret_cast<float4*>(T.gout + row * (int64_t) T.ld)[c] = g; continue; }
-    float4 w = w4[c], m = m4[c], v = v4[c];
-    adam_chunk(w, m, v, scale4(scale, g), p.beta1, p.beta2, p.lr_t, p.eps);
-    mask_tail(w, m, v, c, T.cols);
-    m4[c] = m; v4[c] = v; w4[c] = w;
+    if (MODE == 3 && c < nch) reinterpret_cast<float4*>(T.gout + row * (int64_t) T.ld)[c] = g[u];
   }
+  if (MODE != 3) adam_row<CPL>(p, T, row, nch, lane, g);
   }
 }
 

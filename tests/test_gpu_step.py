@@ -257,3 +257,38 @@ def test_grouping_equals_stable_radix_sort(model, B, k, n_rel):
         outs.append({s: t.storage.clone() for s, t in eng.tab.items()})
     for s in outs[0]:
         assert torch.equal(outs[0][s], outs[1][s]), f"slot {s}"
+
+
+@pytest.mark.parametrize("model,score", [("DistMult", "dot"), ("TransE", "l1"), ("UM", "l2pow")])
+def test_shadow_table_is_bit_identical_to_constraint_pass(model, score):
+    """kge_tables.wn (normalised rows written by the row update for the next batch) must change
+    nothing: train / validation / external assign sequences give the same bits with the shadow and
+    with the full-table constraint pass every batch (KGE_OPT_NO_SHADOW)."""
+    from KGE._b200 import lib as L
+    outs, losses = [], []
+    for no_shadow in (1, 0):
+        rng = np.random.default_rng(23)
+        _, _, eng = make_pair(model, N, R, 40, score=_score_for(model, score), loss=LOSSES["hinge"], k=6, side="h+t")
+        assert eng.tab[0].wn is not None
+        eng.set_option(L.OPT_NO_SHADOW, no_shadow)
+        ls = []
+        try:
+            for step in range(8):
+                X = rand_triples(rng, 96, N, R)
+                if step == 3:                       # validation batch: assigns the constraint, no update
+                    ls.append(float(eng.train_step(X, 5, step, is_train=False).item()))
+                    continue
+                if step == 5:                       # caller overwrites weights: the shadow must be dropped
+                    eng.tab[0].view.mul_(1.5)
+                    eng.tab[0].touch()
+                ls.append(float(eng.train_step(X, 5, step).item()))
+                if not no_shadow:
+                    assert eng.tab[0].wn_valid
+            torch.cuda.synchronize()
+        finally:
+            eng.set_option(L.OPT_NO_SHADOW, 0)
+        outs.append({s: t.storage.clone() for s, t in eng.tab.items()})
+        losses.append(ls)
+    assert losses[0] == losses[1]
+    for s in outs[0]:
+        assert torch.equal(outs[0][s], outs[1][s]), f"slot {s}"
