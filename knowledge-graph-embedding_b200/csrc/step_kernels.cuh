@@ -92,6 +92,40 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
   FwdSaved<NV> sv;
   const float sp = M::template forward<NV>(md, H, R, T, lane, x, y, sv);
 
+  // RotatE with LpDistance(1) (its default, RotatE.py:46): |h o r - N| for tail corruption and
+  // |N o r - t| = |N - t o conj(r)| for head corruption (|r| = 1) are both "distance of the
+  // negative's row to a vector X fixed per positive".  One X instead of H, T, R and their
+  // gradient rows in registers: 1000-float rows no longer spill.
+  bool rot_fast = false;
+  Row<NV> X;
+  if constexpr (M::KIND == KGE_ROTATE) {
+    rot_fast = md.sc.kind == SC_L1 && !md.sc.pow2 && (p.sd.side_mode != KGE_SIDE_HT || (wpp & 1) == 0);
+    if (rot_fast) {
+      const bool head = neg_is_head(p.sd, wig);
+#pragma unroll
+      for (int v = 0; v < NV; ++v) {
+        const float4 cs = R.a.v[v];                         // (cos0, cos1, sin0, sin1)
+        if (head) {                                          // t o conj(r)
+          const float4 e = T.e.v[v];
+          X.v[v] = f4(e.x * cs.x + e.y * cs.z, -e.x * cs.z + e.y * cs.x, e.z * cs.y + e.w * cs.w, -e.z * cs.w + e.w * cs.y);
+        } else {                                             // h o r
+          const float4 e = H.e.v[v];
+          X.v[v] = f4(e.x * cs.x - e.y * cs.z, e.x * cs.z + e.y * cs.x, e.z * cs.y - e.w * cs.w, e.z * cs.w + e.w * cs.y);
+        }
+      }
+    }
+  }
+  // sum of moduli of X - N over the lane's elements (all lanes then reduce)
+  auto rot_dist = [&](const Row<NV>& Nr) {
+    float a = 0.f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const float4 u = X.v[v] - Nr.v[v];
+      a += sqrtf(u.x * u.x + u.y * u.y) + sqrtf(u.z * u.z + u.w * u.w);
+    }
+    return warp_sum(a);
+  };
+
   // self-adversarial weights need all k scores of this positive first (loss.py:176-177)
   float sm_max = 0.f, sm_inv = 1.f;
   const bool softmax = (p.loss.kind == KGE_LOSS_SELF_ADV);
@@ -101,7 +135,9 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
       const int64_t e = p.neg_override ? p.neg_override[i * k + c] : sample_negative(p.sd, i, c, h, t);
       Ent N;
       N.load(md, e, lane);
-      const float sn = M::template forward<NV>(md, head ? N : H, R, head ? T : N, lane, x, y, sv);
+      float sn;
+      if (rot_fast) sn = -fmaxf(rot_dist(N.e), 1e-9f);
+      else sn = M::template forward<NV>(md, head ? N : H, R, head ? T : N, lane, x, y, sv);
       if (lane == 0) s_neg[c] = sn;
     }
     group_barrier(grp, wpp);
@@ -145,6 +181,78 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
   // dneg^2 * (|q|^2 + sum N^2 r^2) for the entity table, dneg^2 * sum N^2 kept^2 for the relation.
   // Needs the corrupted side to be fixed per warp: true unless 'h+t' meets an odd warp count.
   bool fast_done = false;
+  if constexpr (M::KIND == KGE_ROTATE) {
+    if (rot_fast) {
+      fast_done = true;
+      const bool head = neg_is_head(p.sd, wig);
+      Row<NV> A;                     // sum over negatives of coef * unit(X - N)
+      Row<NV> Gp;                    // phase gradient, (g0, g1, 0, 0) per chunk like RelRot's gradient row
+      A.zero(); Gp.zero();
+      for (int it = 0; it < n_it; ++it) {
+        const int c = wig + it * wpp;
+        const int64_t slot = i * k + c;
+        const int64_t e = __shfl_sync(FULL, my_e, it & 31);
+        Ent N;
+        N.load(md, e, lane);
+        if (it + 1 < n_it && ((it + 1) & 31) == 0) draw(it + 1);
+        if (lane == 0 && p.write_keys) {
+          p.neg_ids[slot] = e;
+          if (TRAIN) { p.keys[2 * p.B + slot] = (uint32_t) e; p.vals[2 * p.B + slot] = (uint32_t)(2 * p.B + slot); }
+        }
+        // unit vectors of X - N in place of N, sum of moduli, count of non-zero moduli
+        float acc = 0.f, cnt = 0.f;
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+          const float4 u = X.v[v] - N.e.v[v];
+          const float m0 = sqrtf(u.x * u.x + u.y * u.y), m1 = sqrtf(u.z * u.z + u.w * u.w);
+          const float i0 = m0 > 0.f ? 1.0f / m0 : 0.f, i1 = m1 > 0.f ? 1.0f / m1 : 0.f;
+          acc += m0 + m1;
+          cnt += (m0 > 0.f ? 1.f : 0.f) + (m1 > 0.f ? 1.f : 0.f);
+          N.e.v[v] = f4(u.x * i0, u.y * i0, u.z * i1, u.w * i1);
+        }
+        const float S = warp_sum(acc);
+        const float sn = -fmaxf(S, 1e-9f);
+        const float w = softmax ? expf(p.loss.temperature * sn - sm_max) * sm_inv : 1.f;
+        float term, dneg, dpp;
+        loss_neg(p.loss, sp, sn, w, term, dneg, dpp);
+        lsum += term;
+        gpos += dpp;
+        if (TRAIN) {
+          // d score / d X = -unit(X - N) inside the clip's pass band (score.py:61)
+          const float coef = (S >= 1e-9f) ? -dneg : 0.f;
+          const float cps = (head ? -coef : coef) * md.rotate_scale;
+          float pr = 0.f;
+#pragma unroll
+          for (int v = 0; v < NV; ++v) {
+            const float4 uh = N.e.v[v], xv = X.v[v];
+            A.v[v] += coef * uh;
+            // phase gradient: scale * Im(conj(X) * coef * unit)
+            // (head corruption: unit(N o r - t) = -r o unit(X - N), which flips the sign)
+            const float g0 = (xv.x * uh.y - xv.y * uh.x) * cps;
+            const float g1 = (xv.z * uh.w - xv.w * uh.z) * cps;
+            Gp.v[v].x += g0; Gp.v[v].y += g1;
+            pr += g0 * g0 + g1 * g1;
+            N.e.v[v] = (-coef) * uh;            // d score / d N, up to the rotation for head corruption (same norm)
+          }
+          nrm[KGE_T_ENT] += 2.0f * coef * coef * cnt;      // the negative's row and the kept entity's occurrence
+          nrm[KGE_T_REL_A] += pr;
+          store_row(N.e, p.rec[KGE_T_ENT], 2 * p.B + slot, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+        }
+      }
+      if (TRAIN) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+          const float4 q = A.v[v], cs = R.a.v[v];
+          if (head) {       // kept entity is t: d/dt = -(d/dx) with x = N o r, i.e. -rot(A)... A is in the X = t o conj(r) frame
+            GT.e.v[v] += f4(q.x * cs.x - q.y * cs.z, q.x * cs.z + q.y * cs.x, q.z * cs.y - q.w * cs.w, q.z * cs.w + q.w * cs.y);
+          } else {          // kept entity is h: d/dh = conj(r) o (d/dX)
+            GH.e.v[v] += f4(q.x * cs.x + q.y * cs.z, -q.x * cs.z + q.y * cs.x, q.z * cs.y + q.w * cs.w, -q.z * cs.w + q.w * cs.y);
+          }
+          GR.a.v[v] += Gp.v[v];
+        }
+      }
+    }
+  }
   if constexpr (M::KIND == KGE_DISTMULT) {
     if (p.sd.side_mode != KGE_SIDE_HT || (wpp & 1) == 0) {
       fast_done = true;
