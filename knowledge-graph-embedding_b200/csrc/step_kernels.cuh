@@ -253,6 +253,60 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
       }
     }
   }
+  // TransE / UM: the score depends on the negative through X - N only, X = h + r (tail corrupted)
+  // or t - r (head corrupted; |N + r - t| = |X - N|), for every LpDistance / LpDistancePow / Dot
+  // variant score.cuh knows.  One gradient row per negative (d/dX) feeds the record (= -d/dX), the
+  // kept entity and the relation (+-d/dX, same norm each), instead of three rows and three norms.
+  if constexpr (M::KIND == KGE_TRANSE || M::KIND == KGE_UM) {
+    if (md.sc.kind != SC_DOT && (p.sd.side_mode != KGE_SIDE_HT || (wpp & 1) == 0)) {
+      fast_done = true;
+      const bool head = neg_is_head(p.sd, wig);
+      Row<NV> Xq, A;
+      A.zero();
+#pragma unroll
+      for (int v = 0; v < NV; ++v) {
+        if constexpr (M::KIND == KGE_UM) Xq.v[v] = head ? T.e.v[v] : H.e.v[v];
+        else Xq.v[v] = head ? T.e.v[v] - R.a.v[v] : H.e.v[v] + R.a.v[v];
+      }
+      for (int it = 0; it < n_it; ++it) {
+        const int c = wig + it * wpp;
+        const int64_t slot = i * k + c;
+        const int64_t e = __shfl_sync(FULL, my_e, it & 31);
+        Ent N;
+        if (PREFETCH) N = Nnext; else N.load(md, e, lane);
+        if (it + 1 < n_it) {
+          if (((it + 1) & 31) == 0) draw(it + 1);
+          if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, (it + 1) & 31), lane);
+        }
+        if (lane == 0 && p.write_keys) {
+          p.neg_ids[slot] = e;
+          if (TRAIN) { p.keys[2 * p.B + slot] = (uint32_t) e; p.vals[2 * p.B + slot] = (uint32_t)(2 * p.B + slot); }
+        }
+        const float sn = score_fwd<NV, false>(md.sc, Xq, N.e, sv.sc);
+        const float w = softmax ? expf(p.loss.temperature * sn - sm_max) * sm_inv : 1.f;
+        float term, dneg, dpp;
+        loss_neg(p.loss, sp, sn, w, term, dneg, dpp);
+        lsum += term;
+        gpos += dpp;
+        if (TRAIN) {
+          Row<NV> gx, gy;
+          score_bwd<NV, false>(md.sc, Xq, N.e, sv.sc, dneg, gx, gy);
+          const float ss = row_dot_partial(gx, gx);
+          nrm[KGE_T_ENT] += 2.0f * ss;                     // the negative's row and the kept entity's occurrence
+          if constexpr (M::KIND == KGE_TRANSE) nrm[KGE_T_REL_A] += ss;
+          row_add(A, gx);
+          store_row(gy, p.rec[KGE_T_ENT], 2 * p.B + slot, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+        }
+      }
+      if (TRAIN) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+          if (head) GT.e.v[v] += A.v[v]; else GH.e.v[v] += A.v[v];
+          if constexpr (M::KIND == KGE_TRANSE) GR.a.v[v] += head ? -A.v[v] : A.v[v];
+        }
+      }
+    }
+  }
   if constexpr (M::KIND == KGE_DISTMULT) {
     if (p.sd.side_mode != KGE_SIDE_HT || (wpp & 1) == 0) {
       fast_done = true;
