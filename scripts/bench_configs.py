@@ -20,14 +20,14 @@ def typed_pools(eng, N, n_types, rng):
     eng.set_typed_pools(t, off, order, pos)
 
 
-def run(name, model, N, R, d, dr, score, loss, k, side, B, typed=0, steps=60, evalQ=4096):
+def run(name, model, N, R, d, dr, score, loss, k, side, B, typed=0, steps=60, evalQ=4096, constraint=True):
     rng = np.random.default_rng(7)
-    ref = RM.MODELS[model](N, R, d, dr, score_fn=score, loss_fn=loss, constraint=True, constraint_weight=1.0)
+    ref = RM.MODELS[model](N, R, d, dr, score_fn=score, loss_fn=loss, constraint=constraint, constraint_weight=1.0)
     W = ref.init_weights(5)
     if model == "TransR":
         W.data["rel_proj"] = W.data["rel_proj"] + (torch.rand(W.data["rel_proj"].shape) - 0.5) * 0.2
     cfg = spec.make_cfg(model, N, R, d, dr, score_fn=score, loss_fn=loss, negative_ratio=k, corrupt_side=side,
-                        constraint=True, constraint_weight=1.0, rotate_limit=ref.limit)
+                        constraint=constraint, constraint_weight=1.0, rotate_limit=ref.limit)
     eng = E.Engine(cfg, {spec.SLOTS[model][kk]: v for kk, v in W.data.items()}, device=dev)
     if typed:
         typed_pools(eng, N, typed, rng)
@@ -67,3 +67,6 @@ run("C3 RotatE d=500 L1 self-adv 'h+t' k=256 B=1024", "RotatE", 14505, 237, 500,
     O.SelfAdversarialNegativeSamplingLoss(3.0, 1.0), 256, "h+t", 1024, steps=20, evalQ=2048)
 run("C4 TransR d=100 L2^2 hinge typed(3) 'h+t' k=10 B=1024", "TransR", 14505, 237, 100, 100, O.LpDistancePow(2), hinge, 10, "h+t", 1024, typed=3, evalQ=2048)
 run("C4 TransD d=100 L2^2 hinge typed(32) 'h+t' k=10 B=1024", "TransD", 14505, 237, 100, 100, O.LpDistancePow(2), hinge, 10, "h+t", 1024, typed=32, evalQ=2048)
+# C5 shape at one GPU's share: 1/5 of the entities (1 M x 128, w + m + v = 1.5 GB), B = 65536 / 8
+run("C5-lite TransE d=128 L1 hinge 'h+t' k=32 B=8192 N=1M constraint=False", "TransE", 1000000, 1000, 128, None, O.LpDistance(1), hinge,
+    32, "h+t", 8192, steps=20, evalQ=1024, constraint=False)
