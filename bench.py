@@ -149,7 +149,7 @@ def run_ours(args, rank, world, device):
     train = zipf_triples(W["n_train"], W["n_ent"], W["n_rel"], 12345)
     # data-parallel (world > 1): one GLOBAL batch of world*B positives per step, identical on every
     # rank; rank r owns positives [r*B, (r+1)*B) (weak scaling: per-GPU batch fixed).  Gradients are
-    # summed with one NCCL all-reduce per step inside Engine.train_step_dp.
+    # exchanged inside Engine.train_step_dp (peer staging over NVLink, or one NCCL all-reduce).
     rng = np.random.default_rng(100)
     n_batches = 64
     host_batches = [torch.from_numpy(train[rng.integers(0, len(train), B * world)][rank * B:(rank + 1) * B].copy())
@@ -380,15 +380,17 @@ def main():
         "metric": METRIC, "value": r["triples"] / (r["ms_cold"] * 1e-3), "unit": "triples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_cold"] / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": config, "clocks": r["clocks"],
+        "config": dict(config, exchange=(getattr(r["eng"], "_dp_kind", None) or "none") if world > 1 else "none"),
+        "clocks": r["clocks"],
         "value_steady_state_l2_warm": r["triples"] / (r["ms_warm"] * 1e-3),
         "e2e": {"value": r["triples"] / (r["ms_e2e"] * 1e-3), "unit": "triples/s",
                 "h2d_bytes_per_step": W["B"] * 3 * 8, "d2h_bytes_per_step": 4},
-        "gpu_launches": args.steps * (8 if world == 1 else 9),
+        "gpu_launches": args.steps * (8 if world == 1 else 11),
         "gpu_launches_note": "own kernels per step: k_constrain, k_step (loss/clip reduction folded into its last warp), "
         "k_update_fast on the caller's stream; k_keys, k_scan, k_scatter, k_canon, k_update_heavy on the side stream "
-        "(+ one memset there); data-parallel runs add k_dp_scales and replace the update pair by k_update<3> / k_update<0> "
-        "around one NCCL all-reduce",
+        "(+ one memset there); data-parallel runs split the update pair into k_update_fast/heavy<3> (row sums stored "
+        "into every rank's staging slot over NVLink) + k_push_scal, one cross-GPU barrier, then k_dp_scales + "
+        "k_update_fast<4> (config.exchange = peer), or the same around one NCCL all-reduce (exchange = nccl)",
         "roofline": {"kernel": "k_step<MDistMult,2,true>", "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": ncu_traffic("k_step<MDistMult"),
                      "traffic_note": "ncu dram read+write per launch (cold caches); below the algorithmic bytes because "

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 2
+#define KGE_ABI_VERSION 3
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -178,15 +178,29 @@ int kge_train_step_host(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler
  *   kge_train_apply : per-variable clip_by_norm from the summed norms, dense regularisers,
  *                     TF-semantics Adam on every row; loss_out = summed loss (+ regulariser).
  * grads.dense[s]: [rows x ld] fp32 with the table's own ld (every row is written by _grad).
- * Row-sparse lists (ent_rows / ent_vals) are reserved: must be NULL / 0 in ABI version 1. */
+ * Row-sparse lists (ent_rows / ent_vals) are reserved: must be NULL / 0. */
 typedef struct kge_dp {
   int32_t world, rank;
   int64_t B_global;              /* positives of the whole step */
   int64_t i_base;                /* global index of this rank's first positive */
 } kge_dp;
+#define KGE_MAX_PEERS 8
 typedef struct kge_grads {
   float* dense[KGE_MAX_TABLES];
-  int64_t* ent_rows;  float* ent_vals[2];  int64_t cap;  int32_t lists, reserved;
+  int64_t* ent_rows;  float* ent_vals[2];  int64_t cap;  int32_t lists;
+  /* Fused exchange over peer memory (NVLink / NVSwitch), n_peers > 0: replaces `dense` / scal.
+   *   kge_train_grad : peer[j][s] / peer_scal[j] = the address, mapped into THIS process, of this
+   *                    rank's slot in rank j's staging buffer (j == rank is local memory); the
+   *                    gradient kernels store every row sum to all n_peers destinations, so the
+   *                    all-gather rides on the kernel's own stores.
+   *   (caller)       : one cross-GPU barrier (all ranks' kernels done, stores visible).
+   *   kge_train_apply: peer[j][s] / peer_scal[j] = LOCAL address of rank j's slot; the update
+   *                    sums the n_peers slots in rank order (identical bits on every rank).
+   * The caller alternates two staging buffers between steps (a rank may still be applying
+   * step i while a faster peer already pushes step i + 1). */
+  int32_t n_peers;
+  float* peer[KGE_MAX_PEERS][KGE_MAX_TABLES];
+  float* peer_scal[KGE_MAX_PEERS];
 } kge_grads;
 int kge_train_grad(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const kge_dp*,
                    const void* triples, int64_t B, uint64_t seed, uint64_t step,

@@ -7,8 +7,13 @@ same code runs over gloo on CPU tensors in tests/test_dp_gloo.py).
   * training: every rank holds all tables and `batch_shard` of the step's positives; the
     per-table summed gradients and the five scalars (norm^2 x 4, loss) live in ONE flat fp32
     buffer (`GradBuffer`) so a step needs a single all-reduce; each rank then applies the
-    identical update, so replicas stay bit-identical.
+    identical update, so replicas stay bit-identical;
+  * on one NVLink / NVSwitch node the all-reduce is replaced by `PeerStaging`: the gradient
+    kernels store their row sums straight into every rank's staging slot (peer memory), one
+    cross-GPU barrier follows, and the update kernel sums the slots in rank order.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -81,3 +86,95 @@ class GradBuffer:
         if world()[1] > 1:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
         return self
+
+
+class PeerStaging:
+    """Staging memory of the fused exchange, identical on every rank:
+    [2 step parities][world slots][table 0 | .. | table 3 | scal(8)] fp32.
+    `base_ptrs[j]` = address of rank j's staging buffer as mapped into THIS process
+    (torch symmetric memory on a real node; plain local tensors when ranks are emulated on one
+    device in tests).  `push(parity)` / `slots(parity)` fill the `peer` fields of kge_grads for
+    kge_train_grad / kge_train_apply (include/kge_abi.h)."""
+
+    def __init__(self, tables, world_size, rank, base_ptrs=None, barrier=None, keep=None):
+        from . import lib as L
+        if not (1 <= world_size <= L.KGE_MAX_PEERS):
+            raise ValueError(f"peer exchange supports up to {L.KGE_MAX_PEERS} ranks")
+        self.world, self.rank = int(world_size), int(rank)
+        self.offsets, o = {}, 0
+        for s in sorted(tables):
+            rows, ld = tables[s]
+            if ld % 4:
+                raise ValueError("row stride must be a multiple of 4 floats")
+            self.offsets[s] = o
+            o += rows * ld
+        self.scal_off = o
+        self.per = (o + GradBuffer.N_SCAL + 63) // 64 * 64          # slots stay 256-byte aligned
+        self.base_ptrs = list(base_ptrs) if base_ptrs is not None else None
+        self.barrier = barrier
+        self._keep = keep                                           # owners of the memory
+        self._cache = {}
+
+    def numel(self):
+        return 2 * self.world * self.per
+
+    def _addr(self, owner, parity, slot, off):
+        return self.base_ptrs[owner] + 4 * ((parity * self.world + slot) * self.per + off)
+
+    def _grads(self, parity, push):
+        from . import lib as L
+        key = (parity, push)
+        if key not in self._cache:
+            G = L.Grads()
+            G.n_peers = self.world
+            for j in range(self.world):
+                owner, slot = (j, self.rank) if push else (self.rank, j)
+                for s, off in self.offsets.items():
+                    G.peer[j][s] = self._addr(owner, parity, slot, off)
+                G.peer_scal[j] = self._addr(owner, parity, slot, self.scal_off)
+            self._cache[key] = G
+        return self._cache[key]
+
+    def push(self, parity):
+        """Where this rank's gradients go on every rank."""
+        return self._grads(parity & 1, True)
+
+    def slots(self, parity):
+        """Where every rank's gradients sit in this rank's memory."""
+        return self._grads(parity & 1, False)
+
+    @classmethod
+    def symmetric(cls, tables, device, group=None):
+        """Staging in torch symmetric memory (CUDA VMM peer mappings over NVLink), or None when
+        any rank cannot set it up (the caller then keeps the NCCL all-reduce)."""
+        rank, world_size = world()
+        ok, st = 1, None
+        try:
+            import torch.distributed._symmetric_memory as sm
+            st = cls(tables, world_size, rank)
+            buf = sm.empty(st.numel(), dtype=torch.float32, device=device)
+            hdl = sm.rendezvous(buf, group=group if group is not None else dist.group.WORLD)
+            buf.zero_()
+            st.base_ptrs = [int(p) for p in hdl.buffer_ptrs]
+            st.barrier = hdl.barrier
+            st._keep = (buf, hdl)
+        except Exception as e:                                      # noqa: BLE001 - any failure => NCCL path
+            ok = 0
+            if os.environ.get("KGE_DP_EXCHANGE") == "peer":
+                raise RuntimeError(f"KGE_DP_EXCHANGE=peer but symmetric memory is unavailable: {e!r}")
+        flag = torch.tensor([ok], dtype=torch.int32, device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) != 1:
+            return None
+        hdl.barrier()
+        return st
+
+
+def exchange_kind(world_size):
+    """'peer' (kernel stores into peer staging + one barrier) or 'nccl' (all-reduce of the flat
+    buffer).  Peer stores cost world x the gradient bytes per rank, so the default switches to
+    NCCL beyond 4 ranks; KGE_DP_EXCHANGE=peer|nccl overrides."""
+    e = os.environ.get("KGE_DP_EXCHANGE", "")
+    if e in ("peer", "nccl"):
+        return e
+    return "peer" if 2 <= world_size <= 4 else "nccl"

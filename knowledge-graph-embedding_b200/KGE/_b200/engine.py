@@ -229,9 +229,12 @@ class Engine:
             neg = torch.as_tensor(neg_override, dtype=torch.int64).to(self.device).contiguous()
         neg_out = torch.empty(B * self.k_eff(), dtype=torch.int64, device=self.device) if want_negatives else None
         T = self._tables(with_opt=False)
-        G = self._grads_struct(gb)
+        if isinstance(gb, L.Grads):            # peer staging (dp.PeerStaging.push): scalars travel with it
+            G, scal = gb, None
+        else:
+            G, scal = self._grads_struct(gb), gb.scal
         L.check(L.load().kge_train_grad(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler),
-                                        C.byref(dpd), _ptr(X), B, seed, step, _ptr(neg), C.byref(G), _ptr(gb.scal),
+                                        C.byref(dpd), _ptr(X), B, seed, step, _ptr(neg), C.byref(G), _ptr(scal),
                                         _ptr(neg_out), _ptr(ws), ws.numel(), _stream()))
         return neg_out
 
@@ -242,8 +245,11 @@ class Engine:
             loss_out = torch.empty(1, dtype=torch.float32, device=self.device)
         self.adam_t += 1
         T = self._tables(with_opt=True)
-        G = self._grads_struct(gb)
-        L.check(L.load().kge_train_apply(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(G), _ptr(gb.scal), B,
+        if isinstance(gb, L.Grads):            # peer staging (dp.PeerStaging.slots)
+            G, scal = gb, None
+        else:
+            G, scal = self._grads_struct(gb), gb.scal
+        L.check(L.load().kge_train_apply(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(G), _ptr(scal), B,
                                          self.adam_t, _ptr(loss_out), _ptr(ws), ws.numel(), _stream()))
         self._sync_shadow(T)
         return loss_out
@@ -252,8 +258,22 @@ class Engine:
         """One data-parallel step; every rank of the process group must call it."""
         from . import dp as _dp
         rank, world_size = _dp.world()
-        if getattr(self, "_gbuf", None) is None:
-            self._gbuf = self.grad_buffer()
+        if getattr(self, "_dp_kind", None) is None:
+            self._dp_kind, self._peer, self._gbuf, self._dp_steps = _dp.exchange_kind(world_size), None, None, 0
+            if self._dp_kind == "peer":
+                self._peer = _dp.PeerStaging.symmetric({s: (pt.rows, pt.ld) for s, pt in self.tab.items()},
+                                                       self.device, group)
+                if self._peer is None:
+                    self._dp_kind = "nccl"
+            if self._dp_kind == "nccl":
+                self._gbuf = self.grad_buffer()
+        if self._dp_kind == "peer":
+            # gradient kernels store into every rank's staging slot; one barrier; sum of the slots
+            par = self._dp_steps & 1
+            self._dp_steps += 1
+            self.train_grad(self._peer.push(par), triples_local, seed, step, B_global, i_base, rank, world_size, neg_override)
+            self._peer.barrier()
+            return self.train_apply(self._peer.slots(par), len(triples_local), loss_out)
         self.train_grad(self._gbuf, triples_local, seed, step, B_global, i_base, rank, world_size, neg_override)
         self._gbuf.allreduce(group)                       # the step's single collective
         return self.train_apply(self._gbuf, len(triples_local), loss_out)

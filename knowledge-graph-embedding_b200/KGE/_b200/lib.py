@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 2
+KGE_ABI_VERSION = 3
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -52,9 +52,13 @@ class Dp(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("B_global", C.c_int64), ("i_base", C.c_int64)]
 
 
+KGE_MAX_PEERS = 8
+
+
 class Grads(C.Structure):
     _fields_ = [("dense", C.c_void_p * KGE_MAX_TABLES), ("ent_rows", C.c_void_p),
-                ("ent_vals", C.c_void_p * 2), ("cap", C.c_int64), ("lists", C.c_int32), ("reserved", C.c_int32)]
+                ("ent_vals", C.c_void_p * 2), ("cap", C.c_int64), ("lists", C.c_int32), ("n_peers", C.c_int32),
+                ("peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("peer_scal", C.c_void_p * KGE_MAX_PEERS)]
 
 
 SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destroy",

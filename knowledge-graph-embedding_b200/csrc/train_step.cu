@@ -273,18 +273,27 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   const bool mat = is_matrix_model(cfg->model);
   int64_t B_global = B;
   if (grad_only) {
-    KGE_REQUIRE(grads_out && scal_out, KGE_EINVAL, "grads / scal_out is NULL");
+    KGE_REQUIRE(grads_out, KGE_EINVAL, "grads is NULL");
+    KGE_REQUIRE(grads_out->n_peers >= 0 && grads_out->n_peers <= KGE_MAX_PEERS, KGE_EINVAL, "grads.n_peers %d out of range",
+                grads_out->n_peers);
+    KGE_REQUIRE(grads_out->n_peers > 0 || scal_out, KGE_EINVAL, "scal_out is NULL");
     KGE_REQUIRE(dp->world >= 1 && dp->rank >= 0 && dp->rank < dp->world && dp->i_base >= 0 &&
                     dp->B_global >= dp->i_base + B, KGE_EINVAL, "bad kge_dp (world %d rank %d B_global %lld i_base %lld)",
                 dp->world, dp->rank, (long long) dp->B_global, (long long) dp->i_base);
     KGE_REQUIRE(!mat, KGE_EUNSUPPORTED, "data-parallel steps cover the vector models; SE / TransR / RESCAL are single-GPU");
     KGE_REQUIRE(!grads_out->ent_rows && !grads_out->ent_vals[0] && !grads_out->ent_vals[1], KGE_EUNSUPPORTED,
-                "row-sparse gradient lists are reserved in ABI version 1");
+                "row-sparse gradient lists are reserved");
     int gcols[KGE_MAX_TABLES];
     expected_cols(cfg, gcols);
-    for (int s = 0; s < KGE_MAX_TABLES; ++s)
-      KGE_REQUIRE(!gcols[s] || (grads_out->dense[s] && ((uintptr_t) grads_out->dense[s] & 15) == 0), KGE_EINVAL,
-                  "grads.dense[%d] missing or not 16-byte aligned", s);
+    for (int s = 0; s < KGE_MAX_TABLES; ++s) {
+      if (!gcols[s]) continue;
+      if (grads_out->n_peers == 0)
+        KGE_REQUIRE(grads_out->dense[s] && ((uintptr_t) grads_out->dense[s] & 15) == 0, KGE_EINVAL,
+                    "grads.dense[%d] missing or not 16-byte aligned", s);
+      for (int j = 0; j < grads_out->n_peers; ++j)
+        KGE_REQUIRE(grads_out->peer[j][s] && ((uintptr_t) grads_out->peer[j][s] & 15) == 0 && grads_out->peer_scal[j],
+                    KGE_EINVAL, "grads.peer[%d][%d] / peer_scal missing or not 16-byte aligned", j, s);
+    }
     B_global = dp->B_global;
   }
   const int nv = mat ? pick_nv_strided(cfg) : pick_nv(cfg);
@@ -470,8 +479,17 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   if (is_train) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));     // join the side stream
   if (neg_out)
     KGE_CUDA_OK(cudaMemcpyAsync(neg_out, p.neg_ids, sizeof(int64_t) * (size_t) B * k, cudaMemcpyDeviceToDevice, st));
-  if (grad_only)      // scal[4..8] = norm^2 per slot, loss share
-    KGE_CUDA_OK(cudaMemcpyAsync(scal_out, rp.scal + 4, sizeof(float) * 5, cudaMemcpyDeviceToDevice, st));
+  if (grad_only) {    // scal[4..8] = norm^2 per slot, loss share
+    if (grads_out->n_peers > 0) {
+      ScalSlots ss;
+      ss.n = grads_out->n_peers;
+      for (int j = 0; j < ss.n; ++j) ss.s[j] = grads_out->peer_scal[j];
+      k_push_scal<<<1, 32, 0, st>>>(rp.scal + 4, ss);
+      KGE_CUDA_OK(cudaGetLastError());
+    } else {
+      KGE_CUDA_OK(cudaMemcpyAsync(scal_out, rp.scal + 4, sizeof(float) * 5, cudaMemcpyDeviceToDevice, st));
+    }
+  }
   const bool dense = has_dense_reg(cfg) && !grad_only;    // regularisers are added once, by kge_train_apply
   if (!is_train && !dense) return KGE_OK;
 
@@ -494,7 +512,13 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     U.rec_base = (s < 2) ? 0u : (uint32_t) L.n_ent_rec;
     U.slot = s;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
-    U.gsum = nullptr; U.gout = grad_only ? grads_out->dense[s] : nullptr;
+    U.n_peer = 0;
+    if (grad_only) {
+      if (grads_out->n_peers > 0) {
+        U.n_peer = grads_out->n_peers;
+        for (int j = 0; j < U.n_peer; ++j) U.peer[j] = grads_out->peer[j][s];
+      } else { U.n_peer = 1; U.peer[0] = grads_out->dense[s]; }
+    }
     U.w_in = (shadow_use && s == KGE_T_ENT) ? tables->t[s].wn : tables->t[s].w;
     U.wn_out = (shadow_ok && s == KGE_T_ENT && !dense) ? tables->t[s].wn : nullptr;
     if (dense) {
@@ -660,11 +684,12 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
   if (int rc = check_cfg(cfg)) return rc;
   if (int rc = check_tables(cfg, tables, true)) return rc;
-  KGE_REQUIRE(g && scal_summed && loss_out && ws && B > 0 && adam_t >= 1, KGE_EINVAL, "bad kge_train_apply arguments");
+  KGE_REQUIRE(g && loss_out && ws && B > 0 && adam_t >= 1, KGE_EINVAL, "bad kge_train_apply arguments");
+  KGE_REQUIRE(g->n_peers >= 0 && g->n_peers <= KGE_MAX_PEERS, KGE_EINVAL, "grads.n_peers %d out of range", g->n_peers);
   KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED,
               "data-parallel steps cover the vector models; SE / TransR / RESCAL are single-GPU");
   KGE_REQUIRE(!g->ent_rows && !g->ent_vals[0] && !g->ent_vals[1], KGE_EUNSUPPORTED,
-              "row-sparse gradient lists are reserved in ABI version 1");
+              "row-sparse gradient lists are reserved");
   StepWs L;
   if (int rc = layout_step_ws(cfg, B, L)) return rc;
   KGE_REQUIRE(ws_bytes >= L.total, KGE_EWORKSPACE, "workspace %zu < required %zu bytes", ws_bytes, L.total);
@@ -675,7 +700,12 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   float* scal = reinterpret_cast<float*>(wsb + L.off_scal);
   PhaseTimer pt(ctx, st);
   pt.begin(4);
-  k_dp_scales<<<1, 32, 0, st>>>(scal_summed, cfg->clip_norm, scal, loss_out);
+  ScalSlots ss;
+  if (g->n_peers > 0) {
+    ss.n = g->n_peers;
+    for (int j = 0; j < ss.n; ++j) { KGE_REQUIRE(g->peer_scal[j], KGE_EINVAL, "grads.peer_scal[%d] is NULL", j); ss.s[j] = g->peer_scal[j]; }
+  } else { KGE_REQUIRE(scal_summed, KGE_EINVAL, "scal_summed is NULL"); ss.n = 1; ss.s[0] = scal_summed; }
+  k_dp_scales<<<1, 32, 0, st>>>(ss, cfg->clip_norm, scal, loss_out);
   KGE_CUDA_OK(cudaGetLastError());
 
   const bool dense = has_dense_reg(cfg);
@@ -688,7 +718,6 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   int max_ch = 1;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     if (!cols[s]) continue;
-    KGE_REQUIRE(g->dense[s] && ((uintptr_t) g->dense[s] & 15) == 0, KGE_EINVAL, "grads.dense[%d] missing or not 16-byte aligned", s);
     UpdateTable& U = up.tab[up.n_tabs];
     U.w = tables->t[s].w; U.m = tables->t[s].m; U.v = tables->t[s].v;
     U.rec = nullptr;
@@ -696,7 +725,17 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     U.rec_ld = 0; U.key_base = 0; U.rec_base = 0;
     U.slot = s;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
-    U.gsum = g->dense[s]; U.gout = nullptr;
+    if (g->n_peers > 0) {
+      U.n_peer = g->n_peers;
+      for (int j = 0; j < U.n_peer; ++j) {
+        KGE_REQUIRE(g->peer[j][s] && ((uintptr_t) g->peer[j][s] & 15) == 0, KGE_EINVAL,
+                    "grads.peer[%d][%d] missing or not 16-byte aligned", j, s);
+        U.peer[j] = g->peer[j][s];
+      }
+    } else {
+      KGE_REQUIRE(g->dense[s] && ((uintptr_t) g->dense[s] & 15) == 0, KGE_EINVAL, "grads.dense[%d] missing or not 16-byte aligned", s);
+      U.n_peer = 1; U.peer[0] = g->dense[s];
+    }
     U.w_in = (shadow_ok && tables->wn_valid[KGE_T_ENT] && s == KGE_T_ENT) ? tables->t[s].wn : tables->t[s].w;
     U.wn_out = (shadow_ok && s == KGE_T_ENT && !dense) ? tables->t[s].wn : nullptr;
     if (dense) {            // TransH only (RESCAL is a matrix model)

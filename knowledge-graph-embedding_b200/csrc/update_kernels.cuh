@@ -141,9 +141,28 @@ struct UpdateTable {
   int other_ld;
   const float* w_in;     // where the row's current weights are read: w, or the shadow wn when it is valid
   float* wn_out;         // shadow output: normalise(new row) for the next batch's gathers (or NULL)
-  const float* gsum;     // data-parallel apply: summed gradient [rows x ld] added to the record sum (or NULL)
-  float* gout;           // DENSE=3 (data-parallel grad): where the row's summed gradient goes, [rows x ld]
+  // data-parallel halves, [rows x ld] each:  gradient half (DENSE / MODE 3) stores the row sum to
+  // all n_peer destinations (one local buffer, or every rank's staging slot over NVLink);
+  // apply half adds the n_peer sources to the record sum in index order.
+  float* peer[KGE_MAX_PEERS];
+  int n_peer;
 };
+template <int CPL>
+__device__ __forceinline__ void store_peers(const UpdateTable& T, int64_t row, int nch, int lane, const float4 (&g)[CPL]) {
+  for (int j = 0; j < T.n_peer; ++j) {
+    float4* o = reinterpret_cast<float4*>(T.peer[j] + row * (int64_t) T.ld);
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) o[c] = g[u]; }
+  }
+}
+template <int CPL>
+__device__ __forceinline__ void add_peers(const UpdateTable& T, int64_t row, int nch, int lane, float4 (&g)[CPL]) {
+  for (int j = 0; j < T.n_peer; ++j) {
+    const float4* gs = reinterpret_cast<const float4*>(T.peer[j] + row * (int64_t) T.ld);
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) g[u] += __ldg(gs + c); }
+  }
+}
 struct UpdateParams {
   UpdateTable tab[KGE_MAX_TABLES];
   int n_tabs;
@@ -303,16 +322,10 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
   if (!valid) return;
 
   if (DENSE == 3) {            // gradient only: every row is written (zeros where nothing was looked up)
-    float4* o = reinterpret_cast<float4*>(T.gout + row * (int64_t) T.ld);
-#pragma unroll
-    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) o[c] = g[u]; }
+    store_peers<CPL>(T, row, nch, lane, g);
     return;
   }
-  if (T.gsum != nullptr) {
-    const float4* gs = reinterpret_cast<const float4*>(T.gsum + row * (int64_t) T.ld);
-#pragma unroll
-    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) g[u] += __ldg(gs + c); }
-  }
+  add_peers<CPL>(T, row, nch, lane, g);        // n_peer == 0 outside the data-parallel apply
 
   const float b1 = p.beta1, b2 = p.beta2;
   float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
@@ -432,8 +445,8 @@ __device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTabl
 //   * rows with more than UPD_HEAVY records are left to k_update_heavy (whole-CTA summation),
 //     which runs concurrently on the side stream.
 // Summation order and update arithmetic are those of k_update: results are bit-identical.
-// MODE 0: fused step.  MODE 3: data-parallel gradient half (row sum -> T.gout, tables untouched).
-// MODE 4: data-parallel apply half (gradient = T.gsum row, no records).
+// MODE 0: fused step.  MODE 3: data-parallel gradient half (row sum -> every T.peer destination, tables untouched).
+// MODE 4: data-parallel apply half (gradient = sum of the T.peer rows, no records).
 template <int CPL, int MODE>
 __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
   const int lane = threadIdx.x & 31;
@@ -473,17 +486,8 @@ __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
     sum_chunk<CPL>(mine, n0, T.rec, T.rec_ld, nch, lane, g);
     if (L > 32u) sum_records<CPL>(p.vals, T.rec, T.rec_ld, T.rec_base, (int64_t) lo + 32, (int64_t) lo + L, nch, lane, g);
   }
-  if (MODE == 3) {
-    float4* o = reinterpret_cast<float4*>(T.gout + row * (int64_t) T.ld);
-#pragma unroll
-    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) o[c] = g[u]; }
-    return;
-  }
-  if (MODE == 4) {
-    const float4* gs = reinterpret_cast<const float4*>(T.gsum + row * (int64_t) T.ld);
-#pragma unroll
-    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) g[u] += __ldg(gs + c); }
-  }
+  if (MODE == 3) { store_peers<CPL>(T, row, nch, lane, g); return; }
+  if (MODE == 4) add_peers<CPL>(T, row, nch, lane, g);
   adam_row<CPL>(p, T, row, nch, lane, g);
 }
 
@@ -516,10 +520,9 @@ __global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
   for (int u = 0; u < CPL; ++u) {
     g[u] = f4zero();
     for (int w3 = 0; w3 < 8; ++w3) g[u] += s_part[w3][u * WARP + lane];
-    const int c = lane + 32 * u;
-    if (MODE == 3 && c < nch) reinterpret_cast<float4*>(T.gout + row * (int64_t) T.ld)[c] = g[u];
   }
-  if (MODE != 3) adam_row<CPL>(p, T, row, nch, lane, g);
+  if (MODE == 3) store_peers<CPL>(T, row, nch, lane, g);
+  else adam_row<CPL>(p, T, row, nch, lane, g);
   }
 }
 
@@ -564,14 +567,23 @@ inline int launch_update(const UpdateParams& up, int cpl, int64_t blocks, cudaSt
   return KGE_OK;
 }
 
-// data-parallel apply: clip scales and loss from the rank-summed [norm^2 x4, loss]
-__global__ void k_dp_scales(const float* __restrict__ summed, float clip_norm, float* scal, float* loss_out) {
+// data-parallel apply: clip scales and loss from the [norm^2 x4, loss] blocks — one block already
+// summed over ranks, or every rank's block (summed here in rank order)
+struct ScalSlots { const float* s[KGE_MAX_PEERS]; int n; };
+__global__ void k_dp_scales(const ScalSlots in, float clip_norm, float* scal, float* loss_out) {
   const int t = threadIdx.x;
+  if (t > KGE_MAX_TABLES) return;
+  float a = 0.f;
+  for (int j = 0; j < in.n; ++j) a += in.s[j][t];
   if (t < KGE_MAX_TABLES) {
-    const float n2 = summed[t];
-    scal[4 + t] = n2;
-    scal[t] = clip_norm / fmaxf(sqrtf(n2), clip_norm);
-  } else if (t == KGE_MAX_TABLES) { scal[8] = summed[KGE_MAX_TABLES]; *loss_out = summed[KGE_MAX_TABLES]; }
+    scal[4 + t] = a;
+    scal[t] = clip_norm / fmaxf(sqrtf(a), clip_norm);
+  } else { scal[8] = a; *loss_out = a; }
+}
+// data-parallel gradient half with peer staging: this rank's [norm^2 x4, loss] block to every rank
+__global__ void k_push_scal(const float* __restrict__ src, ScalSlots out) {
+  const int t = threadIdx.x;
+  if (t < 5) for (int j = 0; j < out.n; ++j) const_cast<float*>(out.s[j])[t] = src[t];
 }
 
 // ---- reduction of the dense pass: per-table norm^2 -> clip scale, regulariser -> loss ----

@@ -30,11 +30,18 @@ def main():
     slots = spec.SLOTS["TransE"]
     multi = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)
     single = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)
+    nccl = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)      # same steps over the NCCL all-reduce
     ok = True
     for step in range(5):
         X = np.stack([rng.integers(0, N, B), rng.integers(0, R, B), rng.integers(0, N, B)], 1)
         lo, hi = dp.batch_shard(B)
+        os.environ["KGE_DP_EXCHANGE"] = "peer"
         lm = multi.train_step_dp(X[lo:hi], 11, step, B, lo)
+        os.environ["KGE_DP_EXCHANGE"] = "nccl"
+        ln = nccl.train_step_dp(X[lo:hi], 11, step, B, lo)
+        os.environ.pop("KGE_DP_EXCHANGE")
+        if world == 2:       # a + b in either order: the two exchanges must agree bit for bit
+            ok &= float(lm.item()) == float(ln.item())
         ls = single.train_step(X, 11, step)
         ok &= abs(float(lm.item()) - float(ls.item())) <= 1e-4 * max(1.0, abs(float(ls.item())))
     for s in multi.tab:
@@ -45,6 +52,10 @@ def main():
         gathered = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(gathered, mine)
         ok &= all(torch.equal(gathered[0], t) for t in gathered)            # replicas bit-identical
+        if world == 2:
+            ok &= bool(torch.equal(mine, nccl.tab[s].storage))
+    if rank == 0:
+        print("exchange kinds:", multi._dp_kind, nccl._dp_kind)
     # sharded evaluation: counts over this rank's entity slice, summed == one-GPU counts
     Q = np.stack([rng.integers(0, N, 300), rng.integers(0, R, 300), rng.integers(0, N, 300)], 1)
     posX = np.concatenate([Q, np.stack([rng.integers(0, N, 4000), rng.integers(0, R, 4000), rng.integers(0, N, 4000)], 1)])

@@ -28,6 +28,8 @@ def test_struct_sizes_match_header():
     assert C.sizeof(lib.Table) == 48 and C.sizeof(lib.Tables) == 4 * 48 + 16
     assert C.sizeof(lib.Cfg) == 12 * 4 + 10 * 4 + 2 * 8
     assert C.sizeof(lib.Sampler) == 56 and C.sizeof(lib.Filter) == 16
+    assert C.sizeof(lib.Dp) == 24
+    assert C.sizeof(lib.Grads) == 32 + 8 + 16 + 8 + 4 + 4 + 8 * 4 * 8 + 8 * 8     # kge_grads incl. peer slots
 
 
 def test_no_cpu_fallback():

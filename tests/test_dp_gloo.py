@@ -94,3 +94,29 @@ def test_two_ranks_over_gloo():
     assert r0["g0_sum"] == 17 * 8 * 1 + 16 * 8 * 2
     assert r0["g2"][:2] == [1.0, 2.0]
     assert r0["scal"][0] == 33.0 and r0["scal"][4] == 1.5
+
+
+def test_peer_staging_addresses():
+    """Host logic of the fused exchange: rank r pushes into slot r of every rank's staging, and
+    reads slot j of its own; parities alternate between two disjoint halves."""
+    from KGE._b200 import dp
+    layout = {0: (10, 8), 2: (3, 8)}
+    G = 3
+    bases = [1 << 20, 2 << 20, 3 << 20]
+    ranks = [dp.PeerStaging(layout, G, r, base_ptrs=bases) for r in range(G)]
+    per = ranks[0].per
+    assert per % 64 == 0 and per >= 10 * 8 + 3 * 8 + 8 and ranks[0].numel() == 2 * G * per
+    for par in (0, 1):
+        for r in range(G):
+            P, S = ranks[r].push(par), ranks[r].slots(par)
+            assert P.n_peers == G and S.n_peers == G
+            for j in range(G):
+                # what r pushes to j is what j reads as slot r
+                Sj = ranks[j].slots(par)
+                for s in layout:
+                    assert P.peer[j][s] == Sj.peer[r][s]
+                assert P.peer_scal[j] == Sj.peer_scal[r]
+                assert bases[r] <= S.peer[j][0] < bases[r] + 4 * ranks[r].numel()
+    a0, a1 = ranks[1].slots(0), ranks[1].slots(1)
+    assert a1.peer[0][0] - a0.peer[0][0] == 4 * G * per
+    assert dp.exchange_kind(2) == "peer" and dp.exchange_kind(8) == "nccl" and dp.exchange_kind(1) == "nccl"

@@ -71,3 +71,41 @@ def test_matrix_models_are_refused():
     _, _, eng = make_pair("TransR", N, R, 12, 10, score=O.LpDistancePow(2), loss=O.PairwiseHingeLoss(1.0))
     with pytest.raises(RuntimeError, match="single-GPU"):
         eng.train_grad(eng.grad_buffer(), rand_triples(np.random.default_rng(0), 8, N, R), 1, 0, 8, 0)
+
+
+@pytest.mark.parametrize("G", [2, 3])
+@pytest.mark.parametrize("case", [CASES[0], CASES[1], CASES[3]], ids=["TransE", "DistMult", "TransH"])
+def test_peer_staging_equals_allreduce(case, G):
+    """Fused exchange (kge_grads.peer): every emulated rank's gradient kernels store into all
+    staging buffers, the apply half sums the slots in rank order.  Against the all-reduce
+    emulation (sum of the per-rank buffers in rank order) the weights must be bit-identical —
+    and every rank's staging must hold the same bits."""
+    model, score, loss, k, side, d, constraint = case
+    rng = np.random.default_rng(15)
+    _, _, a = make_pair(model, N, R, d, score=score, loss=loss, k=k, side=side, constraint=constraint)
+    _, _, b = make_pair(model, N, R, d, score=score, loss=loss, k=k, side=side, constraint=constraint)
+    layout = {s: (pt.rows, pt.ld) for s, pt in b.tab.items()}
+    probe = dp.PeerStaging(layout, G, 0)
+    stage = [torch.full((probe.numel(),), 7.0, device=b.device) for _ in range(G)]   # one "rank memory" each
+    ranks = [dp.PeerStaging(layout, G, g, base_ptrs=[t.data_ptr() for t in stage]) for g in range(G)]
+    bufs = [a.grad_buffer() for _ in range(G)]
+    B, seed = 48, 8
+    for step in range(4):
+        X = rand_triples(rng, B, N, R)
+        for g in range(G):
+            lo, hi = dp.split_even(B, G, g)
+            a.train_grad(bufs[g], X[lo:hi], seed, step, B, lo, g, G)
+            b.train_grad(ranks[g].push(step), X[lo:hi], seed, step, B, lo, g, G)
+        acc = torch.zeros_like(bufs[0].flat)
+        for g in range(G):
+            acc += bufs[g].flat
+        bufs[0].flat.copy_(acc)
+        la = a.train_apply(bufs[0], hi - lo)
+        par = step & 1
+        half = G * probe.per
+        for g in range(1, G):                     # all ranks received the same slots
+            assert torch.equal(stage[0][par * half:(par + 1) * half], stage[g][par * half:(par + 1) * half])
+        lb = b.train_apply(ranks[G - 1].slots(step), hi - lo)
+        assert float(la.item()) == float(lb.item())
+        for s in a.tab:
+            assert torch.equal(a.tab[s].storage, b.tab[s].storage), (step, s)
