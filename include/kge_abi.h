@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 3
+#define KGE_ABI_VERSION 4
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -62,6 +62,7 @@ typedef struct kge_table {
   float* v;          /* Adam second moment (NULL for score/rank)   */
   float* wn;         /* optional shadow: the row-normalised table the NEXT batch starts from, same
                         layout as w (see kge_tables.wn_valid); NULL = none                        */
+  uint32_t* last;    /* optional, [rows]: row-lazy replay (see kge_tables.lazy_t); NULL = dense    */
   int64_t rows;
   int32_t cols;      /* logical floats per row                     */
   int32_t ld;        /* row stride in floats, multiple of 4        */
@@ -74,9 +75,24 @@ typedef struct kge_table {
  * sets the flag after a training step that maintained wn; the CALLER clears it whenever it writes
  * w itself (assign / restore / init-time constraint).  Entity table of UM / TransE / DistMult with
  * constraint = True only; ignored elsewhere.  Results are bit-identical with and without wn. */
+/* Row-lazy replay (entity tables much larger than a batch).  The reference
+ * rewrites EVERY row of every table on every batch: the start-of-batch constraint assigns the whole
+ * normalised / clipped table and Keras Adam's sparse apply decays m, v and moves w on all rows
+ * (SURVEY.md App. B.2).  A row without a gradient follows a closed recurrence, so when the entity
+ * tables carry `last` (uint32 per row, zero-initialised together with m and v), kge_train_step
+ * only reads and writes the rows the batch looks up: last[row] = the Adam step the stored
+ * w / m / v of that row belong to, and the skipped steps are replayed in registers, with the
+ * dense kernels' arithmetic, when the row is next looked up.  lazy_t = the Adam step the tables
+ * are logically at (library-maintained like wn_valid; a training call must pass
+ * adam_t == lazy_t + 1).  kge_flush_rows replays every row to lazy_t: afterwards w / m / v are
+ * bit-identical to the dense run.  The caller flushes before it reads w itself, before
+ * kge_score / kge_rank, and before it writes w (then it also sets last[] = lazy_t or resets
+ * both to 0 with m, v).  A validation call (is_train = 0) flushes by itself.  Vector models
+ * without a dense regulariser, single-GPU step only; every used entity slot must carry `last`. */
 typedef struct kge_tables {
   kge_table t[KGE_MAX_TABLES];   /* unused slots: w == NULL */
   int32_t wn_valid[KGE_MAX_TABLES];
+  int64_t lazy_t;
 } kge_tables;
 
 typedef struct kge_cfg {
@@ -217,6 +233,11 @@ int kge_train_apply(kge_ctx*, const kge_cfg*, kge_tables*, const kge_grads* summ
 int kge_rank(kge_ctx*, const kge_cfg*, const kge_tables*, const void* queries, int64_t Q,
              int side, const kge_filter* filter, int64_t ent_lo, int64_t ent_hi,
              int32_t* count_out, void* ws, size_t ws_bytes, void* stream);
+
+/* Materialises the row-lazy tables (kge_tables.lazy_t): every row is replayed to step lazy_t and
+ * last[] = lazy_t.  No-op when no table carries `last`.  One dense pass over the lazy tables
+ * (read + write of w, m, v of the rows that are behind). */
+int kge_flush_rows(kge_ctx*, const kge_cfg*, kge_tables*, void* stream);
 
 /* Implementation switches (testing / A-B measurement; results are identical either way).
  * KGE_OPT_RADIX_SORT: 1 = group the step's gradient records with cub's stable radix sort

@@ -47,6 +47,8 @@ class PaddedTable:
         self.v = None
         self.wn = None            # shadow: normalise(storage) maintained by the training step (kge_tables.wn_valid)
         self.wn_valid = False
+        self.last = None          # row-lazy replay: Adam step of every stored row (kge_tables.lazy_t)
+        self.owner = None         # engine to flush before the table is read from outside the library
 
     def touch(self):
         """Call after writing `storage` / `view` from outside the library: the shadow is stale."""
@@ -54,6 +56,8 @@ class PaddedTable:
 
     @property
     def view(self):
+        if self.last is not None and self.owner is not None:
+            self.owner.flush()
         return self.storage[:, :self.cols].reshape(self.shape)
 
     def ensure_slots(self):
@@ -63,8 +67,10 @@ class PaddedTable:
 
 
 class Engine:
-    def __init__(self, cfg_kwargs, tables, device="cuda:0"):
-        """cfg_kwargs: fields of kge_cfg; tables: {slot: array-like}."""
+    def __init__(self, cfg_kwargs, tables, device="cuda:0", lazy=False):
+        """cfg_kwargs: fields of kge_cfg; tables: {slot: array-like}.  lazy: row-lazy replay of the
+        dense per-batch passes on the entity tables (kge_abi.h, kge_tables.lazy_t) — the training step
+        then touches the looked-up rows only; results are bit-identical to the dense step."""
         self.device = torch.device(device)
         self.ctx = _ctx(self.device.index or 0)
         self.cfg = L.Cfg(abi_version=L.KGE_ABI_VERSION, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-7,
@@ -72,7 +78,15 @@ class Engine:
         for k, v in cfg_kwargs.items():
             setattr(self.cfg, k, v)
         self.tab = {s: PaddedTable(v, self.device) for s, v in tables.items()}
-        if self.cfg.constraint and self.cfg.model in (L.UM, L.TRANSE, L.DISTMULT):
+        self.lazy = bool(lazy)
+        self.lazy_t = 0
+        self._lazy_dirty = False
+        if self.lazy:
+            for s in (L.T_ENT, L.T_ENT_PROJ):
+                if s in self.tab:
+                    self.tab[s].last = torch.zeros(self.tab[s].rows, dtype=torch.int32, device=self.device)
+                    self.tab[s].owner = self
+        elif self.cfg.constraint and self.cfg.model in (L.UM, L.TRANSE, L.DISTMULT):
             self.tab[L.T_ENT].wn = torch.zeros_like(self.tab[L.T_ENT].storage)
         self.sampler = L.Sampler()
         self._sampler_keep = []
@@ -95,14 +109,17 @@ class Engine:
             T = cache[key]
             for s, pt in self.tab.items():
                 T.wn_valid[s] = int(pt.wn_valid)
+            T.lazy_t = self.lazy_t
             return T
         T = L.Tables()
         for s, pt in self.tab.items():
             T.t[s] = L.Table(w=pt.storage.data_ptr(), m=pt.m.data_ptr() if pt.m is not None else None,
                              v=pt.v.data_ptr() if pt.v is not None else None,
                              wn=pt.wn.data_ptr() if pt.wn is not None else None,
+                             last=pt.last.data_ptr() if pt.last is not None else None,
                              rows=pt.rows, cols=pt.cols, ld=pt.ld)
             T.wn_valid[s] = int(pt.wn_valid)
+        T.lazy_t = self.lazy_t
         if len(cache) > 8:
             cache.clear()
         cache[key] = T
@@ -112,6 +129,15 @@ class Engine:
         """The library updates kge_tables.wn_valid; mirror it on the tables."""
         for s, pt in self.tab.items():
             pt.wn_valid = bool(T.wn_valid[s])
+        self.lazy_t = int(T.lazy_t)
+
+    def flush(self):
+        """Row-lazy tables: replay every row to the current step (kge_flush_rows); no-op otherwise."""
+        if not self.lazy or not self._lazy_dirty:
+            return
+        self._lazy_dirty = False
+        T = self._tables(with_opt=True)
+        L.check(L.load().kge_flush_rows(self.ctx, C.byref(self.cfg), C.byref(T), _stream()))
 
     def set_uniform_pool(self, pool=None):
         self.cfg.sampler = L.NS_UNIFORM
@@ -177,7 +203,8 @@ class Engine:
         neg_out = torch.empty(B * self.k_eff(), dtype=torch.int64, device=self.device) if want_negatives else None
         if is_train:
             self.adam_t += 1
-        T = self._tables(with_opt=bool(is_train))
+        T = self._tables(with_opt=bool(is_train) or self.lazy)
+        self._lazy_dirty = bool(is_train)
         L.check(L.load().kge_train_step(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler), _ptr(X), B,
                                         seed, step, max(self.adam_t, 1), _ptr(neg), int(bool(is_train)),
                                         _ptr(loss_out), _ptr(neg_out), _ptr(ws), ws.numel(), _stream()))
@@ -198,7 +225,8 @@ class Engine:
         ws = self._workspace(B, 0)
         if is_train:
             self.adam_t += 1
-        T = self._tables(with_opt=bool(is_train))
+        T = self._tables(with_opt=bool(is_train) or self.lazy)
+        self._lazy_dirty = bool(is_train)
         L.check(L.load().kge_train_step_host(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler),
                                              C.c_void_p(host_triples.data_ptr()), _ptr(st), B, seed, step,
                                              max(self.adam_t, 1), int(bool(is_train)), _ptr(self._stage_loss),
@@ -279,6 +307,7 @@ class Engine:
         return self.train_apply(self._gbuf, len(triples_local), loss_out)
 
     def score(self, h, r, t):
+        self.flush()
         h, r, t = self._ids(h), self._ids(r), self._ids(t)
         out = torch.empty(h.numel(), dtype=torch.float32, device=self.device)
         T = self._tables(False)
@@ -287,11 +316,13 @@ class Engine:
         return out
 
     def constrain_table(self, slot, op):
+        self.flush()
         T = self._tables(False)
         L.check(L.load().kge_constrain_table(self.ctx, C.byref(T), slot, op, _stream()))
         self.tab[slot].touch()
 
     def rank_counts(self, queries, side, f_off=None, f_ids=None, ent_lo=0, ent_hi=None):
+        self.flush()
         Qx = self._ids(queries)
         Q = Qx.shape[0]
         cnt = torch.zeros(Q, dtype=torch.int32, device=self.device)

@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 3
+KGE_ABI_VERSION = 4
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -20,11 +20,12 @@ PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm",
 
 class Table(C.Structure):
     _fields_ = [("w", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("wn", C.c_void_p),
-                ("rows", C.c_int64), ("cols", C.c_int32), ("ld", C.c_int32)]
+                ("last", C.c_void_p), ("rows", C.c_int64), ("cols", C.c_int32), ("ld", C.c_int32)]
 
 
 class Tables(C.Structure):
-    _fields_ = [("t", Table * KGE_MAX_TABLES), ("wn_valid", C.c_int32 * KGE_MAX_TABLES)]
+    _fields_ = [("t", Table * KGE_MAX_TABLES), ("wn_valid", C.c_int32 * KGE_MAX_TABLES),
+                ("lazy_t", C.c_int64)]
 
 
 class Cfg(C.Structure):
@@ -64,7 +65,7 @@ class Grads(C.Structure):
 SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destroy",
            "kge_workspace_bytes", "kge_sample_negatives", "kge_score", "kge_constrain_table",
            "kge_train_step", "kge_train_step_host", "kge_train_grad", "kge_train_apply", "kge_rank", "kge_profile_begin", "kge_profile_end",
-           "kge_set_option"]
+           "kge_set_option", "kge_flush_rows"]
 
 _LIB = None
 
@@ -104,6 +105,7 @@ def load():
                                   C.c_size_t, vp]
     L.kge_rank.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp, i64, i32, C.POINTER(Filter),
                            i64, i64, vp, vp, C.c_size_t, vp]
+    L.kge_flush_rows.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp]
     L.kge_set_option.argtypes = [vp, i32, i32]
     L.kge_profile_begin.argtypes = [vp, i32]
     L.kge_profile_end.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]

@@ -9,12 +9,13 @@
 #include "group_kernels.cuh"
 #include "update_mat_kernels.cuh"
 #include "step_mat_launch.cuh"
+#include "lazy_kernels.cuh"
 
 namespace kge {
 
 struct StepWs {
   size_t off_part, off_scal, off_neg, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub,
-      off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart, off_seg, off_hdr, off_heavy;
+      off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart, off_seg, off_hdr, off_heavy, off_uniq;
   size_t cub_bytes, total, n_seg;
   int64_t n_ent_rec, n_keys, total_rows, n_mat_cta;
   int rld[KGE_MAX_TABLES];
@@ -45,6 +46,7 @@ static bool has_dense_reg(const kge_cfg* c) {
 // constraint is "normalise every entity row" (UM.py:153, TransE.py:171, DistMult.py:162)
 static bool shadow_capable(const kge_ctx_impl* ctx, const kge_cfg* c, const kge_tables* t) {
   return !ctx->opt_no_shadow && !ctx->opt_radix_sort && c->constraint && t->t[KGE_T_ENT].wn != nullptr &&
+         t->t[KGE_T_ENT].last == nullptr &&
          (c->model == KGE_UM || c->model == KGE_TRANSE || c->model == KGE_DISTMULT);
 }
 static int mat_rows(const kge_cfg* c) { return c->d_ent; }
@@ -88,6 +90,7 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   L.off_seg = take(sizeof(uint32_t) * (2 * L.n_seg + 2));   // cnt[K] | off[K+1] | n_heavy   (radix path: seg_lo | seg_hi)
   L.off_hdr = take(sizeof(uint32_t) * 8 * L.n_seg);         // k_canon's per-key headers
   L.off_heavy = take(sizeof(uint32_t) * (size_t) (L.n_keys / UPD_HEAVY + 1));
+  L.off_uniq = take(sizeof(uint32_t) * (4 + 3 * (size_t) L.n_keys));   // row-lazy work list (k_heads)
   size_t scan_bytes = 0;
   if ((int64_t) L.n_seg > SCAN_SMALL_MAX) {
     e = cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (const uint32_t*) nullptr, (uint32_t*) nullptr, (int64_t) L.n_seg,
@@ -125,12 +128,51 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   return KGE_OK;
 }
 
-// constraint jobs of _constraint_loss per model
-static int constraint_jobs(const kge_cfg* c, const kge_tables* t, ConstrainParams& cp) {
+// row-lazy replay (kge_tables.lazy_t): requested by `last` on the entity table
+static bool lazy_requested(const kge_tables* t) { return t->t[KGE_T_ENT].last != nullptr; }
+static int check_lazy(const kge_cfg* c, const kge_tables* t) {
+  KGE_REQUIRE(!is_matrix_model(c->model) && !has_dense_reg(c), KGE_EUNSUPPORTED,
+              "row-lazy tables: vector models without a dense regulariser only");
+  int cols[KGE_MAX_TABLES];
+  expected_cols(c, cols);
+  for (int s = 0; s < 2; ++s)
+    KGE_REQUIRE(!cols[s] || t->t[s].last, KGE_EINVAL, "row-lazy tables: entity slot %d has no `last`", s);
+  KGE_REQUIRE(t->lazy_t >= 0 && t->lazy_t < 0xfffffff0ll, KGE_EINVAL, "lazy_t %lld out of range", (long long) t->lazy_t);
+  return KGE_OK;
+}
+// start-of-batch constraint op of an entity slot (the jobs k_lazy_pre takes over from k_constrain)
+static int lazy_con_op(const kge_cfg* c, int slot) {
+  if (!c->constraint || slot != KGE_T_ENT) return LAZY_CON_NONE;
+  switch (c->model) {
+    case KGE_UM: case KGE_TRANSE: case KGE_DISTMULT: return CON_NORMALIZE;
+    case KGE_TRANSD: return CON_CLIP;
+    default: return LAZY_CON_NONE;
+  }
+}
+static void fill_lazy(const kge_cfg* c, const kge_tables* t, uint32_t step_t, LazyParams& lp) {
+  int cols[KGE_MAX_TABLES];
+  expected_cols(c, cols);
+  lp.n_tabs = 0;
+  for (int s = 0; s < 2; ++s) {
+    if (!cols[s]) continue;
+    LazyTable& T = lp.tab[lp.n_tabs++];
+    T.w = t->t[s].w; T.m = t->t[s].m; T.v = t->t[s].v; T.last = t->t[s].last;
+    T.rec = nullptr; T.rows = t->t[s].rows; T.cols = t->t[s].cols; T.ld = t->t[s].ld; T.rec_ld = 0;
+    T.slot = s; T.con_op = lazy_con_op(c, s);
+  }
+  lp.uniq = nullptr; lp.vals = nullptr; lp.scal = nullptr;
+  lp.lr = c->lr; lp.beta1 = c->beta1; lp.beta2 = c->beta2; lp.eps = c->eps;
+  lp.t = step_t;
+}
+
+// constraint jobs of _constraint_loss per model; skip_ent: the entity slots are
+// row-lazy (k_lazy_pre applies their constraint to the looked-up rows)
+static int constraint_jobs(const kge_cfg* c, const kge_tables* t, ConstrainParams& cp, bool skip_ent = false) {
   cp.n_jobs = 0;
   cp.total_rows = 0;
   if (!c->constraint) return 0;
   auto add = [&](int slot, int op) {
+    if (skip_ent && slot < 2) return;
     ConstrainJob& J = cp.job[cp.n_jobs++];
     J.w = t->t[slot].w; J.rows = t->t[slot].rows; J.cols = t->t[slot].cols; J.ld = t->t[slot].ld; J.op = op;
     cp.total_rows += J.rows;
@@ -261,7 +303,19 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   const bool grad_only = dp != nullptr;
   KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
   if (int rc = check_cfg(cfg)) return rc;
-  if (int rc = check_tables(cfg, tables, is_train != 0 && dp == nullptr)) return rc;
+  if (int rc = check_tables(cfg, tables, (is_train != 0 && dp == nullptr) || (tables && lazy_requested(tables)))) return rc;
+  // row-lazy entity tables: a training call works on the looked-up rows only; a validation call
+  // materialises the tables first and then takes the dense path
+  bool lazy = lazy_requested(tables);
+  const bool flush_first = lazy && !is_train;
+  if (lazy) {
+    if (int rc = check_lazy(cfg, tables)) return rc;
+    KGE_REQUIRE(dp == nullptr, KGE_EUNSUPPORTED, "row-lazy tables: the data-parallel halves are not implemented");
+    KGE_REQUIRE(!is_train || (int64_t) adam_t == tables->lazy_t + 1, KGE_EINVAL,
+                "row-lazy tables: adam_t %llu must be lazy_t + 1 = %lld", (unsigned long long) adam_t,
+                (long long) tables->lazy_t + 1);
+    if (!is_train) lazy = false;
+  }
   if (!neg_override) { if (int rc = check_sampler(cfg, smp)) return rc; }
   KGE_REQUIRE(triples && (loss_out || grad_only) && ws && B > 0, KGE_EINVAL, "triples / loss_out / ws / B invalid");
   KGE_REQUIRE(cfg->loss >= KGE_LOSS_HINGE && cfg->loss <= KGE_LOSS_SQUARE, KGE_EINVAL, "bad loss id %d", cfg->loss);
@@ -311,7 +365,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   //    fork_side() below, once every argument check has passed
   PhaseTimer pt(ctx, st);
   ConstrainParams cp;
-  constraint_jobs(cfg, tables, cp);
+  constraint_jobs(cfg, tables, cp, lazy);
   KGE_REQUIRE(!tables->t[KGE_T_ENT].wn || ((uintptr_t) tables->t[KGE_T_ENT].wn & 15) == 0, KGE_EINVAL, "wn not 16-byte aligned");
   const bool shadow_ok = shadow_capable(ctx, cfg, tables);
   // valid shadow + training call: rows are gathered from wn and the full-table pass is skipped
@@ -369,11 +423,17 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   // the scan itself (first position of key = off[key], one past the last = off[key + 1])
   const uint32_t* use_lo = (ctx->opt_radix_sort != 0) ? seg_lo : seg_lo + L.n_seg;
   const uint32_t* use_hi = (ctx->opt_radix_sort != 0) ? seg_hi : seg_lo + L.n_seg + 1;
+  // row-lazy: segment table of the relation keys only (indexed by key - n_ent), work list for the rest
+  uint32_t* uniq = reinterpret_cast<uint32_t*>(wsb + L.off_uniq);
+  if (lazy) { seg_hi = seg_lo + cfg->n_rel; use_lo = seg_lo; use_hi = seg_hi; }
+  LazyParams lp;
+  if (lazy || flush_first) fill_lazy(cfg, tables, (uint32_t) (flush_first ? tables->lazy_t : (int64_t) adam_t), lp);
   // Host enqueue order: the caller's stream first (fork point, constraint, step kernel), so the
   // GPU starts on the critical path while the host is still enqueueing the side chain.
   auto fork_side = [&]() -> int {
     if (is_train) KGE_CUDA_OK(cudaEventRecord(ctx->ev_fork, st));
     pt.begin(0);
+    if (flush_first) { if (int rc2 = launch_lazy<2>(lp, ctx->sm_count, st)) return rc2; }
     if (int rc2 = launch_constrain(ctx, cp, st)) return rc2;
     pt.end(0);
     return KGE_OK;
@@ -385,6 +445,20 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     pt.begin(3, ax);
     int64_t kb = (L.n_keys + 255) / 256;
     if (kb > (int64_t) ctx->sm_count * 8) kb = (int64_t) ctx->sm_count * 8;
+    if (lazy) {
+      KGE_CUDA_OK(cudaMemsetAsync(seg_lo, 0, sizeof(uint32_t) * 2 * (size_t) cfg->n_rel, ax));
+      KGE_CUDA_OK(cudaMemsetAsync(uniq, 0, sizeof(uint32_t) * 4, ax));
+      k_keys<<<(unsigned) kb, 256, 0, ax>>>(p, nullptr);
+      KGE_CUDA_OK(cudaGetLastError());
+      size_t cub_bytes = L.cub_bytes;
+      KGE_CUDA_OK(cub::DeviceRadixSort::SortPairs(wsb + L.off_cub, cub_bytes, (const uint32_t*) p.keys, keys_out,
+                                                  (const uint32_t*) p.vals, vals_out, (int) L.n_keys, 0, sort_bits(cfg), ax));
+      k_heads<<<(unsigned) ((L.n_keys + 255) / 256), 256, 0, ax>>>(keys_out, L.n_keys, (uint32_t) cfg->n_ent, uniq, seg_lo, seg_hi);
+      KGE_CUDA_OK(cudaGetLastError());
+      pt.end(3, ax);
+      KGE_CUDA_OK(cudaEventRecord(ctx->ev_join, ax));
+      return KGE_OK;
+    }
     KGE_CUDA_OK(cudaMemsetAsync(seg_lo, 0, sizeof(uint32_t) * (2 * L.n_seg + 2), ax));
     if ((ctx->opt_radix_sort != 0)) {
       k_keys<<<(unsigned) kb, 256, 0, ax>>>(p, nullptr);
@@ -436,6 +510,15 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     SL.smem = step_smem_bytes(nv, p.wpp, k, ent_rows, rel_rows);
     KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step needs %zu B shared memory", SL.smem);
     if (int rc2 = fork_side()) return rc2;      // after the last argument check
+    if (lazy) {
+      // the step kernel gathers rows that k_lazy_pre must have replayed: the work list (sort) comes first
+      if (int rc2 = side_chain()) return rc2;
+      KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
+      lp.uniq = uniq; lp.vals = vals_out;
+      pt.begin(0);
+      if (int rc2 = launch_lazy<0>(lp, ctx->sm_count, st)) return rc2;
+      pt.end(0);
+    }
     pt.begin(1);
     switch (cfg->model) {
       case KGE_UM: rc = launch_step_um(p, SL); break;
@@ -466,7 +549,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   }
   if (rc) return rc;
   pt.end(1);
-  if (int rc2 = side_chain()) return rc2;
+  if (!lazy) { if (int rc2 = side_chain()) return rc2; }
 
   // 3. loss + per-table clip scales (sparse-gradient tables)
   const ReduceParams& rp = p.rp;
@@ -503,6 +586,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   rd.row_begin[0] = 0;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     if (!cols[s] || is_matrix_slot(cfg, s)) continue;
+    if (lazy && s < 2) continue;              // k_lazy_update's tables
     UpdateTable& U = up.tab[up.n_tabs];
     U.w = tables->t[s].w; U.m = tables->t[s].m; U.v = tables->t[s].v;
     U.rec = p.rec[s];
@@ -539,12 +623,12 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   up.vals = vals_out;
   up.n_keys = is_train ? L.n_keys : 0;
   up.seg_lo = use_lo; up.seg_hi = use_hi;
+  up.seg_key0 = lazy ? (uint32_t) cfg->n_ent : 0u;
   up.hdr = reinterpret_cast<const uint32_t*>(wsb + L.off_hdr);
   up.heavy_keys = reinterpret_cast<const uint32_t*>(wsb + L.off_heavy);
   up.n_heavy = seg_lo + 2 * L.n_seg + 1;
   up.scal = rp.scal;
-  const float b1p = powf(cfg->beta1, (float) adam_t), b2p = powf(cfg->beta2, (float) adam_t);
-  up.lr_t = cfg->lr * sqrtf(1.0f - b2p) / (1.0f - b1p);
+  up.lr_t = adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t);
   up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
   up.cw = cfg->constraint_weight;
   up.rowpart = dense ? reinterpret_cast<float*>(wsb + L.off_rowpart) : nullptr;
@@ -623,7 +707,21 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     k_update_mat<0><<<mgrid, MU_THREADS, 0, st>>>(mu);
     KGE_CUDA_OK(cudaGetLastError());
   }
-  if (dense) {
+  if (lazy) {
+    // looked-up entity rows on the caller's stream; the small dense tables (relations) beside them
+    KGE_CUDA_OK(cudaEventRecord(ctx->ev_mid, st));
+    if (up.n_tabs > 0) {
+      KGE_CUDA_OK(cudaStreamWaitEvent(ctx->aux, ctx->ev_mid, 0));
+      if (int rc2 = launch_update<0>(up, cpl, ublocks, ctx->aux)) return rc2;
+      KGE_CUDA_OK(cudaEventRecord(ctx->ev_heavy, ctx->aux));
+    }
+    lp.scal = rp.scal;
+    for (int j = 0; j < lp.n_tabs; ++j) { lp.tab[j].rec = p.rec[lp.tab[j].slot]; lp.tab[j].rec_ld = L.rld[lp.tab[j].slot]; }
+    if (int rc2 = launch_lazy<1>(lp, ctx->sm_count, st)) return rc2;
+    if (up.n_tabs > 0) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_heavy, 0));
+    tables->wn_valid[KGE_T_ENT] = 0;
+    tables->lazy_t = (int64_t) adam_t;
+  } else if (dense) {
     if (int rc2 = launch_update<2>(up, cpl, ublocks, st)) return rc2;
     tables->wn_valid[KGE_T_ENT] = 0;
   } else if (ctx->opt_radix_sort) {
@@ -685,6 +783,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   if (int rc = check_cfg(cfg)) return rc;
   if (int rc = check_tables(cfg, tables, true)) return rc;
   KGE_REQUIRE(g && loss_out && ws && B > 0 && adam_t >= 1, KGE_EINVAL, "bad kge_train_apply arguments");
+  KGE_REQUIRE(!lazy_requested(tables), KGE_EUNSUPPORTED, "row-lazy tables: the data-parallel halves are not implemented");
   KGE_REQUIRE(g->n_peers >= 0 && g->n_peers <= KGE_MAX_PEERS, KGE_EINVAL, "grads.n_peers %d out of range", g->n_peers);
   KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED,
               "data-parallel steps cover the vector models; SE / TransR / RESCAL are single-GPU");
@@ -752,11 +851,10 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     rd.row_begin[++up.n_tabs] = up.total_rows;
     max_ch = ((U.cols + 3) / 4 > max_ch) ? (U.cols + 3) / 4 : max_ch;
   }
-  up.keys = nullptr; up.vals = nullptr; up.n_keys = 0; up.seg_lo = nullptr; up.seg_hi = nullptr;
+  up.keys = nullptr; up.vals = nullptr; up.n_keys = 0; up.seg_lo = nullptr; up.seg_hi = nullptr; up.seg_key0 = 0;
   up.hdr = nullptr; up.heavy_keys = nullptr; up.n_heavy = nullptr;
   up.scal = scal;
-  const float b1p = powf(cfg->beta1, (float) adam_t), b2p = powf(cfg->beta2, (float) adam_t);
-  up.lr_t = cfg->lr * sqrtf(1.0f - b2p) / (1.0f - b1p);
+  up.lr_t = adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t);
   up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
   up.cw = cfg->constraint_weight;
   up.rowpart = dense ? reinterpret_cast<float*>(wsb + L.off_rowpart) : nullptr;
@@ -782,4 +880,18 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   tables->wn_valid[KGE_T_ENT] = (shadow_ok && !dense) ? 1 : 0;
   pt.end(4);
   return KGE_OK;
+}
+
+// Materialise the row-lazy tables: every row replayed to tables->lazy_t (kge_abi.h).
+extern "C" int kge_flush_rows(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, void* stream) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
+  if (int rc = check_cfg(cfg)) return rc;
+  KGE_REQUIRE(tables, KGE_EINVAL, "tables is NULL");
+  if (!lazy_requested(tables)) return KGE_OK;
+  if (int rc = check_tables(cfg, tables, true)) return rc;
+  if (int rc = check_lazy(cfg, tables)) return rc;
+  LazyParams lp;
+  fill_lazy(cfg, tables, (uint32_t) tables->lazy_t, lp);
+  return launch_lazy<2>(lp, ctx->sm_count, (cudaStream_t) stream);
 }

@@ -172,6 +172,7 @@ struct UpdateParams {
   int64_t n_keys;
   const uint32_t* seg_lo;  // per key: first sorted position, one past the last (k_segments)
   const uint32_t* seg_hi;
+  uint32_t seg_key0;       // k_update: seg_lo / seg_hi are indexed by key - seg_key0 (row-lazy mode keeps the relation range only)
   const float* scal;
   float lr_t, beta1, beta2, eps;
   float cw;              // constraint_weight
@@ -287,8 +288,8 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
   uint32_t lo = 0, hi = 0;
   if (valid && T.rec != nullptr && p.n_keys > 0) {
     const uint32_t key = T.key_base + (uint32_t) row;
-    lo = __ldg(p.seg_lo + key);
-    hi = __ldg(p.seg_hi + key);
+    lo = __ldg(p.seg_lo + (key - p.seg_key0));
+    hi = __ldg(p.seg_hi + (key - p.seg_key0));
   }
   const int nch = (T.cols + 3) >> 2;
   const bool heavy = (hi - lo) > (uint32_t) UPD_HEAVY;

@@ -6,7 +6,7 @@ from oracle import ref_ops as O, ref_models as RM, ref_step as RS, philox
 
 
 def make_pair(model, N, R, d, d_rel=None, score=None, loss=None, k=2, side="h+t", constraint=True,
-              cw=1.0, seed=7):
+              cw=1.0, seed=7, lazy=False):
     from KGE._b200 import engine as E, spec
     cls = RM.MODELS[model]
     ref = cls(N, R, d, d_rel, score_fn=score, loss_fn=loss, constraint=constraint, constraint_weight=cw)
@@ -21,7 +21,7 @@ def make_pair(model, N, R, d, d_rel=None, score=None, loss=None, k=2, side="h+t"
     cfg = spec.make_cfg(model, N, R, d, d_rel, score_fn=score, loss_fn=loss, negative_ratio=k,
                         corrupt_side=side, constraint=constraint, constraint_weight=cw,
                         rotate_limit=ref.limit)
-    eng = E.Engine(cfg, {spec.SLOTS[model][kk]: v for kk, v in W.data.items()})
+    eng = E.Engine(cfg, {spec.SLOTS[model][kk]: v for kk, v in W.data.items()}, lazy=lazy)
     return ref, W, eng
 
 

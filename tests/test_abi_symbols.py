@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_sizes_match_header():
     from KGE._b200 import lib
-    assert C.sizeof(lib.Table) == 48 and C.sizeof(lib.Tables) == 4 * 48 + 16
+    assert C.sizeof(lib.Table) == 56 and C.sizeof(lib.Tables) == 4 * 56 + 16 + 8
     assert C.sizeof(lib.Cfg) == 12 * 4 + 10 * 4 + 2 * 8
     assert C.sizeof(lib.Sampler) == 56 and C.sizeof(lib.Filter) == 16
     assert C.sizeof(lib.Dp) == 24
