@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 4
+#define KGE_ABI_VERSION 5
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -225,6 +225,55 @@ int kge_train_grad(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, co
 int kge_train_apply(kge_ctx*, const kge_cfg*, kge_tables*, const kge_grads* summed,
                     const float* scal_summed /* [8] device */, int64_t B, uint64_t adam_t,
                     float* loss_out, void* ws, size_t ws_bytes, void* stream);
+
+/* Training step with the ENTITY TABLES SHARDED over the GPUs of one NVLink / NVSwitch node
+ * (configuration C5; the reference is single-device).  Rank g owns entity rows
+ * [g * shard_rows, min(n_ent, (g+1) * shard_rows)): kge_tables slots 0 / 1 of the calls below hold
+ * THIS RANK'S ROWS ONLY (rows = size of the shard) with m, v and `last` (the owner's update is the
+ * row-lazy one, kge_tables.lazy_t); relation tables are replicated.  w of every shard, and the three
+ * inboxes, are mapped into every rank (peer memory: CUDA VMM / torch symmetric memory).  One step,
+ * all ranks in lock-step, B of the step's B_global positives each (kge_dp as for kge_train_grad):
+ *   kge_shard_lookup : negatives on the global Philox counters, unique looked-up rows, their ids
+ *                      stored into the owners' id inboxes over NVLink.
+ *   (caller)           cross-GPU barrier.
+ *   kge_shard_pre    : owner: de-duplicates the ids of all sources, replays the skipped steps of
+ *                      those rows and applies the start-of-batch constraint (w of its shard).
+ *   (caller)           cross-GPU barrier.
+ *   kge_shard_grad   : scores / loss / backward with the rows gathered straight from the owners'
+ *                      memory; one summed gradient row per looked-up row is stored into the owner's
+ *                      value inbox; relation-table gradients go to grads.dense[2..3] and
+ *                      scal_out = [norm^2 x4, loss share] exactly as kge_train_grad does.
+ *   (caller)           all-reduce (sum) of grads.dense[2..3] and scal — also the barrier that
+ *                      makes every rank's inbox stores visible.
+ *   kge_shard_apply  : owner: contributions summed in rank order, global clip, Adam on its rows;
+ *                      every rank: the identical update of the replicated relation tables.
+ * The same workspace must be passed to lookup / grad / apply of one step.  stamp / idx_of / work /
+ * contrib are owner-local scratch, zeroed ONCE by the caller.  Vector models without a dense
+ * regulariser.  With world == 1 the step is bit-identical to kge_train_step on row-lazy tables. */
+typedef struct kge_shard {
+  int32_t world, rank;
+  int64_t shard_rows;
+  int64_t cap;                               /* inbox rows per (owner, source): >= 2 B + B k_eff of any source */
+  const float* w_peer[KGE_MAX_PEERS][2];     /* entity slot s of rank j's shard, as mapped HERE */
+  uint32_t* ids_peer[KGE_MAX_PEERS];         /* rank j's id inbox      uint32[world][cap]       */
+  uint32_t* cnt_peer[KGE_MAX_PEERS];         /* rank j's count inbox   uint32[world]            */
+  float* val_peer[KGE_MAX_PEERS][2];         /* rank j's value inbox of slot s: float[world][cap][ld] */
+  uint32_t* stamp;                           /* [shard_rows]                                    */
+  uint32_t* idx_of;                          /* [shard_rows]                                    */
+  uint32_t* work;                            /* [4 + 3 * min(shard_rows, world * cap)]          */
+  uint32_t* contrib;                         /* [min(shard_rows, world * cap) * world]          */
+} kge_shard;
+int kge_shard_lookup(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const kge_shard*, const kge_dp*,
+                     const void* triples, int64_t B, uint64_t seed, uint64_t step, const int64_t* neg_override,
+                     void* ws, size_t ws_bytes, void* stream);
+int kge_shard_pre(kge_ctx*, const kge_cfg*, kge_tables*, const kge_shard*, uint64_t adam_t, void* stream);
+int kge_shard_grad(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const kge_shard*, const kge_dp*,
+                   const void* triples, int64_t B, uint64_t seed, uint64_t step, const int64_t* neg_override,
+                   kge_grads* out, float* scal_out /* [8] device */, int64_t* neg_out, void* ws, size_t ws_bytes,
+                   void* stream);
+int kge_shard_apply(kge_ctx*, const kge_cfg*, kge_tables*, const kge_shard*, const kge_grads* summed,
+                    const float* scal_summed /* [8] device */, int64_t B, uint64_t adam_t, float* loss_out, void* ws,
+                    size_t ws_bytes, void* stream);
 
 /* Replaces the evaluate()/get_rank() loop (BaseModel.py:602-604, 620-654) for Q
  * queries at once: count_out[q] += #{e in [ent_lo, ent_hi) : score(e) > pos_score(q),

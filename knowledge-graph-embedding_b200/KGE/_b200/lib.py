@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 4
+KGE_ABI_VERSION = 5
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -62,10 +62,18 @@ class Grads(C.Structure):
                 ("peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("peer_scal", C.c_void_p * KGE_MAX_PEERS)]
 
 
+class Shard(C.Structure):
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("shard_rows", C.c_int64), ("cap", C.c_int64),
+                ("w_peer", (C.c_void_p * 2) * KGE_MAX_PEERS), ("ids_peer", C.c_void_p * KGE_MAX_PEERS),
+                ("cnt_peer", C.c_void_p * KGE_MAX_PEERS), ("val_peer", (C.c_void_p * 2) * KGE_MAX_PEERS),
+                ("stamp", C.c_void_p), ("idx_of", C.c_void_p), ("work", C.c_void_p), ("contrib", C.c_void_p)]
+
+
 SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destroy",
            "kge_workspace_bytes", "kge_sample_negatives", "kge_score", "kge_constrain_table",
            "kge_train_step", "kge_train_step_host", "kge_train_grad", "kge_train_apply", "kge_rank", "kge_profile_begin", "kge_profile_end",
-           "kge_set_option", "kge_flush_rows"]
+           "kge_set_option", "kge_flush_rows",
+           "kge_shard_lookup", "kge_shard_pre", "kge_shard_grad", "kge_shard_apply"]
 
 _LIB = None
 
@@ -105,6 +113,13 @@ def load():
                                   C.c_size_t, vp]
     L.kge_rank.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp, i64, i32, C.POINTER(Filter),
                            i64, i64, vp, vp, C.c_size_t, vp]
+    L.kge_shard_lookup.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Shard),
+                                   C.POINTER(Dp), vp, i64, u64, u64, vp, vp, C.c_size_t, vp]
+    L.kge_shard_pre.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Shard), u64, vp]
+    L.kge_shard_grad.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Shard),
+                                 C.POINTER(Dp), vp, i64, u64, u64, vp, C.POINTER(Grads), vp, vp, vp, C.c_size_t, vp]
+    L.kge_shard_apply.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Shard), C.POINTER(Grads), vp, i64,
+                                  u64, vp, vp, C.c_size_t, vp]
     L.kge_flush_rows.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp]
     L.kge_set_option.argtypes = [vp, i32, i32]
     L.kge_profile_begin.argtypes = [vp, i32]

@@ -47,7 +47,7 @@ inline int check_cfg(const kge_cfg* c) {
   return KGE_OK;
 }
 
-inline int check_tables(const kge_cfg* c, const kge_tables* t, bool need_opt) {
+inline int check_tables(const kge_cfg* c, const kge_tables* t, bool need_opt, int64_t ent_rows = -1) {
   KGE_REQUIRE(t != nullptr, KGE_EINVAL, "tables is NULL");
   int cols[KGE_MAX_TABLES];
   expected_cols(c, cols);
@@ -56,7 +56,7 @@ inline int check_tables(const kge_cfg* c, const kge_tables* t, bool need_opt) {
     if (cols[s] == 0) continue;
     KGE_REQUIRE(T.w != nullptr, KGE_EINVAL, "table slot %d: weights missing", s);
     KGE_REQUIRE(T.cols == cols[s], KGE_EINVAL, "table slot %d: cols %d, expected %d", s, T.cols, cols[s]);
-    KGE_REQUIRE(T.rows == (s < 2 ? c->n_ent : c->n_rel), KGE_EINVAL, "table slot %d: rows %lld mismatch", s,
+    KGE_REQUIRE(T.rows == (s < 2 ? (ent_rows >= 0 ? ent_rows : c->n_ent) : c->n_rel), KGE_EINVAL, "table slot %d: rows %lld mismatch", s,
                 (long long) T.rows);
     KGE_REQUIRE(T.ld >= T.cols && T.ld % 4 == 0, KGE_EINVAL, "table slot %d: ld %d must be >= cols and %% 4 == 0", s, T.ld);
     KGE_REQUIRE(((uintptr_t) T.w & 15) == 0, KGE_EINVAL, "table slot %d: base not 16-byte aligned", s);
@@ -82,6 +82,7 @@ inline void fill_model_dev(const kge_cfg* c, const kge_tables* t, ModelDev& md) 
   else if (c->score_p == 1.0f) md.sc.kind = SC_L1;
   else if (c->score_p == 2.0f) md.sc.kind = SC_L2;
   else md.sc.kind = SC_LPGEN;
+  md.shard_rows = 0;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     md.t[s].w = t->t[s].w;
     md.t[s].rows = t->t[s].rows;

@@ -20,7 +20,17 @@ struct ModelDev {
   ScoreDev sc;
   TabDev t[KGE_MAX_TABLES];
   int rld[KGE_MAX_TABLES];   // row stride of the gradient-record buffers (round4(cols))
+  // entity tables sharded over peer GPUs (kge_shard): row id -> owner id / shard_rows, base shard_w[slot][owner]
+  uint32_t shard_rows;       // 0 = not sharded
+  const float* shard_w[2][KGE_MAX_PEERS];
 };
+// base pointer and local row of an entity-table row (slot 0 / 1)
+__device__ __forceinline__ const float* ent_base(const ModelDev& md, int slot, int64_t& id) {
+  if (md.shard_rows == 0) return md.t[slot].w;
+  const uint32_t o = (uint32_t) id / md.shard_rows;
+  id -= (int64_t) o * md.shard_rows;
+  return md.shard_w[slot][o];
+}
 
 // ---- register bundles ------------------------------------------------------------
 template <int NV> struct Ent1 {
@@ -31,7 +41,8 @@ template <int NV> struct Ent1 {
   __device__ __forceinline__ void add(const Ent1& o) { row_add(e, o.e); }
   __device__ __forceinline__ void sumsq(float* n) const { n[KGE_T_ENT] += row_dot_partial(e, e); }
   __device__ __forceinline__ void load(const ModelDev& md, int64_t id, int lane) {
-    load_row(e, md.t[KGE_T_ENT].w, id, md.t[KGE_T_ENT].ld, md.t[KGE_T_ENT].cols, lane);
+    const float* b = ent_base(md, KGE_T_ENT, id);
+    load_row(e, b, id, md.t[KGE_T_ENT].ld, md.t[KGE_T_ENT].cols, lane);
   }
   // store as gradient record `rec` of the entity record buffers
   __device__ __forceinline__ void store(const ModelDev& md, float* const* recs, int64_t rec, int lane) const {
@@ -49,8 +60,11 @@ template <int NV> struct Ent2 {
     n[KGE_T_ENT_PROJ] += row_dot_partial(p, p);
   }
   __device__ __forceinline__ void load(const ModelDev& md, int64_t id, int lane) {
-    load_row(e, md.t[KGE_T_ENT].w, id, md.t[KGE_T_ENT].ld, md.t[KGE_T_ENT].cols, lane);
-    load_row(p, md.t[KGE_T_ENT_PROJ].w, id, md.t[KGE_T_ENT_PROJ].ld, md.t[KGE_T_ENT_PROJ].cols, lane);
+    int64_t id2 = id;
+    const float* b = ent_base(md, KGE_T_ENT, id);
+    const float* b2 = ent_base(md, KGE_T_ENT_PROJ, id2);
+    load_row(e, b, id, md.t[KGE_T_ENT].ld, md.t[KGE_T_ENT].cols, lane);
+    load_row(p, b2, id2, md.t[KGE_T_ENT_PROJ].ld, md.t[KGE_T_ENT_PROJ].cols, lane);
   }
   __device__ __forceinline__ void store(const ModelDev& md, float* const* recs, int64_t rec, int lane) const {
     store_row(e, recs[KGE_T_ENT], rec, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);

@@ -10,12 +10,14 @@
 #include "update_mat_kernels.cuh"
 #include "step_mat_launch.cuh"
 #include "lazy_kernels.cuh"
+#include "shard_kernels.cuh"
 
 namespace kge {
 
 struct StepWs {
   size_t off_part, off_scal, off_neg, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub,
-      off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart, off_seg, off_hdr, off_heavy, off_uniq;
+      off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart, off_seg, off_hdr, off_heavy, off_uniq,
+      off_islot;
   size_t cub_bytes, total, n_seg;
   int64_t n_ent_rec, n_keys, total_rows, n_mat_cta;
   int rld[KGE_MAX_TABLES];
@@ -91,6 +93,7 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   L.off_hdr = take(sizeof(uint32_t) * 8 * L.n_seg);         // k_canon's per-key headers
   L.off_heavy = take(sizeof(uint32_t) * (size_t) (L.n_keys / UPD_HEAVY + 1));
   L.off_uniq = take(sizeof(uint32_t) * (4 + 3 * (size_t) L.n_keys));   // row-lazy work list (k_heads)
+  L.off_islot = take(sizeof(uint32_t) * ((size_t) L.n_keys + 16));      // sharded step: inbox slot per work item | per-owner counters
   size_t scan_bytes = 0;
   if ((int64_t) L.n_seg > SCAN_SMALL_MAX) {
     e = cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (const uint32_t*) nullptr, (uint32_t*) nullptr, (int64_t) L.n_seg,
@@ -163,6 +166,43 @@ static void fill_lazy(const kge_cfg* c, const kge_tables* t, uint32_t step_t, La
   lp.uniq = nullptr; lp.vals = nullptr; lp.scal = nullptr;
   lp.lr = c->lr; lp.beta1 = c->beta1; lp.beta2 = c->beta2; lp.eps = c->eps;
   lp.t = step_t;
+}
+
+// ---- sharded entity tables (kge_shard) ---------------------------------------------------------
+static int64_t shard_local_rows(const kge_cfg* c, const kge_shard* sh) {
+  const int64_t lo = (int64_t) sh->rank * sh->shard_rows;
+  int64_t hi = lo + sh->shard_rows;
+  if (hi > c->n_ent) hi = c->n_ent;
+  return hi > lo ? hi - lo : 0;
+}
+static int check_shard(const kge_cfg* c, const kge_tables* t, const kge_shard* sh, int64_t B) {
+  KGE_REQUIRE(sh, KGE_EINVAL, "shard is NULL");
+  KGE_REQUIRE(sh->world >= 1 && sh->world <= KGE_MAX_PEERS && sh->rank >= 0 && sh->rank < sh->world, KGE_EINVAL,
+              "bad kge_shard (world %d rank %d)", sh->world, sh->rank);
+  KGE_REQUIRE(sh->shard_rows > 0 && sh->shard_rows < 0xffffffffll && sh->shard_rows * sh->world >= c->n_ent, KGE_EINVAL,
+              "shard_rows %lld x world %d does not cover n_ent %lld", (long long) sh->shard_rows, sh->world, (long long) c->n_ent);
+  KGE_REQUIRE(sh->cap > 0 && sh->cap < 0xffffffffll && (B <= 0 || sh->cap >= 2 * B + B * (int64_t) k_eff_of(c)), KGE_EINVAL,
+              "shard.cap %lld < looked-up rows of a batch of %lld", (long long) sh->cap, (long long) B);
+  int cols[KGE_MAX_TABLES];
+  expected_cols(c, cols);
+  for (int j = 0; j < sh->world; ++j) {
+    KGE_REQUIRE(sh->ids_peer[j] && sh->cnt_peer[j], KGE_EINVAL, "shard inbox pointers of rank %d missing", j);
+    for (int s2 = 0; s2 < 2; ++s2)
+      if (cols[s2]) KGE_REQUIRE(sh->w_peer[j][s2] && sh->val_peer[j][s2] && (((uintptr_t) sh->w_peer[j][s2] | (uintptr_t) sh->val_peer[j][s2]) & 15) == 0,
+                                KGE_EINVAL, "shard.w_peer / val_peer [%d][%d] missing or not 16-byte aligned", j, s2);
+  }
+  KGE_REQUIRE(sh->stamp && sh->idx_of && sh->work && sh->contrib, KGE_EINVAL, "shard owner scratch missing");
+  for (int s2 = 0; s2 < 2; ++s2)
+    if (cols[s2]) KGE_REQUIRE(t->t[s2].w == sh->w_peer[sh->rank][s2], KGE_EINVAL, "tables slot %d is not this rank's shard", s2);
+  return KGE_OK;
+}
+static void fill_shard_dev(const kge_shard* sh, ShardDev& sd) {
+  sd.world = sh->world; sd.rank = sh->rank; sd.S = (uint32_t) sh->shard_rows; sd.cap = (uint32_t) sh->cap;
+  for (int j = 0; j < KGE_MAX_PEERS; ++j) {
+    sd.ids_peer[j] = sh->ids_peer[j]; sd.cnt_peer[j] = sh->cnt_peer[j];
+    sd.val_peer[j][0] = sh->val_peer[j][0]; sd.val_peer[j][1] = sh->val_peer[j][1];
+  }
+  sd.stamp = sh->stamp; sd.idx_of = sh->idx_of; sd.work = sh->work; sd.contrib = sh->contrib;
 }
 
 // constraint jobs of _constraint_loss per model; skip_ent: the entity slots are
@@ -297,25 +337,29 @@ extern "C" int kge_workspace_bytes(const kge_cfg* cfg, int64_t B, int64_t Q, siz
 static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
                       const kge_dp* dp, const void* triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
                       const int64_t* neg_override, int is_train, kge_grads* grads_out, float* scal_out,
-                      float* loss_out, int64_t* neg_out, void* ws, size_t ws_bytes, void* stream) {
+                      float* loss_out, int64_t* neg_out, void* ws, size_t ws_bytes, void* stream,
+                      const kge_shard* sh = nullptr, int shard_phase = 0 /* 1 lookup, 2 grad */) {
   auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
   cudaStream_t st = (cudaStream_t) stream;
   const bool grad_only = dp != nullptr;
   KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
   if (int rc = check_cfg(cfg)) return rc;
-  if (int rc = check_tables(cfg, tables, (is_train != 0 && dp == nullptr) || (tables && lazy_requested(tables)))) return rc;
+  if (sh) { if (int rc = check_shard(cfg, tables, sh, B)) return rc; }
+  if (int rc = check_tables(cfg, tables, (is_train != 0 && dp == nullptr) || (tables && lazy_requested(tables)),
+                            sh ? shard_local_rows(cfg, sh) : -1)) return rc;
   // row-lazy entity tables: a training call works on the looked-up rows only; a validation call
   // materialises the tables first and then takes the dense path
   bool lazy = lazy_requested(tables);
   const bool flush_first = lazy && !is_train;
   if (lazy) {
     if (int rc = check_lazy(cfg, tables)) return rc;
-    KGE_REQUIRE(dp == nullptr, KGE_EUNSUPPORTED, "row-lazy tables: the data-parallel halves are not implemented");
-    KGE_REQUIRE(!is_train || (int64_t) adam_t == tables->lazy_t + 1, KGE_EINVAL,
+    KGE_REQUIRE(dp == nullptr || sh, KGE_EUNSUPPORTED, "row-lazy tables: the data-parallel halves are not implemented");
+    KGE_REQUIRE(!is_train || sh || (int64_t) adam_t == tables->lazy_t + 1, KGE_EINVAL,
                 "row-lazy tables: adam_t %llu must be lazy_t + 1 = %lld", (unsigned long long) adam_t,
                 (long long) tables->lazy_t + 1);
     if (!is_train) lazy = false;
   }
+  KGE_REQUIRE(!sh || (lazy && dp), KGE_EINVAL, "sharded step: entity slots need `last`, and kge_dp must be given");
   if (!neg_override) { if (int rc = check_sampler(cfg, smp)) return rc; }
   KGE_REQUIRE(triples && (loss_out || grad_only) && ws && B > 0, KGE_EINVAL, "triples / loss_out / ws / B invalid");
   KGE_REQUIRE(cfg->loss >= KGE_LOSS_HINGE && cfg->loss <= KGE_LOSS_SQUARE, KGE_EINVAL, "bad loss id %d", cfg->loss);
@@ -327,10 +371,13 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   const bool mat = is_matrix_model(cfg->model);
   int64_t B_global = B;
   if (grad_only) {
+    static kge_grads no_grads = {};
+    if (sh && shard_phase == 1) grads_out = &no_grads;
     KGE_REQUIRE(grads_out, KGE_EINVAL, "grads is NULL");
+    KGE_REQUIRE(!sh || grads_out->n_peers == 0, KGE_EUNSUPPORTED, "sharded step: relation gradients use grads.dense");
     KGE_REQUIRE(grads_out->n_peers >= 0 && grads_out->n_peers <= KGE_MAX_PEERS, KGE_EINVAL, "grads.n_peers %d out of range",
                 grads_out->n_peers);
-    KGE_REQUIRE(grads_out->n_peers > 0 || scal_out, KGE_EINVAL, "scal_out is NULL");
+    KGE_REQUIRE(grads_out->n_peers > 0 || scal_out || shard_phase == 1, KGE_EINVAL, "scal_out is NULL");
     KGE_REQUIRE(dp->world >= 1 && dp->rank >= 0 && dp->rank < dp->world && dp->i_base >= 0 &&
                     dp->B_global >= dp->i_base + B, KGE_EINVAL, "bad kge_dp (world %d rank %d B_global %lld i_base %lld)",
                 dp->world, dp->rank, (long long) dp->B_global, (long long) dp->i_base);
@@ -341,6 +388,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     expected_cols(cfg, gcols);
     for (int s = 0; s < KGE_MAX_TABLES; ++s) {
       if (!gcols[s]) continue;
+      if (sh && (s < 2 || shard_phase == 1)) continue;
       if (grads_out->n_peers == 0)
         KGE_REQUIRE(grads_out->dense[s] && ((uintptr_t) grads_out->dense[s] & 15) == 0, KGE_EINVAL,
                     "grads.dense[%d] missing or not 16-byte aligned", s);
@@ -380,6 +428,17 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   MatStepParams mq;
   StepParams& p = mq.s;
   fill_model_dev(cfg, tables, p.md);
+  ShardDev sdv;
+  if (sh) {
+    fill_shard_dev(sh, sdv);
+    p.md.shard_rows = (uint32_t) sh->shard_rows;
+    for (int s2 = 0; s2 < 2; ++s2) {
+      p.md.t[s2].rows = cfg->n_ent;                       // key space and ids stay global
+      for (int j = 0; j < KGE_MAX_PEERS; ++j) p.md.shard_w[s2][j] = sh->w_peer[j][s2];
+    }
+  }
+  uint32_t* item_slot = reinterpret_cast<uint32_t*>(wsb + L.off_islot);
+  uint32_t* rcnt = item_slot + L.n_keys;
   if (shadow_use) p.md.t[KGE_T_ENT].w = tables->t[KGE_T_ENT].wn;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     p.md.rld[s] = L.rld[s];
@@ -434,6 +493,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     if (is_train) KGE_CUDA_OK(cudaEventRecord(ctx->ev_fork, st));
     pt.begin(0);
     if (flush_first) { if (int rc2 = launch_lazy<2>(lp, ctx->sm_count, st)) return rc2; }
+    if (shard_phase == 1) return KGE_OK;                  // lookup: ids only, no table is touched
     if (int rc2 = launch_constrain(ctx, cp, st)) return rc2;
     pt.end(0);
     return KGE_OK;
@@ -509,12 +569,21 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     SL.grid = (B + ppc - 1) / ppc;
     SL.smem = step_smem_bytes(nv, p.wpp, k, ent_rows, rel_rows);
     KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step needs %zu B shared memory", SL.smem);
-    if (int rc2 = fork_side()) return rc2;      // after the last argument check
-    if (lazy) {
+    if (shard_phase != 2) { if (int rc2 = fork_side()) return rc2; }      // after the last argument check
+    else { pt.begin(0); if (int rc2 = launch_constrain(ctx, cp, st)) return rc2; pt.end(0); }
+    lp.uniq = uniq; lp.vals = vals_out;
+    if (lazy && shard_phase != 2) {
       // the step kernel gathers rows that k_lazy_pre must have replayed: the work list (sort) comes first
       if (int rc2 = side_chain()) return rc2;
       KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
-      lp.uniq = uniq; lp.vals = vals_out;
+      if (shard_phase == 1) {                   // route the ids to their owners; the owners replay (kge_shard_pre)
+        KGE_CUDA_OK(cudaMemsetAsync(rcnt, 0, sizeof(uint32_t) * 16, st));
+        k_route<<<(unsigned) ctx->sm_count * 4, 256, 0, st>>>(uniq, sdv, rcnt, item_slot);
+        KGE_CUDA_OK(cudaGetLastError());
+        k_route_cnt<<<1, 32, 0, st>>>(sdv, rcnt);
+        KGE_CUDA_OK(cudaGetLastError());
+        return KGE_OK;
+      }
       pt.begin(0);
       if (int rc2 = launch_lazy<0>(lp, ctx->sm_count, st)) return rc2;
       pt.end(0);
@@ -559,7 +628,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     KGE_CUDA_OK(cudaGetLastError());
     pt.end(2);
   }
-  if (is_train) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));     // join the side stream
+  if (is_train && shard_phase != 2) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));     // join the side stream
   if (neg_out)
     KGE_CUDA_OK(cudaMemcpyAsync(neg_out, p.neg_ids, sizeof(int64_t) * (size_t) B * k, cudaMemcpyDeviceToDevice, st));
   if (grad_only) {    // scal[4..8] = norm^2 per slot, loss share
@@ -668,7 +737,11 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
 
   pt.begin(4);
   if (grad_only) {
-    if (ctx->opt_radix_sort) {
+    if (sh) {           // relation tables -> grads.dense (general kernel on k_heads' segment table); entity rows -> owners
+      if (up.n_tabs > 0) { if (int rc2 = launch_update<3>(up, cpl, ublocks, st)) return rc2; }
+      for (int j = 0; j < lp.n_tabs; ++j) { lp.tab[j].rec = p.rec[lp.tab[j].slot]; lp.tab[j].rec_ld = L.rld[lp.tab[j].slot]; }
+      if (int rc2 = launch_shard_rows<0>(lp, sdv, item_slot, ctx->sm_count, st)) return rc2;
+    } else if (ctx->opt_radix_sort) {
       if (int rc2 = launch_update<3>(up, cpl, ublocks, st)) return rc2;
     } else {
       KGE_CUDA_OK(cudaEventRecord(ctx->ev_mid, st));
@@ -889,9 +962,121 @@ extern "C" int kge_flush_rows(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tab
   if (int rc = check_cfg(cfg)) return rc;
   KGE_REQUIRE(tables, KGE_EINVAL, "tables is NULL");
   if (!lazy_requested(tables)) return KGE_OK;
-  if (int rc = check_tables(cfg, tables, true)) return rc;
+  if (int rc = check_tables(cfg, tables, true, tables->t[KGE_T_ENT].rows)) return rc;   // a shard holds its own rows only
   if (int rc = check_lazy(cfg, tables)) return rc;
   LazyParams lp;
   fill_lazy(cfg, tables, (uint32_t) tables->lazy_t, lp);
   return launch_lazy<2>(lp, ctx->sm_count, (cudaStream_t) stream);
+}
+
+// ---- sharded entity tables: the four calls of one step (kge_abi.h, shard_kernels.cuh) ---------
+extern "C" int kge_shard_lookup(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                                const kge_shard* sh, const kge_dp* dp, const void* triples, int64_t B, uint64_t seed,
+                                uint64_t step, const int64_t* neg_override, void* ws, size_t ws_bytes, void* stream) {
+  KGE_REQUIRE(sh && dp, KGE_EINVAL, "shard / dp is NULL");
+  return train_impl(ctx, cfg, tables, smp, dp, triples, B, seed, step, 1, neg_override, 1, nullptr, nullptr, nullptr,
+                    nullptr, ws, ws_bytes, stream, sh, 1);
+}
+
+extern "C" int kge_shard_pre(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, const kge_shard* sh, uint64_t adam_t,
+                             void* stream) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  cudaStream_t st = (cudaStream_t) stream;
+  KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
+  if (int rc = check_cfg(cfg)) return rc;
+  KGE_REQUIRE(tables && lazy_requested(tables), KGE_EINVAL, "sharded step: entity slots need `last`");
+  if (int rc = check_shard(cfg, tables, sh, 0)) return rc;
+  if (int rc = check_tables(cfg, tables, true, shard_local_rows(cfg, sh))) return rc;
+  if (int rc = check_lazy(cfg, tables)) return rc;
+  KGE_REQUIRE((int64_t) adam_t == tables->lazy_t + 1, KGE_EINVAL, "sharded step: adam_t %llu must be lazy_t + 1 = %lld",
+              (unsigned long long) adam_t, (long long) tables->lazy_t + 1);
+  ShardDev sdv;
+  fill_shard_dev(sh, sdv);
+  KGE_CUDA_OK(cudaMemsetAsync(sh->work, 0, sizeof(uint32_t) * 4, st));
+  int64_t cb = (sh->cap + 255) / 256;
+  if (cb > (int64_t) ctx->sm_count * 2) cb = (int64_t) ctx->sm_count * 2;
+  const dim3 grid((unsigned) cb, (unsigned) sh->world, 1);
+  k_claim<<<grid, 256, 0, st>>>(sdv, (uint32_t) adam_t);
+  KGE_CUDA_OK(cudaGetLastError());
+  k_contrib<<<grid, 256, 0, st>>>(sdv);
+  KGE_CUDA_OK(cudaGetLastError());
+  LazyParams lp;
+  fill_lazy(cfg, tables, (uint32_t) adam_t, lp);
+  lp.uniq = sh->work;
+  return launch_lazy<0>(lp, ctx->sm_count, st);
+}
+
+extern "C" int kge_shard_grad(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                              const kge_shard* sh, const kge_dp* dp, const void* triples, int64_t B, uint64_t seed,
+                              uint64_t step, const int64_t* neg_override, kge_grads* out, float* scal_out,
+                              int64_t* neg_out, void* ws, size_t ws_bytes, void* stream) {
+  KGE_REQUIRE(sh && dp && out && scal_out, KGE_EINVAL, "shard / dp / grads / scal_out is NULL");
+  return train_impl(ctx, cfg, tables, smp, dp, triples, B, seed, step, 1, neg_override, 1, out, scal_out, nullptr,
+                    neg_out, ws, ws_bytes, stream, sh, 2);
+}
+
+extern "C" int kge_shard_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, const kge_shard* sh,
+                               const kge_grads* g, const float* scal_summed, int64_t B, uint64_t adam_t,
+                               float* loss_out, void* ws, size_t ws_bytes, void* stream) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  cudaStream_t st = (cudaStream_t) stream;
+  KGE_REQUIRE(ctx, KGE_EINVAL, "ctx is NULL");
+  if (int rc = check_cfg(cfg)) return rc;
+  KGE_REQUIRE(tables && lazy_requested(tables), KGE_EINVAL, "sharded step: entity slots need `last`");
+  if (int rc = check_shard(cfg, tables, sh, B)) return rc;
+  if (int rc = check_tables(cfg, tables, true, shard_local_rows(cfg, sh))) return rc;
+  if (int rc = check_lazy(cfg, tables)) return rc;
+  KGE_REQUIRE(g && scal_summed && loss_out && ws && B > 0, KGE_EINVAL, "bad kge_shard_apply arguments");
+  KGE_REQUIRE((int64_t) adam_t == tables->lazy_t + 1, KGE_EINVAL, "sharded step: adam_t %llu must be lazy_t + 1 = %lld",
+              (unsigned long long) adam_t, (long long) tables->lazy_t + 1);
+  StepWs L;
+  if (int rc = layout_step_ws(cfg, B, L)) return rc;
+  KGE_REQUIRE(ws_bytes >= L.total, KGE_EWORKSPACE, "workspace %zu < required %zu bytes", ws_bytes, L.total);
+  KGE_REQUIRE(((uintptr_t) ws & 255) == 0, KGE_EINVAL, "workspace must be 256-byte aligned");
+  char* wsb = reinterpret_cast<char*>(ws);
+  int cols[KGE_MAX_TABLES];
+  expected_cols(cfg, cols);
+  float* scal = reinterpret_cast<float*>(wsb + L.off_scal);
+  PhaseTimer pt(ctx, st);
+  pt.begin(4);
+  ScalSlots ss;
+  ss.n = 1; ss.s[0] = scal_summed;
+  k_dp_scales<<<1, 32, 0, st>>>(ss, cfg->clip_norm, scal, loss_out);
+  KGE_CUDA_OK(cudaGetLastError());
+  // replicated relation tables: the data-parallel streaming apply
+  UpdateParams up;
+  up.n_tabs = 0; up.total_rows = 0;
+  int max_ch = 1;
+  for (int s = 2; s < KGE_MAX_TABLES; ++s) {
+    if (!cols[s]) continue;
+    KGE_REQUIRE(g->dense[s] && ((uintptr_t) g->dense[s] & 15) == 0, KGE_EINVAL, "grads.dense[%d] missing or not 16-byte aligned", s);
+    UpdateTable& U = up.tab[up.n_tabs++];
+    U.w = tables->t[s].w; U.m = tables->t[s].m; U.v = tables->t[s].v;
+    U.rec = nullptr; U.rows = tables->t[s].rows; U.cols = tables->t[s].cols; U.ld = tables->t[s].ld;
+    U.rec_ld = 0; U.key_base = 0; U.rec_base = 0; U.slot = s;
+    U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
+    U.n_peer = 1; U.peer[0] = g->dense[s];
+    U.w_in = tables->t[s].w; U.wn_out = nullptr;
+    up.total_rows += U.rows;
+    max_ch = ((U.cols + 3) / 4 > max_ch) ? (U.cols + 3) / 4 : max_ch;
+  }
+  up.keys = nullptr; up.vals = nullptr; up.n_keys = 0; up.seg_lo = nullptr; up.seg_hi = nullptr; up.seg_key0 = 0;
+  up.hdr = nullptr; up.heavy_keys = nullptr; up.n_heavy = nullptr;
+  up.scal = scal;
+  up.lr_t = adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t);
+  up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
+  up.cw = cfg->constraint_weight; up.rowpart = nullptr;
+  const int cpl = max_ch <= 32 ? 1 : (max_ch <= 64 ? 2 : (max_ch <= 128 ? 4 : 8));
+  if (up.n_tabs > 0) { if (int rc = launch_update_fast<4>(up, cpl, st)) return rc; }
+  // this rank's entity rows
+  ShardDev sdv;
+  fill_shard_dev(sh, sdv);
+  LazyParams lp;
+  fill_lazy(cfg, tables, (uint32_t) adam_t, lp);
+  lp.uniq = sh->work; lp.scal = scal;
+  if (int rc = launch_shard_rows<1>(lp, sdv, nullptr, ctx->sm_count, st)) return rc;
+  tables->wn_valid[KGE_T_ENT] = 0;
+  tables->lazy_t = (int64_t) adam_t;
+  pt.end(4);
+  return KGE_OK;
 }
