@@ -125,34 +125,70 @@ __device__ __forceinline__ bool con_row(float4 (&w)[CPL], int op, int nch, int l
   for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) w[u] = div4(w[u], den); }
   return den != 1.0f;
 }
-// Adam step j with a zero gradient on the whole row
+// Adam step j with a zero gradient: adam1() with g = +0 reduced to the operations that can change
+// a bit.  m <- b1 m + (1 - b1) 0 keeps its "+ 0" (it turns a -0 product into +0, as the dense kernel
+// does); v >= 0, so b2 v + 0 == b2 v.  Padding elements stay zero (0 / (0 + eps)).
+__device__ __forceinline__ void idle1(float& w, float& m, float& v, float b1, float b2, float lr_j, float eps) {
+  m = __fadd_rn(__fmul_rn(b1, m), 0.f);
+  v = __fmul_rn(b2, v);
+  w = __fsub_rn(w, __fdiv_rn(__fmul_rn(lr_j, m), __fadd_rn(sqrtf(v), eps)));
+}
 template <int CPL>
-__device__ __forceinline__ void adam_idle(float4 (&w)[CPL], float4 (&m)[CPL], float4 (&v)[CPL], int nch, int lane, int cols,
-                                          float b1, float b2, float lr_j, float eps) {
+__device__ __forceinline__ void adam_idle(float4 (&w)[CPL], float4 (&m)[CPL], float4 (&v)[CPL], float b1, float b2,
+                                          float lr_j, float eps) {
 #pragma unroll
   for (int u = 0; u < CPL; ++u) {
-    const int c = lane + 32 * u;
-    if (c >= nch) continue;
-    adam_chunk(w[u], m[u], v[u], f4zero(), b1, b2, lr_j, eps);
-    mask_tail(w[u], m[u], v[u], c, cols);
+    idle1(w[u].x, m[u].x, v[u].x, b1, b2, lr_j, eps);
+    idle1(w[u].y, m[u].y, v[u].y, b1, b2, lr_j, eps);
+    idle1(w[u].z, m[u].z, v[u].z, b1, b2, lr_j, eps);
+    idle1(w[u].w, m[u].w, v[u].w, b1, b2, lr_j, eps);
   }
+}
+// m, v of `n` zero-gradient steps (w is replayed elsewhere)
+template <int CPL>
+__device__ __forceinline__ void decay_mv(float4 (&m)[CPL], float4 (&v)[CPL], uint32_t n, float b1, float b2) {
+  for (uint32_t j = 0; j < n; ++j) {
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) {
+      m[u] = f4(__fadd_rn(__fmul_rn(b1, m[u].x), 0.f), __fadd_rn(__fmul_rn(b1, m[u].y), 0.f),
+                __fadd_rn(__fmul_rn(b1, m[u].z), 0.f), __fadd_rn(__fmul_rn(b1, m[u].w), 0.f));
+      v[u] = f4(__fmul_rn(b2, v[u].x), __fmul_rn(b2, v[u].y), __fmul_rn(b2, v[u].z), __fmul_rn(b2, v[u].w));
+    }
+  }
+}
+// lr_j of the most recent steps, one table per CTA (adam_lr is ~100 double-precision instructions)
+constexpr int LR_TAB = 256;
+__device__ __forceinline__ void fill_lr_tab(float* s_lr, const LazyParams& p) {
+  for (int i = threadIdx.x; i < LR_TAB; i += blockDim.x) s_lr[i] = (p.t > (uint32_t) i) ? adam_lr(p.lr, p.beta1, p.beta2, p.t - i) : 0.f;
+  __syncthreads();
+}
+__device__ __forceinline__ float lr_of(const float* s_lr, const LazyParams& p, uint32_t j) {
+  const uint32_t back = p.t - j;                       // j <= p.t
+  return back < (uint32_t) LR_TAB ? s_lr[back] : adam_lr(p.lr, p.beta1, p.beta2, j);
 }
 // steps (s, t_end] of an idle row: constraint then zero-gradient Adam, each step.  A row whose m and
 // v are all zero (never touched) is not moved by Adam, and once the constraint leaves it unchanged
 // it is a fixed point: the loop stops early.
 template <int CPL>
-__device__ __forceinline__ void replay_row(const LazyParams& p, const LazyTable& T, float4 (&w)[CPL], float4 (&m)[CPL],
-                                           float4 (&v)[CPL], bool fresh, uint32_t s, uint32_t t_end, int nch, int lane) {
+__device__ __forceinline__ void replay_row(const LazyParams& p, const LazyTable& T, const float* s_lr, float4 (&w)[CPL],
+                                           float4 (&m)[CPL], float4 (&v)[CPL], bool fresh, uint32_t s, uint32_t t_end,
+                                           int nch, int lane) {
   for (uint32_t j = s + 1; j <= t_end; ++j) {
     const bool moved = con_row<CPL>(w, T.con_op, nch, lane);
     if (fresh) { if (!moved) break; continue; }
-    adam_idle<CPL>(w, m, v, nch, lane, T.cols, p.beta1, p.beta2, adam_lr(p.lr, p.beta1, p.beta2, j), p.eps);
+    adam_idle<CPL>(w, m, v, p.beta1, p.beta2, lr_of(s_lr, p, j), p.eps);
+  }
+  if (!fresh) {
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) mask_tail(w[u], m[u], v[u], lane + 32 * u, T.cols);
   }
 }
 
 // ---- before the step kernel: listed rows -> state of step t-1, constrained for step t -------
 template <int CPL>
 __global__ void __launch_bounds__(256) k_lazy_pre(const LazyParams p) {
+  __shared__ float s_lr[LR_TAB];
+  fill_lr_tab(s_lr, p);
   const int lane = threadIdx.x & 31;
   const int64_t nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
   const uint32_t n = __ldg(p.uniq);
@@ -169,7 +205,7 @@ __global__ void __launch_bounds__(256) k_lazy_pre(const LazyParams p) {
       if (idle) {
         load_row<CPL>(T.m + row * (int64_t) T.ld, nch, lane, m);
         load_row<CPL>(T.v + row * (int64_t) T.ld, nch, lane, v);
-        replay_row<CPL>(p, T, w, m, v, all_zero<CPL>(m, v), s, p.t - 1, nch, lane);
+        replay_row<CPL>(p, T, s_lr, w, m, v, all_zero<CPL>(m, v), s, p.t - 1, nch, lane);
       }
       con_row<CPL>(w, T.con_op, nch, lane);                // start-of-batch constraint of step t
       store_row<CPL>(T.w + row * (int64_t) T.ld, nch, lane, w);
@@ -203,18 +239,13 @@ __global__ void __launch_bounds__(256) k_lazy_update(const LazyParams p) {
           float4 part[CPL];
 #pragma unroll
           for (int u = 0; u < CPL; ++u) part[u] = f4zero();
-          sum_records<CPL>(p.vals, T.rec, T.rec_ld, 0u, lo + L * w3 / 8, lo + L * (w3 + 1) / 8, nch, lane, part);
+          sum_records<CPL, RecDepth<CPL>::HEAVY>(p.vals, T.rec, T.rec_ld, 0u, lo + L * w3 / 8, lo + L * (w3 + 1) / 8, nch, lane, part);
 #pragma unroll
           for (int u = 0; u < CPL; ++u) g[u] += part[u];
         }
-      if (s + 1 < p.t && !all_zero<CPL>(m, v)) {
-        // k_lazy_pre already moved w; m and v still belong to step s: their zero-gradient steps are
-        // m <- b1 m + (1 - b1) 0, v <- b2 v + (1 - b2) 0 0, independent of w
-        for (uint32_t j = s + 1; j < p.t; ++j) {
-#pragma unroll
-          for (int u = 0; u < CPL; ++u) { float4 dummy = f4zero(); adam_chunk(dummy, m[u], v[u], f4zero(), p.beta1, p.beta2, 0.f, p.eps); }
-        }
-      }
+      // k_lazy_pre already moved w; m and v still belong to step s: their zero-gradient steps are
+      // independent of w
+      if (s + 1 < p.t && !all_zero<CPL>(m, v)) decay_mv<CPL>(m, v, p.t - 1 - s, p.beta1, p.beta2);
       const float scale = p.scal[T.slot];
 #pragma unroll
       for (int u = 0; u < CPL; ++u) {
@@ -234,6 +265,8 @@ __global__ void __launch_bounds__(256) k_lazy_update(const LazyParams p) {
 // ---- kge_flush_rows: every row of the lazy tables to step t ---------------------------------
 template <int CPL>
 __global__ void __launch_bounds__(256) k_lazy_flush(const LazyParams p) {
+  __shared__ float s_lr[LR_TAB];
+  fill_lr_tab(s_lr, p);
   const int lane = threadIdx.x & 31;
   const int64_t nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
   for (int ti = 0; ti < p.n_tabs; ++ti) {
@@ -247,7 +280,7 @@ __global__ void __launch_bounds__(256) k_lazy_flush(const LazyParams p) {
       load_row<CPL>(T.m + row * (int64_t) T.ld, nch, lane, m);
       load_row<CPL>(T.v + row * (int64_t) T.ld, nch, lane, v);
       const bool fresh = all_zero<CPL>(m, v);
-      replay_row<CPL>(p, T, w, m, v, fresh, s, p.t, nch, lane);
+      replay_row<CPL>(p, T, s_lr, w, m, v, fresh, s, p.t, nch, lane);
       store_row<CPL>(T.w + row * (int64_t) T.ld, nch, lane, w);
       if (!fresh) {
         store_row<CPL>(T.m + row * (int64_t) T.ld, nch, lane, m);

@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(256) k_shard_push(const LazyParams lp, ShardDe
           float4 part[CPL];
 #pragma unroll
           for (int u = 0; u < CPL; ++u) part[u] = f4zero();
-          sum_records<CPL>(lp.vals, T.rec, T.rec_ld, 0u, lo + L * w3 / 8, lo + L * (w3 + 1) / 8, nch, lane, part);
+          sum_records<CPL, RecDepth<CPL>::HEAVY>(lp.vals, T.rec, T.rec_ld, 0u, lo + L * w3 / 8, lo + L * (w3 + 1) / 8, nch, lane, part);
 #pragma unroll
           for (int u = 0; u < CPL; ++u) g[u] += part[u];
         }
@@ -160,12 +160,7 @@ __global__ void __launch_bounds__(256) k_shard_update(const LazyParams lp, Shard
 #pragma unroll
         for (int u = 0; u < CPL; ++u) g[u] += x[u];
       }
-      if (s + 1 < lp.t && !all_zero<CPL>(m, v)) {
-        for (uint32_t j = s + 1; j < lp.t; ++j) {
-#pragma unroll
-          for (int u = 0; u < CPL; ++u) { float4 dummy = f4zero(); adam_chunk(dummy, m[u], v[u], f4zero(), lp.beta1, lp.beta2, 0.f, lp.eps); }
-        }
-      }
+      if (s + 1 < lp.t && !all_zero<CPL>(m, v)) decay_mv<CPL>(m, v, lp.t - 1 - s, lp.beta1, lp.beta2);
       const float scale = lp.scal[T.slot];
 #pragma unroll
       for (int u = 0; u < CPL; ++u) {

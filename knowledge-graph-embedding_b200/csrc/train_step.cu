@@ -738,9 +738,15 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   pt.begin(4);
   if (grad_only) {
     if (sh) {           // relation tables -> grads.dense (general kernel on k_heads' segment table); entity rows -> owners
-      if (up.n_tabs > 0) { if (int rc2 = launch_update<3>(up, cpl, ublocks, st)) return rc2; }
+      if (up.n_tabs > 0) {            // beside the push, on the side stream
+        KGE_CUDA_OK(cudaEventRecord(ctx->ev_mid, st));
+        KGE_CUDA_OK(cudaStreamWaitEvent(ctx->aux, ctx->ev_mid, 0));
+        if (int rc2 = launch_update<3>(up, cpl, ublocks, ctx->aux)) return rc2;
+        KGE_CUDA_OK(cudaEventRecord(ctx->ev_heavy, ctx->aux));
+      }
       for (int j = 0; j < lp.n_tabs; ++j) { lp.tab[j].rec = p.rec[lp.tab[j].slot]; lp.tab[j].rec_ld = L.rld[lp.tab[j].slot]; }
       if (int rc2 = launch_shard_rows<0>(lp, sdv, item_slot, ctx->sm_count, st)) return rc2;
+      if (up.n_tabs > 0) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_heavy, 0));
     } else if (ctx->opt_radix_sort) {
       if (int rc2 = launch_update<3>(up, cpl, ublocks, st)) return rc2;
     } else {

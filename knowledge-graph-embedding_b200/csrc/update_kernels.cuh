@@ -206,10 +206,15 @@ __global__ void __launch_bounds__(256) k_segments(const uint32_t* __restrict__ k
 // c = lane + 32 u strictly in lane (= sorted, stable) order.  The row loads of J records x CPL
 // chunks are independent, so many are in flight; the ragged last batch is predicated, not serial.
 // All 32 lanes must call.
-template <int CPL>
+// records in flight: light rows (a handful of records) / heavy slices (hundreds: the adds are a serial
+// chain by definition, so the only lever is how many row loads are outstanding)
+template <int CPL> struct RecDepth {
+  static constexpr int LIGHT = CPL <= 2 ? 4 : (CPL == 4 ? 2 : 1);
+  static constexpr int HEAVY = CPL == 1 ? 16 : (CPL == 2 ? 8 : (CPL == 4 ? 4 : 2));
+};
+template <int CPL, int J = RecDepth<CPL>::LIGHT>
 __device__ __forceinline__ void sum_chunk(uint32_t mine, int n, const float* __restrict__ rec, int rec_ld, int nch, int lane,
                                           float4 (&g)[CPL]) {
-  constexpr int J = CPL <= 2 ? 4 : (CPL == 4 ? 2 : 1);       // records in flight (register budget)
   for (int j = 0; j < n; j += J) {
     const float4* r[J];
 #pragma unroll
@@ -232,14 +237,14 @@ __device__ __forceinline__ void sum_chunk(uint32_t mine, int n, const float* __r
 }
 
 // Records at sorted positions [lo, hi), ids fetched 32 at a time.
-template <int CPL>
+template <int CPL, int J = RecDepth<CPL>::LIGHT>
 __device__ __forceinline__ void sum_records(const uint32_t* __restrict__ vals, const float* __restrict__ rec, int rec_ld,
                                             uint32_t rec_base, int64_t lo, int64_t hi, int nch, int lane,
                                             float4 (&g)[CPL]) {
   for (int64_t q0 = lo; q0 < hi; q0 += WARP) {
     const int n = (int) ((hi - q0 < WARP) ? hi - q0 : WARP);
     const uint32_t mine = (lane < n) ? __ldg(vals + q0 + lane) - rec_base : 0u;
-    sum_chunk<CPL>(mine, n, rec, rec_ld, nch, lane, g);
+    sum_chunk<CPL, J>(mine, n, rec, rec_ld, nch, lane, g);
   }
 }
 
@@ -308,8 +313,8 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
     float4 part[CPL];
 #pragma unroll
     for (int u = 0; u < CPL; ++u) part[u] = f4zero();
-    sum_records<CPL>(p.vals, H.rec, H.rec_ld, H.rec_base, s_lo[w2] + L * warp / 8, s_lo[w2] + L * (warp + 1) / 8, hn,
-                     lane, part);
+    sum_records<CPL, RecDepth<CPL>::HEAVY>(p.vals, H.rec, H.rec_ld, H.rec_base, s_lo[w2] + L * warp / 8,
+                                           s_lo[w2] + L * (warp + 1) / 8, hn, lane, part);
 #pragma unroll
     for (int u = 0; u < CPL; ++u) s_part[warp][u * WARP + lane] = part[u];
     __syncthreads();
@@ -511,7 +516,8 @@ __global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
   float4 part[CPL];
 #pragma unroll
   for (int u = 0; u < CPL; ++u) part[u] = f4zero();
-  sum_records<CPL>(p.vals, T.rec, T.rec_ld, T.rec_base, lo + L * warp / 8, lo + L * (warp + 1) / 8, nch, lane, part);
+  sum_records<CPL, RecDepth<CPL>::HEAVY>(p.vals, T.rec, T.rec_ld, T.rec_base, lo + L * warp / 8, lo + L * (warp + 1) / 8, nch,
+                                         lane, part);
 #pragma unroll
   for (int u = 0; u < CPL; ++u) s_part[warp][u * WARP + lane] = part[u];
   __syncthreads();
