@@ -168,10 +168,12 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
     if (c < k) my_e = p.neg_override ? p.neg_override[i * k + c] : sample_negative(p.sd, i, c, h, t);
   };
   constexpr bool PREFETCH = (NV <= 2);       // wider rows: the second row in flight would spill
+  // TransE / UM fast loop (below) loads its negatives in groups of GROUP rows instead
+  constexpr int GROUP = 4;
   Ent Nnext;
   if (n_it > 0) {
     draw(0);
-    if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, 0), lane);
+    if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, 0), lane);      // in flight while the positive is scored
   }
   // DistMult fast path.  s = sum(e_h * r * e_t) is linear in the corrupted entity, so with
   // q = r*t (head corrupted) or h*r (tail corrupted) fixed per positive:  s_neg = N . q,
@@ -268,16 +270,9 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
         if constexpr (M::KIND == KGE_UM) Xq.v[v] = head ? T.e.v[v] : H.e.v[v];
         else Xq.v[v] = head ? T.e.v[v] - R.a.v[v] : H.e.v[v] + R.a.v[v];
       }
-      for (int it = 0; it < n_it; ++it) {
+      auto body = [&](int it, int64_t e, const Ent& N) {
         const int c = wig + it * wpp;
         const int64_t slot = i * k + c;
-        const int64_t e = __shfl_sync(FULL, my_e, it & 31);
-        Ent N;
-        if (PREFETCH) N = Nnext; else N.load(md, e, lane);
-        if (it + 1 < n_it) {
-          if (((it + 1) & 31) == 0) draw(it + 1);
-          if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, (it + 1) & 31), lane);
-        }
         if (lane == 0 && p.write_keys) {
           p.neg_ids[slot] = e;
           if (TRAIN) { p.keys[2 * p.B + slot] = (uint32_t) e; p.vals[2 * p.B + slot] = (uint32_t)(2 * p.B + slot); }
@@ -296,6 +291,36 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
           if constexpr (M::KIND == KGE_TRANSE) nrm[KGE_T_REL_A] += ss;
           row_add(A, gx);
           store_row(gy, p.rec[KGE_T_ENT], 2 * p.B + slot, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+        }
+      };
+      if constexpr (NV == 1) {
+        // GROUP rows are requested before the first is consumed: a warp keeps GROUP row loads in
+        // flight (HBM latency; several times that when the row lives in a peer GPU's memory,
+        // kge_shard).  The per-negative arithmetic and its order are unchanged.
+        for (int it0 = 0; it0 < n_it; it0 += GROUP) {
+          Ent Nb[GROUP];
+          int64_t eb[GROUP];
+          if (it0 > 0 && (it0 & 31) == 0) draw(it0);        // GROUP divides 32: a group never straddles a draw
+#pragma unroll
+          for (int x = 0; x < GROUP; ++x)
+            if (it0 + x < n_it) {
+              eb[x] = __shfl_sync(FULL, my_e, (it0 + x) & 31);
+              if (it0 + x == 0) Nb[x] = Nnext; else Nb[x].load(md, eb[x], lane);
+            }
+#pragma unroll
+          for (int x = 0; x < GROUP; ++x)
+            if (it0 + x < n_it) body(it0 + x, eb[x], Nb[x]);
+        }
+      } else {
+        for (int it = 0; it < n_it; ++it) {
+          const int64_t e = __shfl_sync(FULL, my_e, it & 31);
+          Ent N;
+          if (PREFETCH) N = Nnext; else N.load(md, e, lane);
+          if (it + 1 < n_it) {
+            if (((it + 1) & 31) == 0) draw(it + 1);
+            if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, (it + 1) & 31), lane);
+          }
+          body(it, e, N);
         }
       }
       if (TRAIN) {

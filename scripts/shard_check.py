@@ -111,6 +111,7 @@ def bench(rank, world, dev, steps=30, warm=4, N=5_000_000, R=1000, d=128, k=32, 
         ph = {}
         for name in ("lookup", "pre", "grad", "allreduce", "apply"):
             ph[name] = 0.0
+        sh.eng.profile_begin(32)
         for i in range(4):
             X = batches[i % 8]
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
@@ -122,6 +123,10 @@ def bench(rank, world, dev, steps=30, warm=4, N=5_000_000, R=1000, d=128, k=32, 
             ev[5].record(); torch.cuda.synchronize()
             for j, name in enumerate(("lookup", "pre", "grad", "allreduce", "apply")):
                 ph[name] += ev[j].elapsed_time(ev[j + 1]) / 4
+        lib_ph, n_calls = sh.eng.profile_end()
+        ph["lib_step_kernel"] = lib_ph["step"] / 4
+        ph["lib_push_and_rel_update"] = lib_ph["update"] / 4 - ph["apply"]      # phase 4 = grad's push + apply's update
+        ph["lib_sort_chain"] = lib_ph["sort"] / 4
         if rank == 0:
             ms = float(ms.item())
             alg = B_global * (7 * 4 * ((2 + k) * d + d) + 24)
