@@ -291,8 +291,11 @@ int kge_flush_rows(kge_ctx*, const kge_cfg*, kge_tables*, void* stream);
 /* Implementation switches (testing / A-B measurement; results are identical either way).
  * KGE_OPT_RADIX_SORT: 1 = group the step's gradient records with cub's stable radix sort
  * instead of the counting sort of csrc/group_kernels.cuh (default 0).
- * KGE_OPT_NO_SHADOW: 1 = ignore kge_table.wn and run the full-table constraint pass every batch. */
-enum { KGE_OPT_RADIX_SORT = 1, KGE_OPT_NO_SHADOW = 2 };
+ * KGE_OPT_NO_SHADOW: 1 = ignore kge_table.wn and run the full-table constraint pass every batch.
+ * KGE_OPT_NO_FUSED_PUSH: 1 = sharded step: the step kernel writes every gradient record locally and
+ * k_shard_push delivers all rows (default 0: single-record rows are stored into the owner's inbox by
+ * the step kernel itself). */
+enum { KGE_OPT_RADIX_SORT = 1, KGE_OPT_NO_SHADOW = 2, KGE_OPT_NO_FUSED_PUSH = 3 };
 int kge_set_option(kge_ctx*, int option, int value);
 
 /* Per-phase device timing (CUDA events recorded on the call's stream, read back only at

@@ -14,6 +14,7 @@ T_ENT, T_ENT_PROJ, T_REL_A, T_REL_B = range(4)
 CON_NORMALIZE, CON_CLIP = 0, 1
 OPT_RADIX_SORT = 1
 OPT_NO_SHADOW = 2
+OPT_NO_FUSED_PUSH = 3
 N_PHASES = 8
 PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm", "rank_fix"]
 

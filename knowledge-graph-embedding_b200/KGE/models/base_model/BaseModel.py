@@ -159,8 +159,23 @@ class KGEModel:
                              rotate_limit=self._rotate_limit())
         cfg.update(adam_fields(self._optimizer))
         slots = _spec.SLOTS[self.MODEL]
-        self._engine = _engine.Engine(cfg, {slots[k]: v for k, v in values.items()}, device=self.device)
+        self._engine = _engine.Engine(cfg, {slots[k]: v for k, v in values.items()}, device=self.device,
+                                      lazy=self._lazy_rows(cfg, values))
         self.model_weights = {k: WeightView(k, self._engine.tab[slots[k]]) for k in values}
+
+    def _lazy_rows(self, cfg, values):
+        """Row-lazy replay of the dense per-batch table passes (kge_abi.h, kge_tables.lazy_t; results are
+        bit-identical to the dense step).  KGE_B200_LAZY_ROWS=1|0 forces it; by default it is used when
+        the entity table is far larger than L2 (>= 512 MB) on a single GPU, for the models it covers."""
+        eligible = self.MODEL in ("UM", "TransE", "TransD", "RotatE", "DistMult") or \
+            (self.MODEL == "TransH" and not cfg["constraint"])
+        flag = os.environ.get("KGE_B200_LAZY_ROWS", "auto")
+        if not eligible or _dp.world()[1] > 1 or flag == "0":
+            return False
+        if flag == "1":
+            return True
+        ent_bytes = 4 * sum(int(np.prod(v.shape)) for k, v in values.items() if k.startswith("ent"))
+        return ent_bytes >= (512 << 20)
 
     def restore_model_weights(self, model_weights):
         self._check_model_weights(model_weights)

@@ -41,6 +41,7 @@ struct kge_ctx_impl {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_mid = nullptr, ev_heavy = nullptr;
   int opt_radix_sort = 0;         // kge_set_option(KGE_OPT_RADIX_SORT)
   int opt_no_shadow = 0;          // kge_set_option(KGE_OPT_NO_SHADOW)
+  int opt_no_fused_push = 0;      // kge_set_option(KGE_OPT_NO_FUSED_PUSH)
   unsigned* ticket = nullptr;     // device, 64 words, zero between calls (self-resetting counters)
 };
 // RAII marker: records the boundary events of one call when profiling is on

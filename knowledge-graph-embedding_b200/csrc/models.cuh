@@ -48,6 +48,9 @@ template <int NV> struct Ent1 {
   __device__ __forceinline__ void store(const ModelDev& md, float* const* recs, int64_t rec, int lane) const {
     store_row(e, recs[KGE_T_ENT], rec, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
   }
+  __device__ __forceinline__ void store_to(const ModelDev& md, float* b0, float*, int64_t rec, int lane) const {
+    store_row(e, b0, rec, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+  }
 };
 template <int NV> struct Ent2 {
   Row<NV> e, p;
@@ -69,6 +72,10 @@ template <int NV> struct Ent2 {
   __device__ __forceinline__ void store(const ModelDev& md, float* const* recs, int64_t rec, int lane) const {
     store_row(e, recs[KGE_T_ENT], rec, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
     store_row(p, recs[KGE_T_ENT_PROJ], rec, md.rld[KGE_T_ENT_PROJ], md.t[KGE_T_ENT_PROJ].cols, lane);
+  }
+  __device__ __forceinline__ void store_to(const ModelDev& md, float* b0, float* b1, int64_t rec, int lane) const {
+    store_row(e, b0, rec, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+    store_row(p, b1, rec, md.rld[KGE_T_ENT_PROJ], md.t[KGE_T_ENT_PROJ].cols, lane);
   }
 };
 template <int NV> struct Rel0 {

@@ -36,8 +36,11 @@ struct ShardDev {
 // ---- A: route the looked-up row ids to their owners -----------------------------------------
 // uniq = k_heads' work list (global row ids).  Slot inside the (owner, this rank) inbox section by
 // a warp-aggregated atomic on a local counter; item_slot remembers it for k_shard_push.
+// rows with a single gradient record: rec_dest[record] = owner << 29 | slot, so that k_step stores that
+// record straight into the owner's inbox (rec_dest is preset to REC_LOCAL = 0xffffffff).
 __global__ void __launch_bounds__(256) k_route(const uint32_t* __restrict__ uniq, ShardDev sd, uint32_t* __restrict__ rcnt,
-                                               uint32_t* __restrict__ item_slot) {
+                                               uint32_t* __restrict__ item_slot, const uint32_t* __restrict__ vals,
+                                               uint32_t* __restrict__ rec_dest) {
   const uint32_t n = __ldg(uniq);
   const int lane = threadIdx.x & 31;
   for (int64_t base = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) & ~31ll; base < n; base += (int64_t) gridDim.x * blockDim.x) {
@@ -54,6 +57,8 @@ __global__ void __launch_bounds__(256) k_route(const uint32_t* __restrict__ uniq
       const uint32_t slot = b + __popc(peers & ((1u << lane) - 1));
       sd.ids_peer[o][(size_t) sd.rank * sd.cap + slot] = row - o * sd.S;
       item_slot[it] = slot;
+      const uint32_t lo = __ldg(uniq + 4 + 3 * it + 1), hi = __ldg(uniq + 4 + 3 * it + 2);
+      if (hi - lo == 1u) rec_dest[__ldg(vals + lo)] = (o << 29) | slot;
     }
   }
 }
@@ -100,7 +105,8 @@ __global__ void __launch_bounds__(256) k_contrib(ShardDev sd) {
 // ---- C: one summed gradient row per looked-up row -> the owner's value inbox ------------------
 // Record sum in the dense kernels' order (k_lazy_update).  lp.tab[].rec = this rank's records.
 template <int CPL>
-__global__ void __launch_bounds__(256) k_shard_push(const LazyParams lp, ShardDev sd, const uint32_t* __restrict__ item_slot) {
+__global__ void __launch_bounds__(256) k_shard_push(const LazyParams lp, ShardDev sd, const uint32_t* __restrict__ item_slot,
+                                                    int skip_single) {
   const int lane = threadIdx.x & 31;
   const int64_t nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
   const uint32_t n = __ldg(lp.uniq);
@@ -108,6 +114,7 @@ __global__ void __launch_bounds__(256) k_shard_push(const LazyParams lp, ShardDe
     const uint32_t* item = lp.uniq + 4 + 3 * it;
     const uint32_t row = __ldg(item);
     const int64_t lo = __ldg(item + 1), L = (int64_t) __ldg(item + 2) - lo;
+    if (L == 1 && skip_single) continue;        // k_step delivered the row's only record itself
     const uint32_t o = row / sd.S, slot = __ldg(item_slot + it);
     for (int ti = 0; ti < lp.n_tabs; ++ti) {
       const LazyTable& T = lp.tab[ti];
@@ -179,17 +186,18 @@ __global__ void __launch_bounds__(256) k_shard_update(const LazyParams lp, Shard
 }
 
 template <int WHICH>   // 0 push, 1 update
-inline int launch_shard_rows(const LazyParams& lp, const ShardDev& sd, const uint32_t* item_slot, int sm_count, cudaStream_t st) {
+inline int launch_shard_rows(const LazyParams& lp, const ShardDev& sd, const uint32_t* item_slot, int sm_count, cudaStream_t st,
+                             int skip_single = 0) {
   int max_ch = 1;
   for (int j = 0; j < lp.n_tabs; ++j) max_ch = ((lp.tab[j].cols + 3) / 4 > max_ch) ? (lp.tab[j].cols + 3) / 4 : max_ch;
   const int cpl = max_ch <= 32 ? 1 : (max_ch <= 64 ? 2 : (max_ch <= 128 ? 4 : 8));
   const unsigned grid = (unsigned) sm_count * (cpl <= 2 ? 8 : 4);
   if (WHICH == 0) {
     switch (cpl) {
-      case 1: k_shard_push<1><<<grid, 256, 0, st>>>(lp, sd, item_slot); break;
-      case 2: k_shard_push<2><<<grid, 256, 0, st>>>(lp, sd, item_slot); break;
-      case 4: k_shard_push<4><<<grid, 256, 0, st>>>(lp, sd, item_slot); break;
-      default: k_shard_push<8><<<grid, 256, 0, st>>>(lp, sd, item_slot); break;
+      case 1: k_shard_push<1><<<grid, 256, 0, st>>>(lp, sd, item_slot, skip_single); break;
+      case 2: k_shard_push<2><<<grid, 256, 0, st>>>(lp, sd, item_slot, skip_single); break;
+      case 4: k_shard_push<4><<<grid, 256, 0, st>>>(lp, sd, item_slot, skip_single); break;
+      default: k_shard_push<8><<<grid, 256, 0, st>>>(lp, sd, item_slot, skip_single); break;
     }
   } else {
     switch (cpl) {

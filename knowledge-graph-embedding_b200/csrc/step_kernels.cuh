@@ -40,7 +40,31 @@ struct StepParams {
   int tail;                      // 1: the last warp to finish reduces the partials (no k_reduce launch)
   unsigned* done;                // ticket counter for the tail reduction (self-resetting)
   ReduceParams rp;
+  // sharded entity tables (kge_shard): an entity-table record that is the ONLY record of its row is the
+  // row's summed gradient, so the step kernel stores it straight into the owner's value inbox over
+  // NVLink (the outbound stores overlap the inbound row gathers) instead of into the local record
+  // buffer.  rec_dest[record] = owner << 29 | inbox row, or REC_LOCAL; inbox[s][owner] = this rank's
+  // section of owner's value inbox of entity slot s (row stride = the record stride).
+  const uint32_t* rec_dest;      // nullable
+  float* inbox[2][KGE_MAX_PEERS];
 };
+constexpr uint32_t REC_LOCAL = 0xffffffffu;
+// where entity record `rec` goes: the local record buffers (row = rec) or this rank's section of the
+// owner's value inbox
+struct RecTarget { float* b0; float* b1; int64_t row; };
+__device__ __forceinline__ RecTarget rec_target(const StepParams& p, int64_t rec) {
+  RecTarget t;
+  t.b0 = p.rec[KGE_T_ENT]; t.b1 = p.rec[KGE_T_ENT_PROJ]; t.row = rec;
+  if (p.rec_dest != nullptr) {
+    const uint32_t d = __ldg(p.rec_dest + rec);
+    if (d != REC_LOCAL) {
+      const int o = (int) (d >> 29);
+      t.b0 = p.inbox[0][o]; t.b1 = p.inbox[1][o];
+      t.row = (int64_t) (d & 0x1fffffffu);
+    }
+  }
+  return t;
+}
 
 // ticket handshake: the caller's stores are fenced; returns true in the last warp to arrive
 __device__ __forceinline__ bool last_warp_done(unsigned* done, unsigned total, int lane) {
@@ -60,7 +84,7 @@ __device__ __forceinline__ void group_barrier(int grp, int wpp) {
 }
 
 template <class M, int NV, bool TRAIN>
-__global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
+__global__ void __launch_bounds__(STEP_THREADS, ((NV == 1 || (NV == 2 && M::KIND != KGE_TRANSD)) ? 2 : 1)) k_step(const StepParams p) {
   using Ent = typename M::template Ent<NV>;
   using Rel = typename M::template Rel<NV>;
   extern __shared__ float4 smem4[];
@@ -238,7 +262,8 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
           }
           nrm[KGE_T_ENT] += 2.0f * coef * coef * cnt;      // the negative's row and the kept entity's occurrence
           nrm[KGE_T_REL_A] += pr;
-          store_row(N.e, p.rec[KGE_T_ENT], 2 * p.B + slot, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+          { const RecTarget rt = rec_target(p, 2 * p.B + slot);
+            store_row(N.e, rt.b0, rt.row, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane); }
         }
       }
       if (TRAIN) {
@@ -290,7 +315,8 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
           nrm[KGE_T_ENT] += 2.0f * ss;                     // the negative's row and the kept entity's occurrence
           if constexpr (M::KIND == KGE_TRANSE) nrm[KGE_T_REL_A] += ss;
           row_add(A, gx);
-          store_row(gy, p.rec[KGE_T_ENT], 2 * p.B + slot, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+          { const RecTarget rt = rec_target(p, 2 * p.B + slot);
+            store_row(gy, rt.b0, rt.row, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane); }
         }
       };
       if constexpr (NV == 1) {
@@ -380,7 +406,8 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
           const float d2 = dneg * dneg;
           nrm[KGE_T_ENT] += d2 * (q2 + pe);
           nrm[KGE_T_REL_A] += d2 * pr;
-          store_row(gN, p.rec[KGE_T_ENT], 2 * p.B + slot, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+          { const RecTarget rt = rec_target(p, 2 * p.B + slot);
+            store_row(gN, rt.b0, rt.row, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane); }
         }
       }
       if (TRAIN) {
@@ -421,8 +448,9 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
       Rel gR;
       M::template backward<NV>(md, A, R, Bq, x, y, sv, dneg, lane, gA, gR, gB);
       gA.sumsq(nrm); gB.sumsq(nrm); gR.sumsq(nrm);   // each lookup row is one IndexedSlices occurrence
-      if (head) { gA.store(md, p.rec, 2 * p.B + slot, lane); GT.add(gB); }
-      else      { gB.store(md, p.rec, 2 * p.B + slot, lane); GH.add(gA); }
+      const RecTarget rt = rec_target(p, 2 * p.B + slot);
+      if (head) { gA.store_to(md, rt.b0, rt.b1, rt.row, lane); GT.add(gB); }
+      else      { gB.store_to(md, rt.b0, rt.b1, rt.row, lane); GH.add(gA); }
       GR.add(gR);
     }
   }
@@ -520,8 +548,8 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step(const StepParams p) {
   }
   if (p.tail && last_warp_done(p.done, (unsigned) p.B, lane)) tail_reduce_warp(p.rp, lane);
   if (TRAIN) {
-    GH.store(md, p.rec, i, lane);
-    GT.store(md, p.rec, p.B + i, lane);
+    { const RecTarget rt = rec_target(p, i); GH.store_to(md, rt.b0, rt.b1, rt.row, lane); }
+    { const RecTarget rt = rec_target(p, p.B + i); GT.store_to(md, rt.b0, rt.b1, rt.row, lane); }
     GR.store(md, p.rec, i, lane);
     if (lane == 0 && p.write_keys) {
       p.keys[i] = (uint32_t) h;           p.vals[i] = (uint32_t) i;

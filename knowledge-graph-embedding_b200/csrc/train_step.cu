@@ -17,7 +17,7 @@ namespace kge {
 struct StepWs {
   size_t off_part, off_scal, off_neg, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub,
       off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart, off_seg, off_hdr, off_heavy, off_uniq,
-      off_islot;
+      off_islot, off_recdest;
   size_t cub_bytes, total, n_seg;
   int64_t n_ent_rec, n_keys, total_rows, n_mat_cta;
   int rld[KGE_MAX_TABLES];
@@ -94,6 +94,7 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   L.off_heavy = take(sizeof(uint32_t) * (size_t) (L.n_keys / UPD_HEAVY + 1));
   L.off_uniq = take(sizeof(uint32_t) * (4 + 3 * (size_t) L.n_keys));   // row-lazy work list (k_heads)
   L.off_islot = take(sizeof(uint32_t) * ((size_t) L.n_keys + 16));      // sharded step: inbox slot per work item | per-owner counters
+  L.off_recdest = take(sizeof(uint32_t) * (size_t) L.n_ent_rec);        // sharded step: inbox destination of single-record rows
   size_t scan_bytes = 0;
   if ((int64_t) L.n_seg > SCAN_SMALL_MAX) {
     e = cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (const uint32_t*) nullptr, (uint32_t*) nullptr, (int64_t) L.n_seg,
@@ -181,7 +182,7 @@ static int check_shard(const kge_cfg* c, const kge_tables* t, const kge_shard* s
               "bad kge_shard (world %d rank %d)", sh->world, sh->rank);
   KGE_REQUIRE(sh->shard_rows > 0 && sh->shard_rows < 0xffffffffll && sh->shard_rows * sh->world >= c->n_ent, KGE_EINVAL,
               "shard_rows %lld x world %d does not cover n_ent %lld", (long long) sh->shard_rows, sh->world, (long long) c->n_ent);
-  KGE_REQUIRE(sh->cap > 0 && sh->cap < 0xffffffffll && (B <= 0 || sh->cap >= 2 * B + B * (int64_t) k_eff_of(c)), KGE_EINVAL,
+  KGE_REQUIRE(sh->cap > 0 && sh->cap < (1ll << 29) / (sh->world > 0 ? sh->world : 1) && (B <= 0 || sh->cap >= 2 * B + B * (int64_t) k_eff_of(c)), KGE_EINVAL,
               "shard.cap %lld < looked-up rows of a batch of %lld", (long long) sh->cap, (long long) B);
   int cols[KGE_MAX_TABLES];
   expected_cols(c, cols);
@@ -193,7 +194,10 @@ static int check_shard(const kge_cfg* c, const kge_tables* t, const kge_shard* s
   }
   KGE_REQUIRE(sh->stamp && sh->idx_of && sh->work && sh->contrib, KGE_EINVAL, "shard owner scratch missing");
   for (int s2 = 0; s2 < 2; ++s2)
-    if (cols[s2]) KGE_REQUIRE(t->t[s2].w == sh->w_peer[sh->rank][s2], KGE_EINVAL, "tables slot %d is not this rank's shard", s2);
+    if (cols[s2]) {
+      KGE_REQUIRE(t->t[s2].w == sh->w_peer[sh->rank][s2], KGE_EINVAL, "tables slot %d is not this rank's shard", s2);
+      KGE_REQUIRE(t->t[s2].ld == (cols[s2] + 3) / 4 * 4, KGE_EINVAL, "sharded tables: ld of slot %d must be cols rounded up to 4", s2);
+    }
   return KGE_OK;
 }
 static void fill_shard_dev(const kge_shard* sh, ShardDev& sd) {
@@ -439,6 +443,15 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   }
   uint32_t* item_slot = reinterpret_cast<uint32_t*>(wsb + L.off_islot);
   uint32_t* rcnt = item_slot + L.n_keys;
+  uint32_t* rec_dest = reinterpret_cast<uint32_t*>(wsb + L.off_recdest);
+  p.rec_dest = nullptr;
+  if (sh && shard_phase == 2 && !ctx->opt_no_fused_push) {
+    p.rec_dest = rec_dest;
+    for (int s2 = 0; s2 < 2; ++s2)
+      for (int j = 0; j < KGE_MAX_PEERS; ++j)
+        p.inbox[s2][j] = (j < sh->world && sh->val_peer[j][s2])
+                             ? sh->val_peer[j][s2] + (size_t) sh->rank * (size_t) sh->cap * (size_t) tables->t[s2].ld : nullptr;
+  }
   if (shadow_use) p.md.t[KGE_T_ENT].w = tables->t[KGE_T_ENT].wn;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     p.md.rld[s] = L.rld[s];
@@ -578,7 +591,8 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
       KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
       if (shard_phase == 1) {                   // route the ids to their owners; the owners replay (kge_shard_pre)
         KGE_CUDA_OK(cudaMemsetAsync(rcnt, 0, sizeof(uint32_t) * 16, st));
-        k_route<<<(unsigned) ctx->sm_count * 4, 256, 0, st>>>(uniq, sdv, rcnt, item_slot);
+        KGE_CUDA_OK(cudaMemsetAsync(rec_dest, 0xff, sizeof(uint32_t) * (size_t) L.n_ent_rec, st));
+        k_route<<<(unsigned) ctx->sm_count * 4, 256, 0, st>>>(uniq, sdv, rcnt, item_slot, vals_out, rec_dest);
         KGE_CUDA_OK(cudaGetLastError());
         k_route_cnt<<<1, 32, 0, st>>>(sdv, rcnt);
         KGE_CUDA_OK(cudaGetLastError());
@@ -745,7 +759,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
         KGE_CUDA_OK(cudaEventRecord(ctx->ev_heavy, ctx->aux));
       }
       for (int j = 0; j < lp.n_tabs; ++j) { lp.tab[j].rec = p.rec[lp.tab[j].slot]; lp.tab[j].rec_ld = L.rld[lp.tab[j].slot]; }
-      if (int rc2 = launch_shard_rows<0>(lp, sdv, item_slot, ctx->sm_count, st)) return rc2;
+      if (int rc2 = launch_shard_rows<0>(lp, sdv, item_slot, ctx->sm_count, st, p.rec_dest != nullptr)) return rc2;
       if (up.n_tabs > 0) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_heavy, 0));
     } else if (ctx->opt_radix_sort) {
       if (int rc2 = launch_update<3>(up, cpl, ublocks, st)) return rc2;

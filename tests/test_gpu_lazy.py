@@ -108,3 +108,21 @@ def test_lazy_rejects_unsupported_and_out_of_order_calls():
     eng.adam_t += 3                                         # skipping steps is refused
     with pytest.raises(RuntimeError, match="lazy_t"):
         eng.train_step(X, 1, 1)
+
+
+def test_api_train_and_evaluate_identical_with_lazy_rows(tmp_path, monkeypatch):
+    """KGE.models.* with KGE_B200_LAZY_ROWS=1: train() incl. validation / early stopping / checkpoints and
+    evaluate() give the bits of the dense path."""
+    from KGE.models.translating_based.TransE import TransE
+    from toy_kg import train, val, metadata
+    outs = []
+    for flag in ("0", "1"):
+        monkeypatch.setenv("KGE_B200_LAZY_ROWS", flag)
+        m = TransE(embedding_params={"embedding_size": 12}, negative_ratio=2, corrupt_side="h+t")
+        m.train(train, val, metadata, epochs=5, batch_size=4, early_stopping_rounds=10, seed=2, log_path=str(tmp_path / flag))
+        assert m._engine.lazy == (flag == "1")
+        ev = m.evaluate(val, "t", positive_X=np.concatenate([train, val]))
+        outs.append(({k: v.numpy().copy() for k, v in m.model_weights.items()}, ev, list(m.val_loss_history)))
+    for k in outs[0][0]:
+        assert np.array_equal(outs[0][0][k], outs[1][0][k]), k
+    assert outs[0][1] == outs[1][1] and outs[0][2] == outs[1][2]

@@ -119,3 +119,27 @@ def test_shard_inbox_capacity_is_checked():
     X = rand_triples(np.random.default_rng(0), 64, N, R)
     with pytest.raises(RuntimeError, match="cap"):
         ranks[0].lookup(X, 1, 0, 64, 0)
+
+
+@pytest.mark.parametrize("case", [CASES[0], CASES[2]], ids=[IDS[0], IDS[2]])
+def test_fused_push_equals_separate_push_bitwise(case):
+    """The step kernel storing single-record rows straight into the owner's inbox (default) against
+    k_shard_push delivering every row (KGE_OPT_NO_FUSED_PUSH)."""
+    from KGE._b200 import shard as SH, dp, lib as L
+    B, world = 96, 3
+    batches = _batches(np.random.default_rng(8), 5, B)
+    runs = []
+    for nofuse in (1, 0):
+        ranks = _sharded(case, world, B)
+        ranks[0].eng.set_option(L.OPT_NO_FUSED_PUSH, nofuse)
+        try:
+            losses = []
+            for step, X in enumerate(batches):
+                parts = [dp.split_even(B, world, g) for g in range(world)]
+                losses.append(float(SH.emulate_step(ranks, [X[lo:hi] for lo, hi in parts], 5, step, B, [lo for lo, _ in parts]).item()))
+            runs.append((losses, _full_tables(ranks)))
+        finally:
+            ranks[0].eng.set_option(L.OPT_NO_FUSED_PUSH, 0)
+    assert runs[0][0] == runs[1][0]
+    for s in runs[0][1]:
+        assert torch.equal(runs[0][1][s], runs[1][1][s]), f"slot {s}"
