@@ -26,6 +26,9 @@ for _p in (ROOT, os.path.join(ROOT, "knowledge-graph-embedding_b200")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
+if os.environ.get("NCCL_DEBUG", "VERSION") == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line (NCCL prints its version there)
+
 import numpy as np
 import torch
 
@@ -54,36 +57,46 @@ def zipf_triples(n, N, R, seed):
 
 
 class Clocks:
-    """nvidia-smi sampler running during the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi sampler (B200_PROFILING.md recipe), running from before the warm-up to the end of the
+    GPU-timed regions: every sample is taken while the bench keeps the GPU under its own load.  A
+    reader thread collects the lines; `ensure()` keeps the workload running until a sample exists
+    (nvidia-smi needs a second or more to start on an 8-GPU box, a 100-step region lasts 20 ms)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
-        self.rows, self.proc, self.idx = [], None, gpu_index
+        self.rows, self.proc, self.idx, self.thread = [], None, gpu_index, None
 
-    def __enter__(self):
+    def start(self):
+        import threading
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
         except Exception:
             self.proc = None
+            return self
+
+        def read():
+            for line in self.proc.stdout:
+                f = [x.strip() for x in line.split(",")]
+                if len(f) >= 9:
+                    self.rows.append(f)
+        self.thread = threading.Thread(target=read, daemon=True)
+        self.thread.start()
         return self
 
-    def __exit__(self, *a):
+    def stop(self):
         if self.proc is None:
             return
-        time.sleep(0.15)
         self.proc.terminate()
         try:
-            out, _ = self.proc.communicate(timeout=5)
+            self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-            out = ""
-        for line in out.splitlines():
-            f = [x.strip() for x in line.split(",")]
-            if len(f) >= 9:
-                self.rows.append(f)
+        if self.thread is not None:
+            self.thread.join(timeout=2)
+        self.proc = None
 
     def summary(self):
         if not self.rows:
@@ -172,20 +185,20 @@ def run_ours(args, rank, world, device):
             torch.distributed.barrier()
         torch.cuda.synchronize()
 
+    clk = Clocks(torch.cuda.current_device()).start()
     for i in range(args.warmup):
         one_step(dev_batches[i % n_batches])
     barrier()
 
     # ---- value: inputs resident in HBM, L2 flushed between steps, per-step CUDA events ----
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    with Clocks(torch.cuda.current_device()) as clk:
-        barrier()
-        for i in range(args.steps):
-            flush.zero_()
-            ev[i][0].record()
-            one_step(dev_batches[i % n_batches])
-            ev[i][1].record()
-        barrier()
+    barrier()
+    for i in range(args.steps):
+        flush.zero_()
+        ev[i][0].record()
+        one_step(dev_batches[i % n_batches])
+        ev[i][1].record()
+    barrier()
     ms_cold = sum(a.elapsed_time(b) for a, b in ev)
 
     # ---- the same loop again with the library's per-phase events on (they sit between the
@@ -225,6 +238,20 @@ def run_ours(args, rank, world, device):
         torch.cuda.current_stream().synchronize()      # the reference reads loss.numpy() per batch
     barrier()
     ms_e2e = (time.perf_counter() - t0) * 1e3
+
+    # clocks: at least two samples under the bench's own load (same step, untimed) — every rank keeps
+    # stepping for the same number of rounds so data-parallel collectives stay matched
+    need = torch.tensor([1 if (clk.proc is not None and len(clk.rows) < 2) else 0], device=device)
+    for _ in range(60):
+        if world > 1:
+            torch.distributed.all_reduce(need, op=torch.distributed.ReduceOp.MAX)
+        if int(need.item()) == 0:
+            break
+        for i in range(200):
+            one_step(dev_batches[i % n_batches])
+        torch.cuda.synchronize()
+        need[0] = 1 if (clk.proc is not None and len(clk.rows) < 2) else 0
+    clk.stop()
 
     t = torch.tensor([ms_cold, ms_warm, ms_e2e], dtype=torch.float64, device=device)
     if world > 1:
@@ -390,7 +417,7 @@ def main():
         "k_update_fast on the caller's stream; k_keys, k_scan, k_scatter, k_canon, k_update_heavy on the side stream "
         "(+ one memset there); data-parallel runs split the update pair into k_update_fast/heavy<3> (row sums stored "
         "into every rank's staging slot over NVLink) + k_push_scal, one cross-GPU barrier, then k_dp_scales + "
-        "k_update_fast<4> (config.exchange = peer), or the same around one NCCL all-reduce (exchange = nccl)",
+        "k_update_fast<4> (config.exchange = peer), or the same around one NCCL all-reduce (exchange = nccl); exchange = owner: row sums go to the row owner only, the owner runs k_update_fast<4> on its rows and stores the new rows into every replica over NVLink (two barriers)",
         "roofline": {"kernel": "k_step<MDistMult,2,true>", "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": ncu_traffic("k_step<MDistMult"),
                      "traffic_note": "ncu dram read+write per launch (cold caches); below the algorithmic bytes because "

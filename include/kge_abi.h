@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 5
+#define KGE_ABI_VERSION 6
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -217,6 +217,24 @@ typedef struct kge_grads {
   int32_t n_peers;
   float* peer[KGE_MAX_PEERS][KGE_MAX_TABLES];
   float* peer_scal[KGE_MAX_PEERS];
+  /* Owner-partitioned form of the fused exchange (n_peers > 0 and owner_rows[s] > 0 for every used
+   * slot): rank j owns rows [j * owner_rows[s], (j+1) * owner_rows[s]) of table s — a reduce-scatter /
+   * all-gather carried by the kernels' own stores instead of an all-reduce.
+   *   kge_train_grad : the row sum of row r goes to peer[r / owner_rows[s]][s] ONLY.
+   *   (caller)       : cross-GPU barrier.
+   *   kge_train_apply: this rank (owner_rank) sums the n_peers slots of ITS rows in rank order,
+   *                    applies clip + Adam with its own m, v (m, v of rows it does not own are never
+   *                    touched and stay zero) and stores the new row into w_peer[j][s] of EVERY rank
+   *                    (and normalise(row) into wn_peer[j] when the shadow table is in use): the tables
+   *                    must live in peer-mapped memory.  w_peer[owner_rank][s] == tables.t[s].w.
+   *   (caller)       : cross-GPU barrier before the next step gathers.
+   * Per rank and step the NVLink traffic is one gradient table out and (n_peers - 1) / n_peers of a
+   * weight table out, and the update work is divided by n_peers; replicas are identical by
+   * construction.  Vector models without a dense regulariser. */
+  int32_t owner_rank;
+  int32_t owner_rows[KGE_MAX_TABLES];
+  float* w_peer[KGE_MAX_PEERS][KGE_MAX_TABLES];
+  float* wn_peer[KGE_MAX_PEERS];
 } kge_grads;
 int kge_train_grad(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const kge_dp*,
                    const void* triples, int64_t B, uint64_t seed, uint64_t step,

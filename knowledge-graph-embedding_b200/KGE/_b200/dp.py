@@ -88,6 +88,49 @@ class GradBuffer:
         return self
 
 
+class PeerTables:
+    """Weight tables (and the entity table's shadow `wn`) of one rank in peer-mapped memory, for the
+    owner-partitioned exchange (kge_grads.owner_rows): the owner of a row stores the updated row into
+    every rank's table.  Layout [slot a: w | slot a: wn | slot b: w | ...] in floats, 256-byte aligned
+    sections; `tables` = {slot: (rows, ld)}, `wn_slots` = slots that carry a shadow table."""
+
+    def __init__(self, tables, wn_slots=()):
+        self.off, o = {}, 0
+        for s in sorted(tables):
+            rows, ld = tables[s]
+            for kind in ("w", "wn") if s in wn_slots else ("w",):
+                self.off[(kind, s)] = (o, rows, ld)
+                o += (rows * ld + 63) // 64 * 64
+        self.numel = o
+        self.buf, self.base_ptrs, self._keep = None, None, None
+
+    def view(self, kind, s):
+        o, rows, ld = self.off[(kind, s)]
+        return self.buf[o:o + rows * ld].view(rows, ld)
+
+    def addr(self, owner, kind, s):
+        return self.base_ptrs[owner] + 4 * self.off[(kind, s)][0]
+
+    @classmethod
+    def local(cls, tables, wn_slots, world_size, device):
+        """Emulated ranks that share ONE replica (tests): every 'peer' is the same buffer."""
+        t = cls(tables, wn_slots)
+        t.buf = torch.zeros(max(t.numel, 1), dtype=torch.float32, device=device)
+        t.base_ptrs = [t.buf.data_ptr()] * world_size
+        return t
+
+    @classmethod
+    def symmetric(cls, tables, wn_slots, device, group=None):
+        import torch.distributed._symmetric_memory as sm
+        t = cls(tables, wn_slots)
+        t.buf = sm.empty(max(t.numel, 1), dtype=torch.float32, device=device)
+        hdl = sm.rendezvous(t.buf, group=group if group is not None else dist.group.WORLD)
+        t.buf.zero_()
+        t.base_ptrs = [int(p) for p in hdl.buffer_ptrs]
+        t._keep = hdl
+        return t
+
+
 class PeerStaging:
     """Staging memory of the fused exchange, identical on every rank:
     [2 step parities][world slots][table 0 | .. | table 3 | scal(8)] fp32.
@@ -96,7 +139,7 @@ class PeerStaging:
     device in tests).  `push(parity)` / `slots(parity)` fill the `peer` fields of kge_grads for
     kge_train_grad / kge_train_apply (include/kge_abi.h)."""
 
-    def __init__(self, tables, world_size, rank, base_ptrs=None, barrier=None, keep=None):
+    def __init__(self, tables, world_size, rank, base_ptrs=None, barrier=None, keep=None, ptabs=None):
         from . import lib as L
         if not (1 <= world_size <= L.KGE_MAX_PEERS):
             raise ValueError(f"peer exchange supports up to {L.KGE_MAX_PEERS} ranks")
@@ -114,6 +157,9 @@ class PeerStaging:
         self.barrier = barrier
         self._keep = keep                                           # owners of the memory
         self._cache = {}
+        # owner-partitioned exchange: rank j owns rows [j * owner_rows[s], (j+1) * owner_rows[s]) of table s
+        self.ptabs = ptabs
+        self.owner_rows = {s: -(-tables[s][0] // self.world) for s in tables}
 
     def numel(self):
         return 2 * self.world * self.per
@@ -132,6 +178,14 @@ class PeerStaging:
                 for s, off in self.offsets.items():
                     G.peer[j][s] = self._addr(owner, parity, slot, off)
                 G.peer_scal[j] = self._addr(owner, parity, slot, self.scal_off)
+            if self.ptabs is not None:
+                G.owner_rank = self.rank
+                for s in self.offsets:
+                    G.owner_rows[s] = self.owner_rows[s]
+                    for j in range(self.world):
+                        G.w_peer[j][s] = self.ptabs.addr(j, "w", s)
+                        if ("wn", s) in self.ptabs.off:
+                            G.wn_peer[j] = self.ptabs.addr(j, "wn", s)
             self._cache[key] = G
         return self._cache[key]
 
@@ -144,14 +198,17 @@ class PeerStaging:
         return self._grads(parity & 1, False)
 
     @classmethod
-    def symmetric(cls, tables, device, group=None):
+    def symmetric(cls, tables, device, group=None, wn_slots=None):
         """Staging in torch symmetric memory (CUDA VMM peer mappings over NVLink), or None when
-        any rank cannot set it up (the caller then keeps the NCCL all-reduce)."""
+        any rank cannot set it up (the caller then keeps the NCCL all-reduce).  wn_slots not None:
+        owner-partitioned exchange — the weight tables get peer-mapped memory too (`ptabs`)."""
         rank, world_size = world()
         ok, st = 1, None
         try:
             import torch.distributed._symmetric_memory as sm
             st = cls(tables, world_size, rank)
+            if wn_slots is not None:
+                st.ptabs = PeerTables.symmetric(tables, wn_slots, device, group)
             buf = sm.empty(st.numel(), dtype=torch.float32, device=device)
             hdl = sm.rendezvous(buf, group=group if group is not None else dist.group.WORLD)
             buf.zero_()
@@ -170,11 +227,18 @@ class PeerStaging:
         return st
 
 
-def exchange_kind(world_size):
-    """'peer' (kernel stores into peer staging + one barrier) or 'nccl' (all-reduce of the flat
-    buffer).  Peer stores cost world x the gradient bytes per rank, so the default switches to
-    NCCL beyond 4 ranks; KGE_DP_EXCHANGE=peer|nccl overrides."""
+def exchange_kind(world_size, dense_regulariser=False):
+    """'owner' (reduce-scatter / all-gather carried by kernel stores into peer memory: row sums go to
+    the row's owner, the owner updates and stores the new row into every replica; two barriers),
+    'peer' (row sums stored into every rank's staging, every rank updates everything; one barrier)
+    or 'nccl' (all-reduce of the flat buffer).  Default: owner wherever it applies (per-rank NVLink
+    bytes and update work do not grow with the number of ranks); KGE_DP_EXCHANGE=owner|peer|nccl
+    overrides."""
     e = os.environ.get("KGE_DP_EXCHANGE", "")
-    if e in ("peer", "nccl"):
+    if e in ("peer", "nccl") or (e == "owner" and not dense_regulariser):
         return e
-    return "peer" if 2 <= world_size <= 4 else "nccl"
+    if world_size < 2:
+        return "nccl"
+    if not dense_regulariser:
+        return "owner"
+    return "peer" if world_size <= 4 else "nccl"

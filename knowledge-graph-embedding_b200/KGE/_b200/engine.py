@@ -287,12 +287,19 @@ class Engine:
         from . import dp as _dp
         rank, world_size = _dp.world()
         if getattr(self, "_dp_kind", None) is None:
-            self._dp_kind, self._peer, self._gbuf, self._dp_steps = _dp.exchange_kind(world_size), None, None, 0
-            if self._dp_kind == "peer":
-                self._peer = _dp.PeerStaging.symmetric({s: (pt.rows, pt.ld) for s, pt in self.tab.items()},
-                                                       self.device, group)
+            dense_reg = bool(self.cfg.constraint) and self.cfg.model in (L.TRANSH, L.RESCAL)
+            self._dp_kind, self._peer, self._gbuf, self._dp_steps = _dp.exchange_kind(world_size, dense_reg), None, None, 0
+            if self._dp_kind in ("peer", "owner"):
+                layout = {s: (pt.rows, pt.ld) for s, pt in self.tab.items()}
+                wn_slots = None
+                if self._dp_kind == "owner":
+                    wn_slots = [s for s, pt in self.tab.items() if pt.wn is not None]
+                self._peer = _dp.PeerStaging.symmetric(layout, self.device, group, wn_slots=wn_slots)
                 if self._peer is None:
                     self._dp_kind = "nccl"
+                elif self._dp_kind == "owner":
+                    self.adopt_peer_tables(self._peer.ptabs)
+                    self._peer.barrier()
             if self._dp_kind == "nccl":
                 self._gbuf = self.grad_buffer()
         if self._dp_kind == "peer":
@@ -302,9 +309,32 @@ class Engine:
             self.train_grad(self._peer.push(par), triples_local, seed, step, B_global, i_base, rank, world_size, neg_override)
             self._peer.barrier()
             return self.train_apply(self._peer.slots(par), len(triples_local), loss_out)
+        if self._dp_kind == "owner":
+            # row sums to the rows' owners; barrier; every owner updates its rows and stores them into
+            # every replica; barrier (the next step gathers rows other ranks wrote)
+            par = self._dp_steps & 1
+            self._dp_steps += 1
+            self.train_grad(self._peer.push(par), triples_local, seed, step, B_global, i_base, rank, world_size, neg_override)
+            self._peer.barrier()
+            out = self.train_apply(self._peer.slots(par), len(triples_local), loss_out)
+            self._peer.barrier()
+            return out
         self.train_grad(self._gbuf, triples_local, seed, step, B_global, i_base, rank, world_size, neg_override)
         self._gbuf.allreduce(group)                       # the step's single collective
         return self.train_apply(self._gbuf, len(triples_local), loss_out)
+
+    def adopt_peer_tables(self, ptabs):
+        """Move the weight tables (and shadow tables) into peer-mapped memory (dp.PeerTables)."""
+        for s, pt in self.tab.items():
+            region = ptabs.view("w", s)
+            region.copy_(pt.storage)
+            pt.storage = region
+            if pt.wn is not None and ("wn", s) in ptabs.off:
+                rn = ptabs.view("wn", s)
+                rn.copy_(pt.wn)
+                pt.wn = rn
+        self._tables_cache = {}
+        self._ptabs = ptabs
 
     def score(self, h, r, t):
         self.flush()

@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 5
+KGE_ABI_VERSION = 6
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -60,7 +60,9 @@ KGE_MAX_PEERS = 8
 class Grads(C.Structure):
     _fields_ = [("dense", C.c_void_p * KGE_MAX_TABLES), ("ent_rows", C.c_void_p),
                 ("ent_vals", C.c_void_p * 2), ("cap", C.c_int64), ("lists", C.c_int32), ("n_peers", C.c_int32),
-                ("peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("peer_scal", C.c_void_p * KGE_MAX_PEERS)]
+                ("peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("peer_scal", C.c_void_p * KGE_MAX_PEERS),
+                ("owner_rank", C.c_int32), ("owner_rows", C.c_int32 * KGE_MAX_TABLES),
+                ("w_peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("wn_peer", C.c_void_p * KGE_MAX_PEERS)]
 
 
 class Shard(C.Structure):

@@ -390,6 +390,12 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
                 "row-sparse gradient lists are reserved");
     int gcols[KGE_MAX_TABLES];
     expected_cols(cfg, gcols);
+    for (int s = 0; s < KGE_MAX_TABLES; ++s)
+      if (gcols[s] && grads_out->owner_rows[s] != 0)
+        KGE_REQUIRE(grads_out->n_peers > 0 && grads_out->owner_rows[s] > 0 &&
+                        (int64_t) grads_out->owner_rows[s] * grads_out->n_peers >= (s < 2 ? cfg->n_ent : cfg->n_rel),
+                    KGE_EINVAL, "grads.owner_rows[%d] = %d does not cover the table over %d ranks", s,
+                    grads_out->owner_rows[s], grads_out->n_peers);
     for (int s = 0; s < KGE_MAX_TABLES; ++s) {
       if (!gcols[s]) continue;
       if (sh && (s < 2 || shard_phase == 1)) continue;
@@ -680,10 +686,12 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     U.slot = s;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
     U.n_peer = 0;
+    U.owner_rows = 0; U.row_lo = 0; U.n_out = 0;
     if (grad_only) {
       if (grads_out->n_peers > 0) {
         U.n_peer = grads_out->n_peers;
         for (int j = 0; j < U.n_peer; ++j) U.peer[j] = grads_out->peer[j][s];
+        U.owner_rows = grads_out->owner_rows[s];
       } else { U.n_peer = 1; U.peer[0] = grads_out->dense[s]; }
     }
     U.w_in = (shadow_use && s == KGE_T_ENT) ? tables->t[s].wn : tables->t[s].w;
@@ -917,6 +925,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     U.rec_ld = 0; U.key_base = 0; U.rec_base = 0;
     U.slot = s;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
+    U.owner_rows = 0; U.row_lo = 0; U.n_out = 0;
     if (g->n_peers > 0) {
       U.n_peer = g->n_peers;
       for (int j = 0; j < U.n_peer; ++j) {
@@ -930,6 +939,27 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     }
     U.w_in = (shadow_ok && tables->wn_valid[KGE_T_ENT] && s == KGE_T_ENT) ? tables->t[s].wn : tables->t[s].w;
     U.wn_out = (shadow_ok && s == KGE_T_ENT && !dense) ? tables->t[s].wn : nullptr;
+    if (g->n_peers > 0 && g->owner_rows[s] != 0) {        // owner-partitioned: my rows only, new rows to every rank
+      KGE_REQUIRE(!dense, KGE_EUNSUPPORTED, "owner-partitioned exchange: no dense regulariser");
+      KGE_REQUIRE(g->owner_rows[s] > 0 && g->owner_rank >= 0 && g->owner_rank < g->n_peers &&
+                      (int64_t) g->owner_rows[s] * g->n_peers >= U.rows, KGE_EINVAL, "bad grads.owner_rows / owner_rank");
+      U.owner_rows = g->owner_rows[s];
+      U.row_lo = (int64_t) g->owner_rank * g->owner_rows[s];
+      int64_t hi = U.row_lo + g->owner_rows[s];
+      if (hi > U.rows) hi = U.rows;
+      U.rows = hi > U.row_lo ? hi - U.row_lo : 0;
+      U.n_out = g->n_peers;
+      for (int j = 0; j < U.n_out; ++j) {
+        KGE_REQUIRE(g->w_peer[j][s] && ((uintptr_t) g->w_peer[j][s] & 15) == 0, KGE_EINVAL, "grads.w_peer[%d][%d] missing", j, s);
+        U.w_outs[j] = g->w_peer[j][s];
+        U.wn_outs[j] = nullptr;
+        if (U.wn_out) {
+          KGE_REQUIRE(g->wn_peer[j] && ((uintptr_t) g->wn_peer[j] & 15) == 0, KGE_EINVAL, "grads.wn_peer[%d] missing", j);
+          U.wn_outs[j] = g->wn_peer[j];
+        }
+      }
+      KGE_REQUIRE(g->w_peer[g->owner_rank][s] == tables->t[s].w, KGE_EINVAL, "grads.w_peer[owner_rank][%d] is not this rank's table", s);
+    }
     if (dense) {            // TransH only (RESCAL is a matrix model)
       if (s == KGE_T_ENT) U.dense_kind = DK_TRANSH_ENT;
       else {
@@ -1076,6 +1106,7 @@ extern "C" int kge_shard_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     U.rec_ld = 0; U.key_base = 0; U.rec_base = 0; U.slot = s;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
     U.n_peer = 1; U.peer[0] = g->dense[s];
+    U.owner_rows = 0; U.row_lo = 0; U.n_out = 0;
     U.w_in = tables->t[s].w; U.wn_out = nullptr;
     up.total_rows += U.rows;
     max_ch = ((U.cols + 3) / 4 > max_ch) ? (U.cols + 3) / 4 : max_ch;

@@ -146,9 +146,22 @@ struct UpdateTable {
   // apply half adds the n_peer sources to the record sum in index order.
   float* peer[KGE_MAX_PEERS];
   int n_peer;
+  // owner-partitioned exchange (kge_grads.owner_rows): gradient half sends row r to peer[r / owner_rows]
+  // only; apply half works on rows [row_lo, row_lo + rows) and stores the new row to all n_out tables
+  int owner_rows;
+  int64_t row_lo;
+  int n_out;
+  float* w_outs[KGE_MAX_PEERS];
+  float* wn_outs[KGE_MAX_PEERS];
 };
 template <int CPL>
 __device__ __forceinline__ void store_peers(const UpdateTable& T, int64_t row, int nch, int lane, const float4 (&g)[CPL]) {
+  if (T.owner_rows > 0) {                          // reduce-scatter: the row's owner only
+    float4* o = reinterpret_cast<float4*>(T.peer[row / T.owner_rows] + row * (int64_t) T.ld);
+#pragma unroll
+    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) o[c] = g[u]; }
+    return;
+  }
   for (int j = 0; j < T.n_peer; ++j) {
     float4* o = reinterpret_cast<float4*>(T.peer[j] + row * (int64_t) T.ld);
 #pragma unroll
@@ -432,14 +445,26 @@ __device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTabl
     float4 w = wi[c], m = m4[c], v = v4[c];
     adam_chunk(w, m, v, scale4(scale, g[u]), p.beta1, p.beta2, p.lr_t, p.eps);
     mask_tail(w, m, v, c, T.cols);
-    m4[c] = m; v4[c] = v; w4[c] = w;
+    m4[c] = m; v4[c] = v;
+    if (T.n_out == 0) w4[c] = w;
+    else for (int j = 0; j < T.n_out; ++j) reinterpret_cast<float4*>(T.w_outs[j] + row * (int64_t) T.ld)[c] = w;   // all-gather by stores
     wnew[u] = w;
   }
   if (T.wn_out != nullptr) {                       // warp-uniform
     const float nrm = sqrtf(row_sumsq<CPL>(wnew));
-    float4* o = reinterpret_cast<float4*>(T.wn_out + row * (int64_t) T.ld);
+    if (T.n_out == 0) {
+      float4* o = reinterpret_cast<float4*>(T.wn_out + row * (int64_t) T.ld);
 #pragma unroll
-    for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) o[c] = div4(wnew[u], nrm); }
+      for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) o[c] = div4(wnew[u], nrm); }
+    } else {
+#pragma unroll
+      for (int u = 0; u < CPL; ++u) {
+        const int c = lane + 32 * u;
+        if (c >= nch) continue;
+        const float4 q = div4(wnew[u], nrm);
+        for (int j = 0; j < T.n_out; ++j) reinterpret_cast<float4*>(T.wn_outs[j] + row * (int64_t) T.ld)[c] = q;
+      }
+    }
   }
 }
 
@@ -462,6 +487,8 @@ __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
   int j = 0;
   while (j < p.n_tabs - 1 && row >= p.tab[j].rows) { row -= p.tab[j].rows; ++j; }
   const UpdateTable& T = p.tab[j];
+  if (row >= T.rows) return;                       // owner-partitioned apply: the last table may own no rows
+  row += T.row_lo;
   const int nch = (T.cols + 3) >> 2;
   const float4* w4 = reinterpret_cast<const float4*>(T.w_in + row * (int64_t) T.ld);
   const float4* m4 = reinterpret_cast<const float4*>(T.m + row * (int64_t) T.ld);

@@ -31,12 +31,16 @@ def main():
     multi = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)
     single = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)
     nccl = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)      # same steps over the NCCL all-reduce
+    owner = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)     # owner-partitioned exchange
     ok = True
     for step in range(5):
         X = np.stack([rng.integers(0, N, B), rng.integers(0, R, B), rng.integers(0, N, B)], 1)
         lo, hi = dp.batch_shard(B)
         os.environ["KGE_DP_EXCHANGE"] = "peer"
         lm = multi.train_step_dp(X[lo:hi], 11, step, B, lo)
+        os.environ["KGE_DP_EXCHANGE"] = "owner"
+        lo_ = owner.train_step_dp(X[lo:hi], 11, step, B, lo)
+        ok &= float(lm.item()) == float(lo_.item())          # both sum the rank slots in rank order
         os.environ["KGE_DP_EXCHANGE"] = "nccl"
         ln = nccl.train_step_dp(X[lo:hi], 11, step, B, lo)
         os.environ.pop("KGE_DP_EXCHANGE")
@@ -54,8 +58,12 @@ def main():
         ok &= all(torch.equal(gathered[0], t) for t in gathered)            # replicas bit-identical
         if world == 2:
             ok &= bool(torch.equal(mine, nccl.tab[s].storage))
+        ok &= bool(torch.equal(mine, owner.tab[s].storage))   # owner-partitioned == store-to-all, any world size
+        go = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(go, owner.tab[s].storage.contiguous())
+        ok &= all(torch.equal(go[0], t) for t in go)
     if rank == 0:
-        print("exchange kinds:", multi._dp_kind, nccl._dp_kind)
+        print("exchange kinds:", multi._dp_kind, nccl._dp_kind, owner._dp_kind)
     # sharded evaluation: counts over this rank's entity slice, summed == one-GPU counts
     Q = np.stack([rng.integers(0, N, 300), rng.integers(0, R, 300), rng.integers(0, N, 300)], 1)
     posX = np.concatenate([Q, np.stack([rng.integers(0, N, 4000), rng.integers(0, R, 4000), rng.integers(0, N, 4000)], 1)])

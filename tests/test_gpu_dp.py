@@ -109,3 +109,49 @@ def test_peer_staging_equals_allreduce(case, G):
         assert float(la.item()) == float(lb.item())
         for s in a.tab:
             assert torch.equal(a.tab[s].storage, b.tab[s].storage), (step, s)
+
+
+@pytest.mark.parametrize("G", [2, 3, 8])
+@pytest.mark.parametrize("case", [CASES[0], CASES[1], CASES[4]], ids=["TransE", "DistMult", "TransD"])
+def test_owner_partitioned_exchange_equals_allreduce(case, G):
+    """kge_grads.owner_rows: row sums go to the row's owner only, every emulated owner applies its rows
+    and stores them into 'every replica' (one shared replica here).  Against the all-reduce emulation
+    the weights — and the shadow table — must be bit-identical; m / v too (each row updated once)."""
+    model, score, loss, k, side, d, constraint = case
+    rng = np.random.default_rng(15)
+    _, _, a = make_pair(model, N, R, d, score=score, loss=loss, k=k, side=side, constraint=constraint)
+    _, _, b = make_pair(model, N, R, d, score=score, loss=loss, k=k, side=side, constraint=constraint)
+    layout = {s: (pt.rows, pt.ld) for s, pt in b.tab.items()}
+    ptabs = dp.PeerTables.local(layout, [s for s, pt in b.tab.items() if pt.wn is not None], G, b.device)
+    b.adopt_peer_tables(ptabs)
+    probe = dp.PeerStaging(layout, G, 0)
+    stage = [torch.full((probe.numel(),), 7.0, device=b.device) for _ in range(G)]
+    ranks = [dp.PeerStaging(layout, G, g, base_ptrs=[t.data_ptr() for t in stage], ptabs=ptabs) for g in range(G)]
+    bufs = [a.grad_buffer() for _ in range(G)]
+    B, seed = 48, 8
+    for step in range(4):
+        X = rand_triples(rng, B, N, R)
+        if step == 2:                             # a validation batch in between (drops the shadow table)
+            assert float(a.train_step(X, seed, 77, is_train=False).item()) == float(b.train_step(X, seed, 77, is_train=False).item())
+        for g in range(G):
+            lo, hi = dp.split_even(B, G, g)
+            a.train_grad(bufs[g], X[lo:hi], seed, step, B, lo, g, G)
+            b.train_grad(ranks[g].push(step), X[lo:hi], seed, step, B, lo, g, G)
+        acc = torch.zeros_like(bufs[0].flat)
+        for g in range(G):
+            acc += bufs[g].flat
+        bufs[0].flat.copy_(acc)
+        la = a.train_apply(bufs[0], hi - lo)
+        t0, valid0 = b.adam_t, {s: pt.wn_valid for s, pt in b.tab.items()}
+        for g in range(G):                        # every owner applies its rows (each from the pre-step state)
+            b.adam_t = t0
+            for s, pt in b.tab.items():
+                pt.wn_valid = valid0[s]
+            lb = b.train_apply(ranks[g].slots(step), hi - lo)
+        assert float(la.item()) == float(lb.item())
+        for s in a.tab:
+            assert torch.equal(a.tab[s].storage, b.tab[s].storage), (step, s)
+            assert torch.equal(a.tab[s].m, b.tab[s].m) and torch.equal(a.tab[s].v, b.tab[s].v), (step, s)
+        if a.tab[0].wn is not None:
+            assert a.tab[0].wn_valid and b.tab[0].wn_valid
+            assert torch.equal(a.tab[0].wn, b.tab[0].wn), step
