@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 6
+#define KGE_ABI_VERSION 7
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -236,6 +236,27 @@ typedef struct kge_grads {
   float* w_peer[KGE_MAX_PEERS][KGE_MAX_TABLES];
   float* wn_peer[KGE_MAX_PEERS];
 } kge_grads;
+/* Cross-GPU barrier over peer memory, enqueued on `stream` like a kernel (no host involvement):
+ * flags[j] = rank j's flag array (uint32[KGE_MAX_PEERS], zeroed once) as mapped HERE.  Every rank calls
+ * it with the same strictly increasing `epoch`: the kernel fences its stream's earlier stores at system
+ * scope, stores epoch into flags[j][rank] of every peer and spins until flags[rank][j] >= epoch for all
+ * j.  The spin is bounded (~2 s): on expiry flags[rank][KGE_MAX_PEERS - 1 ... ] is left untouched and
+ * the kernel exits with error word flags[rank][world] = 0xdead (world < KGE_MAX_PEERS) so a lost peer
+ * cannot hang the GPU. */
+typedef struct kge_peer_flags {
+  int32_t world, rank;
+  uint32_t* flags[KGE_MAX_PEERS];
+} kge_peer_flags;
+int kge_peer_barrier(kge_ctx*, const kge_peer_flags*, uint32_t epoch, void* stream);
+
+/* One data-parallel step in ONE call (host work of a single-GPU step): kge_train_grad(push) ->
+ * kge_peer_barrier(epoch) -> kge_train_apply(slots) -> kge_peer_barrier(epoch + 1).  `push` / `slots`
+ * are the kge_grads of the two halves (n_peers > 0: peer staging, store-to-all or owner-partitioned). */
+int kge_train_step_dp(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const kge_dp*,
+                      const void* triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
+                      kge_grads* push, const kge_grads* slots, const kge_peer_flags*, uint32_t epoch,
+                      float* loss_out, void* ws, size_t ws_bytes, void* stream);
+
 int kge_train_grad(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const kge_dp*,
                    const void* triples, int64_t B, uint64_t seed, uint64_t step,
                    const int64_t* neg_override, kge_grads* out, float* scal_out /* [8] device */,

@@ -162,7 +162,17 @@ class PeerStaging:
         self.owner_rows = {s: -(-tables[s][0] // self.world) for s in tables}
 
     def numel(self):
-        return 2 * self.world * self.per
+        return 2 * self.world * self.per + 64          # + the flag words of kge_peer_barrier
+
+    def peer_flags(self):
+        """kge_peer_flags over the last 64 words of every rank's staging buffer (zeroed at set-up)."""
+        from . import lib as L
+        if "flags" not in self._cache:
+            F = L.PeerFlags(world=self.world, rank=self.rank)
+            for j in range(self.world):
+                F.flags[j] = self.base_ptrs[j] + 4 * (2 * self.world * self.per)
+            self._cache["flags"] = F
+        return self._cache["flags"]
 
     def _addr(self, owner, parity, slot, off):
         return self.base_ptrs[owner] + 4 * ((parity * self.world + slot) * self.per + off)

@@ -4,6 +4,7 @@ torch is plumbing only: it owns device memory (tables, Adam slots, workspace) an
 stream; every computation on the hot path is a kernel of the library.
 """
 import ctypes as C
+import os
 import math
 import numpy as np
 import torch
@@ -302,6 +303,25 @@ class Engine:
                     self._peer.barrier()
             if self._dp_kind == "nccl":
                 self._gbuf = self.grad_buffer()
+        if self._dp_kind in ("peer", "owner") and neg_override is None and os.environ.get("KGE_DP_ONE_CALL", "1") != "0":
+            # grad -> barrier kernel -> apply -> barrier kernel enqueued by ONE library call (kge_train_step_dp)
+            par = self._dp_steps & 1
+            self._dp_steps += 1
+            X = self._ids(triples_local)
+            B = X.shape[0]
+            ws = self._workspace(B, 0)
+            if loss_out is None:
+                loss_out = torch.empty(1, dtype=torch.float32, device=self.device)
+            dpd = L.Dp(world=world_size, rank=rank, B_global=B_global, i_base=i_base)
+            self.adam_t += 1
+            T = self._tables(with_opt=True)
+            self._dp_epoch = getattr(self, "_dp_epoch", 0) + 2
+            L.check(L.load().kge_train_step_dp(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler), C.byref(dpd),
+                                               _ptr(X), B, seed, step, self.adam_t, C.byref(self._peer.push(par)),
+                                               C.byref(self._peer.slots(par)), C.byref(self._peer.peer_flags()),
+                                               self._dp_epoch - 1, _ptr(loss_out), _ptr(ws), ws.numel(), _stream()))
+            self._sync_shadow(T)
+            return loss_out
         if self._dp_kind == "peer":
             # gradient kernels store into every rank's staging slot; one barrier; sum of the slots
             par = self._dp_steps & 1

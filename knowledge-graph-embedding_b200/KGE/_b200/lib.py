@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 6
+KGE_ABI_VERSION = 7
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -65,6 +65,10 @@ class Grads(C.Structure):
                 ("w_peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("wn_peer", C.c_void_p * KGE_MAX_PEERS)]
 
 
+class PeerFlags(C.Structure):
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("flags", C.c_void_p * KGE_MAX_PEERS)]
+
+
 class Shard(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("shard_rows", C.c_int64), ("cap", C.c_int64),
                 ("w_peer", (C.c_void_p * 2) * KGE_MAX_PEERS), ("ids_peer", C.c_void_p * KGE_MAX_PEERS),
@@ -76,7 +80,8 @@ SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destr
            "kge_workspace_bytes", "kge_sample_negatives", "kge_score", "kge_constrain_table",
            "kge_train_step", "kge_train_step_host", "kge_train_grad", "kge_train_apply", "kge_rank", "kge_profile_begin", "kge_profile_end",
            "kge_set_option", "kge_flush_rows",
-           "kge_shard_lookup", "kge_shard_pre", "kge_shard_grad", "kge_shard_apply"]
+           "kge_shard_lookup", "kge_shard_pre", "kge_shard_grad", "kge_shard_apply",
+           "kge_peer_barrier", "kge_train_step_dp"]
 
 _LIB = None
 
@@ -123,6 +128,10 @@ def load():
                                  C.POINTER(Dp), vp, i64, u64, u64, vp, C.POINTER(Grads), vp, vp, vp, C.c_size_t, vp]
     L.kge_shard_apply.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Shard), C.POINTER(Grads), vp, i64,
                                   u64, vp, vp, C.c_size_t, vp]
+    L.kge_peer_barrier.argtypes = [vp, C.POINTER(PeerFlags), C.c_uint32, vp]
+    L.kge_train_step_dp.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Dp), vp, i64,
+                                    u64, u64, u64, C.POINTER(Grads), C.POINTER(Grads), C.POINTER(PeerFlags), C.c_uint32,
+                                    vp, vp, C.c_size_t, vp]
     L.kge_flush_rows.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp]
     L.kge_set_option.argtypes = [vp, i32, i32]
     L.kge_profile_begin.argtypes = [vp, i32]

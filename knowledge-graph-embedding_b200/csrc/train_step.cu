@@ -1131,3 +1131,54 @@ extern "C" int kge_shard_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   pt.end(4);
   return KGE_OK;
 }
+
+// ---- cross-GPU barrier over peer memory + the one-call data-parallel step -----------------------
+namespace kge {
+struct PeerFlagsDev { int world, rank; uint32_t* flags[KGE_MAX_PEERS]; };
+__global__ void k_peer_barrier(PeerFlagsDev f, uint32_t epoch) {
+  const int j = threadIdx.x;
+  if (j >= f.world) return;
+  __threadfence_system();                                        // this stream's earlier stores first
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f.flags[j] + f.rank), "r"(epoch) : "memory");
+  const uint32_t* mine = f.flags[f.rank] + j;
+  const long long t0 = clock64();
+  uint32_t v;
+  do {
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+    if (v >= epoch) break;
+    if (clock64() - t0 > 4000000000ll) {                         // ~2 s: a peer is gone; do not hang the GPU
+      if (f.world < KGE_MAX_PEERS) f.flags[f.rank][f.world] = 0xdeadu;
+      break;
+    }
+  } while (true);
+  __threadfence_system();
+}
+}  // namespace kge
+
+extern "C" int kge_peer_barrier(kge_ctx* ctx_, const kge_peer_flags* pf, uint32_t epoch, void* stream) {
+  KGE_REQUIRE(ctx_ && pf, KGE_EINVAL, "ctx / flags is NULL");
+  KGE_REQUIRE(pf->world >= 1 && pf->world <= KGE_MAX_PEERS && pf->rank >= 0 && pf->rank < pf->world, KGE_EINVAL,
+              "bad kge_peer_flags (world %d rank %d)", pf->world, pf->rank);
+  PeerFlagsDev f;
+  f.world = pf->world; f.rank = pf->rank;
+  for (int j = 0; j < KGE_MAX_PEERS; ++j) {
+    f.flags[j] = pf->flags[j];
+    KGE_REQUIRE(j >= pf->world || pf->flags[j], KGE_EINVAL, "kge_peer_flags.flags[%d] is NULL", j);
+  }
+  k_peer_barrier<<<1, 32, 0, (cudaStream_t) stream>>>(f, epoch);
+  KGE_CUDA_OK(cudaGetLastError());
+  return KGE_OK;
+}
+
+extern "C" int kge_train_step_dp(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                                 const kge_dp* dp, const void* triples, int64_t B, uint64_t seed, uint64_t step,
+                                 uint64_t adam_t, kge_grads* push, const kge_grads* slots, const kge_peer_flags* pf,
+                                 uint32_t epoch, float* loss_out, void* ws, size_t ws_bytes, void* stream) {
+  KGE_REQUIRE(push && slots && push->n_peers > 0 && slots->n_peers > 0, KGE_EINVAL,
+              "kge_train_step_dp needs the peer-staging form of kge_grads");
+  if (int rc = kge_train_grad(ctx, cfg, tables, smp, dp, triples, B, seed, step, nullptr, push, nullptr, nullptr, ws,
+                              ws_bytes, stream)) return rc;
+  if (int rc = kge_peer_barrier(ctx, pf, epoch, stream)) return rc;
+  if (int rc = kge_train_apply(ctx, cfg, tables, slots, nullptr, B, adam_t, loss_out, ws, ws_bytes, stream)) return rc;
+  return kge_peer_barrier(ctx, pf, epoch + 1, stream);
+}

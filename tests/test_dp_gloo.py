@@ -105,7 +105,7 @@ def test_peer_staging_addresses():
     bases = [1 << 20, 2 << 20, 3 << 20]
     ranks = [dp.PeerStaging(layout, G, r, base_ptrs=bases) for r in range(G)]
     per = ranks[0].per
-    assert per % 64 == 0 and per >= 10 * 8 + 3 * 8 + 8 and ranks[0].numel() == 2 * G * per
+    assert per % 64 == 0 and per >= 10 * 8 + 3 * 8 + 8 and ranks[0].numel() == 2 * G * per + 64
     for par in (0, 1):
         for r in range(G):
             P, S = ranks[r].push(par), ranks[r].slots(par)
@@ -119,4 +119,35 @@ def test_peer_staging_addresses():
                 assert bases[r] <= S.peer[j][0] < bases[r] + 4 * ranks[r].numel()
     a0, a1 = ranks[1].slots(0), ranks[1].slots(1)
     assert a1.peer[0][0] - a0.peer[0][0] == 4 * G * per
-    assert dp.exchange_kind(2) == "peer" and dp.exchange_kind(8) == "nccl" and dp.exchange_kind(1) == "nccl"
+    assert dp.exchange_kind(2) == "owner" and dp.exchange_kind(8) == "owner" and dp.exchange_kind(1) == "nccl"
+    assert dp.exchange_kind(2, dense_regulariser=True) == "peer" and dp.exchange_kind(8, dense_regulariser=True) == "nccl"
+    F = ranks[1].peer_flags()                       # kge_peer_barrier's flag words: after both parities of every rank
+    assert F.world == G and F.rank == 1
+    assert [F.flags[j] for j in range(G)] == [bases[j] + 4 * 2 * G * per for j in range(G)]
+
+
+def test_owner_partitioned_exchange_host_logic():
+    """kge_grads.owner_rows / w_peer / wn_peer as PeerStaging fills them, and the PeerTables layout."""
+    from KGE._b200 import dp
+    layout = {0: (10, 8), 2: (3, 8)}
+    G = 4
+    pt = dp.PeerTables(layout, wn_slots=[0])
+    assert set(pt.off) == {("w", 0), ("wn", 0), ("w", 2)}
+    offs = sorted(v[0] for v in pt.off.values())
+    assert offs == [0, 128, 256] and pt.numel == 320              # 256-byte aligned sections
+    pt.base_ptrs = [j << 24 for j in range(1, G + 1)]
+    st = [dp.PeerStaging(layout, G, r, base_ptrs=[j << 20 for j in range(1, G + 1)], ptabs=pt) for r in range(G)]
+    assert st[0].owner_rows == {0: 3, 2: 1}                         # ceil(rows / world)
+    for r in range(G):
+        for Gs in (st[r].push(0), st[r].slots(1)):
+            assert Gs.owner_rank == r and list(Gs.owner_rows) == [3, 0, 1, 0]
+            for j in range(G):
+                assert Gs.w_peer[j][0] == pt.base_ptrs[j] + 4 * pt.off[("w", 0)][0]
+                assert Gs.w_peer[j][2] == pt.base_ptrs[j] + 4 * pt.off[("w", 2)][0]
+                assert Gs.wn_peer[j] == pt.base_ptrs[j] + 4 * pt.off[("wn", 0)][0]
+    # every row has exactly one owner and the owners tile the table
+    for s, (rows, _) in layout.items():
+        owners = [r // st[0].owner_rows[s] for r in range(rows)]
+        assert max(owners) < G and owners == sorted(owners)
+    plain = dp.PeerStaging(layout, G, 0, base_ptrs=[1 << 20] * G)   # store-to-all form: owner fields stay zero
+    assert list(plain.push(0).owner_rows) == [0, 0, 0, 0]
