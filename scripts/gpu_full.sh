@@ -8,6 +8,8 @@ python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${TAG}_bench_
 python bench.py --steps 6 --warmup 3 --cpu-steps 1 --cpu-queries 2 > gpurun_out/${TAG}_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/${TAG}_launches.csv \
   python bench.py --steps 6 --warmup 3 --cpu-steps 1 --cpu-queries 2 > gpurun_out/${TAG}_ncu_list.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:'k_step|k_update_fast|k_canon|k_rank_dot_tc' -c 8 -o gpurun_out/${TAG}_prof \
-  python bench.py --steps 6 --warmup 3 --cpu-steps 1 --cpu-queries 2 > gpurun_out/${TAG}_ncu.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'k_step|k_update_fast|k_canon' -c 6 -o gpurun_out/${TAG}_prof \
+  python bench.py --steps 6 --warmup 3 --cpu-steps 1 --cpu-queries 2 > gpurun_out/${TAG}_ncu.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:'k_rank_dot' -c 4 -o gpurun_out/${TAG}_prof_rank \
+  python bench.py --steps 6 --warmup 3 --cpu-steps 1 --cpu-queries 2 > gpurun_out/${TAG}_ncu_rank.log 2>&1
 tail -2 gpurun_out/${TAG}_ncu.log
