@@ -44,6 +44,14 @@ typedef enum { KGE_SCORE_LP = 0, KGE_SCORE_LP_POW = 1, KGE_SCORE_DOT = 2 } kge_s
 /* KGE/loss.py:49,84,115,145,184 */
 typedef enum { KGE_LOSS_HINGE = 0, KGE_LOSS_LOGISTIC = 1, KGE_LOSS_BCE = 2,
                KGE_LOSS_SELF_ADV = 3, KGE_LOSS_SQUARE = 4 } kge_loss_kind;
+/* BaseModel.py:243-246 accepts any Keras optimizer.  Row update of the touched rows (TF 2.5 OptimizerV2
+ * sparse apply on the de-duplicated, summed rows):
+ *   ADAM    m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; w -= lr_t m / (sqrt(v) + eps)   — m, v, w of EVERY row move
+ *   SGD     w -= lr g                                  (momentum = 0; slots m, v unused)
+ *   ADAGRAD v += g^2; w -= lr g / (sqrt(v) + eps)      (v = accumulator, caller initialises it to
+ *                                                       initial_accumulator_value = 0.1; m unused)
+ * cfg.lr / cfg.eps carry learning_rate / epsilon.  Row-lazy and sharded tables: Adam only. */
+typedef enum { KGE_OPTIM_ADAM = 0, KGE_OPTIM_SGD = 1, KGE_OPTIM_ADAGRAD = 2 } kge_opt_kind;
 /* BaseModel.py:49 corrupt_side */
 typedef enum { KGE_SIDE_H = 0, KGE_SIDE_T = 1, KGE_SIDE_HT = 2 } kge_side;
 /* KGE/ns_strategy.py:23 UniformStrategy, :67 TypedStrategy */
@@ -106,7 +114,7 @@ typedef struct kge_cfg {
   int32_t constraint;            /* model's constraint flag */
   int32_t id_dtype;              /* 0 = int32 triples, 1 = int64 (test_data_utils.py:82,90) */
   int32_t d_ent, d_rel;          /* embedding sizes (RotatE: complex dimension) */
-  int32_t reserved;
+  int32_t optimizer;             /* kge_opt_kind (0 = Adam: structs zeroed by older callers keep their meaning) */
   float score_p;                 /* LpDistance.p; INFINITY allowed (score.py:60) */
   float margin, temperature;     /* loss.py:77, 171-172 */
   float constraint_weight;       /* TransH.py:66, DistMult.py:40, RESCAL.py:39 */

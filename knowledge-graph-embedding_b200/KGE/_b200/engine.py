@@ -61,10 +61,12 @@ class PaddedTable:
             self.owner.flush()
         return self.storage[:, :self.cols].reshape(self.shape)
 
-    def ensure_slots(self):
+    def ensure_slots(self, acc_init=0.0):
         if self.m is None:
             self.m = torch.zeros_like(self.storage)
             self.v = torch.zeros_like(self.storage)
+            if acc_init:
+                self.v[:, :self.cols] = acc_init      # padding stays zero
 
 
 class Engine:
@@ -76,8 +78,10 @@ class Engine:
         self.ctx = _ctx(self.device.index or 0)
         self.cfg = L.Cfg(abi_version=L.KGE_ABI_VERSION, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-7,
                          clip_norm=5.0, id_dtype=1, score_p=2.0, rotate_scale=1.0)
+        self.acc_init = float(cfg_kwargs.get("acc_init", 0.0))      # Adagrad: initial_accumulator_value of the v slot
         for k, v in cfg_kwargs.items():
-            setattr(self.cfg, k, v)
+            if k != "acc_init":
+                setattr(self.cfg, k, v)
         self.tab = {s: PaddedTable(v, self.device) for s, v in tables.items()}
         self.lazy = bool(lazy)
         self.lazy_t = 0
@@ -100,7 +104,7 @@ class Engine:
         updated in place; Adam slots appear once)."""
         if with_opt:
             for pt in self.tab.values():
-                pt.ensure_slots()
+                pt.ensure_slots(self.acc_init)
         key = (bool(with_opt),) + tuple((pt.storage.data_ptr(), 0 if pt.m is None else pt.m.data_ptr())
                                         for pt in self.tab.values())
         cache = getattr(self, "_tables_cache", None)

@@ -12,6 +12,7 @@ SIDE_H, SIDE_T, SIDE_HT = 0, 1, 2
 NS_UNIFORM, NS_TYPED = 0, 1
 T_ENT, T_ENT_PROJ, T_REL_A, T_REL_B = range(4)
 CON_NORMALIZE, CON_CLIP = 0, 1
+OPTIM_ADAM, OPTIM_SGD, OPTIM_ADAGRAD = 0, 1, 2
 OPT_RADIX_SORT = 1
 OPT_NO_SHADOW = 2
 OPT_NO_FUSED_PUSH = 3
@@ -33,7 +34,7 @@ class Cfg(C.Structure):
     _fields_ = [("abi_version", C.c_int32), ("model", C.c_int32), ("score", C.c_int32),
                 ("loss", C.c_int32), ("sampler", C.c_int32), ("corrupt_side", C.c_int32),
                 ("negative_ratio", C.c_int32), ("constraint", C.c_int32), ("id_dtype", C.c_int32),
-                ("d_ent", C.c_int32), ("d_rel", C.c_int32), ("reserved", C.c_int32),
+                ("d_ent", C.c_int32), ("d_rel", C.c_int32), ("optimizer", C.c_int32),
                 ("score_p", C.c_float), ("margin", C.c_float), ("temperature", C.c_float),
                 ("constraint_weight", C.c_float), ("lr", C.c_float), ("beta1", C.c_float),
                 ("beta2", C.c_float), ("eps", C.c_float), ("clip_norm", C.c_float),

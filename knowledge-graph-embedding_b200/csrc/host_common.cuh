@@ -37,6 +37,7 @@ inline int check_cfg(const kge_cfg* c) {
   KGE_REQUIRE((uint64_t) c->n_ent + (uint64_t) c->n_rel < 0xffffffffull, KGE_EUNSUPPORTED,
               "n_ent + n_rel must fit 32-bit sort keys");
   KGE_REQUIRE(c->id_dtype == 0 || c->id_dtype == 1, KGE_EINVAL, "id_dtype must be 0 (int32) or 1 (int64)");
+  KGE_REQUIRE(c->optimizer >= KGE_OPTIM_ADAM && c->optimizer <= KGE_OPTIM_ADAGRAD, KGE_EINVAL, "bad optimizer id %d", c->optimizer);
   if (uses_score_fn(c->model)) {
     KGE_REQUIRE(c->score >= KGE_SCORE_LP && c->score <= KGE_SCORE_DOT, KGE_EINVAL, "bad score id %d", c->score);
     if (c->score != KGE_SCORE_DOT)

@@ -142,6 +142,7 @@ static int check_lazy(const kge_cfg* c, const kge_tables* t) {
   for (int s = 0; s < 2; ++s)
     KGE_REQUIRE(!cols[s] || t->t[s].last, KGE_EINVAL, "row-lazy tables: entity slot %d has no `last`", s);
   KGE_REQUIRE(t->lazy_t >= 0 && t->lazy_t < 0xfffffff0ll, KGE_EINVAL, "lazy_t %lld out of range", (long long) t->lazy_t);
+  KGE_REQUIRE(c->optimizer == KGE_OPTIM_ADAM, KGE_EUNSUPPORTED, "row-lazy / sharded tables: Adam only");
   return KGE_OK;
 }
 // start-of-batch constraint op of an entity slot (the jobs k_lazy_pre takes over from k_constrain)
@@ -719,7 +720,8 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   up.heavy_keys = reinterpret_cast<const uint32_t*>(wsb + L.off_heavy);
   up.n_heavy = seg_lo + 2 * L.n_seg + 1;
   up.scal = rp.scal;
-  up.lr_t = adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t);
+  up.lr_t = cfg->optimizer == KGE_OPTIM_ADAM ? adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t) : cfg->lr;
+  up.opt = cfg->optimizer;
   up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
   up.cw = cfg->constraint_weight;
   up.rowpart = dense ? reinterpret_cast<float*>(wsb + L.off_rowpart) : nullptr;
@@ -750,6 +752,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     mu.keys = keys_out; mu.vals = vals_out; mu.n_keys = is_train ? L.n_keys : 0;
     mu.seg_lo = use_lo; mu.seg_hi = use_hi;
     mu.key_base = (uint32_t) cfg->n_ent; mu.rec_base = (uint32_t) L.n_ent_rec;
+    mu.opt = cfg->optimizer;
     mu.scal = rp.scal; mu.lr_t = up.lr_t; mu.beta1 = cfg->beta1; mu.beta2 = cfg->beta2; mu.eps = cfg->eps;
     mu.reg_coef = (dense && cfg->model == KGE_RESCAL) ? 2.0f * cfg->constraint_weight / (float) cfg->n_rel : 0.f;
     mu.part = dense ? reinterpret_cast<float*>(wsb + L.off_matpart) : nullptr;
@@ -977,7 +980,8 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   up.keys = nullptr; up.vals = nullptr; up.n_keys = 0; up.seg_lo = nullptr; up.seg_hi = nullptr; up.seg_key0 = 0;
   up.hdr = nullptr; up.heavy_keys = nullptr; up.n_heavy = nullptr;
   up.scal = scal;
-  up.lr_t = adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t);
+  up.lr_t = cfg->optimizer == KGE_OPTIM_ADAM ? adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t) : cfg->lr;
+  up.opt = cfg->optimizer;
   up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
   up.cw = cfg->constraint_weight;
   up.rowpart = dense ? reinterpret_cast<float*>(wsb + L.off_rowpart) : nullptr;
@@ -1114,7 +1118,8 @@ extern "C" int kge_shard_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   up.keys = nullptr; up.vals = nullptr; up.n_keys = 0; up.seg_lo = nullptr; up.seg_hi = nullptr; up.seg_key0 = 0;
   up.hdr = nullptr; up.heavy_keys = nullptr; up.n_heavy = nullptr;
   up.scal = scal;
-  up.lr_t = adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t);
+  up.lr_t = cfg->optimizer == KGE_OPTIM_ADAM ? adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t) : cfg->lr;
+  up.opt = cfg->optimizer;
   up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
   up.cw = cfg->constraint_weight; up.rowpart = nullptr;
   const int cpl = max_ch <= 32 ? 1 : (max_ch <= 64 ? 2 : (max_ch <= 128 ? 4 : 8));

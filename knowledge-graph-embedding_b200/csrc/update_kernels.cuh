@@ -188,6 +188,7 @@ struct UpdateParams {
   uint32_t seg_key0;       // k_update: seg_lo / seg_hi are indexed by key - seg_key0 (row-lazy mode keeps the relation range only)
   const float* scal;
   float lr_t, beta1, beta2, eps;
+  int opt;               // kge_opt_kind
   float cw;              // constraint_weight
   float* rowpart;        // DENSE=1: [2][total_rows]  (norm^2, loss term) per row
   const uint32_t* hdr;   // k_update_fast: per key [count, first position, first 6 record ids] (k_canon)
@@ -272,8 +273,21 @@ __device__ __forceinline__ float adam1(float& w, float& m, float& v, float g, fl
   w = __fsub_rn(w, __fdiv_rn(__fmul_rn(lr_t, m), __fadd_rn(sqrtf(v), eps)));
   return w;
 }
+// Keras SGD (momentum 0) and Adagrad on the summed row gradient; a zero gradient leaves the row as it
+// is, so the every-row passes of the Adam path stay correct (only superfluous) for them
+__device__ __forceinline__ void sgd1(float& w, float g, float lr) { w = __fsub_rn(w, __fmul_rn(lr, g)); }
+__device__ __forceinline__ void adagrad1(float& w, float& acc, float g, float lr, float eps) {
+  acc = __fadd_rn(acc, __fmul_rn(g, g));
+  w = __fsub_rn(w, __fdiv_rn(__fmul_rn(lr, g), __fadd_rn(sqrtf(acc), eps)));
+}
 __device__ __forceinline__ void adam_chunk(float4& w, float4& m, float4& v, const float4 gg, float b1, float b2, float lr_t,
-                                           float eps) {
+                                           float eps, int opt = KGE_OPTIM_ADAM) {
+  if (opt == KGE_OPTIM_SGD) { sgd1(w.x, gg.x, lr_t); sgd1(w.y, gg.y, lr_t); sgd1(w.z, gg.z, lr_t); sgd1(w.w, gg.w, lr_t); return; }
+  if (opt == KGE_OPTIM_ADAGRAD) {
+    adagrad1(w.x, v.x, gg.x, lr_t, eps); adagrad1(w.y, v.y, gg.y, lr_t, eps);
+    adagrad1(w.z, v.z, gg.z, lr_t, eps); adagrad1(w.w, v.w, gg.w, lr_t, eps);
+    return;
+  }
   adam1(w.x, m.x, v.x, gg.x, b1, b2, lr_t, eps);
   adam1(w.y, m.y, v.y, gg.y, b1, b2, lr_t, eps);
   adam1(w.z, m.z, v.z, gg.z, b1, b2, lr_t, eps);
@@ -420,7 +434,7 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
     }
     gg = scale4(scale, gg);
     float4 m = m4[c], v = v4[c];
-    adam_chunk(w, m, v, gg, b1, b2, p.lr_t, p.eps);
+    adam_chunk(w, m, v, gg, b1, b2, p.lr_t, p.eps, p.opt);
     mask_tail(w, m, v, c, T.cols);
     m4[c] = m; v4[c] = v; w4[c] = w;
   }
@@ -443,7 +457,7 @@ __device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTabl
     wnew[u] = f4zero();
     if (c >= nch) continue;
     float4 w = wi[c], m = m4[c], v = v4[c];
-    adam_chunk(w, m, v, scale4(scale, g[u]), p.beta1, p.beta2, p.lr_t, p.eps);
+    adam_chunk(w, m, v, scale4(scale, g[u]), p.beta1, p.beta2, p.lr_t, p.eps, p.opt);
     mask_tail(w, m, v, c, T.cols);
     m4[c] = m; v4[c] = v;
     if (T.n_out == 0) w4[c] = w;

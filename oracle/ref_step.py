@@ -52,6 +52,53 @@ class TFAdam:
         w.sub_(self.lr_t * m / (torch.sqrt(v) + self.eps))
 
 
+class TFSGD:
+    """tf.optimizers.SGD(momentum=0), TF 2.5: dense var -= lr g; sparse = scatter_add(var, idx, -lr g) per
+    occurrence (gradient_descent.py _resource_apply_sparse_duplicate_indices)."""
+
+    def __init__(self, lr=0.01):
+        self.lr, self.t = lr, 0
+
+    def begin_step(self):
+        self.t += 1
+
+    def apply_dense(self, k, w, g):
+        w.sub_(self.lr * g)
+
+    def apply_sparse(self, k, w, idx, vals):
+        w.index_add_(0, idx, -self.lr * vals)
+
+
+class TFAdagrad:
+    """tf.optimizers.Adagrad, TF 2.5: accumulator starts at initial_accumulator_value; sparse apply on the
+    de-duplicated (summed) rows: acc[i] += g^2; var[i] -= lr g / (sqrt(acc[i]) + eps)
+    (optimizer_v2._resource_apply_sparse_duplicate_indices + ResourceSparseApplyAdagradV2)."""
+
+    def __init__(self, lr=0.001, initial_accumulator_value=0.1, eps=1e-7):
+        self.lr, self.init, self.eps, self.t, self.acc = lr, initial_accumulator_value, eps, 0, {}
+
+    def begin_step(self):
+        self.t += 1
+
+    def _acc(self, k, w):
+        if k not in self.acc:
+            self.acc[k] = torch.full_like(w, self.init)
+        return self.acc[k]
+
+    def apply_dense(self, k, w, g):
+        a = self._acc(k, w)
+        a.add_(g * g)
+        w.sub_(self.lr * g / (torch.sqrt(a) + self.eps))
+
+    def apply_sparse(self, k, w, idx, vals):
+        a = self._acc(k, w)
+        uniq, inv = torch.unique(idx, return_inverse=True)
+        summed = torch.zeros((len(uniq),) + tuple(vals.shape[1:]), dtype=vals.dtype)
+        summed.index_add_(0, inv, vals)
+        a[uniq] += summed * summed
+        w[uniq] -= self.lr * summed / (torch.sqrt(a[uniq]) + self.eps)
+
+
 def clip_by_norm(values, clip):
     """tf.clip_by_norm (BaseModel.py:327): g*clip/max(||g||, clip)."""
     l2 = torch.sqrt(torch.sum(values * values))
