@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(STEP_THREADS, ((NV == 1 || (NV == 2 && M::KIND
   Ent Nnext;
   if (n_it > 0) {
     draw(0);
-    if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, 0), lane);      // in flight while the positive is scored
+    if (PREFETCH) Nnext.load(md, (int64_t) __shfl_sync(FULL, (uint32_t) my_e, 0), lane);      // in flight while the positive is scored
   }
   // DistMult fast path.  s = sum(e_h * r * e_t) is linear in the corrupted entity, so with
   // q = r*t (head corrupted) or h*r (tail corrupted) fixed per positive:  s_neg = N . q,
@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(STEP_THREADS, ((NV == 1 || (NV == 2 && M::KIND
       for (int it = 0; it < n_it; ++it) {
         const int c = wig + it * wpp;
         const int64_t slot = i * k + c;
-        const int64_t e = __shfl_sync(FULL, my_e, it & 31);
+        const int64_t e = (int64_t) __shfl_sync(FULL, (uint32_t) my_e, it & 31);
         Ent N;
         N.load(md, e, lane);
         if (it + 1 < n_it && ((it + 1) & 31) == 0) draw(it + 1);
@@ -330,7 +330,7 @@ __global__ void __launch_bounds__(STEP_THREADS, ((NV == 1 || (NV == 2 && M::KIND
 #pragma unroll
           for (int x = 0; x < GROUP; ++x)
             if (it0 + x < n_it) {
-              eb[x] = __shfl_sync(FULL, my_e, (it0 + x) & 31);
+              eb[x] = (int64_t) __shfl_sync(FULL, (uint32_t) my_e, (it0 + x) & 31);
               if (it0 + x == 0) Nb[x] = Nnext; else Nb[x].load(md, eb[x], lane);
             }
 #pragma unroll
@@ -339,12 +339,12 @@ __global__ void __launch_bounds__(STEP_THREADS, ((NV == 1 || (NV == 2 && M::KIND
         }
       } else {
         for (int it = 0; it < n_it; ++it) {
-          const int64_t e = __shfl_sync(FULL, my_e, it & 31);
+          const int64_t e = (int64_t) __shfl_sync(FULL, (uint32_t) my_e, it & 31);
           Ent N;
           if (PREFETCH) N = Nnext; else N.load(md, e, lane);
           if (it + 1 < n_it) {
             if (((it + 1) & 31) == 0) draw(it + 1);
-            if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, (it + 1) & 31), lane);
+            if (PREFETCH) Nnext.load(md, (int64_t) __shfl_sync(FULL, (uint32_t) my_e, (it + 1) & 31), lane);
           }
           body(it, e, N);
         }
@@ -375,12 +375,12 @@ __global__ void __launch_bounds__(STEP_THREADS, ((NV == 1 || (NV == 2 && M::KIND
       for (int it = 0; it < n_it; ++it) {
         const int c = wig + it * wpp;
         const int64_t slot = i * k + c;
-        const int64_t e = __shfl_sync(FULL, my_e, it & 31);
+        const int64_t e = (int64_t) __shfl_sync(FULL, (uint32_t) my_e, it & 31);
         Ent N;
         if (PREFETCH) N = Nnext; else N.load(md, e, lane);
         if (it + 1 < n_it) {
           if (((it + 1) & 31) == 0) draw(it + 1);
-          if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, (it + 1) & 31), lane);
+          if (PREFETCH) Nnext.load(md, (int64_t) __shfl_sync(FULL, (uint32_t) my_e, (it + 1) & 31), lane);
         }
         if (lane == 0 && p.write_keys) {
           p.neg_ids[slot] = e;
@@ -424,12 +424,12 @@ __global__ void __launch_bounds__(STEP_THREADS, ((NV == 1 || (NV == 2 && M::KIND
     const int c = wig + it * wpp;
     const bool head = neg_is_head(p.sd, c);
     const int64_t slot = i * k + c;
-    const int64_t e = __shfl_sync(FULL, my_e, it & 31);
+    const int64_t e = (int64_t) __shfl_sync(FULL, (uint32_t) my_e, it & 31);
     Ent N;
     if (PREFETCH) N = Nnext; else N.load(md, e, lane);
     if (it + 1 < n_it) {
       if (((it + 1) & 31) == 0) draw(it + 1);
-      if (PREFETCH) Nnext.load(md, __shfl_sync(FULL, my_e, (it + 1) & 31), lane);
+      if (PREFETCH) Nnext.load(md, (int64_t) __shfl_sync(FULL, (uint32_t) my_e, (it + 1) & 31), lane);
     }
     if (lane == 0 && p.write_keys) {
       p.neg_ids[slot] = e;
