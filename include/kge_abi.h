@@ -248,9 +248,8 @@ typedef struct kge_grads {
  * flags[j] = rank j's flag array (uint32[KGE_MAX_PEERS], zeroed once) as mapped HERE.  Every rank calls
  * it with the same strictly increasing `epoch`: the kernel fences its stream's earlier stores at system
  * scope, stores epoch into flags[j][rank] of every peer and spins until flags[rank][j] >= epoch for all
- * j.  The spin is bounded (~2 s): on expiry flags[rank][KGE_MAX_PEERS - 1 ... ] is left untouched and
- * the kernel exits with error word flags[rank][world] = 0xdead (world < KGE_MAX_PEERS) so a lost peer
- * cannot hang the GPU. */
+ * j.  The spin is bounded (~20 s of SM clocks): on expiry the kernel gives up and leaves the error word
+ * flags[rank][world] = 0xdead (when world < KGE_MAX_PEERS), so a lost peer cannot hang the GPU. */
 typedef struct kge_peer_flags {
   int32_t world, rank;
   uint32_t* flags[KGE_MAX_PEERS];

@@ -1151,7 +1151,7 @@ __global__ void k_peer_barrier(PeerFlagsDev f, uint32_t epoch) {
   do {
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
     if (v >= epoch) break;
-    if (clock64() - t0 > 4000000000ll) {                         // ~2 s: a peer is gone; do not hang the GPU
+    if (clock64() - t0 > 40000000000ll) {                        // ~20 s: a peer is gone; do not hang the GPU
       if (f.world < KGE_MAX_PEERS) f.flags[f.rank][f.world] = 0xdeadu;
       break;
     }
