@@ -84,7 +84,7 @@ __device__ __forceinline__ void group_barrier(int grp, int wpp) {
 }
 
 template <class M, int NV, bool TRAIN>
-__global__ void __launch_bounds__(STEP_THREADS, ((NV == 1 || (NV == 2 && M::KIND != KGE_TRANSD)) ? 2 : 1)) k_step(const StepParams p) {
+__global__ void __launch_bounds__(STEP_THREADS, (M::KIND == KGE_TRANSD ? (NV == 1 ? 2 : 1) : (NV == 1 ? 3 : (NV == 2 ? 2 : 1)))) k_step(const StepParams p) {
   using Ent = typename M::template Ent<NV>;
   using Rel = typename M::template Rel<NV>;
   extern __shared__ float4 smem4[];

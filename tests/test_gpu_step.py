@@ -233,6 +233,8 @@ def test_matrix_step_is_bitwise_deterministic():
 @pytest.mark.parametrize("model,B,k,n_rel", [
     ("DistMult", 512, 64, 11),        # long relation segments (> 32 ids): bitmap windows
     ("TransE", 2048, 40, 3),          # segments longer than one 32768-id window span
+    ("TransE", 4096, 40, 2),          # hot rows (> 1024 records): ordered by the whole CTA, one 262144-id window
+    ("UM", 8192, 40, 2),              # ... and over more than one window
     ("TransD", 64, 2, 11),            # short segments only: warp bitonic network
     ("TransR", 96, 6, 4),             # matrix gradients read the relation segments in order
 ])
