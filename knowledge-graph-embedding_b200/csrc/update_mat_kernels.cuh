@@ -13,7 +13,7 @@
 
 namespace kge {
 
-constexpr int MU_TILE = 64, MU_KC = 8, MU_THREADS = 256;
+constexpr int MU_TILE = 64, MU_KC = 16, MU_THREADS = 256;
 
 struct MatUpdTable {
   float *w, *m, *v;
@@ -62,6 +62,8 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
   __shared__ float s_row[MU_KC][MU_TILE];
   __shared__ float s_col[MU_KC][MU_TILE];
   __shared__ float s_red[2][MU_THREADS / 32];
+  __shared__ int64_t s_rec[MU_KC], s_ent[MU_KC];
+  __shared__ int s_entrow[MU_KC];
   const MatUpdTable& T = p.tab[blockIdx.z];
   const int64_t r = blockIdx.y;
   const int tiles_c = (T.cols_m + MU_TILE - 1) / MU_TILE;
@@ -84,27 +86,39 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
     for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
 
   for (int64_t u0 = 0; u0 < n_pairs; u0 += MU_KC) {
-    // stage MU_KC pairs: 2 * MU_KC * 64 floats by 256 threads
-    for (int e = threadIdx.x; e < 2 * MU_KC * MU_TILE; e += MU_THREADS) {
-      const int which = e / (MU_KC * MU_TILE);            // 0 row vectors, 1 column vectors
-      const int kk = (e / MU_TILE) % MU_KC, off = e % MU_TILE;
-      const int64_t u = u0 + kk;
-      float val = 0.f;
+    // stage MU_KC pairs.  The dependent lookups (sorted position -> positive -> entity / record id) are
+    // done ONCE per pair by MU_KC threads; the 2 * MU_KC * 64 vector loads that follow are then
+    // independent of each other and stay in flight together.
+    if (threadIdx.x < MU_KC) {
+      const int64_t u = u0 + threadIdx.x;
+      int64_t rec = -1, ent = 0;
+      int ent_row = 0;
       if (u < n_pairs) {
         const int64_t pos = (int64_t) (__ldg(p.vals + lo + u / S) - p.rec_base);
-        int s = (int) (u % S);
-        int64_t rec, ent; int ent_row;
+        const int s = (int) (u % S);
         if (T.use_sh && s == 0) { rec = pos; ent = load_id(p.triples, 3 * pos, p.id64); ent_row = T.ent_row_sh; }
         else if (T.use_st && s == T.use_sh) { rec = p.B + pos; ent = load_id(p.triples, 3 * pos + 2, p.id64); ent_row = T.ent_row_st; }
         else {
           const int c = mu_neg_c(T.neg_mode, p.side_mode, s - T.use_sh - T.use_st);
           rec = 2 * p.B + pos * p.k + c; ent = __ldg(p.neg_ids + pos * p.k + c); ent_row = T.ent_row_neg;
         }
-        const bool from_ent = (which == 0) == (ent_row != 0);
+      }
+      s_rec[threadIdx.x] = rec; s_ent[threadIdx.x] = ent; s_entrow[threadIdx.x] = ent_row;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int e0 = 0; e0 < 2 * MU_KC * MU_TILE; e0 += MU_THREADS) {
+      const int e = e0 + threadIdx.x;
+      const int which = e / (MU_KC * MU_TILE);            // 0 row vectors, 1 column vectors
+      const int kk = (e / MU_TILE) % MU_KC, off = e % MU_TILE;
+      const int64_t rec = s_rec[kk];
+      float val = 0.f;
+      if (rec >= 0) {
+        const bool from_ent = (which == 0) == (s_entrow[kk] != 0);
         const int idx = (which == 0 ? row0 : col0) + off;
         const int lim = which == 0 ? T.rows_m : T.cols_m;
         if (idx < lim)
-          val = from_ent ? __ldg(p.ent_w + ent * (int64_t) p.ent_ld + idx) : __ldg(p.recP + rec * (int64_t) p.ldp + idx);
+          val = from_ent ? __ldg(p.ent_w + s_ent[kk] * (int64_t) p.ent_ld + idx) : __ldg(p.recP + rec * (int64_t) p.ldp + idx);
       }
       (which == 0 ? s_row : s_col)[kk][off] = val;
     }
