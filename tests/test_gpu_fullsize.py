@@ -1,0 +1,116 @@
+"""Parity at the FULL sizes of BASELINE.json's configurations (the small-shape tests cover the variants):
+the CUDA step against the oracle on one or two whole batches, negatives against the Philox spec, and
+size-independent properties (bitwise reproducibility, unit norms, filtered <= raw, tensor-core path ==
+generic path, row-lazy == dense)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import make_pair, tables_of, rand_triples, assert_weights_close
+from oracle import ref_ops as O, ref_step as RS
+
+pytestmark = pytest.mark.gpu
+
+
+def _zipf(rng, n, N, R):
+    def z(count, size):
+        w = 1.0 / np.arange(1, count + 1)
+        return rng.permutation(count)[rng.choice(count, size=size, p=w / w.sum())]
+    return np.stack([z(N, n), z(R, n), z(N, n)], 1).astype(np.int64)
+
+
+def test_c2_full_batch_matches_oracle_and_is_reproducible():
+    N, R, d, B, k = 14951, 1345, 200, 1024, 64                    # BASELINE.json configs[1]
+    rng = np.random.default_rng(1)
+    batches = [_zipf(rng, B, N, R) for _ in range(3)]
+    ref, W, eng = make_pair("DistMult", N, R, d, loss=O.BinaryCrossEntropyLoss(), k=k, side="h+t", constraint=True)
+    _, _, eng2 = make_pair("DistMult", N, R, d, loss=O.BinaryCrossEntropyLoss(), k=k, side="h+t", constraint=True)
+    opt = RS.TFAdam()
+    for step, X in enumerate(batches):
+        l_gpu, neg = eng.train_step(X, 12345, step, want_negatives=True)
+        l2 = eng2.train_step(X, 12345, step)
+        assert float(l_gpu.item()) == float(l2.item())                # bitwise reproducible
+        if step < 2:                                                   # the oracle needs ~0.1 s per step here
+            ids, k_eff = RS.sample_negatives(12345, step, X, k, "h+t", N)
+            assert np.array_equal(neg.cpu().numpy(), ids), "negatives differ from the Philox spec"
+            l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, "h+t", True)
+            assert abs(float(l_gpu.item()) - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, float(l_gpu.item()), l_ref)
+    got = tables_of(eng, "DistMult")
+    # the oracle stopped after two steps: compare the tables of a third engine run for two steps
+    _, _, eng3 = make_pair("DistMult", N, R, d, loss=O.BinaryCrossEntropyLoss(), k=k, side="h+t", constraint=True)
+    for step, X in enumerate(batches[:2]):
+        eng3.train_step(X, 12345, step)
+    got2 = tables_of(eng3, "DistMult")
+    for kk, v in W.data.items():
+        assert_weights_close(got2[kk], v, 1e-3, 2, kk)
+    for s in eng.tab:
+        assert torch.equal(eng.tab[s].storage, eng2.tab[s].storage)
+    assert eng.tab[0].wn_valid                                         # shadow rows: unit norm (constraint.py:26-31)
+    nrm = eng.tab[0].wn[:, :d].norm(dim=1)
+    assert float((nrm - 1).abs().max()) < 1e-6
+    assert all(torch.isfinite(v).all() for v in got.values())
+
+
+def test_c2_full_ranking_properties():
+    from KGE._b200.filter import build_filter
+    N, R, d = 14951, 1345, 200
+    rng = np.random.default_rng(2)
+    ref, W, eng = make_pair("DistMult", N, R, d, loss=O.BinaryCrossEntropyLoss(), k=64, side="h+t", constraint=True)
+    train = _zipf(rng, 200_000, N, R)
+    Q = train[rng.integers(0, len(train), 512)]
+    for side, sname in ((0, "h"), (1, "t")):
+        off, ids = build_filter(train, Q, sname, N, eng.device)
+        raw = eng.rank_counts(Q, side).cpu().numpy()
+        flt = eng.rank_counts(Q, side, off, ids).cpu().numpy()
+        assert (flt <= raw).all() and (flt >= 0).all() and raw.max() < N
+        # entity shards sum to the whole (sharded evaluation), at an uneven split
+        parts = sum(eng.rank_counts(Q, side, off, ids, ent_lo=lo, ent_hi=hi).cpu().numpy()
+                    for lo, hi in ((0, 5000), (5000, 5001), (5001, N)))
+        assert np.array_equal(parts, flt)
+        os.environ["KGE_RANK_GENERIC"] = "1"                         # tensor-core path == generic fp32 path
+        try:
+            gen = eng.rank_counts(Q, side, off, ids).cpu().numpy()
+        finally:
+            os.environ.pop("KGE_RANK_GENERIC")
+        assert np.array_equal(gen, flt)
+    for q in range(4):                                                 # and the oracle on a few queries
+        want = RS.get_rank(ref, W, Q[q], None, "t") - 1
+        sc = RS.get_scores_all(ref, W, Q[q], "t")
+        pos = float(sc[int(Q[q][2])])
+        near = int(((sc - pos).abs() <= 1e-5 * max(1.0, abs(pos))).sum())
+        assert abs(int(eng.rank_counts(Q[q:q + 1], 1).item()) - want) <= near
+
+
+def test_c1_full_batch_matches_oracle():
+    N, R, d, B = 14505, 237, 50, 4096                                 # configs[0], headline batch
+    rng = np.random.default_rng(3)
+    ref, W, eng = make_pair("TransE", N, R, d, score=O.LpDistance(1), loss=O.PairwiseHingeLoss(1.0), k=1, side="t")
+    opt = RS.TFAdam()
+    for step in range(2):
+        X = rand_triples(rng, B, N, R)
+        ids, k_eff = RS.sample_negatives(7, step, X, 1, "t", N)
+        l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, "t", True)
+        l_gpu, neg = eng.train_step(X, 7, step, want_negatives=True)
+        assert np.array_equal(neg.cpu().numpy(), ids)
+        assert abs(float(l_gpu.item()) - l_ref) <= 1e-4 * max(1.0, abs(l_ref))
+    got = tables_of(eng, "TransE")
+    for kk, v in W.data.items():
+        assert_weights_close(got[kk], v, 1e-3, 2, kk)
+
+
+def test_c5_shape_row_lazy_equals_dense_at_scale():
+    """C5's shape scaled to 400 k entities (the dense twin must fit the test's time): B = 8192, k' = 32."""
+    N, R, d, B = 400_000, 1000, 128, 8192
+    outs = []
+    for lazy in (False, True):
+        rng = np.random.default_rng(4)
+        _, _, eng = make_pair("TransE", N, R, d, score=O.LpDistance(1), loss=O.PairwiseHingeLoss(1.0), k=32, side="h+t",
+                              constraint=True, lazy=lazy)
+        ls = [float(eng.train_step(rand_triples(rng, B, N, R), 12345, step).item()) for step in range(5)]
+        eng.flush()
+        outs.append((ls, eng.tab[0].storage.clone(), eng.tab[0].v.clone()))
+        del eng
+    assert outs[0][0] == outs[1][0]
+    assert torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2])
