@@ -114,3 +114,48 @@ def test_c5_shape_row_lazy_equals_dense_at_scale():
         del eng
     assert outs[0][0] == outs[1][0]
     assert torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2])
+
+
+def test_c3_rotate_full_rows_and_negatives_match_oracle():
+    """configs[2]: RotatE d = 500 (1000-float rows), self-adversarial, 256 negatives; 128 positives keep the
+    oracle's autograd graph small, the row width / negative count / table shape are the full ones."""
+    N, R, d, B, k = 14505, 237, 500, 128, 256
+    rng = np.random.default_rng(5)
+    loss = O.SelfAdversarialNegativeSamplingLoss(3.0, 1.0)
+    ref, W, eng = make_pair("RotatE", N, R, d, score=O.LpDistance(1), loss=loss, k=k, side="h+t", constraint=True)
+    opt = RS.TFAdam()
+    for step in range(2):
+        X = rand_triples(rng, B, N, R)
+        ids, k_eff = RS.sample_negatives(5, step, X, k, "h+t", N)
+        l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, "h+t", True)
+        l_gpu, neg = eng.train_step(X, 5, step, want_negatives=True)
+        assert np.array_equal(neg.cpu().numpy(), ids)
+        assert abs(float(l_gpu.item()) - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, float(l_gpu.item()), l_ref)
+    got = tables_of(eng, "RotatE")
+    for kk, v in W.data.items():
+        assert_weights_close(got[kk], v, 1e-3, 2, kk)
+
+
+@pytest.mark.parametrize("model", ["TransR", "TransD"])
+def test_c4_typed_full_batch_matches_oracle(model):
+    """configs[3]: d_e = d_r = 100, LpDistancePow(2), hinge, typed sampling over 32 types, 'h+t' k = 10, B = 1024."""
+    from oracle import philox
+    N, R, d, B, k = 14505, 237, 100, 1024, 10
+    rng = np.random.default_rng(6)
+    types = rng.integers(0, 32, N)
+    pools = philox.TypedPools(ind2type=[int(t) for t in types])
+    ref, W, eng = make_pair(model, N, R, d, d, score=O.LpDistancePow(2), loss=O.PairwiseHingeLoss(1.0), k=k, side="h+t",
+                            constraint=True)
+    eng.set_typed_pools(pools.ent_type, pools.offsets, pools.members, pools.pos)
+    opt = RS.TFAdam()
+    for step in range(2):
+        X = rand_triples(rng, B, N, R)
+        ids, k_eff = RS.sample_negatives(8, step, X, k, "h+t", N, typed=pools)
+        l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, "h+t", True)
+        l_gpu, neg = eng.train_step(X, 8, step, want_negatives=True)
+        assert np.array_equal(neg.cpu().numpy(), ids), "typed negatives differ from the spec"
+        assert (types[ids.reshape(B, k_eff)[:, 0::2]] == types[X[:, 0]][:, None]).all()      # type preserved
+        assert abs(float(l_gpu.item()) - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, float(l_gpu.item()), l_ref)
+    got = tables_of(eng, model)
+    for kk, v in W.data.items():
+        assert_weights_close(got[kk], v, 1e-3, 2, kk)
