@@ -440,12 +440,12 @@ def main():
         "e2e_loss_one_step_late": {"value": r["triples"] / (r["ms_e2e_lag"] * 1e-3), "unit": "triples/s",
                                    "note": "same H2D / step / D2H per step, loss of step i read while step i+1 runs "
                                            "(KGEModel.train reads losses once per epoch)"},
-        "gpu_launches": args.steps * (8 if world == 1 else 11),
+        "gpu_launches": args.steps * (8 if world == 1 else 12),
         "gpu_launches_note": "own kernels per step: k_constrain, k_step (loss/clip reduction folded into its last warp), "
         "k_update_fast on the caller's stream; k_keys, k_scan, k_scatter, k_canon, k_update_heavy on the side stream "
         "(+ one memset there); data-parallel runs split the update pair into k_update_fast/heavy<3> (row sums stored "
         "into every rank's staging slot over NVLink) + k_push_scal, one cross-GPU barrier, then k_dp_scales + "
-        "k_update_fast<4> (config.exchange = peer), or the same around one NCCL all-reduce (exchange = nccl); exchange = owner: row sums go to the row owner only, the owner runs k_update_fast<4> on its rows and stores the new rows into every replica over NVLink (two barriers)",
+        "k_update_fast<4> (config.exchange = peer), or the same around one NCCL all-reduce (exchange = nccl); exchange = owner (12 kernels: k_step, k_keys, k_scan, k_scatter, k_canon, k_update_heavy<3>, k_update_fast<3>, k_push_scal, k_peer_barrier, k_dp_scales, k_update_fast<4>, k_peer_barrier): row sums go to the row owner only, the owner runs k_update_fast<4> on its rows and stores the new rows into every replica over NVLink, all enqueued by one kge_train_step_dp call",
         "roofline": {"kernel": "k_step<MDistMult,2,true>", "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": ncu_traffic("k_step<MDistMult"),
                      "traffic_note": "ncu dram read+write per launch (cold caches); below the algorithmic bytes because "
