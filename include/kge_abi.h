@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 7
+#define KGE_ABI_VERSION 8
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -202,7 +202,7 @@ int kge_train_step_host(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler
  *   kge_train_apply : per-variable clip_by_norm from the summed norms, dense regularisers,
  *                     TF-semantics Adam on every row; loss_out = summed loss (+ regulariser).
  * grads.dense[s]: [rows x ld] fp32 with the table's own ld (every row is written by _grad).
- * Row-sparse lists (ent_rows / ent_vals) are reserved: must be NULL / 0. */
+ * (Tables where records << rows do not use this form at all: they are sharded, kge_shard below.) */
 typedef struct kge_dp {
   int32_t world, rank;
   int64_t B_global;              /* positives of the whole step */
@@ -211,7 +211,6 @@ typedef struct kge_dp {
 #define KGE_MAX_PEERS 8
 typedef struct kge_grads {
   float* dense[KGE_MAX_TABLES];
-  int64_t* ent_rows;  float* ent_vals[2];  int64_t cap;  int32_t lists;
   /* Fused exchange over peer memory (NVLink / NVSwitch), n_peers > 0: replaces `dense` / scal.
    *   kge_train_grad : peer[j][s] / peer_scal[j] = the address, mapped into THIS process, of this
    *                    rank's slot in rank j's staging buffer (j == rank is local memory); the
@@ -243,13 +242,20 @@ typedef struct kge_grads {
   int32_t owner_rows[KGE_MAX_TABLES];
   float* w_peer[KGE_MAX_PEERS][KGE_MAX_TABLES];
   float* wn_peer[KGE_MAX_PEERS];
+  /* kge_train_apply: this rank's error word of kge_peer_barrier (flags[rank] + KGE_MAX_PEERS), or NULL.
+   * When it reads KGE_PEER_DEAD the apply half leaves every table as it is (a peer never arrived: its
+   * staging slots are stale) and loss_out = NaN; the host reads the word at its next sync and raises. */
+  const uint32_t* abort_word;
 } kge_grads;
 /* Cross-GPU barrier over peer memory, enqueued on `stream` like a kernel (no host involvement):
- * flags[j] = rank j's flag array (uint32[KGE_MAX_PEERS], zeroed once) as mapped HERE.  Every rank calls
+ * flags[j] = rank j's flag array (uint32[KGE_MAX_PEERS + 1], zeroed once) as mapped HERE.  Every rank calls
  * it with the same strictly increasing `epoch`: the kernel fences its stream's earlier stores at system
  * scope, stores epoch into flags[j][rank] of every peer and spins until flags[rank][j] >= epoch for all
- * j.  The spin is bounded (~20 s of SM clocks): on expiry the kernel gives up and leaves the error word
- * flags[rank][world] = 0xdead (when world < KGE_MAX_PEERS), so a lost peer cannot hang the GPU. */
+ * j.  The spin is bounded (~20 s of SM clocks) so a lost peer cannot hang the GPU: on expiry the kernel
+ * writes KGE_PEER_DEAD into the error word flags[rank][KGE_MAX_PEERS] — a sticky, fatal condition: every
+ * later kge_train_apply given the word (kge_grads.abort_word; kge_train_step_dp passes it itself) skips its
+ * update, and the caller must read the word whenever it synchronises and stop (KGE._b200.engine raises). */
+#define KGE_PEER_DEAD 0xdeadu
 typedef struct kge_peer_flags {
   int32_t world, rank;
   uint32_t* flags[KGE_MAX_PEERS];
@@ -348,8 +354,11 @@ int kge_set_option(kge_ctx*, int option, int value);
  * kge_profile_end: no sync inside the timed region).  Phases: 0 constraint, 1 fused
  * sample+gather+score+loss+backward, 2 partial reduction, 3 record sort, 4 row update,
  * 5 ranking (whole call), 6 ranking: tensor-core GEMM kernel alone, 7 ranking: exact fix-up +
- * filter kernels.  phase_ms[p] = summed milliseconds over the n_calls recorded calls. */
-#define KGE_N_PHASES 8
+ * filter kernels, 8 data-parallel apply half (kge_train_apply; phase 4 is then the gradient half's
+ * row sums), 9 cross-GPU barriers of kge_train_step_dp.  phase_ms[p] = summed milliseconds over the
+ * n_calls recorded calls; one data-parallel step (kge_train_grad followed by kge_train_apply, or
+ * kge_train_step_dp) is ONE recorded call. */
+#define KGE_N_PHASES 10
 int kge_profile_begin(kge_ctx*, int max_calls);
 int kge_profile_end(kge_ctx*, float* phase_ms /* [KGE_N_PHASES] */, int* n_calls);
 

@@ -174,6 +174,19 @@ class PeerStaging:
             self._cache["flags"] = F
         return self._cache["flags"]
 
+    def check_alive(self):
+        """Raise if an in-stream barrier (kge_peer_barrier) ever timed out on this rank: the error word
+        flags[rank][KGE_MAX_PEERS] is sticky and the apply halves have been skipping their updates since.
+        Costs a device sync: call where the host synchronises anyway (per epoch)."""
+        from . import lib as L
+        buf = self._keep[0] if isinstance(self._keep, tuple) else self._keep
+        if buf is None or not torch.is_tensor(buf):
+            return
+        word = buf[2 * self.world * self.per + L.KGE_MAX_PEERS:2 * self.world * self.per + L.KGE_MAX_PEERS + 1]
+        if int(word.view(torch.int32).item()) == L.PEER_DEAD:
+            raise RuntimeError("data-parallel step: a peer GPU did not reach the in-stream barrier within ~20 s "
+                               "(kge_peer_barrier gave up); the tables of this rank were left at the last completed step")
+
     def _addr(self, owner, parity, slot, off):
         return self.base_ptrs[owner] + 4 * ((parity * self.world + slot) * self.per + off)
 
@@ -188,6 +201,8 @@ class PeerStaging:
                 for s, off in self.offsets.items():
                     G.peer[j][s] = self._addr(owner, parity, slot, off)
                 G.peer_scal[j] = self._addr(owner, parity, slot, self.scal_off)
+            if not push:            # the apply half skips its update once the barrier's error word is set
+                G.abort_word = self.base_ptrs[self.rank] + 4 * (2 * self.world * self.per + L.KGE_MAX_PEERS)
             if self.ptabs is not None:
                 G.owner_rank = self.rank
                 for s in self.offsets:

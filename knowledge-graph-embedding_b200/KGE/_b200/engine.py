@@ -347,6 +347,12 @@ class Engine:
         self._gbuf.allreduce(group)                       # the step's single collective
         return self.train_apply(self._gbuf, len(triples_local), loss_out)
 
+    def check_peers_alive(self):
+        """Data-parallel runs over peer memory: raise if a cross-GPU barrier timed out (syncs the device)."""
+        peer = getattr(self, "_peer", None)
+        if peer is not None:
+            peer.check_alive()
+
     def adopt_peer_tables(self, ptabs):
         """Move the weight tables (and shadow tables) into peer-mapped memory (dp.PeerTables)."""
         for s, pt in self.tab.items():

@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 7
+KGE_ABI_VERSION = 8
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -16,8 +16,9 @@ OPTIM_ADAM, OPTIM_SGD, OPTIM_ADAGRAD = 0, 1, 2
 OPT_RADIX_SORT = 1
 OPT_NO_SHADOW = 2
 OPT_NO_FUSED_PUSH = 3
-N_PHASES = 8
-PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm", "rank_fix"]
+N_PHASES = 10
+PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm", "rank_fix", "apply", "barrier"]
+PEER_DEAD = 0xdead
 
 
 class Table(C.Structure):
@@ -59,11 +60,11 @@ KGE_MAX_PEERS = 8
 
 
 class Grads(C.Structure):
-    _fields_ = [("dense", C.c_void_p * KGE_MAX_TABLES), ("ent_rows", C.c_void_p),
-                ("ent_vals", C.c_void_p * 2), ("cap", C.c_int64), ("lists", C.c_int32), ("n_peers", C.c_int32),
+    _fields_ = [("dense", C.c_void_p * KGE_MAX_TABLES), ("n_peers", C.c_int32),
                 ("peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("peer_scal", C.c_void_p * KGE_MAX_PEERS),
                 ("owner_rank", C.c_int32), ("owner_rows", C.c_int32 * KGE_MAX_TABLES),
-                ("w_peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("wn_peer", C.c_void_p * KGE_MAX_PEERS)]
+                ("w_peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("wn_peer", C.c_void_p * KGE_MAX_PEERS),
+                ("abort_word", C.c_void_p)]
 
 
 class PeerFlags(C.Structure):

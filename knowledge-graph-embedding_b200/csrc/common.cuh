@@ -35,6 +35,7 @@ struct kge_ctx_impl {
   cudaEvent_t* ev = nullptr;
   unsigned* ev_mask = nullptr;
   int prof_cap = 0, prof_n = 0;
+  int prof_open = -1;             // slot opened by kge_train_grad: the kge_train_apply that follows records into it
   // side stream of kge_train_step (sort keys are independent of the weights, so key generation,
   // the radix sort and the segment table overlap the step kernel) + its fork / join events
   cudaStream_t aux = nullptr;
@@ -47,9 +48,14 @@ struct kge_ctx_impl {
 // RAII marker: records the boundary events of one call when profiling is on
 struct PhaseTimer {
   kge_ctx_impl* c; cudaStream_t st; int slot;
-  PhaseTimer(kge_ctx_impl* c_, cudaStream_t s) : c(c_), st(s), slot(-1) {
-    if (c->ev && c->prof_n < c->prof_cap) { slot = c->prof_n++; c->ev_mask[slot] = 0; }
+  // join: continue the slot the preceding gradient half opened (one data-parallel step = one call)
+  PhaseTimer(kge_ctx_impl* c_, cudaStream_t s, bool join = false) : c(c_), st(s), slot(-1) {
+    if (!c->ev) return;
+    if (join && c->prof_open >= 0) { slot = c->prof_open; c->prof_open = -1; return; }
+    c->prof_open = -1;
+    if (c->prof_n < c->prof_cap) { slot = c->prof_n++; c->ev_mask[slot] = 0; }
   }
+  void keep_open() { if (slot >= 0) c->prof_open = slot; }
   void begin(int phase) { begin(phase, st); }
   void end(int phase) { end(phase, st); }
   void begin(int phase, cudaStream_t s) { if (slot >= 0) cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + 2 * phase], s); }

@@ -387,8 +387,6 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
                     dp->B_global >= dp->i_base + B, KGE_EINVAL, "bad kge_dp (world %d rank %d B_global %lld i_base %lld)",
                 dp->world, dp->rank, (long long) dp->B_global, (long long) dp->i_base);
     KGE_REQUIRE(!mat, KGE_EUNSUPPORTED, "data-parallel steps cover the vector models; SE / TransR / RESCAL are single-GPU");
-    KGE_REQUIRE(!grads_out->ent_rows && !grads_out->ent_vals[0] && !grads_out->ent_vals[1], KGE_EUNSUPPORTED,
-                "row-sparse gradient lists are reserved");
     int gcols[KGE_MAX_TABLES];
     expected_cols(cfg, gcols);
     for (int s = 0; s < KGE_MAX_TABLES; ++s)
@@ -783,6 +781,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
       KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_heavy, 0));
     }
     pt.end(4);
+    if (!sh) pt.keep_open();           // kge_train_apply continues this call's profile slot
     return KGE_OK;
   }
   if (dense) {
@@ -891,8 +890,6 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   KGE_REQUIRE(g->n_peers >= 0 && g->n_peers <= KGE_MAX_PEERS, KGE_EINVAL, "grads.n_peers %d out of range", g->n_peers);
   KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED,
               "data-parallel steps cover the vector models; SE / TransR / RESCAL are single-GPU");
-  KGE_REQUIRE(!g->ent_rows && !g->ent_vals[0] && !g->ent_vals[1], KGE_EUNSUPPORTED,
-              "row-sparse gradient lists are reserved");
   StepWs L;
   if (int rc = layout_step_ws(cfg, B, L)) return rc;
   KGE_REQUIRE(ws_bytes >= L.total, KGE_EWORKSPACE, "workspace %zu < required %zu bytes", ws_bytes, L.total);
@@ -901,14 +898,14 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   int cols[KGE_MAX_TABLES];
   expected_cols(cfg, cols);
   float* scal = reinterpret_cast<float*>(wsb + L.off_scal);
-  PhaseTimer pt(ctx, st);
-  pt.begin(4);
+  PhaseTimer pt(ctx, st, true);
+  pt.begin(8);
   ScalSlots ss;
   if (g->n_peers > 0) {
     ss.n = g->n_peers;
     for (int j = 0; j < ss.n; ++j) { KGE_REQUIRE(g->peer_scal[j], KGE_EINVAL, "grads.peer_scal[%d] is NULL", j); ss.s[j] = g->peer_scal[j]; }
   } else { KGE_REQUIRE(scal_summed, KGE_EINVAL, "scal_summed is NULL"); ss.n = 1; ss.s[0] = scal_summed; }
-  k_dp_scales<<<1, 32, 0, st>>>(ss, cfg->clip_norm, scal, loss_out);
+  k_dp_scales<<<1, 32, 0, st>>>(ss, cfg->clip_norm, scal, loss_out, g->abort_word);
   KGE_CUDA_OK(cudaGetLastError());
 
   const bool dense = has_dense_reg(cfg);
@@ -1005,7 +1002,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     if (int rc = launch_update_fast<4>(up, cpl, st)) return rc;      // streaming pass: gradient = gsum row
   }
   tables->wn_valid[KGE_T_ENT] = (shadow_ok && !dense) ? 1 : 0;
-  pt.end(4);
+  pt.end(8);
   return KGE_OK;
 }
 
@@ -1095,7 +1092,7 @@ extern "C" int kge_shard_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   pt.begin(4);
   ScalSlots ss;
   ss.n = 1; ss.s[0] = scal_summed;
-  k_dp_scales<<<1, 32, 0, st>>>(ss, cfg->clip_norm, scal, loss_out);
+  k_dp_scales<<<1, 32, 0, st>>>(ss, cfg->clip_norm, scal, loss_out, nullptr);
   KGE_CUDA_OK(cudaGetLastError());
   // replicated relation tables: the data-parallel streaming apply
   UpdateParams up;
@@ -1152,7 +1149,7 @@ __global__ void k_peer_barrier(PeerFlagsDev f, uint32_t epoch) {
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
     if (v >= epoch) break;
     if (clock64() - t0 > 40000000000ll) {                        // ~20 s: a peer is gone; do not hang the GPU
-      if (f.world < KGE_MAX_PEERS) f.flags[f.rank][f.world] = 0xdeadu;
+      f.flags[f.rank][KGE_MAX_PEERS] = KGE_PEER_DEAD;            // sticky error word: the apply half skips, the host raises
       break;
     }
   } while (true);
@@ -1181,9 +1178,18 @@ extern "C" int kge_train_step_dp(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* t
                                  uint32_t epoch, float* loss_out, void* ws, size_t ws_bytes, void* stream) {
   KGE_REQUIRE(push && slots && push->n_peers > 0 && slots->n_peers > 0, KGE_EINVAL,
               "kge_train_step_dp needs the peer-staging form of kge_grads");
+  KGE_REQUIRE(pf && pf->rank >= 0 && pf->rank < KGE_MAX_PEERS && pf->flags[pf->rank], KGE_EINVAL, "bad kge_peer_flags");
+  auto* c = reinterpret_cast<kge_ctx_impl*>(ctx);
   if (int rc = kge_train_grad(ctx, cfg, tables, smp, dp, triples, B, seed, step, nullptr, push, nullptr, nullptr, ws,
                               ws_bytes, stream)) return rc;
+  const int slot = c ? c->prof_open : -1;           // the step's profile slot (the halves share it)
+  auto mark = [&](int idx) { if (slot >= 0) cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + idx], (cudaStream_t) stream); };
+  mark(2 * 9);
   if (int rc = kge_peer_barrier(ctx, pf, epoch, stream)) return rc;
-  if (int rc = kge_train_apply(ctx, cfg, tables, slots, nullptr, B, adam_t, loss_out, ws, ws_bytes, stream)) return rc;
+  mark(2 * 9 + 1);
+  if (slot >= 0) c->ev_mask[slot] |= 1u << 9;
+  kge_grads sl = *slots;
+  sl.abort_word = pf->flags[pf->rank] + KGE_MAX_PEERS;
+  if (int rc = kge_train_apply(ctx, cfg, tables, &sl, nullptr, B, adam_t, loss_out, ws, ws_bytes, stream)) return rc;
   return kge_peer_barrier(ctx, pf, epoch + 1, stream);
 }

@@ -176,6 +176,7 @@ __device__ __forceinline__ void add_peers(const UpdateTable& T, int64_t row, int
     for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) g[u] += __ldg(gs + c); }
   }
 }
+constexpr int SCAL_ABORT = 12;        // scal[12] != 0: a cross-GPU barrier gave up (k_dp_scales), the apply half must not run
 struct UpdateParams {
   UpdateTable tab[KGE_MAX_TABLES];
   int n_tabs;
@@ -502,6 +503,7 @@ __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
   while (j < p.n_tabs - 1 && row >= p.tab[j].rows) { row -= p.tab[j].rows; ++j; }
   const UpdateTable& T = p.tab[j];
   if (row >= T.rows) return;                       // owner-partitioned apply: the last table may own no rows
+  if (MODE == 4 && p.scal[SCAL_ABORT] != 0.f) return;   // a peer never reached the barrier: leave the tables alone
   row += T.row_lo;
   const int nch = (T.cols + 3) >> 2;
   const float4* w4 = reinterpret_cast<const float4*>(T.w_in + row * (int64_t) T.ld);
@@ -618,15 +620,19 @@ inline int launch_update(const UpdateParams& up, int cpl, int64_t blocks, cudaSt
 // data-parallel apply: clip scales and loss from the [norm^2 x4, loss] blocks — one block already
 // summed over ranks, or every rank's block (summed here in rank order)
 struct ScalSlots { const float* s[KGE_MAX_PEERS]; int n; };
-__global__ void k_dp_scales(const ScalSlots in, float clip_norm, float* scal, float* loss_out) {
+// abort (nullable): the error word of kge_peer_barrier.  KGE_PEER_DEAD => scal[SCAL_ABORT] = 1: the update
+// kernels of the apply half return before touching a row, and the loss is NaN.
+__global__ void k_dp_scales(const ScalSlots in, float clip_norm, float* scal, float* loss_out, const uint32_t* abort) {
   const int t = threadIdx.x;
   if (t > KGE_MAX_TABLES) return;
+  const bool dead = abort != nullptr && *reinterpret_cast<const volatile uint32_t*>(abort) == KGE_PEER_DEAD;
   float a = 0.f;
   for (int j = 0; j < in.n; ++j) a += in.s[j][t];
   if (t < KGE_MAX_TABLES) {
     scal[4 + t] = a;
     scal[t] = clip_norm / fmaxf(sqrtf(a), clip_norm);
-  } else { scal[8] = a; *loss_out = a; }
+    if (t == 0) scal[SCAL_ABORT] = dead ? 1.f : 0.f;
+  } else { scal[8] = a; *loss_out = dead ? __int_as_float(0x7fc00000) : a; }
 }
 // data-parallel gradient half with peer staging: this rank's [norm^2 x4, loss] block to every rank
 __global__ void k_push_scal(const float* __restrict__ src, ScalSlots out) {

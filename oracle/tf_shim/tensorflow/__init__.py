@@ -420,7 +420,70 @@ class _Adam:
                 w.sub_(lr_t * m / (_torch.sqrt(v) + self.epsilon))
 
 
-optimizers = _types.SimpleNamespace(Adam=_Adam)
+class _SGD:
+    """tf.optimizers.SGD, TF 2.5 gradient_descent.py: dense `var -= lr * g`; sparse (momentum = 0)
+    `_resource_apply_sparse_duplicate_indices` = resource_scatter_add(var, indices, -lr * g): every
+    IndexedSlices occurrence is applied, no de-duplication needed."""
+
+    def __init__(self, learning_rate=0.01, momentum=0.0, nesterov=False, name="SGD"):
+        assert momentum == 0.0 and not nesterov, "shim: plain SGD only"
+        self.learning_rate, self.iterations = learning_rate, 0
+
+    def apply_gradients(self, grads_and_vars):
+        self.iterations += 1
+        lr = float(_np.float32(self.learning_rate))
+        with _torch.no_grad():
+            for g, var in grads_and_vars:
+                if g is None:
+                    continue
+                w = var.as_subclass(_torch.Tensor)
+                if isinstance(g, IndexedSlices):
+                    vals = g.values.detach().as_subclass(_torch.Tensor)
+                    w.index_add_(0, g.indices, vals * (-lr))
+                else:
+                    w.sub_(g.detach().as_subclass(_torch.Tensor) * lr)
+
+
+class _Adagrad:
+    """tf.optimizers.Adagrad, TF 2.5 adagrad.py: slot `accumulator` = initial_accumulator_value; dense
+    ResourceApplyAdagradV2 `acc += g*g; var -= lr * g / (sqrt(acc) + eps)`; sparse: OptimizerV2 first
+    sums duplicate indices (_deduplicate_indexed_slices), then ResourceSparseApplyAdagradV2 does the same
+    on the listed rows only (other rows are untouched)."""
+
+    def __init__(self, learning_rate=0.001, initial_accumulator_value=0.1, epsilon=1e-7, name="Adagrad"):
+        self.learning_rate, self.initial_accumulator_value, self.epsilon = learning_rate, initial_accumulator_value, epsilon
+        self.iterations, self._acc = 0, {}
+
+    def _slot(self, var):
+        k = id(var)
+        if k not in self._acc:
+            self._acc[k] = _torch.full_like(var.detach().as_subclass(_torch.Tensor), self.initial_accumulator_value)
+        return self._acc[k]
+
+    def apply_gradients(self, grads_and_vars):
+        self.iterations += 1
+        lr, eps = float(_np.float32(self.learning_rate)), float(_np.float32(self.epsilon))
+        with _torch.no_grad():
+            for g, var in grads_and_vars:
+                if g is None:
+                    continue
+                acc = self._slot(var)
+                w = var.as_subclass(_torch.Tensor)
+                if isinstance(g, IndexedSlices):
+                    vals = g.values.detach().as_subclass(_torch.Tensor)
+                    uniq, inv = _torch.unique(g.indices, return_inverse=True)
+                    summed = _torch.zeros((len(uniq),) + tuple(vals.shape[1:]), dtype=vals.dtype)
+                    summed.index_add_(0, inv, vals)
+                    a = acc[uniq] + summed * summed
+                    acc[uniq] = a
+                    w[uniq] = w[uniq] - lr * summed / (_torch.sqrt(a) + eps)
+                else:
+                    gd = g.detach().as_subclass(_torch.Tensor)
+                    acc.add_(gd * gd)
+                    w.sub_(lr * gd / (_torch.sqrt(acc) + eps))
+
+
+optimizers = _types.SimpleNamespace(Adam=_Adam, SGD=_SGD, Adagrad=_Adagrad)
 keras = _types.SimpleNamespace(optimizers=optimizers)
 
 

@@ -136,7 +136,7 @@ class GoldenSampler:
         return tf.constant(ids, dtype=X.dtype)
 
 
-def build_reference_model(model, score, loss, k, side, constraint, cw, d, dr, w0, sampler):
+def build_reference_model(model, score, loss, k, side, constraint, cw, d, dr, w0, sampler, optimizer=None):
     emb = {"embedding_size": d} if model not in ("TransR", "TransD") else \
         {"ent_embedding_size": d, "rel_embedding_size": dr}
     kw = dict(embedding_params=emb, negative_ratio=k, corrupt_side=side, loss_fn=loss, ns_strategy=sampler)
@@ -157,7 +157,8 @@ def build_reference_model(model, score, loss, k, side, constraint, cw, d, dr, w0
     else:
         m._model_weights_initial = W
         m._init_embeddings(seed=None)        # the reference's own path (RESCAL normalises here)
-    m._KGEModel__optimizer = tf.optimizers.Adam()
+    # BaseModel.py:243-246: "Adam" -> tf.optimizers.Adam(), anything else is used as given
+    m._KGEModel__optimizer = tf.optimizers.Adam() if optimizer is None else optimizer
     return m
 
 
@@ -188,17 +189,39 @@ CASES = {
     "rescal": ("RESCAL", None, "square", 4, "h+t", True, 1.0, 6, 6),
     "rescal_logistic_nocon": ("RESCAL", None, "logistic", 2, "t", False, 1.0, 6, 6),
 }
+# user-supplied Keras optimizers (BaseModel.py:243-246).  name: (case spec, optimizer, lr)
+OPT_CASES = {
+    "opt_transe_sgd": (("TransE", "l1", "hinge", 4, "h+t", True, 1.0, 8, 8), "sgd", 0.05),
+    "opt_transe_adagrad": (("TransE", "l1", "hinge", 4, "h+t", True, 1.0, 8, 8), "adagrad", 0.05),
+    "opt_distmult_sgd": (("DistMult", None, "bce", 6, "h+t", True, 1.0, 8, 8), "sgd", 0.05),
+    "opt_distmult_adagrad": (("DistMult", None, "bce", 6, "h+t", True, 1.0, 8, 8), "adagrad", 0.05),
+    "opt_transh_sgd": (("TransH", "l2pow", "hinge", 4, "h+t", True, 0.5, 8, 8), "sgd", 0.05),       # dense regulariser
+    "opt_transh_adagrad": (("TransH", "l2pow", "hinge", 4, "h+t", True, 0.5, 8, 8), "adagrad", 0.05),
+    "opt_transr_sgd": (("TransR", "l2pow", "hinge", 4, "h+t", True, 1.0, 8, 6), "sgd", 0.05),       # matrix table
+    "opt_transr_adagrad": (("TransR", "l2pow", "hinge", 4, "h+t", True, 1.0, 8, 6), "adagrad", 0.05),
+    "opt_rotate_adagrad": (("RotatE", "l1", "selfadv", 6, "h+t", True, 1.0, 7, 7), "adagrad", 0.05),
+    "opt_transd_sgd": (("TransD", "l2pow", "hinge", 4, "h+t", True, 1.0, 8, 6), "sgd", 0.05),
+}
 B, STEPS, SEED = 16, 3, 4242
 
 
-def gen_case(name, spec):
+def make_optimizer(kind, lr):
+    if kind == "sgd":
+        return tf.optimizers.SGD(learning_rate=lr)
+    if kind == "adagrad":
+        return tf.optimizers.Adagrad(learning_rate=lr, initial_accumulator_value=0.1, epsilon=1e-7)
+    raise ValueError(kind)
+
+
+def gen_case(name, spec, opt=None):
     model, sc, ls, k, side, con, cw, d, dr = spec
     rng = np.random.default_rng(abs(hash(name)) % (2 ** 31) if False else sum(map(ord, name)))
     loss = LOSSES[ls]()
     rot_limit = (getattr(loss, "margin", 6.0) + 2.0) / d
     w_in = random_weights(model, d, dr, rng, rot_limit)
     sampler = GoldenSampler(SEED)
-    m = build_reference_model(model, SCORES[sc](), loss, k, side, con, cw, d, dr, w_in, sampler)
+    m = build_reference_model(model, SCORES[sc](), loss, k, side, con, cw, d, dr, w_in, sampler,
+                              optimizer=None if opt is None else make_optimizer(*opt))
     out = {"w0_" + kk: npy(v).copy() for kk, v in m.model_weights.items()}      # post-init state
 
     def triples(n):
@@ -243,11 +266,23 @@ def gen_case(name, spec):
     for s in ("h", "t"):
         out["rank_raw_" + s] = np.asarray([m.get_rank(tf.constant(x[None]), None, s) for x in ev], dtype=np.int64)
         out["rank_flt_" + s] = np.asarray([m.get_rank(tf.constant(x[None]), pos, s) for x in ev], dtype=np.int64)
+        # the two score paths get_rank compares (BaseModel.py:639-654): every candidate through the
+        # h=None / t=None expansion, the true triple through the scalar call — the tests take the
+        # documented tie band (and the reference's occasional self-count) from THESE
+        sc_all = []
+        for x in ev:
+            q = tf.constant(x)
+            sc_all.append(npy(m.score_hrt(h=None, r=q[1], t=q[2]) if s == "h" else m.score_hrt(h=q[0], r=q[1], t=None)))
+        out["rank_scores_" + s] = np.stack(sc_all).astype(np.float32)
+    out["rank_pos_score"] = np.asarray([float(npy(m.score_hrt(tf.constant(x)[0], tf.constant(x)[1], tf.constant(x)[2])).reshape(-1)[0])
+                                        for x in ev], dtype=np.float32)
     with contextlib.redirect_stderr(io.StringIO()):
         res = m.evaluate(ev, "t", pos)
     out["eval_keys"] = np.asarray(list(res.keys()))
     out["eval_vals"] = np.asarray([float(v) for v in res.values()], dtype=np.float64)
     out["spec"] = np.asarray([str(x) for x in spec])
+    if opt is not None:
+        out["opt"] = np.asarray([str(opt[0]), repr(float(opt[1]))])
     np.savez_compressed(os.path.join(HERE, "case_%s.npz" % name), **out)
     return rec["loss"]
 
@@ -324,6 +359,9 @@ if __name__ == "__main__":
     print("ops:", gen_ops(), "arrays")
     for name, spec in CASES.items():
         ls = gen_case(name, spec)
+        print("case %-24s losses %s" % (name, " ".join("%.5f" % v for v in ls)))
+    for name, (spec, kind, lr) in OPT_CASES.items():
+        ls = gen_case(name, spec, (kind, lr))
         print("case %-24s losses %s" % (name, " ".join("%.5f" % v for v in ls)))
     gen_typed()
     print("train loop batches:", gen_train_loop())

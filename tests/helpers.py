@@ -48,4 +48,66 @@ def assert_weights_close(got, want, lr, steps, where=""):
     scale = float(want.abs().max()) + 1e-12
     assert float(diff.max()) <= steps * lr * 1.01 + 1e-6 * scale, (where, float(diff.max()))
     frac = float((diff > 1e-4 * scale).double().mean())
+    print("weights %s: max|dW| %.3g (%.3g of scale, bound %.3g), outside 1e-4: %.5f" % (
+        where, float(diff.max()), float(diff.max()) / scale, steps * lr, frac))
     assert frac < 0.01, (where, frac, float(diff.max()))
+
+
+class RankBand:
+    """north_star: "ranks ... must match exactly except for documented ties within 1e-5".
+
+    A rank may differ from the reference's only by candidates that are ELIGIBLE (not the true entity,
+    not filtered out) and whose reference score lies within 1e-5 relative of the true triple's score,
+    plus the reference's documented self-count (get_rank scores the true triple on a
+    separate scalar path, BaseModel.py:652; when the unfiltered true entity's vector-path score rounds
+    above it the reference counts the true entity itself — the kernels never do).  `used` counts the
+    queries that needed either allowance, so a systematic +-1 cannot hide in the band."""
+
+    def __init__(self, tol=1e-5):
+        self.tol, self.n, self.used, self.self_counts, self.worst = tol, 0, 0, 0, 0
+
+    def check(self, got_rank, want_rank, scores, pos_score, true_ent, excluded=None, where=""):
+        """scores: the reference's candidate scores [N]; pos_score: its scalar-path true score;
+        excluded: ids filtered for this query (may include true_ent)."""
+        self.n += 1
+        sc = np.asarray(scores, dtype=np.float64)
+        p = float(pos_score)
+        elig = np.ones(len(sc), dtype=bool)
+        elig[int(true_ent)] = False
+        true_filtered = False
+        if excluded is not None and len(excluded):
+            ex = np.asarray(excluded, dtype=np.int64)
+            elig[ex] = False
+            true_filtered = bool((ex == int(true_ent)).any())
+        self_count = int((not true_filtered) and sc[int(true_ent)] > p)
+        want_kernel = int(want_rank) - self_count          # what an exact ranking without the self-count gives
+        self.self_counts += self_count
+        if int(got_rank) == want_kernel:
+            return
+        near = int((np.abs(sc - p) <= self.tol * max(1.0, abs(p)))[elig].sum())
+        assert abs(int(got_rank) - want_kernel) <= near, (where, int(got_rank), int(want_rank), self_count, near)
+        self.used += 1
+        self.worst = max(self.worst, abs(int(got_rank) - want_kernel))
+
+    def summary(self):
+        return "rank parity: %d queries, %d needed the 1e-5 tie band (worst |diff| %d); reference self-counts (C.6): %d" % (
+            self.n, self.used, self.worst, self.self_counts)
+
+
+def filtered_ids(positive_X, x, side):
+    """Entities the reference's filter removes for query x (BaseModel.py:646-650)."""
+    P = np.asarray(positive_X)
+    fs, cs = (2, 0) if side == "h" else (0, 2)
+    return P[(P[:, 1] == x[1]) & (P[:, fs] == x[fs]), cs]
+
+
+def oracle_rank_check(band, ref, W, x, side, positive_X, got_rank, where=""):
+    """One query against the oracle's get_rank with the strict tie band (no shortcut when the ranks
+    agree: an oracle self-count matched by an off-by-one here must not cancel unseen)."""
+    want = RS.get_rank(ref, W, x, positive_X, side)
+    sc = RS.get_scores_all(ref, W, x, side)
+    with torch.no_grad():
+        one = lambda v: torch.tensor([int(v)])      # noqa: E731
+        p = float(ref.score_hrt(W, one(x[0]), one(x[1]), one(x[2]))[0])
+    ex = filtered_ids(positive_X, x, side) if positive_X is not None else None
+    band.check(got_rank, want, sc.numpy(), p, x[0] if side == "h" else x[2], ex, where)

@@ -7,6 +7,7 @@ import pytest
 import torch
 
 from test_golden_oracle import CASES, GOLD, TOL, close, load_case, weights, neg_ids_from_triples
+from helpers import RankBand, filtered_ids
 
 pytestmark = pytest.mark.gpu
 N_ENT, N_REL = 40, 5
@@ -42,6 +43,11 @@ def engine_for(spec, W):
     cfg = SP.make_cfg(spec["model"], N_ENT, N_REL, spec["d"], spec["dr"], score_fn=_score(spec["score"]), loss_fn=loss,
                       negative_ratio=spec["k"], corrupt_side=spec["side"], constraint=spec["constraint"],
                       constraint_weight=spec["cw"], rotate_limit=limit)
+    if spec.get("opt", "adam") != "adam":       # case_opt_*: SGD / Adagrad as the reference was given them
+        from KGE._b200 import lib as L
+        cfg.update(optimizer={"sgd": L.OPTIM_SGD, "adagrad": L.OPTIM_ADAGRAD}[spec["opt"]], lr=spec["lr"], eps=1e-7)
+        if spec["opt"] == "adagrad":
+            cfg["acc_init"] = 0.1
     return E.Engine(cfg, {SP.SLOTS[spec["model"]][k]: v for k, v in W.items()})
 
 
@@ -81,8 +87,13 @@ def test_step_sequence_golden(name):
     for k, v in weights(g, "wT_").items():
         # Adam's 1/sqrt(v) amplifies 1e-7 summation-order noise where a gradient cancels:
         # bound by the per-step Adam move (3 train steps * lr) and require 99% within 1e-4
+        if spec["opt"] != "adam":           # SGD / Adagrad (accumulator >= 0.1) are well conditioned: plain 1e-4
+            close(got[k], v)
+            continue
         diff = (got[k].double() - v.double()).abs()
         scale = float(v.abs().max())
+        print("golden %s %s: max|dW| %.3g (%.3g of scale), outside 1e-4: %.4f" % (
+            name, k, float(diff.max()), float(diff.max()) / scale, float((diff > TOL * scale).double().mean())))
         assert float(diff.max()) <= 3 * 1e-3 * 1.01 + 1e-6 * scale, (k, float(diff.max()))
         assert float((diff > TOL * scale).double().mean()) < 0.01, k
 
@@ -93,22 +104,22 @@ def test_ranks_golden(name):
     g, spec = load_case(name)
     eng = engine_for(spec, weights(g, "wT_"))
     pos, ev = g["rank_pos"], g["rank_X"]
+    band = RankBand()
     for s in ("h", "t"):
         side = 0 if s == "h" else 1
         ent = ev[:, 0 if s == "h" else 2]
         raw = eng.rank_counts(ev, side).cpu().numpy() + 1
         off, ids = build_filter(pos, ev, s, N_ENT, eng.device)
         flt = eng.rank_counts(ev, side, off, ids).cpu().numpy() + 1
-        # tie band: candidates within 1e-5 relative of the true score (north_star)
-        ar = np.arange(N_ENT)
+        # tie band from the REFERENCE's own two score paths stored in the fixture (north_star: exact except
+        # eligible candidates within 1e-5 relative of the true score; the reference's self-count)
         for q, x in enumerate(ev):
-            sc = (eng.score(ar, np.full(N_ENT, x[1]), np.full(N_ENT, x[2])) if s == "h"
-                  else eng.score(np.full(N_ENT, x[0]), np.full(N_ENT, x[1]), ar)).cpu().double()
-            p = float(sc[int(ent[q])])
-            near = int(((sc - p).abs() <= 1e-5 * max(1.0, abs(p))).sum())
-            assert abs(int(raw[q]) - int(g["rank_raw_" + s][q])) <= near, (s, q, raw[q], g["rank_raw_" + s][q])
-            assert abs(int(flt[q]) - int(g["rank_flt_" + s][q])) <= near, (s, q, flt[q], g["rank_flt_" + s][q])
+            sc, p = g["rank_scores_" + s][q], g["rank_pos_score"][q]
+            band.check(raw[q], g["rank_raw_" + s][q], sc, p, ent[q], None, (name, s, q, "raw"))
+            band.check(flt[q], g["rank_flt_" + s][q], sc, p, ent[q], filtered_ids(pos, x, s), (name, s, q, "flt"))
         assert (flt <= raw).all()
+    print(name, band.summary())
+    assert band.used <= 2, band.summary()
 
 
 def test_full_train_loop_golden():

@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import make_pair, rand_triples
+from helpers import make_pair, rand_triples, RankBand, oracle_rank_check
 from oracle import ref_ops as O, ref_step as RS
 from test_gpu_step import SCORES, LOSSES, VECTOR_MODELS, _score_for
 
@@ -24,15 +24,11 @@ def _check(model, score, side, filtered, d=50, d_rel=None, Q=40):
     if filtered:
         off, ids = build_filter(pos, Xq, side, N, eng.device)
     cnt = eng.rank_counts(Xq, 0 if side == "h" else 1, off, ids).cpu().numpy()
+    band = RankBand()
     for q, x in enumerate(Xq):
-        want = RS.get_rank(ref, W, x, pos if filtered else None, side)
-        if cnt[q] + 1 != want:
-            s = RS.get_scores_all(ref, W, x, side)
-            with torch.no_grad():
-                one = lambda v: torch.tensor([int(v)])
-                p = float(ref.score_hrt(W, one(x[0]), one(x[1]), one(x[2]))[0])
-            near = int(((s - p).abs() <= 1e-5 * max(1.0, abs(p))).sum())
-            assert abs(int(cnt[q]) + 1 - want) <= near, (model, q, int(cnt[q]) + 1, want, near)
+        oracle_rank_check(band, ref, W, x, side, pos if filtered else None, int(cnt[q]) + 1, (model, q))
+    print(model, score, side, band.summary())
+    assert band.used <= max(2, Q // 10), band.summary()     # the band is an exception, not the rule
 
 
 @pytest.mark.parametrize("model", VECTOR_MODELS)
@@ -147,14 +143,9 @@ def test_lp_tile_rank_equals_generic(model, score, d, n_ent, side):
     parts = sum(eng.rank_counts(Xq, s, off, ids, ent_lo=lo, ent_hi=hi).cpu().numpy()
                 for lo, hi in [(0, n_ent // 3), (n_ent // 3, n_ent // 3 + 77), (n_ent // 3 + 77, n_ent)])
     assert np.array_equal(parts, t_flt)
-    # the oracle's ranks on a sample (ties within 1e-5 relative of the true score excepted)
+    # the oracle's ranks on a sample (eligible candidates within 1e-5 relative of the true score excepted)
+    band = RankBand()
     for qi in range(40):
-        x = Xq[qi]
-        want = RS.get_rank(ref, W, x, pos, side)
-        if t_flt[qi] + 1 != want:
-            sc = RS.get_scores_all(ref, W, x, side)
-            with torch.no_grad():
-                one = lambda v: torch.tensor([int(v)])
-                pp = float(ref.score_hrt(W, one(x[0]), one(x[1]), one(x[2]))[0])
-            near = int(((sc - pp).abs() <= 1e-5 * max(1.0, abs(pp))).sum())
-            assert abs(int(t_flt[qi]) + 1 - want) <= near, (qi, int(t_flt[qi]) + 1, want, near)
+        oracle_rank_check(band, ref, W, Xq[qi], side, pos, int(t_flt[qi]) + 1, qi)
+    print(model, score, side, band.summary())
+    assert band.used <= 4, band.summary()
