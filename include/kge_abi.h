@@ -335,6 +335,22 @@ int kge_rank(kge_ctx*, const kge_cfg*, const kge_tables*, const void* queries, i
              int side, const kge_filter* filter, int64_t ent_lo, int64_t ent_hi,
              int32_t* count_out, void* ws, size_t ws_bytes, void* stream);
 
+/* kge_rank for callers that cannot allocate or hand over scratch memory (CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments and results as kge_rank minus the workspace; covers the CUDA-core
+ * Lp-tile path only (UM / TransE / RotatE with LpDistance / LpDistancePow, else KGE_EUNSUPPORTED).  The
+ * scratch (query vectors + thresholds, 4 * (ld + 1) bytes per query rounded up to 128 queries, ld = row
+ * floats rounded up to 4) is a `static __device__` array of KGE_RANK_STATIC_BYTES inside the library —
+ * every GPU that loads the library holds it until exit — and a call that needs more returns
+ * KGE_EWORKSPACE (C1, d = 50: up to 19 712 queries per call).  The call allocates nothing (no cudaMalloc /
+ * cudaFree / allocating library routine).  All calls share the array: it keeps the previous call's
+ * contents (the part a call uses is cleared first) and calls that overlap on the GPU race — one call at a
+ * time per device. */
+#define KGE_RANK_STATIC_BYTES (4 << 20)
+int kge_rank_lp_static(kge_ctx*, const kge_cfg*, const kge_tables*, const void* queries, int64_t Q,
+                       int side, const kge_filter* filter, int64_t ent_lo, int64_t ent_hi,
+                       int32_t* count_out, void* stream);
+
 /* Materialises the row-lazy tables (kge_tables.lazy_t): every row is replayed to step lazy_t and
  * last[] = lazy_t.  No-op when no table carries `last`.  One dense pass over the lazy tables
  * (read + write of w, m, v of the rows that are behind). */

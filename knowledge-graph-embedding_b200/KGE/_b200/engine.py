@@ -396,6 +396,21 @@ class Engine:
                                   ws.numel(), _stream()))
         return cnt
 
+    def rank_counts_static(self, queries, side, f_off=None, f_ids=None, ent_lo=0, ent_hi=None, out=None):
+        """kge_rank_lp_static: rank_counts without a workspace — the scratch is the library's static device
+        array (include/kge_abi.h); `out` (zeroed int32[Q]) lets the caller keep the call allocation-free."""
+        self.flush()
+        Qx = self._ids(queries)
+        Q = Qx.shape[0]
+        cnt = torch.zeros(Q, dtype=torch.int32, device=self.device) if out is None else out
+        flt = L.Filter()
+        if f_off is not None:
+            flt.off, flt.ids = f_off.data_ptr(), f_ids.data_ptr()
+        T = self._tables(False)
+        L.check(L.load().kge_rank_lp_static(self.ctx, C.byref(self.cfg), C.byref(T), _ptr(Qx), Q, side, C.byref(flt),
+                                            ent_lo, self.cfg.n_ent if ent_hi is None else ent_hi, _ptr(cnt), _stream()))
+        return cnt
+
     def set_option(self, option, value):
         """Implementation switch of the context (shared by every engine on the device)."""
         L.check(L.load().kge_set_option(self.ctx, option, int(value)))

@@ -83,7 +83,8 @@ SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destr
            "kge_train_step", "kge_train_step_host", "kge_train_grad", "kge_train_apply", "kge_rank", "kge_profile_begin", "kge_profile_end",
            "kge_set_option", "kge_flush_rows",
            "kge_shard_lookup", "kge_shard_pre", "kge_shard_grad", "kge_shard_apply",
-           "kge_peer_barrier", "kge_train_step_dp"]
+           "kge_peer_barrier", "kge_train_step_dp", "kge_rank_lp_static"]
+RANK_STATIC_BYTES = 4 << 20
 
 _LIB = None
 
@@ -123,6 +124,8 @@ def load():
                                   C.c_size_t, vp]
     L.kge_rank.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp, i64, i32, C.POINTER(Filter),
                            i64, i64, vp, vp, C.c_size_t, vp]
+    L.kge_rank_lp_static.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp, i64, i32, C.POINTER(Filter),
+                                     i64, i64, vp, vp]
     L.kge_shard_lookup.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Shard),
                                    C.POINTER(Dp), vp, i64, u64, u64, vp, vp, C.c_size_t, vp]
     L.kge_shard_pre.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Shard), u64, vp]
