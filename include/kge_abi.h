@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 8
+#define KGE_ABI_VERSION 9
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -135,11 +135,14 @@ typedef struct kge_sampler {
   int64_t n_types;
 } kge_sampler;
 
-/* Known-positive filter for ranking, CSR per query (replaces the two scans of
- * positive_X per query at BaseModel.py:646-650): ids[off[q] .. off[q+1]) are the
- * candidate entities to exclude for query q.  off == NULL means unfiltered. */
+/* Known-positive filter for ranking (replaces the two scans of positive_X per query at
+ * BaseModel.py:646-650): ids[off[q] .. END(q)) are the candidate entities to exclude for query q, with
+ * END(q) = end[q] when `end` is given, else off[q + 1] (a packed CSR).  off == NULL means unfiltered.
+ * An entity must not be listed twice for one query.  kge_filter_lookup fills this struct from a
+ * kge_filter_index (ranges into the index's own sorted entity array: nothing is copied). */
 typedef struct kge_filter {
   const int64_t* off;  const int64_t* ids;
+  const int64_t* end;   /* nullable */
 } kge_filter;
 
 typedef struct kge_ctx kge_ctx;
@@ -350,6 +353,25 @@ int kge_rank(kge_ctx*, const kge_cfg*, const kge_tables*, const void* queries, i
 int kge_rank_lp_static(kge_ctx*, const kge_cfg*, const kge_tables*, const void* queries, int64_t Q,
                        int side, const kge_filter* filter, int64_t ent_lo, int64_t ent_hi,
                        int32_t* count_out, void* stream);
+
+/* Filter index on the device: ONE sort of positive_X per (positive_X, side) instead of two
+ * scans of it per query (BaseModel.py:646-650).
+ *   kge_filter_index_bytes : bytes of the index and of the build workspace for n_pos triples.
+ *   kge_filter_index_build : positive = (n_pos, 3) ids of cfg->id_dtype on the device; sorts the composite
+ *                            key (r * n_ent + kept entity) * n_ent + candidate (64-bit radix sort), drops
+ *                            duplicate triples and triples with ids outside the tables, and leaves
+ *                            [header | pair keys | candidate entities] in `index`.  The workspace is free
+ *                            again when the call's work has run; the index is read by the calls below.
+ *   kge_filter_lookup      : begin_out[q], end_out[q] = the range of query q's (r, kept entity) pair in the
+ *                            index; filter_out (host struct, nullable) is filled for kge_rank.
+ * No host synchronisation anywhere: the number of unique triples never leaves the device.
+ * n_rel * n_ent^2 must stay below 2^63. */
+int kge_filter_index_bytes(const kge_cfg*, int64_t n_pos, size_t* index_bytes, size_t* ws_bytes);
+int kge_filter_index_build(kge_ctx*, const kge_cfg*, const void* positive, int64_t n_pos, int side,
+                           void* index, size_t index_bytes, void* ws, size_t ws_bytes, void* stream);
+int kge_filter_lookup(kge_ctx*, const kge_cfg*, const void* index, int64_t n_pos, const void* queries,
+                      int64_t Q, int side, int64_t* begin_out, int64_t* end_out, kge_filter* filter_out,
+                      void* stream);
 
 /* Materialises the row-lazy tables (kge_tables.lazy_t): every row is replayed to step lazy_t and
  * last[] = lazy_t.  No-op when no table carries `last`.  One dense pass over the lazy tables

@@ -381,15 +381,31 @@ class Engine:
         L.check(L.load().kge_constrain_table(self.ctx, C.byref(T), slot, op, _stream()))
         self.tab[slot].touch()
 
+    @staticmethod
+    def _filter_struct(f_off, f_ids):
+        """kge_filter from (f_off, f_ids): f_off int64[Q + 1] = a packed CSR, or int64[2, Q] = begin | end
+        ranges into f_ids (what filter.FilterIndex.lookup returns)."""
+        flt = L.Filter()
+        if f_off is not None:
+            if f_off.dim() == 2:
+                flt.off, flt.end = f_off[0].data_ptr(), f_off[1].data_ptr()
+            else:
+                flt.off = f_off.data_ptr()
+            flt.ids = f_ids.data_ptr()
+        return flt
+
+    def filter_index(self, positive_X, side):
+        """Device-side known-positive index of positive_X for one corrupt side (kge_filter_index_build)."""
+        from . import filter as _filter
+        return _filter.FilterIndex(self.ctx, self.cfg, positive_X, side, self.device)
+
     def rank_counts(self, queries, side, f_off=None, f_ids=None, ent_lo=0, ent_hi=None):
         self.flush()
         Qx = self._ids(queries)
         Q = Qx.shape[0]
         cnt = torch.zeros(Q, dtype=torch.int32, device=self.device)
         ws = self._workspace(0, Q)
-        flt = L.Filter()
-        if f_off is not None:
-            flt.off, flt.ids = f_off.data_ptr(), f_ids.data_ptr()
+        flt = self._filter_struct(f_off, f_ids)
         T = self._tables(False)
         L.check(L.load().kge_rank(self.ctx, C.byref(self.cfg), C.byref(T), _ptr(Qx), Q, side, C.byref(flt),
                                   ent_lo, self.cfg.n_ent if ent_hi is None else ent_hi, _ptr(cnt), _ptr(ws),
@@ -403,9 +419,7 @@ class Engine:
         Qx = self._ids(queries)
         Q = Qx.shape[0]
         cnt = torch.zeros(Q, dtype=torch.int32, device=self.device) if out is None else out
-        flt = L.Filter()
-        if f_off is not None:
-            flt.off, flt.ids = f_off.data_ptr(), f_ids.data_ptr()
+        flt = self._filter_struct(f_off, f_ids)
         T = self._tables(False)
         L.check(L.load().kge_rank_lp_static(self.ctx, C.byref(self.cfg), C.byref(T), _ptr(Qx), Q, side, C.byref(flt),
                                             ent_lo, self.cfg.n_ent if ent_hi is None else ent_hi, _ptr(cnt), _stream()))

@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 8
+KGE_ABI_VERSION = 9
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -49,7 +49,7 @@ class Sampler(C.Structure):
 
 
 class Filter(C.Structure):
-    _fields_ = [("off", C.c_void_p), ("ids", C.c_void_p)]
+    _fields_ = [("off", C.c_void_p), ("ids", C.c_void_p), ("end", C.c_void_p)]
 
 
 class Dp(C.Structure):
@@ -83,7 +83,8 @@ SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destr
            "kge_train_step", "kge_train_step_host", "kge_train_grad", "kge_train_apply", "kge_rank", "kge_profile_begin", "kge_profile_end",
            "kge_set_option", "kge_flush_rows",
            "kge_shard_lookup", "kge_shard_pre", "kge_shard_grad", "kge_shard_apply",
-           "kge_peer_barrier", "kge_train_step_dp", "kge_rank_lp_static"]
+           "kge_peer_barrier", "kge_train_step_dp", "kge_rank_lp_static",
+           "kge_filter_index_bytes", "kge_filter_index_build", "kge_filter_lookup"]
 RANK_STATIC_BYTES = 4 << 20
 
 _LIB = None
@@ -126,6 +127,9 @@ def load():
                            i64, i64, vp, vp, C.c_size_t, vp]
     L.kge_rank_lp_static.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp, i64, i32, C.POINTER(Filter),
                                      i64, i64, vp, vp]
+    L.kge_filter_index_bytes.argtypes = [C.POINTER(Cfg), i64, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
+    L.kge_filter_index_build.argtypes = [vp, C.POINTER(Cfg), vp, i64, i32, vp, C.c_size_t, vp, C.c_size_t, vp]
+    L.kge_filter_lookup.argtypes = [vp, C.POINTER(Cfg), vp, i64, vp, i64, i32, vp, vp, C.POINTER(Filter), vp]
     L.kge_shard_lookup.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Shard),
                                    C.POINTER(Dp), vp, i64, u64, u64, vp, vp, C.c_size_t, vp]
     L.kge_shard_pre.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Shard), u64, vp]

@@ -355,15 +355,17 @@ class KGEModel:
         assert corrupt_side in ("h", "t"), "corrupt_side can be 'h' or 't'"
         X = np.asarray(_plain(X)).reshape(-1, 3).astype(np.int64)
         side = _lib.SIDE_H if corrupt_side == "h" else _lib.SIDE_T
-        pos = None if positive_X is None else torch.as_tensor(np.asarray(_plain(positive_X))).to(eng.device)
+        # the known-positive index is built ONCE per call (one device sort of positive_X), every block of
+        # queries then costs two binary searches per query (kge_filter_lookup)
+        index = None if positive_X is None else eng.filter_index(np.asarray(_plain(positive_X)), corrupt_side)
         ranks = []
         # multi-GPU: each rank counts over its slice of the entity table, counts are summed
         e_lo, e_hi = _dp.entity_shard(n_ent)
         for lo in range(0, len(X), 16384):
-            blk = X[lo:lo + 16384]
+            blk = eng._ids(X[lo:lo + 16384])
             off = ids = None
-            if pos is not None:
-                off, ids = _filter.build_filter(pos, blk, corrupt_side, n_ent, eng.device)
+            if index is not None:
+                off, ids = index.lookup(blk)
             cnt = _dp.allreduce_counts(eng.rank_counts(blk, side, off, ids, ent_lo=e_lo, ent_hi=e_hi))
             ranks.append(cnt.cpu().numpy().astype(np.int64) + 1)
         return np.concatenate(ranks)

@@ -100,6 +100,7 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
   fill_model_dev(cfg, tables, p.md);
   p.queries = queries; p.id64 = cfg->id_dtype; p.Q = Q; p.side = side;
   p.f_off = filter ? filter->off : nullptr;
+  p.f_end = (filter && filter->off) ? (filter->end ? filter->end : filter->off + 1) : nullptr;
   p.f_ids = filter ? filter->ids : nullptr;
   p.ent_lo = ent_lo; p.ent_hi = ent_hi;
   p.count = count_out;
@@ -130,7 +131,7 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
     RankParams pp = p;
     pp.queries = (const char*) queries + (size_t) q0 * 3 * (cfg->id_dtype ? 8 : 4);
     pp.count = count_out + q0;
-    if (pp.f_off) pp.f_off = p.f_off + q0;
+    if (pp.f_off) { pp.f_off = p.f_off + q0; pp.f_end = p.f_end + q0; }
     pp.Q = qn;
     L.grid = dim3((unsigned) ((span + chunk - 1) / chunk), (unsigned) qn);
     int rc;

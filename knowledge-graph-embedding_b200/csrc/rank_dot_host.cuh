@@ -134,8 +134,8 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
     if (filtered) {
       filt = reinterpret_cast<uint32_t*>(wsb + L.off_filt);
       KGE_CUDA_OK(cudaMemsetAsync(filt, 0, sizeof(uint32_t) * (size_t) qn * L.words_per_q, st));
-      k_rank_filter_bits<<<(unsigned) ((qn + 7) / 8), 256, 0, st>>>(filter->off + q0, filter->ids, qn, ent_lo, ent_hi,
-                                                                    filt, L.words_per_q);
+      k_rank_filter_bits<<<(unsigned) ((qn + 7) / 8), 256, 0, st>>>(filter->off + q0, (filter->end ? filter->end : filter->off + 1) + q0,
+                                                                    filter->ids, qn, ent_lo, ent_hi, filt, L.words_per_q);
       KGE_CUDA_OK(cudaGetLastError());
     }
 

@@ -142,12 +142,12 @@ __global__ void __launch_bounds__(256) k_rank_split_table(const float* w, int ld
 }
 
 // CSR filter -> per-query bitmask over the candidate shard (bit = excluded)
-__global__ void __launch_bounds__(256) k_rank_filter_bits(const int64_t* f_off, const int64_t* f_ids, int64_t Q,
+__global__ void __launch_bounds__(256) k_rank_filter_bits(const int64_t* f_off, const int64_t* f_end, const int64_t* f_ids, int64_t Q,
                                                           int64_t ent_lo, int64_t ent_hi, uint32_t* bits, int words_per_q) {
   const int lane = threadIdx.x & 31;
   const int64_t q = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (q >= Q) return;
-  for (int64_t f = f_off[q] + lane; f < f_off[q + 1]; f += WARP) {
+  for (int64_t f = f_off[q] + lane; f < f_end[q]; f += WARP) {
     const int64_t e = f_ids[f];
     if (e >= ent_lo && e < ent_hi) atomicOr(bits + q * (int64_t) words_per_q + ((e - ent_lo) >> 5), 1u << ((e - ent_lo) & 31));
   }

@@ -47,7 +47,8 @@ struct RankParams {
   int id64;
   int64_t Q;
   int side;                  // KGE_SIDE_H: candidates replace h; KGE_SIDE_T: replace t
-  const int64_t* f_off;      // nullable CSR filter
+  const int64_t* f_off;      // nullable filter: ids[f_off[q] .. f_end[q])   (kge_filter; packed CSR: f_end = f_off + 1)
+  const int64_t* f_end;
   const int64_t* f_ids;
   int64_t ent_lo, ent_hi;    // candidate shard
   int chunk;                 // candidates per CTA
@@ -73,7 +74,7 @@ __global__ void __launch_bounds__(RANK_THREADS) k_rank_generic(const RankParams 
   FwdSaved<NV> sv;
   const float pos = M::template forward<NV>(p.md, H, R, T, lane, x, y, sv);
 
-  const int64_t f0 = p.f_off ? p.f_off[q] : 0, f1 = p.f_off ? p.f_off[q + 1] : 0;
+  const int64_t f0 = p.f_off ? p.f_off[q] : 0, f1 = p.f_off ? p.f_end[q] : 0;
   const int64_t c0 = p.ent_lo + (int64_t) blockIdx.x * p.chunk;
   const int64_t c1 = (c0 + p.chunk < p.ent_hi) ? c0 + p.chunk : p.ent_hi;
   const bool head = (p.side == KGE_SIDE_H);

@@ -56,7 +56,7 @@ struct LpParams {
   float* thr;                      // [Q] clipped S of the true triple
   const float* E; int ldE; int d;  // candidate table; d = floats per row (2 x complex dimension for RotatE)
   int64_t ent_lo, ent_hi;
-  const int64_t* f_off; const int64_t* f_ids;
+  const int64_t* f_off; const int64_t* f_end; const int64_t* f_ids;      // kge_filter (f_end = f_off + 1 for a packed CSR)
   int32_t* count;
   float p;
 };
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(LP_THREADS) k_rank_lp_tile(const LpParams p) {
 template <int KIND, bool CPLX>
 __global__ void __launch_bounds__(256) k_rank_lp_filter(const LpParams p) {
   const int64_t q = blockIdx.x;
-  const int64_t lo = p.f_off[q], hi = p.f_off[q + 1];
+  const int64_t lo = p.f_off[q], hi = p.f_end[q];
   const float thr = p.thr[q];
   const float* qv = p.Qv + q * (int64_t) p.ldq;
   int c = 0;
@@ -251,6 +251,7 @@ inline int rank_lp_tiled(const kge_cfg* cfg, const kge_tables* tables, const voi
     p.queries = (const char*) queries + (size_t) q0 * 3 * (cfg->id_dtype ? 8 : 4);
     p.count = count_out + q0;
     p.f_off = (filter && filter->off) ? filter->off + q0 : nullptr;
+    p.f_end = (filter && filter->off) ? (filter->end ? filter->end : filter->off + 1) + q0 : nullptr;
     p.f_ids = filter ? filter->ids : nullptr;
     int rc;
     switch (kind) {

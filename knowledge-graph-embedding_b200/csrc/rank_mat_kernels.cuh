@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(RANK_THREADS) k_rank_mat(const RankParams p, c
   };
   const float pos = cand_score(head ? Eh : Et);       // same code path as the candidates
 
-  const int64_t f0 = p.f_off ? p.f_off[q] : 0, f1 = p.f_off ? p.f_off[q + 1] : 0;
+  const int64_t f0 = p.f_off ? p.f_off[q] : 0, f1 = p.f_off ? p.f_end[q] : 0;
   const int64_t c0 = p.ent_lo + (int64_t) blockIdx.x * p.chunk;
   const int64_t c1 = (c0 + p.chunk < p.ent_hi) ? c0 + p.chunk : p.ent_hi;
   int cnt = 0;
