@@ -39,11 +39,53 @@ METRIC = "train triples/sec (pos+neg)"
 
 
 def peaks():
+    """HBM / bf16 peaks: the driver-written MEASURED_PEAKS.json.  TF32 dense and NVLink store bandwidth are not in
+    that file: measured on the box by scripts/measure_peaks.py -> profiles/r02_extra_peaks.json (committed)."""
+    out = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "src": "fallback"}
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"], "src": "measured"}
-    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "src": "fallback"}
+        out = {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"], "src": "measured"}
+    out["tf32_tflops"], out["tf32_src"] = out["bf16_tflops"] / 2, "tf32 dense assumed = bf16 cuBLAS burst / 2"
+    x = os.path.join(ROOT, "profiles", "r02_extra_peaks.json")
+    if os.path.exists(x):
+        e = json.load(open(x))
+        if e.get("tf32_tflops"):
+            out["tf32_tflops"] = e["tf32_tflops"]
+            out["tf32_src"] = "measured: cuBLAS TF32 8192^3 best of 10 (profiles/r02_extra_peaks.json)"
+        out["nvlink_store_gbs"] = e.get("nvlink_store_gbs")
+    return out
+
+
+def roofline_all(share, fwd_bytes, upd_bytes, pk, world):
+    """One entry per phase of the C2 step (library CUDA events, ms per step): the critical path is
+    max(constraint + step, grouping chain) + update (+ apply and barriers when data parallel)."""
+    W = WORKLOAD
+    k_eff = 2 * (W["k"] // 2)
+    n_rec = W["B"] * (2 + k_eff) + W["B"]
+    n_keys = n_rec
+    rec_bytes = 4 * W["d"] * n_rec
+    rows = W["n_ent"] + W["n_rel"]
+    items = [("k_step<MDistMult,2,true>", "step", fwd_bytes, "forward gather 4*((2+k')*d + d) B per positive + ids"),
+             ("grouping chain: k_keys, k_scan, k_scatter, k_canon (side stream)", "sort", 28 * n_keys + 32 * rows,
+              "12*n_keys (keys) + 16*n_keys (scatter + canon) + 32 B header per table row"),
+             ("k_update_fast / k_update_heavy" + ("<3> (row sums to owners)" if world > 1 else ""), "update",
+              (upd_bytes if world == 1 else 4 * W["d"] * rows) + rec_bytes,
+              "6*4*rows*cols (w, m, v read + write) + the gradient records read back" if world == 1 else
+              "gradient records read + one row sum written per table row"),
+             ("k_dp_scales + k_update_fast<4> (owner apply, rows stored to every replica)", "apply",
+              upd_bytes // max(world, 1) + 4 * W["d"] * rows, "6*4*rows/G*cols + (G-1)/G of a w (+ wn) table out over NVLink"),
+             ("k_peer_barrier (first of two)", "barrier", 0, "latency only"),
+             ("k_constrain (skipped when the shadow table is valid)", "constraint", 8 * W["d"] * W["n_ent"], "2*4*rows*cols")]
+    out = []
+    for name, ph, nbytes, what in items:
+        ms = share.get(ph)
+        if not ms:
+            continue
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        out.append({"kernel": name, "phase": ph, "avg_ms_per_step": ms, "bound": "hbm", "algorithmic_bytes": int(nbytes),
+                    "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"], "bytes_are": what})
+    return out
 
 
 def zipf_triples(n, N, R, seed):
@@ -283,52 +325,88 @@ def run_ours(args, rank, world, device):
     ms_cold, ms_warm, ms_e2e, ms_e2e_lag = t.tolist()
     triples = world * B * (1 + k_eff) * args.steps
     return {"eng": eng, "ms_cold": ms_cold, "ms_warm": ms_warm, "ms_e2e": ms_e2e, "ms_e2e_lag": ms_e2e_lag, "triples": triples,
-            "phases": phases, "n_calls": n_calls, "clocks": clk.summary(), "train": train,
+            "phases": phases, "n_calls": n_calls, "n_prof": n_prof, "clocks": clk.summary(), "train": train,
             "loss": float(loss_host.item())}
 
 
 def run_eval(eng, train, rank, world, device, reps=3):
-    """Filtered ranking, both sides, Q queries per side; queries sharded over ranks (tables
-    are replicated for this config, so no collective on the data path).  DistMult scores are
-    dot products: kge_rank runs the tcgen05 GEMM path (csrc/rank_dot_tc.cuh)."""
-    from KGE._b200.filter import build_filter
+    """Filtered ranking, both sides, Q queries per side.  DistMult scores are dot products: kge_rank runs the
+    tcgen05 GEMM path (csrc/rank_dot_tc.cuh).  One GPU: the whole entity table.  N > 1: every rank scores ALL
+    queries against its slice of the entity table (kge_rank ent_lo / ent_hi) and the int32 counts are summed by one
+    NCCL all-reduce — the collective is inside both timed regions.
+
+    kernel-only (`ms`): queries, filter index and ranges resident; kge_rank (+ all-reduce) only.
+    e2e (`ms_e2e`): what evaluate() does per call, from HOST buffers: H2D of positive_X and of the queries,
+    kge_filter_index_build (one sort per side), kge_filter_lookup, kge_rank, all-reduce, D2H of the counts."""
+    from KGE._b200 import dp as _dp
     W = WORKLOAD
     Q = W["eval_Q"]
     rng = np.random.default_rng(777)
     q_all = train[rng.integers(0, len(train), Q)]
-    mine = q_all[rank::world]
-    filt = {s: build_filter(train, mine, s, W["n_ent"], device) for s in ("h", "t")}
-    qd = torch.from_numpy(mine).to(device)
-    cnts = {}
-    for s in ("h", "t"):
-        cnts[s] = eng.rank_counts(qd, 0 if s == "h" else 1, *filt[s])
+    e_lo, e_hi = _dp.split_even(W["n_ent"], world, rank)
+    qd = torch.from_numpy(q_all).to(device)
+    index = {s: eng.filter_index(train, s) for s in ("h", "t")}
+    filt = {s: index[s].lookup(qd) for s in ("h", "t")}
+    side_id = {"h": 0, "t": 1}
+
+    def counts(s, q, f):
+        c = eng.rank_counts(q, side_id[s], f[0], f[1], ent_lo=e_lo, ent_hi=e_hi)
+        if world > 1:
+            torch.distributed.all_reduce(c)
+        return c
+    cnts = {s: counts(s, qd, filt[s]) for s in ("h", "t")}
     torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     eng.profile_begin(2 * reps)
     a.record()
     for _ in range(reps):
         for s in ("h", "t"):
-            eng.rank_counts(qd, 0 if s == "h" else 1, *filt[s])
+            counts(s, qd, filt[s])
     b.record()
     torch.cuda.synchronize()
     phases, n_calls = eng.profile_end()
-    t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=device)
+
+    # ---- e2e: host positive_X + host queries -> ranks on the host, per evaluate() call ----
+    pos_host = torch.from_numpy(train).pin_memory()
+    q_host = torch.from_numpy(q_all).pin_memory()
+    out_host = {s: torch.zeros(Q, dtype=torch.int32).pin_memory() for s in ("h", "t")}
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        for s in ("h", "t"):
+            pos_dev = pos_host.to(device, non_blocking=True)
+            q_dev = q_host.to(device, non_blocking=True)
+            idx = eng.filter_index(pos_dev, s)
+            out_host[s].copy_(counts(s, q_dev, idx.lookup(q_dev)), non_blocking=True)
+        torch.cuda.synchronize()
+    ms_e2e = (time.perf_counter() - t0) * 1e3
+    for s in ("h", "t"):
+        assert torch.equal(out_host[s], cnts[s].cpu()), "e2e ranks differ from the resident-input ranks"
+
+    t = torch.tensor([a.elapsed_time(b), ms_e2e], dtype=torch.float64, device=device)
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-    ms = float(t.item())
+    ms, ms_e2e = t.tolist()
     ranks = {s: (c.cpu().numpy() + 1).astype(np.float64) for s, c in cnts.items()}
     both = np.concatenate([ranks["h"], ranks["t"]])
     gemm_ms = phases["rank_gemm"] / max(n_calls, 1)
-    flops = 2.0 * W["n_ent"] * W["d"] * len(mine)            # algorithmic: 2*N*d per query (SURVEY 8d)
-    return {"queries": 2 * len(mine) * reps * world, "ms": ms, "kernel_ms": phases["rank"], "gemm_ms": gemm_ms,
+    flops = 2.0 * (e_hi - e_lo) * W["d"] * Q                  # algorithmic, this rank's slice: 2*N*d per query (SURVEY 8d)
+    return {"queries": 2 * Q * reps, "ms": ms, "ms_e2e": ms_e2e, "kernel_ms": phases["rank"], "gemm_ms": gemm_ms,
+            "h2d_bytes_per_call": int(pos_host.numel() * 8 + q_host.numel() * 8), "d2h_bytes_per_call": 4 * Q,
             "fix_ms": phases["rank_fix"] / max(n_calls, 1), "gemm_tflops": flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms else None,
-            "mrr": float(np.mean(1 / both)), "hits10": float(np.mean(both <= 10)), "ranks": ranks, "queries_used": mine}
+            "gemm_flops": flops, "sharding": "entity shards + NCCL all-reduce of int32 counts" if world > 1 else "none",
+            "mrr": float(np.mean(1 / both)), "hits10": float(np.mean(both <= 10)), "ranks": ranks, "queries_used": q_all}
 
 
 def cpu_oracle_eval(eng, train, ev, n_queries, threads):
     """The reference's get_rank loop (BaseModel.py:602-654: per query, two scans of positive_X, score all
-    entities) on host cores, on the first n_queries of the GPU's query set; also returns whether the GPU
-    ranks of those queries match (ties within 1e-5 excepted by construction of the oracle test)."""
+    entities) on host cores, on the first n_queries of the GPU's query set.  GPU ranks must equal the oracle's
+    except where an ELIGIBLE candidate (not the true entity, not filtered) scores within 1e-5 relative of the
+    true triple (north_star's documented tie band): `ranks_outside_tie_band` must be 0."""
     from oracle import ref_ops as O, ref_models as RM, ref_step as RS
     from KGE._b200 import spec
     W = WORKLOAD
@@ -341,15 +419,38 @@ def cpu_oracle_eval(eng, train, ev, n_queries, threads):
     dt = time.perf_counter() - t0
     cpu_all = np.concatenate([r_cpu["h"], r_cpu["t"]])
     gpu_all = np.concatenate([ev["ranks"]["h"][:n_queries], ev["ranks"]["t"][:n_queries]])
+    in_band = outside = 0
+    for s, col, fs in (("h", 0, 2), ("t", 2, 0)):
+        for q, x in enumerate(qs):
+            got, want = int(ev["ranks"][s][q]), int(r_cpu[s][q])
+            sc = RS.get_scores_all(ref, Wt, x, s).double().numpy()
+            with torch.no_grad():
+                one = lambda v: torch.tensor([int(v)])                    # noqa: E731
+                p = float(ref.score_hrt(Wt, one(x[0]), one(x[1]), one(x[2]))[0])
+            ex = train[(train[:, 1] == x[1]) & (train[:, fs] == x[fs]), col]
+            elig = np.ones(len(sc), bool)
+            elig[ex] = False
+            true_filtered = bool((ex == x[col]).any())
+            elig[x[col]] = False
+            want -= int((not true_filtered) and sc[x[col]] > p)           # the reference's self-count
+            if got == want:
+                continue
+            near = int((np.abs(sc - p) <= 1e-5 * max(1.0, abs(p)))[elig].sum())
+            if abs(got - want) <= near:
+                in_band += 1
+            else:
+                outside += 1
     return {"value": 2 * len(qs) / dt, "unit": "queries/s", "cores": threads, "kind": "port",
             "sample": f"{2 * len(qs)} queries (both sides of the first {len(qs)} eval triples), filter = train set",
             "mrr_cpu": float(np.mean(1 / cpu_all)), "mrr_gpu_same_queries": float(np.mean(1 / gpu_all)),
             "hits10_cpu": float(np.mean(cpu_all <= 10)), "hits10_gpu_same_queries": float(np.mean(gpu_all <= 10)),
-            "ranks_identical": int((cpu_all == gpu_all).sum()), "ranks_compared": int(len(cpu_all))}
+            "ranks_identical": int((cpu_all == gpu_all).sum()), "ranks_compared": int(len(cpu_all)),
+            "ranks_inside_tie_band": in_band, "ranks_outside_tie_band": outside}
 
 
-def cpu_oracle_steps(n_steps, threads):
-    """The reference math on host cores: oracle/ref_step.run_single_batch on the bench workload."""
+def cpu_oracle_steps(n_steps, threads, warmup=1):
+    """The reference math on host cores: oracle/ref_step.run_single_batch on the bench workload
+    (`warmup` untimed steps first)."""
     from oracle import ref_ops as O, ref_models as RM, ref_step as RS
     W = WORKLOAD
     torch.set_num_threads(threads)
@@ -359,15 +460,176 @@ def cpu_oracle_steps(n_steps, threads):
     train = zipf_triples(20000, W["n_ent"], W["n_rel"], 12345)
     rng = np.random.default_rng(5)
     times = []
-    for step in range(n_steps + 1):
+    for step in range(n_steps + warmup):
         X = train[rng.integers(0, len(train), W["B"])]
         t0 = time.perf_counter()
         ids, ke = RS.sample_negatives(12345, step, X, W["k"], W["side"], W["n_ent"])
         RS.run_single_batch(ref, Wt, opt, X, ids, ke, W["side"], True)
-        if step:                       # first step is warm-up
+        if step >= warmup:
             times.append(time.perf_counter() - t0)
     k_eff = 2 * (W["k"] // 2)
     return W["B"] * (1 + k_eff) * len(times) / sum(times), sum(times) / len(times)
+
+
+# ---------------------------------------------------------------------------------------------------
+# C5 (BASELINE.json configs[4]): synthetic 5 M entities x 1 k relations, TransE d = 128, L1, hinge, uniform
+# 'h+t' k = 32 — the one configuration whose tables (2.56 GB + Adam slots) do not sit in L2.
+#   N = 1 : row-lazy step on one GPU (kge_tables.lazy_t);   N > 1 : entity tables SHARDED over the ranks
+#   (kge_shard_*, the class KGEModel.train uses: _b200.shard.ShardedTrainer), weak scaling: 8192 positives per rank.
+# ---------------------------------------------------------------------------------------------------
+C5 = {"workload": "C5 TransE d=128 L1 hinge uniform h+t k=32, N=5,000,000 R=1,000 synthetic (h,t uniform, r Zipf)",
+      "n_ent": 5_000_000, "n_rel": 1000, "d": 128, "k": 32, "B_local": 8192, "eval_Q": 10000}
+
+
+def c5_batches(n, B, seed):
+    W = C5
+    rng = np.random.default_rng(seed)
+    wrel = 1.0 / np.arange(1, W["n_rel"] + 1)
+    wrel /= wrel.sum()
+    return [np.stack([rng.integers(0, W["n_ent"], B), rng.choice(W["n_rel"], size=B, p=wrel),
+                      rng.integers(0, W["n_ent"], B)], 1).astype(np.int64) for _ in range(n)]
+
+
+def run_c5(args, rank, world, device, pk):
+    from KGE._b200 import engine as E, spec, shard as SH, dp as _dp
+    W = C5
+    N, R, d, k = W["n_ent"], W["n_rel"], W["d"], W["k"]
+    B_local, B_global = W["B_local"], W["B_local"] * world
+    steps, warm = max(10, min(args.steps, 60)), 5
+
+    class _D:
+        pass
+
+    def desc(name, **kw):
+        o = type(name, (), {})()
+        for kk, v in kw.items():
+            setattr(o, kk, v)
+        return o
+    cfg = spec.make_cfg("TransE", N, R, d, score_fn=desc("LpDistance", p=1), loss_fn=desc("PairwiseHingeLoss", margin=1.0),
+                        negative_ratio=k, corrupt_side="h+t", constraint=True)
+    g = torch.Generator(device=device).manual_seed(12345)          # same stream on every rank (same GPU model)
+    lim = 6.0 / d ** 0.5
+    tabs = {0: (torch.rand((N, d), generator=g, device=device) * 2 - 1) * lim,
+            2: (torch.rand((R, d), generator=g, device=device) * 2 - 1) * lim}
+    batches = c5_batches(8, B_global, 4242)                       # GLOBAL batches, identical on every rank
+    dev_batches = [torch.from_numpy(b).to(device) for b in batches]
+    loss = torch.zeros(1, dtype=torch.float32, device=device)
+    parity = None
+    if world == 1:
+        eng = E.Engine(cfg, tabs, device=device, lazy=True)
+        step_fn = lambda X, i: eng.train_step(X, 3, i, loss_out=loss)                  # noqa: E731
+        prof_eng, slots_per_step = eng, 1
+    else:
+        tr = SH.ShardedTrainer(cfg, tabs, B_global, device)
+        step_fn = lambda X, i: tr.train_step(X, 3, i, loss_out=loss)                   # noqa: E731
+        prof_eng, slots_per_step = tr.ranks[0].eng, 3
+        # parity: the sharded step equals a one-GPU row-lazy step on the whole global batch (rank 0 runs it)
+        single = E.Engine(cfg, tabs, device=device, lazy=True) if rank == 0 else None
+        ls, lm = [], []
+        for i in range(2):
+            lm.append(float(step_fn(dev_batches[i], i).item()))
+            if single is not None:
+                ls.append(float(single.train_step(dev_batches[i], 3, i).item()))
+        if rank == 0:
+            parity = {"loss_sharded": lm, "loss_single_gpu_row_lazy": ls,
+                      "max_rel_diff": max(abs(a - b) / max(1.0, abs(b)) for a, b in zip(lm, ls)), "tolerance": 1e-5}
+        del single
+        torch.cuda.empty_cache()
+    del tabs
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+    for i in range(warm):
+        step_fn(dev_batches[i % 8], 10 + i)
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(steps):
+        step_fn(dev_batches[i % 8], 100 + i)
+    b.record()
+    barrier()
+    ms = a.elapsed_time(b)
+    n_prof = min(steps, 20)
+    prof_eng.profile_begin(n_prof * slots_per_step)
+    for i in range(n_prof):
+        step_fn(dev_batches[i % 8], 1000 + i)
+    barrier()
+    phases, n_calls = prof_eng.profile_end()
+    # e2e: pinned host GLOBAL batch -> H2D -> step -> D2H of the loss, stream synchronised every step
+    host_batches = [torch.from_numpy(x).pin_memory() for x in batches]
+    loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+    stage = torch.empty((B_global, 3), dtype=torch.int64, device=device)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        stage.copy_(host_batches[i % 8], non_blocking=True)
+        step_fn(stage, 2000 + i)
+        loss_host.copy_(loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    barrier()
+    ms_e2e = (time.perf_counter() - t0) * 1e3
+
+    # filtered eval: Q queries x 2 sides against all 5 M entities (CUDA-core Lp tile kernel), entity shards +
+    # all-reduce of the counts at N > 1 (the gathered table is replicated for evaluation only)
+    ev_eng = eng if world == 1 else tr.eval_engine()
+    Qn = W["eval_Q"]
+    known = np.concatenate(c5_batches(4, 50_000, 99))
+    rngq = np.random.default_rng(5)
+    Xq = torch.from_numpy(known[rngq.integers(0, len(known), Qn)]).to(device)
+    e_lo, e_hi = _dp.split_even(N, world, rank)
+    idx = {s: ev_eng.filter_index(known, s) for s in ("h", "t")}
+
+    def rank_all():
+        out = []
+        for s, sid in (("h", 0), ("t", 1)):
+            c = ev_eng.rank_counts(Xq, sid, *idx[s].lookup(Xq), ent_lo=e_lo, ent_hi=e_hi)
+            if world > 1:
+                torch.distributed.all_reduce(c)
+            out.append(c)
+        return out
+    ev_eng.rank_counts(Xq[:256], 1)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    cnt = rank_all()
+    e1.record()
+    barrier()
+    ms_eval = e0.elapsed_time(e1)
+    t = torch.tensor([ms, ms_e2e, ms_eval], dtype=torch.float64, device=device)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    ms, ms_e2e, ms_eval = t.tolist()
+    if rank != 0:
+        return None
+    k_eff = 2 * (k // 2)
+    triples = B_global * (1 + k_eff) * steps
+    alg = B_global * (7 * 4 * ((2 + k_eff) * d + d) + 24)           # 125 452 B per positive
+    gbs_per_gpu = alg / world / (ms / steps * 1e-3) / 1e9
+    rk = np.concatenate([c.cpu().numpy() for c in cnt]).astype(np.float64) + 1
+    out = {"workload": W["workload"], "metric": METRIC, "value": triples / (ms * 1e-3), "unit": "triples/s",
+           "n_gpus": world, "global_batch": B_global, "per_gpu_batch": B_local, "steps": steps, "ms_per_step": ms / steps,
+           "tables": "row-lazy, one GPU (kge_tables.lazy_t)" if world == 1 else
+                     "entity tables sharded over the ranks (kge_shard_*), relation table replicated",
+           "e2e": {"value": triples / (ms_e2e * 1e-3), "unit": "triples/s", "h2d_bytes_per_step": B_global * 24,
+                   "d2h_bytes_per_step": 4},
+           "roofline": {"bound": "hbm", "achieved": gbs_per_gpu, "peak": pk["hbm_gbs"], "unit": "GB/s per GPU",
+                        "frac": gbs_per_gpu / pk["hbm_gbs"], "algorithmic_bytes_per_step": alg,
+                        "note": "whole step (lookup, replay, gather, scores, backward, row update), 3 802 B per triple"},
+           "phase_ms_per_step": {kk: round(v / max(n_prof, 1), 5) for kk, v in phases.items() if v > 0},
+           "profile_slots": n_calls,
+           "nvlink_bytes_per_rank_per_step": 0 if world == 1 else int(
+               (world - 1) / world * B_local * (2 + k_eff) * (2 * d * 4 + 4)),
+           "nvlink_note": "owner-applies: one row read + one gradient row written per looked-up remote row, + its id",
+           "parity": parity,
+           "eval": {"metric": "filtered-eval queries/sec", "value": 2 * Qn / (ms_eval * 1e-3), "unit": "queries/s",
+                    "queries": 2 * Qn, "ms": ms_eval, "kernel": "k_rank_lp_tile (CUDA-core L1 tile)",
+                    "sharding": "entity shards + NCCL all-reduce of int32 counts" if world > 1 else "none",
+                    "lp_ops_per_s_T": 2 * Qn * N * d * 3 / (ms_eval * 1e-3) / 1e12,
+                    "mrr": float(np.mean(1 / rk)), "hits10": float(np.mean(rk <= 10))},
+           "final_loss": float(loss_host.item())}
+    return out
 
 
 def main():
@@ -378,6 +640,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-steps", type=int, default=30)
     ap.add_argument("--cpu-queries", type=int, default=64)
+    ap.add_argument("--no-c5", action="store_true", help="skip the C5 (5 M entities) leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -391,13 +654,17 @@ def main():
               "parallelism": f"dp{world}"}
 
     if args.impl == "reference":
+        # the reference's own CPU path for this step (TensorFlow 2.5 is not installable here: the oracle port),
+        # all host threads, rank 0 only; each timed step is one full step of the workload (B = 1024, 65 triples
+        # per positive), at most --cpu-steps of them so the run ends within minutes
         if rank != 0:
             return
         steps = min(args.steps, args.cpu_steps)
-        tps, spstep = cpu_oracle_steps(steps, cores)
-        sample = f"{steps} full steps of the bench workload (B={W['B']}, k'={k_eff}) after 1 warm-up step"
+        tps, spstep = cpu_oracle_steps(steps, cores, warmup=args.warmup)
+        sample = (f"{steps} full steps of the bench workload (B={W['B']}, k'={k_eff}) after {args.warmup} warm-up steps"
+                  + (f" (--steps {args.steps} capped at --cpu-steps {args.cpu_steps})" if steps < args.steps else ""))
         print(json.dumps({"impl": "reference", "metric": METRIC, "value": tps, "unit": "triples/s", "n_gpus": args.gpus,
-                          "steps": steps, "warmup": 1, "ms_per_step": spstep * 1e3, "higher_is_better": True,
+                          "steps": steps, "warmup": args.warmup, "ms_per_step": spstep * 1e3, "higher_is_better": True,
                           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
                           "cpu_baseline": {"value": tps, "unit": "triples/s", "cores": cores, "kind": "port",
                                            "sample": sample},
@@ -414,6 +681,11 @@ def main():
         torch.distributed.init_process_group("nccl", device_id=device)
     r = run_ours(args, rank, world, device)
     ev = run_eval(r["eng"], r["train"], rank, world, device)
+    c5 = None
+    if not args.no_c5:
+        eng_keep = r.pop("eng")
+        c5 = run_c5(args, rank, world, device, peaks())
+        r["eng"] = eng_keep
     if rank != 0:
         if world > 1:
             torch.distributed.destroy_process_group()
@@ -426,12 +698,14 @@ def main():
     # segment table) runs on the side stream concurrently with constraint + step
     share = {k: round(v / max(r["n_calls"], 1), 5) for k, v in r["phases"].items() if v > 0}
     cpu_tps, cpu_s = cpu_oracle_steps(args.cpu_steps, cores)
+    assert r["n_calls"] == r["n_prof"], ("profile slots", r["n_calls"], r["n_prof"])     # one slot per step, also data-parallel
     cpu_ev = cpu_oracle_eval(r["eng"], r["train"], ev, args.cpu_queries, cores)
     out = {
         "metric": METRIC, "value": r["triples"] / (r["ms_cold"] * 1e-3), "unit": "triples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_cold"] / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": dict(config, exchange=(getattr(r["eng"], "_dp_kind", None) or "none") if world > 1 else "none"),
+        "config": config,
+        "exchange": (getattr(r["eng"], "_dp_kind", None) or "none") if world > 1 else "none",
         "clocks": r["clocks"],
         "value_steady_state_l2_warm": r["triples"] / (r["ms_warm"] * 1e-3),
         "e2e": {"value": r["triples"] / (r["ms_e2e"] * 1e-3), "unit": "triples/s",
@@ -452,18 +726,27 @@ def main():
                                      "the 12 MB entity table is read from HBM once and re-gathered from L2",
                      "peak_src": pk["src"],
                      "algorithmic_bytes_per_launch": fwd_bytes, "avg_launch_ms": step_ms, "phase_ms_per_step": share},
+        "roofline_all": roofline_all(share, fwd_bytes, upd_bytes, pk, world),
         "cpu_baseline": {"value": cpu_tps, "unit": "triples/s", "cores": cores, "kind": "port",
                          "sample": f"{args.cpu_steps} full steps of the same workload on the host (oracle port; "
                                    "TensorFlow reference not installable)"},
         "eval": {"metric": "filtered-eval queries/sec", "value": ev["queries"] / (ev["ms"] * 1e-3), "unit": "queries/s",
-                 "queries": ev["queries"], "kernel": "k_rank_dot_tc (tcgen05 kind::tf32) + k_rank_dot_fix/filter",
+                 "value_note": "kernel-only: queries, filter index and ranges resident; kge_rank (+ all-reduce of counts at N > 1)",
+                 "e2e": {"value": ev["queries"] / (ev["ms_e2e"] * 1e-3), "unit": "queries/s",
+                         "h2d_bytes_per_call": ev["h2d_bytes_per_call"], "d2h_bytes_per_call": ev["d2h_bytes_per_call"],
+                         "what": "per evaluate() call and side: H2D of positive_X (483 142 triples) and of the queries, "
+                                 "kge_filter_index_build (one 64-bit radix sort), kge_filter_lookup, kge_rank, "
+                                 "all-reduce, D2H of the counts; host synchronised after both sides"},
+                 "queries": ev["queries"], "sharding": ev["sharding"],
+                 "kernel": "k_rank_dot_tc (tcgen05 kind::tf32) + k_rank_dot_fix/filter",
                  "mrr": ev["mrr"], "hits10": ev["hits10"],
-                 "roofline": {"bound": "tensor", "achieved": ev["gemm_tflops"], "peak": pk["bf16_tflops"] / 2,
-                              "unit": "TFLOP/s", "frac": (ev["gemm_tflops"] or 0) / (pk["bf16_tflops"] / 2),
-                              "peak_note": "tf32 dense = measured bf16 cuBLAS burst / 2 (MEASURED_PEAKS.json has no tf32 entry)",
-                              "algorithmic_flops_per_launch": 2.0 * W["n_ent"] * W["d"] * W["eval_Q"] / world,
+                 "roofline": {"bound": "tensor", "achieved": ev["gemm_tflops"], "peak": pk["tf32_tflops"],
+                              "unit": "TFLOP/s", "frac": (ev["gemm_tflops"] or 0) / pk["tf32_tflops"],
+                              "peak_note": pk["tf32_src"],
+                              "algorithmic_flops_per_launch": ev["gemm_flops"],
                               "avg_launch_ms": ev["gemm_ms"], "fixup_filter_ms": ev["fix_ms"], "traffic": ncu_traffic("k_rank_dot_tc")},
                  "cpu_baseline": cpu_ev},
+        "c5": c5,
         "final_loss": r["loss"],
     }
     print(json.dumps(out))

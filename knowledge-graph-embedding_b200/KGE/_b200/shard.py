@@ -208,3 +208,110 @@ def emulate_step(ranks, batches, seed, step, B_global, bases, neg_overrides=None
     for r in ranks:
         r.gbuf.flat.copy_(total)
     return [r.apply() for r in ranks][0]
+
+
+class ShardedTrainer:
+    """What KGEModel.train / evaluate drive when the entity tables are sharded: either
+    this process's rank of a torchrun job (`emulate` = 0: one ShardedEngine, peers over torch symmetric
+    memory, collectives over the default process group) or `emulate` = G ranks on ONE device (tests,
+    single-GPU dry runs: plain buffers, phases in lock-step, the all-reduce replaced by a rank-ordered sum).
+
+    `values` = {slot: full (rows, ...) tensor}: every rank is given the same full initial tables (same
+    seed) and keeps its own rows of the entity slots."""
+
+    def __init__(self, cfg_kwargs, values, B_global_max, device, emulate=0, group=None):
+        self.device, self.group = torch.device(device), group
+        self.emulated = int(emulate) > 1
+        self.rank, self.world = (0, int(emulate)) if self.emulated else _dp.world()
+        self.cfg_kwargs = dict(cfg_kwargs)
+        self.n_ent = int(cfg_kwargs["n_ent"])
+        self.S = shard_rows(self.n_ent, self.world)
+        ent = {s: torch.as_tensor(v, dtype=torch.float32) for s, v in values.items() if s < 2}
+        rel = {s: v for s, v in values.items() if s >= 2}
+        self.shapes = {s: tuple(v.shape) for s, v in ent.items()}
+        lds = {s: (int(np.prod(v.shape[1:])) + 3) // 4 * 4 for s, v in ent.items()}
+        probe = _engine.Engine.__new__(_engine.Engine)          # k_eff without building an engine
+        probe.cfg = L.Cfg(negative_ratio=int(cfg_kwargs["negative_ratio"]), corrupt_side=int(cfg_kwargs["corrupt_side"]))
+        k_eff = probe.k_eff()
+        self.B_local_max = -(-int(B_global_max) // self.world)
+        cap = (2 + k_eff) * self.B_local_max
+        rows = lambda g: (g * self.S, min(self.n_ent, (g + 1) * self.S))      # noqa: E731
+        if self.emulated:
+            mems = ShardMemory.local(self.S, lds, self.world, cap, self.device)
+            self.ranks = [ShardedEngine(cfg_kwargs, {s: v[rows(g)[0]:rows(g)[1]] for s, v in ent.items()}, rel, g,
+                                        self.world, mems[g], self.B_local_max, device=self.device)
+                          for g in range(self.world)]
+        else:
+            mem = ShardMemory.symmetric(self.S, lds, cap, self.device, group)
+            lo, hi = rows(self.rank)
+            self.ranks = [ShardedEngine(cfg_kwargs, {s: v[lo:hi] for s, v in ent.items()}, rel, self.rank, self.world,
+                                        mem, self.B_local_max, device=self.device)]
+        self._eval_engine = None
+
+    # ---- engines ------------------------------------------------------------------------------
+    @property
+    def engines(self):
+        return [r.eng for r in self.ranks]
+
+    def each_engine(self, fn):
+        for r in self.ranks:
+            fn(r.eng)
+
+    # ---- training -----------------------------------------------------------------------------
+    def train_step(self, batch, seed, step, loss_out=None):
+        """One step on the GLOBAL batch (identical on every rank): each rank takes its contiguous share."""
+        B = int(batch.shape[0])
+        self._eval_engine = None
+        if self.emulated:
+            parts, bases = [], []
+            for g in range(self.world):
+                lo, hi = _dp.split_even(B, self.world, g)
+                parts.append(batch[lo:hi])
+                bases.append(lo)
+            if min(len(p) for p in parts) == 0:
+                raise ValueError(f"batch of {B} positives cannot be split over {self.world} ranks")
+            loss = emulate_step(self.ranks, parts, seed, step, B, bases)
+            if loss_out is not None:
+                loss_out.copy_(loss)
+                return loss_out
+            return loss
+        lo, hi = _dp.split_even(B, self.world, self.rank)
+        if hi == lo:
+            raise ValueError(f"batch of {B} positives cannot be split over {self.world} ranks")
+        return self.ranks[0].train_step(batch[lo:hi], seed, step, B, lo, loss_out=loss_out, group=self.group)
+
+    # ---- reading / writing whole tables -----------------------------------------------------------
+    def full_table(self, slot):
+        """(n_ent, ...) entity table or the replicated relation table, materialised (flushed), on this rank."""
+        if slot >= 2:
+            return self.ranks[0].eng.tab[slot].view
+        if self.emulated:
+            flat = torch.cat([r.local_rows(slot).reshape(r.hi - r.lo, -1) for r in self.ranks], 0)
+        else:
+            flat = self.ranks[0].gather_entity_table(slot, self.group)
+        return flat.reshape(self.shapes[slot])
+
+    def assign_table(self, slot, value):
+        """Overwrite a table from a full tensor (restore / assign): every rank keeps its rows; optimizer state
+        of the touched rows is kept, the lazy stamps are brought to the current step first."""
+        value = torch.as_tensor(value, dtype=torch.float32).to(self.device)
+        self._eval_engine = None
+        for r in self.ranks:
+            r.eng.flush()
+            pt = r.eng.tab[slot]
+            if slot >= 2:
+                pt.view.copy_(value.reshape(pt.shape))
+            else:
+                pt.view.copy_(value[r.lo:r.hi].reshape(pt.shape))
+            pt.touch()
+
+    def eval_engine(self):
+        """Engine on the gathered (replicated) tables for scoring / ranking: only the TRAINING state
+        (w, m, v, last) is sharded; evaluation keeps w replicated (2.56 GB at C5) and shards the candidates
+        (kge_rank ent_lo / ent_hi + all-reduce of the counts).  Cached until the next training step."""
+        if self._eval_engine is None:
+            tabs = {s: self.full_table(s) for s in self.ranks[0].eng.tab}
+            self._eval_engine = _engine.Engine(self.cfg_kwargs, tabs, device=self.device)
+            self._eval_engine.sampler, self._eval_engine._sampler_keep = self.ranks[0].eng.sampler, self.ranks[0].eng._sampler_keep
+            self._eval_engine.cfg.sampler = self.ranks[0].eng.cfg.sampler
+        return self._eval_engine

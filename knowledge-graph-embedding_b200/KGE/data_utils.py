@@ -145,6 +145,16 @@ class DeviceBatchStream:
     def __iter__(self):
         return self
 
+    def skip(self, n_batches):
+        """Advance by n_batches without materialising them (resume): same generator draws as iterating."""
+        need = int(n_batches) * self.batch_size
+        while need > 0:
+            take = min(need, self.n - self.cursor)
+            self.cursor += take
+            need -= take
+            if self.cursor == self.n:
+                self.order, self.cursor = self._new_pass(), 0
+
     def __next__(self):
         need, pieces = self.batch_size, []
         while need > 0:

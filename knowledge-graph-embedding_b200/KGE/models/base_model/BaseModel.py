@@ -27,7 +27,7 @@ from ... import metrics as _metrics
 from ...data_utils import DeviceBatchStream, calculate_data_size, load_triples
 from ...ns_strategy import TypedStrategy, UniformStrategy, _type_csr, check_typed_pools
 from ...optimizers import adam_fields
-from ..._b200 import dp as _dp, engine as _engine, filter as _filter, lib as _lib, spec as _spec
+from ..._b200 import dp as _dp, engine as _engine, lib as _lib, shard as _shard, spec as _spec
 
 logging.getLogger().setLevel(logging.INFO)
 
@@ -63,12 +63,30 @@ class WeightView:
         v = torch.as_tensor(np.asarray(v) if not torch.is_tensor(v) else v, dtype=torch.float32)
         if tuple(v.shape) != self.shape:
             raise ValueError(f"{self.name}: shape {tuple(v.shape)} != {self.shape}")
+        if hasattr(self._table, "assign"):          # sharded table: every rank keeps its own rows
+            self._table.assign(v)
+            return self
         self._table.view.copy_(v.to(self._table.storage.device))
         self._table.touch()          # the training step's shadow of this table is stale now
         return self
 
     def __repr__(self):
         return f"WeightView({self.name}, shape={self.shape})"
+
+
+class ShardedTableView:
+    """The table object behind a WeightView when the entity tables are sharded over the GPUs
+    (_b200/shard.py): reading gathers the full table, assigning scatters it."""
+
+    def __init__(self, trainer, slot, shape):
+        self._trainer, self._slot, self.shape = trainer, slot, tuple(shape)
+
+    @property
+    def view(self):
+        return self._trainer.full_table(self._slot)
+
+    def assign(self, value):
+        self._trainer.assign_table(self._slot, value)
 
 
 class KGEModel:
@@ -91,6 +109,7 @@ class KGEModel:
         self.metadata = None
         self._model_weights_initial = None
         self._engine = None
+        self._sharded = None                 # _b200.shard.ShardedTrainer when the entity tables are sharded
         self._optimizer = "Adam"
         self.seed = None
 
@@ -159,18 +178,59 @@ class KGEModel:
                              rotate_limit=self._rotate_limit())
         cfg.update(adam_fields(self._optimizer))
         slots = _spec.SLOTS[self.MODEL]
+        self._sharded = None
+        world = self._shard_world(cfg, values)
+        if world:
+            # entity tables (w, m, v, last) sharded over the ranks; relation tables replicated
+            self._sharded = _shard.ShardedTrainer(cfg, {slots[k]: v for k, v in values.items()},
+                                                  getattr(self, "batch_size", None) or 1, self.device,
+                                                  emulate=world if _dp.world()[1] == 1 else 0)
+            self._engine = None
+            self.model_weights = {k: WeightView(k, ShardedTableView(self._sharded, slots[k], values[k].shape))
+                                  for k in values}
+            return
         self._engine = _engine.Engine(cfg, {slots[k]: v for k, v in values.items()}, device=self.device,
                                       lazy=self._lazy_rows(cfg, values))
         self.model_weights = {k: WeightView(k, self._engine.tab[slots[k]]) for k in values}
+
+    def _row_sparse_eligible(self, cfg):
+        """Models / settings the row-lazy and sharded steps cover: vector models without a dense regulariser,
+        Adam (kge_abi.h: 'Row-lazy and sharded tables: Adam only')."""
+        vec = self.MODEL in ("UM", "TransE", "TransD", "RotatE", "DistMult") or \
+            (self.MODEL == "TransH" and not cfg["constraint"])
+        return vec and cfg.get("optimizer", _lib.OPTIM_ADAM) == _lib.OPTIM_ADAM
+
+    def _shard_world(self, cfg, values):
+        """Number of ranks the entity tables are sharded over, 0 = replicated tables.  Under torchrun
+        (or KGE_B200_SHARD_EMULATE=G ranks emulated on one device) the tables are sharded when they exceed
+        KGE_B200_SHARD_BYTES (default 512 MB: far beyond L2, the dense per-batch passes would dominate) or when
+        KGE_B200_SHARD=1 forces it; KGE_B200_SHARD=0 keeps full replicas + the data-parallel step."""
+        emu = int(os.environ.get("KGE_B200_SHARD_EMULATE", "0"))
+        world = _dp.world()[1] if _dp.world()[1] > 1 else (emu if emu > 1 else 1)
+        flag = os.environ.get("KGE_B200_SHARD", "auto")
+        if world < 2 or flag == "0" or getattr(self, "batch_size", None) is None:
+            return 0
+        if not self._row_sparse_eligible(cfg):
+            if flag == "1":
+                raise NotImplementedError("KGE_B200_SHARD=1: sharded entity tables cover the vector models without a "
+                                          "dense regulariser, with Adam")
+            return 0
+        if flag == "1":
+            return world
+        ent_bytes = 4 * sum(int(np.prod(v.shape)) for k, v in values.items() if k.startswith("ent"))
+        return world if ent_bytes >= int(os.environ.get("KGE_B200_SHARD_BYTES", str(512 << 20))) else 0
 
     def _lazy_rows(self, cfg, values):
         """Row-lazy replay of the dense per-batch table passes (kge_abi.h, kge_tables.lazy_t; results are
         bit-identical to the dense step).  KGE_B200_LAZY_ROWS=1|0 forces it; by default it is used when
         the entity table is far larger than L2 (>= 512 MB) on a single GPU, for the models it covers."""
-        eligible = self.MODEL in ("UM", "TransE", "TransD", "RotatE", "DistMult") or \
-            (self.MODEL == "TransH" and not cfg["constraint"])
         flag = os.environ.get("KGE_B200_LAZY_ROWS", "auto")
-        if not eligible or _dp.world()[1] > 1 or flag == "0":
+        if _dp.world()[1] > 1 or flag == "0":
+            return False
+        if not self._row_sparse_eligible(cfg):
+            if flag == "1":
+                raise NotImplementedError("KGE_B200_LAZY_ROWS=1: row-lazy tables cover the vector models without a "
+                                          "dense regulariser, with Adam (other optimizers take the dense step)")
             return False
         if flag == "1":
             return True
@@ -179,7 +239,7 @@ class KGEModel:
 
     def restore_model_weights(self, model_weights):
         self._check_model_weights(model_weights)
-        if self._engine is None:
+        if self._engine is None and self._sharded is None:
             self._model_weights_initial = model_weights
             self._init_embeddings(self.seed)
             return
@@ -187,13 +247,20 @@ class KGEModel:
             view.assign(_plain(model_weights[k]))
 
     def _require_engine(self):
+        """The engine scoring / ranking run on: the model's own, or — sharded entity tables — one on the
+        gathered tables (ShardedTrainer.eval_engine; under torchrun every rank must make the call)."""
+        if self._sharded is not None:
+            return self._sharded.eval_engine()
         if self._engine is None:
             raise RuntimeError("model has no weights yet: call train() or _init_embeddings() first")
         return self._engine
 
+    def _train_engines(self):
+        return self._sharded.engines if self._sharded is not None else [self._require_engine()]
+
     # ---- sampler ----------------------------------------------------------------------
     def _setup_sampler(self):
-        eng, n_ent = self._require_engine(), self._sizes()[0]
+        n_ent = self._sizes()[0]
         ns = self.ns_strategy
         if ns is UniformStrategy:
             self.ns_strategy = ns = UniformStrategy(sample_pool=np.arange(n_ent))
@@ -205,11 +272,13 @@ class KGEModel:
                                                                        "ind2type": labels})
         if isinstance(ns, UniformStrategy):
             pool = ns.pool_array()
-            eng.set_uniform_pool(None if np.array_equal(pool, np.arange(n_ent)) else pool)
+            for eng in self._train_engines():
+                eng.set_uniform_pool(None if np.array_equal(pool, np.arange(n_ent)) else pool)
         elif isinstance(ns, TypedStrategy):
             ent_type, off, members, pos = ns.csr()
             check_typed_pools(ent_type, off, pos)
-            eng.set_typed_pools(ent_type, off, members, pos)
+            for eng in self._train_engines():
+                eng.set_typed_pools(ent_type, off, members, pos)
         else:
             raise NotImplementedError("ns_strategy must be UniformStrategy or TypedStrategy (class or instance): "
                                       "negatives are drawn inside the CUDA step kernel")
@@ -217,9 +286,11 @@ class KGEModel:
     # ---- training ---------------------------------------------------------------------
     def train(self, train_X, val_X, metadata, epochs, batch_size, early_stopping_rounds=None,
               model_weights_initial=None, restore_best_weight=True, optimizer="Adam", seed=None,
-              log_path="./logs", log_projector=False):
+              log_path="./logs", log_projector=False, resume=False):
         """Same arguments as the reference (BaseModel.py:58-61).  `seed` additionally seeds the
-        Philox negative-sampling stream (the reference leaves that stream unseeded)."""
+        Philox negative-sampling stream (the reference leaves that stream unseeded).
+        `resume=True` (extension): continue from the checkpoint in `log_path` — weights, optimizer slots,
+        step counters and the position in the seeded batch stream."""
         self.metadata = metadata
         self.batch_size = batch_size
         self._model_weights_initial = model_weights_initial
@@ -237,37 +308,56 @@ class KGEModel:
         val_iter = DeviceBatchStream(val_X, batch_size, shuffle=False, device=self.device) if val_X is not None else None
         self._init_embeddings(seed=seed)
         self._setup_sampler()
-        eng = self._engine
+        eng, sharded = self._engine, self._sharded
+        device = torch.device(self.device)
         ns_seed = int(seed) if seed is not None else int.from_bytes(os.urandom(7), "little")
-        # multi-GPU (torch.distributed initialised by the launcher): every rank walks the same
-        # seeded batch sequence and owns a contiguous share of each batch; gradients are summed
-        # with one all-reduce per step, replicas stay identical.  Matrix models (SE / TransR /
-        # RESCAL) have no split step yet: their ranks repeat the whole batch (identical replicas).
+        # multi-GPU (torch.distributed initialised by the launcher): every rank walks the same seeded batch
+        # sequence and owns a contiguous share of each batch.  Tables that fit one GPU are replicated and the
+        # gradients exchanged per step (kge_train_step_dp); entity tables beyond KGE_B200_SHARD_BYTES are
+        # sharded over the ranks (kge_shard_*).  Matrix models (SE / TransR / RESCAL) have no split step:
+        # their ranks repeat the whole batch (identical replicas).
         rank, world_size = _dp.world()
-        split = world_size > 1 and self.MODEL not in ("SE", "TransR", "RESCAL")
+        split = world_size > 1 and sharded is None and self.MODEL not in ("SE", "TransR", "RESCAL")
         if world_size > 1:
             assert seed is not None, "multi-GPU training needs a seed: every rank must walk the same batch sequence"
-        step = 0
+        step, first_epoch = 0, 0
         self.train_loss_history, self.val_loss_history = [], []
         self.best_step, patience = None, 0
+        if resume:
+            state = self._load_checkpoint(with_optimizer=True)
+            step, first_epoch = int(state.get("step", 0)), int(state.get("epoch", -1)) + 1
+            self.train_loss_history = list(state.get("train_loss_history", []))
+            self.val_loss_history = list(state.get("val_loss_history", []))
+            self.best_step, patience = state.get("best_step"), int(state.get("patience", 0))
+            train_iter.skip(first_epoch * n_batches)
+            if val_iter is not None:
+                val_iter.skip(first_epoch * min(n_batches, n_val_batches))
 
         logging.info("[%s] Start Training..." % _now())
-        for epoch in range(epochs):
-            t_loss = torch.zeros(n_batches, dtype=torch.float32, device=eng.device)
-            v_loss = torch.zeros(max(n_val_batches, 1), dtype=torch.float32, device=eng.device)
+        for epoch in range(first_epoch, epochs):
+            t_loss = torch.zeros(n_batches, dtype=torch.float32, device=device)
+            v_loss = torch.zeros(max(n_val_batches, 1), dtype=torch.float32, device=device)
             for b in range(n_batches):
                 batch = next(train_iter)
-                if split:
+                if sharded is not None:
+                    sharded.train_step(batch, ns_seed, step, loss_out=t_loss[b:b + 1])
+                elif split:
                     lo, hi = _dp.batch_shard(len(batch))
                     eng.train_step_dp(batch[lo:hi], ns_seed, step, len(batch), lo, loss_out=t_loss[b:b + 1])
                 else:
                     eng.train_step(batch, ns_seed, step, is_train=True, loss_out=t_loss[b:b + 1])
                 step += 1
                 if val_iter is not None and b < n_val_batches:
-                    # validation batches draw negatives and apply the constraint too
-                    eng.train_step(next(val_iter), ns_seed, step, is_train=False, loss_out=v_loss[b:b + 1])
+                    # validation batches draw negatives and apply the constraint too.  Sharded
+                    # tables: the loss is computed on the gathered replica and the constraint's rewrite of w is
+                    # left to the next training step, which applies the same constraint (differs by rounding of
+                    # normalise(normalise(w)) only)
+                    veng = sharded.eval_engine() if sharded is not None else eng
+                    veng.train_step(next(val_iter), ns_seed, step, is_train=False, loss_out=v_loss[b:b + 1])
                     step += 1
             self.train_loss_history.append(float(t_loss.sum().item()) / n_batches)       # one sync per epoch
+            if eng is not None:
+                eng.check_peers_alive()          # a cross-GPU barrier that timed out is fatal (kge_peer_barrier)
             writers.scalar("train", self.train_loss_history[-1], epoch)
             if val_iter is not None:
                 self.val_loss_history.append(float(v_loss.sum().item()) / n_val_batches)
@@ -276,7 +366,9 @@ class KGEModel:
                              % (epoch, self.train_loss_history[-1], self.val_loss_history[-1]))
             else:
                 logging.info("epoch: %i, train loss: %f" % (epoch, self.train_loss_history[-1]))
-            writers.histograms(self.model_weights, epoch)
+            if sharded is None:
+                writers.histograms(self.model_weights, epoch)
+            self._progress = {"epoch": epoch, "step": step}
 
             if early_stopping_rounds is not None:
                 assert val_X is not None, "val_X should be given if want to check early stopping."
@@ -287,7 +379,11 @@ class KGEModel:
                                  % (_now(), early_stopping_rounds))
                     break
             else:
-                self._save_checkpoint()
+                self._save_checkpoint(patience=patience)
+            # rank-0-only host work (checkpoint file, histograms) must not race the in-stream peer barriers of
+            # the next step: every rank waits here
+            if world_size > 1:
+                torch.distributed.barrier()
         if log_projector:
             writers.projector(self.model_weights, self.metadata)
         writers.close()
@@ -297,41 +393,92 @@ class KGEModel:
 
     def _check_early_stopping(self, history, patience, patience_max, step, restore_best_weight):
         if step == 0 or self.best_step is None:
-            self._save_checkpoint()
             self.best_step = step
+            self._save_checkpoint(patience=patience)
             return False, patience
         if history[step] >= history[self.best_step]:
             patience += 1
         else:
             patience, self.best_step = 0, step
-            self._save_checkpoint()
+            self._save_checkpoint(patience=patience)
         if patience == patience_max:
             if restore_best_weight:
                 logging.info("[%s] Restore best weight from %i to %i step." % (_now(), step, self.best_step))
-                self._load_checkpoint()
+                self._load_checkpoint(with_optimizer=False)
             return True, patience
         return False, patience
 
+    # ---- checkpoints (reference: tf.train.CheckpointManager, BaseModel.py:247-253, 515-537) ------
     def _ckpt_path(self):
         return os.path.join(self.log_path, "ckpt.pt")
 
-    def _save_checkpoint(self):
-        """max_to_keep=1 like the reference's CheckpointManager (BaseModel.py:253); unlike the
-        reference the Adam slots and step are saved too."""
-        eng = self._engine
-        if _dp.world()[0] != 0:      # replicas are identical: rank 0 writes, everyone can read
-            return
-        torch.save({"weights": {k: v.tensor.detach().cpu() for k, v in self.model_weights.items()},
-                    "adam_m": {s: t.m.cpu() for s, t in eng.tab.items() if t.m is not None},
-                    "adam_v": {s: t.v.cpu() for s, t in eng.tab.items() if t.v is not None},
-                    "adam_t": eng.adam_t}, self._ckpt_path())
+    def _opt_path(self, rank):
+        return os.path.join(self.log_path, "ckpt.opt.rank%d.pt" % rank)
 
-    def _load_checkpoint(self):
-        if _dp.world()[1] > 1:
+    def _save_checkpoint(self, patience=0):
+        """max_to_keep=1 like the reference's CheckpointManager (BaseModel.py:253).  `ckpt.pt` (rank 0): the
+        weights — all the reference saves — plus the step counters; `ckpt.opt.rank<r>.pt` (EVERY rank): the
+        optimizer slots as that rank holds them (whole tables on one GPU; the rows a rank owns under the
+        owner-partitioned exchange; its shard under sharded tables) with the row-lazy stamps.  Under torchrun
+        every rank must call this (reading a sharded table is a collective)."""
+        rank, world = _dp.world()
+        weights = {k: v.tensor.detach().cpu() for k, v in self.model_weights.items()}       # collective when sharded
+        engines = self._train_engines()
+        prog = getattr(self, "_progress", {"epoch": -1, "step": 0})
+        if rank == 0:
+            torch.save({"weights": weights, "adam_t": engines[0].adam_t, "epoch": prog["epoch"], "step": prog["step"],
+                        "world": world, "sharded": self._sharded is not None, "n_engines": len(engines),
+                        "train_loss_history": list(getattr(self, "train_loss_history", [])),
+                        "val_loss_history": list(getattr(self, "val_loss_history", [])),
+                        "best_step": getattr(self, "best_step", None), "patience": int(patience)}, self._ckpt_path())
+        opt = []
+        for e in engines:
+            e.flush()
+            opt.append({"adam_t": e.adam_t, "lazy_t": e.lazy_t,
+                        "m": {s: t.m.cpu() for s, t in e.tab.items() if t.m is not None},
+                        "v": {s: t.v.cpu() for s, t in e.tab.items() if t.v is not None},
+                        "last": {s: t.last.cpu() for s, t in e.tab.items() if t.last is not None}})
+        torch.save({"world": world, "sharded": self._sharded is not None, "engines": opt}, self._opt_path(rank))
+
+    def _load_checkpoint(self, with_optimizer=True):
+        """Weights from `ckpt.pt`; with_optimizer: also this rank's optimizer slots, Adam step and lazy stamps
+        (only when the file was written by the same world size / sharding, else the slots restart at zero with
+        a warning).  Returns the checkpoint's bookkeeping dict."""
+        rank, world = _dp.world()
+        if world > 1:
             torch.distributed.barrier()
         state = torch.load(self._ckpt_path())
         for k, v in state["weights"].items():
             self.model_weights[k].assign(v)
+        if not with_optimizer:
+            return state
+        engines = self._train_engines()
+        path = self._opt_path(rank)
+        ok = os.path.exists(path)
+        if ok:
+            opt = torch.load(path)
+            ok = opt["world"] == world and opt["sharded"] == (self._sharded is not None) and len(opt["engines"]) == len(engines)
+        if not ok:
+            logging.warning("checkpoint has no optimizer state for this rank / layout: slots restart at zero")
+            return state
+        for e, o in zip(engines, opt["engines"]):
+            e.flush()
+            for t in e.tab.values():
+                t.ensure_slots(e.acc_init)
+            for s, m in o["m"].items():
+                e.tab[s].m.copy_(m.to(e.device))
+                e.tab[s].v.copy_(o["v"][s].to(e.device))
+            for s, l in o["last"].items():
+                e.tab[s].last.copy_(l.to(e.device))
+            e.adam_t, e.lazy_t = int(o["adam_t"]), int(o["lazy_t"])
+        return state
+
+    def load_checkpoint(self, log_path=None, with_optimizer=True):
+        """Public restore of the checkpoint in `log_path` (default: the last train() call's) into a model whose
+        tables exist (after train() or restore_model_weights())."""
+        if log_path is not None:
+            self.log_path = log_path
+        return self._load_checkpoint(with_optimizer=with_optimizer)
 
     # ---- scoring / ranking ------------------------------------------------------------
     def score_hrt(self, h, r, t):

@@ -27,4 +27,5 @@ class TransE(TranslatingModel):
     def _post_init(self):
         # TransE.py:108-109 (works with model_weights_initial too: SURVEY.md C.2 fixed)
         if self.constraint:
-            self._engine.constrain_table(_lib.T_REL_A, _lib.CON_NORMALIZE)
+            for eng in self._train_engines():        # the relation table is replicated on every rank
+                eng.constrain_table(_lib.T_REL_A, _lib.CON_NORMALIZE)

@@ -223,3 +223,81 @@ def test_train_step_host_equals_device_step():
         assert float(la.item()) == float(host_loss.item())
     for s in a.tab:
         assert torch.equal(a.tab[s].storage, b.tab[s].storage)
+
+
+# ---- sharded entity tables through the model API (ranks emulated on one device) --------------
+def _random_kg(n_ent=600, n_rel=7, n_train=4000, n_val=300, seed=3):
+    rng = np.random.default_rng(seed)
+    tri = lambda n: np.stack([rng.integers(0, n_ent, n), rng.integers(0, n_rel, n), rng.integers(0, n_ent, n)], 1)   # noqa: E731
+    md = {"ind2ent": ["e%d" % i for i in range(n_ent)], "ind2rel": ["r%d" % i for i in range(n_rel)]}
+    return tri(n_train).astype(np.int64), tri(n_val).astype(np.int64), md
+
+
+@pytest.mark.parametrize("name,ranks", [("TransE", 2), ("DistMult", 3), ("TransD", 2)])
+def test_train_with_sharded_tables_on_emulated_ranks(name, ranks, tmp_path, monkeypatch):
+    """KGEModel.train picks the sharded step (kge_shard_*) when the entity tables are sharded; losses, weights and
+    filtered metrics equal the replicated single-GPU run of the same model / seed."""
+    tr, va, md = _random_kg()
+    out = {}
+    for mode in ("single", "sharded"):
+        monkeypatch.setenv("KGE_B200_SHARD", "1" if mode == "sharded" else "0")
+        monkeypatch.setenv("KGE_B200_SHARD_EMULATE", str(ranks) if mode == "sharded" else "0")
+        m = ALL[name](embedding_params=emb(name, 24), negative_ratio=4, corrupt_side="h+t")
+        m.train(train_X=tr, val_X=va, metadata=md, epochs=2, batch_size=250, seed=11, log_path=str(tmp_path / mode))
+        assert (m._sharded is not None) == (mode == "sharded")
+        res = m.evaluate(va[:100], "t", positive_X=np.concatenate([tr, va]))
+        out[mode] = (m.train_loss_history, m.val_loss_history, {k: v.numpy() for k, v in m.model_weights.items()}, res,
+                     m.score_hrt(va[:50, 0], va[:50, 1], va[:50, 2]).cpu().numpy())
+    a, b = out["single"], out["sharded"]
+    np.testing.assert_allclose(b[0], a[0], rtol=1e-5)
+    np.testing.assert_allclose(b[1], a[1], rtol=1e-4)
+    n_steps = 2 * 16
+    for k in a[2]:
+        diff = np.abs(a[2][k] - b[2][k])
+        assert diff.max() <= n_steps * 1e-3 * 1.01 and (diff > 1e-4 * np.abs(a[2][k]).max()).mean() < 0.01, (k, diff.max())
+    np.testing.assert_allclose(b[4], a[4], rtol=2e-3, atol=2e-3)
+    assert abs(a[3]["mean_reciprocal_rank"] - b[3]["mean_reciprocal_rank"]) < 0.02
+    # the checkpoint holds every rank's optimizer shard
+    assert (tmp_path / "sharded" / "ckpt.pt").exists() and (tmp_path / "sharded" / "ckpt.opt.rank0.pt").exists()
+
+
+def test_shard_and_lazy_are_not_chosen_for_other_optimizers(monkeypatch):
+    """row-lazy / sharded tables are Adam-only in the library, so the automatic choice must not
+    pick them for SGD / Adagrad (and forcing them must fail in Python, not at the first step)."""
+    from KGE._b200 import lib as L
+    m = TransE(embedding_params={"embedding_size": 128}, negative_ratio=2, corrupt_side="h+t")
+    m.batch_size = 64
+    big = {"ent_emb": torch.empty((2_000_000, 128), device="meta"), "rel_emb": torch.empty((10, 128), device="meta")}
+    for opt, want in ((L.OPTIM_ADAM, True), (L.OPTIM_SGD, False), (L.OPTIM_ADAGRAD, False)):
+        cfg = {"constraint": 1, "optimizer": opt}
+        assert m._lazy_rows(cfg, big) is want
+        monkeypatch.setenv("KGE_B200_SHARD_EMULATE", "2")
+        assert bool(m._shard_world(cfg, big)) is want
+        monkeypatch.delenv("KGE_B200_SHARD_EMULATE")
+    monkeypatch.setenv("KGE_B200_LAZY_ROWS", "1")
+    with pytest.raises(NotImplementedError):
+        m._lazy_rows({"constraint": 1, "optimizer": L.OPTIM_SGD}, big)
+
+
+# ---- checkpoints with optimizer state + resume (SURVEY.md 8f-3) -------------------------------------------------
+@pytest.mark.parametrize("lazy", ["0", "1"])
+def test_resume_continues_bitwise(lazy, tmp_path, monkeypatch):
+    """4 epochs in one go == 2 epochs, a fresh model object, resume=True for the remaining 2: weights, Adam slots
+    and losses bit for bit (the reference's checkpoints hold the weights only, BaseModel.py:247-253)."""
+    monkeypatch.setenv("KGE_B200_LAZY_ROWS", lazy)
+    tr, va, md = _random_kg(n_ent=300, n_train=1500, n_val=100)
+    kw = dict(train_X=tr, val_X=va, metadata=md, batch_size=128, seed=5)
+    full = TransE(embedding_params={"embedding_size": 16}, negative_ratio=4, corrupt_side="h+t")
+    full.train(epochs=4, log_path=str(tmp_path / "full"), **kw)
+    part = TransE(embedding_params={"embedding_size": 16}, negative_ratio=4, corrupt_side="h+t")
+    part.train(epochs=2, log_path=str(tmp_path / "part"), **kw)
+    again = TransE(embedding_params={"embedding_size": 16}, negative_ratio=4, corrupt_side="h+t")
+    again.train(epochs=4, log_path=str(tmp_path / "part"), resume=True, **kw)
+    assert again.train_loss_history == full.train_loss_history and again.val_loss_history == full.val_loss_history
+    for k in full.model_weights:
+        assert np.array_equal(full.model_weights[k].numpy(), again.model_weights[k].numpy()), k
+    ef, ea = full._engine, again._engine
+    ef.flush(); ea.flush()
+    assert ef.adam_t == ea.adam_t
+    for s in ef.tab:
+        assert torch.equal(ef.tab[s].m, ea.tab[s].m) and torch.equal(ef.tab[s].v, ea.tab[s].v), s
