@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 9
+#define KGE_ABI_VERSION 10
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -192,6 +192,52 @@ int kge_train_step_host(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler
                         const void* host_triples, void* dev_triples, int64_t B, uint64_t seed,
                         uint64_t step, uint64_t adam_t, int is_train, float* dev_loss,
                         float* host_loss_out, void* ws, size_t ws_bytes, void* stream);
+
+/* kge_train_step (training) that also groups the NEXT batch's gradient records while this step runs.  The
+ * reference's loop (BaseModel.py:139-147) draws batch t + 1 from its iterator only after step t; here the caller
+ * that already holds it (a device-resident epoch, an iterator with one batch of look-ahead) passes it along: the
+ * record keys of a batch depend on its ids and the Philox stream (seed, next_step) only, so their counting sort —
+ * otherwise the longer of the two concurrent branches of a step — runs on a stream of its own beside this step's
+ * kernels, into the second of two grouping sets of the workspace.  The next call that names the same
+ * (triples pointer, B, seed, step, workspace) skips its own grouping; any other call groups inline as before.
+ * next_triples must stay unchanged until that call.  NULL = no look-ahead.  Results are identical either way.
+ * Dense tables (not row-lazy), counting-sort mode; otherwise next_* is ignored.
+ * _host_next: kge_train_step_host with the look-ahead batch in host memory: host_next is copied into its own
+ * staging buffer dev_next ahead of the grouping, and the call whose dev_triples is that buffer copies nothing. */
+int kge_train_step_next(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const void* triples, int64_t B,
+                        uint64_t seed, uint64_t step, uint64_t adam_t, float* loss_out, const void* next_triples,
+                        uint64_t next_step, void* ws, size_t ws_bytes, void* stream);
+int kge_train_step_host_next(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const void* host_triples,
+                             void* dev_triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
+                             float* dev_loss, float* host_loss_out, const void* host_next, void* dev_next,
+                             uint64_t next_step, void* ws, size_t ws_bytes, void* stream);
+
+/* A training step captured ONCE as a CUDA graph and replayed: the ~20 launches / event calls of kge_train_step
+ * become one graph launch, and the kernels of a step are released by the GPU's own dependency tracking instead of
+ * the host's enqueue order.  What changes from step to step — the Philox step, lr_t of the Adam step, the
+ * look-ahead step — lives in a device block written by the graph's first node, whose arguments are patched per
+ * launch (cudaGraphExecKernelNodeSetParams).  Per launch the host issues: the copy of the batch into the staging
+ * buffer (from host or device memory), one node update, one graph launch, and (host_loss_out != NULL) the copy of
+ * the loss — no host synchronisation.
+ *   kge_step_graph_create : fixes cfg, table pointers, sampler, batch size B, seed, loss word and workspace.
+ *                           dev_triples / dev_triples_next: (B, 3) device staging buffers of cfg->id_dtype the
+ *                           graph's kernels read (the second one is for the look-ahead batch, NULL = none).
+ *                           Capturing happens lazily at the first launch of each variant (shadow table valid or
+ *                           not, batch grouped ahead or not, look-ahead or not, staging parity).
+ *   kge_step_graph_launch : one training step on `triples` (host or device pointer; ignored when the previous
+ *                           launch passed this batch as next_triples with next_step == step) with Adam step
+ *                           adam_t (1-based); next_triples (nullable) = the batch of the following launch, grouped
+ *                           under this step as kge_train_step_next does.  `tables` is the caller's struct: its
+ *                           wn_valid is read and updated as kge_train_step does.
+ * Dense tables, training steps, single GPU; results are bit-identical to kge_train_step.  One graph serves one
+ * stream at a time (the step's scalars live in the context's device block). */
+typedef struct kge_step_graph kge_step_graph;
+int kge_step_graph_create(kge_ctx*, const kge_cfg*, const kge_tables*, const kge_sampler*, void* dev_triples,
+                          void* dev_triples_next, int64_t B, uint64_t seed, float* dev_loss, void* ws, size_t ws_bytes,
+                          kge_step_graph** out);
+int kge_step_graph_launch(kge_step_graph*, kge_tables*, const void* triples, uint64_t step, uint64_t adam_t,
+                          const void* next_triples, uint64_t next_step, float* host_loss_out, void* stream);
+int kge_step_graph_destroy(kge_step_graph*);
 
 /* Data-parallel form of kge_train_step (the reference is single-device): every
  * rank holds all tables and B of the step's B_global positives, [i_base, i_base + B).
@@ -384,8 +430,10 @@ int kge_flush_rows(kge_ctx*, const kge_cfg*, kge_tables*, void* stream);
  * KGE_OPT_NO_SHADOW: 1 = ignore kge_table.wn and run the full-table constraint pass every batch.
  * KGE_OPT_NO_FUSED_PUSH: 1 = sharded step: the step kernel writes every gradient record locally and
  * k_shard_push delivers all rows (default 0: single-record rows are stored into the owner's inbox by
- * the step kernel itself). */
-enum { KGE_OPT_RADIX_SORT = 1, KGE_OPT_NO_SHADOW = 2, KGE_OPT_NO_FUSED_PUSH = 3 };
+ * the step kernel itself).
+ * KGE_OPT_RING_SLOTS: deepest per-warp ring (rows: 32, 16, 8, 4, or 0 = none) of negative rows the DistMult
+ * step kernel stages through shared memory with TMA bulk copies (default 32). */
+enum { KGE_OPT_RADIX_SORT = 1, KGE_OPT_NO_SHADOW = 2, KGE_OPT_NO_FUSED_PUSH = 3, KGE_OPT_RING_SLOTS = 4 };
 int kge_set_option(kge_ctx*, int option, int value);
 
 /* Per-phase device timing (CUDA events recorded on the call's stream, read back only at

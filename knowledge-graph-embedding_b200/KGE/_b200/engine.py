@@ -19,6 +19,8 @@ def _ctx(device_index):
             raise RuntimeError("KGE (B200 build) needs a CUDA device: there is no CPU fallback")
         h = C.c_void_p()
         L.check(L.load().kge_ctx_create(device_index, C.byref(h)))
+        if os.environ.get("KGE_RING_SLOTS") is not None:      # A/B switch: depth of the step kernel's TMA row ring
+            L.check(L.load().kge_set_option(h, 4, int(os.environ["KGE_RING_SLOTS"])))
         _CTX[device_index] = h
     return _CTX[device_index]
 
@@ -67,6 +69,52 @@ class PaddedTable:
             self.v = torch.zeros_like(self.storage)
             if acc_init:
                 self.v[:, :self.cols] = acc_init      # padding stays zero
+
+
+class StepGraph:
+    """kge_step_graph of an Engine: one captured training step replayed per batch.  `launch` takes the batch from
+    host (pinned) or device memory; with `next_triples` the following batch is staged and grouped under this step,
+    and the launch that trains on it (same `next_step`) passes no data at all."""
+
+    def __init__(self, eng, B, seed, lookahead=True):
+        if eng.lazy:
+            raise RuntimeError("step graphs cover dense tables (not row-lazy)")
+        self.eng, self.B, self.seed = eng, int(B), int(seed)
+        dt = torch.int64 if eng.cfg.id_dtype == 1 else torch.int32
+        self.stage = [torch.empty((B, 3), dtype=dt, device=eng.device) for _ in range(2 if lookahead else 1)]
+        self.loss = torch.zeros(1, dtype=torch.float32, device=eng.device)
+        self.ws = torch.empty(eng._workspace(B, 0).numel(), dtype=torch.uint8, device=eng.device)   # the graph owns its workspace
+        self.T = eng._tables(with_opt=True)
+        self.h = C.c_void_p()
+        L.check(L.load().kge_step_graph_create(eng.ctx, C.byref(eng.cfg), C.byref(self.T), C.byref(eng.sampler),
+                                               _ptr(self.stage[0]), _ptr(self.stage[1]) if lookahead else C.c_void_p(0),
+                                               self.B, self.seed, _ptr(self.loss), _ptr(self.ws), self.ws.numel(),
+                                               C.byref(self.h)))
+
+    def launch(self, triples, step, next_triples=None, next_step=None, host_loss=None):
+        """triples / next_triples: contiguous (B, 3) id tensors on the host (pinned for an asynchronous copy) or
+        on the device; host_loss: pinned float tensor the loss is copied to (valid once the stream is synchronised).
+        Returns the device loss tensor."""
+        eng = self.eng
+        eng.adam_t += 1
+        T = eng._tables(with_opt=True)
+        eng._lazy_dirty = False
+        L.check(L.load().kge_step_graph_launch(self.h, C.byref(T), C.c_void_p(triples.data_ptr()) if triples is not None else C.c_void_p(0),
+                                               step, eng.adam_t,
+                                               C.c_void_p(next_triples.data_ptr()) if next_triples is not None else C.c_void_p(0),
+                                               (step + 1 if next_step is None else next_step),
+                                               C.c_void_p(host_loss.data_ptr()) if host_loss is not None else C.c_void_p(0),
+                                               _stream()))
+        eng._sync_shadow(T)
+        return self.loss
+
+    def __del__(self):
+        try:
+            if self.h:
+                L.load().kge_step_graph_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
 
 
 class Engine:
@@ -196,8 +244,28 @@ class Engine:
         return out
 
     def train_step(self, triples, seed, step, is_train=True, neg_override=None, loss_out=None,
-                   want_negatives=False):
+                   want_negatives=False, next_triples=None, next_step=None):
+        """One batch through kge_train_step.  next_triples (a device tensor of the engine's id dtype that stays
+        unchanged until the call that trains on it) / next_step: the following batch, whose gradient records are
+        grouped while this step runs (kge_train_step_next); the results do not depend on it."""
         X = self._ids(triples)
+        if next_triples is not None and is_train and neg_override is None and not want_negatives and not self.lazy:
+            B = X.shape[0]
+            ws = self._workspace(B, 0)
+            if loss_out is None:
+                loss_out = torch.empty(1, dtype=torch.float32, device=self.device)
+            Xn = self._ids(next_triples)
+            if Xn.shape[0] != B:
+                Xn = None                               # ragged last batch: grouped inline by its own call
+            self.adam_t += 1
+            T = self._tables(with_opt=True)
+            L.check(L.load().kge_train_step_next(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler), _ptr(X), B,
+                                                 seed, step, self.adam_t, _ptr(loss_out), _ptr(Xn),
+                                                 step + 1 if next_step is None else next_step, _ptr(ws), ws.numel(),
+                                                 _stream()))
+            self._sync_shadow(T)
+            self._keep_next = Xn                        # the library reads it when the next step is enqueued
+            return loss_out
         B = X.shape[0]
         ws = self._workspace(B, 0)
         if loss_out is None:
@@ -216,10 +284,34 @@ class Engine:
         self._sync_shadow(T)
         return (loss_out, neg_out) if want_negatives else loss_out
 
-    def train_step_host(self, host_triples, seed, step, host_loss, is_train=True):
+    def train_step_host(self, host_triples, seed, step, host_loss, is_train=True, next_host=None, next_step=None):
         """Batch and loss in (pinned) host memory: H2D copy, step and D2H of the loss are enqueued by
-        ONE library call (kge_train_step_host); the caller synchronises the stream to read the loss."""
+        ONE library call (kge_train_step_host); the caller synchronises the stream to read the loss.
+        next_host: the following batch (pinned host tensor, same shape): copied and grouped under this step
+        (kge_train_step_host_next); the call that trains on it copies nothing."""
         B = host_triples.shape[0]
+        if next_host is not None and is_train and not self.lazy and next_host.shape[0] == B:
+            dt = torch.int64 if self.cfg.id_dtype == 1 else torch.int32
+            if host_triples.dtype != dt or next_host.dtype != dt or not host_triples.is_contiguous() or not next_host.is_contiguous():
+                raise ValueError(f"host batches must be contiguous {dt} tensors")
+            st2 = getattr(self, "_stage2", None)
+            if st2 is None or st2[0].shape[0] != B:
+                st2 = self._stage2 = [torch.empty((B, 3), dtype=dt, device=self.device) for _ in range(2)]
+                self._stage2_cur = 0
+                self._stage_loss = torch.zeros(1, dtype=torch.float32, device=self.device)
+            cur = self._stage2_cur
+            ws = self._workspace(B, 0)
+            self.adam_t += 1
+            T = self._tables(with_opt=True)
+            L.check(L.load().kge_train_step_host_next(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler),
+                                                      C.c_void_p(host_triples.data_ptr()), _ptr(st2[cur]), B, seed, step,
+                                                      self.adam_t, _ptr(self._stage_loss), C.c_void_p(host_loss.data_ptr()),
+                                                      C.c_void_p(next_host.data_ptr()), _ptr(st2[1 - cur]),
+                                                      step + 1 if next_step is None else next_step, _ptr(ws), ws.numel(),
+                                                      _stream()))
+            self._sync_shadow(T)
+            self._stage2_cur = 1 - cur
+            return host_loss
         dt = torch.int64 if self.cfg.id_dtype == 1 else torch.int32
         if host_triples.dtype != dt or not host_triples.is_contiguous():
             raise ValueError(f"host_triples must be a contiguous {dt} tensor")
@@ -238,6 +330,10 @@ class Engine:
                                              C.c_void_p(host_loss.data_ptr()), _ptr(ws), ws.numel(), _stream()))
         self._sync_shadow(T)
         return host_loss
+
+    def step_graph(self, B, seed, lookahead=True):
+        """A training step for batches of B triples captured as a CUDA graph (kge_step_graph): see StepGraph."""
+        return StepGraph(self, B, seed, lookahead)
 
     # ---- data-parallel step (SURVEY.md 8e): grad -> one all-reduce -> apply ---------------
     def grad_buffer(self):

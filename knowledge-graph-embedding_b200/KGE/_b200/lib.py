@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 9
+KGE_ABI_VERSION = 10
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -16,6 +16,7 @@ OPTIM_ADAM, OPTIM_SGD, OPTIM_ADAGRAD = 0, 1, 2
 OPT_RADIX_SORT = 1
 OPT_NO_SHADOW = 2
 OPT_NO_FUSED_PUSH = 3
+OPT_RING_SLOTS = 4
 N_PHASES = 10
 PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm", "rank_fix", "apply", "barrier"]
 PEER_DEAD = 0xdead
@@ -84,7 +85,9 @@ SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destr
            "kge_set_option", "kge_flush_rows",
            "kge_shard_lookup", "kge_shard_pre", "kge_shard_grad", "kge_shard_apply",
            "kge_peer_barrier", "kge_train_step_dp", "kge_rank_lp_static",
-           "kge_filter_index_bytes", "kge_filter_index_build", "kge_filter_lookup"]
+           "kge_filter_index_bytes", "kge_filter_index_build", "kge_filter_lookup",
+           "kge_train_step_next", "kge_train_step_host_next",
+           "kge_step_graph_create", "kge_step_graph_launch", "kge_step_graph_destroy"]
 RANK_STATIC_BYTES = 4 << 20
 
 _LIB = None
@@ -119,6 +122,14 @@ def load():
                                  u64, u64, u64, vp, i32, vp, vp, vp, C.c_size_t, vp]
     L.kge_train_step_host.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), vp, vp, i64,
                                       u64, u64, u64, i32, vp, vp, vp, C.c_size_t, vp]
+    L.kge_train_step_next.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), vp, i64, u64, u64, u64, vp,
+                                      vp, u64, vp, C.c_size_t, vp]
+    L.kge_train_step_host_next.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), vp, vp, i64, u64, u64,
+                                           u64, vp, vp, vp, vp, u64, vp, C.c_size_t, vp]
+    L.kge_step_graph_create.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), vp, vp, i64, u64, vp, vp,
+                                        C.c_size_t, C.POINTER(vp)]
+    L.kge_step_graph_launch.argtypes = [vp, C.POINTER(Tables), vp, u64, u64, vp, u64, vp, vp]
+    L.kge_step_graph_destroy.argtypes = [vp]
     L.kge_train_grad.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Dp), vp, i64,
                                  u64, u64, vp, C.POINTER(Grads), vp, vp, vp, C.c_size_t, vp]
     L.kge_train_apply.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Grads), vp, i64, u64, vp, vp,

@@ -41,6 +41,11 @@ extern "C" int kge_ctx_create(int device, kge_ctx** out) {
   KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_mid, cudaEventDisableTiming));
   KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_heavy, cudaEventDisableTiming));
+  KGE_CUDA_OK(cudaStreamCreateWithPriority(&c->pre_stream, cudaStreamNonBlocking, prio_greatest));
+  KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_pre_fork, cudaEventDisableTiming));
+  KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_pre_done, cudaEventDisableTiming));
+  KGE_CUDA_OK(cudaMalloc(&c->dyn, 64));
+  KGE_CUDA_OK(cudaMemset(c->dyn, 0, 64));
   KGE_CUDA_OK(cudaMalloc(&c->ticket, 64 * sizeof(unsigned)));
   KGE_CUDA_OK(cudaMemset(c->ticket, 0, 64 * sizeof(unsigned)));
   *out = reinterpret_cast<kge_ctx*>(c);
@@ -62,6 +67,10 @@ extern "C" int kge_ctx_destroy(kge_ctx* ctx) {
     if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->ev_mid) cudaEventDestroy(c->ev_mid);
     if (c->ev_heavy) cudaEventDestroy(c->ev_heavy);
+    if (c->pre_stream) { cudaStreamSynchronize(c->pre_stream); cudaStreamDestroy(c->pre_stream); }
+    if (c->ev_pre_fork) cudaEventDestroy(c->ev_pre_fork);
+    if (c->ev_pre_done) cudaEventDestroy(c->ev_pre_done);
+    if (c->dyn) cudaFree(c->dyn);
     if (c->ticket) cudaFree(c->ticket);
   }
   delete c;
@@ -74,6 +83,7 @@ extern "C" int kge_set_option(kge_ctx* ctx, int option, int value) {
     case KGE_OPT_RADIX_SORT: c->opt_radix_sort = value; return KGE_OK;
     case KGE_OPT_NO_SHADOW: c->opt_no_shadow = value; return KGE_OK;
     case KGE_OPT_NO_FUSED_PUSH: c->opt_no_fused_push = value; return KGE_OK;
+    case KGE_OPT_RING_SLOTS: c->opt_ring_max = value; return KGE_OK;
     default: set_error("unknown option %d", option); return KGE_EINVAL;
   }
 }

@@ -27,6 +27,22 @@ void set_error(const char* fmt, ...);
     if (!(cond)) { kge::set_error(__VA_ARGS__); return (code); }                   \
   } while (0)
 
+// Per-step scalars of a captured step graph (kge_step_graph): written by the graph's first node
+// (k_set_dyn, arguments patched per launch) and read by the kernels in place of their by-value copies.
+struct DynScal {
+  unsigned long long step;      // Philox step counter
+  unsigned long long step_next; // ... of the batch grouped ahead (kge_train_step_next)
+  float lr_t;                   // Adam: lr * sqrt(1 - b2^t) / (1 - b1^t); SGD / Adagrad: lr
+  uint32_t epoch;               // cross-GPU barrier epoch of the data-parallel step
+};
+// a batch whose gradient records were grouped ahead of its step (kge_train_step_next)
+struct Prefetched {
+  bool valid = false;
+  const void* triples = nullptr; void* ws = nullptr;
+  int64_t B = 0, i_base = 0, n_ent = 0;
+  uint64_t seed = 0, step = 0;
+  int k = 0, side = 0, sampler = 0, set = 0, graph = 0;
+};
 struct kge_ctx_impl {
   int device;
   int sm_count;
@@ -43,14 +59,20 @@ struct kge_ctx_impl {
   int opt_radix_sort = 0;         // kge_set_option(KGE_OPT_RADIX_SORT)
   int opt_no_shadow = 0;          // kge_set_option(KGE_OPT_NO_SHADOW)
   int opt_no_fused_push = 0;      // kge_set_option(KGE_OPT_NO_FUSED_PUSH)
+  int opt_ring_max = 32;          // kge_set_option(KGE_OPT_RING_SLOTS): deepest TMA row ring of the step kernel (0 = none)
   unsigned* ticket = nullptr;     // device, 64 words, zero between calls (self-resetting counters)
+  cudaStream_t pre_stream = nullptr;               // the next batch's grouping chain (kge_train_step_next)
+  cudaEvent_t ev_pre_fork = nullptr, ev_pre_done = nullptr;
+  Prefetched pre;
+  DynScal* dyn = nullptr;         // device; used only while `capturing` (kge_step_graph_create)
+  int capturing = 0;              // the call is being captured into a CUDA graph: per-step scalars come from `dyn`
 };
 // RAII marker: records the boundary events of one call when profiling is on
 struct PhaseTimer {
   kge_ctx_impl* c; cudaStream_t st; int slot;
   // join: continue the slot the preceding gradient half opened (one data-parallel step = one call)
   PhaseTimer(kge_ctx_impl* c_, cudaStream_t s, bool join = false) : c(c_), st(s), slot(-1) {
-    if (!c->ev) return;
+    if (!c->ev || c->capturing) return;
     if (join && c->prof_open >= 0) { slot = c->prof_open; c->prof_open = -1; return; }
     c->prof_open = -1;
     if (c->prof_n < c->prof_cap) { slot = c->prof_n++; c->ev_mask[slot] = 0; }
@@ -187,6 +209,7 @@ struct SamplerDev {
   int side_mode;            // kge_side
   int k_eff, k_side;
   uint64_t seed, step;
+  const unsigned long long* step_dyn;   // nullable: the step counter lives on the device (captured step graph)
   int64_t n_ent;
   int64_t i_base;           // global index of this call's first positive (data-parallel ranks)
   kge_sampler s;
@@ -199,7 +222,8 @@ __device__ __forceinline__ int64_t sample_negative(const SamplerDev& sd, int64_t
   bool head = neg_is_head(sd, c);
   int jj = (sd.side_mode == KGE_SIDE_HT) ? (c >> 1) : c;
   uint64_t n = (uint64_t) (i + sd.i_base) * (uint64_t) sd.k_side + (uint64_t) jj;
-  const uint32_t u = philox_word0(sd.seed, sd.step, head ? 0u : 1u, n);
+  const uint64_t step = sd.step_dyn ? (uint64_t) __ldg(sd.step_dyn) : sd.step;
+  const uint32_t u = philox_word0(sd.seed, step, head ? 0u : 1u, n);
   if (sd.kind == KGE_NS_UNIFORM) {      // 32-bit modulo: n_ent < 2^32 is checked on the host
     if (sd.s.pool == nullptr) return (int64_t) ((uint32_t) u % (uint32_t) sd.n_ent);
     return sd.s.pool[(uint32_t) u % (uint32_t) sd.s.pool_len];

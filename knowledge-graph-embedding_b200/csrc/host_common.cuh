@@ -123,6 +123,7 @@ inline void fill_sampler_dev(const kge_cfg* c, const kge_sampler* s, uint64_t se
   sd.k_side = c->corrupt_side == KGE_SIDE_HT ? c->negative_ratio / 2 : c->negative_ratio;
   sd.seed = seed;
   sd.step = step;
+  sd.step_dyn = nullptr;
   sd.n_ent = c->n_ent;
   sd.i_base = 0;
   if (s) sd.s = *s; else { sd.s = kge_sampler{}; }

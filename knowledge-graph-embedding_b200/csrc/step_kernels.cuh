@@ -14,11 +14,19 @@
 #include "models.cuh"
 #include "loss.cuh"
 #include "reduce_tail.cuh"
+#include "tc_ptx.cuh"
 
 namespace kge {
 
 constexpr int STEP_THREADS = 256;
 constexpr int STEP_WARPS = STEP_THREADS / WARP;
+constexpr int STEP_MAX_WARPS = 14;           // DistMult (NV <= 2): the CTA size is picked per launch (StepParams.nwarps)
+// launch bounds of k_step<M, NV>: threads per CTA the kernel may be launched with, CTAs per SM it is built for
+template <class M, int NV> struct StepBounds {
+  static constexpr bool WIDE = (M::KIND == KGE_DISTMULT && NV <= 2);
+  static constexpr int THREADS = WIDE ? STEP_MAX_WARPS * WARP : STEP_THREADS;
+  static constexpr int MIN_CTAS = WIDE ? 1 : (M::KIND == KGE_TRANSD ? (NV == 1 ? 2 : 1) : (NV == 1 ? 3 : (NV == 2 ? 2 : 1)));
+};
 constexpr int N_PART = 1 + KGE_MAX_TABLES;   // loss + norm^2 per table
 
 struct StepParams {
@@ -30,6 +38,7 @@ struct StepParams {
   int64_t B;
   int k_eff;
   int wpp;                       // warps per positive: 1, 2, 4 or 8
+  int nwarps;                    // warps per CTA (= STEP_WARPS except where StepBounds::WIDE lets the host pick)
   const int64_t* neg_override;   // nullable
   int64_t* neg_ids;              // [B*k_eff] negatives used (always written)
   float* rec[KGE_MAX_TABLES];    // gradient records per table slot
@@ -47,7 +56,24 @@ struct StepParams {
   // section of owner's value inbox of entity slot s (row stride = the record stride).
   const uint32_t* rec_dest;      // nullable
   float* inbox[2][KGE_MAX_PEERS];
+  // Factored records (DistMult fast loop, dense single-GPU / data-parallel step): the gradient of a
+  // negative's entity row is dneg * q with q = r o t or h o r fixed per (positive, corrupted side), so the
+  // step kernel publishes q once (fac_q[(i * n_side + side) * rld]) and ONE float per negative
+  // (fac_coef[i * k + c] = dneg) instead of a full record row; the update kernels rebuild
+  // fl(dneg * q) element by element (update_kernels.cuh, RecSrc) — the bits the stored row would have had.
+  float* fac_coef;               // nullable = records are materialised
+  float* fac_q;
+  // Negative rows staged through shared memory by TMA bulk copies (DistMult loop): every warp owns a ring of
+  // ring_slots rows (multiple of 4; 0 = rows are loaded straight into registers) behind the step kernel's
+  // other shared memory, at byte offset ring_off; one mbarrier per group of four rows.
+  int ring_slots;
+  uint32_t ring_off;
 };
+// one row global -> shared by the TMA unit (cp.async.bulk), completion counted on `bar`
+__device__ __forceinline__ void bulk_row_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   tc::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(tc::smem_u32(bar)) : "memory");
+}
 constexpr uint32_t REC_LOCAL = 0xffffffffu;
 // where entity record `rec` goes: the local record buffers (row = rec) or this rank's section of the
 // owner's value inbox
@@ -84,13 +110,14 @@ __device__ __forceinline__ void group_barrier(int grp, int wpp) {
 }
 
 template <class M, int NV, bool TRAIN>
-__global__ void __launch_bounds__(STEP_THREADS, (M::KIND == KGE_TRANSD ? (NV == 1 ? 2 : 1) : (NV == 1 ? 3 : (NV == 2 ? 2 : 1)))) k_step(const StepParams p) {
+__global__ void __launch_bounds__(StepBounds<M, NV>::THREADS, StepBounds<M, NV>::MIN_CTAS) k_step(const StepParams p) {
   using Ent = typename M::template Ent<NV>;
   using Rel = typename M::template Rel<NV>;
   extern __shared__ float4 smem4[];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int wpp = p.wpp, ppc = STEP_WARPS / wpp;
+  const int nw = StepBounds<M, NV>::WIDE ? (int) (blockDim.x >> 5) : STEP_WARPS;
+  const int wpp = p.wpp, ppc = nw / wpp;
   const int grp = warp / wpp, wig = warp % wpp;
   const int64_t i = (int64_t) blockIdx.x * ppc + grp;
   if (i >= p.B) return;                       // whole group leaves together
@@ -101,11 +128,55 @@ __global__ void __launch_bounds__(STEP_THREADS, (M::KIND == KGE_TRANSD ? (NV == 
   constexpr int ACC_F4 = (2 * Ent::NROWS + Rel::NROWS) * NV;   // float4 per lane
   float* s_neg = reinterpret_cast<float*>(smem4) + (size_t) grp * k;
   float* s_red = reinterpret_cast<float*>(smem4) + (((size_t) ppc * k + 3) & ~(size_t) 3) + warp * 8;
-  float4* s_acc = smem4 + (((size_t) ppc * k + 3) / 4) + (STEP_WARPS * 8) / 4 + (size_t) warp * ACC_F4 * WARP;
+  float4* s_acc = smem4 + (((size_t) ppc * k + 3) / 4) + (nw * 8) / 4 + (size_t) warp * ACC_F4 * WARP;
 
   const int64_t h = load_id(p.triples, 3 * i + 0, p.id64);
   const int64_t r = load_id(p.triples, 3 * i + 1, p.id64);
   const int64_t t = load_id(p.triples, 3 * i + 2, p.id64);
+
+  // Negative ids: lane l draws the id of this warp's (it0 + l)-th negative, so the ~100
+  // instruction Philox runs once per 32 negatives per lane instead of once per negative per
+  // warp; the next negative's rows are requested before the current one is processed.
+  const int n_it = (k - wig + wpp - 1) / wpp;
+  int64_t my_e = 0;
+  auto draw = [&](int it0) {
+    const int c = wig + (it0 + lane) * wpp;
+    if (c < k) my_e = p.neg_override ? p.neg_override[i * k + c] : sample_negative(p.sd, i, c, h, t);
+  };
+  // DistMult: the negatives' rows travel global -> shared by TMA bulk copies into this warp's ring, requested
+  // before anything else so that they are in flight while the positive is loaded and scored.  Rows
+  // j0 .. j0+3 (j0 % 4 == 0) share one mbarrier; the lane that holds a row's id issues its copy.
+  const int RS = (M::KIND == KGE_DISTMULT && md.shard_rows == 0) ? p.ring_slots : 0;
+  const int RSM = RS > 0 ? RS : 4, RSG = RSM >> 2;       // modulo operands (never zero)
+  const uint32_t row_bytes = (uint32_t) md.rld[KGE_T_ENT] * 4u;
+  uint64_t* ring_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(smem4) + p.ring_off) + (size_t) warp * (RS >> 2);
+  float* ring = reinterpret_cast<float*>(reinterpret_cast<char*>(smem4) + p.ring_off + (((size_t) nw * (RS >> 2) * 8 + 15) & ~(size_t) 15)) +
+                (size_t) warp * RS * md.rld[KGE_T_ENT];
+  auto ring_issue = [&](int j0) {
+    const int l0 = j0 & 31, nrows = (n_it - j0 < 4) ? n_it - j0 : 4;
+    uint64_t* bar = ring_bar + ((j0 >> 2) % RSG);
+    if (lane == l0) tc::mbar_expect_tx(bar, (uint32_t) nrows * row_bytes);
+    const int x = lane - l0;
+    if (x >= 0 && x < nrows) {
+      bulk_row_g2s(ring + (size_t) ((j0 + x) % RSM) * md.rld[KGE_T_ENT], md.t[KGE_T_ENT].w + my_e * (int64_t) md.t[KGE_T_ENT].ld,
+                   row_bytes, bar);
+      if (p.write_keys) {
+        const int64_t slot = i * k + wig + (int64_t) (j0 + x) * wpp;
+        p.neg_ids[slot] = my_e;
+        if (TRAIN) { p.keys[2 * p.B + slot] = (uint32_t) my_e; p.vals[2 * p.B + slot] = (uint32_t)(2 * p.B + slot); }
+      }
+    }
+  };
+  if constexpr (M::KIND == KGE_DISTMULT) {
+    if (n_it > 0) draw(0);
+    if (RS > 0) {
+      if (lane < (RS >> 2)) tc::mbar_init(ring_bar + lane, 1);
+      tc::mbar_fence_init();
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      for (int j0 = 0; j0 < RS && j0 < n_it; j0 += 4) ring_issue(j0);
+    }
+  }
   Ent H, T;
   Rel R;
   H.load(md, h, lane);
@@ -182,22 +253,13 @@ __global__ void __launch_bounds__(STEP_THREADS, (M::KIND == KGE_TRANSD ? (NV == 
   float lsum = 0.f, gpos = 0.f;
   const int64_t nE = 2 * p.B + p.B * (int64_t) k;
 
-  // Negative ids: lane l draws the id of this warp's (it0 + l)-th negative, so the ~100
-  // instruction Philox runs once per 32 negatives per lane instead of once per negative per
-  // warp; the next negative's rows are requested before the current one is processed.
-  const int n_it = (k - wig + wpp - 1) / wpp;
-  int64_t my_e = 0;
-  auto draw = [&](int it0) {
-    const int c = wig + (it0 + lane) * wpp;
-    if (c < k) my_e = p.neg_override ? p.neg_override[i * k + c] : sample_negative(p.sd, i, c, h, t);
-  };
   constexpr bool PREFETCH = (NV <= 2);       // wider rows: the second row in flight would spill
   // TransE / UM fast loop (below) loads its negatives in groups of GROUP rows instead
   constexpr int GROUP = 4;
   Ent Nnext;
   if (n_it > 0) {
-    draw(0);
-    if (PREFETCH) Nnext.load(md, (int64_t) __shfl_sync(FULL, (uint32_t) my_e, 0), lane);      // in flight while the positive is scored
+    if constexpr (M::KIND != KGE_DISTMULT) draw(0);
+    if (PREFETCH && RS == 0) Nnext.load(md, (int64_t) __shfl_sync(FULL, (uint32_t) my_e, 0), lane);      // in flight while the positive is scored
   }
   // DistMult fast path.  s = sum(e_h * r * e_t) is linear in the corrupted entity, so with
   // q = r*t (head corrupted) or h*r (tail corrupted) fixed per positive:  s_neg = N . q,
@@ -372,44 +434,109 @@ __global__ void __launch_bounds__(STEP_THREADS, (M::KIND == KGE_TRANSD ? (NV == 
         o2.v[v] = o * o;
       }
       const float q2 = row_dot_partial(q, q);
-      for (int it = 0; it < n_it; ++it) {
-        const int c = wig + it * wpp;
-        const int64_t slot = i * k + c;
-        const int64_t e = (int64_t) __shfl_sync(FULL, (uint32_t) my_e, it & 31);
-        Ent N;
-        if (PREFETCH) N = Nnext; else N.load(md, e, lane);
-        if (it + 1 < n_it) {
-          if (((it + 1) & 31) == 0) draw(it + 1);
-          if (PREFETCH) Nnext.load(md, (int64_t) __shfl_sync(FULL, (uint32_t) my_e, (it + 1) & 31), lane);
+      const bool ht = p.sd.side_mode == KGE_SIDE_HT;
+      if (TRAIN && p.fac_coef != nullptr && wig < (ht ? 2 : 1))      // one writer per (positive, side)
+        store_row(q, p.fac_q, ht ? 2 * i + wig : i, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+      // Four negatives per pass: their rows are requested together, the four partial dot products are
+      // reduced "transposed" (xor 16 / 8 hand half of the values to the partner lane, xor 4 / 2 / 1
+      // finish one value per lane: 6 shuffles for 4 sums, the same addition tree as warp_sum, so the
+      // scores keep their bits) and lanes 8x .. 8x+7 then hold the score of negative x: the loss term
+      // and its derivative are evaluated ONCE per pass for four negatives in different lane groups,
+      // not once per negative by every lane.  lsum / gpos are kept per lane group and combined after
+      // the loop.
+      const int lx = lane >> 3;
+      constexpr int G4 = 4;
+      for (int it0 = 0; it0 < n_it; it0 += G4) {
+        Ent Nb[G4];
+        float d[G4];
+        if (RS > 0) {
+          tc::mbar_wait(ring_bar + ((it0 >> 2) % RSG), (uint32_t) ((it0 / RSM) & 1));
+#pragma unroll
+          for (int x = 0; x < G4; ++x) {
+            const float4* src = reinterpret_cast<const float4*>(ring + (size_t) ((it0 + x) % RSM) * md.rld[KGE_T_ENT]);
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+              const int c = lane + v * WARP;
+              Nb[x].e.v[v] = (it0 + x < n_it && 4 * c < md.t[KGE_T_ENT].cols) ? src[c] : f4zero();
+            }
+          }
+        } else {
+          if (it0 > 0 && (it0 & 31) == 0) draw(it0);          // G4 divides 32: a pass never straddles a draw
+#pragma unroll
+          for (int x = 0; x < G4; ++x) {
+            if (it0 + x < n_it) {
+              const int64_t e = (int64_t) __shfl_sync(FULL, (uint32_t) my_e, (it0 + x) & 31);
+              if (it0 + x == 0 && PREFETCH) Nb[x] = Nnext; else Nb[x].load(md, e, lane);
+              if (lane == 0 && p.write_keys) {
+                const int64_t slot = i * k + wig + (int64_t) (it0 + x) * wpp;
+                p.neg_ids[slot] = e;
+                if (TRAIN) { p.keys[2 * p.B + slot] = (uint32_t) e; p.vals[2 * p.B + slot] = (uint32_t)(2 * p.B + slot); }
+              }
+            } else Nb[x].zero();
+          }
         }
-        if (lane == 0 && p.write_keys) {
-          p.neg_ids[slot] = e;
-          if (TRAIN) { p.keys[2 * p.B + slot] = (uint32_t) e; p.vals[2 * p.B + slot] = (uint32_t)(2 * p.B + slot); }
-        }
-        const float sn = warp_sum(row_dot_partial(N.e, q));
+#pragma unroll
+        for (int x = 0; x < G4; ++x) d[x] = row_dot_partial(Nb[x].e, q);
+        const bool b16 = (lane & 16) != 0, b8 = (lane & 8) != 0;
+        float k0 = b16 ? d[2] : d[0], k1 = b16 ? d[3] : d[1];
+        const float g0 = b16 ? d[0] : d[2], g1 = b16 ? d[1] : d[3];
+        k0 += __shfl_xor_sync(FULL, g0, 16);
+        k1 += __shfl_xor_sync(FULL, g1, 16);
+        float sn = b8 ? k1 : k0;
+        sn += __shfl_xor_sync(FULL, b8 ? k0 : k1, 8);
+        sn += __shfl_xor_sync(FULL, sn, 4);
+        sn += __shfl_xor_sync(FULL, sn, 2);
+        sn += __shfl_xor_sync(FULL, sn, 1);
         const float w = softmax ? expf(p.loss.temperature * sn - sm_max) * sm_inv : 1.f;
         float term, dneg, dpp;
         loss_neg(p.loss, sp, sn, w, term, dneg, dpp);
+        if (it0 + lx >= n_it) { term = 0.f; dneg = 0.f; dpp = 0.f; }
         lsum += term;
         gpos += dpp;
         if (TRAIN) {
-          Row<NV> gN;
-          float pe = 0.f, pr = 0.f;
 #pragma unroll
-          for (int v = 0; v < NV; ++v) {
-            gN.v[v] = dneg * q.v[v];
-            A.v[v] += dneg * N.e.v[v];
-            const float4 n2 = N.e.v[v] * N.e.v[v];
-            pe += dot4(n2, r2.v[v]);
-            pr += dot4(n2, o2.v[v]);
+          for (int x = 0; x < G4; ++x) {
+            if (it0 + x >= n_it) break;
+            const float dn = __shfl_sync(FULL, dneg, 8 * x);
+            float pe = 0.f, pr = 0.f;
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+              A.v[v] += dn * Nb[x].e.v[v];
+              const float4 n2 = Nb[x].e.v[v] * Nb[x].e.v[v];
+              pe += dot4(n2, r2.v[v]);
+              pr += dot4(n2, o2.v[v]);
+            }
+            const float d2 = dn * dn;
+            nrm[KGE_T_ENT] += d2 * (q2 + pe);
+            nrm[KGE_T_REL_A] += d2 * pr;
+            if (p.fac_coef == nullptr) {
+              Row<NV> gN;
+#pragma unroll
+              for (int v = 0; v < NV; ++v) gN.v[v] = dn * q.v[v];
+              const RecTarget rt = rec_target(p, 2 * p.B + i * k + wig + (int64_t) (it0 + x) * wpp);
+              store_row(gN, rt.b0, rt.row, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+            }
           }
-          const float d2 = dneg * dneg;
-          nrm[KGE_T_ENT] += d2 * (q2 + pe);
-          nrm[KGE_T_REL_A] += d2 * pr;
-          { const RecTarget rt = rec_target(p, 2 * p.B + slot);
-            store_row(gN, rt.b0, rt.row, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane); }
+          if (p.fac_coef != nullptr && (lane & 7) == 0 && it0 + lx < n_it)
+            p.fac_coef[i * k + wig + (int64_t) (it0 + lx) * wpp] = dneg;
+        }
+        if (RS > 0 && it0 + RS < n_it) {                   // the pass's four slots are free: request rows it0 + RS ..
+          __syncwarp();
+          if (((it0 + RS) & 31) == 0) draw(it0 + RS);      // every row of the previous 32 has been requested
+          ring_issue(it0 + RS);
         }
       }
+      // lane groups -> warp-uniform sums (fixed order)
+      {
+        float ls = 0.f, gs = 0.f;
+#pragma unroll
+        for (int x = 0; x < G4; ++x) { ls += __shfl_sync(FULL, lsum, 8 * x); gs += __shfl_sync(FULL, gpos, 8 * x); }
+        lsum = ls; gpos = gs;
+      }
+      // the positive's rows were dead during the loop (registers): fetched again (L1 / L2 hits)
+      H.load(md, h, lane);
+      T.load(md, t, lane);
+      R.load(md, r, lane);
       if (TRAIN) {
 #pragma unroll
         for (int v = 0; v < NV; ++v) {

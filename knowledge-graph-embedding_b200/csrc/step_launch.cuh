@@ -14,10 +14,10 @@ struct StepLaunch {
 };
 
 // shared memory k_step needs for (nv, wpp, k) and a model with n_ent/n_rel row bundles
-inline size_t step_smem_bytes(int nv, int wpp, int k, int ent_rows, int rel_rows) {
-  const int ppc = STEP_WARPS / wpp;
-  size_t f4 = ((size_t) ppc * k + 3) / 4 + (STEP_WARPS * 8) / 4;
-  if (wpp > 1) f4 += (size_t) STEP_WARPS * (2 * ent_rows + rel_rows) * nv * WARP;
+inline size_t step_smem_bytes(int nv, int wpp, int k, int ent_rows, int rel_rows, int nwarps = STEP_WARPS) {
+  const int ppc = nwarps / wpp;
+  size_t f4 = ((size_t) ppc * k + 3) / 4 + (nwarps * 8) / 4;
+  if (wpp > 1) f4 += (size_t) nwarps * (2 * ent_rows + rel_rows) * nv * WARP;
   return f4 * sizeof(float4);
 }
 
@@ -26,7 +26,8 @@ int launch_step_one(const StepParams& p, const StepLaunch& L) {
   auto kern = k_step<M, NV, TRAIN>;
   if (L.smem > 48 * 1024)
     KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) L.smem));
-  kern<<<(unsigned) L.grid, STEP_THREADS, L.smem, L.stream>>>(p);
+  const int threads = StepBounds<M, NV>::WIDE ? p.nwarps * WARP : STEP_THREADS;
+  kern<<<(unsigned) L.grid, threads, L.smem, L.stream>>>(p);
   KGE_CUDA_OK(cudaGetLastError());
   return KGE_OK;
 }

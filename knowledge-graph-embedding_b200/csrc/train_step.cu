@@ -17,8 +17,10 @@ namespace kge {
 struct StepWs {
   size_t off_part, off_scal, off_neg, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub,
       off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart, off_seg, off_hdr, off_heavy, off_uniq,
-      off_islot, off_recdest;
+      off_islot, off_recdest, off_facq, off_fcoef;
   size_t cub_bytes, total, n_seg;
+  size_t gdelta;          // the grouping buffers (negatives, keys, record ids, scan, headers, heavy list) exist twice:
+                          // set s lives at offset + s * gdelta (the next batch is grouped while this one is applied)
   int64_t n_ent_rec, n_keys, total_rows, n_mat_cta;
   int rld[KGE_MAX_TABLES];
   int ldp;
@@ -68,11 +70,18 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   auto take = [&](size_t bytes) { size_t at = o; o += align_up(bytes); return at; };
   L.off_part = take(sizeof(float) * N_PART * (size_t) B);
   L.off_scal = take(sizeof(float) * 16);
+  L.n_seg = (size_t) c->n_ent + (size_t) c->n_rel;
+  const size_t g0 = o;
   L.off_neg = take(sizeof(int64_t) * (size_t) B * (k > 0 ? k : 1));
   L.off_keys_in = take(sizeof(uint32_t) * (size_t) L.n_keys);
-  L.off_keys_out = take(sizeof(uint32_t) * (size_t) L.n_keys);
   L.off_vals_in = take(sizeof(uint32_t) * (size_t) L.n_keys);
   L.off_vals_out = take(sizeof(uint32_t) * (size_t) L.n_keys);
+  L.off_seg = take(sizeof(uint32_t) * (2 * L.n_seg + 2));   // cnt[K] | off[K+1] | n_heavy   (radix path: seg_lo | seg_hi)
+  L.off_hdr = take(sizeof(uint32_t) * 8 * L.n_seg);         // k_canon's per-key headers
+  L.off_heavy = take(sizeof(uint32_t) * (size_t) (L.n_keys / UPD_HEAVY + 1));
+  L.gdelta = o - g0;
+  o += L.gdelta;                                            // the second set
+  L.off_keys_out = take(sizeof(uint32_t) * (size_t) L.n_keys);
   // temp size of the radix-sort mode: queried once per (n_keys, bits), this runs on every call
   static thread_local int64_t memo_n = -1;
   static thread_local int memo_bits = -1;
@@ -88,10 +97,6 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   }
   L.cub_bytes = memo_bytes;
   L.off_cub = take(L.cub_bytes);
-  L.n_seg = (size_t) c->n_ent + (size_t) c->n_rel;
-  L.off_seg = take(sizeof(uint32_t) * (2 * L.n_seg + 2));   // cnt[K] | off[K+1] | n_heavy   (radix path: seg_lo | seg_hi)
-  L.off_hdr = take(sizeof(uint32_t) * 8 * L.n_seg);         // k_canon's per-key headers
-  L.off_heavy = take(sizeof(uint32_t) * (size_t) (L.n_keys / UPD_HEAVY + 1));
   L.off_uniq = take(sizeof(uint32_t) * (4 + 3 * (size_t) L.n_keys));   // row-lazy work list (k_heads)
   L.off_islot = take(sizeof(uint32_t) * ((size_t) L.n_keys + 16));      // sharded step: inbox slot per work item | per-owner counters
   L.off_recdest = take(sizeof(uint32_t) * (size_t) L.n_ent_rec);        // sharded step: inbox destination of single-record rows
@@ -111,6 +116,11 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
     const bool vec = cols[s] && !is_matrix_slot(c, s);
     L.off_rec[s] = vec ? take(sizeof(float) * (size_t) nrec * L.rld[s]) : 0;
     if (vec) L.total_rows += (s < 2) ? c->n_ent : c->n_rel;
+  }
+  L.off_facq = L.off_fcoef = 0;
+  if (c->model == KGE_DISTMULT) {                            // factored records (StepParams.fac_coef)
+    L.off_facq = take(sizeof(float) * 2 * (size_t) B * L.rld[KGE_T_ENT]);
+    L.off_fcoef = take(sizeof(float) * (size_t) B * (k > 0 ? k : 1));
   }
   L.ldp = 0; L.off_recP = 0; L.n_mat_cta = 0;
   if (is_matrix_model(c->model)) {
@@ -343,7 +353,8 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
                       const kge_dp* dp, const void* triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
                       const int64_t* neg_override, int is_train, kge_grads* grads_out, float* scal_out,
                       float* loss_out, int64_t* neg_out, void* ws, size_t ws_bytes, void* stream,
-                      const kge_shard* sh = nullptr, int shard_phase = 0 /* 1 lookup, 2 grad */) {
+                      const kge_shard* sh = nullptr, int shard_phase = 0 /* 1 lookup, 2 grad */,
+                      const void* next_triples = nullptr, uint64_t next_step = 0, const void* next_host = nullptr) {
   auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
   cudaStream_t st = (cudaStream_t) stream;
   const bool grad_only = dp != nullptr;
@@ -418,6 +429,19 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   int cols[KGE_MAX_TABLES];
   expected_cols(cfg, cols);
 
+  // Grouping of the NEXT batch under this step (kge_train_step_next): the record keys depend on ids and the
+  // Philox stream only, so the previous call may already have grouped THIS batch into one of the two sets.
+  const bool can_pre = is_train && !lazy && !sh && !ctx->opt_radix_sort && (int64_t) L.n_seg <= SCAN_SMALL_MAX && !neg_override;
+  Prefetched& pre = ctx->pre;
+  const bool pre_hit = can_pre && pre.valid && pre.triples == triples && pre.B == B && pre.seed == seed && pre.step == step &&
+                       pre.ws == ws && pre.i_base == (dp ? dp->i_base : 0) && pre.k == k && pre.n_ent == cfg->n_ent &&
+                       pre.side == cfg->corrupt_side && pre.sampler == cfg->sampler && pre.graph == ctx->capturing;
+  const int gs = pre_hit ? pre.set : (pre.valid ? 1 - pre.set : 0);
+  if (!pre_hit && pre.valid && is_train && !pre.graph && !ctx->capturing)   // a grouped batch nobody asked for: its chain
+    KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_pre_done, 0));               // must finish before its set is reused
+  if (is_train) pre.valid = false;
+  char* gb = wsb + (size_t) gs * L.gdelta;               // base of this step's grouping set
+
   // 1. start-of-batch constraint (train AND validation batches, BaseModel.py:319): enqueued by
   //    fork_side() below, once every argument check has passed
   PhaseTimer pt(ctx, st);
@@ -468,16 +492,33 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   p.loss.inv_n = 1.0f / (float) B_global;                 // loss normalisations use the whole step's batch
   p.loss.inv_nk = 1.0f / ((float) B_global * (float) k);
   fill_sampler_dev(cfg, smp, seed, step, p.sd);
+  // captured step graph: Philox step and lr_t are read from the device block the graph's first node writes
+  const DynScal* dyn = ctx->capturing ? ctx->dyn : nullptr;
+  KGE_REQUIRE(!dyn || (!lazy && !flush_first && !sh && is_train), KGE_EUNSUPPORTED,
+              "step graphs cover dense-table training steps (not row-lazy / sharded tables, not validation)");
+  if (dyn) p.sd.step_dyn = &dyn->step;
   if (grad_only) p.sd.i_base = dp->i_base;
   p.triples = triples;
   p.id64 = cfg->id_dtype;
   p.B = B;
   p.k_eff = k;
   p.wpp = mat ? STEP_WARPS : pick_wpp(cfg, k, B, ctx->sm_count);
+  // DistMult (rows <= 256 floats): CTA size chosen so that ONE balanced wave covers the batch when it can
+  // (C2: 1024 positives x 2 warps over 148 SMs -> 14 warps per CTA, 147 CTAs), else the usual 8 warps
+  p.nwarps = STEP_WARPS;
+  if (!mat && cfg->model == KGE_DISTMULT && nv <= 2) {
+    const int64_t per_sm = (B * p.wpp + ctx->sm_count - 1) / ctx->sm_count;
+    if (per_sm <= STEP_MAX_WARPS) p.nwarps = (int) ((per_sm + p.wpp - 1) / p.wpp) * p.wpp;
+  }
+  // factored records: dense (not row-lazy / sharded) training step whose warps each corrupt one side
+  const bool fac = !mat && cfg->model == KGE_DISTMULT && is_train && !lazy && !sh &&
+                   (cfg->corrupt_side != KGE_SIDE_HT || (p.wpp & 1) == 0);
+  p.fac_coef = fac ? reinterpret_cast<float*>(wsb + L.off_fcoef) : nullptr;
+  p.fac_q = fac ? reinterpret_cast<float*>(wsb + L.off_facq) : nullptr;
   p.neg_override = neg_override;
-  p.neg_ids = reinterpret_cast<int64_t*>(wsb + L.off_neg);
-  p.keys = reinterpret_cast<uint32_t*>(wsb + L.off_keys_in);
-  p.vals = reinterpret_cast<uint32_t*>(wsb + L.off_vals_in);
+  p.neg_ids = reinterpret_cast<int64_t*>(gb + L.off_neg);
+  p.keys = reinterpret_cast<uint32_t*>(gb + L.off_keys_in);
+  p.vals = reinterpret_cast<uint32_t*>(gb + L.off_vals_in);
   p.part = reinterpret_cast<float*>(wsb + L.off_part);
   // training: keys / record ids / negatives come from k_keys on the side stream
   p.write_keys = is_train ? 0 : 1;
@@ -493,8 +534,8 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   // side stream: sort keys depend on ids only, so key generation, the stable radix sort and the
   // segment table run concurrently with the step kernel and join before the update kernels
   uint32_t* keys_out = reinterpret_cast<uint32_t*>(wsb + L.off_keys_out);
-  uint32_t* vals_out = reinterpret_cast<uint32_t*>(wsb + L.off_vals_out);
-  uint32_t* seg_lo = reinterpret_cast<uint32_t*>(wsb + L.off_seg);
+  uint32_t* vals_out = reinterpret_cast<uint32_t*>(gb + L.off_vals_out);
+  uint32_t* seg_lo = reinterpret_cast<uint32_t*>(gb + L.off_seg);
   uint32_t* seg_hi = seg_lo + L.n_seg;
   // what the update kernels read: radix path = the two tables of k_segments; counting sort =
   // the scan itself (first position of key = off[key], one past the last = off[key + 1])
@@ -505,9 +546,65 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   if (lazy) { seg_hi = seg_lo + cfg->n_rel; use_lo = seg_lo; use_hi = seg_hi; }
   LazyParams lp;
   if (lazy || flush_first) fill_lazy(cfg, tables, (uint32_t) (flush_first ? tables->lazy_t : (int64_t) adam_t), lp);
+  // counting sort of one batch's record keys into the grouping set at `gbase`: histogram (in k_keys) -> scan ->
+  // scatter -> canonical order inside each segment (group_kernels.cuh); kp carries the batch (triples, Philox step)
+  auto group_chain = [&](cudaStream_t ax, const StepParams& kp0, char* gbase) -> int {
+    StepParams kp = kp0;
+    kp.neg_ids = reinterpret_cast<int64_t*>(gbase + L.off_neg);
+    kp.keys = reinterpret_cast<uint32_t*>(gbase + L.off_keys_in);
+    kp.vals = reinterpret_cast<uint32_t*>(gbase + L.off_vals_in);
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(gbase + L.off_seg);
+    uint32_t* off = cnt + L.n_seg;
+    const int64_t K = (int64_t) L.n_seg;
+    int64_t kb = (L.n_keys + 255) / 256;
+    if (kb > (int64_t) ctx->sm_count * 8) kb = (int64_t) ctx->sm_count * 8;
+    KGE_CUDA_OK(cudaMemsetAsync(cnt, 0, sizeof(uint32_t) * (2 * L.n_seg + 2), ax));
+    k_keys<<<(unsigned) kb, 256, 0, ax>>>(kp, cnt);
+    KGE_CUDA_OK(cudaGetLastError());
+    if (K <= SCAN_SMALL_MAX) k_scan<<<1, SCAN_THREADS, 0, ax>>>(cnt, off, K);
+    else {
+      size_t scan_bytes = L.cub_bytes;
+      KGE_CUDA_OK(cub::DeviceScan::ExclusiveSum(wsb + L.off_cub, scan_bytes, (const uint32_t*) cnt, off, K, ax));
+      k_scan_close<<<1, 1, 0, ax>>>(cnt, off, K);
+    }
+    KGE_CUDA_OK(cudaGetLastError());
+    k_scatter<<<(unsigned) kb, 256, 0, ax>>>(kp.keys, L.n_keys, off, cnt, kp.vals);
+    KGE_CUDA_OK(cudaGetLastError());
+    int64_t cb = (K + CANON_WARPS - 1) / CANON_WARPS;
+    if (cb > (int64_t) ctx->sm_count * 16) cb = (int64_t) ctx->sm_count * 16;
+    k_canon<<<(unsigned) cb, CANON_WARPS * 32, 0, ax>>>(off, K, kp.vals, reinterpret_cast<uint32_t*>(gbase + L.off_vals_out),
+                                                        reinterpret_cast<uint32_t*>(gbase + L.off_hdr),
+                                                        reinterpret_cast<uint32_t*>(gbase + L.off_heavy), cnt + 2 * L.n_seg + 1);
+    KGE_CUDA_OK(cudaGetLastError());
+    return KGE_OK;
+  };
+  // the NEXT batch's grouping, on its own stream, behind everything enqueued on `st` so far (the previous step,
+  // which last used that set, and whatever produced next_triples)
+  auto prefetch_next = [&]() -> int {
+    if (!can_pre || next_triples == nullptr) return KGE_OK;
+    cudaStream_t px = ctx->pre_stream;
+    KGE_CUDA_OK(cudaEventRecord(ctx->ev_pre_fork, st));
+    KGE_CUDA_OK(cudaStreamWaitEvent(px, ctx->ev_pre_fork, 0));
+    if (next_host)          // the next batch comes from host memory: its copy rides the same stream, ahead of the chain
+      KGE_CUDA_OK(cudaMemcpyAsync(const_cast<void*>(next_triples), next_host, (size_t) B * 3 * (cfg->id_dtype ? 8 : 4),
+                                  cudaMemcpyHostToDevice, px));
+    StepParams kp = p;
+    kp.triples = next_triples;
+    kp.sd.step = next_step;
+    if (dyn) kp.sd.step_dyn = &dyn->step_next;
+    pt.begin(3, px);
+    if (int rc2 = group_chain(px, kp, wsb + (size_t) (1 - gs) * L.gdelta)) return rc2;
+    pt.end(3, px);
+    KGE_CUDA_OK(cudaEventRecord(ctx->ev_pre_done, px));
+    pre.valid = true; pre.triples = next_triples; pre.B = B; pre.seed = seed; pre.step = next_step; pre.ws = ws;
+    pre.i_base = dp ? dp->i_base : 0; pre.k = k; pre.n_ent = cfg->n_ent; pre.side = cfg->corrupt_side;
+    pre.sampler = cfg->sampler; pre.set = 1 - gs; pre.graph = ctx->capturing;
+    return KGE_OK;
+  };
   // Host enqueue order: the caller's stream first (fork point, constraint, step kernel), so the
   // GPU starts on the critical path while the host is still enqueueing the side chain.
   auto fork_side = [&]() -> int {
+    if (int rc2 = prefetch_next()) return rc2;
     if (is_train) KGE_CUDA_OK(cudaEventRecord(ctx->ev_fork, st));
     pt.begin(0);
     if (flush_first) { if (int rc2 = launch_lazy<2>(lp, ctx->sm_count, st)) return rc2; }
@@ -518,6 +615,10 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   };
   auto side_chain = [&]() -> int {
     if (!is_train) return KGE_OK;
+    if (pre_hit) {          // grouped by the previous call: join its stream (a captured graph is ordered by its launches)
+      if (!ctx->capturing) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_pre_done, 0));
+      return KGE_OK;
+    }
     cudaStream_t ax = ctx->aux;
     KGE_CUDA_OK(cudaStreamWaitEvent(ax, ctx->ev_fork, 0));
     pt.begin(3, ax);
@@ -537,6 +638,12 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
       KGE_CUDA_OK(cudaEventRecord(ctx->ev_join, ax));
       return KGE_OK;
     }
+    if (!ctx->opt_radix_sort) {
+      if (int rc2 = group_chain(ax, p, gb)) return rc2;
+      pt.end(3, ax);
+      KGE_CUDA_OK(cudaEventRecord(ctx->ev_join, ax));
+      return KGE_OK;
+    }
     KGE_CUDA_OK(cudaMemsetAsync(seg_lo, 0, sizeof(uint32_t) * (2 * L.n_seg + 2), ax));
     if ((ctx->opt_radix_sort != 0)) {
       k_keys<<<(unsigned) kb, 256, 0, ax>>>(p, nullptr);
@@ -545,29 +652,6 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
       KGE_CUDA_OK(cub::DeviceRadixSort::SortPairs(wsb + L.off_cub, cub_bytes, (const uint32_t*) p.keys, keys_out,
                                                   (const uint32_t*) p.vals, vals_out, (int) L.n_keys, 0, sort_bits(cfg), ax));
       k_segments<<<(unsigned) ((L.n_keys + 255) / 256), 256, 0, ax>>>(keys_out, L.n_keys, seg_lo, seg_hi);
-      KGE_CUDA_OK(cudaGetLastError());
-    } else {
-      // counting sort: histogram (in k_keys) -> scan -> scatter -> canonical order inside each segment
-      uint32_t* cnt = seg_lo;
-      uint32_t* off = seg_lo + L.n_seg;
-      const int64_t K = (int64_t) L.n_seg;
-      k_keys<<<(unsigned) kb, 256, 0, ax>>>(p, cnt);
-      KGE_CUDA_OK(cudaGetLastError());
-      if (K <= SCAN_SMALL_MAX) k_scan<<<1, SCAN_THREADS, 0, ax>>>(cnt, off, K);
-      else {
-        size_t scan_bytes = L.cub_bytes;
-        KGE_CUDA_OK(cub::DeviceScan::ExclusiveSum(wsb + L.off_cub, scan_bytes, (const uint32_t*) cnt, off, K, ax));
-        k_scan_close<<<1, 1, 0, ax>>>(cnt, off, K);
-      }
-      KGE_CUDA_OK(cudaGetLastError());
-      k_scatter<<<(unsigned) kb, 256, 0, ax>>>(p.keys, L.n_keys, off, cnt, p.vals);
-      KGE_CUDA_OK(cudaGetLastError());
-      int64_t cb = (K + CANON_WARPS - 1) / CANON_WARPS;
-      if (cb > (int64_t) ctx->sm_count * 16) cb = (int64_t) ctx->sm_count * 16;
-      k_canon<<<(unsigned) cb, CANON_WARPS * 32, 0, ax>>>(off, K, p.vals, vals_out,
-                                                          reinterpret_cast<uint32_t*>(wsb + L.off_hdr),
-                                                          reinterpret_cast<uint32_t*>(wsb + L.off_heavy),
-                                                          seg_lo + 2 * L.n_seg + 1);
       KGE_CUDA_OK(cudaGetLastError());
     }
     pt.end(3, ax);
@@ -583,9 +667,23 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   if (!mat) {
     int ent_rows = (cfg->model == KGE_TRANSD) ? 2 : 1;
     int rel_rows = (cfg->model == KGE_UM) ? 0 : ((cfg->model == KGE_TRANSH || cfg->model == KGE_TRANSD) ? 2 : 1);
-    const int ppc = STEP_WARPS / p.wpp;
+    const int ppc = p.nwarps / p.wpp;
     SL.grid = (B + ppc - 1) / ppc;
-    SL.smem = step_smem_bytes(nv, p.wpp, k, ent_rows, rel_rows);
+    SL.smem = step_smem_bytes(nv, p.wpp, k, ent_rows, rel_rows, p.nwarps);
+    // DistMult: per-warp ring of negative rows filled by TMA bulk copies (StepParams.ring_slots) — the deepest
+    // of 32 / 16 / 8 / 4 rows that fits the shared memory left, never deeper than a warp's negatives
+    p.ring_slots = 0; p.ring_off = 0;
+    if (cfg->model == KGE_DISTMULT && nv <= 2 && !sh && (cfg->corrupt_side != KGE_SIDE_HT || (p.wpp & 1) == 0)) {   // the fast loop's condition
+      const int n_it_max = (k + p.wpp - 1) / p.wpp;
+      const size_t base = (SL.smem + 15) & ~(size_t) 15;
+      for (int S = 32; S >= 4; S >>= 1) {
+        if (S > ctx->opt_ring_max || (S > 4 && (S >> 1) >= n_it_max)) continue;
+        const size_t need = base + (((size_t) p.nwarps * (S >> 2) * 8 + 15) & ~(size_t) 15) + (size_t) p.nwarps * S * L.rld[KGE_T_ENT] * 4;
+        if (need > (size_t) ctx->smem_optin) continue;
+        p.ring_slots = S; p.ring_off = (uint32_t) base; SL.smem = need;
+        break;
+      }
+    }
     KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step needs %zu B shared memory", SL.smem);
     if (shard_phase != 2) { if (int rc2 = fork_side()) return rc2; }      // after the last argument check
     else { pt.begin(0); if (int rc2 = launch_constrain(ctx, cp, st)) return rc2; pt.end(0); }
@@ -647,7 +745,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     KGE_CUDA_OK(cudaGetLastError());
     pt.end(2);
   }
-  if (is_train && shard_phase != 2) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));     // join the side stream
+  if (is_train && shard_phase != 2 && !pre_hit) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));     // join the side stream
   if (neg_out)
     KGE_CUDA_OK(cudaMemcpyAsync(neg_out, p.neg_ids, sizeof(int64_t) * (size_t) B * k, cudaMemcpyDeviceToDevice, st));
   if (grad_only) {    // scal[4..8] = norm^2 per slot, loss share
@@ -683,6 +781,11 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     U.key_base = (s < 2) ? 0u : (uint32_t) cfg->n_ent;
     U.rec_base = (s < 2) ? 0u : (uint32_t) L.n_ent_rec;
     U.slot = s;
+    U.fac_coef = nullptr; U.fac_q = nullptr; U.fac_first = 0; U.fac_k = 1; U.fac_ht = 0;
+    if (s == KGE_T_ENT && p.fac_coef != nullptr) {
+      U.fac_coef = p.fac_coef; U.fac_q = p.fac_q; U.fac_first = (uint32_t) (2 * B); U.fac_k = k;
+      U.fac_ht = cfg->corrupt_side == KGE_SIDE_HT;
+    }
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
     U.n_peer = 0;
     U.owner_rows = 0; U.row_lo = 0; U.n_out = 0;
@@ -714,11 +817,12 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   up.n_keys = is_train ? L.n_keys : 0;
   up.seg_lo = use_lo; up.seg_hi = use_hi;
   up.seg_key0 = lazy ? (uint32_t) cfg->n_ent : 0u;
-  up.hdr = reinterpret_cast<const uint32_t*>(wsb + L.off_hdr);
-  up.heavy_keys = reinterpret_cast<const uint32_t*>(wsb + L.off_heavy);
+  up.hdr = reinterpret_cast<const uint32_t*>(gb + L.off_hdr);
+  up.heavy_keys = reinterpret_cast<const uint32_t*>(gb + L.off_heavy);
   up.n_heavy = seg_lo + 2 * L.n_seg + 1;
   up.scal = rp.scal;
   up.lr_t = cfg->optimizer == KGE_OPTIM_ADAM ? adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t) : cfg->lr;
+  up.lr_dyn = dyn ? &dyn->lr_t : nullptr;
   up.opt = cfg->optimizer;
   up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
   up.cw = cfg->constraint_weight;
@@ -751,7 +855,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     mu.seg_lo = use_lo; mu.seg_hi = use_hi;
     mu.key_base = (uint32_t) cfg->n_ent; mu.rec_base = (uint32_t) L.n_ent_rec;
     mu.opt = cfg->optimizer;
-    mu.scal = rp.scal; mu.lr_t = up.lr_t; mu.beta1 = cfg->beta1; mu.beta2 = cfg->beta2; mu.eps = cfg->eps;
+    mu.scal = rp.scal; mu.lr_t = up.lr_t; mu.lr_dyn = up.lr_dyn; mu.beta1 = cfg->beta1; mu.beta2 = cfg->beta2; mu.eps = cfg->eps;
     mu.reg_coef = (dense && cfg->model == KGE_RESCAL) ? 2.0f * cfg->constraint_weight / (float) cfg->n_rel : 0.f;
     mu.part = dense ? reinterpret_cast<float*>(wsb + L.off_matpart) : nullptr;
     mgrid = dim3((unsigned) mat_tiles(cfg), (unsigned) cfg->n_rel, (unsigned) mu.n_tabs);
@@ -782,6 +886,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     }
     pt.end(4);
     if (!sh) pt.keep_open();           // kge_train_apply continues this call's profile slot
+    if (ctx->capturing && pre.valid) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_pre_done, 0));   // a graph ends joined
     return KGE_OK;
   }
   if (dense) {
@@ -842,6 +947,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     tables->wn_valid[KGE_T_ENT] = shadow_ok ? 1 : 0;        // wn now holds normalise(new w)
   }
   pt.end(4);
+  if (ctx->capturing && pre.valid) KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_pre_done, 0));     // a graph ends joined
   return KGE_OK;
 }
 
@@ -863,6 +969,36 @@ extern "C" int kge_train_step_host(kge_ctx* ctx, const kge_cfg* cfg, kge_tables*
   KGE_CUDA_OK(cudaMemcpyAsync(dev_triples, host_triples, (size_t) B * 3 * (cfg->id_dtype ? 8 : 4), cudaMemcpyHostToDevice, st));
   if (int rc = train_impl(ctx, cfg, tables, smp, nullptr, dev_triples, B, seed, step, adam_t, nullptr, is_train, nullptr,
                           nullptr, dev_loss, nullptr, ws, ws_bytes, stream)) return rc;
+  KGE_CUDA_OK(cudaMemcpyAsync(host_loss_out, dev_loss, sizeof(float), cudaMemcpyDeviceToHost, st));
+  return KGE_OK;
+}
+
+extern "C" int kge_train_step_next(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                                   const void* triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
+                                   float* loss_out, const void* next_triples, uint64_t next_step, void* ws, size_t ws_bytes,
+                                   void* stream) {
+  return train_impl(ctx, cfg, tables, smp, nullptr, triples, B, seed, step, adam_t, nullptr, 1, nullptr, nullptr, loss_out,
+                    nullptr, ws, ws_bytes, stream, nullptr, 0, next_triples, next_step);
+}
+
+extern "C" int kge_train_step_host_next(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                                        const void* host_triples, void* dev_triples, int64_t B, uint64_t seed, uint64_t step,
+                                        uint64_t adam_t, float* dev_loss, float* host_loss_out, const void* host_next,
+                                        void* dev_next, uint64_t next_step, void* ws, size_t ws_bytes, void* stream) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  KGE_REQUIRE(ctx && cfg && host_triples && dev_triples && dev_loss && host_loss_out && B > 0, KGE_EINVAL,
+              "ctx / cfg / host_triples / dev_triples / dev_loss / host_loss_out / B invalid");
+  KGE_REQUIRE(!host_next || (dev_next && dev_next != dev_triples), KGE_EINVAL, "host_next needs its own staging buffer dev_next");
+  cudaStream_t st = (cudaStream_t) stream;
+  // the previous call copied (and grouped) this batch as its `next`: nothing to copy
+  const Prefetched& pre = ctx->pre;
+  const bool staged = pre.valid && !pre.graph && pre.triples == dev_triples && pre.B == B && pre.seed == seed && pre.step == step &&
+                      pre.ws == ws;
+  if (!staged)
+    KGE_CUDA_OK(cudaMemcpyAsync(dev_triples, host_triples, (size_t) B * 3 * (cfg->id_dtype ? 8 : 4), cudaMemcpyHostToDevice, st));
+  if (int rc = train_impl(ctx_, cfg, tables, smp, nullptr, dev_triples, B, seed, step, adam_t, nullptr, 1, nullptr, nullptr,
+                          dev_loss, nullptr, ws, ws_bytes, stream, nullptr, 0, host_next ? dev_next : nullptr, next_step, host_next))
+    return rc;
   KGE_CUDA_OK(cudaMemcpyAsync(host_loss_out, dev_loss, sizeof(float), cudaMemcpyDeviceToHost, st));
   return KGE_OK;
 }
@@ -924,6 +1060,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     U.rows = tables->t[s].rows; U.cols = tables->t[s].cols; U.ld = tables->t[s].ld;
     U.rec_ld = 0; U.key_base = 0; U.rec_base = 0;
     U.slot = s;
+    U.fac_coef = nullptr; U.fac_q = nullptr; U.fac_first = 0; U.fac_k = 1; U.fac_ht = 0;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
     U.owner_rows = 0; U.row_lo = 0; U.n_out = 0;
     if (g->n_peers > 0) {
@@ -978,6 +1115,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   up.hdr = nullptr; up.heavy_keys = nullptr; up.n_heavy = nullptr;
   up.scal = scal;
   up.lr_t = cfg->optimizer == KGE_OPTIM_ADAM ? adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t) : cfg->lr;
+  up.lr_dyn = ctx->capturing ? &ctx->dyn->lr_t : nullptr;
   up.opt = cfg->optimizer;
   up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
   up.cw = cfg->constraint_weight;
@@ -1105,6 +1243,7 @@ extern "C" int kge_shard_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     U.w = tables->t[s].w; U.m = tables->t[s].m; U.v = tables->t[s].v;
     U.rec = nullptr; U.rows = tables->t[s].rows; U.cols = tables->t[s].cols; U.ld = tables->t[s].ld;
     U.rec_ld = 0; U.key_base = 0; U.rec_base = 0; U.slot = s;
+    U.fac_coef = nullptr; U.fac_q = nullptr; U.fac_first = 0; U.fac_k = 1; U.fac_ht = 0;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
     U.n_peer = 1; U.peer[0] = g->dense[s];
     U.owner_rows = 0; U.row_lo = 0; U.n_out = 0;
@@ -1116,6 +1255,7 @@ extern "C" int kge_shard_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   up.hdr = nullptr; up.heavy_keys = nullptr; up.n_heavy = nullptr;
   up.scal = scal;
   up.lr_t = cfg->optimizer == KGE_OPTIM_ADAM ? adam_lr(cfg->lr, cfg->beta1, cfg->beta2, adam_t) : cfg->lr;
+  up.lr_dyn = nullptr;
   up.opt = cfg->optimizer;
   up.beta1 = cfg->beta1; up.beta2 = cfg->beta2; up.eps = cfg->eps;
   up.cw = cfg->constraint_weight; up.rowpart = nullptr;
@@ -1192,4 +1332,137 @@ extern "C" int kge_train_step_dp(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* t
   sl.abort_word = pf->flags[pf->rank] + KGE_MAX_PEERS;
   if (int rc = kge_train_apply(ctx, cfg, tables, &sl, nullptr, B, adam_t, loss_out, ws, ws_bytes, stream)) return rc;
   return kge_peer_barrier(ctx, pf, epoch + 1, stream);
+}
+
+// ---- a training step captured once as a CUDA graph and replayed (kge_abi.h: kge_step_graph) -----------
+namespace kge {
+// first node of every captured step: the launch's scalars, patched per launch with
+// cudaGraphExecKernelNodeSetParams, land in the device block the other kernels read
+__global__ void k_set_dyn(DynScal* d, unsigned long long step, unsigned long long step_next, float lr_t, uint32_t epoch) {
+  d->step = step; d->step_next = step_next; d->lr_t = lr_t; d->epoch = epoch;
+}
+struct GraphVariant {
+  cudaGraphExec_t exec = nullptr;
+  cudaGraph_t graph = nullptr;
+  cudaGraphNode_t set_node = nullptr;
+  int wn_valid_after = 0;
+};
+}  // namespace kge
+struct kge_step_graph {
+  kge_ctx_impl* ctx;
+  kge_cfg cfg;
+  kge_tables tables;         // pointers as of creation (wn_valid / lazy_t are taken from the caller's struct per launch)
+  kge_sampler smp; bool has_smp;
+  void* stage[2];            // device staging buffers of the batch (two: this batch / the look-ahead batch)
+  int64_t B; uint64_t seed;
+  float* dev_loss; void* ws; size_t ws_bytes;
+  cudaStream_t cap;
+  // variant key: bit 0 shadow table valid, bit 1 this batch was grouped by the previous launch, bit 2 this launch groups
+  // the next batch, bit 3 staging parity of this batch
+  kge::GraphVariant var[16];
+  int parity;                // staging buffer the NEXT ungrouped batch goes to
+  bool next_grouped;         // the previous launch grouped a batch (into stage[parity])
+  uint64_t next_step;
+};
+
+static int graph_capture(kge_step_graph* g, int key) {
+  kge_ctx_impl* ctx = g->ctx;
+  kge::GraphVariant& V = g->var[key];
+  const int par = (key >> 3) & 1;
+  kge_tables T = g->tables;
+  T.wn_valid[KGE_T_ENT] = key & 1;
+  const Prefetched saved = ctx->pre;
+  ctx->pre = Prefetched{};
+  if (key & 2) {             // pretend the previous launch grouped this batch into the set this parity uses
+    Prefetched& P = ctx->pre;
+    P.valid = true; P.triples = g->stage[par]; P.ws = g->ws; P.B = g->B; P.i_base = 0; P.n_ent = g->cfg.n_ent;
+    P.seed = g->seed; P.step = 0; P.k = k_eff_of(&g->cfg); P.side = g->cfg.corrupt_side; P.sampler = g->cfg.sampler;
+    P.set = par; P.graph = 1;
+  }
+  KGE_CUDA_OK(cudaStreamBeginCapture(g->cap, cudaStreamCaptureModeRelaxed));
+  ctx->capturing = 1;
+  k_set_dyn<<<1, 1, 0, g->cap>>>(ctx->dyn, 0ull, 0ull, 0.f, 0u);
+  int rc = train_impl(reinterpret_cast<kge_ctx*>(ctx), &g->cfg, &T, g->has_smp ? &g->smp : nullptr, nullptr, g->stage[par], g->B,
+                      g->seed, 0, 1, nullptr, 1, nullptr, nullptr, g->dev_loss, nullptr, g->ws, g->ws_bytes, g->cap, nullptr, 0,
+                      (key & 4) ? g->stage[1 - par] : nullptr, 0);
+  ctx->capturing = 0;
+  ctx->pre = saved;
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(g->cap, &graph);
+  if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+  KGE_REQUIRE(e == cudaSuccess && graph, KGE_ECUDA, "step graph capture failed: %s", cudaGetErrorString(e));
+  size_t n_root = 0;
+  KGE_CUDA_OK(cudaGraphGetRootNodes(graph, nullptr, &n_root));
+  KGE_REQUIRE(n_root == 1, KGE_ECUDA, "step graph has %zu root nodes, expected the scalar node alone", n_root);
+  KGE_CUDA_OK(cudaGraphGetRootNodes(graph, &V.set_node, &n_root));
+  KGE_CUDA_OK(cudaGraphInstantiate(&V.exec, graph, 0));
+  V.graph = graph;
+  V.wn_valid_after = T.wn_valid[KGE_T_ENT];
+  return KGE_OK;
+}
+
+extern "C" int kge_step_graph_create(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tables, const kge_sampler* smp,
+                                     void* dev_triples, void* dev_triples_next, int64_t B, uint64_t seed, float* dev_loss,
+                                     void* ws, size_t ws_bytes, kge_step_graph** out) {
+  auto* ctx = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  KGE_REQUIRE(ctx && cfg && tables && dev_triples && dev_loss && ws && out && B > 0, KGE_EINVAL, "bad kge_step_graph_create arguments");
+  KGE_REQUIRE(dev_triples_next != dev_triples, KGE_EINVAL, "the look-ahead staging buffer must differ from dev_triples");
+  if (int rc = check_cfg(cfg)) return rc;
+  if (int rc = check_tables(cfg, tables, true)) return rc;
+  KGE_REQUIRE(!lazy_requested(tables), KGE_EUNSUPPORTED, "step graphs cover dense tables (not row-lazy / sharded)");
+  auto* g = new kge_step_graph();
+  g->ctx = ctx; g->cfg = *cfg; g->tables = *tables; g->has_smp = smp != nullptr;
+  if (smp) g->smp = *smp;
+  g->stage[0] = dev_triples; g->stage[1] = dev_triples_next;
+  g->B = B; g->seed = seed; g->dev_loss = dev_loss; g->ws = ws; g->ws_bytes = ws_bytes;
+  g->parity = 0; g->next_grouped = false; g->next_step = 0;
+  if (cudaStreamCreateWithFlags(&g->cap, cudaStreamNonBlocking) != cudaSuccess) { delete g; set_error("stream create failed"); return KGE_ECUDA; }
+  *out = g;
+  return KGE_OK;
+}
+
+extern "C" int kge_step_graph_launch(kge_step_graph* g, kge_tables* tables, const void* triples, uint64_t step, uint64_t adam_t,
+                                     const void* next_triples, uint64_t next_step, float* host_loss_out, void* stream) {
+  KGE_REQUIRE(g && tables && adam_t >= 1, KGE_EINVAL, "bad kge_step_graph_launch arguments");
+  KGE_REQUIRE(!next_triples || g->stage[1], KGE_EINVAL, "the graph was created without a look-ahead staging buffer");
+  cudaStream_t st = (cudaStream_t) stream;
+  const size_t bytes = (size_t) g->B * 3 * (g->cfg.id_dtype ? 8 : 4);
+  const bool grouped = g->next_grouped && g->next_step == step;       // the previous launch staged + grouped this batch
+  if (!grouped) g->parity = 0;                                         // no staged batch (or not taken up): buffer / set 0
+  const int par = g->parity;
+  if (!grouped) {
+    KGE_REQUIRE(triples, KGE_EINVAL, "triples is NULL and the batch was not staged by the previous launch");
+    KGE_CUDA_OK(cudaMemcpyAsync(g->stage[par], triples, bytes, cudaMemcpyDefault, st));
+  }
+  if (next_triples) KGE_CUDA_OK(cudaMemcpyAsync(g->stage[1 - par], next_triples, bytes, cudaMemcpyDefault, st));
+  const int key = (tables->wn_valid[KGE_T_ENT] ? 1 : 0) | (grouped ? 2 : 0) | (next_triples ? 4 : 0) | (par << 3);
+  kge::GraphVariant& V = g->var[key];
+  if (!V.exec) { if (int rc = graph_capture(g, key)) return rc; }
+  unsigned long long a0 = step, a1 = next_step;
+  float lr_t = g->cfg.optimizer == KGE_OPTIM_ADAM ? adam_lr(g->cfg.lr, g->cfg.beta1, g->cfg.beta2, adam_t) : g->cfg.lr;
+  uint32_t epoch = 0;
+  DynScal* dptr = g->ctx->dyn;
+  void* args[5] = {&dptr, &a0, &a1, &lr_t, &epoch};
+  cudaKernelNodeParams np = {};
+  np.func = (void*) kge::k_set_dyn;
+  np.gridDim = dim3(1, 1, 1); np.blockDim = dim3(1, 1, 1); np.sharedMemBytes = 0; np.kernelParams = args; np.extra = nullptr;
+  KGE_CUDA_OK(cudaGraphExecKernelNodeSetParams(V.exec, V.set_node, &np));
+  KGE_CUDA_OK(cudaGraphLaunch(V.exec, st));
+  if (host_loss_out) KGE_CUDA_OK(cudaMemcpyAsync(host_loss_out, g->dev_loss, sizeof(float), cudaMemcpyDeviceToHost, st));
+  tables->wn_valid[KGE_T_ENT] = V.wn_valid_after;
+  g->next_grouped = next_triples != nullptr;
+  g->next_step = next_step;
+  if (next_triples) g->parity = 1 - par;         // the grouped batch sits in the other buffer / set
+  return KGE_OK;
+}
+
+extern "C" int kge_step_graph_destroy(kge_step_graph* g) {
+  if (!g) return KGE_OK;
+  for (auto& V : g->var) {
+    if (V.exec) cudaGraphExecDestroy(V.exec);
+    if (V.graph) cudaGraphDestroy(V.graph);
+  }
+  if (g->cap) cudaStreamDestroy(g->cap);
+  delete g;
+  return KGE_OK;
 }

@@ -133,6 +133,12 @@ struct UpdateTable {
   int64_t rows;
   int cols, ld;
   int rec_ld;            // row stride of rec
+  // factored records (StepParams.fac_coef): record ids >= fac_first are negatives whose row is
+  // fac_coef[id - fac_first] * fac_q[(i * n_side + side) * rec_ld], i = slot / fac_k
+  const float* fac_coef; // nullable
+  const float* fac_q;
+  uint32_t fac_first;
+  int fac_k, fac_ht;
   uint32_t key_base;     // key of row 0 in the sorted key space
   uint32_t rec_base;     // subtract from a sorted value to get this table's record row
   int slot;              // table slot (index into scal)
@@ -176,6 +182,15 @@ __device__ __forceinline__ void add_peers(const UpdateTable& T, int64_t row, int
     for (int u = 0; u < CPL; ++u) { const int c = lane + 32 * u; if (c < nch) g[u] += __ldg(gs + c); }
   }
 }
+// where a table's gradient records live: materialised rows, or (factored) coefficient x shared row
+struct RecSrc {
+  const float* rec; int rec_ld;
+  const float* fac_coef; const float* fac_q;
+  uint32_t fac_first; int fac_k, fac_ht;
+};
+__device__ __forceinline__ RecSrc rec_src(const UpdateTable& T) {
+  return RecSrc{T.rec, T.rec_ld, T.fac_coef, T.fac_q, T.fac_first, T.fac_k, T.fac_ht};
+}
 constexpr int SCAL_ABORT = 12;        // scal[12] != 0: a cross-GPU barrier gave up (k_dp_scales), the apply half must not run
 struct UpdateParams {
   UpdateTable tab[KGE_MAX_TABLES];
@@ -189,6 +204,7 @@ struct UpdateParams {
   uint32_t seg_key0;       // k_update: seg_lo / seg_hi are indexed by key - seg_key0 (row-lazy mode keeps the relation range only)
   const float* scal;
   float lr_t, beta1, beta2, eps;
+  const float* lr_dyn;   // nullable: lr_t lives on the device (captured step graph, DynScal)
   int opt;               // kge_opt_kind
   float cw;              // constraint_weight
   float* rowpart;        // DENSE=1: [2][total_rows]  (norm^2, loss term) per row
@@ -227,14 +243,26 @@ template <int CPL> struct RecDepth {
   static constexpr int LIGHT = CPL <= 2 ? 4 : (CPL == 4 ? 2 : 1);
   static constexpr int HEAVY = CPL == 1 ? 16 : (CPL == 2 ? 8 : (CPL == 4 ? 4 : 2));
 };
+__device__ __forceinline__ float4 scale4(float s, float4 a) {
+  return f4(__fmul_rn(s, a.x), __fmul_rn(s, a.y), __fmul_rn(s, a.z), __fmul_rn(s, a.w));
+}
 template <int CPL, int J = RecDepth<CPL>::LIGHT>
-__device__ __forceinline__ void sum_chunk(uint32_t mine, int n, const float* __restrict__ rec, int rec_ld, int nch, int lane,
-                                          float4 (&g)[CPL]) {
+__device__ __forceinline__ void sum_chunk(uint32_t mine, int n, const RecSrc& R, int nch, int lane, float4 (&g)[CPL]) {
   for (int j = 0; j < n; j += J) {
     const float4* r[J];
+    float cf[J];
+    bool fc[J];
 #pragma unroll
-    for (int x = 0; x < J; ++x)
-      r[x] = reinterpret_cast<const float4*>(rec + (int64_t) __shfl_sync(FULL, mine, (j + x) & 31) * rec_ld);
+    for (int x = 0; x < J; ++x) {
+      const uint32_t rid = __shfl_sync(FULL, mine, (j + x) & 31);
+      fc[x] = R.fac_coef != nullptr && rid >= R.fac_first && j + x < n;
+      cf[x] = 0.f;
+      if (fc[x]) {
+        const uint32_t slot = rid - R.fac_first, i = slot / (uint32_t) R.fac_k, c = slot - i * (uint32_t) R.fac_k;
+        cf[x] = __ldg(R.fac_coef + slot);
+        r[x] = reinterpret_cast<const float4*>(R.fac_q + (int64_t) (R.fac_ht ? 2 * i + (c & 1u) : i) * R.rec_ld);
+      } else r[x] = reinterpret_cast<const float4*>(R.rec + (int64_t) rid * R.rec_ld);
+    }
     float4 a[CPL][J];
 #pragma unroll
     for (int u = 0; u < CPL; ++u) {
@@ -245,22 +273,29 @@ __device__ __forceinline__ void sum_chunk(uint32_t mine, int n, const float* __r
 #pragma unroll
     for (int x = 0; x < J; ++x)
       if (j + x < n) {
+        // fl(coef * q): the row the step kernel would have stored (explicit rounding, no FMA with the add)
 #pragma unroll
-        for (int u = 0; u < CPL; ++u) g[u] += a[u][x];
+        for (int u = 0; u < CPL; ++u) g[u] += fc[x] ? scale4(cf[x], a[u][x]) : a[u][x];
       }
   }
 }
 
 // Records at sorted positions [lo, hi), ids fetched 32 at a time.
 template <int CPL, int J = RecDepth<CPL>::LIGHT>
-__device__ __forceinline__ void sum_records(const uint32_t* __restrict__ vals, const float* __restrict__ rec, int rec_ld,
-                                            uint32_t rec_base, int64_t lo, int64_t hi, int nch, int lane,
-                                            float4 (&g)[CPL]) {
+__device__ __forceinline__ void sum_records(const uint32_t* __restrict__ vals, const RecSrc& R, uint32_t rec_base, int64_t lo,
+                                            int64_t hi, int nch, int lane, float4 (&g)[CPL]) {
   for (int64_t q0 = lo; q0 < hi; q0 += WARP) {
     const int n = (int) ((hi - q0 < WARP) ? hi - q0 : WARP);
     const uint32_t mine = (lane < n) ? __ldg(vals + q0 + lane) - rec_base : 0u;
-    sum_chunk<CPL, J>(mine, n, rec, rec_ld, nch, lane, g);
+    sum_chunk<CPL, J>(mine, n, R, nch, lane, g);
   }
+}
+// plain materialised records (row-lazy / sharded kernels)
+template <int CPL, int J = RecDepth<CPL>::LIGHT>
+__device__ __forceinline__ void sum_records(const uint32_t* __restrict__ vals, const float* __restrict__ rec, int rec_ld,
+                                            uint32_t rec_base, int64_t lo, int64_t hi, int nch, int lane, float4 (&g)[CPL]) {
+  const RecSrc R{rec, rec_ld, nullptr, nullptr, 0u, 1, 0};
+  sum_records<CPL, J>(vals, R, rec_base, lo, hi, nch, lane, g);
 }
 
 // Keras Adam, sparse path: m = b1*m (+ (1-b1) g on touched rows), likewise v; then
@@ -293,9 +328,6 @@ __device__ __forceinline__ void adam_chunk(float4& w, float4& m, float4& v, cons
   adam1(w.y, m.y, v.y, gg.y, b1, b2, lr_t, eps);
   adam1(w.z, m.z, v.z, gg.z, b1, b2, lr_t, eps);
   adam1(w.w, m.w, v.w, gg.w, b1, b2, lr_t, eps);
-}
-__device__ __forceinline__ float4 scale4(float s, float4 a) {
-  return f4(__fmul_rn(s, a.x), __fmul_rn(s, a.y), __fmul_rn(s, a.z), __fmul_rn(s, a.w));
 }
 // keep the zero-padding invariant on the ragged last chunk
 __device__ __forceinline__ void mask_tail(float4& w, float4& m, float4& v, int c, int cols) {
@@ -332,7 +364,7 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
   float4 g[CPL];
 #pragma unroll
   for (int u = 0; u < CPL; ++u) g[u] = f4zero();
-  if (!heavy) sum_records<CPL>(p.vals, T.rec, T.rec_ld, T.rec_base, lo, hi, nch, lane, g);
+  if (!heavy) sum_records<CPL>(p.vals, rec_src(T), T.rec_base, lo, hi, nch, lane, g);
   for (int w2 = 0; w2 < 8; ++w2) {                     // CTA-uniform loop
     if (!s_heavy[w2]) continue;
     const UpdateTable& H = p.tab[s_tab[w2]];
@@ -341,7 +373,7 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
     float4 part[CPL];
 #pragma unroll
     for (int u = 0; u < CPL; ++u) part[u] = f4zero();
-    sum_records<CPL, RecDepth<CPL>::HEAVY>(p.vals, H.rec, H.rec_ld, H.rec_base, s_lo[w2] + L * warp / 8,
+    sum_records<CPL, RecDepth<CPL>::HEAVY>(p.vals, rec_src(H), H.rec_base, s_lo[w2] + L * warp / 8,
                                            s_lo[w2] + L * (warp + 1) / 8, hn, lane, part);
 #pragma unroll
     for (int u = 0; u < CPL; ++u) s_part[warp][u * WARP + lane] = part[u];
@@ -435,7 +467,7 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
     }
     gg = scale4(scale, gg);
     float4 m = m4[c], v = v4[c];
-    adam_chunk(w, m, v, gg, b1, b2, p.lr_t, p.eps, p.opt);
+    adam_chunk(w, m, v, gg, b1, b2, p.lr_dyn ? __ldg(p.lr_dyn) : p.lr_t, p.eps, p.opt);
     mask_tail(w, m, v, c, T.cols);
     m4[c] = m; v4[c] = v; w4[c] = w;
   }
@@ -451,6 +483,7 @@ __device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTabl
   float4* m4 = reinterpret_cast<float4*>(T.m + row * (int64_t) T.ld);
   float4* v4 = reinterpret_cast<float4*>(T.v + row * (int64_t) T.ld);
   const float scale = p.scal[T.slot];
+  const float lr_t = p.lr_dyn ? __ldg(p.lr_dyn) : p.lr_t;
   float4 wnew[CPL];
 #pragma unroll
   for (int u = 0; u < CPL; ++u) {
@@ -458,7 +491,7 @@ __device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTabl
     wnew[u] = f4zero();
     if (c >= nch) continue;
     float4 w = wi[c], m = m4[c], v = v4[c];
-    adam_chunk(w, m, v, scale4(scale, g[u]), p.beta1, p.beta2, p.lr_t, p.eps, p.opt);
+    adam_chunk(w, m, v, scale4(scale, g[u]), p.beta1, p.beta2, lr_t, p.eps, p.opt);
     mask_tail(w, m, v, c, T.cols);
     m4[c] = m; v4[c] = v;
     if (T.n_out == 0) w4[c] = w;
@@ -532,8 +565,9 @@ __global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
     uint32_t mine = __shfl_sync(FULL, hv, (lane + 2) & 31);           // lanes 0..5: ids from the header
     if (lane >= 6 && lane < n0) mine = __ldg(p.vals + lo + lane);
     mine = (lane < n0) ? mine - T.rec_base : 0u;
-    sum_chunk<CPL>(mine, n0, T.rec, T.rec_ld, nch, lane, g);
-    if (L > 32u) sum_records<CPL>(p.vals, T.rec, T.rec_ld, T.rec_base, (int64_t) lo + 32, (int64_t) lo + L, nch, lane, g);
+    const RecSrc RS = rec_src(T);
+    sum_chunk<CPL>(mine, n0, RS, nch, lane, g);
+    if (L > 32u) sum_records<CPL>(p.vals, RS, T.rec_base, (int64_t) lo + 32, (int64_t) lo + L, nch, lane, g);
   }
   if (MODE == 3) { store_peers<CPL>(T, row, nch, lane, g); return; }
   if (MODE == 4) add_peers<CPL>(T, row, nch, lane, g);
@@ -559,7 +593,7 @@ __global__ void __launch_bounds__(256) k_update_heavy(const UpdateParams p) {
   float4 part[CPL];
 #pragma unroll
   for (int u = 0; u < CPL; ++u) part[u] = f4zero();
-  sum_records<CPL, RecDepth<CPL>::HEAVY>(p.vals, T.rec, T.rec_ld, T.rec_base, lo + L * warp / 8, lo + L * (warp + 1) / 8, nch,
+  sum_records<CPL, RecDepth<CPL>::HEAVY>(p.vals, rec_src(T), T.rec_base, lo + L * warp / 8, lo + L * (warp + 1) / 8, nch,
                                          lane, part);
 #pragma unroll
   for (int u = 0; u < CPL; ++u) s_part[warp][u * WARP + lane] = part[u];

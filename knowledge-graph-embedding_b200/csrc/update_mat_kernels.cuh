@@ -39,6 +39,7 @@ struct MatUpdParams {
   uint32_t key_base, rec_base;      // relation keys are key_base + r; vals - rec_base = positive index
   const float* scal;
   float lr_t, beta1, beta2, eps;
+  const float* lr_dyn;   // nullable: lr_t on the device (captured step graph)
   int opt;               // kge_opt_kind
   float reg_coef;                   // dense regulariser: g += reg_coef * w   (RESCAL.py:191-198), 0 = none
   float* part;                      // MODE 1: [2][n_tabs * n_rel * tiles] (norm^2, sum w^2)
@@ -140,6 +141,7 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
   float* mr = T.m + r * (int64_t) T.ld;
   float* vr = T.v + r * (int64_t) T.ld;
   const float scale = (MODE == 0) ? p.scal[T.slot] : 1.f;
+  const float lr_t = p.lr_dyn ? __ldg(p.lr_dyn) : p.lr_t;
   float n2 = 0.f, w2 = 0.f;
 #pragma unroll
   for (int a = 0; a < 4; ++a) {
@@ -154,16 +156,16 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
         if (MODE == 1) { n2 += g * g; w2 += w * w; }
         else {
           g *= scale;
-          if (p.opt == KGE_OPTIM_SGD) wr[o] = w - p.lr_t * g;
+          if (p.opt == KGE_OPTIM_SGD) wr[o] = w - lr_t * g;
           else if (p.opt == KGE_OPTIM_ADAGRAD) {
             const float acc = vr[o] + g * g;
             vr[o] = acc;
-            wr[o] = w - p.lr_t * g / (sqrtf(acc) + p.eps);
+            wr[o] = w - lr_t * g / (sqrtf(acc) + p.eps);
           } else {
             float m = p.beta1 * mr[o] + (1.f - p.beta1) * g;
             float v = p.beta2 * vr[o] + (1.f - p.beta2) * g * g;
             mr[o] = m; vr[o] = v;
-            wr[o] = w - p.lr_t * m / (sqrtf(v) + p.eps);
+            wr[o] = w - lr_t * m / (sqrtf(v) + p.eps);
           }
         }
       }

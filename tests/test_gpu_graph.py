@@ -1,0 +1,125 @@
+"""Look-ahead grouping (kge_train_step_next / _host_next) and the captured step graph (kge_step_graph) against
+the plain kge_train_step: the results must be bit-identical — losses at every step, every table and optimizer
+slot at the end — because only WHEN the grouping runs and HOW the launches are issued changes."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import make_pair, rand_triples
+from oracle import ref_ops as O
+
+pytestmark = pytest.mark.gpu
+
+N, R = 500, 13
+CASES = [("DistMult", 48, None, "bce", 8, "h+t"), ("DistMult", 200, None, "bce", 64, "h+t"), ("DistMult", 50, None, "square", 3, "t"),
+         ("TransE", 50, "l1", "hinge", 4, "h+t"), ("TransD", 40, "l2", "hinge", 2, "h"), ("RotatE", 30, "l1", "selfadv", 6, "h+t"),
+         ("TransR", 24, "l2", "hinge", 2, "h+t"), ("RESCAL", 16, None, "bce", 2, "t")]
+LOSSES = {"hinge": O.PairwiseHingeLoss(1.0), "bce": O.BinaryCrossEntropyLoss(), "square": O.SquareErrorLoss(),
+          "selfadv": O.SelfAdversarialNegativeSamplingLoss(3.0, 1.0)}
+SCORES = {"l1": O.LpDistance(1), "l2": O.LpDistance(2), None: None}
+
+
+def _engine(case):
+    model, d, score, loss, k, side = case
+    _, _, eng = make_pair(model, N, R, d, None, score=SCORES[score], loss=LOSSES[loss], k=k, side=side)
+    return eng
+
+
+def _state(eng):
+    out = {}
+    for s, pt in eng.tab.items():
+        out[("w", s)] = pt.storage.clone()
+        if pt.m is not None:
+            out[("m", s)], out[("v", s)] = pt.m.clone(), pt.v.clone()
+    return out
+
+
+def _assert_same(a, b, where):
+    for key in a:
+        assert torch.equal(a[key], b[key]), (where, key, float((a[key] - b[key]).abs().max()))
+
+
+def _batches(n, B, seed=5):
+    rng = np.random.default_rng(seed)
+    return [torch.from_numpy(rand_triples(rng, B, N, R)) for _ in range(n)]
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] + "-" + str(c[1]) for c in CASES])
+def test_lookahead_equals_plain_bitwise(case):
+    B, steps = 96, 6
+    Xs = [x.cuda() for x in _batches(steps, B)]
+    plain, ahead = _engine(case), _engine(case)
+    lp, la = [], []
+    for i in range(steps):
+        lp.append(float(plain.train_step(Xs[i], 7, i).item()))
+        nxt = Xs[i + 1] if i + 1 < steps and i != 2 else None        # step 3 groups inline: the look-ahead may be dropped any time
+        la.append(float(ahead.train_step(Xs[i], 7, i, next_triples=nxt).item()))
+    assert lp == la, (lp, la)
+    _assert_same(_state(plain), _state(ahead), case)
+
+
+def test_lookahead_not_taken_up_is_harmless():
+    case = CASES[0]
+    B = 64
+    Xs = [x.cuda() for x in _batches(4, B)]
+    plain, ahead = _engine(case), _engine(case)
+    for i in range(3):
+        plain.train_step(Xs[i], 7, i)
+        ahead.train_step(Xs[i], 7, i, next_triples=Xs[3], next_step=99)       # announces a batch that never comes
+    _assert_same(_state(plain), _state(ahead), "look-ahead ignored")
+
+
+@pytest.mark.parametrize("case", CASES[:5], ids=[c[0] + "-" + str(c[1]) for c in CASES[:5]])
+def test_host_lookahead_equals_plain_bitwise(case):
+    B, steps = 80, 5
+    Xh = [x.pin_memory() for x in _batches(steps, B)]
+    plain, ahead = _engine(case), _engine(case)
+    l1, l2 = torch.zeros(1).pin_memory(), torch.zeros(1).pin_memory()
+    for i in range(steps):
+        plain.train_step_host(Xh[i], 7, i, l1)
+        ahead.train_step_host(Xh[i], 7, i, l2, next_host=Xh[i + 1] if i + 1 < steps else None)
+        torch.cuda.synchronize()
+        assert float(l1.item()) == float(l2.item()), (i, float(l1.item()), float(l2.item()))
+    _assert_same(_state(plain), _state(ahead), case)
+
+
+@pytest.mark.parametrize("lookahead", [False, True])
+@pytest.mark.parametrize("case", CASES, ids=[c[0] + "-" + str(c[1]) for c in CASES])
+def test_step_graph_equals_plain_bitwise(case, lookahead):
+    """Captured graph vs kge_train_step over the first steps (the shadow table becomes valid after step 1, so two
+    variants are captured), from host batches, with and without the look-ahead batch."""
+    B, steps = 96, 7
+    Xh = [x.pin_memory() for x in _batches(steps, B)]
+    plain, gr = _engine(case), _engine(case)
+    G = gr.step_graph(B, 7, lookahead=lookahead)
+    lh = torch.zeros(1).pin_memory()
+    for i in range(steps):
+        want = float(plain.train_step(Xh[i].cuda(), 7, i).item())
+        nxt = Xh[i + 1] if lookahead and i + 1 < steps and i != 3 else None
+        G.launch(Xh[i], i, next_triples=nxt, host_loss=lh)
+        torch.cuda.synchronize()
+        assert float(lh.item()) == want, (i, float(lh.item()), want)
+    _assert_same(_state(plain), _state(gr), case)
+    # the graph and the plain call can be mixed on one engine (same tables, Adam step counter shared)
+    X = Xh[0].cuda()
+    a = float(plain.train_step(X, 7, 50).item())
+    b = float(gr.train_step(X, 7, 50).item())
+    assert a == b
+    _assert_same(_state(plain), _state(gr), "mixed")
+
+
+def test_step_graph_device_batches_and_sgd():
+    from KGE._b200 import lib as L
+    case = ("TransE", 50, "l1", "hinge", 4, "h+t")
+    B, steps = 64, 5
+    Xd = [x.cuda() for x in _batches(steps, B)]
+    plain, gr = _engine(case), _engine(case)
+    for e in (plain, gr):
+        e.cfg.optimizer = L.OPTIM_SGD if hasattr(L, "OPTIM_SGD") else 1
+        e.cfg.lr = 0.05
+    G = gr.step_graph(B, 3)
+    for i in range(steps):
+        want = float(plain.train_step(Xd[i], 3, i).item())
+        got = float(G.launch(Xd[i], i, next_triples=Xd[i + 1] if i + 1 < steps else None).item())
+        assert got == want, (i, got, want)
+    _assert_same(_state(plain), _state(gr), "sgd")
