@@ -215,11 +215,19 @@ def run_ours(args, rank, world, device):
     seed = 12345
     step_no = [0]
 
-    def one_step(batch):
+    def one_step(batch, nxt=None):
+        """One step through the plain C-ABI call; nxt = the following batch (look-ahead grouping, single GPU)."""
         if world > 1:
             eng.train_step_dp(batch, seed, step_no[0], B * world, rank * B, loss_out=loss_dev)
         else:
-            eng.train_step(batch, seed, step_no[0], is_train=True, loss_out=loss_dev)
+            eng.train_step(batch, seed, step_no[0], is_train=True, loss_out=loss_dev, next_triples=nxt)
+        step_no[0] += 1
+
+    graph = eng.step_graph(B, seed) if world == 1 and os.environ.get("KGE_BENCH_GRAPH", "1") != "0" else None
+
+    def graph_step(batch, nxt, host_loss=None):
+        """The same step through the captured graph (kge_step_graph): batch / nxt from device or pinned host memory."""
+        graph.launch(batch, step_no[0], next_triples=nxt, host_loss=host_loss)
         step_no[0] += 1
 
     def barrier():
@@ -229,19 +237,27 @@ def run_ours(args, rank, world, device):
 
     clk = Clocks(torch.cuda.current_device()).start()
     for i in range(args.warmup):
-        one_step(dev_batches[i % n_batches])
+        one_step(dev_batches[i % n_batches], dev_batches[(i + 1) % n_batches])
+    if graph is not None:
+        for i in range(args.warmup):
+            graph_step(dev_batches[i % n_batches], dev_batches[(i + 1) % n_batches])
     barrier()
 
-    # ---- value: inputs resident in HBM, L2 flushed between steps, per-step CUDA events ----
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    barrier()
-    for i in range(args.steps):
-        flush.zero_()
-        ev[i][0].record()
-        one_step(dev_batches[i % n_batches])
-        ev[i][1].record()
-    barrier()
-    ms_cold = sum(a.elapsed_time(b) for a, b in ev)
+    # ---- value: inputs resident in HBM, L2 flushed between steps, per-step CUDA events.  Single GPU: the step is
+    # the captured graph with the next batch's grouping under it (the product's training loop); the plain-call
+    # figure (same kernels, ~20 launches per step issued by the host) is kept beside it. ----
+    def timed_cold(step_fn):
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        barrier()
+        for i in range(args.steps):
+            flush.zero_()
+            ev[i][0].record()
+            step_fn(dev_batches[i % n_batches], dev_batches[(i + 1) % n_batches])
+            ev[i][1].record()
+        barrier()
+        return sum(a.elapsed_time(b) for a, b in ev)
+    ms_cold_plain = timed_cold(one_step)
+    ms_cold = timed_cold(graph_step) if graph is not None else ms_cold_plain
 
     # ---- the same loop again with the library's per-phase events on (they sit between the
     # kernels, so this pass is for the phase breakdown / roofline only, not for `value`) ----
@@ -250,7 +266,7 @@ def run_ours(args, rank, world, device):
     barrier()
     for i in range(n_prof):
         flush.zero_()
-        one_step(dev_batches[i % n_batches])
+        one_step(dev_batches[i % n_batches], dev_batches[(i + 1) % n_batches])
     barrier()
     phases, n_calls = eng.profile_end()
 
@@ -259,7 +275,7 @@ def run_ours(args, rank, world, device):
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for i in range(args.steps):
-        one_step(dev_batches[i % n_batches])
+        (graph_step if graph is not None else one_step)(dev_batches[i % n_batches], dev_batches[(i + 1) % n_batches])
     b.record()
     barrier()
     ms_warm = a.elapsed_time(b)
@@ -274,12 +290,24 @@ def run_ours(args, rank, world, device):
             stage.copy_(host_batches[i % n_batches], non_blocking=True)
             one_step(stage)
             loss_host.copy_(loss_dev, non_blocking=True)
+        elif graph is not None:   # host buffers through the captured graph: H2D of this (first step) / the next batch,
+            graph_step(host_batches[i % n_batches], host_batches[(i + 1) % n_batches], loss_host)   # step, D2H of the loss
         else:           # host buffers straight through the C-ABI: H2D + step + D2H enqueued by kge_train_step_host
             eng.train_step_host(host_batches[i % n_batches], seed, step_no[0], loss_host)
             step_no[0] += 1
         torch.cuda.current_stream().synchronize()      # the reference reads loss.numpy() per batch
     barrier()
     ms_e2e = (time.perf_counter() - t0) * 1e3
+    ms_e2e_plain = None
+    if graph is not None:       # the same through kge_train_step_host (no graph, no look-ahead), for comparison
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            eng.train_step_host(host_batches[i % n_batches], seed, step_no[0], loss_host)
+            step_no[0] += 1
+            torch.cuda.current_stream().synchronize()
+        barrier()
+        ms_e2e_plain = (time.perf_counter() - t0) * 1e3
 
     # ---- the same with the loss of step i read one step late (what KGEModel.train does even more
     # lazily: it keeps the per-batch losses on the device and syncs once per epoch); extra information,
@@ -294,6 +322,8 @@ def run_ours(args, rank, world, device):
             stage.copy_(host_batches[i % n_batches], non_blocking=True)
             one_step(stage)
             loss2[i & 1].copy_(loss_dev, non_blocking=True)
+        elif graph is not None:
+            graph_step(host_batches[i % n_batches], host_batches[(i + 1) % n_batches], loss2[i & 1])
         else:
             eng.train_step_host(host_batches[i % n_batches], seed, step_no[0], loss2[i & 1])
             step_no[0] += 1
@@ -314,7 +344,7 @@ def run_ours(args, rank, world, device):
         if int(need.item()) == 0:
             break
         for i in range(200):
-            one_step(dev_batches[i % n_batches])
+            one_step(dev_batches[i % n_batches], dev_batches[(i + 1) % n_batches])
         torch.cuda.synchronize()
         need[0] = 1 if (clk.proc is not None and len(clk.rows) < 2) else 0
     clk.stop()
@@ -324,7 +354,7 @@ def run_ours(args, rank, world, device):
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     ms_cold, ms_warm, ms_e2e, ms_e2e_lag = t.tolist()
     triples = world * B * (1 + k_eff) * args.steps
-    return {"eng": eng, "ms_cold": ms_cold, "ms_warm": ms_warm, "ms_e2e": ms_e2e, "ms_e2e_lag": ms_e2e_lag, "triples": triples,
+    return {"eng": eng, "ms_cold_plain": ms_cold_plain, "ms_e2e_plain": ms_e2e_plain, "graph": graph is not None, "ms_cold": ms_cold, "ms_warm": ms_warm, "ms_e2e": ms_e2e, "ms_e2e_lag": ms_e2e_lag, "triples": triples,
             "phases": phases, "n_calls": n_calls, "n_prof": n_prof, "clocks": clk.summary(), "train": train,
             "loss": float(loss_host.item())}
 
@@ -708,13 +738,18 @@ def main():
         "exchange": (getattr(r["eng"], "_dp_kind", None) or "none") if world > 1 else "none",
         "clocks": r["clocks"],
         "value_steady_state_l2_warm": r["triples"] / (r["ms_warm"] * 1e-3),
+        "step_api": ("kge_step_graph_launch (captured CUDA graph, next batch grouped under the step)" if r["graph"] else
+                     "kge_train_step_dp" if world > 1 else "kge_train_step_next"),
+        "value_plain_calls": r["triples"] / (r["ms_cold_plain"] * 1e-3),
+        "value_plain_calls_note": "same kernels through kge_train_step_next: ~20 launches / event calls per step issued by the host",
+        "e2e_plain_calls": (r["triples"] / (r["ms_e2e_plain"] * 1e-3)) if r["ms_e2e_plain"] else None,
         "e2e": {"value": r["triples"] / (r["ms_e2e"] * 1e-3), "unit": "triples/s",
                 "h2d_bytes_per_step": W["B"] * 3 * 8, "d2h_bytes_per_step": 4,
                 "sync": "stream synchronised and the loss read on the host after every step"},
         "e2e_loss_one_step_late": {"value": r["triples"] / (r["ms_e2e_lag"] * 1e-3), "unit": "triples/s",
                                    "note": "same H2D / step / D2H per step, loss of step i read while step i+1 runs "
                                            "(KGEModel.train reads losses once per epoch)"},
-        "gpu_launches": args.steps * (8 if world == 1 else 12),
+        "gpu_launches": args.steps * (8 if world == 1 else 12),      # single GPU: k_set_dyn, k_step, k_keys, k_scan, k_scatter, k_canon, k_update_heavy, k_update_fast
         "gpu_launches_note": "own kernels per step: k_constrain, k_step (loss/clip reduction folded into its last warp), "
         "k_update_fast on the caller's stream; k_keys, k_scan, k_scatter, k_canon, k_update_heavy on the side stream "
         "(+ one memset there); data-parallel runs split the update pair into k_update_fast/heavy<3> (row sums stored "

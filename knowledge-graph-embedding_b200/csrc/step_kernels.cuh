@@ -147,18 +147,19 @@ __global__ void __launch_bounds__(StepBounds<M, NV>::THREADS, StepBounds<M, NV>:
   // before anything else so that they are in flight while the positive is loaded and scored.  Rows
   // j0 .. j0+3 (j0 % 4 == 0) share one mbarrier; the lane that holds a row's id issues its copy.
   const int RS = (M::KIND == KGE_DISTMULT && md.shard_rows == 0) ? p.ring_slots : 0;
-  const int RSM = RS > 0 ? RS : 4, RSG = RSM >> 2;       // modulo operands (never zero)
+  const int RSM = RS > 0 ? RS : 4, RSG = RSM >> 2;       // ring depth is a power of two: modulo = mask
+  const int rs_log = 31 - __clz(RSM);
   const uint32_t row_bytes = (uint32_t) md.rld[KGE_T_ENT] * 4u;
   uint64_t* ring_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(smem4) + p.ring_off) + (size_t) warp * (RS >> 2);
   float* ring = reinterpret_cast<float*>(reinterpret_cast<char*>(smem4) + p.ring_off + (((size_t) nw * (RS >> 2) * 8 + 15) & ~(size_t) 15)) +
                 (size_t) warp * RS * md.rld[KGE_T_ENT];
   auto ring_issue = [&](int j0) {
     const int l0 = j0 & 31, nrows = (n_it - j0 < 4) ? n_it - j0 : 4;
-    uint64_t* bar = ring_bar + ((j0 >> 2) % RSG);
+    uint64_t* bar = ring_bar + ((j0 >> 2) & (RSG - 1));
     if (lane == l0) tc::mbar_expect_tx(bar, (uint32_t) nrows * row_bytes);
     const int x = lane - l0;
     if (x >= 0 && x < nrows) {
-      bulk_row_g2s(ring + (size_t) ((j0 + x) % RSM) * md.rld[KGE_T_ENT], md.t[KGE_T_ENT].w + my_e * (int64_t) md.t[KGE_T_ENT].ld,
+      bulk_row_g2s(ring + (size_t) ((j0 + x) & (RSM - 1)) * md.rld[KGE_T_ENT], md.t[KGE_T_ENT].w + my_e * (int64_t) md.t[KGE_T_ENT].ld,
                    row_bytes, bar);
       if (p.write_keys) {
         const int64_t slot = i * k + wig + (int64_t) (j0 + x) * wpp;
@@ -436,7 +437,7 @@ __global__ void __launch_bounds__(StepBounds<M, NV>::THREADS, StepBounds<M, NV>:
       const float q2 = row_dot_partial(q, q);
       const bool ht = p.sd.side_mode == KGE_SIDE_HT;
       if (TRAIN && p.fac_coef != nullptr && wig < (ht ? 2 : 1))      // one writer per (positive, side)
-        store_row(q, p.fac_q, ht ? 2 * i + wig : i, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
+        store_row(q, p.fac_q, ht ? 2 * i + (wig & 1) : i, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
       // Four negatives per pass: their rows are requested together, the four partial dot products are
       // reduced "transposed" (xor 16 / 8 hand half of the values to the partner lane, xor 4 / 2 / 1
       // finish one value per lane: 6 shuffles for 4 sums, the same addition tree as warp_sum, so the
@@ -446,19 +447,25 @@ __global__ void __launch_bounds__(StepBounds<M, NV>::THREADS, StepBounds<M, NV>:
       // the loop.
       const int lx = lane >> 3;
       constexpr int G4 = 4;
+      // loop-invariant pieces of the index arithmetic
+      const int ld4 = md.rld[KGE_T_ENT] >> 2;                         // float4 per staged row
+      const float4* ring4 = reinterpret_cast<const float4*>(ring) + lane;
+      bool cok[NV];
+#pragma unroll
+      for (int v = 0; v < NV; ++v) cok[v] = 4 * (lane + v * WARP) < md.t[KGE_T_ENT].cols;
+      float2* coef_w = p.fac_coef != nullptr ? reinterpret_cast<float2*>(p.fac_coef) + (i * k + wig) : nullptr;
+      const float qrow = __uint_as_float((uint32_t) (ht ? 2 * i + (wig & 1) : i));       // index of this warp's q row (wig parity = side)
       for (int it0 = 0; it0 < n_it; it0 += G4) {
         Ent Nb[G4];
         float d[G4];
+        const int nval = n_it - it0;                                   // negatives of this pass: x < nval
         if (RS > 0) {
-          tc::mbar_wait(ring_bar + ((it0 >> 2) % RSG), (uint32_t) ((it0 / RSM) & 1));
+          tc::mbar_wait(ring_bar + ((it0 >> 2) & (RSG - 1)), (uint32_t) ((it0 >> rs_log) & 1));
+          const float4* src = ring4 + (it0 & (RSM - 1)) * ld4;        // a pass never wraps: it0 and the depth are multiples of 4
 #pragma unroll
           for (int x = 0; x < G4; ++x) {
-            const float4* src = reinterpret_cast<const float4*>(ring + (size_t) ((it0 + x) % RSM) * md.rld[KGE_T_ENT]);
 #pragma unroll
-            for (int v = 0; v < NV; ++v) {
-              const int c = lane + v * WARP;
-              Nb[x].e.v[v] = (it0 + x < n_it && 4 * c < md.t[KGE_T_ENT].cols) ? src[c] : f4zero();
-            }
+            for (int v = 0; v < NV; ++v) Nb[x].e.v[v] = (x < nval && cok[v]) ? src[x * ld4 + v * WARP] : f4zero();
           }
         } else {
           if (it0 > 0 && (it0 & 31) == 0) draw(it0);          // G4 divides 32: a pass never straddles a draw
@@ -490,13 +497,13 @@ __global__ void __launch_bounds__(StepBounds<M, NV>::THREADS, StepBounds<M, NV>:
         const float w = softmax ? expf(p.loss.temperature * sn - sm_max) * sm_inv : 1.f;
         float term, dneg, dpp;
         loss_neg(p.loss, sp, sn, w, term, dneg, dpp);
-        if (it0 + lx >= n_it) { term = 0.f; dneg = 0.f; dpp = 0.f; }
+        if (lx >= nval) { term = 0.f; dneg = 0.f; dpp = 0.f; }
         lsum += term;
         gpos += dpp;
         if (TRAIN) {
 #pragma unroll
           for (int x = 0; x < G4; ++x) {
-            if (it0 + x >= n_it) break;
+            if (x >= nval) break;
             const float dn = __shfl_sync(FULL, dneg, 8 * x);
             float pe = 0.f, pr = 0.f;
 #pragma unroll
@@ -517,8 +524,7 @@ __global__ void __launch_bounds__(StepBounds<M, NV>::THREADS, StepBounds<M, NV>:
               store_row(gN, rt.b0, rt.row, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane);
             }
           }
-          if (p.fac_coef != nullptr && (lane & 7) == 0 && it0 + lx < n_it)
-            p.fac_coef[i * k + wig + (int64_t) (it0 + lx) * wpp] = dneg;
+          if (coef_w != nullptr && (lane & 7) == 0 && lx < nval) coef_w[(it0 + lx) * wpp] = make_float2(dneg, qrow);
         }
         if (RS > 0 && it0 + RS < n_it) {                   // the pass's four slots are free: request rows it0 + RS ..
           __syncwarp();
@@ -669,11 +675,29 @@ __global__ void __launch_bounds__(StepBounds<M, NV>::THREADS, StepBounds<M, NV>:
       }
     }
   }
-  if (lane == 0) {
+  if (p.tail) {
+    // CTA level: the leader warps of the CTA's positives meet on their own named barrier (the other warps
+    // have left), the first one sums their partials in positive order and publishes one value per quantity
+    const int left = (int) (p.B - (int64_t) blockIdx.x * ppc), nvalid = left < ppc ? left : ppc;
+    float* s_red0 = s_red - warp * 8;
+    if (lane == 0) {
+#pragma unroll
+      for (int q = 0; q < N_PART; ++q) s_red[q] = red[q];
+    }
+    if (nvalid > 1) asm volatile("bar.sync 15, %0;" ::"r"(nvalid * WARP) : "memory");
+    else __syncwarp();
+    if (grp == 0) {
+      if (lane < N_PART) {
+        float a = 0.f;
+        for (int g2 = 0; g2 < nvalid; ++g2) a += s_red0[g2 * wpp * 8 + lane];
+        p.part[(size_t) lane * gridDim.x + blockIdx.x] = a;
+      }
+      if (last_warp_done(p.done, gridDim.x, lane)) tail_reduce_ctas(p.rp, (int) gridDim.x, lane);
+    }
+  } else if (lane == 0) {
 #pragma unroll
     for (int q = 0; q < N_PART; ++q) p.part[(size_t) q * p.B + i] = red[q];
   }
-  if (p.tail && last_warp_done(p.done, (unsigned) p.B, lane)) tail_reduce_warp(p.rp, lane);
   if (TRAIN) {
     { const RecTarget rt = rec_target(p, i); GH.store_to(md, rt.b0, rt.b1, rt.row, lane); }
     { const RecTarget rt = rec_target(p, p.B + i); GT.store_to(md, rt.b0, rt.b1, rt.row, lane); }

@@ -262,7 +262,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_mat(const MatStepParams q
       for (int w2 = 0; w2 < STEP_WARPS; ++w2) a += s_red[w2 * 8 + lane];
       p.part[(size_t) lane * p.B + i] = a;
     }
-    if (p.tail && last_warp_done(p.done, (unsigned) p.B, lane)) tail_reduce_warp(p.rp, lane);
+    if (p.tail && last_warp_done(p.done, (unsigned) p.B, lane)) tail_reduce_ctas(p.rp, (int) p.B, lane);
   }
   if (TRAIN && warp < MAT_ACC_ROWS) {
     Row<NV> acc;

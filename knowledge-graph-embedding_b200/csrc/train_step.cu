@@ -120,7 +120,7 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   L.off_facq = L.off_fcoef = 0;
   if (c->model == KGE_DISTMULT) {                            // factored records (StepParams.fac_coef)
     L.off_facq = take(sizeof(float) * 2 * (size_t) B * L.rld[KGE_T_ENT]);
-    L.off_fcoef = take(sizeof(float) * (size_t) B * (k > 0 ? k : 1));
+    L.off_fcoef = take(sizeof(float) * 2 * (size_t) B * (k > 0 ? k : 1));   // {coefficient, q-row index} per negative
   }
   L.ldp = 0; L.off_recP = 0; L.n_mat_cta = 0;
   if (is_matrix_model(c->model)) {
@@ -508,7 +508,10 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   p.nwarps = STEP_WARPS;
   if (!mat && cfg->model == KGE_DISTMULT && nv <= 2) {
     const int64_t per_sm = (B * p.wpp + ctx->sm_count - 1) / ctx->sm_count;
-    if (per_sm <= STEP_MAX_WARPS) p.nwarps = (int) ((per_sm + p.wpp - 1) / p.wpp) * p.wpp;
+    if (per_sm <= STEP_MAX_WARPS) {
+      p.nwarps = (int) ((per_sm + p.wpp - 1) / p.wpp) * p.wpp;
+      if (p.nwarps > STEP_MAX_WARPS) p.nwarps = STEP_MAX_WARPS / p.wpp * p.wpp;
+    }
   }
   // factored records: dense (not row-lazy / sharded) training step whose warps each corrupt one side
   const bool fac = !mat && cfg->model == KGE_DISTMULT && is_train && !lazy && !sh &&
@@ -1357,6 +1360,8 @@ struct kge_step_graph {
   int64_t B; uint64_t seed;
   float* dev_loss; void* ws; size_t ws_bytes;
   cudaStream_t cap;
+  cudaEvent_t ev[6];         // the context's fork / join events are replaced by these while capturing (an event recorded
+                             // inside a capture cannot be waited on by ordinary calls afterwards)
   // variant key: bit 0 shadow table valid, bit 1 this batch was grouped by the previous launch, bit 2 this launch groups
   // the next batch, bit 3 staging parity of this batch
   kge::GraphVariant var[16];
@@ -1379,6 +1384,13 @@ static int graph_capture(kge_step_graph* g, int key) {
     P.seed = g->seed; P.step = 0; P.k = k_eff_of(&g->cfg); P.side = g->cfg.corrupt_side; P.sampler = g->cfg.sampler;
     P.set = par; P.graph = 1;
   }
+  cudaEvent_t* slots[6] = {&ctx->ev_fork, &ctx->ev_join, &ctx->ev_mid, &ctx->ev_heavy, &ctx->ev_pre_fork, &ctx->ev_pre_done};
+  cudaEvent_t keep[6];
+  for (int j = 0; j < 6; ++j) { keep[j] = *slots[j]; *slots[j] = g->ev[j]; }
+  struct Restore {
+    cudaEvent_t** slots; cudaEvent_t* keep; kge_ctx_impl* c; const Prefetched* saved;
+    ~Restore() { for (int j = 0; j < 6; ++j) *slots[j] = keep[j]; c->capturing = 0; c->pre = *saved; }
+  } restore{slots, keep, ctx, &saved};
   KGE_CUDA_OK(cudaStreamBeginCapture(g->cap, cudaStreamCaptureModeRelaxed));
   ctx->capturing = 1;
   k_set_dyn<<<1, 1, 0, g->cap>>>(ctx->dyn, 0ull, 0ull, 0.f, 0u);
@@ -1386,7 +1398,6 @@ static int graph_capture(kge_step_graph* g, int key) {
                       g->seed, 0, 1, nullptr, 1, nullptr, nullptr, g->dev_loss, nullptr, g->ws, g->ws_bytes, g->cap, nullptr, 0,
                       (key & 4) ? g->stage[1 - par] : nullptr, 0);
   ctx->capturing = 0;
-  ctx->pre = saved;
   cudaGraph_t graph = nullptr;
   cudaError_t e = cudaStreamEndCapture(g->cap, &graph);
   if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
@@ -1417,6 +1428,8 @@ extern "C" int kge_step_graph_create(kge_ctx* ctx_, const kge_cfg* cfg, const kg
   g->B = B; g->seed = seed; g->dev_loss = dev_loss; g->ws = ws; g->ws_bytes = ws_bytes;
   g->parity = 0; g->next_grouped = false; g->next_step = 0;
   if (cudaStreamCreateWithFlags(&g->cap, cudaStreamNonBlocking) != cudaSuccess) { delete g; set_error("stream create failed"); return KGE_ECUDA; }
+  for (int j = 0; j < 6; ++j)
+    if (cudaEventCreateWithFlags(&g->ev[j], cudaEventDisableTiming) != cudaSuccess) { set_error("event create failed"); return KGE_ECUDA; }
   *out = g;
   return KGE_OK;
 }
@@ -1463,6 +1476,7 @@ extern "C" int kge_step_graph_destroy(kge_step_graph* g) {
     if (V.graph) cudaGraphDestroy(V.graph);
   }
   if (g->cap) cudaStreamDestroy(g->cap);
+  for (int j = 0; j < 6; ++j) if (g->ev[j]) cudaEventDestroy(g->ev[j]);
   delete g;
   return KGE_OK;
 }

@@ -134,7 +134,7 @@ struct UpdateTable {
   int cols, ld;
   int rec_ld;            // row stride of rec
   // factored records (StepParams.fac_coef): record ids >= fac_first are negatives whose row is
-  // fac_coef[id - fac_first] * fac_q[(i * n_side + side) * rec_ld], i = slot / fac_k
+  // c * fac_q[j * rec_ld] with {c, j} = the float / uint32 pair fac_coef[2 * (id - fac_first)]
   const float* fac_coef; // nullable
   const float* fac_q;
   uint32_t fac_first;
@@ -257,10 +257,10 @@ __device__ __forceinline__ void sum_chunk(uint32_t mine, int n, const RecSrc& R,
       const uint32_t rid = __shfl_sync(FULL, mine, (j + x) & 31);
       fc[x] = R.fac_coef != nullptr && rid >= R.fac_first && j + x < n;
       cf[x] = 0.f;
-      if (fc[x]) {
-        const uint32_t slot = rid - R.fac_first, i = slot / (uint32_t) R.fac_k, c = slot - i * (uint32_t) R.fac_k;
-        cf[x] = __ldg(R.fac_coef + slot);
-        r[x] = reinterpret_cast<const float4*>(R.fac_q + (int64_t) (R.fac_ht ? 2 * i + (c & 1u) : i) * R.rec_ld);
+      if (fc[x]) {                    // {coefficient, shared-row index} written by the step kernel
+        const float2 cq = __ldg(reinterpret_cast<const float2*>(R.fac_coef) + (rid - R.fac_first));
+        cf[x] = cq.x;
+        r[x] = reinterpret_cast<const float4*>(R.fac_q + (int64_t) __float_as_uint(cq.y) * R.rec_ld);
       } else r[x] = reinterpret_cast<const float4*>(R.rec + (int64_t) rid * R.rec_ld);
     }
     float4 a[CPL][J];
@@ -492,7 +492,7 @@ __device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTabl
     if (c >= nch) continue;
     float4 w = wi[c], m = m4[c], v = v4[c];
     adam_chunk(w, m, v, scale4(scale, g[u]), p.beta1, p.beta2, lr_t, p.eps, p.opt);
-    mask_tail(w, m, v, c, T.cols);
+    if (T.cols & 3) mask_tail(w, m, v, c, T.cols);
     m4[c] = m; v4[c] = v;
     if (T.n_out == 0) w4[c] = w;
     else for (int j = 0; j < T.n_out; ++j) reinterpret_cast<float4*>(T.w_outs[j] + row * (int64_t) T.ld)[c] = w;   // all-gather by stores
@@ -527,7 +527,7 @@ __device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTabl
 // MODE 0: fused step.  MODE 3: data-parallel gradient half (row sum -> every T.peer destination, tables untouched).
 // MODE 4: data-parallel apply half (gradient = sum of the T.peer rows, no records).
 template <int CPL, int MODE>
-__global__ void __launch_bounds__(64) k_update_fast(const UpdateParams p) {
+__global__ void __launch_bounds__(64, CPL <= 2 ? 16 : 1) k_update_fast(const UpdateParams p) {
   const int lane = threadIdx.x & 31;
   const int64_t gw = (int64_t) blockIdx.x * 2 + (threadIdx.x >> 5);
   if (gw >= p.total_rows) return;

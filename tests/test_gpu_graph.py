@@ -123,3 +123,22 @@ def test_step_graph_device_batches_and_sgd():
         got = float(G.launch(Xd[i], i, next_triples=Xd[i + 1] if i + 1 < steps else None).item())
         assert got == want, (i, got, want)
     _assert_same(_state(plain), _state(gr), "sgd")
+
+
+def test_graph_and_lookahead_calls_interleaved():
+    """bench.py's order: look-ahead calls, graph launches, look-ahead calls again, each leaving a grouped batch
+    behind that the next kind of call does not take up."""
+    case = CASES[1]
+    B = 128
+    Xd = [x.cuda() for x in _batches(9, B)]
+    plain, mix = _engine(case), _engine(case)
+    G = mix.step_graph(B, 7)
+    for i in range(9):
+        want = float(plain.train_step(Xd[i], 7, i).item())
+        nxt = Xd[i + 1] if i + 1 < 9 else None
+        if (i // 3) % 2 == 0:
+            got = float(mix.train_step(Xd[i], 7, i, next_triples=nxt).item())
+        else:
+            got = float(G.launch(Xd[i], i, next_triples=nxt).item())
+        assert got == want, (i, got, want)
+    _assert_same(_state(plain), _state(mix), "interleaved")
