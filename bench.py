@@ -218,12 +218,14 @@ def run_ours(args, rank, world, device):
     def one_step(batch, nxt=None):
         """One step through the plain C-ABI call; nxt = the following batch (look-ahead grouping, single GPU)."""
         if world > 1:
-            eng.train_step_dp(batch, seed, step_no[0], B * world, rank * B, loss_out=loss_dev)
+            eng.train_step_dp(batch, seed, step_no[0], B * world, rank * B, loss_out=loss_dev, next_triples=nxt)
         else:
             eng.train_step(batch, seed, step_no[0], is_train=True, loss_out=loss_dev, next_triples=nxt)
         step_no[0] += 1
 
-    graph = eng.step_graph(B, seed) if world == 1 and os.environ.get("KGE_BENCH_GRAPH", "1") != "0" else None
+    graph = None
+    if os.environ.get("KGE_BENCH_GRAPH", "1") != "0":
+        graph = eng.step_graph(B, seed) if world == 1 else eng.step_graph_dp(B, seed, B * world, rank * B)
 
     def graph_step(batch, nxt, host_loss=None):
         """The same step through the captured graph (kge_step_graph): batch / nxt from device or pinned host memory."""
@@ -286,7 +288,7 @@ def run_ours(args, rank, world, device):
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        if world > 1:
+        if graph is None and world > 1:
             stage.copy_(host_batches[i % n_batches], non_blocking=True)
             one_step(stage)
             loss_host.copy_(loss_dev, non_blocking=True)
@@ -299,7 +301,7 @@ def run_ours(args, rank, world, device):
     barrier()
     ms_e2e = (time.perf_counter() - t0) * 1e3
     ms_e2e_plain = None
-    if graph is not None:       # the same through kge_train_step_host (no graph, no look-ahead), for comparison
+    if graph is not None and world == 1:       # the same through kge_train_step_host (no graph, no look-ahead), for comparison
         barrier()
         t0 = time.perf_counter()
         for i in range(args.steps):
@@ -318,7 +320,7 @@ def run_ours(args, rank, world, device):
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        if world > 1:
+        if graph is None and world > 1:
             stage.copy_(host_batches[i % n_batches], non_blocking=True)
             one_step(stage)
             loss2[i & 1].copy_(loss_dev, non_blocking=True)
@@ -738,8 +740,9 @@ def main():
         "exchange": (getattr(r["eng"], "_dp_kind", None) or "none") if world > 1 else "none",
         "clocks": r["clocks"],
         "value_steady_state_l2_warm": r["triples"] / (r["ms_warm"] * 1e-3),
-        "step_api": ("kge_step_graph_launch (captured CUDA graph, next batch grouped under the step)" if r["graph"] else
-                     "kge_train_step_dp" if world > 1 else "kge_train_step_next"),
+        "step_api": (("kge_step_graph_launch_dp" if world > 1 else "kge_step_graph_launch") +
+                     " (captured CUDA graph, next batch grouped under the step)" if r["graph"] else
+                     "kge_train_step_dp_next" if world > 1 else "kge_train_step_next"),
         "value_plain_calls": r["triples"] / (r["ms_cold_plain"] * 1e-3),
         "value_plain_calls_note": "same kernels through kge_train_step_next: ~20 launches / event calls per step issued by the host",
         "e2e_plain_calls": (r["triples"] / (r["ms_e2e_plain"] * 1e-3)) if r["ms_e2e_plain"] else None,

@@ -319,6 +319,25 @@ int kge_train_step_dp(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*,
                       kge_grads* push, const kge_grads* slots, const kge_peer_flags*, uint32_t epoch,
                       float* loss_out, void* ws, size_t ws_bytes, void* stream);
 
+/* kge_train_step_dp with the look-ahead batch of kge_train_step_next: next_triples = this rank's share of the
+ * NEXT step's positives (same B, same i_base), grouped while this step and its exchange run. */
+int kge_train_step_dp_next(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const kge_dp*,
+                           const void* triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
+                           kge_grads* push, const kge_grads* slots, const kge_peer_flags*, uint32_t epoch,
+                           float* loss_out, const void* next_triples, uint64_t next_step, void* ws, size_t ws_bytes,
+                           void* stream);
+/* The data-parallel step as a captured graph (kge_step_graph above): push2 / slots2 = the kge_grads of the two
+ * staging parities the caller alternates between, kge_dp / flags as for kge_train_step_dp.  Per launch the
+ * caller passes the barrier epoch (strictly increasing by 2, the graph's barriers use epoch and epoch + 1) and
+ * the staging parity of this step.  Every rank launches the same sequence. */
+int kge_step_graph_create_dp(kge_ctx*, const kge_cfg*, const kge_tables*, const kge_sampler*, const kge_dp*,
+                             const kge_grads* push2, const kge_grads* slots2, const kge_peer_flags*, void* dev_triples,
+                             void* dev_triples_next, int64_t B, uint64_t seed, float* dev_loss, void* ws,
+                             size_t ws_bytes, kge_step_graph** out);
+int kge_step_graph_launch_dp(kge_step_graph*, kge_tables*, const void* triples, uint64_t step, uint64_t adam_t,
+                             uint32_t epoch, int staging_parity, const void* next_triples, uint64_t next_step,
+                             float* host_loss_out, void* stream);
+
 int kge_train_grad(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const kge_dp*,
                    const void* triples, int64_t B, uint64_t seed, uint64_t step,
                    const int64_t* neg_override, kge_grads* out, float* scal_out /* [8] device */,

@@ -76,20 +76,31 @@ class StepGraph:
     host (pinned) or device memory; with `next_triples` the following batch is staged and grouped under this step,
     and the launch that trains on it (same `next_step`) passes no data at all."""
 
-    def __init__(self, eng, B, seed, lookahead=True):
+    def __init__(self, eng, B, seed, lookahead=True, dp=None):
         if eng.lazy:
             raise RuntimeError("step graphs cover dense tables (not row-lazy)")
-        self.eng, self.B, self.seed = eng, int(B), int(seed)
+        self.eng, self.B, self.seed, self.dp = eng, int(B), int(seed), dp
         dt = torch.int64 if eng.cfg.id_dtype == 1 else torch.int32
         self.stage = [torch.empty((B, 3), dtype=dt, device=eng.device) for _ in range(2 if lookahead else 1)]
         self.loss = torch.zeros(1, dtype=torch.float32, device=eng.device)
         self.ws = torch.empty(eng._workspace(B, 0).numel(), dtype=torch.uint8, device=eng.device)   # the graph owns its workspace
         self.T = eng._tables(with_opt=True)
         self.h = C.c_void_p()
-        L.check(L.load().kge_step_graph_create(eng.ctx, C.byref(eng.cfg), C.byref(self.T), C.byref(eng.sampler),
-                                               _ptr(self.stage[0]), _ptr(self.stage[1]) if lookahead else C.c_void_p(0),
-                                               self.B, self.seed, _ptr(self.loss), _ptr(self.ws), self.ws.numel(),
-                                               C.byref(self.h)))
+        nxt = _ptr(self.stage[1]) if lookahead else C.c_void_p(0)
+        if dp is None:
+            L.check(L.load().kge_step_graph_create(eng.ctx, C.byref(eng.cfg), C.byref(self.T), C.byref(eng.sampler),
+                                                   _ptr(self.stage[0]), nxt, self.B, self.seed, _ptr(self.loss),
+                                                   _ptr(self.ws), self.ws.numel(), C.byref(self.h)))
+        else:
+            from . import dp as _dp
+            rank, world_size = _dp.world() if getattr(eng, "_dp_world", None) is None else eng._dp_world
+            dpd = L.Dp(world=world_size, rank=rank, B_global=dp[0], i_base=dp[1])
+            push = (L.Grads * 2)(eng._peer.push(0), eng._peer.push(1))
+            slots = (L.Grads * 2)(eng._peer.slots(0), eng._peer.slots(1))
+            L.check(L.load().kge_step_graph_create_dp(eng.ctx, C.byref(eng.cfg), C.byref(self.T), C.byref(eng.sampler),
+                                                      C.byref(dpd), push, slots, C.byref(eng._peer.peer_flags()),
+                                                      _ptr(self.stage[0]), nxt, self.B, self.seed, _ptr(self.loss),
+                                                      _ptr(self.ws), self.ws.numel(), C.byref(self.h)))
 
     def launch(self, triples, step, next_triples=None, next_step=None, host_loss=None):
         """triples / next_triples: contiguous (B, 3) id tensors on the host (pinned for an asynchronous copy) or
@@ -99,12 +110,18 @@ class StepGraph:
         eng.adam_t += 1
         T = eng._tables(with_opt=True)
         eng._lazy_dirty = False
-        L.check(L.load().kge_step_graph_launch(self.h, C.byref(T), C.c_void_p(triples.data_ptr()) if triples is not None else C.c_void_p(0),
-                                               step, eng.adam_t,
-                                               C.c_void_p(next_triples.data_ptr()) if next_triples is not None else C.c_void_p(0),
-                                               (step + 1 if next_step is None else next_step),
-                                               C.c_void_p(host_loss.data_ptr()) if host_loss is not None else C.c_void_p(0),
-                                               _stream()))
+        a_tr = C.c_void_p(triples.data_ptr()) if triples is not None else C.c_void_p(0)
+        a_nx = C.c_void_p(next_triples.data_ptr()) if next_triples is not None else C.c_void_p(0)
+        a_hl = C.c_void_p(host_loss.data_ptr()) if host_loss is not None else C.c_void_p(0)
+        ns = step + 1 if next_step is None else next_step
+        if self.dp is None:
+            L.check(L.load().kge_step_graph_launch(self.h, C.byref(T), a_tr, step, eng.adam_t, a_nx, ns, a_hl, _stream()))
+        else:                       # the engine owns the exchange's step parity and barrier epoch (shared with train_step_dp)
+            par = eng._dp_steps & 1
+            eng._dp_steps += 1
+            eng._dp_epoch = getattr(eng, "_dp_epoch", 0) + 2
+            L.check(L.load().kge_step_graph_launch_dp(self.h, C.byref(T), a_tr, step, eng.adam_t, eng._dp_epoch - 1, par,
+                                                      a_nx, ns, a_hl, _stream()))
         eng._sync_shadow(T)
         return self.loss
 
@@ -383,8 +400,8 @@ class Engine:
         self._sync_shadow(T)
         return loss_out
 
-    def train_step_dp(self, triples_local, seed, step, B_global, i_base, loss_out=None, neg_override=None, group=None):
-        """One data-parallel step; every rank of the process group must call it."""
+    def _dp_setup(self, group=None):
+        """First data-parallel call: pick the exchange and set up its peer memory (collective)."""
         from . import dp as _dp
         rank, world_size = _dp.world()
         if getattr(self, "_dp_kind", None) is None:
@@ -403,6 +420,21 @@ class Engine:
                     self._peer.barrier()
             if self._dp_kind == "nccl":
                 self._gbuf = self.grad_buffer()
+        return rank, world_size
+
+    def step_graph_dp(self, B, seed, B_global, i_base, group=None, lookahead=True):
+        """The data-parallel step (kge_train_step_dp_next) captured as a CUDA graph; None when the exchange is not
+        carried by peer memory (NCCL all-reduce path: the collective is not capturable here)."""
+        self._dp_setup(group)
+        if self._dp_kind not in ("peer", "owner"):
+            return None
+        return StepGraph(self, B, seed, lookahead, dp=(B_global, i_base))
+
+    def train_step_dp(self, triples_local, seed, step, B_global, i_base, loss_out=None, neg_override=None, group=None,
+                      next_triples=None, next_step=None):
+        """One data-parallel step; every rank of the process group must call it.  next_triples: this rank's
+        share of the following step's batch (look-ahead grouping, kge_train_step_dp_next)."""
+        rank, world_size = self._dp_setup(group)
         if self._dp_kind in ("peer", "owner") and neg_override is None and os.environ.get("KGE_DP_ONE_CALL", "1") != "0":
             # grad -> barrier kernel -> apply -> barrier kernel enqueued by ONE library call (kge_train_step_dp)
             par = self._dp_steps & 1
@@ -416,11 +448,17 @@ class Engine:
             self.adam_t += 1
             T = self._tables(with_opt=True)
             self._dp_epoch = getattr(self, "_dp_epoch", 0) + 2
-            L.check(L.load().kge_train_step_dp(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler), C.byref(dpd),
-                                               _ptr(X), B, seed, step, self.adam_t, C.byref(self._peer.push(par)),
-                                               C.byref(self._peer.slots(par)), C.byref(self._peer.peer_flags()),
-                                               self._dp_epoch - 1, _ptr(loss_out), _ptr(ws), ws.numel(), _stream()))
+            Xn = self._ids(next_triples) if next_triples is not None else None
+            if Xn is not None and Xn.shape[0] != B:
+                Xn = None
+            L.check(L.load().kge_train_step_dp_next(self.ctx, C.byref(self.cfg), C.byref(T), C.byref(self.sampler), C.byref(dpd),
+                                                    _ptr(X), B, seed, step, self.adam_t, C.byref(self._peer.push(par)),
+                                                    C.byref(self._peer.slots(par)), C.byref(self._peer.peer_flags()),
+                                                    self._dp_epoch - 1, _ptr(loss_out), _ptr(Xn),
+                                                    step + 1 if next_step is None else next_step, _ptr(ws), ws.numel(),
+                                                    _stream()))
             self._sync_shadow(T)
+            self._keep_next = Xn
             return loss_out
         if self._dp_kind == "peer":
             # gradient kernels store into every rank's staging slot; one barrier; sum of the slots

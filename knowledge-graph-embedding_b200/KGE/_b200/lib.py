@@ -87,7 +87,8 @@ SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destr
            "kge_peer_barrier", "kge_train_step_dp", "kge_rank_lp_static",
            "kge_filter_index_bytes", "kge_filter_index_build", "kge_filter_lookup",
            "kge_train_step_next", "kge_train_step_host_next",
-           "kge_step_graph_create", "kge_step_graph_launch", "kge_step_graph_destroy"]
+           "kge_step_graph_create", "kge_step_graph_launch", "kge_step_graph_destroy",
+           "kge_train_step_dp_next", "kge_step_graph_create_dp", "kge_step_graph_launch_dp"]
 RANK_STATIC_BYTES = 4 << 20
 
 _LIB = None
@@ -152,6 +153,13 @@ def load():
     L.kge_train_step_dp.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Dp), vp, i64,
                                     u64, u64, u64, C.POINTER(Grads), C.POINTER(Grads), C.POINTER(PeerFlags), C.c_uint32,
                                     vp, vp, C.c_size_t, vp]
+    L.kge_train_step_dp_next.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Dp), vp, i64,
+                                         u64, u64, u64, C.POINTER(Grads), C.POINTER(Grads), C.POINTER(PeerFlags), C.c_uint32,
+                                         vp, vp, u64, vp, C.c_size_t, vp]
+    L.kge_step_graph_create_dp.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Dp),
+                                           C.POINTER(Grads), C.POINTER(Grads), C.POINTER(PeerFlags), vp, vp, i64, u64, vp, vp,
+                                           C.c_size_t, C.POINTER(vp)]
+    L.kge_step_graph_launch_dp.argtypes = [vp, C.POINTER(Tables), vp, u64, u64, C.c_uint32, i32, vp, u64, vp, vp]
     L.kge_flush_rows.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), vp]
     L.kge_set_option.argtypes = [vp, i32, i32]
     L.kge_profile_begin.argtypes = [vp, i32]

@@ -1280,9 +1280,10 @@ extern "C" int kge_shard_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
 // ---- cross-GPU barrier over peer memory + the one-call data-parallel step -----------------------
 namespace kge {
 struct PeerFlagsDev { int world, rank; uint32_t* flags[KGE_MAX_PEERS]; };
-__global__ void k_peer_barrier(PeerFlagsDev f, uint32_t epoch) {
+__global__ void k_peer_barrier(PeerFlagsDev f, uint32_t epoch, const uint32_t* epoch_dyn) {
   const int j = threadIdx.x;
   if (j >= f.world) return;
+  if (epoch_dyn) epoch += *epoch_dyn;                            // captured step graph: base epoch of this launch (DynScal)
   __threadfence_system();                                        // this stream's earlier stores first
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f.flags[j] + f.rank), "r"(epoch) : "memory");
   const uint32_t* mine = f.flags[f.rank] + j;
@@ -1310,22 +1311,24 @@ extern "C" int kge_peer_barrier(kge_ctx* ctx_, const kge_peer_flags* pf, uint32_
     f.flags[j] = pf->flags[j];
     KGE_REQUIRE(j >= pf->world || pf->flags[j], KGE_EINVAL, "kge_peer_flags.flags[%d] is NULL", j);
   }
-  k_peer_barrier<<<1, 32, 0, (cudaStream_t) stream>>>(f, epoch);
+  auto* c = reinterpret_cast<kge_ctx_impl*>(ctx_);
+  k_peer_barrier<<<1, 32, 0, (cudaStream_t) stream>>>(f, epoch, c->capturing ? &c->dyn->epoch : nullptr);
   KGE_CUDA_OK(cudaGetLastError());
   return KGE_OK;
 }
 
-extern "C" int kge_train_step_dp(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
-                                 const kge_dp* dp, const void* triples, int64_t B, uint64_t seed, uint64_t step,
-                                 uint64_t adam_t, kge_grads* push, const kge_grads* slots, const kge_peer_flags* pf,
-                                 uint32_t epoch, float* loss_out, void* ws, size_t ws_bytes, void* stream) {
-  KGE_REQUIRE(push && slots && push->n_peers > 0 && slots->n_peers > 0, KGE_EINVAL,
-              "kge_train_step_dp needs the peer-staging form of kge_grads");
+extern "C" int kge_train_step_dp_next(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                                      const kge_dp* dp, const void* triples, int64_t B, uint64_t seed, uint64_t step,
+                                      uint64_t adam_t, kge_grads* push, const kge_grads* slots, const kge_peer_flags* pf,
+                                      uint32_t epoch, float* loss_out, const void* next_triples, uint64_t next_step, void* ws,
+                                      size_t ws_bytes, void* stream) {
+  KGE_REQUIRE(dp && push && slots && push->n_peers > 0 && slots->n_peers > 0, KGE_EINVAL,
+              "kge_train_step_dp needs kge_dp and the peer-staging form of kge_grads");
   KGE_REQUIRE(pf && pf->rank >= 0 && pf->rank < KGE_MAX_PEERS && pf->flags[pf->rank], KGE_EINVAL, "bad kge_peer_flags");
   auto* c = reinterpret_cast<kge_ctx_impl*>(ctx);
-  if (int rc = kge_train_grad(ctx, cfg, tables, smp, dp, triples, B, seed, step, nullptr, push, nullptr, nullptr, ws,
-                              ws_bytes, stream)) return rc;
-  const int slot = c ? c->prof_open : -1;           // the step's profile slot (the halves share it)
+  if (int rc = train_impl(ctx, cfg, tables, smp, dp, triples, B, seed, step, 1, nullptr, 1, push, nullptr, nullptr, nullptr, ws,
+                          ws_bytes, stream, nullptr, 0, next_triples, next_step)) return rc;
+  const int slot = (c && !c->capturing) ? c->prof_open : -1;           // the step's profile slot (the halves share it)
   auto mark = [&](int idx) { if (slot >= 0) cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + idx], (cudaStream_t) stream); };
   mark(2 * 9);
   if (int rc = kge_peer_barrier(ctx, pf, epoch, stream)) return rc;
@@ -1335,6 +1338,13 @@ extern "C" int kge_train_step_dp(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* t
   sl.abort_word = pf->flags[pf->rank] + KGE_MAX_PEERS;
   if (int rc = kge_train_apply(ctx, cfg, tables, &sl, nullptr, B, adam_t, loss_out, ws, ws_bytes, stream)) return rc;
   return kge_peer_barrier(ctx, pf, epoch + 1, stream);
+}
+extern "C" int kge_train_step_dp(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
+                                 const kge_dp* dp, const void* triples, int64_t B, uint64_t seed, uint64_t step,
+                                 uint64_t adam_t, kge_grads* push, const kge_grads* slots, const kge_peer_flags* pf,
+                                 uint32_t epoch, float* loss_out, void* ws, size_t ws_bytes, void* stream) {
+  return kge_train_step_dp_next(ctx, cfg, tables, smp, dp, triples, B, seed, step, adam_t, push, slots, pf, epoch, loss_out,
+                                nullptr, 0, ws, ws_bytes, stream);
 }
 
 // ---- a training step captured once as a CUDA graph and replayed (kge_abi.h: kge_step_graph) -----------
@@ -1364,12 +1374,18 @@ struct kge_step_graph {
                              // inside a capture cannot be waited on by ordinary calls afterwards)
   // variant key: bit 0 shadow table valid, bit 1 this batch was grouped by the previous launch, bit 2 this launch groups
   // the next batch, bit 3 staging parity of this batch
-  kge::GraphVariant var[16];
+  kge::GraphVariant var[32];
+  // data-parallel form (kge_step_graph_create_dp): the captured step is kge_train_step_dp_next
+  bool dp_mode;
+  kge_dp dp;
+  kge_grads push[2], slots[2];   // by staging parity of the exchange (bit 4 of the variant key)
+  kge_peer_flags pf;
   int parity;                // staging buffer the NEXT ungrouped batch goes to
   bool next_grouped;         // the previous launch grouped a batch (into stage[parity])
   uint64_t next_step;
 };
 
+static void P_fix_ibase(Prefetched& P, int64_t i_base) { if (P.valid) P.i_base = i_base; }
 static int graph_capture(kge_step_graph* g, int key) {
   kge_ctx_impl* ctx = g->ctx;
   kge::GraphVariant& V = g->var[key];
@@ -1394,9 +1410,17 @@ static int graph_capture(kge_step_graph* g, int key) {
   KGE_CUDA_OK(cudaStreamBeginCapture(g->cap, cudaStreamCaptureModeRelaxed));
   ctx->capturing = 1;
   k_set_dyn<<<1, 1, 0, g->cap>>>(ctx->dyn, 0ull, 0ull, 0.f, 0u);
-  int rc = train_impl(reinterpret_cast<kge_ctx*>(ctx), &g->cfg, &T, g->has_smp ? &g->smp : nullptr, nullptr, g->stage[par], g->B,
-                      g->seed, 0, 1, nullptr, 1, nullptr, nullptr, g->dev_loss, nullptr, g->ws, g->ws_bytes, g->cap, nullptr, 0,
-                      (key & 4) ? g->stage[1 - par] : nullptr, 0);
+  int rc;
+  if (g->dp_mode) {
+    const int sp = (key >> 4) & 1;
+    P_fix_ibase(ctx->pre, g->dp.i_base);
+    rc = kge_train_step_dp_next(reinterpret_cast<kge_ctx*>(ctx), &g->cfg, &T, g->has_smp ? &g->smp : nullptr, &g->dp, g->stage[par],
+                                g->B, g->seed, 0, 1, &g->push[sp], &g->slots[sp], &g->pf, 0, g->dev_loss,
+                                (key & 4) ? g->stage[1 - par] : nullptr, 0, g->ws, g->ws_bytes, g->cap);
+  } else
+    rc = train_impl(reinterpret_cast<kge_ctx*>(ctx), &g->cfg, &T, g->has_smp ? &g->smp : nullptr, nullptr, g->stage[par], g->B,
+                    g->seed, 0, 1, nullptr, 1, nullptr, nullptr, g->dev_loss, nullptr, g->ws, g->ws_bytes, g->cap, nullptr, 0,
+                    (key & 4) ? g->stage[1 - par] : nullptr, 0);
   ctx->capturing = 0;
   cudaGraph_t graph = nullptr;
   cudaError_t e = cudaStreamEndCapture(g->cap, &graph);
@@ -1426,7 +1450,7 @@ extern "C" int kge_step_graph_create(kge_ctx* ctx_, const kge_cfg* cfg, const kg
   if (smp) g->smp = *smp;
   g->stage[0] = dev_triples; g->stage[1] = dev_triples_next;
   g->B = B; g->seed = seed; g->dev_loss = dev_loss; g->ws = ws; g->ws_bytes = ws_bytes;
-  g->parity = 0; g->next_grouped = false; g->next_step = 0;
+  g->parity = 0; g->next_grouped = false; g->next_step = 0; g->dp_mode = false;
   if (cudaStreamCreateWithFlags(&g->cap, cudaStreamNonBlocking) != cudaSuccess) { delete g; set_error("stream create failed"); return KGE_ECUDA; }
   for (int j = 0; j < 6; ++j)
     if (cudaEventCreateWithFlags(&g->ev[j], cudaEventDisableTiming) != cudaSuccess) { set_error("event create failed"); return KGE_ECUDA; }
@@ -1434,8 +1458,34 @@ extern "C" int kge_step_graph_create(kge_ctx* ctx_, const kge_cfg* cfg, const kg
   return KGE_OK;
 }
 
+extern "C" int kge_step_graph_create_dp(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tables, const kge_sampler* smp,
+                                        const kge_dp* dp, const kge_grads* push2, const kge_grads* slots2, const kge_peer_flags* pf,
+                                        void* dev_triples, void* dev_triples_next, int64_t B, uint64_t seed, float* dev_loss,
+                                        void* ws, size_t ws_bytes, kge_step_graph** out) {
+  KGE_REQUIRE(dp && push2 && slots2 && pf, KGE_EINVAL, "dp / push / slots / flags is NULL");
+  KGE_REQUIRE(push2[0].n_peers > 0 && slots2[0].n_peers > 0, KGE_EINVAL, "the data-parallel step graph needs the peer-staging form of kge_grads");
+  if (int rc = kge_step_graph_create(ctx_, cfg, tables, smp, dev_triples, dev_triples_next, B, seed, dev_loss, ws, ws_bytes, out)) return rc;
+  kge_step_graph* g = *out;
+  g->dp_mode = true; g->dp = *dp; g->pf = *pf;
+  for (int j = 0; j < 2; ++j) { g->push[j] = push2[j]; g->slots[j] = slots2[j]; }
+  return KGE_OK;
+}
+
+static int graph_launch(kge_step_graph* g, kge_tables* tables, const void* triples, uint64_t step, uint64_t adam_t, uint32_t epoch,
+                        int staging_parity, const void* next_triples, uint64_t next_step, float* host_loss_out, void* stream);
 extern "C" int kge_step_graph_launch(kge_step_graph* g, kge_tables* tables, const void* triples, uint64_t step, uint64_t adam_t,
                                      const void* next_triples, uint64_t next_step, float* host_loss_out, void* stream) {
+  KGE_REQUIRE(g && !g->dp_mode, KGE_EINVAL, "kge_step_graph_launch: not a single-GPU step graph");
+  return graph_launch(g, tables, triples, step, adam_t, 0, 0, next_triples, next_step, host_loss_out, stream);
+}
+extern "C" int kge_step_graph_launch_dp(kge_step_graph* g, kge_tables* tables, const void* triples, uint64_t step, uint64_t adam_t,
+                                        uint32_t epoch, int staging_parity, const void* next_triples, uint64_t next_step,
+                                        float* host_loss_out, void* stream) {
+  KGE_REQUIRE(g && g->dp_mode, KGE_EINVAL, "kge_step_graph_launch_dp: not a data-parallel step graph");
+  return graph_launch(g, tables, triples, step, adam_t, epoch, staging_parity & 1, next_triples, next_step, host_loss_out, stream);
+}
+static int graph_launch(kge_step_graph* g, kge_tables* tables, const void* triples, uint64_t step, uint64_t adam_t, uint32_t epoch,
+                        int staging_parity, const void* next_triples, uint64_t next_step, float* host_loss_out, void* stream) {
   KGE_REQUIRE(g && tables && adam_t >= 1, KGE_EINVAL, "bad kge_step_graph_launch arguments");
   KGE_REQUIRE(!next_triples || g->stage[1], KGE_EINVAL, "the graph was created without a look-ahead staging buffer");
   cudaStream_t st = (cudaStream_t) stream;
@@ -1448,12 +1498,11 @@ extern "C" int kge_step_graph_launch(kge_step_graph* g, kge_tables* tables, cons
     KGE_CUDA_OK(cudaMemcpyAsync(g->stage[par], triples, bytes, cudaMemcpyDefault, st));
   }
   if (next_triples) KGE_CUDA_OK(cudaMemcpyAsync(g->stage[1 - par], next_triples, bytes, cudaMemcpyDefault, st));
-  const int key = (tables->wn_valid[KGE_T_ENT] ? 1 : 0) | (grouped ? 2 : 0) | (next_triples ? 4 : 0) | (par << 3);
+  const int key = (tables->wn_valid[KGE_T_ENT] ? 1 : 0) | (grouped ? 2 : 0) | (next_triples ? 4 : 0) | (par << 3) | (staging_parity << 4);
   kge::GraphVariant& V = g->var[key];
   if (!V.exec) { if (int rc = graph_capture(g, key)) return rc; }
   unsigned long long a0 = step, a1 = next_step;
   float lr_t = g->cfg.optimizer == KGE_OPTIM_ADAM ? adam_lr(g->cfg.lr, g->cfg.beta1, g->cfg.beta2, adam_t) : g->cfg.lr;
-  uint32_t epoch = 0;
   DynScal* dptr = g->ctx->dyn;
   void* args[5] = {&dptr, &a0, &a1, &lr_t, &epoch};
   cudaKernelNodeParams np = {};

@@ -32,15 +32,29 @@ def main():
     single = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)
     nccl = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)      # same steps over the NCCL all-reduce
     owner = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)     # owner-partitioned exchange
+    ahead = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)     # owner exchange + look-ahead grouping
+    graph = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)     # the same step as a captured graph
     ok = True
+    Xs = [np.stack([rng.integers(0, N, B), rng.integers(0, R, B), rng.integers(0, N, B)], 1) for _ in range(5)]
+    lo, hi = dp.batch_shard(B)
+    Xl = [torch.as_tensor(x[lo:hi]).to(dev) for x in Xs]
+    os.environ["KGE_DP_EXCHANGE"] = "owner"
+    G = graph.step_graph_dp(hi - lo, 11, B, lo)
+    os.environ.pop("KGE_DP_EXCHANGE")
+    ok &= G is not None
     for step in range(5):
-        X = np.stack([rng.integers(0, N, B), rng.integers(0, R, B), rng.integers(0, N, B)], 1)
-        lo, hi = dp.batch_shard(B)
+        X = Xs[step]
+        os.environ["KGE_DP_EXCHANGE"] = "owner"
+        nxt = Xl[step + 1] if step + 1 < 5 and step != 2 else None
+        la = ahead.train_step_dp(Xl[step], 11, step, B, lo, next_triples=nxt)
+        lg = G.launch(Xl[step], step, next_triples=nxt)
+        os.environ.pop("KGE_DP_EXCHANGE")
         os.environ["KGE_DP_EXCHANGE"] = "peer"
         lm = multi.train_step_dp(X[lo:hi], 11, step, B, lo)
         os.environ["KGE_DP_EXCHANGE"] = "owner"
         lo_ = owner.train_step_dp(X[lo:hi], 11, step, B, lo)
         ok &= float(lm.item()) == float(lo_.item())          # both sum the rank slots in rank order
+        ok &= float(la.item()) == float(lo_.item()) and float(lg.item()) == float(lo_.item())   # look-ahead / graph: same bits
         os.environ["KGE_DP_EXCHANGE"] = "nccl"
         ln = nccl.train_step_dp(X[lo:hi], 11, step, B, lo)
         os.environ.pop("KGE_DP_EXCHANGE")
@@ -59,11 +73,12 @@ def main():
         if world == 2:
             ok &= bool(torch.equal(mine, nccl.tab[s].storage))
         ok &= bool(torch.equal(mine, owner.tab[s].storage))   # owner-partitioned == store-to-all, any world size
+        ok &= bool(torch.equal(ahead.tab[s].storage, owner.tab[s].storage)) and bool(torch.equal(graph.tab[s].storage, owner.tab[s].storage))
         go = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(go, owner.tab[s].storage.contiguous())
         ok &= all(torch.equal(go[0], t) for t in go)
     if rank == 0:
-        print("exchange kinds:", multi._dp_kind, nccl._dp_kind, owner._dp_kind)
+        print("exchange kinds:", multi._dp_kind, nccl._dp_kind, owner._dp_kind, ahead._dp_kind, graph._dp_kind)
     # sharded evaluation: counts over this rank's entity slice, summed == one-GPU counts
     Q = np.stack([rng.integers(0, N, 300), rng.integers(0, R, 300), rng.integers(0, N, 300)], 1)
     posX = np.concatenate([Q, np.stack([rng.integers(0, N, 4000), rng.integers(0, R, 4000), rng.integers(0, N, 4000)], 1)])
