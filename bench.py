@@ -201,6 +201,7 @@ def run_ours(args, rank, world, device):
     W = WORKLOAD
     B, k_eff = W["B"], 2 * (W["k"] // 2)
     eng = make_engine(device)
+    eng.dp_w_private = world > 1 and os.environ.get("KGE_DP_W_PRIVATE", "1") != "0"   # only wn travels per step (kge_grads.w_private)
     train = zipf_triples(W["n_train"], W["n_ent"], W["n_rel"], 12345)
     # data-parallel (world > 1): one GLOBAL batch of world*B positives per step, identical on every
     # rank; rank r owns positives [r*B, (r+1)*B) (weak scaling: per-GPU batch fixed).  Gradients are
@@ -271,6 +272,28 @@ def run_ours(args, rank, world, device):
         one_step(dev_batches[i % n_batches], dev_batches[(i + 1) % n_batches])
     barrier()
     phases, n_calls = eng.profile_end()
+
+    # ---- the graph's own timeline: a second graph created with phase events inside (kge_step_graph_phases) ----
+    graph_phases = None
+    if graph is not None:
+        from KGE._b200 import lib as _L
+        eng.set_option(_L.OPT_GRAPH_PROFILE, 1)
+        gprof = eng.step_graph(B, seed) if world == 1 else eng.step_graph_dp(B, seed, B * world, rank * B)
+        eng.set_option(_L.OPT_GRAPH_PROFILE, 0)
+        acc, tot, n_gp = {}, 0.0, min(args.steps, 40)
+        for i in range(n_gp + 4):
+            flush.zero_()
+            gprof.launch(dev_batches[i % n_batches], step_no[0], next_triples=dev_batches[(i + 1) % n_batches])
+            step_no[0] += 1
+            ph, t_all = gprof.phases()
+            if i >= 4:
+                tot += t_all
+                for kk, v in ph.items():
+                    acc[kk] = acc.get(kk, 0.0) + v
+        graph_phases = {kk: round(v / n_gp, 5) for kk, v in acc.items() if v > 0}
+        graph_phases["first_to_last_node"] = round(tot / n_gp, 5)
+        del gprof
+        barrier()
 
     # ---- steady state (no flush): what a training loop sees, state is L2 resident ----
     barrier()
@@ -351,12 +374,13 @@ def run_ours(args, rank, world, device):
         need[0] = 1 if (clk.proc is not None and len(clk.rows) < 2) else 0
     clk.stop()
 
+    eng.dp_sync_weights()                 # w of the rows other ranks own (no-op unless dp_w_private)
     t = torch.tensor([ms_cold, ms_warm, ms_e2e, ms_e2e_lag], dtype=torch.float64, device=device)
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     ms_cold, ms_warm, ms_e2e, ms_e2e_lag = t.tolist()
     triples = world * B * (1 + k_eff) * args.steps
-    return {"eng": eng, "ms_cold_plain": ms_cold_plain, "ms_e2e_plain": ms_e2e_plain, "graph": graph is not None, "ms_cold": ms_cold, "ms_warm": ms_warm, "ms_e2e": ms_e2e, "ms_e2e_lag": ms_e2e_lag, "triples": triples,
+    return {"eng": eng, "graph_phases": graph_phases, "ms_cold_plain": ms_cold_plain, "ms_e2e_plain": ms_e2e_plain, "graph": graph is not None, "ms_cold": ms_cold, "ms_warm": ms_warm, "ms_e2e": ms_e2e, "ms_e2e_lag": ms_e2e_lag, "triples": triples,
             "phases": phases, "n_calls": n_calls, "n_prof": n_prof, "clocks": clk.summary(), "train": train,
             "loss": float(loss_host.item())}
 
@@ -738,11 +762,15 @@ def main():
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config,
         "exchange": (getattr(r["eng"], "_dp_kind", None) or "none") if world > 1 else "none",
+        "exchange_w_private": bool(world > 1 and getattr(getattr(r["eng"], "_peer", None), "w_private", False)),
+        "exchange_multicast": bool(world > 1 and getattr(getattr(getattr(r["eng"], "_peer", None), "ptabs", None), "mc_ptr", 0)),
         "clocks": r["clocks"],
         "value_steady_state_l2_warm": r["triples"] / (r["ms_warm"] * 1e-3),
         "step_api": (("kge_step_graph_launch_dp" if world > 1 else "kge_step_graph_launch") +
                      " (captured CUDA graph, next batch grouped under the step)" if r["graph"] else
                      "kge_train_step_dp_next" if world > 1 else "kge_train_step_next"),
+        "graph_phase_ms_per_step": r["graph_phases"],
+        "graph_phase_note": "events recorded BY a second, instrumented graph (kge_step_graph_phases); 'sort' is the NEXT batch's grouping chain, concurrent with step + update",
         "value_plain_calls": r["triples"] / (r["ms_cold_plain"] * 1e-3),
         "value_plain_calls_note": "same kernels through kge_train_step_next: ~20 launches / event calls per step issued by the host",
         "e2e_plain_calls": (r["triples"] / (r["ms_e2e_plain"] * 1e-3)) if r["ms_e2e_plain"] else None,

@@ -238,6 +238,10 @@ int kge_step_graph_create(kge_ctx*, const kge_cfg*, const kge_tables*, const kge
 int kge_step_graph_launch(kge_step_graph*, kge_tables*, const void* triples, uint64_t step, uint64_t adam_t,
                           const void* next_triples, uint64_t next_step, float* host_loss_out, void* stream);
 int kge_step_graph_destroy(kge_step_graph*);
+/* Phase times of the LAST launch of a graph created while KGE_OPT_GRAPH_PROFILE was 1 (the graph then records
+ * its own phase-boundary events: measuring, not for production): phase_ms[KGE_N_PHASES] as kge_profile_end,
+ * *total_ms = first to last node.  Synchronises the device. */
+int kge_step_graph_phases(kge_step_graph*, float* phase_ms, float* total_ms);
 
 /* Data-parallel form of kge_train_step (the reference is single-device): every
  * rank holds all tables and B of the step's B_global positives, [i_base, i_base + B).
@@ -295,6 +299,19 @@ typedef struct kge_grads {
    * When it reads KGE_PEER_DEAD the apply half leaves every table as it is (a peer never arrived: its
    * staging slots are stale) and loss_out = NaN; the host reads the word at its next sync and raises. */
   const uint32_t* abort_word;
+  /* Optional NVSwitch multicast (NVLS) addresses of the weight tables / the shadow table, i.e. one address
+   * whose stores land in the same place of EVERY rank's replica (CUDA multicast objects; torch symmetric
+   * memory's multicast_ptr).  When given, the owner's apply half writes each new row once with multimem.st
+   * instead of once per rank: outbound NVLink bytes of the all-gather drop from n_peers - 1 replicas to one.
+   * NULL = unicast stores through w_peer / wn_peer. */
+  float* w_mc[KGE_MAX_TABLES];
+  float* wn_mc;
+  /* Owner-partitioned apply with the shadow table in use: != 0 keeps the new w row at its owner and sends only
+   * wn = normalise(w) to the replicas — all a training step ever reads from another rank's rows (it gathers
+   * from wn, and the owner's update starts from wn as well): half the all-gather bytes.  The replicas' w of
+   * rows they do not own then go stale; the caller gathers w from the owners before anything reads it
+   * (evaluation, validation batches, checkpoints: KGE._b200.engine.Engine.dp_sync_weights). */
+  int32_t w_private;
 } kge_grads;
 /* Cross-GPU barrier over peer memory, enqueued on `stream` like a kernel (no host involvement):
  * flags[j] = rank j's flag array (uint32[KGE_MAX_PEERS + 1], zeroed once) as mapped HERE.  Every rank calls
@@ -451,8 +468,10 @@ int kge_flush_rows(kge_ctx*, const kge_cfg*, kge_tables*, void* stream);
  * k_shard_push delivers all rows (default 0: single-record rows are stored into the owner's inbox by
  * the step kernel itself).
  * KGE_OPT_RING_SLOTS: deepest per-warp ring (rows: 32, 16, 8, 4, or 0 = none) of negative rows the DistMult
- * step kernel stages through shared memory with TMA bulk copies (default 32). */
-enum { KGE_OPT_RADIX_SORT = 1, KGE_OPT_NO_SHADOW = 2, KGE_OPT_NO_FUSED_PUSH = 3, KGE_OPT_RING_SLOTS = 4 };
+ * step kernel stages through shared memory with TMA bulk copies (default 32).
+ * KGE_OPT_GRAPH_PROFILE: 1 = step graphs created from now on record phase-boundary events (kge_step_graph_phases). */
+enum { KGE_OPT_RADIX_SORT = 1, KGE_OPT_NO_SHADOW = 2, KGE_OPT_NO_FUSED_PUSH = 3, KGE_OPT_RING_SLOTS = 4,
+       KGE_OPT_GRAPH_PROFILE = 5 };
 int kge_set_option(kge_ctx*, int option, int value);
 
 /* Per-phase device timing (CUDA events recorded on the call's stream, read back only at

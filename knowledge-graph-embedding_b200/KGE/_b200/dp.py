@@ -102,7 +102,7 @@ class PeerTables:
                 self.off[(kind, s)] = (o, rows, ld)
                 o += (rows * ld + 63) // 64 * 64
         self.numel = o
-        self.buf, self.base_ptrs, self._keep = None, None, None
+        self.buf, self.base_ptrs, self._keep, self.mc_ptr = None, None, None, 0
 
     def view(self, kind, s):
         o, rows, ld = self.off[(kind, s)]
@@ -127,6 +127,13 @@ class PeerTables:
         hdl = sm.rendezvous(t.buf, group=group if group is not None else dist.group.WORLD)
         t.buf.zero_()
         t.base_ptrs = [int(p) for p in hdl.buffer_ptrs]
+        # NVSwitch multicast mapping of the same buffer (0 where NVLS is not available): one store, every replica
+        t.mc_ptr = 0
+        if os.environ.get("KGE_DP_MULTICAST", "1") != "0":
+            try:
+                t.mc_ptr = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            except Exception:                                       # noqa: BLE001
+                t.mc_ptr = 0
         t._keep = hdl
         return t
 
@@ -139,7 +146,7 @@ class PeerStaging:
     device in tests).  `push(parity)` / `slots(parity)` fill the `peer` fields of kge_grads for
     kge_train_grad / kge_train_apply (include/kge_abi.h)."""
 
-    def __init__(self, tables, world_size, rank, base_ptrs=None, barrier=None, keep=None, ptabs=None):
+    def __init__(self, tables, world_size, rank, base_ptrs=None, barrier=None, keep=None, ptabs=None, w_private=False):
         from . import lib as L
         if not (1 <= world_size <= L.KGE_MAX_PEERS):
             raise ValueError(f"peer exchange supports up to {L.KGE_MAX_PEERS} ranks")
@@ -159,6 +166,7 @@ class PeerStaging:
         self._cache = {}
         # owner-partitioned exchange: rank j owns rows [j * owner_rows[s], (j+1) * owner_rows[s]) of table s
         self.ptabs = ptabs
+        self.w_private = bool(w_private)      # kge_grads.w_private: only wn is sent to the replicas
         self.owner_rows = {s: -(-tables[s][0] // self.world) for s in tables}
 
     def numel(self):
@@ -205,12 +213,17 @@ class PeerStaging:
                 G.abort_word = self.base_ptrs[self.rank] + 4 * (2 * self.world * self.per + L.KGE_MAX_PEERS)
             if self.ptabs is not None:
                 G.owner_rank = self.rank
+                G.w_private = int(self.w_private)
                 for s in self.offsets:
                     G.owner_rows[s] = self.owner_rows[s]
                     for j in range(self.world):
                         G.w_peer[j][s] = self.ptabs.addr(j, "w", s)
                         if ("wn", s) in self.ptabs.off:
                             G.wn_peer[j] = self.ptabs.addr(j, "wn", s)
+                    if self.ptabs.mc_ptr and not push:
+                        G.w_mc[s] = self.ptabs.mc_ptr + 4 * self.ptabs.off[("w", s)][0]
+                        if ("wn", s) in self.ptabs.off:
+                            G.wn_mc = self.ptabs.mc_ptr + 4 * self.ptabs.off[("wn", s)][0]
             self._cache[key] = G
         return self._cache[key]
 
@@ -223,7 +236,7 @@ class PeerStaging:
         return self._grads(parity & 1, False)
 
     @classmethod
-    def symmetric(cls, tables, device, group=None, wn_slots=None):
+    def symmetric(cls, tables, device, group=None, wn_slots=None, w_private=False):
         """Staging in torch symmetric memory (CUDA VMM peer mappings over NVLink), or None when
         any rank cannot set it up (the caller then keeps the NCCL all-reduce).  wn_slots not None:
         owner-partitioned exchange — the weight tables get peer-mapped memory too (`ptabs`)."""
@@ -231,7 +244,7 @@ class PeerStaging:
         ok, st = 1, None
         try:
             import torch.distributed._symmetric_memory as sm
-            st = cls(tables, world_size, rank)
+            st = cls(tables, world_size, rank, w_private=w_private and bool(wn_slots))
             if wn_slots is not None:
                 st.ptabs = PeerTables.symmetric(tables, wn_slots, device, group)
             buf = sm.empty(st.numel(), dtype=torch.float32, device=device)
@@ -250,6 +263,19 @@ class PeerStaging:
             return None
         hdl.barrier()
         return st
+
+    def sync_weights(self, tabs, group=None):
+        """w_private: every owner broadcasts its rows of w of the shadow-carrying tables (collective)."""
+        if not (self.w_private and self.ptabs is not None):
+            return
+        for s, pt in tabs.items():
+            if ("wn", s) not in self.ptabs.off:
+                continue
+            n = self.owner_rows[s]
+            for j in range(self.world):
+                lo, hi = j * n, min((j + 1) * n, pt.rows)
+                if hi > lo:
+                    dist.broadcast(pt.storage[lo:hi], src=j, group=group)
 
 
 def exchange_kind(world_size, dense_regulariser=False):

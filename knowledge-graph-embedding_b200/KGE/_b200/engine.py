@@ -59,6 +59,9 @@ class PaddedTable:
 
     @property
     def view(self):
+        if self.owner is not None and getattr(self.owner, "_w_stale", False):
+            raise RuntimeError("data-parallel run with dp_w_private: call Engine.dp_sync_weights() on every rank before "
+                               "reading the weights")
         if self.last is not None and self.owner is not None:
             self.owner.flush()
         return self.storage[:, :self.cols].reshape(self.shape)
@@ -122,8 +125,16 @@ class StepGraph:
             eng._dp_epoch = getattr(eng, "_dp_epoch", 0) + 2
             L.check(L.load().kge_step_graph_launch_dp(self.h, C.byref(T), a_tr, step, eng.adam_t, eng._dp_epoch - 1, par,
                                                       a_nx, ns, a_hl, _stream()))
+            eng._w_stale = bool(getattr(eng._peer, "w_private", False))
         eng._sync_shadow(T)
         return self.loss
+
+    def phases(self):
+        """-> ({phase: ms}, total ms) of the last launch (graph created under set_option(OPT_GRAPH_PROFILE, 1))."""
+        ms = (C.c_float * L.N_PHASES)()
+        tot = C.c_float()
+        L.check(L.load().kge_step_graph_phases(self.h, ms, C.byref(tot)))
+        return {L.PHASES[i]: float(ms[i]) for i in range(L.N_PHASES)}, float(tot.value)
 
     def __del__(self):
         try:
@@ -148,6 +159,8 @@ class Engine:
             if k != "acc_init":
                 setattr(self.cfg, k, v)
         self.tab = {s: PaddedTable(v, self.device) for s, v in tables.items()}
+        for pt in self.tab.values():
+            pt.owner = self
         self.lazy = bool(lazy)
         self.lazy_t = 0
         self._lazy_dirty = False
@@ -203,6 +216,8 @@ class Engine:
 
     def flush(self):
         """Row-lazy tables: replay every row to the current step (kge_flush_rows); no-op otherwise."""
+        if getattr(self, "_w_stale", False):
+            raise RuntimeError("data-parallel run with dp_w_private: call Engine.dp_sync_weights() on every rank first")
         if not self.lazy or not self._lazy_dirty:
             return
         self._lazy_dirty = False
@@ -266,6 +281,8 @@ class Engine:
         unchanged until the call that trains on it) / next_step: the following batch, whose gradient records are
         grouped while this step runs (kge_train_step_next); the results do not depend on it."""
         X = self._ids(triples)
+        if not is_train:
+            self.flush()                    # (also refuses stale data-parallel replicas)
         if next_triples is not None and is_train and neg_override is None and not want_negatives and not self.lazy:
             B = X.shape[0]
             ws = self._workspace(B, 0)
@@ -412,7 +429,8 @@ class Engine:
                 wn_slots = None
                 if self._dp_kind == "owner":
                     wn_slots = [s for s, pt in self.tab.items() if pt.wn is not None]
-                self._peer = _dp.PeerStaging.symmetric(layout, self.device, group, wn_slots=wn_slots)
+                self._peer = _dp.PeerStaging.symmetric(layout, self.device, group, wn_slots=wn_slots,
+                                                       w_private=getattr(self, "dp_w_private", False))
                 if self._peer is None:
                     self._dp_kind = "nccl"
                 elif self._dp_kind == "owner":
@@ -421,6 +439,16 @@ class Engine:
             if self._dp_kind == "nccl":
                 self._gbuf = self.grad_buffer()
         return rank, world_size
+
+    def dp_sync_weights(self, group=None):
+        """Data-parallel runs with dp_w_private = True (set before the first data-parallel step): the new w rows
+        stay with their owners and only wn travels per step; this gathers w from the owners (collective: every rank
+        must call it) — before evaluation, validation batches, checkpoints or any read of the weights."""
+        peer = getattr(self, "_peer", None)
+        if peer is not None and getattr(self, "_w_stale", False):
+            torch.cuda.current_stream().synchronize()
+            peer.sync_weights(self.tab, group)
+            self._w_stale = False
 
     def step_graph_dp(self, B, seed, B_global, i_base, group=None, lookahead=True):
         """The data-parallel step (kge_train_step_dp_next) captured as a CUDA graph; None when the exchange is not
@@ -459,6 +487,7 @@ class Engine:
                                                     _stream()))
             self._sync_shadow(T)
             self._keep_next = Xn
+            self._w_stale = bool(getattr(self._peer, "w_private", False))
             return loss_out
         if self._dp_kind == "peer":
             # gradient kernels store into every rank's staging slot; one barrier; sum of the slots

@@ -17,6 +17,7 @@ OPT_RADIX_SORT = 1
 OPT_NO_SHADOW = 2
 OPT_NO_FUSED_PUSH = 3
 OPT_RING_SLOTS = 4
+OPT_GRAPH_PROFILE = 5
 N_PHASES = 10
 PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm", "rank_fix", "apply", "barrier"]
 PEER_DEAD = 0xdead
@@ -65,7 +66,8 @@ class Grads(C.Structure):
                 ("peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("peer_scal", C.c_void_p * KGE_MAX_PEERS),
                 ("owner_rank", C.c_int32), ("owner_rows", C.c_int32 * KGE_MAX_TABLES),
                 ("w_peer", (C.c_void_p * KGE_MAX_TABLES) * KGE_MAX_PEERS), ("wn_peer", C.c_void_p * KGE_MAX_PEERS),
-                ("abort_word", C.c_void_p)]
+                ("abort_word", C.c_void_p), ("w_mc", C.c_void_p * KGE_MAX_TABLES), ("wn_mc", C.c_void_p),
+                ("w_private", C.c_int32)]
 
 
 class PeerFlags(C.Structure):
@@ -88,7 +90,7 @@ SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destr
            "kge_filter_index_bytes", "kge_filter_index_build", "kge_filter_lookup",
            "kge_train_step_next", "kge_train_step_host_next",
            "kge_step_graph_create", "kge_step_graph_launch", "kge_step_graph_destroy",
-           "kge_train_step_dp_next", "kge_step_graph_create_dp", "kge_step_graph_launch_dp"]
+           "kge_train_step_dp_next", "kge_step_graph_create_dp", "kge_step_graph_launch_dp", "kge_step_graph_phases"]
 RANK_STATIC_BYTES = 4 << 20
 
 _LIB = None
@@ -131,6 +133,7 @@ def load():
                                         C.c_size_t, C.POINTER(vp)]
     L.kge_step_graph_launch.argtypes = [vp, C.POINTER(Tables), vp, u64, u64, vp, u64, vp, vp]
     L.kge_step_graph_destroy.argtypes = [vp]
+    L.kge_step_graph_phases.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     L.kge_train_grad.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Dp), vp, i64,
                                  u64, u64, vp, C.POINTER(Grads), vp, vp, vp, C.c_size_t, vp]
     L.kge_train_apply.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Grads), vp, i64, u64, vp, vp,

@@ -64,15 +64,19 @@ struct kge_ctx_impl {
   cudaStream_t pre_stream = nullptr;               // the next batch's grouping chain (kge_train_step_next)
   cudaEvent_t ev_pre_fork = nullptr, ev_pre_done = nullptr;
   Prefetched pre;
+  cudaEvent_t* gev = nullptr;     // capturing with phase events on (kge_step_graph, KGE_OPT_GRAPH_PROFILE): [2 * KGE_N_PHASES]
+  unsigned gev_mask = 0;
+  int opt_graph_profile = 0;
   DynScal* dyn = nullptr;         // device; used only while `capturing` (kge_step_graph_create)
   int capturing = 0;              // the call is being captured into a CUDA graph: per-step scalars come from `dyn`
 };
 // RAII marker: records the boundary events of one call when profiling is on
 struct PhaseTimer {
-  kge_ctx_impl* c; cudaStream_t st; int slot;
+  kge_ctx_impl* c; cudaStream_t st; int slot; bool g = false;
   // join: continue the slot the preceding gradient half opened (one data-parallel step = one call)
   PhaseTimer(kge_ctx_impl* c_, cudaStream_t s, bool join = false) : c(c_), st(s), slot(-1) {
-    if (!c->ev || c->capturing) return;
+    if (c->capturing) { g = c->gev != nullptr; return; }      // a captured step records into the graph's own events
+    if (!c->ev) return;
     if (join && c->prof_open >= 0) { slot = c->prof_open; c->prof_open = -1; return; }
     c->prof_open = -1;
     if (c->prof_n < c->prof_cap) { slot = c->prof_n++; c->ev_mask[slot] = 0; }
@@ -80,9 +84,13 @@ struct PhaseTimer {
   void keep_open() { if (slot >= 0) c->prof_open = slot; }
   void begin(int phase) { begin(phase, st); }
   void end(int phase) { end(phase, st); }
-  void begin(int phase, cudaStream_t s) { if (slot >= 0) cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + 2 * phase], s); }
+  void begin(int phase, cudaStream_t s) {
+    if (slot >= 0) cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + 2 * phase], s);
+    else if (g) cudaEventRecordWithFlags(c->gev[2 * phase], s, cudaEventRecordExternal);    // a real event-record node
+  }
   void end(int phase, cudaStream_t s) {
     if (slot >= 0) { cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + 2 * phase + 1], s); c->ev_mask[slot] |= 1u << phase; }
+    else if (g) { cudaEventRecordWithFlags(c->gev[2 * phase + 1], s, cudaEventRecordExternal); c->gev_mask |= 1u << phase; }
   }
 };
 

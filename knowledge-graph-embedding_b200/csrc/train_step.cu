@@ -791,7 +791,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     }
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
     U.n_peer = 0;
-    U.owner_rows = 0; U.row_lo = 0; U.n_out = 0;
+    U.owner_rows = 0; U.row_lo = 0; U.n_out = 0; U.w_mc = nullptr; U.wn_mc = nullptr; U.w_private = 0;
     if (grad_only) {
       if (grads_out->n_peers > 0) {
         U.n_peer = grads_out->n_peers;
@@ -1065,7 +1065,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     U.slot = s;
     U.fac_coef = nullptr; U.fac_q = nullptr; U.fac_first = 0; U.fac_k = 1; U.fac_ht = 0;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
-    U.owner_rows = 0; U.row_lo = 0; U.n_out = 0;
+    U.owner_rows = 0; U.row_lo = 0; U.n_out = 0; U.w_mc = nullptr; U.wn_mc = nullptr; U.w_private = 0;
     if (g->n_peers > 0) {
       U.n_peer = g->n_peers;
       for (int j = 0; j < U.n_peer; ++j) {
@@ -1089,6 +1089,11 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
       if (hi > U.rows) hi = U.rows;
       U.rows = hi > U.row_lo ? hi - U.row_lo : 0;
       U.n_out = g->n_peers;
+      U.w_private = g->w_private;
+      U.w_mc = g->w_mc[s];
+      U.wn_mc = (U.wn_out && g->w_mc[s]) ? g->wn_mc : nullptr;
+      KGE_REQUIRE(!(U.wn_out && U.w_mc) || U.wn_mc, KGE_EINVAL, "grads.w_mc is given but grads.wn_mc is missing");
+      KGE_REQUIRE((((uintptr_t) U.w_mc | (uintptr_t) U.wn_mc) & 15) == 0, KGE_EINVAL, "grads.w_mc / wn_mc not 16-byte aligned");
       for (int j = 0; j < U.n_out; ++j) {
         KGE_REQUIRE(g->w_peer[j][s] && ((uintptr_t) g->w_peer[j][s] & 15) == 0, KGE_EINVAL, "grads.w_peer[%d][%d] missing", j, s);
         U.w_outs[j] = g->w_peer[j][s];
@@ -1249,7 +1254,7 @@ extern "C" int kge_shard_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     U.fac_coef = nullptr; U.fac_q = nullptr; U.fac_first = 0; U.fac_k = 1; U.fac_ht = 0;
     U.dense_kind = DK_NONE; U.other_w = nullptr; U.other_ld = 0;
     U.n_peer = 1; U.peer[0] = g->dense[s];
-    U.owner_rows = 0; U.row_lo = 0; U.n_out = 0;
+    U.owner_rows = 0; U.row_lo = 0; U.n_out = 0; U.w_mc = nullptr; U.wn_mc = nullptr; U.w_private = 0;
     U.w_in = tables->t[s].w; U.wn_out = nullptr;
     up.total_rows += U.rows;
     max_ch = ((U.cols + 3) / 4 > max_ch) ? (U.cols + 3) / 4 : max_ch;
@@ -1329,7 +1334,10 @@ extern "C" int kge_train_step_dp_next(kge_ctx* ctx, const kge_cfg* cfg, kge_tabl
   if (int rc = train_impl(ctx, cfg, tables, smp, dp, triples, B, seed, step, 1, nullptr, 1, push, nullptr, nullptr, nullptr, ws,
                           ws_bytes, stream, nullptr, 0, next_triples, next_step)) return rc;
   const int slot = (c && !c->capturing) ? c->prof_open : -1;           // the step's profile slot (the halves share it)
-  auto mark = [&](int idx) { if (slot >= 0) cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + idx], (cudaStream_t) stream); };
+  auto mark = [&](int idx) {
+    if (slot >= 0) cudaEventRecord(c->ev[slot * 2 * KGE_N_PHASES + idx], (cudaStream_t) stream);
+    else if (c && c->capturing && c->gev) { cudaEventRecordWithFlags(c->gev[idx], (cudaStream_t) stream, cudaEventRecordExternal); c->gev_mask |= 1u << 9; }
+  };
   mark(2 * 9);
   if (int rc = kge_peer_barrier(ctx, pf, epoch, stream)) return rc;
   mark(2 * 9 + 1);
@@ -1355,6 +1363,7 @@ __global__ void k_set_dyn(DynScal* d, unsigned long long step, unsigned long lon
   d->step = step; d->step_next = step_next; d->lr_t = lr_t; d->epoch = epoch;
 }
 struct GraphVariant {
+  unsigned ev_mask = 0;          // phases whose events this variant records (KGE_OPT_GRAPH_PROFILE)
   cudaGraphExec_t exec = nullptr;
   cudaGraph_t graph = nullptr;
   cudaGraphNode_t set_node = nullptr;
@@ -1370,6 +1379,9 @@ struct kge_step_graph {
   int64_t B; uint64_t seed;
   float* dev_loss; void* ws; size_t ws_bytes;
   cudaStream_t cap;
+  cudaEvent_t gev[2 * KGE_N_PHASES + 2];   // phase boundaries recorded BY the graph (+ whole step), timing enabled; NULL = off
+  bool prof;
+  unsigned last_mask;
   cudaEvent_t ev[6];         // the context's fork / join events are replaced by these while capturing (an event recorded
                              // inside a capture cannot be waited on by ordinary calls afterwards)
   // variant key: bit 0 shadow table valid, bit 1 this batch was grouped by the previous launch, bit 2 this launch groups
@@ -1409,7 +1421,10 @@ static int graph_capture(kge_step_graph* g, int key) {
   } restore{slots, keep, ctx, &saved};
   KGE_CUDA_OK(cudaStreamBeginCapture(g->cap, cudaStreamCaptureModeRelaxed));
   ctx->capturing = 1;
+  ctx->gev = g->prof ? g->gev : nullptr;
+  ctx->gev_mask = 0;
   k_set_dyn<<<1, 1, 0, g->cap>>>(ctx->dyn, 0ull, 0ull, 0.f, 0u);
+  if (g->prof) cudaEventRecordWithFlags(g->gev[2 * KGE_N_PHASES], g->cap, cudaEventRecordExternal);
   int rc;
   if (g->dp_mode) {
     const int sp = (key >> 4) & 1;
@@ -1421,7 +1436,10 @@ static int graph_capture(kge_step_graph* g, int key) {
     rc = train_impl(reinterpret_cast<kge_ctx*>(ctx), &g->cfg, &T, g->has_smp ? &g->smp : nullptr, nullptr, g->stage[par], g->B,
                     g->seed, 0, 1, nullptr, 1, nullptr, nullptr, g->dev_loss, nullptr, g->ws, g->ws_bytes, g->cap, nullptr, 0,
                     (key & 4) ? g->stage[1 - par] : nullptr, 0);
+  if (g->prof) cudaEventRecordWithFlags(g->gev[2 * KGE_N_PHASES + 1], g->cap, cudaEventRecordExternal);
   ctx->capturing = 0;
+  ctx->gev = nullptr;
+  V.ev_mask = ctx->gev_mask;
   cudaGraph_t graph = nullptr;
   cudaError_t e = cudaStreamEndCapture(g->cap, &graph);
   if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
@@ -1454,6 +1472,11 @@ extern "C" int kge_step_graph_create(kge_ctx* ctx_, const kge_cfg* cfg, const kg
   if (cudaStreamCreateWithFlags(&g->cap, cudaStreamNonBlocking) != cudaSuccess) { delete g; set_error("stream create failed"); return KGE_ECUDA; }
   for (int j = 0; j < 6; ++j)
     if (cudaEventCreateWithFlags(&g->ev[j], cudaEventDisableTiming) != cudaSuccess) { set_error("event create failed"); return KGE_ECUDA; }
+  g->prof = ctx->opt_graph_profile != 0; g->last_mask = 0;
+  for (int j = 0; j < 2 * KGE_N_PHASES + 2; ++j) {
+    g->gev[j] = nullptr;
+    if (g->prof && cudaEventCreate(&g->gev[j]) != cudaSuccess) { set_error("event create failed"); return KGE_ECUDA; }
+  }
   *out = g;
   return KGE_OK;
 }
@@ -1512,9 +1535,22 @@ static int graph_launch(kge_step_graph* g, kge_tables* tables, const void* tripl
   KGE_CUDA_OK(cudaGraphLaunch(V.exec, st));
   if (host_loss_out) KGE_CUDA_OK(cudaMemcpyAsync(host_loss_out, g->dev_loss, sizeof(float), cudaMemcpyDeviceToHost, st));
   tables->wn_valid[KGE_T_ENT] = V.wn_valid_after;
+  g->last_mask = V.ev_mask;
   g->next_grouped = next_triples != nullptr;
   g->next_step = next_step;
   if (next_triples) g->parity = 1 - par;         // the grouped batch sits in the other buffer / set
+  return KGE_OK;
+}
+
+extern "C" int kge_step_graph_phases(kge_step_graph* g, float* phase_ms, float* total_ms) {
+  KGE_REQUIRE(g && phase_ms && total_ms, KGE_EINVAL, "bad kge_step_graph_phases arguments");
+  KGE_REQUIRE(g->prof, KGE_EINVAL, "the graph was created without KGE_OPT_GRAPH_PROFILE");
+  KGE_CUDA_OK(cudaDeviceSynchronize());
+  for (int p = 0; p < KGE_N_PHASES; ++p) {
+    phase_ms[p] = 0.f;
+    if (g->last_mask & (1u << p)) KGE_CUDA_OK(cudaEventElapsedTime(&phase_ms[p], g->gev[2 * p], g->gev[2 * p + 1]));
+  }
+  KGE_CUDA_OK(cudaEventElapsedTime(total_ms, g->gev[2 * KGE_N_PHASES], g->gev[2 * KGE_N_PHASES + 1]));
   return KGE_OK;
 }
 
@@ -1526,6 +1562,7 @@ extern "C" int kge_step_graph_destroy(kge_step_graph* g) {
   }
   if (g->cap) cudaStreamDestroy(g->cap);
   for (int j = 0; j < 6; ++j) if (g->ev[j]) cudaEventDestroy(g->ev[j]);
+  for (int j = 0; j < 2 * KGE_N_PHASES + 2; ++j) if (g->gev[j]) cudaEventDestroy(g->gev[j]);
   delete g;
   return KGE_OK;
 }

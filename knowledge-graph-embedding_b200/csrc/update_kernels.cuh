@@ -159,6 +159,10 @@ struct UpdateTable {
   int n_out;
   float* w_outs[KGE_MAX_PEERS];
   float* wn_outs[KGE_MAX_PEERS];
+  // NVSwitch multicast addresses of the tables (kge_grads.w_mc): ONE multimem.st reaches every replica
+  float* w_mc;
+  float* wn_mc;
+  int w_private;         // kge_grads.w_private: the new w row stays with its owner, only wn travels
 };
 template <int CPL>
 __device__ __forceinline__ void store_peers(const UpdateTable& T, int64_t row, int nch, int lane, const float4 (&g)[CPL]) {
@@ -473,6 +477,10 @@ __global__ void __launch_bounds__(256) k_update(const UpdateParams p) {
   }
 }
 
+// one 16-byte store through a multicast (NVLS) address: the switch writes every replica
+__device__ __forceinline__ void st_mc(float* addr, float4 v) {
+  asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 // Clip scale + Adam on one row held by a warp (g = summed, unscaled gradient); optionally also
 // writes normalise(new row) to the shadow table the next batch gathers from.
 template <int CPL>
@@ -494,7 +502,8 @@ __device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTabl
     adam_chunk(w, m, v, scale4(scale, g[u]), p.beta1, p.beta2, lr_t, p.eps, p.opt);
     if (T.cols & 3) mask_tail(w, m, v, c, T.cols);
     m4[c] = m; v4[c] = v;
-    if (T.n_out == 0) w4[c] = w;
+    if (T.n_out == 0 || (T.w_private && T.wn_out != nullptr)) w4[c] = w;
+    else if (T.w_mc != nullptr) st_mc(T.w_mc + row * (int64_t) T.ld + 4 * c, w);                                   // all-gather by ONE multicast store
     else for (int j = 0; j < T.n_out; ++j) reinterpret_cast<float4*>(T.w_outs[j] + row * (int64_t) T.ld)[c] = w;   // all-gather by stores
     wnew[u] = w;
   }
@@ -510,7 +519,8 @@ __device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTabl
         const int c = lane + 32 * u;
         if (c >= nch) continue;
         const float4 q = div4(wnew[u], nrm);
-        for (int j = 0; j < T.n_out; ++j) reinterpret_cast<float4*>(T.wn_outs[j] + row * (int64_t) T.ld)[c] = q;
+        if (T.wn_mc != nullptr) st_mc(T.wn_mc + row * (int64_t) T.ld + 4 * c, q);
+        else for (int j = 0; j < T.n_out; ++j) reinterpret_cast<float4*>(T.wn_outs[j] + row * (int64_t) T.ld)[c] = q;
       }
     }
   }

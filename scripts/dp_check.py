@@ -34,6 +34,7 @@ def main():
     owner = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)     # owner-partitioned exchange
     ahead = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)     # owner exchange + look-ahead grouping
     graph = E.Engine(cfg, {slots[n]: v for n, v in W.items()}, device=dev)     # the same step as a captured graph
+    graph.dp_w_private = True                                                    # ... with only wn sent to the replicas
     ok = True
     Xs = [np.stack([rng.integers(0, N, B), rng.integers(0, R, B), rng.integers(0, N, B)], 1) for _ in range(5)]
     lo, hi = dp.batch_shard(B)
@@ -62,6 +63,12 @@ def main():
             ok &= float(lm.item()) == float(ln.item())
         ls = single.train_step(X, 11, step)
         ok &= abs(float(lm.item()) - float(ls.item())) <= 1e-4 * max(1.0, abs(float(ls.item())))
+    try:
+        graph.tab[0].view
+        ok = False                      # stale replicas must refuse to be read
+    except RuntimeError:
+        pass
+    graph.dp_sync_weights()
     for s in multi.tab:
         mine = multi.tab[s].storage
         ref = single.tab[s].storage

@@ -7,5 +7,5 @@ python - <<PY
 import json
 d=json.loads([l for l in open('gpurun_out/${TAG}_bench_n$N.json') if l.startswith('{')][-1])
 print('N', d['n_gpus'], 'value', d['value'], 'ms', d['ms_per_step'], 'plain', d.get('value_plain_calls'), 'e2e', d['e2e']['value'], d['exchange'], d['step_api'])
-print(d['roofline']['phase_ms_per_step'], 'eval', d['eval']['value'], d['eval']['e2e']['value'])
+print('graph', d.get('graph_phase_ms_per_step')); print(d['roofline']['phase_ms_per_step'], 'eval', d['eval']['value'], d['eval']['e2e']['value'])
 PY

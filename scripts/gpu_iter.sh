@@ -7,6 +7,6 @@ python - <<PY
 import json
 d=json.loads(open('gpurun_out/${TAG}_bench.json').read().strip().splitlines()[-1])
 print('value', d['value'], 'ms', d['ms_per_step'], 'e2e', d['e2e']['value'], 'warm', d['value_steady_state_l2_warm'])
-print(d['roofline']['phase_ms_per_step'])
+print(d['roofline']['phase_ms_per_step']); print('graph', d.get('graph_phase_ms_per_step'))
 print('eval', d['eval']['value'], d['eval']['e2e']['value'], d['eval']['cpu_baseline'].get('ranks_outside_tie_band'))
 PY

@@ -29,7 +29,7 @@ def test_struct_sizes_match_header():
     assert C.sizeof(lib.Cfg) == 12 * 4 + 10 * 4 + 2 * 8
     assert C.sizeof(lib.Sampler) == 56 and C.sizeof(lib.Filter) == 24
     assert C.sizeof(lib.Dp) == 24
-    assert C.sizeof(lib.Grads) == 712   # kge_grads (gcc sizeof): dense, n_peers, peer slots, owner fields, abort_word
+    assert C.sizeof(lib.Grads) == 760   # kge_grads (gcc sizeof): dense, n_peers, peer slots, owner fields, abort_word, multicast
 
 
 def test_no_cpu_fallback():
