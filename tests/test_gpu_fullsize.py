@@ -222,3 +222,16 @@ def test_c4_typed_full_batch_matches_oracle(model):
     got = tables_of(eng, model)
     for kk, v in W.data.items():
         assert_weights_close(got[kk], v, 1e-3, 2, kk)
+
+
+def test_fb15k237_gpu_trained_vs_oracle_trained_metrics():
+    """north_star "matching MRR/Hits@10": the same seeded epoch on the bundled FB15k-237 through the GPU step graph
+    and through the CPU oracle; the two sets of weights then rank the same validation queries with their own code."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
+    import accuracy_parity
+    r = accuracy_parity.run(epochs=1, n_queries=200, log=lambda *_: None)
+    print({kk: r[kk] for kk in ("gpu", "cpu_oracle", "epoch_loss_max_rel_diff", "ranks_identical_fraction", "max_abs_weight_diff")})
+    assert r["epoch_loss_max_rel_diff"] < 1e-4
+    assert r["abs_diff"]["mrr"] < 5e-3 and r["abs_diff"]["hits10"] < 1e-2, r["abs_diff"]
+    assert r["ranks_identical_fraction"] > 0.9
