@@ -85,6 +85,7 @@ extern "C" int kge_set_option(kge_ctx* ctx, int option, int value) {
     case KGE_OPT_NO_FUSED_PUSH: c->opt_no_fused_push = value; return KGE_OK;
     case KGE_OPT_RING_SLOTS: c->opt_ring_max = value; return KGE_OK;
     case KGE_OPT_GRAPH_PROFILE: c->opt_graph_profile = value; return KGE_OK;
+    case KGE_OPT_RANK_TC_PASSES: c->opt_tc_passes = value; return KGE_OK;
     default: set_error("unknown option %d", option); return KGE_EINVAL;
   }
 }

@@ -15,7 +15,7 @@ inline bool rank_dot_eligible(const kge_cfg* c) {
 struct DotWs {
   int kpad, words_per_q, n_etiles;
   int64_t qblk;                    // queries per launch (multiple of 128)
-  size_t off_qm, off_qhi, off_qlo, off_ehi, off_elo, off_pos, off_bias, off_hi, off_lo, off_maxn, off_mask, off_filt, total;
+  size_t off_qm, off_qhi, off_qlo, off_ehi, off_elo, off_nlo, off_nq, off_pos, off_bias, off_hi, off_lo, off_maxn, off_wins, off_ucnt, off_ulist, off_filt, total;
   int ldE;
 };
 inline void layout_dot_ws(const kge_cfg* c, int64_t Q, int64_t span, DotWs& L) {
@@ -37,11 +37,15 @@ inline void layout_dot_ws(const kge_cfg* c, int64_t Q, int64_t span, DotWs& L) {
   L.ldE = (c->d_ent + 3) / 4 * 4;
   L.off_ehi = take(sizeof(float) * (size_t) span * L.ldE);
   L.off_elo = take(sizeof(float) * (size_t) span * L.ldE);
+  L.off_nlo = take(sizeof(float) * (size_t) L.n_etiles * TC_BN);       // ||e_lo|| per candidate, whole tiles
+  L.off_nq = take(sizeof(float) * (size_t) L.qblk);
   L.off_pos = take(sizeof(float) * (size_t) L.qblk);
   L.off_bias = take(sizeof(float) * (size_t) L.qblk);
   L.off_hi = take(sizeof(float) * (size_t) L.qblk);
   L.off_lo = take(sizeof(float) * (size_t) L.qblk);
-  L.off_mask = take(sizeof(uint32_t) * (size_t) L.qblk * L.words_per_q);
+  L.off_wins = take(sizeof(int32_t) * (size_t) L.qblk);
+  L.off_ucnt = take(256);                                         // directly behind wins: one memset clears both
+  L.off_ulist = take(sizeof(uint2) * (size_t) L.qblk * TC_UCAP);
   L.off_filt = take(sizeof(uint32_t) * (size_t) L.qblk * L.words_per_q);
   L.total = o;
 }
@@ -84,9 +88,11 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
   const kge_table& E = tables->t[KGE_T_ENT];
   static bool attr_set = false;
   if (!attr_set) {
-    KGE_CUDA_OK(cudaFuncSetAttribute(k_rank_dot_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+    KGE_CUDA_OK(cudaFuncSetAttribute(k_rank_dot_tc<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<3>::SMEM_BYTES));
+    KGE_CUDA_OK(cudaFuncSetAttribute(k_rank_dot_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<2>::SMEM_BYTES));
     attr_set = true;
   }
+  const int passes = ctx->opt_tc_passes == 2 ? 2 : 3;
   unsigned* maxn = reinterpret_cast<unsigned*>(wsb + L.off_maxn);
   KGE_CUDA_OK(cudaMemsetAsync(maxn, 0, 256, st));
   {
@@ -98,12 +104,14 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
   // exact TF32 split of the candidate shard (E = E_hi + E_lo)
   const int64_t span = ent_hi - ent_lo;
   float* Ehi = reinterpret_cast<float*>(wsb + L.off_ehi);
-  float* Elo = reinterpret_cast<float*>(wsb + L.off_elo);
+  float* Elo = passes == 3 ? reinterpret_cast<float*>(wsb + L.off_elo) : nullptr;
+  float* nlo = reinterpret_cast<float*>(wsb + L.off_nlo);
+  KGE_CUDA_OK(cudaMemsetAsync(nlo, 0, sizeof(float) * (size_t) L.n_etiles * TC_BN, st));
   KGE_REQUIRE(E.ld == L.ldE, KGE_EUNSUPPORTED, "tensor-core ranking needs ld == round4(cols) (got %d)", E.ld);
   {
-    int64_t blocks = (span * (E.ld / 4) + 255) / 256;
+    int64_t blocks = (span + 7) / 8;
     if (blocks > (int64_t) ctx->sm_count * 32) blocks = (int64_t) ctx->sm_count * 32;
-    k_rank_split_table<<<(unsigned) blocks, 256, 0, st>>>(E.w, E.ld, E.cols, ent_lo, ent_hi, Ehi, Elo);
+    k_rank_split_table<<<(unsigned) blocks, 256, 0, st>>>(E.w, E.ld, E.cols, ent_lo, ent_hi, Ehi, Elo, nlo);
     KGE_CUDA_OK(cudaGetLastError());
   }
   CUtensorMap map_ah, map_al, map_bh, map_bl;
@@ -113,7 +121,7 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
   if (int rc = make_map_2d(&map_ah, Qhi, (uint64_t) L.kpad, (uint64_t) L.qblk, (uint64_t) L.kpad, TC_BM)) return rc;
   if (int rc = make_map_2d(&map_al, Qlo, (uint64_t) L.kpad, (uint64_t) L.qblk, (uint64_t) L.kpad, TC_BM)) return rc;
   if (int rc = make_map_2d(&map_bh, Ehi, (uint64_t) E.cols, (uint64_t) span, (uint64_t) E.ld, TC_BN)) return rc;
-  if (int rc = make_map_2d(&map_bl, Elo, (uint64_t) E.cols, (uint64_t) span, (uint64_t) E.ld, TC_BN)) return rc;
+  if (int rc = make_map_2d(&map_bl, passes == 3 ? Elo : Ehi, (uint64_t) E.cols, (uint64_t) span, (uint64_t) E.ld, TC_BN)) return rc;
   const size_t idb = cfg->id_dtype ? 8 : 4;
   const bool filtered = filter && filter->off;
   for (int64_t q0 = 0; q0 < Q; q0 += L.qblk) {
@@ -125,8 +133,10 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
     pp.Qm = Qm; pp.Qhi = Qhi; pp.Qlo = Qlo; pp.kpad = L.kpad;
     pp.pos = reinterpret_cast<float*>(wsb + L.off_pos); pp.bias = reinterpret_cast<float*>(wsb + L.off_bias);
     pp.thr_hi = reinterpret_cast<float*>(wsb + L.off_hi); pp.thr_lo = reinterpret_cast<float*>(wsb + L.off_lo);
+    pp.nq = reinterpret_cast<float*>(wsb + L.off_nq);
     pp.maxnorm_bits = maxn;
-    // dropped q_lo.e_lo (2^-20) + truncation of the lo parts (2 * 2^-21) + fp32 accumulation of 3*kpad terms
+    // apart from q.e_lo (bounded per candidate by ||q|| ||e_lo||): truncation of q_lo to TF32 inside the MMA
+    // (2^-21) + fp32 accumulation of 2*kpad products, with a wide safety factor
     pp.eps = 4.0e-6f + 3.6e-7f * (float) L.kpad;
     k_rank_dot_prep<<<(unsigned) ((qn + 7) / 8), 256, 0, st>>>(pp);
     KGE_CUDA_OK(cudaGetLastError());
@@ -140,28 +150,34 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
     }
 
     DotTcParams tp;
-    tp.n_kc = L.kpad / TC_BK; tp.Q = qn; tp.n_qblocks = (int) ((qn + TC_BM - 1) / TC_BM);
+    tp.n_kc = L.kpad / TC_BK; tp.n_k8 = (cfg->d_ent + 7) / 8; tp.Q = qn; tp.n_qblocks = (int) ((qn + TC_BM - 1) / TC_BM);
     tp.ent_lo = ent_lo; tp.ent_hi = ent_hi; tp.n_etiles = L.n_etiles;
     int split = 1;
     while (tp.n_qblocks * split < 2 * ctx->sm_count && split * 2 <= L.n_etiles) split *= 2;
     tp.n_split = split;
-    tp.thr_hi = pp.thr_hi; tp.thr_lo = pp.thr_lo; tp.count = count_out + q0;
-    tp.mask = reinterpret_cast<uint32_t*>(wsb + L.off_mask); tp.words_per_q = L.words_per_q;
+    tp.thr_hi = pp.thr_hi; tp.thr_lo = pp.thr_lo; tp.nq = pp.nq; tp.nlo = nlo;
+    tp.wins = reinterpret_cast<int32_t*>(wsb + L.off_wins); tp.ucnt = reinterpret_cast<uint32_t*>(wsb + L.off_ucnt);
+    tp.ulist = reinterpret_cast<uint2*>(wsb + L.off_ulist); tp.ucap = (uint32_t) ((size_t) L.qblk * TC_UCAP);
+    tp.words_per_q = L.words_per_q;
+    KGE_CUDA_OK(cudaMemsetAsync(wsb + L.off_wins, 0, (L.off_ulist - L.off_wins), st));
     tp.filt = filt;
     int grid = tp.n_qblocks * split;
     if (grid > ctx->sm_count) grid = ctx->sm_count;
     const bool timed = (q0 == 0);           // phase slots hold one interval per call: time the first query block
     if (timed) pt->begin(6);
-    k_rank_dot_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(map_ah, map_al, map_bh, map_bl, tp);
+    if (passes == 3) k_rank_dot_tc<3><<<grid, TC_THREADS, TcCfg<3>::SMEM_BYTES, st>>>(map_ah, map_al, map_bh, map_bl, tp);
+    else k_rank_dot_tc<2><<<grid, TC_THREADS, TcCfg<2>::SMEM_BYTES, st>>>(map_ah, map_al, map_bh, map_bl, tp);
     KGE_CUDA_OK(cudaGetLastError());
     if (timed) { pt->end(6); pt->begin(7); }
 
     DotFixParams fp;
     fp.Qm = Qm; fp.kpad = L.kpad; fp.E = E.w; fp.ldE = E.ld; fp.cols = E.cols;
-    fp.pos = pp.pos; fp.bias = pp.bias; fp.mask = tp.mask; fp.words_per_q = L.words_per_q;
-    fp.Q = qn; fp.ent_lo = ent_lo; fp.count = count_out + q0;
-    const int64_t fix_warps = qn * ((L.words_per_q + 31) / 32);
-    k_rank_dot_fix<<<(unsigned) ((fix_warps + 7) / 8), 256, 0, st>>>(fp);
+    fp.pos = pp.pos; fp.bias = pp.bias; fp.wins = tp.wins; fp.ucnt = tp.ucnt; fp.ulist = tp.ulist; fp.ucap = tp.ucap;
+    fp.filt = filt; fp.words_per_q = L.words_per_q;
+    fp.Q = qn; fp.ent_lo = ent_lo; fp.ent_hi = ent_hi; fp.count = count_out + q0;
+    k_rank_dot_fix<<<(unsigned) ctx->sm_count * 8, 256, 0, st>>>(fp);
+    KGE_CUDA_OK(cudaGetLastError());
+    k_rank_dot_final<<<(unsigned) ((qn + FIX_WARPS * 32 - 1) / (FIX_WARPS * 32)), FIX_WARPS * 32, 0, st>>>(fp);
     KGE_CUDA_OK(cudaGetLastError());
     if (timed) pt->end(7);
   }

@@ -107,6 +107,34 @@ def test_tensor_core_rank_equals_generic(model, score, d, n_ent, side):
     assert np.array_equal(parts, tc_flt)
 
 
+@pytest.mark.parametrize("n_proto", [2, 5])
+def test_tensor_core_rank_with_mass_ties_falls_back_exactly(n_proto):
+    """A table of only a few distinct rows: hundreds of candidates tie with the true score EXACTLY and every one of
+    them is "uncertain" for the tensor-core pass.  Five distinct rows: a long list of pairs for the exact fix-up;
+    two: the list (512 pairs per query) overflows and the block is re-ranked in fp32 as a whole.  Counts (strict >)
+    must equal the generic path's bit for bit."""
+    import os
+    from KGE._b200.filter import build_filter
+    n_ent, d = 3000, 64
+    rng = np.random.default_rng(3)
+    ref, W, eng = make_pair("DistMult", n_ent, R, d, None, score=None, loss=LOSSES["hinge"])
+    proto = eng.tab[0].storage[:n_proto].clone()
+    eng.tab[0].storage.copy_(proto[torch.from_numpy(rng.integers(0, n_proto, n_ent)).cuda()])
+    eng.tab[0].touch()
+    pos = rand_triples(rng, 5000, n_ent, R)
+    Xq = pos[:300]
+    for side, s in (("h", 0), ("t", 1)):
+        off, ids = build_filter(pos, Xq, side, n_ent, eng.device)
+        tc = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+        os.environ["KGE_RANK_GENERIC"] = "1"
+        try:
+            gen = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+        finally:
+            os.environ.pop("KGE_RANK_GENERIC")
+        assert np.array_equal(tc, gen), (side, np.abs(tc - gen).max())
+        assert tc.max() > 100            # the ties are real: whole groups of candidates rank above
+
+
 @pytest.mark.parametrize("model,score,d,n_ent,side", [
     ("TransE", "l1", 50, 1500, "t"), ("TransE", "l1", 50, 1500, "h"),
     ("TransE", "l2", 37, 700, "h"), ("TransE", "l2pow", 128, 333, "t"),
