@@ -333,19 +333,45 @@ class KGEModel:
             if val_iter is not None:
                 val_iter.skip(first_epoch * min(n_batches, n_val_batches))
 
+        # Dense tables: the step runs as a captured CUDA graph (kge_step_graph: one launch per batch instead of ~20) and
+        # the NEXT batch — the stream is one batch ahead — is grouped while this one trains (kge_train_step_next);
+        # results are bit-identical to plain kge_train_step calls (tests/test_gpu_graph.py).  KGE_B200_GRAPH=0: plain calls.
+        graph = None
+        lookahead = sharded is None and eng is not None and not eng.lazy
+        if lookahead and split:
+            lo, hi = _dp.batch_shard(batch_size)
+            # without validation batches nothing reads w during an epoch: only wn travels between the ranks per step
+            eng.dp_w_private = val_iter is None and os.environ.get("KGE_DP_W_PRIVATE", "1") != "0"
+        if lookahead and os.environ.get("KGE_B200_GRAPH", "1") != "0":
+            graph = eng.step_graph_dp(hi - lo, ns_seed, batch_size, lo) if split else eng.step_graph(batch_size, ns_seed)
+        nxt = next(train_iter) if lookahead else None
+
         logging.info("[%s] Start Training..." % _now())
         for epoch in range(first_epoch, epochs):
             t_loss = torch.zeros(n_batches, dtype=torch.float32, device=device)
             v_loss = torch.zeros(max(n_val_batches, 1), dtype=torch.float32, device=device)
             for b in range(n_batches):
-                batch = next(train_iter)
-                if sharded is not None:
-                    sharded.train_step(batch, ns_seed, step, loss_out=t_loss[b:b + 1])
-                elif split:
-                    lo, hi = _dp.batch_shard(len(batch))
-                    eng.train_step_dp(batch[lo:hi], ns_seed, step, len(batch), lo, loss_out=t_loss[b:b + 1])
+                if lookahead:
+                    batch, nxt = nxt, next(train_iter)
+                    n_step = step + 1 + (1 if (val_iter is not None and b < n_val_batches) else 0)   # the next TRAINING step
+                    cur, ahead = (batch[lo:hi], nxt[lo:hi]) if split else (batch, nxt)
+                    if graph is not None:
+                        t_loss[b:b + 1].copy_(graph.launch(cur, step, next_triples=ahead, next_step=n_step))
+                    elif split:
+                        eng.train_step_dp(cur, ns_seed, step, len(batch), lo, loss_out=t_loss[b:b + 1], next_triples=ahead,
+                                          next_step=n_step)
+                    else:
+                        eng.train_step(cur, ns_seed, step, is_train=True, loss_out=t_loss[b:b + 1], next_triples=ahead,
+                                       next_step=n_step)
                 else:
-                    eng.train_step(batch, ns_seed, step, is_train=True, loss_out=t_loss[b:b + 1])
+                    batch = next(train_iter)
+                    if sharded is not None:
+                        sharded.train_step(batch, ns_seed, step, loss_out=t_loss[b:b + 1])
+                    elif split:
+                        lo, hi = _dp.batch_shard(len(batch))
+                        eng.train_step_dp(batch[lo:hi], ns_seed, step, len(batch), lo, loss_out=t_loss[b:b + 1])
+                    else:
+                        eng.train_step(batch, ns_seed, step, is_train=True, loss_out=t_loss[b:b + 1])
                 step += 1
                 if val_iter is not None and b < n_val_batches:
                     # validation batches draw negatives and apply the constraint too.  Sharded
@@ -358,6 +384,7 @@ class KGEModel:
             self.train_loss_history.append(float(t_loss.sum().item()) / n_batches)       # one sync per epoch
             if eng is not None:
                 eng.check_peers_alive()          # a cross-GPU barrier that timed out is fatal (kge_peer_barrier)
+                eng.dp_sync_weights()            # dp_w_private: w of the rows other ranks own (collective, once per epoch)
             writers.scalar("train", self.train_loss_history[-1], epoch)
             if val_iter is not None:
                 self.val_loss_history.append(float(v_loss.sum().item()) / n_val_batches)

@@ -17,9 +17,12 @@ train, val = X[:3600], X[3600:]
 md = {"ind2ent": [f"e{i}" for i in range(N)], "ent2ind": {f"e{i}": i for i in range(N)},
       "ind2rel": [f"r{i}" for i in range(R)], "rel2ind": {f"r{i}": i for i in range(R)}}
 ok = True
-for cls, kw in ((TransE, {}), (DistMult, {})):
+for cls, kw, with_val in ((TransE, {}, True), (DistMult, {}, True), (DistMult, {}, False)):
+    # without validation batches the owners keep w to themselves during an epoch (kge_grads.w_private)
     m = cls(embedding_params={"embedding_size": 32}, negative_ratio=4, corrupt_side="h+t", **kw)
-    m.train(train, val, md, epochs=3, batch_size=256, seed=5, log_path=tempfile.mkdtemp())
+    m.train(train, val if with_val else None, md, epochs=3, batch_size=256, seed=5, log_path=tempfile.mkdtemp(),
+            early_stopping_rounds=None)
+    ok &= bool(getattr(m._engine._peer, "w_private", False)) == (not with_val and m._engine._dp_kind == "owner")
     kind = m._engine._dp_kind
     for k, v in m.model_weights.items():
         t = v.tensor.contiguous()
@@ -32,7 +35,7 @@ for cls, kw in ((TransE, {}), (DistMult, {})):
     ok &= all(o == objs[0] for o in objs)
     ok &= np.isfinite(m.train_loss_history[-1]) and m.train_loss_history[-1] < m.train_loss_history[0]
     if rank == 0:
-        print(cls.__name__, "exchange", kind, "loss", [round(x, 4) for x in m.train_loss_history], "mrr", round(objs[0].get("mrr", objs[0].get("MRR", 0)), 4), flush=True)
+        print(cls.__name__, "exchange", kind, "w_private", not with_val, "loss", [round(x, 4) for x in m.train_loss_history], "mrr", round(objs[0].get("mrr", objs[0].get("MRR", 0)), 4), flush=True)
 flag = torch.tensor([int(ok)], device="cuda")
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:
