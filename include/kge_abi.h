@@ -471,9 +471,13 @@ int kge_flush_rows(kge_ctx*, const kge_cfg*, kge_tables*, void* stream);
  * step kernel stages through shared memory with TMA bulk copies (default 32).
  * KGE_OPT_GRAPH_PROFILE: 1 = step graphs created from now on record phase-boundary events (kge_step_graph_phases).
  * KGE_OPT_RANK_TC_PASSES: MMAs per K step of the tensor-core ranking GEMM: 3 (default: 3xTF32) or 2 (candidate side in
- * TF32 only, looser per-candidate bound: fewer tensor operations, more candidates for the exact fix-up). */
+ * TF32 only, looser per-candidate bound: fewer tensor operations, more candidates for the exact fix-up).
+ * KGE_OPT_CLUSTER_GROUP: 1 = group the gradient records with ONE kernel on one thread-block cluster (k_group_cluster:
+ * histogram / scan / scatter through distributed shared memory) where the key space is small enough, instead of the
+ * four-kernel chain (default 0: identical results, but measured slower inside a step — its 1024-thread CTAs cannot
+ * run beside the step kernel). */
 enum { KGE_OPT_RADIX_SORT = 1, KGE_OPT_NO_SHADOW = 2, KGE_OPT_NO_FUSED_PUSH = 3, KGE_OPT_RING_SLOTS = 4,
-       KGE_OPT_GRAPH_PROFILE = 5, KGE_OPT_RANK_TC_PASSES = 6 };
+       KGE_OPT_GRAPH_PROFILE = 5, KGE_OPT_RANK_TC_PASSES = 6, KGE_OPT_CLUSTER_GROUP = 7 };
 int kge_set_option(kge_ctx*, int option, int value);
 
 /* Per-phase device timing (CUDA events recorded on the call's stream, read back only at

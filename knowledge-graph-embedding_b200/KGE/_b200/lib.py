@@ -18,6 +18,8 @@ OPT_NO_SHADOW = 2
 OPT_NO_FUSED_PUSH = 3
 OPT_RING_SLOTS = 4
 OPT_GRAPH_PROFILE = 5
+OPT_RANK_TC_PASSES = 6
+OPT_CLUSTER_GROUP = 7
 N_PHASES = 10
 PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm", "rank_fix", "apply", "barrier"]
 PEER_DEAD = 0xdead

@@ -86,6 +86,7 @@ extern "C" int kge_set_option(kge_ctx* ctx, int option, int value) {
     case KGE_OPT_RING_SLOTS: c->opt_ring_max = value; return KGE_OK;
     case KGE_OPT_GRAPH_PROFILE: c->opt_graph_profile = value; return KGE_OK;
     case KGE_OPT_RANK_TC_PASSES: c->opt_tc_passes = value; return KGE_OK;
+    case KGE_OPT_CLUSTER_GROUP: c->opt_cluster_group = value; return KGE_OK;
     default: set_error("unknown option %d", option); return KGE_EINVAL;
   }
 }

@@ -67,6 +67,7 @@ struct kge_ctx_impl {
   cudaEvent_t* gev = nullptr;     // capturing with phase events on (kge_step_graph, KGE_OPT_GRAPH_PROFILE): [2 * KGE_N_PHASES]
   unsigned gev_mask = 0;
   int opt_graph_profile = 0;
+  int opt_cluster_group = 0;      // kge_set_option(KGE_OPT_CLUSTER_GROUP): grouping by k_group_cluster (one kernel, one cluster)
   int opt_tc_passes = 3;          // kge_set_option(KGE_OPT_RANK_TC_PASSES): MMAs per K step of the ranking GEMM (3 or 2)
   DynScal* dyn = nullptr;         // device; used only while `capturing` (kge_step_graph_create)
   int capturing = 0;              // the call is being captured into a CUDA graph: per-step scalars come from `dyn`

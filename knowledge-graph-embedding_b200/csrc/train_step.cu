@@ -17,7 +17,7 @@ namespace kge {
 struct StepWs {
   size_t off_part, off_scal, off_neg, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub,
       off_rec[KGE_MAX_TABLES], off_recP, off_snap[2], off_rowpart, off_matpart, off_seg, off_hdr, off_heavy, off_uniq,
-      off_islot, off_recdest, off_facq, off_fcoef;
+      off_islot, off_recdest, off_facq, off_fcoef, off_long;
   size_t cub_bytes, total, n_seg;
   size_t gdelta;          // the grouping buffers (negatives, keys, record ids, scan, headers, heavy list) exist twice:
                           // set s lives at offset + s * gdelta (the next batch is grouped while this one is applied)
@@ -79,6 +79,7 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   L.off_seg = take(sizeof(uint32_t) * (2 * L.n_seg + 2));   // cnt[K] | off[K+1] | n_heavy   (radix path: seg_lo | seg_hi)
   L.off_hdr = take(sizeof(uint32_t) * 8 * L.n_seg);         // k_canon's per-key headers
   L.off_heavy = take(sizeof(uint32_t) * (size_t) (L.n_keys / UPD_HEAVY + 1));
+  L.off_long = take(sizeof(uint32_t) * (size_t) (L.n_keys / 32 + 2));          // k_group_cluster: [count | keys with > 32 records]
   L.gdelta = o - g0;
   o += L.gdelta;                                            // the second set
   L.off_keys_out = take(sizeof(uint32_t) * (size_t) L.n_keys);
@@ -269,6 +270,25 @@ __global__ void __launch_bounds__(256) k_keys(const StepParams p, uint32_t* cnt)
   }
 }
 
+
+// the same key function for k_group_cluster (group_kernels.cuh)
+struct StepKeyFn {
+  StepParams p;
+  __device__ __forceinline__ uint32_t operator()(int64_t s) const {
+    const int64_t nneg = p.B * (int64_t) p.k_eff, nE = 2 * p.B + nneg;
+    if (s < 2 * p.B) return (uint32_t) load_id(p.triples, 3 * (s % p.B) + (s < p.B ? 0 : 2), p.id64);
+    if (s < nE) {
+      const int64_t slot = s - 2 * p.B, i = slot / p.k_eff;
+      const int c = (int) (slot - i * p.k_eff);
+      const int64_t e = p.neg_override ? p.neg_override[slot]
+                                       : sample_negative(p.sd, i, c, load_id(p.triples, 3 * i, p.id64),
+                                                         load_id(p.triples, 3 * i + 2, p.id64));
+      p.neg_ids[slot] = e;
+      return (uint32_t) e;
+    }
+    return (uint32_t) (p.md.t[KGE_T_ENT].rows + load_id(p.triples, 3 * (s - nE) + 1, p.id64));
+  }
+};
 
 __global__ void k_sample(SamplerDev sd, const void* triples, int id64, int64_t B, int64_t* out) {
   const int64_t n = (int64_t) B * sd.k_eff;
@@ -559,6 +579,29 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     uint32_t* cnt = reinterpret_cast<uint32_t*>(gbase + L.off_seg);
     uint32_t* off = cnt + L.n_seg;
     const int64_t K = (int64_t) L.n_seg;
+    if (ctx->opt_cluster_group && K <= (int64_t) GC_CTAS * GC_MAX_KC) {
+      // opt-in (KGE_OPT_CLUSTER_GROUP): the whole chain in one kernel on one thread-block cluster (+ the long segments'
+      // pass).  Same results; measured SLOWER inside a step (C2: grouping 65 -> 144 us): its 1024-thread CTAs need
+      // eight empty SMs at once, which the step and update kernels never leave, so it runs after them instead of beside them.
+      GroupOut go;
+      go.keys = kp.keys; go.vals_tmp = kp.vals; go.vals = reinterpret_cast<uint32_t*>(gbase + L.off_vals_out);
+      go.off = off; go.hdr = reinterpret_cast<uint32_t*>(gbase + L.off_hdr);
+      go.heavy_keys = reinterpret_cast<uint32_t*>(gbase + L.off_heavy); go.n_heavy = cnt + 2 * L.n_seg + 1;
+      go.n_long = reinterpret_cast<uint32_t*>(gbase + L.off_long); go.long_keys = go.n_long + 1;
+      go.K = K; go.n_keys = L.n_keys; go.Kc = (int) ((K + GC_CTAS - 1) / GC_CTAS);
+      const size_t gsm = group_cluster_smem(go.Kc);
+      static size_t gsm_set = 0;
+      if (gsm > 48 * 1024 && gsm > gsm_set) {
+        KGE_CUDA_OK(cudaFuncSetAttribute(k_group_cluster<StepKeyFn>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) gsm));
+        gsm_set = gsm;
+      }
+      StepKeyFn kf{kp};
+      k_group_cluster<StepKeyFn><<<GC_CTAS, GC_THREADS, gsm, ax>>>(kf, go);
+      KGE_CUDA_OK(cudaGetLastError());
+      k_canon_long<<<64, CANON_WARPS * 32, 0, ax>>>(off, go.long_keys, go.n_long, kp.vals, go.vals, go.hdr);
+      KGE_CUDA_OK(cudaGetLastError());
+      return KGE_OK;
+    }
     int64_t kb = (L.n_keys + 255) / 256;
     if (kb > (int64_t) ctx->sm_count * 8) kb = (int64_t) ctx->sm_count * 8;
     KGE_CUDA_OK(cudaMemsetAsync(cnt, 0, sizeof(uint32_t) * (2 * L.n_seg + 2), ax));

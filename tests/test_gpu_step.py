@@ -246,9 +246,11 @@ def test_grouping_equals_stable_radix_sort(model, B, k, n_rel):
     score = None if model == "DistMult" else SCORES["l2pow"]
     d, dr = (24, 20) if model == "TransR" else (40, None)
     outs = []
-    for radix in (1, 0):
+    # radix sort | four-kernel counting sort (default) | one-kernel cluster grouping (k_group_cluster, opt-in)
+    for radix, cluster in ((1, 0), (0, 0), (0, 1)):
         _, _, eng = make_pair(model, 120, n_rel, d, dr, score=score, loss=LOSSES["hinge"], k=k, side="h+t")
         eng.set_option(L.OPT_RADIX_SORT, radix)
+        eng.set_option(L.OPT_CLUSTER_GROUP, cluster)
         r2 = np.random.default_rng(17)
         try:
             for step in range(3):
@@ -256,9 +258,11 @@ def test_grouping_equals_stable_radix_sort(model, B, k, n_rel):
             torch.cuda.synchronize()
         finally:
             eng.set_option(L.OPT_RADIX_SORT, 0)
+            eng.set_option(L.OPT_CLUSTER_GROUP, 0)
         outs.append({s: t.storage.clone() for s, t in eng.tab.items()})
-    for s in outs[0]:
-        assert torch.equal(outs[0][s], outs[1][s]), f"slot {s}"
+    for o in outs[1:]:
+        for s in outs[0]:
+            assert torch.equal(outs[0][s], o[s]), f"slot {s}"
 
 
 @pytest.mark.parametrize("model,score", [("DistMult", "dot"), ("TransE", "l1"), ("UM", "l2pow")])
