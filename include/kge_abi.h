@@ -50,7 +50,8 @@ typedef enum { KGE_LOSS_HINGE = 0, KGE_LOSS_LOGISTIC = 1, KGE_LOSS_BCE = 2,
  *   SGD     w -= lr g                                  (momentum = 0; slots m, v unused)
  *   ADAGRAD v += g^2; w -= lr g / (sqrt(v) + eps)      (v = accumulator, caller initialises it to
  *                                                       initial_accumulator_value = 0.1; m unused)
- * cfg.lr / cfg.eps carry learning_rate / epsilon.  Row-lazy and sharded tables: Adam only. */
+ * cfg.lr / cfg.eps carry learning_rate / epsilon.  Every optimizer works on every table form (dense, row-lazy,
+ * sharded): a row without a gradient is not moved by SGD / Adagrad, so its skipped steps replay the constraint only. */
 typedef enum { KGE_OPTIM_ADAM = 0, KGE_OPTIM_SGD = 1, KGE_OPTIM_ADAGRAD = 2 } kge_opt_kind;
 /* BaseModel.py:49 corrupt_side */
 typedef enum { KGE_SIDE_H = 0, KGE_SIDE_T = 1, KGE_SIDE_HT = 2 } kge_side;

@@ -194,11 +194,10 @@ class KGEModel:
         self.model_weights = {k: WeightView(k, self._engine.tab[slots[k]]) for k in values}
 
     def _row_sparse_eligible(self, cfg):
-        """Models / settings the row-lazy and sharded steps cover: vector models without a dense regulariser,
-        Adam (kge_abi.h: 'Row-lazy and sharded tables: Adam only')."""
-        vec = self.MODEL in ("UM", "TransE", "TransD", "RotatE", "DistMult") or \
+        """Models / settings the row-lazy and sharded steps cover: vector models without a dense regulariser
+        (any of the optimizers: Adam, SGD, Adagrad)."""
+        return self.MODEL in ("UM", "TransE", "TransD", "RotatE", "DistMult") or \
             (self.MODEL == "TransH" and not cfg["constraint"])
-        return vec and cfg.get("optimizer", _lib.OPTIM_ADAM) == _lib.OPTIM_ADAM
 
     def _shard_world(self, cfg, values):
         """Number of ranks the entity tables are sharded over, 0 = replicated tables.  Under torchrun
@@ -230,7 +229,7 @@ class KGEModel:
         if not self._row_sparse_eligible(cfg):
             if flag == "1":
                 raise NotImplementedError("KGE_B200_LAZY_ROWS=1: row-lazy tables cover the vector models without a "
-                                          "dense regulariser, with Adam (other optimizers take the dense step)")
+                                          "dense regulariser")
             return False
         if flag == "1":
             return True

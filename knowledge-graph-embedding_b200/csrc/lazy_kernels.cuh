@@ -53,6 +53,8 @@ struct LazyParams {
   const uint32_t* vals;  // record ids in sorted-key order (stable)
   const float* scal;
   float lr, beta1, beta2, eps;
+  int opt;               // kge_opt_kind.  SGD / Adagrad: a row without a gradient is not moved by the optimizer at all
+                         // (w - lr * 0, acc + 0), so its skipped steps replay the constraint only, to its fixed point
   uint32_t t;            // the Adam step being applied (pre: rows go to t-1 + constraint; flush: rows go to t)
 };
 
@@ -205,7 +207,7 @@ __global__ void __launch_bounds__(256) k_lazy_pre(const LazyParams p) {
       if (idle) {
         load_row<CPL>(T.m + row * (int64_t) T.ld, nch, lane, m);
         load_row<CPL>(T.v + row * (int64_t) T.ld, nch, lane, v);
-        replay_row<CPL>(p, T, s_lr, w, m, v, all_zero<CPL>(m, v), s, p.t - 1, nch, lane);
+        replay_row<CPL>(p, T, s_lr, w, m, v, p.opt != KGE_OPTIM_ADAM || all_zero<CPL>(m, v), s, p.t - 1, nch, lane);
       }
       con_row<CPL>(w, T.con_op, nch, lane);                // start-of-batch constraint of step t
       store_row<CPL>(T.w + row * (int64_t) T.ld, nch, lane, w);
@@ -219,7 +221,7 @@ __global__ void __launch_bounds__(256) k_lazy_update(const LazyParams p) {
   const int lane = threadIdx.x & 31;
   const int64_t nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
   const uint32_t n = __ldg(p.uniq);
-  const float lr_t = adam_lr(p.lr, p.beta1, p.beta2, p.t);
+  const float lr_t = p.opt == KGE_OPTIM_ADAM ? adam_lr(p.lr, p.beta1, p.beta2, p.t) : p.lr;
   for (int64_t it = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5; it < n; it += nw) {
     const uint32_t* item = p.uniq + 4 + 3 * it;
     const int64_t row = __ldg(item), lo = __ldg(item + 1), L = (int64_t) __ldg(item + 2) - lo;
@@ -245,13 +247,13 @@ __global__ void __launch_bounds__(256) k_lazy_update(const LazyParams p) {
         }
       // k_lazy_pre already moved w; m and v still belong to step s: their zero-gradient steps are
       // independent of w
-      if (s + 1 < p.t && !all_zero<CPL>(m, v)) decay_mv<CPL>(m, v, p.t - 1 - s, p.beta1, p.beta2);
+      if (p.opt == KGE_OPTIM_ADAM && s + 1 < p.t && !all_zero<CPL>(m, v)) decay_mv<CPL>(m, v, p.t - 1 - s, p.beta1, p.beta2);
       const float scale = p.scal[T.slot];
 #pragma unroll
       for (int u = 0; u < CPL; ++u) {
         const int c = lane + 32 * u;
         if (c >= nch) continue;
-        adam_chunk(w[u], m[u], v[u], scale4(scale, g[u]), p.beta1, p.beta2, lr_t, p.eps);
+        adam_chunk(w[u], m[u], v[u], scale4(scale, g[u]), p.beta1, p.beta2, lr_t, p.eps, p.opt);
         mask_tail(w[u], m[u], v[u], c, T.cols);
       }
       store_row<CPL>(T.m + row * (int64_t) T.ld, nch, lane, m);
@@ -279,7 +281,7 @@ __global__ void __launch_bounds__(256) k_lazy_flush(const LazyParams p) {
       load_row<CPL>(T.w + row * (int64_t) T.ld, nch, lane, w);
       load_row<CPL>(T.m + row * (int64_t) T.ld, nch, lane, m);
       load_row<CPL>(T.v + row * (int64_t) T.ld, nch, lane, v);
-      const bool fresh = all_zero<CPL>(m, v);
+      const bool fresh = p.opt != KGE_OPTIM_ADAM || all_zero<CPL>(m, v);
       replay_row<CPL>(p, T, s_lr, w, m, v, fresh, s, p.t, nch, lane);
       store_row<CPL>(T.w + row * (int64_t) T.ld, nch, lane, w);
       if (!fresh) {

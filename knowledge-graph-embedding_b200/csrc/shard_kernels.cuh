@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(256) k_shard_update(const LazyParams lp, Shard
   const int lane = threadIdx.x & 31;
   const int64_t nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
   const uint32_t n = __ldg(lp.uniq);
-  const float lr_t = adam_lr(lp.lr, lp.beta1, lp.beta2, lp.t);
+  const float lr_t = lp.opt == KGE_OPTIM_ADAM ? adam_lr(lp.lr, lp.beta1, lp.beta2, lp.t) : lp.lr;
   for (int64_t it = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5; it < n; it += nw) {
     const int64_t row = __ldg(lp.uniq + 4 + 3 * it);
     uint32_t* cb = sd.contrib + (size_t) it * sd.world;
@@ -167,13 +167,13 @@ __global__ void __launch_bounds__(256) k_shard_update(const LazyParams lp, Shard
 #pragma unroll
         for (int u = 0; u < CPL; ++u) g[u] += x[u];
       }
-      if (s + 1 < lp.t && !all_zero<CPL>(m, v)) decay_mv<CPL>(m, v, lp.t - 1 - s, lp.beta1, lp.beta2);
+      if (lp.opt == KGE_OPTIM_ADAM && s + 1 < lp.t && !all_zero<CPL>(m, v)) decay_mv<CPL>(m, v, lp.t - 1 - s, lp.beta1, lp.beta2);
       const float scale = lp.scal[T.slot];
 #pragma unroll
       for (int u = 0; u < CPL; ++u) {
         const int c = lane + 32 * u;
         if (c >= nch) continue;
-        adam_chunk(w[u], m[u], v[u], scale4(scale, g[u]), lp.beta1, lp.beta2, lr_t, lp.eps);
+        adam_chunk(w[u], m[u], v[u], scale4(scale, g[u]), lp.beta1, lp.beta2, lr_t, lp.eps, lp.opt);
         mask_tail(w[u], m[u], v[u], c, T.cols);
       }
       store_row<CPL>(T.m + row * (int64_t) T.ld, nch, lane, m);

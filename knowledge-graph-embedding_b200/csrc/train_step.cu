@@ -153,7 +153,6 @@ static int check_lazy(const kge_cfg* c, const kge_tables* t) {
   for (int s = 0; s < 2; ++s)
     KGE_REQUIRE(!cols[s] || t->t[s].last, KGE_EINVAL, "row-lazy tables: entity slot %d has no `last`", s);
   KGE_REQUIRE(t->lazy_t >= 0 && t->lazy_t < 0xfffffff0ll, KGE_EINVAL, "lazy_t %lld out of range", (long long) t->lazy_t);
-  KGE_REQUIRE(c->optimizer == KGE_OPTIM_ADAM, KGE_EUNSUPPORTED, "row-lazy / sharded tables: Adam only");
   return KGE_OK;
 }
 // start-of-batch constraint op of an entity slot (the jobs k_lazy_pre takes over from k_constrain)
@@ -178,6 +177,7 @@ static void fill_lazy(const kge_cfg* c, const kge_tables* t, uint32_t step_t, La
   }
   lp.uniq = nullptr; lp.vals = nullptr; lp.scal = nullptr;
   lp.lr = c->lr; lp.beta1 = c->beta1; lp.beta2 = c->beta2; lp.eps = c->eps;
+  lp.opt = c->optimizer;
   lp.t = step_t;
 }
 

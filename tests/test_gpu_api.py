@@ -261,22 +261,27 @@ def test_train_with_sharded_tables_on_emulated_ranks(name, ranks, tmp_path, monk
     assert (tmp_path / "sharded" / "ckpt.pt").exists() and (tmp_path / "sharded" / "ckpt.opt.rank0.pt").exists()
 
 
-def test_shard_and_lazy_are_not_chosen_for_other_optimizers(monkeypatch):
-    """row-lazy / sharded tables are Adam-only in the library, so the automatic choice must not
-    pick them for SGD / Adagrad (and forcing them must fail in Python, not at the first step)."""
+def test_shard_and_lazy_are_chosen_for_every_optimizer(monkeypatch, tmp_path):
+    """Row-lazy / sharded tables cover Adam, SGD and Adagrad (round 1 was Adam-only and the automatic choice had to
+    step around the others): the choice depends on model and table size alone, and a forced row-lazy run with SGD
+    trains through the model API."""
     from KGE._b200 import lib as L
+    from KGE import optimizers
+    from toy_kg import train, val, metadata
     m = TransE(embedding_params={"embedding_size": 128}, negative_ratio=2, corrupt_side="h+t")
     m.batch_size = 64
     big = {"ent_emb": torch.empty((2_000_000, 128), device="meta"), "rel_emb": torch.empty((10, 128), device="meta")}
-    for opt, want in ((L.OPTIM_ADAM, True), (L.OPTIM_SGD, False), (L.OPTIM_ADAGRAD, False)):
+    for opt in (L.OPTIM_ADAM, L.OPTIM_SGD, L.OPTIM_ADAGRAD):
         cfg = {"constraint": 1, "optimizer": opt}
-        assert m._lazy_rows(cfg, big) is want
+        assert m._lazy_rows(cfg, big) is True
         monkeypatch.setenv("KGE_B200_SHARD_EMULATE", "2")
-        assert bool(m._shard_world(cfg, big)) is want
+        assert bool(m._shard_world(cfg, big)) is True
         monkeypatch.delenv("KGE_B200_SHARD_EMULATE")
     monkeypatch.setenv("KGE_B200_LAZY_ROWS", "1")
-    with pytest.raises(NotImplementedError):
-        m._lazy_rows({"constraint": 1, "optimizer": L.OPTIM_SGD}, big)
+    for opt in (optimizers.SGD(0.05), optimizers.Adagrad(0.05)):
+        m2 = TransE(embedding_params={"embedding_size": 8}, negative_ratio=2, corrupt_side="h+t")
+        m2.train(train, val, metadata, epochs=2, batch_size=4, optimizer=opt, seed=1, log_path=str(tmp_path))
+        assert m2._engine.lazy and np.isfinite(m2.train_loss_history[-1])
 
 
 # ---- checkpoints with optimizer state + resume (SURVEY.md 8f-3) -------------------------------------------------
@@ -301,3 +306,21 @@ def test_resume_continues_bitwise(lazy, tmp_path, monkeypatch):
     assert ef.adam_t == ea.adam_t
     for s in ef.tab:
         assert torch.equal(ef.tab[s].m, ea.tab[s].m) and torch.equal(ef.tab[s].v, ea.tab[s].v), s
+
+
+def test_device_batch_stream_on_the_gpu():
+    """the batch pipeline lives on the device (one permutation per epoch, one gather per batch); the
+    training loop reads it one batch ahead (look-ahead grouping).  Round 1 tested it on the CPU only."""
+    from KGE.data_utils import DeviceBatchStream
+    X = np.stack([np.arange(1000), np.arange(1000) % 7, np.arange(1000)[::-1]], 1).astype(np.int64)
+    a = DeviceBatchStream(X, 128, shuffle=True, seed=3, device="cuda:0")
+    b = DeviceBatchStream(X, 128, shuffle=True, seed=3, device="cuda:0")
+    first = [next(a) for _ in range(20)]
+    assert all(t.is_cuda and t.shape == (128, 3) and t.dtype == torch.int64 for t in first)
+    epoch = torch.cat(first)[:1000]                               # the first 1000 rows are one permutation of the data
+    assert torch.equal(epoch[:, 0].sort().values.cpu(), torch.arange(1000))
+    assert torch.equal(epoch[:, 2], 999 - epoch[:, 0])            # rows stay intact
+    b.skip(7)                                                     # resume: same draws as iterating
+    assert torch.equal(next(b), first[7])
+    c = DeviceBatchStream(X, 100, shuffle=False, device="cuda:0")
+    assert torch.equal(next(c).cpu(), torch.from_numpy(X[:100]))

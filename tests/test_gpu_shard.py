@@ -143,3 +143,29 @@ def test_fused_push_equals_separate_push_bitwise(case):
     assert runs[0][0] == runs[1][0]
     for s in runs[0][1]:
         assert torch.equal(runs[0][1][s], runs[1][1][s]), f"slot {s}"
+
+
+@pytest.mark.parametrize("opt", ["sgd", "adagrad"])
+def test_one_rank_shard_equals_lazy_step_bitwise_sgd_adagrad(opt):
+    """SGD / Adagrad on sharded tables: the owner's row update takes kge_cfg.optimizer."""
+    from KGE._b200 import shard as SH
+    case = CASES[0]
+    model, score, loss, con, d, k, side = case
+    B = 64
+    batches = _batches(np.random.default_rng(3), 6, B)
+    _, _, eng = make_pair(model, N, R, d, score=score, loss=loss, k=k, side=side, constraint=con, lazy=True)
+    ranks = _sharded(case, 1, B)
+    for e in [eng] + [r.eng for r in ranks]:
+        e.cfg.optimizer, e.cfg.lr = (1 if opt == "sgd" else 2), 0.05
+        if opt == "adagrad":
+            e.acc_init = 0.1
+    for step, X in enumerate(batches):
+        l_ref = eng.train_step(X, 5, step)
+        l_sh = SH.emulate_step(ranks, [X], 5, step, B, [0])
+        assert float(l_ref.item()) == float(l_sh.item()), step
+    eng.flush()
+    for r in ranks:
+        r.eng.flush()
+    full = _full_tables(ranks)
+    for s, pt in eng.tab.items():
+        assert torch.equal(pt.view.cpu(), full[s]), s
