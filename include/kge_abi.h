@@ -476,9 +476,11 @@ int kge_flush_rows(kge_ctx*, const kge_cfg*, kge_tables*, void* stream);
  * KGE_OPT_CLUSTER_GROUP: 1 = group the gradient records with ONE kernel on one thread-block cluster (k_group_cluster:
  * histogram / scan / scatter through distributed shared memory) where the key space is small enough, instead of the
  * four-kernel chain (default 0: identical results, but measured slower inside a step — its 1024-thread CTAs cannot
- * run beside the step kernel). */
+ * run beside the step kernel).
+ * KGE_OPT_PRE_EARLY: 0 = the look-ahead grouping (kge_train_step_next) starts behind the step kernel instead of beside it
+ * (default 1; measured: the chain then outlasts the update kernels). */
 enum { KGE_OPT_RADIX_SORT = 1, KGE_OPT_NO_SHADOW = 2, KGE_OPT_NO_FUSED_PUSH = 3, KGE_OPT_RING_SLOTS = 4,
-       KGE_OPT_GRAPH_PROFILE = 5, KGE_OPT_RANK_TC_PASSES = 6, KGE_OPT_CLUSTER_GROUP = 7 };
+       KGE_OPT_GRAPH_PROFILE = 5, KGE_OPT_RANK_TC_PASSES = 6, KGE_OPT_CLUSTER_GROUP = 7, KGE_OPT_PRE_EARLY = 8 };
 int kge_set_option(kge_ctx*, int option, int value);
 
 /* Per-phase device timing (CUDA events recorded on the call's stream, read back only at

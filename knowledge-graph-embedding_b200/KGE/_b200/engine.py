@@ -21,6 +21,8 @@ def _ctx(device_index):
         L.check(L.load().kge_ctx_create(device_index, C.byref(h)))
         if os.environ.get("KGE_RANK_TC_PASSES") is not None:  # A/B switch: MMAs per K step of the ranking GEMM (3 | 2)
             L.check(L.load().kge_set_option(h, 6, int(os.environ["KGE_RANK_TC_PASSES"])))
+        if os.environ.get("KGE_PRE_EARLY") is not None:          # A/B switch: look-ahead grouping beside the step kernel
+            L.check(L.load().kge_set_option(h, 8, int(os.environ["KGE_PRE_EARLY"])))
         if os.environ.get("KGE_CLUSTER_GROUP") is not None:      # A/B switch: one-kernel cluster grouping
             L.check(L.load().kge_set_option(h, 7, int(os.environ["KGE_CLUSTER_GROUP"])))
         if os.environ.get("KGE_RING_SLOTS") is not None:      # A/B switch: depth of the step kernel's TMA row ring

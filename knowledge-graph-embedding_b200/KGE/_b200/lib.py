@@ -20,6 +20,7 @@ OPT_RING_SLOTS = 4
 OPT_GRAPH_PROFILE = 5
 OPT_RANK_TC_PASSES = 6
 OPT_CLUSTER_GROUP = 7
+OPT_PRE_EARLY = 8
 N_PHASES = 10
 PHASES = ["constraint", "step", "reduce", "sort", "update", "rank", "rank_gemm", "rank_fix", "apply", "barrier"]
 PEER_DEAD = 0xdead

@@ -41,7 +41,8 @@ extern "C" int kge_ctx_create(int device, kge_ctx** out) {
   KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_mid, cudaEventDisableTiming));
   KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_heavy, cudaEventDisableTiming));
-  KGE_CUDA_OK(cudaStreamCreateWithPriority(&c->pre_stream, cudaStreamNonBlocking, prio_greatest));
+  // the look-ahead grouping has a whole step of slack: lowest priority, it fills what the step and update kernels leave
+  KGE_CUDA_OK(cudaStreamCreateWithPriority(&c->pre_stream, cudaStreamNonBlocking, prio_least));
   KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_pre_fork, cudaEventDisableTiming));
   KGE_CUDA_OK(cudaEventCreateWithFlags(&c->ev_pre_done, cudaEventDisableTiming));
   KGE_CUDA_OK(cudaMalloc(&c->dyn, 64));
@@ -87,6 +88,7 @@ extern "C" int kge_set_option(kge_ctx* ctx, int option, int value) {
     case KGE_OPT_GRAPH_PROFILE: c->opt_graph_profile = value; return KGE_OK;
     case KGE_OPT_RANK_TC_PASSES: c->opt_tc_passes = value; return KGE_OK;
     case KGE_OPT_CLUSTER_GROUP: c->opt_cluster_group = value; return KGE_OK;
+    case KGE_OPT_PRE_EARLY: c->opt_pre_early = value; return KGE_OK;
     default: set_error("unknown option %d", option); return KGE_EINVAL;
   }
 }

@@ -68,6 +68,7 @@ struct kge_ctx_impl {
   unsigned gev_mask = 0;
   int opt_graph_profile = 0;
   int opt_cluster_group = 0;      // kge_set_option(KGE_OPT_CLUSTER_GROUP): grouping by k_group_cluster (one kernel, one cluster)
+  int opt_pre_early = 1;          // kge_set_option(KGE_OPT_PRE_EARLY): 1 = the look-ahead grouping starts beside the step kernel
   int opt_tc_passes = 3;          // kge_set_option(KGE_OPT_RANK_TC_PASSES): MMAs per K step of the ranking GEMM (3 or 2)
   DynScal* dyn = nullptr;         // device; used only while `capturing` (kge_step_graph_create)
   int capturing = 0;              // the call is being captured into a CUDA graph: per-step scalars come from `dyn`
