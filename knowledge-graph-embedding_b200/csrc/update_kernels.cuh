@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(256) k_segments(const uint32_t* __restrict__ k
 // records in flight: light rows (a handful of records) / heavy slices (hundreds: the adds are a serial
 // chain by definition, so the only lever is how many row loads are outstanding)
 template <int CPL> struct RecDepth {
-  static constexpr int LIGHT = CPL <= 2 ? 4 : (CPL == 4 ? 2 : 1);
+  static constexpr int LIGHT = CPL <= 2 ? 2 : (CPL == 4 ? 2 : 1);
   static constexpr int HEAVY = CPL == 1 ? 16 : (CPL == 2 ? 8 : (CPL == 4 ? 4 : 2));
 };
 __device__ __forceinline__ float4 scale4(float s, float4 a) {
@@ -537,11 +537,13 @@ __device__ __forceinline__ void adam_row(const UpdateParams& p, const UpdateTabl
 // MODE 0: fused step.  MODE 3: data-parallel gradient half (row sum -> every T.peer destination, tables untouched).
 // MODE 4: data-parallel apply half (gradient = sum of the T.peer rows, no records).
 template <int CPL, int MODE>
-__global__ void __launch_bounds__(64, CPL <= 2 ? 16 : 1) k_update_fast(const UpdateParams p) {
+__global__ void __launch_bounds__(64, CPL <= 2 ? 18 : 1) k_update_fast(const UpdateParams p) {
   const int lane = threadIdx.x & 31;
   const int64_t gw = (int64_t) blockIdx.x * 2 + (threadIdx.x >> 5);
   if (gw >= p.total_rows) return;
-  int64_t row = gw;
+  // last table first: the relation rows (few rows, many records each: the long-running warps) start at once
+  // instead of forming the kernel's tail behind thousands of short entity rows
+  int64_t row = p.total_rows - 1 - gw;
   int j = 0;
   while (j < p.n_tabs - 1 && row >= p.tab[j].rows) { row -= p.tab[j].rows; ++j; }
   const UpdateTable& T = p.tab[j];
