@@ -456,7 +456,8 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   const bool pre_hit = can_pre && pre.valid && pre.triples == triples && pre.B == B && pre.seed == seed && pre.step == step &&
                        pre.ws == ws && pre.i_base == (dp ? dp->i_base : 0) && pre.k == k && pre.n_ent == cfg->n_ent &&
                        pre.side == cfg->corrupt_side && pre.sampler == cfg->sampler && pre.graph == ctx->capturing;
-  const int gs = pre_hit ? pre.set : (pre.valid ? 1 - pre.set : 0);
+  // steps that span several calls (sharded: lookup / grad / apply) or never look ahead always use set 0
+  const int gs = !can_pre ? 0 : (pre_hit ? pre.set : (pre.valid ? 1 - pre.set : 0));
   if (!pre_hit && pre.valid && is_train && !pre.graph && !ctx->capturing)   // a grouped batch nobody asked for: its chain
     KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_pre_done, 0));               // must finish before its set is reused
   if (is_train) pre.valid = false;

@@ -142,3 +142,26 @@ def test_graph_and_lookahead_calls_interleaved():
             got = float(G.launch(Xd[i], i, next_triples=nxt).item())
         assert got == want, (i, got, want)
     _assert_same(_state(plain), _state(mix), "interleaved")
+
+
+def test_pending_lookahead_does_not_disturb_sharded_or_lazy_steps():
+    """A look-ahead batch left pending by one engine (the context is shared per device) must not move the grouping
+    set of steps that span several calls: sharded lookup / grad / apply, row-lazy steps (bench.py runs C2 with
+    look-ahead, then C5 sharded, in one process)."""
+    import test_gpu_shard as TS
+    from KGE._b200 import shard as SH
+    case = CASES[1]
+    Xs = [x.cuda() for x in _batches(3, 64)]
+    ahead = _engine(case)
+    scase = TS.CASES[0]
+    model, score, loss, con, d, k, side = scase
+    B = 64
+    batches = TS._batches(np.random.default_rng(3), 4, B)
+    _, _, lazy_eng = make_pair(model, TS.N, TS.R, d, score=score, loss=loss, k=k, side=side, constraint=con, lazy=True)
+    ranks = TS._sharded(scase, 1, B)
+    for step, X in enumerate(batches):
+        ahead.train_step(Xs[step % 3], 7, step, next_triples=Xs[(step + 1) % 3])      # leaves a grouped batch pending
+        l_ref = lazy_eng.train_step(X, 5, step)
+        ahead.train_step(Xs[step % 3], 7, 100 + step, next_triples=Xs[(step + 1) % 3])
+        l_sh = SH.emulate_step(ranks, [X], 5, step, B, [0])
+        assert float(l_ref.item()) == float(l_sh.item()), step
