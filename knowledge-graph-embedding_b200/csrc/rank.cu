@@ -4,6 +4,7 @@
 #include "rank_mat_kernels.cuh"
 #include "rank_dot_host.cuh"
 #include "rank_lp_tile.cuh"
+#include "rank_proj_tile.cuh"
 #include <stdlib.h>
 
 namespace kge {
@@ -21,6 +22,11 @@ size_t rank_workspace_bytes(const kge_cfg* cfg, int64_t Q) {
     LpWs L;
     layout_lp_ws(cfg, Q, L);
     return L.total;
+  }
+  if (rank_proj_eligible(cfg)) {
+    ProjWs L;
+    layout_proj_ws(cfg, Q, cfg->n_ent, L);
+    return L.total_max;
   }
   return 256;
 }
@@ -93,6 +99,14 @@ extern "C" int kge_rank(kge_ctx* ctx_, const kge_cfg* cfg, const kge_tables* tab
     if (int rc = rank_lp_tiled(cfg, tables, queries, Q, side, filter, ent_lo, ent_hi, count_out, ws, ws_bytes,
                                (cudaStream_t) stream)) return rc;
     ptl.end(5);
+    return KGE_OK;
+  }
+  if (rank_proj_eligible(cfg) && !force_generic_rank()) {
+    PhaseTimer ptp(ctx, (cudaStream_t) stream);
+    ptp.begin(5);
+    if (int rc = rank_proj_tiled(ctx, cfg, tables, queries, Q, side, filter, ent_lo, ent_hi, count_out, ws, ws_bytes,
+                                 (cudaStream_t) stream)) return rc;
+    ptp.end(5);
     return KGE_OK;
   }
   const bool mat = is_matrix_model(cfg->model);

@@ -177,3 +177,46 @@ def test_lp_tile_rank_equals_generic(model, score, d, n_ent, side):
         oracle_rank_check(band, ref, W, Xq[qi], side, pos, int(t_flt[qi]) + 1, qi)
     print(model, score, side, band.summary())
     assert band.used <= 4, band.summary()
+
+
+@pytest.mark.parametrize("model,score,d,dr,n_ent,side", [
+    ("TransH", "l2pow", 50, None, 1500, "t"), ("TransH", "l1", 37, None, 700, "h"),
+    ("TransD", "l2pow", 50, 30, 1500, "h"), ("TransD", "l1", 64, 64, 900, "t"), ("TransD", "l2", 33, 41, 600, "t"),
+    ("TransR", "l2pow", 40, 24, 1000, "t"), ("TransR", "l1", 24, 40, 700, "h"), ("TransR", "l2", 160, 160, 400, "h"),
+    ("SE", "l1", 24, None, 900, "h"), ("SE", "l2", 50, None, 600, "t"), ("SE", "linf", 20, None, 500, "t"),
+    ("TransH", "l3", 24, None, 400, "t"),
+])
+def test_projected_table_rank_equals_generic(model, score, d, dr, n_ent, side):
+    """Per-relation projected candidate tables + the Lp tile kernel (csrc/rank_proj_tile.cuh) against the
+    warp-per-(query, candidate) kernel: exact fp32 rankings in different evaluation orders, so only candidates
+    within rounding of the true score may move; shards add up exactly; filtered <= raw; oracle ranks on a sample."""
+    import os
+    from KGE._b200.filter import build_filter
+    rng = np.random.default_rng(23)
+    ref, W, eng = make_pair(model, n_ent, R, d, dr, score=_score_for(model, score), loss=LOSSES["hinge"])
+    pos = rand_triples(rng, 20000, n_ent, R)
+    Xq = pos[:700].copy()
+    Xq[::4] = rand_triples(rng, len(Xq[::4]), n_ent, R)
+    Xq[Xq[:, 1] == 3, 1] = 4                                 # a relation no query asks for
+    off, ids = build_filter(pos, Xq, side, n_ent, eng.device)
+    s = 0 if side == "h" else 1
+    t_raw = eng.rank_counts(Xq, s).cpu().numpy()
+    t_flt = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+    os.environ["KGE_RANK_GENERIC"] = "1"
+    try:
+        g_raw = eng.rank_counts(Xq, s).cpu().numpy()
+        g_flt = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+    finally:
+        os.environ.pop("KGE_RANK_GENERIC")
+    for a, b in ((t_raw, g_raw), (t_flt, g_flt)):
+        diff = np.abs(a.astype(np.int64) - b)
+        assert diff.max() <= 2 and (diff > 0).mean() <= 0.01, (diff.max(), (diff > 0).mean())
+    assert (t_flt <= t_raw).all() and (t_flt >= 0).all()
+    parts = sum(eng.rank_counts(Xq, s, off, ids, ent_lo=lo, ent_hi=hi).cpu().numpy()
+                for lo, hi in [(0, n_ent // 3), (n_ent // 3, n_ent // 3 + 77), (n_ent // 3 + 77, n_ent)])
+    assert np.array_equal(parts, t_flt)
+    band = RankBand()
+    for qi in range(40):
+        oracle_rank_check(band, ref, W, Xq[qi], side, pos, int(t_flt[qi]) + 1, qi)
+    print(model, score, side, band.summary())
+    assert band.used <= 4, band.summary()
