@@ -18,6 +18,7 @@
 // and the true entity never beats itself.  Round 1 scored these models one warp per (query, candidate) with a
 // full projection per pair (TransD 233 K, TransR 29 K queries/s).
 #pragma once
+#include <stdlib.h>
 #include "host_common.cuh"
 #include "rank_lp_tile.cuh"
 #include "rank_mat_kernels.cuh"
@@ -188,6 +189,102 @@ __global__ void __launch_bounds__(256) k_proj_table_mat(const ProjParams p, int 
     sstore(row, p.P + ((int64_t) rl * p.span_pad + el) * p.ldp, p.dout, lane);
   }
 }
+// The same rows as an fp32 register-tiled GEMM per relation: C[e][n] = sum_k E[e][k] B_r[k][n], one thread per
+// element, k ascending from acc = 0 with fmaf — the evaluation order of matvec_rowin / matvec_colin, so every raw
+// element equals proj_fwd's bit for bit (k_proj_queries_mat keeps computing the queries' rows by proj_fwd itself).
+// blockIdx = (entity tile, relation of the chunk, 128-column block).  TransR's clip and + r follow in k_proj_post.
+template <class M>
+__global__ void __launch_bounds__(LP_THREADS) k_proj_gemm(const ProjParams p) {
+  __shared__ __align__(16) float sA[LP_DK][LP_T];
+  __shared__ __align__(16) float sB[LP_DK][LP_T];
+  const int rl = blockIdx.y;
+  const int64_t r = p.rel0 + rl;
+  if (p.goff[r + 1] == p.goff[r]) return;
+  const ModelDev& md = p.md;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int64_t span = p.ent_hi - p.ent_lo, e0 = (int64_t) blockIdx.x * LP_T;
+  const int n0 = blockIdx.z * LP_T;
+  const int din = M::d_in(md), dout = M::d_out(md);
+  MatCtx cx;
+  mat_ctx_global<M>(md, r, cx);
+  const float* Mat = (M::TWO_MATS && p.side != KGE_SIDE_H) ? cx.M1 : cx.M0;
+  const int ldm = cx.ld0;
+  constexpr bool TR = M::KIND == KGE_SE;                 // SE: out[n] = sum_k M[n][k] e[k];  TransR: sum_k e[k] M[k][n]
+  const float* Et = md.t[KGE_T_ENT].w + p.ent_lo * (int64_t) md.t[KGE_T_ENT].ld;
+  const int lde = md.t[KGE_T_ENT].ld;
+  float acc[8][8];
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int b = 0; b < 8; ++b) acc[a][b] = 0.f;
+  for (int k0 = 0; k0 < din; k0 += LP_DK) {
+    __syncthreads();
+    for (int it = tid; it < LP_T * (LP_DK / 4); it += LP_THREADS) {
+      const int row = it % LP_T, c4 = it / LP_T;
+      const int k = k0 + 4 * c4;
+      float4 v = f4zero();
+      if (e0 + row < span && k < din) v = *reinterpret_cast<const float4*>(Et + (e0 + row) * (int64_t) lde + k);   // rows are zero padded to lde
+      sA[4 * c4 + 0][row] = v.x; sA[4 * c4 + 1][row] = v.y; sA[4 * c4 + 2][row] = v.z; sA[4 * c4 + 3][row] = v.w;
+    }
+    for (int it = tid; it < LP_T * LP_DK; it += LP_THREADS) {
+      const int n = it % LP_T, kk = it / LP_T;
+      const int k = k0 + kk, col = n0 + n;
+      float v = 0.f;
+      if (k < din && col < dout) v = TR ? Mat[(int64_t) col * ldm + k] : Mat[(int64_t) k * ldm + col];
+      sB[kk][n] = v;
+    }
+    __syncthreads();
+    const int kn = (din - k0 < LP_DK) ? din - k0 : LP_DK;
+    for (int j = 0; j < kn; ++j) {
+      const float4 aa = *reinterpret_cast<const float4*>(&sA[j][ty * 4]), ab = *reinterpret_cast<const float4*>(&sA[j][64 + ty * 4]);
+      const float4 ba = *reinterpret_cast<const float4*>(&sB[j][tx * 4]), bb = *reinterpret_cast<const float4*>(&sB[j][64 + tx * 4]);
+      const float av[8] = {aa.x, aa.y, aa.z, aa.w, ab.x, ab.y, ab.z, ab.w};
+      const float bv[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+      for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < 8; ++b) acc[a][b] = fmaf(av[a], bv[b], acc[a][b]);
+    }
+  }
+  float* P = p.P + ((int64_t) rl * p.span_pad) * p.ldp;
+#pragma unroll
+  for (int a = 0; a < 8; ++a) {
+    const int64_t el = e0 + ((a < 4) ? ty * 4 + a : 64 + ty * 4 + (a - 4));
+    if (el >= span) continue;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int col = n0 + h * 64 + tx * 4;
+      if (col < p.ldp)                                   // columns dout .. ldp are zeros (B is zero there)
+        *reinterpret_cast<float4*>(P + el * p.ldp + col) = make_float4(acc[a][4 * h], acc[a][4 * h + 1], acc[a][4 * h + 2], acc[a][4 * h + 3]);
+    }
+  }
+}
+// TransR: c = clip1(raw), x = c + r — by proj_fwd's own clip on the raw row, warp per (relation, candidate)
+template <class M, int NV>
+__global__ void __launch_bounds__(256) k_proj_post(const ProjParams p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t span = p.ent_hi - p.ent_lo;
+  const int64_t nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
+  const bool want_x = p.side == KGE_SIDE_H;
+  for (int64_t w = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < span * p.n_rel_chunk; w += nw) {
+    const int rl = (int) (w / span);
+    const int64_t el = w - (int64_t) rl * span;
+    const int64_t r = p.rel0 + rl;
+    if (p.goff[r + 1] == p.goff[r]) continue;
+    float* row = p.P + ((int64_t) rl * p.span_pad + el) * p.ldp;
+    Row<NV> c;
+    sload(c, row, p.dout, lane);
+    clip1(c, p.md.constraint != 0);
+    if (want_x) {
+      Row<NV> Rv;
+      sload(Rv, p.md.t[KGE_T_REL_A].w + r * (int64_t) p.md.t[KGE_T_REL_A].ld, p.dout, lane);
+#pragma unroll
+      for (int u = 0; u < NV; ++u) c.v[u] = c.v[u] + Rv.v[u];
+    }
+    sstore(c, row, p.dout, lane);
+  }
+}
+
 template <class M, int NV, int KIND>
 __global__ void __launch_bounds__(256) k_proj_queries_mat(const ProjParams p, int dpad) {
   extern __shared__ float4 smem4[];
@@ -345,7 +442,13 @@ inline int rank_proj_chunk(const ProjParams& p, int64_t span, int sm_count, size
   if (blocks > (int64_t) sm_count * 32) blocks = (int64_t) sm_count * 32;
   const unsigned qblocks = (unsigned) ((p.Q + 7) / 8);
   if constexpr (MAT) {
-    k_proj_table_mat<M, NV><<<(unsigned) blocks, 256, msmem, st>>>(p, dpad);
+    if (getenv("KGE_PROJ_MATVEC")) {                     // A/B switch: the warp-per-row table of the first version
+      k_proj_table_mat<M, NV><<<(unsigned) blocks, 256, msmem, st>>>(p, dpad);
+    } else {
+      const dim3 gg((unsigned) (p.span_pad / LP_T), (unsigned) p.n_rel_chunk, (unsigned) ((p.dout + LP_T - 1) / LP_T));
+      k_proj_gemm<M><<<gg, LP_THREADS, 0, st>>>(p);
+      if (M::KIND == KGE_TRANSR) k_proj_post<M, NV><<<(unsigned) blocks, 256, 0, st>>>(p);
+    }
     k_proj_queries_mat<M, NV, KIND><<<qblocks, 256, msmem, st>>>(p, dpad);
   } else {
     k_proj_table<M, NV><<<(unsigned) blocks, 256, 0, st>>>(p);

@@ -74,8 +74,8 @@ run("C1 TransE d=50 L1 hinge 't' k=1 B=65536", "TransE", 14505, 237, 50, None, O
 run("C2 DistMult d=200 BCE 'h+t' k=64 B=1024", "DistMult", 14951, 1345, 200, None, None, O.BinaryCrossEntropyLoss(), 64, "h+t", 1024, evalQ=16384)
 run("C3 RotatE d=500 L1 self-adv 'h+t' k=256 B=1024", "RotatE", 14505, 237, 500, None, O.LpDistance(1),
     O.SelfAdversarialNegativeSamplingLoss(3.0, 1.0), 256, "h+t", 1024, steps=20, evalQ=2048)
-run("C4 TransR d=100 L2^2 hinge typed(3) 'h+t' k=10 B=1024", "TransR", 14505, 237, 100, 100, O.LpDistancePow(2), hinge, 10, "h+t", 1024, typed=3, evalQ=2048)
-run("C4 TransD d=100 L2^2 hinge typed(32) 'h+t' k=10 B=1024", "TransD", 14505, 237, 100, 100, O.LpDistancePow(2), hinge, 10, "h+t", 1024, typed=32, evalQ=2048)
+run("C4 TransR d=100 L2^2 hinge typed(3) 'h+t' k=10 B=1024", "TransR", 14505, 237, 100, 100, O.LpDistancePow(2), hinge, 10, "h+t", 1024, typed=3, evalQ=16384)
+run("C4 TransD d=100 L2^2 hinge typed(32) 'h+t' k=10 B=1024", "TransD", 14505, 237, 100, 100, O.LpDistancePow(2), hinge, 10, "h+t", 1024, typed=32, evalQ=16384)
 # C5 shape at one GPU's share: 1/5 of the entities (1 M x 128, w + m + v = 1.5 GB), B = 65536 / 8
 # (C5 itself is bench.py's c5 leg: row-lazy / sharded tables)
 if False: run("C5-lite TransE d=128 L1 hinge 'h+t' k=32 B=8192 N=1M constraint=False", "TransE", 1000000, 1000, 128, None, O.LpDistance(1), hinge,

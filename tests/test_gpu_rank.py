@@ -215,6 +215,14 @@ def test_projected_table_rank_equals_generic(model, score, d, dr, n_ent, side):
     parts = sum(eng.rank_counts(Xq, s, off, ids, ent_lo=lo, ent_hi=hi).cpu().numpy()
                 for lo, hi in [(0, n_ent // 3), (n_ent // 3, n_ent // 3 + 77), (n_ent // 3 + 77, n_ent)])
     assert np.array_equal(parts, t_flt)
+    if model in ("TransR", "SE"):
+        # the table rows come from a register-tiled GEMM whose every element is proj_fwd's own fmaf chain:
+        # counts equal the warp-per-row table's bit for bit
+        os.environ["KGE_PROJ_MATVEC"] = "1"
+        try:
+            assert np.array_equal(eng.rank_counts(Xq, s, off, ids).cpu().numpy(), t_flt)
+        finally:
+            os.environ.pop("KGE_PROJ_MATVEC")
     band = RankBand()
     for qi in range(40):
         oracle_rank_check(band, ref, W, Xq[qi], side, pos, int(t_flt[qi]) + 1, qi)
