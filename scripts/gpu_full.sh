@@ -13,3 +13,4 @@ ncu --set full --clock-control none --import-source on -k regex:'k_step|k_update
 ncu --set full --clock-control none --import-source on -k regex:'k_rank_dot' -c 4 -o gpurun_out/${TAG}_prof_rank \
   python bench.py --steps 6 --warmup 3 --cpu-steps 1 --cpu-queries 2 > gpurun_out/${TAG}_ncu_rank.log 2>&1
 tail -2 gpurun_out/${TAG}_ncu.log
+timeout 600 python scripts/bench_configs.py > gpurun_out/${TAG}_configs.jsonl 2> gpurun_out/${TAG}_configs.err; wc -l gpurun_out/${TAG}_configs.jsonl
