@@ -19,6 +19,7 @@ struct MatStepParams {
   int ldp;
   int stage;          // matrices fit in shared memory
   int dpad;           // floats per scratch / shared-projection vector (multiple of 4)
+  int proj;           // TransR / SE: the phase-structured kernel (step_proj_kernels.cuh) instead of k_step_mat
 };
 
 constexpr int MAT_ACC_ROWS = 5;   // GH, GT, GR, SPH, SPT

@@ -2,6 +2,7 @@
 #pragma once
 #include "step_launch.cuh"
 #include "step_mat_kernels.cuh"
+#include "step_proj_kernels.cuh"
 
 namespace kge {
 
@@ -15,6 +16,16 @@ inline size_t step_mat_smem_bytes(int nv, int k, int dpad, bool train, bool stag
 
 template <class M, int NV, bool TRAIN>
 int launch_step_mat_one(const MatStepParams& q, const StepLaunch& L) {
+  if constexpr (!M::BILINEAR) {
+    if (q.proj) {
+      auto kp = k_step_proj<M, NV, TRAIN>;
+      if (L.smem > 48 * 1024)
+        KGE_CUDA_OK(cudaFuncSetAttribute(kp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) L.smem));
+      kp<<<(unsigned) L.grid, STEP_THREADS, L.smem, L.stream>>>(q);
+      KGE_CUDA_OK(cudaGetLastError());
+      return KGE_OK;
+    }
+  }
   auto kern = k_step_mat<M, NV, TRAIN>;
   if (L.smem > 48 * 1024)
     KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) L.smem));

@@ -4,6 +4,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include "host_common.cuh"
+#include <stdlib.h>
 #include "step_launch.cuh"
 #include "update_kernels.cuh"
 #include "group_kernels.cuh"
@@ -772,6 +773,12 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     mq.stage = SL.smem <= (size_t) ctx->smem_optin;
     if (!mq.stage) SL.smem = step_mat_smem_bytes(nv, k, mq.dpad, SL.train, false, n_mats, mat_rows(cfg), mat_cols(cfg));
     KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step_mat needs %zu B shared memory", SL.smem);
+    // TransR / SE: four vectors per warp through every mat-vec (k_step_proj) when the positive's rows fit shared memory
+    mq.proj = 0;
+    if (cfg->model != KGE_RESCAL && k + 2 < PJ_MAX_ROWS && !getenv("KGE_STEP_MAT_OLD")) {
+      const size_t pb = sizeof(float) * step_proj_smem_floats(nv, k, mq.dpad, SL.train, n_mats, mat_rows(cfg), mat_cols(cfg));
+      if (pb <= (size_t) ctx->smem_optin) { mq.proj = 1; SL.smem = pb; }
+    }
     if (int rc2 = fork_side()) return rc2;      // after the last argument check
     pt.begin(1);
     switch (cfg->model) {

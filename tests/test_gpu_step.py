@@ -298,3 +298,36 @@ def test_shadow_table_is_bit_identical_to_constraint_pass(model, score):
     assert losses[0] == losses[1]
     for s in outs[0]:
         assert torch.equal(outs[0][s], outs[1][s]), f"slot {s}"
+
+
+@pytest.mark.parametrize("model,d,dr,k,side,loss", [
+    ("TransR", 100, 100, 10, "h+t", "hinge"), ("TransR", 40, 70, 3, "h", "logistic"), ("TransR", 70, 40, 5, "t", "selfadv"),
+    ("TransR", 50, 30, 33, "h+t", "selfadv"), ("SE", 50, 50, 6, "h+t", "bce"), ("SE", 33, 33, 2, "t", "hinge"),
+    ("SE", 24, 24, 9, "h", "logistic"), ("TransR", 160, 130, 4, "h+t", "hinge"),
+])
+def test_projection_step_kernel_equals_per_negative_kernel(model, d, dr, k, side, loss):
+    """k_step_proj (four vectors per warp through every mat-vec, csrc/step_proj_kernels.cuh) against k_step_mat
+    (KGE_STEP_MAT_OLD=1): every projection is the same fmaf chain, only the fixed order of the sums over a
+    positive's negatives differs — losses to rounding, weights at the parity tolerance, validation batches too."""
+    import os
+    score = {"TransR": "l2pow", "SE": "l1"}[model]
+    outs = []
+    for old in (False, True):
+        if old:
+            os.environ["KGE_STEP_MAT_OLD"] = "1"
+        try:
+            rng = np.random.default_rng(29)
+            ref, W, eng = make_pair(model, N, R, d, dr, score=_score_mat(model, score), loss=LOSSES[loss], k=k, side=side)
+            losses = []
+            for step in range(3):
+                X = rand_triples(rng, 72, N, R)
+                l, neg = eng.train_step(X, 4, step, is_train=step != 1, want_negatives=True)
+                losses.append((float(l.item()), neg.cpu().numpy().copy()))
+            outs.append((losses, tables_of(eng, model)))
+        finally:
+            os.environ.pop("KGE_STEP_MAT_OLD", None)
+    for (la, na), (lb, nb) in zip(outs[0][0], outs[1][0]):
+        assert np.array_equal(na, nb)
+        assert abs(la - lb) <= 2e-6 * max(1.0, abs(lb)), (la, lb)
+    for kk in outs[0][1]:
+        assert_weights_close(outs[0][1][kk], outs[1][1][kk], 1e-3, 2, kk)
