@@ -113,17 +113,20 @@ __device__ __forceinline__ void acc_to_row(Row<NV>& o, const float (&a)[4 * NV],
 
 // shared memory (floats) of k_step_proj, see the carve-up in the kernel
 inline size_t step_proj_smem_floats(int nv, int k, int dpad, bool train, int n_mats, int mrows, int mcols) {
-  size_t f = 2 * (size_t) (k + 2) * dpad                 // s_E, s_C
-           + (size_t) ((k + 2 + 3) & ~3)                 // s_n
-           + (size_t) ((k + 1 + 3) & ~3)                 // s_score
-           + STEP_WARPS * 8 + 2 * PJ_MAX_ROWS;           // s_red, row lists (as ints)
-  if (train) f += 2 * (size_t) (k + 1) * dpad + (size_t) STEP_WARPS * MAT_ACC_ROWS * nv * WARP * 4;   // s_P, s_acc
-  f += (size_t) n_mats * mrows * (mcols | 1);
-  return f;
+  size_t rows = 2 * (size_t) (k + 2) * dpad;             // s_E, s_C
+  if (train) {
+    rows += 2 * (size_t) (k + 1) * dpad;                 // s_P
+    const size_t acc = (size_t) STEP_WARPS * MAT_ACC_ROWS * nv * WARP * 4;   // s_acc lies over the rows once they are dead
+    rows = rows > acc ? rows : acc;
+  }
+  return rows + (size_t) ((k + 2 + 3) & ~3)              // s_n
+       + (size_t) ((k + 1 + 3) & ~3)                     // s_score
+       + STEP_WARPS * 8 + 2 * PJ_MAX_ROWS                // s_red, row lists (as ints)
+       + (size_t) n_mats * mrows * (mcols | 1);
 }
 
 template <class M, int NV, bool TRAIN>
-__global__ void __launch_bounds__(STEP_THREADS) k_step_proj(const MatStepParams q) {
+__global__ void __launch_bounds__(STEP_THREADS, NV == 1 ? 3 : 1) k_step_proj(const MatStepParams q) {
   static_assert(!M::BILINEAR, "projection models only");
   extern __shared__ float4 smem4[];
   const StepParams& p = q.s;
@@ -141,24 +144,50 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_proj(const MatStepParams 
 
   // ---- shared-memory carve-up (every array starts on a 16-byte boundary) ----------------
   float* sm = reinterpret_cast<float*>(smem4);
-  float* s_E = sm;                                sm += (size_t) nrow * dpad;      // raw entity rows: 0 = h, 1 = t, 2 + c = negative c
-  float* s_C = sm;                                sm += (size_t) nrow * dpad;      // their projections
+  float4* s_acc = reinterpret_cast<float4*>(sm);                                   // P6 only: over the rows of P0 - P5
+  {
+    size_t rows = 2 * (size_t) nrow * dpad + (TRAIN ? 2 * (size_t) ntri * dpad : 0);
+    const size_t acc = TRAIN ? (size_t) STEP_WARPS * MAT_ACC_ROWS * NV * WARP * 4 : 0;
+    sm += rows > acc ? rows : acc;
+  }
+  float* s_E = reinterpret_cast<float*>(smem4);                                    // raw entity rows: 0 = h, 1 = t, 2 + c = negative c
+  float* s_C = s_E + (size_t) nrow * dpad;                                         // their projections
+  float* s_P = s_C + (size_t) nrow * dpad;                                         // pair vectors [side][triple] (TRAIN)
   float* s_n = sm;                                sm += (nrow + 3) & ~3;           // clip norms (0 = not clipped)
   float* s_score = sm;                            sm += (ntri + 3) & ~3;           // triple 0 = positive, 1 + c = negative c
   float* s_red = sm;                              sm += STEP_WARPS * 8;
   int* s_list = reinterpret_cast<int*>(sm);       sm += 2 * PJ_MAX_ROWS;           // forward row lists: [0] head role, [1] tail role
-  float* s_P = sm;                                sm += TRAIN ? 2 * (size_t) ntri * dpad : 0;   // pair vectors [side][triple]
-  float4* s_acc = reinterpret_cast<float4*>(sm);  sm += TRAIN ? STEP_WARPS * MAT_ACC_ROWS * NV * WARP * 4 : 0;
   float* s_mat = sm;
 
   const int mrows = md.d_ent, mcols = TR ? md.d_rel : md.d_ent, lds = mcols | 1;
   {
     const float* g0 = md.t[s0].w + r * (int64_t) md.t[s0].ld;
     const float* g1 = M::TWO_MATS ? md.t[KGE_T_REL_B].w + r * (int64_t) md.t[KGE_T_REL_B].ld : nullptr;
-    for (int e = threadIdx.x; e < mrows * mcols; e += STEP_THREADS) {
-      const int a = e / mcols, b = e - a * mcols;
-      s_mat[a * lds + b] = __ldg(g0 + e);
-      if (M::TWO_MATS) s_mat[mrows * lds + a * lds + b] = __ldg(g1 + e);
+    if ((mcols & 3) == 0) {          // 128-bit loads (matrix rows stay 16-byte aligned), one division per thread
+      const int c4 = mcols >> 2, n4 = mrows * c4;
+      int a = threadIdx.x / c4, b = threadIdx.x - a * c4;
+      const int da = STEP_THREADS / c4, db = STEP_THREADS - da * c4;
+      for (int e = threadIdx.x; e < n4; e += STEP_THREADS) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(g0) + e);
+        float* d = s_mat + a * lds + 4 * b;
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        if (M::TWO_MATS) {
+          const float4 w = __ldg(reinterpret_cast<const float4*>(g1) + e);
+          float* d1 = d + mrows * lds;
+          d1[0] = w.x; d1[1] = w.y; d1[2] = w.z; d1[3] = w.w;
+        }
+        a += da; b += db;
+        if (b >= c4) { b -= c4; ++a; }
+      }
+    } else {
+      int a = threadIdx.x / mcols, b = threadIdx.x - a * mcols;
+      const int da = STEP_THREADS / mcols, db = STEP_THREADS - da * mcols;
+      for (int e = threadIdx.x; e < mrows * mcols; e += STEP_THREADS) {
+        s_mat[a * lds + b] = __ldg(g0 + e);
+        if (M::TWO_MATS) s_mat[mrows * lds + a * lds + b] = __ldg(g1 + e);
+        a += da; b += db;
+        if (b >= mcols) { b -= mcols; ++a; }
+      }
     }
   }
   const float* M0 = s_mat;
@@ -364,6 +393,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_proj(const MatStepParams 
     for (int u = 0; u < N_PART; ++u) s_red[warp * 8 + u] = red[u];
   }
   if (TRAIN) {
+    __syncthreads();                 // every warp is through with s_E / s_C / s_P: s_acc takes their place
     float4* mine = s_acc + (size_t) warp * MAT_ACC_ROWS * NV * WARP;
     const Row<NV>* rows[MAT_ACC_ROWS] = {&GH, &GT, &GR, &SPH, &SPT};
 #pragma unroll
