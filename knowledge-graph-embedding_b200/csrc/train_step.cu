@@ -57,7 +57,8 @@ static bool shadow_capable(const kge_ctx_impl* ctx, const kge_cfg* c, const kge_
 static int mat_rows(const kge_cfg* c) { return c->d_ent; }
 static int mat_cols(const kge_cfg* c) { return c->model == KGE_TRANSR ? c->d_rel : c->d_ent; }
 static int mat_tiles(const kge_cfg* c) {
-  return ((mat_rows(c) + MU_TILE - 1) / MU_TILE) * ((mat_cols(c) + MU_TILE - 1) / MU_TILE);
+  const int tc = mu_tile_cols(mat_cols(c));
+  return ((mat_rows(c) + MU_TILE - 1) / MU_TILE) * ((mat_cols(c) + tc - 1) / tc);
 }
 
 int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
@@ -959,7 +960,8 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     rd.rowpart = up.rowpart; rd.total_rows = up.total_rows; rd.n_tabs = up.n_tabs;
     rd.matpart = nullptr; rd.n_mat = 0; rd.mat_slot = KGE_T_REL_A; rd.mat_loss_coef = 0.f;
     if (mat) {
-      k_update_mat<1><<<mgrid, MU_THREADS, 0, st>>>(mu);
+      if (mu_tile_cols(mat_cols(cfg)) == MU_TILE) k_update_mat<1, MU_TILE><<<mgrid, MU_THREADS, 0, st>>>(mu);
+      else k_update_mat<1, 2 * MU_TILE><<<mgrid, MU_THREADS, 0, st>>>(mu);
       KGE_CUDA_OK(cudaGetLastError());
       rd.matpart = mu.part; rd.n_mat = L.n_mat_cta; rd.mat_loss_coef = cfg->constraint_weight / (float) cfg->n_rel;
     }
@@ -969,7 +971,8 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     if (!is_train) { pt.end(4); return KGE_OK; }
   }
   if (mat) {      // reads the pre-update entity rows: must precede k_update
-    k_update_mat<0><<<mgrid, MU_THREADS, 0, st>>>(mu);
+    if (mu_tile_cols(mat_cols(cfg)) == MU_TILE) k_update_mat<0, MU_TILE><<<mgrid, MU_THREADS, 0, st>>>(mu);
+    else k_update_mat<0, 2 * MU_TILE><<<mgrid, MU_THREADS, 0, st>>>(mu);
     KGE_CUDA_OK(cudaGetLastError());
   }
   if (lazy) {

@@ -10,6 +10,7 @@
 // regulariser's loss term per CTA instead of updating.  No atomics: deterministic.
 #pragma once
 #include "update_kernels.cuh"
+#include <stdlib.h>
 
 namespace kge {
 
@@ -58,20 +59,29 @@ __device__ __forceinline__ int mu_neg_c(int neg_mode, int side_mode, int j) {
   return 2 * j + (neg_mode == 2 ? 0 : 1);       // 'h+t': even c = head corruption
 }
 
-template <int MODE>
+// TC = columns per tile.  128-column tiles (a 100 x 100 matrix as 2 CTAs of 4 x 8 outputs per thread: one wave of
+// 474 CTAs instead of 1.6 waves of 948) were measured SLOWER on C4 (update phase TransR 66 -> 84 us, SE 81 -> 108 us):
+// the kernel is bound by the per-CTA chain of pair chunks, and halving the CTAs halves the chains in flight.
+// The wide instantiation stays compiled for the A/B (KGE_MU_WIDE=1).
+inline int mu_tile_cols(int cols_m) {
+  static const bool wide = getenv("KGE_MU_WIDE") != nullptr;
+  return (wide && cols_m > MU_TILE) ? 2 * MU_TILE : MU_TILE;
+}
+template <int MODE, int TC>
 __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p) {
+  constexpr int NB = TC / 16;          // output columns per thread: 4 + 4 (second set 64 columns on) for TC = 128
   __shared__ float s_row[MU_KC][MU_TILE];
-  __shared__ float s_col[MU_KC][MU_TILE];
+  __shared__ float s_col[MU_KC][TC];
   __shared__ float s_red[2][MU_THREADS / 32];
-  __shared__ int64_t s_rec[MU_KC], s_ent[MU_KC];
-  __shared__ int s_entrow[MU_KC];
+  __shared__ int64_t s_rec[2][MU_KC], s_ent[2][MU_KC];
+  __shared__ int s_entrow[2][MU_KC];
   const MatUpdTable& T = p.tab[blockIdx.z];
   const int64_t r = blockIdx.y;
-  const int tiles_c = (T.cols_m + MU_TILE - 1) / MU_TILE;
+  const int tiles_c = (T.cols_m + TC - 1) / TC;
   const int tr = blockIdx.x / tiles_c, tc = blockIdx.x % tiles_c;
   if (tr * MU_TILE >= T.rows_m) return;
   const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-  const int row0 = tr * MU_TILE, col0 = tc * MU_TILE;
+  const int row0 = tr * MU_TILE, col0 = tc * TC;
 
   const uint32_t key = p.key_base + (uint32_t) r;
   const int64_t lo = p.n_keys > 0 ? (int64_t) __ldg(p.seg_lo + key) : 0;
@@ -80,16 +90,17 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
   const int S = T.use_sh + T.use_st + n_neg;
   const int64_t n_pairs = (hi - lo) * S;
 
-  float acc[4][4];
+  float acc[4][NB];
 #pragma unroll
   for (int a = 0; a < 4; ++a)
 #pragma unroll
-    for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    for (int b = 0; b < NB; ++b) acc[a][b] = 0.f;
 
-  for (int64_t u0 = 0; u0 < n_pairs; u0 += MU_KC) {
-    // stage MU_KC pairs.  The dependent lookups (sorted position -> positive -> entity / record id) are
-    // done ONCE per pair by MU_KC threads; the 2 * MU_KC * 64 vector loads that follow are then
-    // independent of each other and stay in flight together.
+  // Software pipeline over chunks of MU_KC pairs.  The dependent lookups of a pair (sorted position -> positive ->
+  // entity / record id) are done by MU_KC threads TWO chunks ahead, the 2 * MU_KC * 64 vector loads of the next
+  // chunk are issued into registers before this chunk's FMAs, so a chunk costs one store-to-shared, its FMAs and
+  // two barriers instead of two dependent global round trips (the update of C4 TransR was latency-bound on them).
+  auto lookup = [&](int64_t u0, int buf) {
     if (threadIdx.x < MU_KC) {
       const int64_t u = u0 + threadIdx.x;
       int64_t rec = -1, ent = 0;
@@ -104,35 +115,63 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
           rec = 2 * p.B + pos * p.k + c; ent = __ldg(p.neg_ids + pos * p.k + c); ent_row = T.ent_row_neg;
         }
       }
-      s_rec[threadIdx.x] = rec; s_ent[threadIdx.x] = ent; s_entrow[threadIdx.x] = ent_row;
+      s_rec[buf][threadIdx.x] = rec; s_ent[buf][threadIdx.x] = ent; s_entrow[buf][threadIdx.x] = ent_row;
     }
-    __syncthreads();
+  };
+  constexpr int NROWV = MU_KC * MU_TILE;                          // row-vector elements of a chunk; column vectors follow
+  constexpr int NLD = MU_KC * (MU_TILE + TC) / MU_THREADS;        // vector elements per thread and chunk
+  float stage[NLD];
+  auto fetch = [&](int buf) {
 #pragma unroll
-    for (int e0 = 0; e0 < 2 * MU_KC * MU_TILE; e0 += MU_THREADS) {
-      const int e = e0 + threadIdx.x;
-      const int which = e / (MU_KC * MU_TILE);            // 0 row vectors, 1 column vectors
-      const int kk = (e / MU_TILE) % MU_KC, off = e % MU_TILE;
-      const int64_t rec = s_rec[kk];
+    for (int x = 0; x < NLD; ++x) {
+      const int e = x * MU_THREADS + threadIdx.x;
+      const int which = e >= NROWV;                       // 0 row vectors, 1 column vectors
+      const int e2 = which ? e - NROWV : e;
+      const int kk = which ? e2 / TC : e2 / MU_TILE, off = which ? e2 % TC : e2 % MU_TILE;
+      const int64_t rec = s_rec[buf][kk];
       float val = 0.f;
       if (rec >= 0) {
-        const bool from_ent = (which == 0) == (s_entrow[kk] != 0);
+        const bool from_ent = (which == 0) == (s_entrow[buf][kk] != 0);
         const int idx = (which == 0 ? row0 : col0) + off;
         const int lim = which == 0 ? T.rows_m : T.cols_m;
         if (idx < lim)
-          val = from_ent ? __ldg(p.ent_w + s_ent[kk] * (int64_t) p.ent_ld + idx) : __ldg(p.recP + rec * (int64_t) p.ldp + idx);
+          val = from_ent ? __ldg(p.ent_w + s_ent[buf][kk] * (int64_t) p.ent_ld + idx) : __ldg(p.recP + rec * (int64_t) p.ldp + idx);
       }
-      (which == 0 ? s_row : s_col)[kk][off] = val;
+      stage[x] = val;
     }
+  };
+  if (n_pairs > 0) {
+    lookup(0, 0);
     __syncthreads();
+    fetch(0);
+    lookup(MU_KC, 1);
+  }
+  int cb = 0;
+  for (int64_t u0 = 0; u0 < n_pairs; u0 += MU_KC, cb ^= 1) {
+#pragma unroll
+    for (int x = 0; x < NLD; ++x) {
+      const int e = x * MU_THREADS + threadIdx.x;
+      const int which = e >= NROWV;
+      const int e2 = which ? e - NROWV : e;
+      if (which) s_col[e2 / TC][e2 % TC] = stage[x];
+      else s_row[e2 / MU_TILE][e2 % MU_TILE] = stage[x];
+    }
+    __syncthreads();                                        // the chunk is staged; lookups of chunk + 1 are visible
+    if (u0 + MU_KC < n_pairs) {
+      fetch(cb ^ 1);                                        // next chunk's vectors, in flight under the FMAs
+      lookup(u0 + 2 * MU_KC, cb);                           // this chunk's lookup slots are free: its loads have landed
+    }
 #pragma unroll
     for (int kk = 0; kk < MU_KC; ++kk) {
-      float a4[4], b4[4];
+      float a4[4], b4[NB];
 #pragma unroll
-      for (int a = 0; a < 4; ++a) { a4[a] = s_row[kk][ty * 4 + a]; b4[a] = s_col[kk][tx * 4 + a]; }
+      for (int a = 0; a < 4; ++a) a4[a] = s_row[kk][ty * 4 + a];
+#pragma unroll
+      for (int b = 0; b < NB; ++b) b4[b] = s_col[kk][(b >> 2) * 64 + tx * 4 + (b & 3)];
 #pragma unroll
       for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(a4[a], b4[b], acc[a][b]);
+        for (int b = 0; b < NB; ++b) acc[a][b] = fmaf(a4[a], b4[b], acc[a][b]);
     }
     __syncthreads();
   }
@@ -147,8 +186,8 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
   for (int a = 0; a < 4; ++a) {
     const int ra = row0 + ty * 4 + a;
 #pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      const int cb = col0 + tx * 4 + b;
+    for (int b = 0; b < NB; ++b) {
+      const int cb = col0 + (b >> 2) * 64 + tx * 4 + (b & 3);
       if (ra < T.rows_m && cb < T.cols_m) {
         const int64_t o = (int64_t) ra * T.cols_m + cb;
         float w = wr[o];

@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from helpers import make_pair, tables_of, rand_triples, rel_err, assert_weights_close
-from oracle import ref_ops as O, ref_step as RS
+from oracle import ref_ops as O, ref_step as RS, ref_models as RM
 
 pytestmark = pytest.mark.gpu
 
@@ -331,3 +331,37 @@ def test_projection_step_kernel_equals_per_negative_kernel(model, d, dr, k, side
         assert abs(la - lb) <= 2e-6 * max(1.0, abs(lb)), (la, lb)
     for kk in outs[0][1]:
         assert_weights_close(outs[0][1][kk], outs[1][1][kk], 1e-3, 2, kk)
+
+
+def test_transr_at_the_reference_default_init():
+    """The reference initialises rel_proj to the rectangular identity (TransR.py:125-128), so after the
+    start-of-batch normalisation ||e M_r|| sits ON the clip threshold of TransR.py:187-189 and rounding decides
+    the branch (helpers.make_pair perturbs the matrices for that reason).  At the unperturbed init the clip is
+    still continuous in VALUE: losses agree to 1e-4 over three steps and every weight stays inside Adam's
+    per-step bound; how many elements leave the 1e-4 band is printed, not asserted (the gradient of the clip
+    jumps where the branch flips)."""
+    from KGE._b200 import engine as E, spec
+    rng = np.random.default_rng(31)
+    d, dr, k = 40, 24, 4
+    ref = RM.MODELS["TransR"](N, R, d, dr, score_fn=SCORES["l2pow"], loss_fn=LOSSES["hinge"], constraint=True,
+                              constraint_weight=1.0)
+    W = ref.init_weights(11)
+    eye = W.data["rel_proj"].reshape(R, d, dr)
+    assert torch.equal(eye[0], torch.eye(d, dr)), "rel_proj must start at the rectangular identity"
+    cfg = spec.make_cfg("TransR", N, R, d, dr, score_fn=SCORES["l2pow"], loss_fn=LOSSES["hinge"], negative_ratio=k,
+                        corrupt_side="h+t", constraint=True, constraint_weight=1.0, rotate_limit=ref.limit)
+    eng = E.Engine(cfg, {spec.SLOTS["TransR"][kk]: v for kk, v in W.data.items()})
+    opt = RS.TFAdam()
+    for step in range(3):
+        X = rand_triples(rng, 64, N, R)
+        ids, k_eff = RS.sample_negatives(9, step, X, k, "h+t", N)
+        l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, "h+t", True)
+        l_gpu = float(eng.train_step(X, 9, step).item())
+        assert abs(l_gpu - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, l_gpu, l_ref)
+        got = tables_of(eng, "TransR")
+        for kk, v in W.data.items():
+            diff = (got[kk].double() - torch.as_tensor(v).double()).abs()
+            scale = float(torch.as_tensor(v).abs().max()) + 1e-12
+            print("TransR identity init, step %d, %s: max|dW| %.3g, outside 1e-4: %.5f" % (
+                step, kk, float(diff.max()), float((diff > 1e-4 * scale).double().mean())))
+            assert float(diff.max()) <= (step + 1) * 1e-3 * 1.01 + 1e-6 * scale, (step, kk, float(diff.max()))
