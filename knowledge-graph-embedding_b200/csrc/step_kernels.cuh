@@ -329,6 +329,10 @@ __global__ void __launch_bounds__(StepBounds<M, NV>::THREADS, StepBounds<M, NV>:
             store_row(N.e, rt.b0, rt.row, md.rld[KGE_T_ENT], md.t[KGE_T_ENT].cols, lane); }
         }
       }
+      // the positive's rows were dead during the loop (1000-float rows: 96 registers): fetched again (L1 / L2 hits)
+      H.load(md, h, lane);
+      T.load(md, t, lane);
+      R.load(md, r, lane);
       if (TRAIN) {
 #pragma unroll
         for (int v = 0; v < NV; ++v) {

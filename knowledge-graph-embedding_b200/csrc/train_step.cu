@@ -733,6 +733,25 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
         break;
       }
     }
+    // RotatE with LpDistance(1) on wide rows: the streamed kernel (step_rot_kernels.cuh) — same arithmetic, accumulators in
+    // shared memory, two CTAs per SM where k_step's 255 registers allow one
+    bool rot_stream = false;
+    if (cfg->model == KGE_ROTATE && nv >= 4 && !sh && cfg->score == KGE_SCORE_LP && cfg->score_p == 1.0f &&
+        (cfg->corrupt_side != KGE_SIDE_HT || (p.wpp & 1) == 0) && !getenv("KGE_STEP_ROT_OLD")) {
+      // CTA size: one balanced wave when the batch allows it (as DistMult's step), else 8 warps; fewer if the rings do not fit
+      int nwp = STEP_WARPS;
+      const int64_t per_sm = (B * p.wpp + ctx->sm_count - 1) / ctx->sm_count;
+      if (per_sm <= STEP_MAX_WARPS) {
+        nwp = (int) ((per_sm + p.wpp - 1) / p.wpp) * p.wpp;
+        if (nwp > STEP_MAX_WARPS) nwp = STEP_MAX_WARPS / p.wpp * p.wpp;
+      }
+      while (nwp > p.wpp && step_rot_smem_bytes_host(nv, p.wpp, k, nwp, (int) tables->t[KGE_T_ENT].ld) > (size_t) ctx->smem_optin) nwp -= p.wpp;
+      const size_t rb = step_rot_smem_bytes_host(nv, p.wpp, k, nwp, (int) tables->t[KGE_T_ENT].ld);
+      if (rb <= (size_t) ctx->smem_optin && nwp >= p.wpp) {
+        rot_stream = true; SL.smem = rb; p.nwarps = nwp;
+        SL.grid = (B + nwp / p.wpp - 1) / (nwp / p.wpp);
+      }
+    }
     KGE_REQUIRE(SL.smem <= (size_t) ctx->smem_optin, KGE_EUNSUPPORTED, "k_step needs %zu B shared memory", SL.smem);
     if (shard_phase != 2) { if (int rc2 = fork_side()) return rc2; }      // after the last argument check
     else { pt.begin(0); if (int rc2 = launch_constrain(ctx, cp, st)) return rc2; pt.end(0); }
@@ -760,7 +779,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
       case KGE_TRANSE: rc = launch_step_transe(p, SL); break;
       case KGE_TRANSH: rc = launch_step_transh(p, SL); break;
       case KGE_TRANSD: rc = launch_step_transd(p, SL); break;
-      case KGE_ROTATE: rc = launch_step_rotate(p, SL); break;
+      case KGE_ROTATE: rc = rot_stream ? launch_step_rot(p, SL) : launch_step_rotate(p, SL); break;
       case KGE_DISTMULT: rc = launch_step_distmult(p, SL); break;
       default: set_error("model %d has no step kernel", cfg->model); rc = KGE_EUNSUPPORTED;
     }

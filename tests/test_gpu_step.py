@@ -365,3 +365,45 @@ def test_transr_at_the_reference_default_init():
             print("TransR identity init, step %d, %s: max|dW| %.3g, outside 1e-4: %.5f" % (
                 step, kk, float(diff.max()), float((diff > 1e-4 * scale).double().mean())))
             assert float(diff.max()) <= (step + 1) * 1e-3 * 1.01 + 1e-6 * scale, (step, kk, float(diff.max()))
+
+
+@pytest.mark.parametrize("d,k,side,loss,B", [
+    (300, 64, "h+t", "selfadv", 40), (300, 6, "t", "hinge", 72), (130, 64, "h+t", "bce", 33), (130, 5, "h", "logistic", 64),
+    (500, 16, "h+t", "selfadv", 24), (140, 1, "t", "hinge", 50),
+])
+def test_rotate_streamed_kernel_equals_register_kernel(d, k, side, loss, B):
+    """k_step_rot (csrc/step_rot_kernels.cuh: rows streamed chunk by chunk, accumulators in shared memory) against
+    k_step's register-resident RotatE path (KGE_STEP_ROT_OLD=1): the same expressions in the same order — losses and
+    negatives bitwise equal over train / validation / train steps, tables to rounding — and both against the oracle."""
+    import os
+    outs = []
+    for old in (False, True):
+        if old:
+            os.environ["KGE_STEP_ROT_OLD"] = "1"
+        try:
+            rng = np.random.default_rng(37)
+            ref, W, eng = make_pair("RotatE", N, R, d, None, score=SCORES["l1"], loss=LOSSES[loss], k=k, side=side)
+            opt = RS.TFAdam()
+            losses = []
+            for step in range(3):
+                X = rand_triples(rng, B, N, R)
+                l, neg = eng.train_step(X, 6, step, is_train=step != 1, want_negatives=True)
+                losses.append((float(l.item()), neg.cpu().numpy().copy()))
+                if not old:
+                    ids, k_eff = RS.sample_negatives(6, step, X, k, side, N)
+                    l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, side, step != 1)
+                    assert np.array_equal(neg.cpu().numpy(), ids)
+                    assert abs(losses[-1][0] - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, losses[-1][0], l_ref)
+            got = tables_of(eng, "RotatE")
+            if not old:
+                for kk, v in W.data.items():
+                    assert_weights_close(got[kk], v, 1e-3, 2, kk)
+            outs.append((losses, got))
+        finally:
+            os.environ.pop("KGE_STEP_ROT_OLD", None)
+    for (la, na), (lb, nb) in zip(outs[0][0], outs[1][0]):
+        assert np.array_equal(na, nb)
+        assert abs(la - lb) <= 1e-6 * max(1.0, abs(lb)), (la, lb)
+    for kk in outs[0][1]:          # same expressions; the compiler contracts a few multiply-adds differently in the two kernels
+        assert_weights_close(outs[0][1][kk], outs[1][1][kk], 1e-3, 2, "streamed vs register kernel, " + kk)
+        assert float((outs[0][1][kk] - outs[1][1][kk]).abs().max()) <= 2e-5
