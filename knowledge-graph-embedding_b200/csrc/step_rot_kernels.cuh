@@ -18,8 +18,8 @@
 //     shared memory, and a warp no longer sits out one L2 round trip per pass and negative (measured: that
 //     wait, not occupancy, was the 9 us a warp spent per negative)
 //   * CTAs of up to 14 warps sized so that the batch is ONE balanced wave (C3: 1024 positives x 2 warps = 147 CTAs)
-// Every per-element expression and every summation order is k_step's: losses agree bitwise, tables to rounding
-// (the compiler contracts a few multiply-adds differently in the two kernels)
+// Scores, loss terms and every summation order are k_step's (losses agree bitwise); the negatives' unit vectors
+// u / |u| use MUFU.RSQ instead of an IEEE square root and division, so tables agree to rounding (<= 2 ulp per element)
 // (tests/test_gpu_step.py::test_rotate_streamed_kernel_equals_register_kernel).
 #pragma once
 #include "step_kernels.cuh"
@@ -207,9 +207,11 @@ __global__ void __launch_bounds__(STEP_MAX_WARPS * WARP, 1) k_step_rot(const Ste
         if (c4 < nch) {
           const float4 xv = X.v[v];
           const float4 u = xv - Np[c4];
-          const float m0 = sqrtf(u.x * u.x + u.y * u.y), m1 = sqrtf(u.z * u.z + u.w * u.w);
-          const float i0 = m0 > 0.f ? 1.0f / m0 : 0.f, i1 = m1 > 0.f ? 1.0f / m1 : 0.f;
-          cnt += (m0 > 0.f ? 1.f : 0.f) + (m1 > 0.f ? 1.f : 0.f);
+          // 1 / |u| by MUFU.RSQ (<= 2 ulp) where k_step divides by an IEEE square root: the SCORE above is exact,
+          // only the gradient's unit vectors carry the 2 ulp (36 instructions and two slow-path branches less per chunk)
+          const float q0 = u.x * u.x + u.y * u.y, q1 = u.z * u.z + u.w * u.w;
+          const float i0 = q0 > 0.f ? rsqrtf(q0) : 0.f, i1 = q1 > 0.f ? rsqrtf(q1) : 0.f;
+          cnt += (q0 > 0.f ? 1.f : 0.f) + (q1 > 0.f ? 1.f : 0.f);
           const float4 uh = f4(u.x * i0, u.y * i0, u.z * i1, u.w * i1);
           float4 a = s_A[v * WARP + lane];
           a += coef * uh;
