@@ -82,19 +82,20 @@ def train_test_split_no_unseen(X, test_size, seed):
     rnd = np.random.RandomState(seed)
     chosen = set()
     candidates = np.arange(len(X))
-    for _ in range(len(X) * 10):
-        if len(chosen) >= test_size:
-            break
+    loops, max_loops = 0, len(X) * 10
+    while len(chosen) < test_size:
+        # the reference's loop (data_utils.py:139-154) verbatim in behaviour: an index drawn a second time is tested and
+        # its counters are decremented AGAIN (np.unique then collapses it), so with the same seed the split is the
+        # reference's split
         i = int(rnd.choice(candidates))
-        if i in chosen:
-            continue
         h, r, t = X[i]
         if left_e[h] > 1 and left_r[r] > 1 and left_e[t] > 1:
             left_e[h] -= 1; left_r[r] -= 1; left_e[t] -= 1
             chosen.add(i)
-    else:
-        logging.error("Cannot split a test set with desired size, please reduce the test size")
-        return None
+        loops += 1
+        if loops == max_loops:
+            logging.error("Cannot split a test set with desired size, please reduce the test size")
+            return None
     test_id = np.array(sorted(chosen), dtype=int)
     return X[np.setdiff1d(candidates, test_id)], X[test_id]
 

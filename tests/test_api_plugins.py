@@ -120,3 +120,41 @@ def test_batch_stream_semantics_cpu():
     w = data_utils.DeviceBatchStream(data, 4, shuffle=False, device="cpu")
     got = torch.cat([next(w) for _ in range(3)])
     assert got[:, 0].tolist() == [0, 3, 6, 9, 12, 15, 18, 21, 24, 27, 0, 3]
+
+
+def test_train_test_split_follows_the_reference_on_duplicate_draws():
+    """/root/reference/KGE/data_utils.py:139-154 restated: an index drawn twice is tested and its entity / relation
+    counters are decremented again before np.unique collapses it.  With the same seed the mirror must return the
+    same split (the mirror used to skip repeated draws)."""
+    import numpy as np
+    from KGE import data_utils
+
+    def reference_split(X, test_size, seed):
+        if isinstance(test_size, float):
+            test_size = int(len(X) * test_size)
+        e, e_cnt = np.unique(np.append(X[:, 0], X[:, 2]), return_counts=True)
+        r, r_cnt = np.unique(X[:, 1], return_counts=True)
+        e_dict, r_dict = dict(zip(e, e_cnt)), dict(zip(r, r_cnt))
+        test_id, train_id = np.array([], dtype=int), np.arange(len(X))
+        loop_count, max_loop = 0, len(X) * 10
+        rnd = np.random.RandomState(seed)
+        while len(test_id) < test_size:
+            i = rnd.choice(train_id)
+            if e_dict[X[i, 0]] > 1 and r_dict[X[i, 1]] > 1 and e_dict[X[i, 2]] > 1:
+                e_dict[X[i, 0]] -= 1
+                r_dict[X[i, 1]] -= 1
+                e_dict[X[i, 2]] -= 1
+                test_id = np.unique(np.append(test_id, i))
+            loop_count += 1
+            if loop_count == max_loop:
+                return None
+        return X[np.setdiff1d(train_id, test_id)], X[test_id]
+
+    rng = np.random.default_rng(0)
+    for n, N, R, ts in [(400, 40, 5, 0.4), (300, 25, 4, 120), (1000, 60, 7, 0.3)]:
+        X = np.stack([rng.integers(0, N, n), rng.integers(0, R, n), rng.integers(0, N, n)], 1)
+        for seed in (1, 2, 3):
+            want, got = reference_split(X, ts, seed), data_utils.train_test_split_no_unseen(X, ts, seed)
+            assert (want is None) == (got is None)
+            if want is not None:
+                assert np.array_equal(want[0], got[0]) and np.array_equal(want[1], got[1])
