@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 10
+#define KGE_ABI_VERSION 11
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -455,6 +455,23 @@ int kge_filter_index_build(kge_ctx*, const kge_cfg*, const void* positive, int64
 int kge_filter_lookup(kge_ctx*, const kge_cfg*, const void* index, int64_t n_pos, const void* queries,
                       int64_t Q, int side, int64_t* begin_out, int64_t* end_out, kge_filter* filter_out,
                       void* stream);
+
+/* Batch pipeline on the device.  Replaces the reference's tf.data iterator
+ * (KGE/data_utils.py:176-196: from_tensor_slices / csv -> shuffle -> repeat -> batch, one host -> device copy
+ * per step) for training sets that fit the GPU.
+ *   kge_epoch_perm_bytes : workspace bytes of kge_epoch_perm for n triples.
+ *   kge_epoch_perm       : perm_out[0 .. n) = the order of pass `epoch`: STABLE argsort of the keys
+ *                          Philox4x32-10(key = seed; counter = (i, epoch, bit 1)) word 0 — the sampler's
+ *                          generator (oracle/philox.py: draw_u32(seed, epoch, 1, n)); stateless, so any pass
+ *                          can be regenerated (resume).  n < 2^32.
+ *   kge_batch_gather     : out[(B, 3)] = triples[perm[offset .. offset + B)] (perm NULL = identity), ids of
+ *                          in_id_dtype in, out_id_dtype out (0 = int32, 1 = int64); offset + B <= n: a batch that
+ *                          straddles two passes is two calls. */
+int kge_epoch_perm_bytes(int64_t n, size_t* ws_bytes);
+int kge_epoch_perm(kge_ctx*, int64_t n, uint64_t seed, uint64_t epoch, uint32_t* perm_out, void* ws,
+                   size_t ws_bytes, void* stream);
+int kge_batch_gather(kge_ctx*, int in_id_dtype, const void* triples, int64_t n, const uint32_t* perm,
+                     int64_t offset, int64_t B, int out_id_dtype, void* out, void* stream);
 
 /* Materialises the row-lazy tables (kge_tables.lazy_t): every row is replayed to step lazy_t and
  * last[] = lazy_t.  No-op when no table carries `last`.  One dense pass over the lazy tables

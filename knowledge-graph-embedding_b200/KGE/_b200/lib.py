@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 10
+KGE_ABI_VERSION = 11
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -93,7 +93,8 @@ SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destr
            "kge_filter_index_bytes", "kge_filter_index_build", "kge_filter_lookup",
            "kge_train_step_next", "kge_train_step_host_next",
            "kge_step_graph_create", "kge_step_graph_launch", "kge_step_graph_destroy",
-           "kge_train_step_dp_next", "kge_step_graph_create_dp", "kge_step_graph_launch_dp", "kge_step_graph_phases"]
+           "kge_train_step_dp_next", "kge_step_graph_create_dp", "kge_step_graph_launch_dp", "kge_step_graph_phases",
+           "kge_epoch_perm_bytes", "kge_epoch_perm", "kge_batch_gather"]
 RANK_STATIC_BYTES = 4 << 20
 
 _LIB = None
@@ -148,6 +149,9 @@ def load():
     L.kge_filter_index_bytes.argtypes = [C.POINTER(Cfg), i64, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
     L.kge_filter_index_build.argtypes = [vp, C.POINTER(Cfg), vp, i64, i32, vp, C.c_size_t, vp, C.c_size_t, vp]
     L.kge_filter_lookup.argtypes = [vp, C.POINTER(Cfg), vp, i64, vp, i64, i32, vp, vp, C.POINTER(Filter), vp]
+    L.kge_epoch_perm_bytes.argtypes = [i64, C.POINTER(C.c_size_t)]
+    L.kge_epoch_perm.argtypes = [vp, i64, u64, u64, vp, vp, C.c_size_t, vp]
+    L.kge_batch_gather.argtypes = [vp, i32, vp, i64, vp, i64, i64, i32, vp, vp]
     L.kge_shard_lookup.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Shard),
                                    C.POINTER(Dp), vp, i64, u64, u64, vp, vp, C.c_size_t, vp]
     L.kge_shard_pre.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Shard), u64, vp]

@@ -121,34 +121,68 @@ def calculate_data_size(X):
 # device batch pipeline
 # ---------------------------------------------------------------------------------------
 class DeviceBatchStream:
-    """Infinite iterator of (batch_size, 3) id tensors resident on `device`."""
+    """Infinite iterator of (batch_size, 3) id tensors resident on `device` — the reference's
+    from_tensor_slices / csv -> shuffle -> repeat -> batch pipeline (data_utils.py:176-196) without the per-step
+    host -> device copy.
+
+    On a CUDA device the work is the library's (csrc/batch_stream.cu): `kge_epoch_perm` draws the order of a pass
+    (stable argsort of Philox keys of (seed, pass): stateless, so `skip` / resume regenerate it) and
+    `kge_batch_gather` cuts one batch; a batch that straddles two passes is two gathers.  `device="cpu"` keeps a
+    torch-only iterator for host-side tooling and the CPU tests of this class (no kernels involved)."""
 
     def __init__(self, data, batch_size, shuffle, seed=None, device="cuda:0"):
         arr = load_triples(data)
         self.dtype = torch.int32 if arr.dtype == np.int32 else torch.int64
-        self.store = torch.as_tensor(arr.astype(np.int64)).to(device)        # kernels take int64 ids
+        self.device = torch.device(device)
+        self.store = torch.as_tensor(arr.astype(np.int64)).to(self.device)        # kernels take int64 ids
         self.n, self.batch_size, self.shuffle = len(arr), int(batch_size), bool(shuffle)
+        self.cuda = self.device.type == "cuda"
         self.gen = None
-        if self.shuffle:
-            self.gen = torch.Generator(device=device)
-            if seed is None:
-                self.gen.seed()
-            else:
-                self.gen.manual_seed(int(seed))
+        self.seed = int(seed) if seed is not None else int(np.random.SeedSequence().entropy % (1 << 63))
+        self.pass_no = 0
+        if self.cuda:
+            import ctypes as C
+            from ._b200 import lib as L, engine as E
+            self._L, self._C, self._E = L, C, E
+            self._ctx = E._ctx(self.device.index if self.device.index is not None else torch.cuda.current_device())
+            if self.shuffle:
+                nb = C.c_size_t()
+                L.check(L.load().kge_epoch_perm_bytes(self.n, C.byref(nb)))
+                self._ws = torch.empty(nb.value, dtype=torch.uint8, device=self.device)
+                self._perm = [torch.empty(self.n, dtype=torch.int32, device=self.device) for _ in range(2)]
+        elif self.shuffle:
+            self.gen = torch.Generator(device=self.device)
+            self.gen.manual_seed(self.seed)
         self.order = self._new_pass()
         self.cursor = 0
 
     def _new_pass(self):
-        if self.shuffle:
-            return torch.randperm(self.n, generator=self.gen, device=self.store.device)
-        return torch.arange(self.n, device=self.store.device)
+        k = self.pass_no
+        self.pass_no += 1
+        if not self.shuffle:
+            return None if self.cuda else torch.arange(self.n, device=self.device)
+        if not self.cuda:
+            return torch.randperm(self.n, generator=self.gen, device=self.device)
+        out = self._perm[k & 1]          # two buffers: a straddling batch still reads the previous pass
+        with torch.cuda.device(self.device):
+            self._L.check(self._L.load().kge_epoch_perm(self._ctx, self.n, self.seed, k, self._E._ptr(out), self._E._ptr(self._ws),
+                                                        self._ws.numel(), self._E._stream()))
+        return out
 
     def __iter__(self):
         return self
 
     def skip(self, n_batches):
-        """Advance by n_batches without materialising them (resume): same generator draws as iterating."""
+        """Advance by n_batches without materialising them (resume).  CUDA: passes are a function of (seed, pass), so
+        only the pass the cursor lands in is generated; CPU: the same generator draws as iterating."""
         need = int(n_batches) * self.batch_size
+        if self.cuda:
+            total = self.cursor + need
+            passes, self.cursor = divmod(total, self.n)
+            if passes > 0:
+                self.pass_no += passes - 1
+                self.order = self._new_pass()
+            return
         while need > 0:
             take = min(need, self.n - self.cursor)
             self.cursor += take
@@ -157,16 +191,26 @@ class DeviceBatchStream:
                 self.order, self.cursor = self._new_pass(), 0
 
     def __next__(self):
-        need, pieces = self.batch_size, []
+        if self.cuda:
+            out = torch.empty((self.batch_size, 3), dtype=torch.int64, device=self.device)
+        need, pieces, done = self.batch_size, [], 0
         while need > 0:
             take = min(need, self.n - self.cursor)
-            pieces.append(self.order[self.cursor:self.cursor + take])
+            if self.cuda:       # gathers are enqueued at once: a later pass may then reuse the permutation buffer (stream order)
+                with torch.cuda.device(self.device):
+                    self._L.check(self._L.load().kge_batch_gather(
+                        self._ctx, 1, self._E._ptr(self.store), self.n, self._E._ptr(self.order), self.cursor, take, 1,
+                        self._C.c_void_p(out.data_ptr() + 24 * done), self._E._stream()))
+                done += take
+            else:
+                pieces.append(self.order[self.cursor:self.cursor + take])
             self.cursor += take
             need -= take
             if self.cursor == self.n:
                 self.order, self.cursor = self._new_pass(), 0
-        idx = pieces[0] if len(pieces) == 1 else torch.cat(pieces)
-        return self.store.index_select(0, idx)
+        if self.cuda:
+            return out
+        return self.store.index_select(0, pieces[0] if len(pieces) == 1 else torch.cat(pieces))
 
 
 def set_tf_iterator(data, batch_size, shuffle, buffer_size=None, seed=None, device="cuda:0"):

@@ -63,6 +63,13 @@ def draw_u32(seed, step, side_bit, count):
     return philox4x32_10(ctr, key)[:, 0]
 
 
+def epoch_permutation(seed, epoch, n):
+    """Order of pass `epoch` over n training triples (kge_epoch_perm, include/kge_abi.h): stable argsort of
+    u[i] = draw_u32(seed, epoch, 1, n).  The reference shuffles with tf.data (data_utils.py:186-190, unseeded
+    stream); the permutation is defined on the library's own counter-based stream like the negatives."""
+    return np.argsort(draw_u32(seed, epoch, 1, n), kind="stable").astype(np.uint32)
+
+
 def sample_uniform(seed, step, side, B, k_side, n_ent, pool=None):
     """Restates UniformStrategy.__call__ (ns_strategy.py:39-64) on our stream."""
     u = draw_u32(seed, step, 0 if side == "h" else 1, B * k_side).astype(np.int64)

@@ -324,3 +324,24 @@ def test_device_batch_stream_on_the_gpu():
     assert torch.equal(next(b), first[7])
     c = DeviceBatchStream(X, 100, shuffle=False, device="cuda:0")
     assert torch.equal(next(c).cpu(), torch.from_numpy(X[:100]))
+
+
+def test_epoch_permutation_and_batch_gather_match_the_spec():
+    """kge_epoch_perm / kge_batch_gather (csrc/batch_stream.cu) against oracle/philox.py::epoch_permutation:
+    every pass is the stable argsort of the Philox keys of (seed, pass); batches are slices of it, also across the
+    boundary of two passes; int32 sources, resume by skip()."""
+    from oracle import philox
+    from KGE.data_utils import DeviceBatchStream
+    n, B, seed = 1000, 96, 12345
+    X = np.stack([np.arange(n), np.arange(n) % 11, (np.arange(n) * 7) % n], 1).astype(np.int32)
+    it = DeviceBatchStream(X, B, shuffle=True, seed=seed, device="cuda:0")
+    got = torch.cat([next(it) for _ in range(32)]).cpu().numpy()               # 3072 rows: three passes and a bit
+    want = np.concatenate([X[philox.epoch_permutation(seed, e, n).astype(np.int64)] for e in range(4)])[:len(got)]
+    assert np.array_equal(got, want.astype(np.int64))
+    it2 = DeviceBatchStream(X, B, shuffle=True, seed=seed, device="cuda:0")
+    it2.skip(25)                                                                # lands in the third pass
+    assert np.array_equal(next(it2).cpu().numpy(), got[25 * B:26 * B])
+    big = DeviceBatchStream(X[:50], 128, shuffle=True, seed=1, device="cuda:0")  # a batch longer than two passes
+    rows = next(big).cpu().numpy()
+    want = np.concatenate([X[:50][philox.epoch_permutation(1, e, 50).astype(np.int64)] for e in range(3)])[:128]
+    assert np.array_equal(rows, want.astype(np.int64))

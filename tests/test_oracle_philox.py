@@ -71,3 +71,13 @@ def test_typed_singleton_pool_raises():
     pools = philox.TypedPools(["A", "B", "B"])
     with pytest.raises(ValueError):
         philox.sample_typed(1, 0, "h", np.array([[0, 0, 1]]), 2, pools)
+
+
+def test_epoch_permutation_is_a_reproducible_permutation():
+    """Spec of kge_epoch_perm (csrc/batch_stream.cu): stable argsort of the Philox keys of (seed, pass)."""
+    import numpy as np
+    from oracle import philox
+    a = philox.epoch_permutation(7, 0, 5000)
+    assert np.array_equal(np.sort(a), np.arange(5000)) and a.dtype == np.uint32
+    assert np.array_equal(a, philox.epoch_permutation(7, 0, 5000))
+    assert not np.array_equal(a, philox.epoch_permutation(7, 1, 5000)) and not np.array_equal(a, philox.epoch_permutation(8, 0, 5000))
