@@ -7,6 +7,7 @@ namespace kge {
 
 // ---- fixed-order reduction of per-positive partials ---------------------------------
 // scal[0..3] = clip scale per table, scal[4..7] = norm^2 per table, scal[8] = loss.
+constexpr int N_PART_MAX = 5;     // loss + norm^2 per table (1 + KGE_MAX_TABLES)
 struct ReduceParams {
   const float* part;     // [n_part][B]
   int64_t B;
@@ -14,7 +15,10 @@ struct ReduceParams {
   float clip_norm;
   float* scal;
   float* loss_out;
+  float* stage;          // k_reduce: [N_PART_MAX][RED_CTAS] per-CTA sums (behind the partials in the workspace)
+  unsigned* done;        // k_reduce: self-resetting ticket counter
 };
+constexpr int RED_CTAS = 64;      // k_reduce: CTAs of the first level (one SM's L2 bandwidth was the single-CTA kernel's limit)
 
 // The same reduction folded into the step kernel (saves a launch when B is small), in two levels so that
 // the serial end of the kernel stays short: every CTA sums the partials of its own positives (shared memory)

@@ -70,7 +70,7 @@ int layout_step_ws(const kge_cfg* c, int64_t B, StepWs& L) {
   KGE_REQUIRE(L.n_keys < 0x7fffffffll, KGE_EUNSUPPORTED, "batch too large: %lld gradient records", (long long) L.n_keys);
   size_t o = 0;
   auto take = [&](size_t bytes) { size_t at = o; o += align_up(bytes); return at; };
-  L.off_part = take(sizeof(float) * N_PART * (size_t) B);
+  L.off_part = take(sizeof(float) * (N_PART * (size_t) B + N_PART_MAX * RED_CTAS));      // partials | k_reduce's per-CTA sums
   L.off_scal = take(sizeof(float) * 16);
   L.n_seg = (size_t) c->n_ent + (size_t) c->n_rel;
   const size_t g0 = o;
@@ -556,6 +556,8 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   p.rp.clip_norm = cfg->clip_norm;
   p.rp.scal = reinterpret_cast<float*>(wsb + L.off_scal);
   p.rp.loss_out = grad_only ? p.rp.scal + 9 : loss_out;
+  p.rp.stage = p.part + N_PART * (size_t) B;
+  p.rp.done = ctx->ticket + 1;
 
   // side stream: sort keys depend on ids only, so key generation, the stable radix sort and the
   // segment table run concurrently with the step kernel and join before the update kernels
@@ -818,7 +820,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   const ReduceParams& rp = p.rp;
   if (!p.tail) {
     pt.begin(2);
-    k_reduce<<<1, 1024, 0, st>>>(rp);
+    k_reduce<<<(unsigned) (B >= 8192 ? RED_CTAS : (B + 1023) / 1024), 1024, 0, st>>>(rp);
     KGE_CUDA_OK(cudaGetLastError());
     pt.end(2);
   }

@@ -95,28 +95,57 @@ inline int launch_constrain_kernel(const ConstrainParams& cp, int sm_count, cuda
 }
 
 __global__ void __launch_bounds__(1024) k_reduce(const ReduceParams p) {
-  __shared__ float sm[32];
+  // Two levels, fixed shape: CTA c sums the contiguous slice [c * S, (c + 1) * S) of every quantity (thread t takes
+  // i = t, t + 1024, ... ascending; all quantities in one sweep so the loads of a thread stay in flight together),
+  // publishes ONE value per quantity, and the last CTA to finish (ticket) adds the gridDim.x values in CTA order.
+  // The single-CTA version was bound by one SM's L2 bandwidth: 45 us for the 1.3 MB of partials at B = 65 536.
+  __shared__ float sm[N_PART_MAX][32];
+  __shared__ int s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-  for (int q = 0; q < p.n_part; ++q) {
-    const float* src = p.part + (size_t) q * p.B;
-    float a = 0.f;
-    for (int64_t i = threadIdx.x; i < p.B; i += blockDim.x) a += src[i];
-    a = warp_sum(a);
-    if (lane == 0) sm[warp] = a;
-    __syncthreads();
-    if (warp == 0) {
-      float b = (lane < nwarp) ? sm[lane] : 0.f;
-      b = warp_sum(b);
-      if (lane == 0) {
-        if (q == 0) { p.scal[8] = b; *p.loss_out = b; }
-        else {
-          p.scal[4 + q - 1] = b;
-          // tf.clip_by_norm: g * clip / max(||g||, clip)      (BaseModel.py:327)
-          p.scal[q - 1] = p.clip_norm / fmaxf(sqrtf(b), p.clip_norm);
-        }
+  const int64_t S = (p.B + gridDim.x - 1) / gridDim.x;
+  const int64_t lo = (int64_t) blockIdx.x * S, hi = (lo + S < p.B) ? lo + S : p.B;
+  float a[N_PART_MAX];
+#pragma unroll
+  for (int q = 0; q < N_PART_MAX; ++q) a[q] = 0.f;
+#pragma unroll 4
+  for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+#pragma unroll
+    for (int q = 0; q < N_PART_MAX; ++q)
+      if (q < p.n_part) a[q] += p.part[(size_t) q * p.B + i];
+  }
+#pragma unroll
+  for (int q = 0; q < N_PART_MAX; ++q) {
+    a[q] = warp_sum(a[q]);
+    if (lane == 0) sm[q][warp] = a[q];
+  }
+  __syncthreads();
+  if (warp < N_PART_MAX) {
+    float b = (lane < nwarp) ? sm[warp][lane] : 0.f;
+    b = warp_sum(b);
+    if (lane == 0) p.stage[warp * RED_CTAS + blockIdx.x] = b;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned t = atomicAdd(p.done, 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) *p.done = 0u;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (warp < p.n_part && warp < N_PART_MAX) {
+    const int q = warp;
+    float b = 0.f;
+    for (int c = 0; c < (int) gridDim.x; ++c) b += __ldcg(p.stage + q * RED_CTAS + c);      // CTA order (warp-uniform)
+    if (lane == 0) {
+      if (q == 0) { p.scal[8] = b; *p.loss_out = b; }
+      else {
+        p.scal[4 + q - 1] = b;
+        // tf.clip_by_norm: g * clip / max(||g||, clip)      (BaseModel.py:327)
+        p.scal[q - 1] = p.clip_norm / fmaxf(sqrtf(b), p.clip_norm);
       }
     }
-    __syncthreads();
   }
 }
 
