@@ -108,6 +108,18 @@ __device__ __forceinline__ float warp_max(float v) {
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(FULL, v, o));
   return v;
 }
+// the same butterflies over aligned groups of W lanes (W = 16: two independent rows per warp, step_narrow_kernels.cuh).
+// With the upper half of a warp holding zeros, warp_sum and warp_sum_w<16> return the same bits in the lower half.
+template <int W> __device__ __forceinline__ float warp_sum_w(float v) {
+#pragma unroll
+  for (int o = W / 2; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+template <int W> __device__ __forceinline__ float warp_max_w(float v) {
+#pragma unroll
+  for (int o = W / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(FULL, v, o));
+  return v;
+}
 __device__ __forceinline__ void warp_sum2(float& a, float& b) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {

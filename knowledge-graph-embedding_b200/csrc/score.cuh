@@ -44,11 +44,11 @@ __device__ __forceinline__ float chunk_fwd(int kind, float p, float4 u) {
 }
 
 // Forward: all lanes return the same score.  score.py:59-63 (Lp), :76 (pow), :89 (Dot).
-template <int NV, bool CPLX>
+template <int NV, bool CPLX, int W = 32>
 __device__ __forceinline__ float score_fwd(const ScoreDev& sc, const Row<NV>& x, const Row<NV>& y,
                                            ScoreSaved& sv) {
   if (sc.kind == SC_DOT) {
-    float s = warp_sum(row_dot_partial(x, y));
+    float s = warp_sum_w<W>(row_dot_partial(x, y));
     sv.S = s; sv.s = s; sv.ties = 1.f;
     return s;
   }
@@ -60,7 +60,7 @@ __device__ __forceinline__ float score_fwd(const ScoreDev& sc, const Row<NV>& x,
   }
   float S, s;
   if (sc.kind == SC_LINF) {
-    S = warp_max(acc);
+    S = warp_max_w<W>(acc);
     s = -S;
     float t = 0.f;
 #pragma unroll
@@ -72,9 +72,9 @@ __device__ __forceinline__ float score_fwd(const ScoreDev& sc, const Row<NV>& x,
         t += (cmod(u.x, u.y) == S) + (cmod(u.z, u.w) == S);
       }
     }
-    sv.ties = warp_sum(t);
+    sv.ties = warp_sum_w<W>(t);
   } else {
-    S = warp_sum(acc);
+    S = warp_sum_w<W>(acc);
     float Sc = fmaxf(S, 1e-9f);                       // clip_by_value(., 1e-9, inf)
     s = (sc.kind == SC_L1) ? -Sc : (sc.kind == SC_L2 ? -sqrtf(Sc) : -powf(Sc, 1.0f / sc.p));
     sv.ties = 1.f;

@@ -54,6 +54,8 @@ int launch_step_transe(const StepParams&, const StepLaunch&);
 int launch_step_transh(const StepParams&, const StepLaunch&);
 int launch_step_transd(const StepParams&, const StepLaunch&);
 int launch_step_rotate(const StepParams&, const StepLaunch&);
+int launch_step_narrow_transe(const StepParams&, const StepLaunch&);   // step_narrow_kernels.cuh
+int launch_step_narrow_um(const StepParams&, const StepLaunch&);
 int launch_step_rot(const StepParams&, const StepLaunch&);      // step_rot_kernels.cuh (model_rotate.cu)
 size_t step_rot_smem_bytes_host(int nv, int wpp, int k, int nwarps, int ld);
 int launch_step_distmult(const StepParams&, const StepLaunch&);

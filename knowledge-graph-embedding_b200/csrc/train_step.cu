@@ -735,6 +735,11 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
         break;
       }
     }
+    // TransE / UM rows of <= 64 floats, one warp per positive, one corrupted side: two positives per warp
+    // (step_narrow_kernels.cuh) — k_step's fast path for these models, bit for bit, in half the warps
+    const bool narrow = (cfg->model == KGE_TRANSE || cfg->model == KGE_UM) && nv == 1 && tables->t[KGE_T_ENT].cols <= 64 &&
+                        p.wpp == 1 && cfg->corrupt_side != KGE_SIDE_HT && cfg->score != KGE_SCORE_DOT &&
+                        cfg->loss != KGE_LOSS_SELF_ADV && !getenv("KGE_STEP_NARROW_OFF");
     // RotatE with LpDistance(1) on wide rows: the streamed kernel (step_rot_kernels.cuh) — same arithmetic, accumulators in
     // shared memory, two CTAs per SM where k_step's 255 registers allow one
     bool rot_stream = false;
@@ -777,8 +782,8 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     }
     pt.begin(1);
     switch (cfg->model) {
-      case KGE_UM: rc = launch_step_um(p, SL); break;
-      case KGE_TRANSE: rc = launch_step_transe(p, SL); break;
+      case KGE_UM: rc = narrow ? launch_step_narrow_um(p, SL) : launch_step_um(p, SL); break;
+      case KGE_TRANSE: rc = narrow ? launch_step_narrow_transe(p, SL) : launch_step_transe(p, SL); break;
       case KGE_TRANSH: rc = launch_step_transh(p, SL); break;
       case KGE_TRANSD: rc = launch_step_transd(p, SL); break;
       case KGE_ROTATE: rc = rot_stream ? launch_step_rot(p, SL) : launch_step_rotate(p, SL); break;

@@ -407,3 +407,40 @@ def test_rotate_streamed_kernel_equals_register_kernel(d, k, side, loss, B):
     for kk in outs[0][1]:          # same expressions; the compiler contracts a few multiply-adds differently in the two kernels
         assert_weights_close(outs[0][1][kk], outs[1][1][kk], 1e-3, 2, "streamed vs register kernel, " + kk)
         assert float((outs[0][1][kk] - outs[1][1][kk]).abs().max()) <= 2e-5
+
+
+@pytest.mark.parametrize("model,d,k,side,score,loss,B", [
+    ("TransE", 50, 1, "t", "l1", "hinge", 4096), ("TransE", 50, 1, "h", "l2", "logistic", 333), ("TransE", 64, 2, "t", "l2pow", "bce", 77),
+    ("UM", 33, 1, "h", "l2pow", "hinge", 500), ("TransE", 13, 2, "t", "linf", "square", 129), ("UM", 50, 1, "t", "l3", "hinge", 5000),
+])
+def test_two_positives_per_warp_kernel_equals_k_step_bitwise(model, d, k, side, score, loss, B):
+    """k_step_narrow (csrc/step_narrow_kernels.cuh: rows of <= 64 floats, one 16-lane half per positive) against
+    k_step (KGE_STEP_NARROW_OFF=1): same loads, expressions and butterfly sums, the in-kernel tail in k_step's order
+    (also B > 4096: per-positive partials + k_reduce) — losses, negatives and tables bitwise equal over train /
+    validation / train steps; the new kernel also against the oracle."""
+    import os
+    outs = []
+    for off in (False, True):
+        if off:
+            os.environ["KGE_STEP_NARROW_OFF"] = "1"
+        try:
+            rng = np.random.default_rng(43)
+            ref, W, eng = make_pair(model, N, R, d, None, score=SCORES[score], loss=LOSSES[loss], k=k, side=side)
+            opt = RS.TFAdam()
+            losses = []
+            for step in range(3):
+                X = rand_triples(rng, B, N, R)
+                l, neg = eng.train_step(X, 8, step, is_train=step != 1, want_negatives=True)
+                losses.append((float(l.item()), neg.cpu().numpy().copy()))
+                if not off and B <= 600:
+                    ids, k_eff = RS.sample_negatives(8, step, X, k, side, N)
+                    l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, side, step != 1)
+                    assert np.array_equal(neg.cpu().numpy(), ids)
+                    assert abs(losses[-1][0] - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, losses[-1][0], l_ref)
+            outs.append((losses, tables_of(eng, model)))
+        finally:
+            os.environ.pop("KGE_STEP_NARROW_OFF", None)
+    for (la, na), (lb, nb) in zip(outs[0][0], outs[1][0]):
+        assert np.array_equal(na, nb) and la == lb, (la, lb)
+    for kk in outs[0][1]:
+        assert torch.equal(outs[0][1][kk], outs[1][1][kk]), kk
