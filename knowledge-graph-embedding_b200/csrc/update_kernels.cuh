@@ -1,6 +1,7 @@
 // update_kernels.cuh — constraint, partial reduction and row update kernels.
 // All are model independent: they see tables, records and sorted keys only.
 #pragma once
+#include <stdlib.h>
 #include "common.cuh"
 #include "reduce_tail.cuh"
 
@@ -615,6 +616,76 @@ __global__ void __launch_bounds__(64, CPL <= 2 ? 18 : 1) k_update_fast(const Upd
   adam_row<CPL>(p, T, row, nch, lane, g);
 }
 
+// k_update_fast<1, 0> for tables whose rows are <= 64 floats (C1: d = 50): at 13 of 32 lanes per row a warp is mostly
+// idle, so a warp takes TWO rows, one per 16-lane half.  Same header / record / Adam sequence per row, the records
+// added strictly in sorted order, the shadow row's norm by the same butterfly (the upper half of k_update_fast's
+// warp holds zeros): bit-identical results (tests/test_gpu_step.py::test_two_rows_per_warp_update_equals_k_update_fast).
+// Plain fused step only (MODE 0, materialised records, no data-parallel outputs).
+__global__ void __launch_bounds__(64, 18) k_update_narrow(const UpdateParams p) {
+  const int lane = threadIdx.x & 31, sub = lane >> 4, hl = lane & 15;
+  const int64_t idx = (((int64_t) blockIdx.x * 2 + (threadIdx.x >> 5)) << 1) + sub;
+  const bool in_range = idx < p.total_rows;
+  int64_t row = in_range ? p.total_rows - 1 - idx : 0;       // last table first, as k_update_fast
+  int j = 0;
+  while (j < p.n_tabs - 1 && row >= p.tab[j].rows) { row -= p.tab[j].rows; ++j; }
+  const UpdateTable& T = p.tab[j];
+  const bool valid = in_range && row < T.rows;
+  const int nch = (T.cols + 3) >> 2;
+  const bool mine_l = hl < nch;
+  const float4* wi = reinterpret_cast<const float4*>(T.w_in + row * (int64_t) T.ld);
+  float4* w4 = reinterpret_cast<float4*>(T.w + row * (int64_t) T.ld);
+  float4* m4 = reinterpret_cast<float4*>(T.m + row * (int64_t) T.ld);
+  float4* v4 = reinterpret_cast<float4*>(T.v + row * (int64_t) T.ld);
+  if (valid && mine_l && (hl & 7) == 0) {                     // one request per 128-byte line
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(wi + hl));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(m4 + hl));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(v4 + hl));
+  }
+  uint32_t hv = 0;
+  if (valid && T.rec != nullptr && hl < 8) hv = __ldg(p.hdr + ((int64_t) T.key_base + row) * 8 + hl);
+  const uint32_t L = __shfl_sync(FULL, hv, 0, 16), lo = __shfl_sync(FULL, hv, 1, 16);
+  const bool active = valid && L <= (uint32_t) UPD_HEAVY;     // heavier rows are k_update_heavy's
+  const uint32_t Lm = active ? L : 0u;
+  const uint32_t hid = __shfl_sync(FULL, hv, (hl + 2) & 15, 16);      // lanes 0..5: the header's record ids
+  float4 g = f4zero();
+  for (uint32_t base = 0; __any_sync(FULL, base < Lm); base += 16) {
+    const int n = base < Lm ? (int) (Lm - base < 16u ? Lm - base : 16u) : 0;
+    uint32_t mine = 0;
+    if (hl < n) {
+      const uint32_t pos = base + hl;
+      mine = (pos < 6u ? hid : __ldg(p.vals + lo + pos)) - T.rec_base;
+    }
+    const int n_other = __shfl_xor_sync(FULL, n, 16);
+    const int nmax = n > n_other ? n : n_other;
+    for (int x = 0; x < nmax; ++x) {
+      const uint32_t rid = __shfl_sync(FULL, mine, x, 16);
+      if (x < n && mine_l) g += __ldg(reinterpret_cast<const float4*>(T.rec + (int64_t) rid * T.rec_ld) + hl);
+    }
+  }
+  float4 wnew = f4zero();
+  if (active && mine_l) {
+    const float scale = p.scal[T.slot];
+    const float lr_t = p.lr_dyn ? __ldg(p.lr_dyn) : p.lr_t;
+    float4 w = wi[hl], m = m4[hl], v = v4[hl];
+    adam_chunk(w, m, v, scale4(scale, g), p.beta1, p.beta2, lr_t, p.eps, p.opt);
+    if (T.cols & 3) mask_tail(w, m, v, hl, T.cols);
+    m4[hl] = m; v4[hl] = v; w4[hl] = w;
+    wnew = w;
+  }
+  // shadow row: normalise(new row) for the next batch's gathers (row_sumsq + div4, over the half)
+  float ss = 0.f;
+  ss = __fmaf_rn(wnew.x, wnew.x, ss); ss = __fmaf_rn(wnew.y, wnew.y, ss);
+  ss = __fmaf_rn(wnew.z, wnew.z, ss); ss = __fmaf_rn(wnew.w, wnew.w, ss);
+  const float nrm = sqrtf(warp_sum_w<16>(ss));
+  if (active && mine_l && T.wn_out != nullptr) reinterpret_cast<float4*>(T.wn_out + row * (int64_t) T.ld)[hl] = div4(wnew, nrm);
+}
+inline bool update_narrow_ok(const UpdateParams& up, int cpl) {
+  if (cpl != 1 || getenv("KGE_UPDATE_NARROW_OFF")) return false;
+  for (int j = 0; j < up.n_tabs; ++j)
+    if (up.tab[j].cols > 64 || up.tab[j].fac_coef != nullptr || up.tab[j].n_out != 0 || up.tab[j].n_peer != 0 || up.tab[j].row_lo != 0) return false;
+  return true;
+}
+
 // Rows with many records (hot entities / relations): one CTA per (heavy key, table), the eight
 // warps sum contiguous slices of the sorted record list, partials are combined in slice order —
 // the order k_update uses for its heavy rows, so the bits agree.
@@ -667,6 +738,12 @@ inline int launch_update_heavy(const UpdateParams& up, int cpl, int64_t max_heav
 
 template <int MODE>
 inline int launch_update_fast(const UpdateParams& up, int cpl, cudaStream_t st) {
+  if (MODE == 0 && update_narrow_ok(up, cpl)) {
+    k_update_narrow<<<(unsigned) ((up.total_rows + 3) / 4), 64, 0, st>>>(up);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("k_update_narrow launch failed: %s", cudaGetErrorString(e)); return KGE_ECUDA; }
+    return KGE_OK;
+  }
   const unsigned blocks = (unsigned) ((up.total_rows + 1) / 2);
   switch (cpl) {
     case 1: k_update_fast<1, MODE><<<blocks, 64, 0, st>>>(up); break;

@@ -444,3 +444,31 @@ def test_two_positives_per_warp_kernel_equals_k_step_bitwise(model, d, k, side, 
         assert np.array_equal(na, nb) and la == lb, (la, lb)
     for kk in outs[0][1]:
         assert torch.equal(outs[0][1][kk], outs[1][1][kk]), kk
+
+
+@pytest.mark.parametrize("model,d,k,side,score,loss,B,n_ent", [
+    ("TransE", 50, 1, "t", "l1", "hinge", 4096, N), ("TransE", 50, 8, "h+t", "l2", "logistic", 600, 61),
+    ("UM", 33, 3, "h", "l2pow", "hinge", 500, N), ("DistMult", 13, 2, "t", None, "bce", 129, 40), ("TransH", 24, 4, "h+t", "l1", "hinge", 200, N),
+])
+def test_two_rows_per_warp_update_equals_k_update_fast(model, d, k, side, score, loss, B, n_ent):
+    """k_update_narrow (rows of <= 64 floats, one 16-lane half per table row) against k_update_fast<1, 0>
+    (KGE_UPDATE_NARROW_OFF=1): records added in the same order, same Adam, same shadow rows — tables and Adam slots
+    bitwise equal; a 61 / 40-entity graph makes hot rows (k_update_heavy's) and rows without records share warps."""
+    import os
+    outs = []
+    for off in (False, True):
+        if off:
+            os.environ["KGE_UPDATE_NARROW_OFF"] = "1"
+        try:
+            rng = np.random.default_rng(47)
+            ref, W, eng = make_pair(model, n_ent, R, d, None, score=_score_for(model, score) if score else None, loss=LOSSES[loss], k=k, side=side)
+            losses = [float(eng.train_step(rand_triples(rng, B, n_ent, R), 8, step, is_train=step != 1).item()) for step in range(4)]
+            eng.flush()
+            outs.append((losses, tables_of(eng, model), {s: (t.m.clone(), t.v.clone()) for s, t in eng.tab.items() if t.m is not None}))
+        finally:
+            os.environ.pop("KGE_UPDATE_NARROW_OFF", None)
+    assert outs[0][0] == outs[1][0]
+    for kk in outs[0][1]:
+        assert torch.equal(outs[0][1][kk], outs[1][1][kk]), kk
+    for s in outs[0][2]:
+        assert torch.equal(outs[0][2][s][0], outs[1][2][s][0]) and torch.equal(outs[0][2][s][1], outs[1][2][s][1]), s
