@@ -356,6 +356,9 @@ int kge_step_graph_launch_dp(kge_step_graph*, kge_tables*, const void* triples, 
                              uint32_t epoch, int staging_parity, const void* next_triples, uint64_t next_step,
                              float* host_loss_out, void* stream);
 
+/* Matrix models (SE / TransR / RESCAL without its dense regulariser): kge_train_grad / kge_train_apply through
+ * grads.dense only (n_peers = 0) — dense[slot] of a matrix table is the [n_rel x ld] sum of this rank's pair outer
+ * products (k_update_mat<2>), kge_train_apply steps every element from the rank-summed table (k_mat_apply). */
 int kge_train_grad(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sampler*, const kge_dp*,
                    const void* triples, int64_t B, uint64_t seed, uint64_t step,
                    const int64_t* neg_override, kge_grads* out, float* scal_out /* [8] device */,

@@ -430,6 +430,10 @@ class Engine:
         if getattr(self, "_dp_kind", None) is None:
             dense_reg = bool(self.cfg.constraint) and self.cfg.model in (L.TRANSH, L.RESCAL)
             self._dp_kind, self._peer, self._gbuf, self._dp_steps = _dp.exchange_kind(world_size, dense_reg), None, None, 0
+            if self.cfg.model in (L.SE, L.TRANSR, L.RESCAL):
+                # matrix models: the relation matrices' gradients are dense [n_rel x d d'] tables, exchanged by ONE
+                # all-reduce of the flat buffer (kge_train_grad / kge_train_apply through grads.dense)
+                self._dp_kind = "nccl"
             if self._dp_kind in ("peer", "owner"):
                 layout = {s: (pt.rows, pt.ld) for s, pt in self.tab.items()}
                 wn_slots = None

@@ -313,10 +313,11 @@ class KGEModel:
         # multi-GPU (torch.distributed initialised by the launcher): every rank walks the same seeded batch
         # sequence and owns a contiguous share of each batch.  Tables that fit one GPU are replicated and the
         # gradients exchanged per step (kge_train_step_dp); entity tables beyond KGE_B200_SHARD_BYTES are
-        # sharded over the ranks (kge_shard_*).  Matrix models (SE / TransR / RESCAL) have no split step:
-        # their ranks repeat the whole batch (identical replicas).
+        # sharded over the ranks (kge_shard_*).  Matrix models (SE / TransR / RESCAL) split the batch too, their
+        # matrix gradients travelling in the all-reduced flat buffer; only RESCAL with its dense regulariser
+        # (constraint=True) has no split step: its ranks repeat the whole batch (identical replicas).
         rank, world_size = _dp.world()
-        split = world_size > 1 and sharded is None and self.MODEL not in ("SE", "TransR", "RESCAL")
+        split = world_size > 1 and sharded is None and not (self.MODEL == "RESCAL" and bool(eng.cfg.constraint))
         if world_size > 1:
             assert seed is not None, "multi-GPU training needs a seed: every rank must walk the same batch sequence"
         step, first_epoch = 0, 0

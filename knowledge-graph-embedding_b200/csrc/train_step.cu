@@ -419,7 +419,10 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     KGE_REQUIRE(dp->world >= 1 && dp->rank >= 0 && dp->rank < dp->world && dp->i_base >= 0 &&
                     dp->B_global >= dp->i_base + B, KGE_EINVAL, "bad kge_dp (world %d rank %d B_global %lld i_base %lld)",
                 dp->world, dp->rank, (long long) dp->B_global, (long long) dp->i_base);
-    KGE_REQUIRE(!mat, KGE_EUNSUPPORTED, "data-parallel steps cover the vector models; SE / TransR / RESCAL are single-GPU");
+    // matrix models: the relation matrices' gradients travel as dense [n_rel x d d'] tables (grads.dense: all-reduce);
+    // the peer / owner exchanges and the dense regulariser of RESCAL (constraint = True) stay single-GPU
+    KGE_REQUIRE(!mat || (grads_out->n_peers == 0 && !has_dense_reg(cfg) && !sh), KGE_EUNSUPPORTED,
+                "data-parallel SE / TransR / RESCAL: gradients through grads.dense only, no dense regulariser (else single-GPU)");
     int gcols[KGE_MAX_TABLES];
     expected_cols(cfg, gcols);
     for (int s = 0; s < KGE_MAX_TABLES; ++s)
@@ -926,6 +929,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
       T.rows_m = mat_rows(cfg); T.cols_m = mat_cols(cfg); T.ld = tables->t[slot].ld; T.slot = slot;
       T.use_sh = sh; T.use_st = st_; T.neg_mode = neg_mode;
       T.ent_row_sh = er_sh; T.ent_row_st = er_st; T.ent_row_neg = er_neg;
+      T.gout = grad_only ? grads_out->dense[slot] : nullptr;
     };
     if (cfg->model == KGE_TRANSR) add(KGE_T_REL_B, 1, 1, 1, 1, 1, 1);          // G += ent (x) P
     else if (cfg->model == KGE_SE) { add(KGE_T_REL_A, 1, 0, 2, 0, 0, 0); add(KGE_T_REL_B, 0, 1, 3, 0, 0, 0); }   // G += P (x) ent
@@ -967,6 +971,11 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
       KGE_CUDA_OK(cudaEventRecord(ctx->ev_heavy, ctx->aux));
       if (int rc2 = launch_update_fast<3>(up, cpl, st)) return rc2;
       KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_heavy, 0));
+    }
+    if (mat) {          // this rank's share of every relation matrix's gradient, dense (tables untouched)
+      if (mu_tile_cols(mat_cols(cfg)) == MU_TILE) k_update_mat<2, MU_TILE><<<mgrid, MU_THREADS, 0, st>>>(mu);
+      else k_update_mat<2, 2 * MU_TILE><<<mgrid, MU_THREADS, 0, st>>>(mu);
+      KGE_CUDA_OK(cudaGetLastError());
     }
     pt.end(4);
     if (!sh) pt.keep_open();           // kge_train_apply continues this call's profile slot
@@ -1110,8 +1119,9 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   KGE_REQUIRE(g && loss_out && ws && B > 0 && adam_t >= 1, KGE_EINVAL, "bad kge_train_apply arguments");
   KGE_REQUIRE(!lazy_requested(tables), KGE_EUNSUPPORTED, "row-lazy tables: the data-parallel halves are not implemented");
   KGE_REQUIRE(g->n_peers >= 0 && g->n_peers <= KGE_MAX_PEERS, KGE_EINVAL, "grads.n_peers %d out of range", g->n_peers);
-  KGE_REQUIRE(!is_matrix_model(cfg->model), KGE_EUNSUPPORTED,
-              "data-parallel steps cover the vector models; SE / TransR / RESCAL are single-GPU");
+  const bool mat = is_matrix_model(cfg->model);
+  KGE_REQUIRE(!mat || (g->n_peers == 0 && !has_dense_reg(cfg)), KGE_EUNSUPPORTED,
+              "data-parallel SE / TransR / RESCAL: gradients through grads.dense only, no dense regulariser (else single-GPU)");
   StepWs L;
   if (int rc = layout_step_ws(cfg, B, L)) return rc;
   KGE_REQUIRE(ws_bytes >= L.total, KGE_EWORKSPACE, "workspace %zu < required %zu bytes", ws_bytes, L.total);
@@ -1139,7 +1149,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   rd.row_begin[0] = 0;
   int max_ch = 1;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
-    if (!cols[s]) continue;
+    if (!cols[s] || is_matrix_slot(cfg, s)) continue;      // matrix tables: k_mat_apply below
     UpdateTable& U = up.tab[up.n_tabs];
     U.w = tables->t[s].w; U.m = tables->t[s].m; U.v = tables->t[s].v;
     U.rec = nullptr;
@@ -1229,6 +1239,22 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     if (int rc = launch_update<2>(up, cpl, ublocks, st)) return rc;
   } else {
     if (int rc = launch_update_fast<4>(up, cpl, st)) return rc;      // streaming pass: gradient = gsum row
+  }
+  if (mat) {
+    for (int s = 0; s < KGE_MAX_TABLES; ++s) {
+      if (!cols[s] || !is_matrix_slot(cfg, s)) continue;
+      KGE_REQUIRE(g->dense[s] && ((uintptr_t) g->dense[s] & 15) == 0, KGE_EINVAL, "grads.dense[%d] missing or not 16-byte aligned", s);
+      MatApplyParams ma;
+      ma.w = tables->t[s].w; ma.m = tables->t[s].m; ma.v = tables->t[s].v; ma.gsum = g->dense[s];
+      ma.n_rel = cfg->n_rel; ma.elems = cols[s]; ma.ld = tables->t[s].ld; ma.slot = s;
+      ma.scal = scal; ma.lr_t = up.lr_t; ma.lr_dyn = up.lr_dyn; ma.beta1 = cfg->beta1; ma.beta2 = cfg->beta2; ma.eps = cfg->eps;
+      ma.opt = cfg->optimizer;
+      const int64_t total = cfg->n_rel * (int64_t) cols[s];
+      int64_t blocks = (total + 255) / 256;
+      if (blocks > (int64_t) ctx->sm_count * 16) blocks = (int64_t) ctx->sm_count * 16;
+      k_mat_apply<<<(unsigned) blocks, 256, 0, st>>>(ma);
+      KGE_CUDA_OK(cudaGetLastError());
+    }
   }
   tables->wn_valid[KGE_T_ENT] = (shadow_ok && !dense) ? 1 : 0;
   pt.end(8);

@@ -24,7 +24,22 @@ struct MatUpdTable {
   int use_sh, use_st;      // shared-h / shared-t pair slots feed this table
   int neg_mode;            // per-negative pair slots: 0 none, 1 all, 2 head-corrupted, 3 tail-corrupted
   int ent_row_sh, ent_row_st, ent_row_neg;   // 1: entity row indexes matrix rows (P indexes columns)
+  float* gout;             // MODE 2 (data-parallel gradient half): the relation's summed gradient goes here ([n_rel x ld]), tables untouched
 };
+
+// optimizer step of one matrix element (the arithmetic of k_update_mat's epilogue; k_mat_apply shares it)
+__device__ __forceinline__ void mat_opt1(float& w, float& m, float& v, float g, int opt, float lr_t, float beta1, float beta2, float eps) {
+  if (opt == KGE_OPTIM_SGD) w = w - lr_t * g;
+  else if (opt == KGE_OPTIM_ADAGRAD) {
+    const float acc = v + g * g;
+    v = acc;
+    w = w - lr_t * g / (sqrtf(acc) + eps);
+  } else {
+    m = beta1 * m + (1.f - beta1) * g;
+    v = beta2 * v + (1.f - beta2) * g * g;
+    w = w - lr_t * m / (sqrtf(v) + eps);
+  }
+}
 
 struct MatUpdParams {
   MatUpdTable tab[2];
@@ -179,7 +194,7 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
   float* wr = T.w + r * (int64_t) T.ld;
   float* mr = T.m + r * (int64_t) T.ld;
   float* vr = T.v + r * (int64_t) T.ld;
-  const float scale = (MODE == 0) ? p.scal[T.slot] : 1.f;
+  const float scale = (MODE == 0) ? p.scal[T.slot] : 1.f;     // MODE 2 never reads it
   const float lr_t = p.lr_dyn ? __ldg(p.lr_dyn) : p.lr_t;
   float n2 = 0.f, w2 = 0.f;
 #pragma unroll
@@ -190,22 +205,17 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
       const int cb = col0 + (b >> 2) * 64 + tx * 4 + (b & 3);
       if (ra < T.rows_m && cb < T.cols_m) {
         const int64_t o = (int64_t) ra * T.cols_m + cb;
+        if (MODE == 2) { T.gout[r * (int64_t) T.ld + o] = acc[a][b]; continue; }      // gradient half: raw sum of this rank's pairs
         float w = wr[o];
         float g = acc[a][b] + p.reg_coef * w;
         if (MODE == 1) { n2 += g * g; w2 += w * w; }
         else {
           g *= scale;
-          if (p.opt == KGE_OPTIM_SGD) wr[o] = w - lr_t * g;
-          else if (p.opt == KGE_OPTIM_ADAGRAD) {
-            const float acc = vr[o] + g * g;
-            vr[o] = acc;
-            wr[o] = w - lr_t * g / (sqrtf(acc) + p.eps);
-          } else {
-            float m = p.beta1 * mr[o] + (1.f - p.beta1) * g;
-            float v = p.beta2 * vr[o] + (1.f - p.beta2) * g * g;
-            mr[o] = m; vr[o] = v;
-            wr[o] = w - lr_t * m / (sqrtf(v) + p.eps);
-          }
+          float m = p.opt == KGE_OPTIM_ADAM ? mr[o] : 0.f, v = p.opt != KGE_OPTIM_SGD ? vr[o] : 0.f;
+          mat_opt1(w, m, v, g, p.opt, lr_t, p.beta1, p.beta2, p.eps);
+          if (p.opt == KGE_OPTIM_ADAM) mr[o] = m;
+          if (p.opt != KGE_OPTIM_SGD) vr[o] = v;
+          wr[o] = w;
         }
       }
     }
@@ -222,6 +232,33 @@ __global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p)
       p.part[me] = a;
       p.part[n_cta + me] = b;
     }
+  }
+}
+
+// Data-parallel apply half for a matrix table: g = clip scale * (rank-summed gradient), optimizer step on EVERY
+// element (Keras Adam moves all rows, App. B.2).  One thread per element of the [n_rel x rows_m * cols_m] table.
+struct MatApplyParams {
+  float *w, *m, *v;
+  const float* gsum;       // [n_rel x ld]
+  int64_t n_rel; int elems, ld, slot;
+  const float* scal;
+  float lr_t, beta1, beta2, eps;
+  const float* lr_dyn;
+  int opt;
+};
+__global__ void __launch_bounds__(256) k_mat_apply(const MatApplyParams p) {
+  const int64_t total = p.n_rel * (int64_t) p.elems;
+  const float scale = p.scal[p.slot];
+  const float lr_t = p.lr_dyn ? __ldg(p.lr_dyn) : p.lr_t;
+  for (int64_t x = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; x < total; x += (int64_t) gridDim.x * blockDim.x) {
+    const int64_t r = x / p.elems;
+    const int64_t o = r * p.ld + (x - r * p.elems);
+    float w = p.w[o], m = p.opt == KGE_OPTIM_ADAM ? p.m[o] : 0.f, v = p.opt != KGE_OPTIM_SGD ? p.v[o] : 0.f;
+    const float g = p.gsum[o] * scale;
+    mat_opt1(w, m, v, g, p.opt, lr_t, p.beta1, p.beta2, p.eps);
+    if (p.opt == KGE_OPTIM_ADAM) p.m[o] = m;
+    if (p.opt != KGE_OPTIM_SGD) p.v[o] = v;
+    p.w[o] = w;
   }
 }
 

@@ -10,6 +10,7 @@ torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 from KGE.models.translating_based.TransE import TransE
 from KGE.models.semantic_based.DistMult import DistMult
+from KGE.models.translating_based.TransR import TransR
 rng = np.random.default_rng(0)
 N, R = 500, 9
 X = np.stack([rng.integers(0, N, 4000), rng.integers(0, R, 4000), rng.integers(0, N, 4000)], 1)
@@ -17,9 +18,11 @@ train, val = X[:3600], X[3600:]
 md = {"ind2ent": [f"e{i}" for i in range(N)], "ent2ind": {f"e{i}": i for i in range(N)},
       "ind2rel": [f"r{i}" for i in range(R)], "rel2ind": {f"r{i}": i for i in range(R)}}
 ok = True
-for cls, kw, with_val in ((TransE, {}, True), (DistMult, {}, True), (DistMult, {}, False)):
-    # without validation batches the owners keep w to themselves during an epoch (kge_grads.w_private)
-    m = cls(embedding_params={"embedding_size": 32}, negative_ratio=4, corrupt_side="h+t", **kw)
+for cls, kw, with_val in ((TransE, {}, True), (DistMult, {}, True), (DistMult, {}, False), (TransR, {}, True)):
+    # without validation batches the owners keep w to themselves during an epoch (kge_grads.w_private);
+    # TransR: matrix gradients in the all-reduced flat buffer (exchange "nccl")
+    ep = {"ent_embedding_size": 32, "rel_embedding_size": 24} if cls is TransR else {"embedding_size": 32}
+    m = cls(embedding_params=ep, negative_ratio=4, corrupt_side="h+t", **kw)
     m.train(train, val if with_val else None, md, epochs=3, batch_size=256, seed=5, log_path=tempfile.mkdtemp(),
             early_stopping_rounds=None)
     ok &= bool(getattr(m._engine._peer, "w_private", False)) == (not with_val and m._engine._dp_kind == "owner")

@@ -67,10 +67,49 @@ def test_one_rank_equals_fused_step_bitwise():
         assert torch.equal(a.tab[s].storage, b.tab[s].storage)
 
 
-def test_matrix_models_are_refused():
-    _, _, eng = make_pair("TransR", N, R, 12, 10, score=O.LpDistancePow(2), loss=O.PairwiseHingeLoss(1.0))
+def test_rescal_with_dense_regulariser_is_refused():
+    _, _, eng = make_pair("RESCAL", N, R, 12, loss=O.SquareErrorLoss(), constraint=True)
     with pytest.raises(RuntimeError, match="single-GPU"):
         eng.train_grad(eng.grad_buffer(), rand_triples(np.random.default_rng(0), 8, N, R), 1, 0, 8, 0)
+
+
+MATRIX_CASES = [
+    ("TransR", O.LpDistancePow(2), O.PairwiseHingeLoss(1.0), 4, "h+t", 24, 16, True),
+    ("TransR", O.LpDistance(1), O.SelfAdversarialNegativeSamplingLoss(3.0, 1.0), 5, "t", 20, 28, True),
+    ("SE", O.LpDistance(1), O.PairwiseLogisticLoss(), 3, "h+t", 20, None, True),
+    ("RESCAL", None, O.SquareErrorLoss(), 4, "h", 16, None, False),
+]
+
+
+@pytest.mark.parametrize("G", [1, 2, 3])
+@pytest.mark.parametrize("case", MATRIX_CASES, ids=[c[0] + str(i) for i, c in enumerate(MATRIX_CASES)])
+def test_matrix_models_emulated_ranks_match_full_batch_oracle(case, G):
+    """SE / TransR / RESCAL data parallel: every rank's k_update_mat writes its share of each relation matrix's
+    gradient into the flat buffer (MODE 2), the buffers are summed as the all-reduce would, k_mat_apply steps the
+    matrices — equal to the oracle's step on the whole batch (same negatives, losses 1e-4, weights at the parity
+    tolerance); G = 1 against the fused step as well."""
+    model, score, loss, k, side, d, dr, constraint = case
+    rng = np.random.default_rng(5)
+    ref, W, eng = make_pair(model, N, R, d, dr, score=score, loss=loss, k=k, side=side, constraint=constraint)
+    opt = RS.TFAdam()
+    B, seed = 48, 21
+    bufs = [eng.grad_buffer() for _ in range(G)]
+    for step in range(3):
+        X = rand_triples(rng, B, N, R)
+        ids, k_eff = RS.sample_negatives(seed, step, X, k, side, N)
+        l_ref, _ = RS.run_single_batch(ref, W, opt, X, ids, k_eff, side, True)
+        negs = []
+        for g in range(G):
+            lo, hi = dp.split_even(B, G, g)
+            negs.append(eng.train_grad(bufs[g], X[lo:hi], seed, step, B, lo, g, G, want_negatives=True))
+        assert np.array_equal(torch.cat(negs).cpu().numpy(), ids), "ranks must draw the one-GPU negatives"
+        for g in range(1, G):
+            bufs[0].flat += bufs[g].flat
+        l_gpu = eng.train_apply(bufs[0], hi - lo)
+        assert abs(float(l_gpu.item()) - l_ref) <= 1e-4 * max(1.0, abs(l_ref)), (step, float(l_gpu.item()), l_ref)
+        got = tables_of(eng, model)
+        for kk, v in W.data.items():
+            assert_weights_close(got[kk], v, 1e-3, step + 1, (step, kk))
 
 
 @pytest.mark.parametrize("G", [2, 3])
