@@ -83,7 +83,7 @@ inline int mu_tile_cols(int cols_m) {
   return (wide && cols_m > MU_TILE) ? 2 * MU_TILE : MU_TILE;
 }
 template <int MODE, int TC>
-__global__ void __launch_bounds__(MU_THREADS) k_update_mat(const MatUpdParams p) {
+__global__ void __launch_bounds__(MU_THREADS, TC == MU_TILE ? 4 : 2) k_update_mat(const MatUpdParams p) {
   constexpr int NB = TC / 16;          // output columns per thread: 4 + 4 (second set 64 columns on) for TC = 128
   __shared__ float s_row[MU_KC][MU_TILE];
   __shared__ float s_col[MU_KC][TC];
