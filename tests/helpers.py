@@ -41,12 +41,14 @@ def rel_err(a, b):
 
 def assert_weights_close(got, want, lr, steps, where=""):
     """Adam divides by sqrt(v): where a summed gradient cancels to ~1e-6 the update
-    lr*g/(|g|+eps') amplifies 1e-7 summation-order noise to a fraction of lr.  So: all
-    elements within steps*lr (Adam's per-step bound), and all but 1% within 1e-4 relative."""
+    lr*g/(|g|+eps') amplifies 1e-7 summation-order noise to a fraction of lr.  Observed over the 594 table
+    comparisons of the GPU suite (round 2, gpurun_out/weights_obs.log): max |dW| = 0.069 of steps*lr (Adam's
+    per-step bound), at most 0.55 % of a table's elements outside 1e-4 relative.  Asserted at twice that: all
+    elements within 0.15 * steps*lr, all but 1 % within 1e-4 relative; the observed values are printed."""
     got, want = torch.as_tensor(got).double(), torch.as_tensor(want).double()
     diff = (got - want).abs()
     scale = float(want.abs().max()) + 1e-12
-    assert float(diff.max()) <= steps * lr * 1.01 + 1e-6 * scale, (where, float(diff.max()))
+    assert float(diff.max()) <= 0.15 * steps * lr + 1e-6 * scale, (where, float(diff.max()))
     frac = float((diff > 1e-4 * scale).double().mean())
     print("weights %s: max|dW| %.3g (%.3g of scale, bound %.3g), outside 1e-4: %.5f" % (
         where, float(diff.max()), float(diff.max()) / scale, steps * lr, frac))
