@@ -412,7 +412,9 @@ inline void layout_proj_ws(const kge_cfg* c, int64_t Q, int64_t span, ProjWs& L)
   L.ldp = (proj_dout(c) + 3) / 4 * 4;
   L.span_pad = (span + LP_T - 1) / LP_T * LP_T;
   const size_t per_rel = sizeof(float) * (size_t) L.span_pad * L.ldp;
-  int64_t rc = (int64_t) (PROJ_TABLE_BUDGET / per_rel);
+  size_t budget = PROJ_TABLE_BUDGET;
+  if (const char* e = getenv("KGE_PROJ_BUDGET_KB")) budget = (size_t) atoll(e) << 10;      // tests: force several relation chunks
+  int64_t rc = (int64_t) (budget / per_rel);
   rc = rc < 1 ? 1 : (rc > c->n_rel ? c->n_rel : rc);
   const int64_t qt = Q / LP_T + 1;                       // tiles of one chunk <= Q / 128 + rel_chunk <= 65535 (gridDim.y)
   if (rc > 65535 - qt) rc = 65535 - qt > 1 ? 65535 - qt : 1;
@@ -431,7 +433,7 @@ inline void layout_proj_ws(const kge_cfg* c, int64_t Q, int64_t span, ProjWs& L)
   L.total = o;
   // a narrower shard fits more relations per chunk: what any shard of this span or less can ask for
   const size_t all = per_rel * (size_t) c->n_rel;
-  const size_t cap = all < PROJ_TABLE_BUDGET ? all : PROJ_TABLE_BUDGET;
+  const size_t cap = all < budget ? all : budget;
   L.total_max = L.off_p + ((per_rel > cap ? per_rel : cap) + 255) / 256 * 256;
 }
 

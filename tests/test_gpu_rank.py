@@ -228,3 +228,28 @@ def test_projected_table_rank_equals_generic(model, score, d, dr, n_ent, side):
         oracle_rank_check(band, ref, W, Xq[qi], side, pos, int(t_flt[qi]) + 1, qi)
     print(model, score, side, band.summary())
     assert band.used <= 4, band.summary()
+
+
+@pytest.mark.parametrize("model,d,dr", [("TransD", 50, 30), ("TransR", 40, 24), ("SE", 24, None)])
+def test_projected_table_rank_in_relation_chunks(model, d, dr):
+    """The projected tables of all relations rarely fit the workspace budget (256 MB; FB15k-237 TransR: 1.4 GB):
+    relations are then taken a chunk at a time.  With the budget forced down to two relations per chunk
+    (KGE_PROJ_BUDGET_KB) the counts must equal the one-chunk run exactly."""
+    import os
+    from KGE._b200.filter import build_filter
+    n_ent = 900
+    rng = np.random.default_rng(29)
+    ref, W, eng = make_pair(model, n_ent, R, d, dr, score=_score_for(model, "l1"), loss=LOSSES["hinge"])
+    pos = rand_triples(rng, 12000, n_ent, R)
+    Xq = pos[:500]
+    for side, s in (("h", 0), ("t", 1)):
+        off, ids = build_filter(pos, Xq, side, n_ent, eng.device)
+        one = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+        dout = dr if (dr and model != "SE") else d
+        per_rel_kb = (1024 * ((dout + 3) // 4 * 4) * 4) // 1024 + 1
+        os.environ["KGE_PROJ_BUDGET_KB"] = str(2 * per_rel_kb)
+        try:
+            many = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+        finally:
+            os.environ.pop("KGE_PROJ_BUDGET_KB")
+        assert np.array_equal(one, many), side
