@@ -34,7 +34,7 @@ import torch
 
 WORKLOAD = {"workload": "C2 DistMult d=200 BCE uniform h+t k=64 B=1024 FB15k-shape (N=14951,R=1345)",
             "model": "DistMult", "n_ent": 14951, "n_rel": 1345, "d": 200, "B": 1024, "k": 64,
-            "side": "h+t", "n_train": 483142, "eval_Q": 16384}
+            "side": "h+t", "n_train": 483142, "eval_Q": 16384, "eval_Q_e2e": 59071}
 METRIC = "train triples/sec (pos+neg)"
 
 
@@ -424,24 +424,35 @@ def run_eval(eng, train, rank, world, device, reps=3):
     torch.cuda.synchronize()
     phases, n_calls = eng.profile_end()
 
-    # ---- e2e: host positive_X + host queries -> ranks on the host, per evaluate() call ----
+    # ---- e2e: host positive_X + host queries -> ranks on the host, one evaluate() call per side ----
+    # KGEModel.evaluate (BaseModel._rank_block) uploads positive_X and the queries, builds the filter index ONCE and
+    # ranks the queries in blocks of Q; the call timed here has the FB15k test split's size (59 071 queries = 4 blocks)
+    Qe, blk = W["eval_Q_e2e"], Q
+    q_e2e = np.concatenate([q_all, train[rng.integers(0, len(train), Qe - Q)]])
     pos_host = torch.from_numpy(train).pin_memory()
-    q_host = torch.from_numpy(q_all).pin_memory()
-    out_host = {s: torch.zeros(Q, dtype=torch.int32).pin_memory() for s in ("h", "t")}
+    q_host = torch.from_numpy(q_e2e).pin_memory()
+    out_host = {s: torch.zeros(Qe, dtype=torch.int32).pin_memory() for s in ("h", "t")}
+
+    def evaluate_call(s):
+        pos_dev = pos_host.to(device, non_blocking=True)
+        q_dev = q_host.to(device, non_blocking=True)
+        idx = eng.filter_index(pos_dev, s)
+        for lo in range(0, Qe, blk):
+            qb = q_dev[lo:lo + blk]
+            out_host[s][lo:lo + blk].copy_(counts(s, qb, idx.lookup(qb)), non_blocking=True)
+    for s in ("h", "t"):          # one untimed call per side (first cudaMalloc of the staging / index / ragged-block buffers)
+        evaluate_call(s)
     if world > 1:
         torch.distributed.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(reps):
         for s in ("h", "t"):
-            pos_dev = pos_host.to(device, non_blocking=True)
-            q_dev = q_host.to(device, non_blocking=True)
-            idx = eng.filter_index(pos_dev, s)
-            out_host[s].copy_(counts(s, q_dev, idx.lookup(q_dev)), non_blocking=True)
+            evaluate_call(s)
         torch.cuda.synchronize()
     ms_e2e = (time.perf_counter() - t0) * 1e3
     for s in ("h", "t"):
-        assert torch.equal(out_host[s], cnts[s].cpu()), "e2e ranks differ from the resident-input ranks"
+        assert torch.equal(out_host[s][:Q], cnts[s].cpu()), "e2e ranks differ from the resident-input ranks"
 
     t = torch.tensor([a.elapsed_time(b), ms_e2e], dtype=torch.float64, device=device)
     if world > 1:
@@ -451,8 +462,8 @@ def run_eval(eng, train, rank, world, device, reps=3):
     both = np.concatenate([ranks["h"], ranks["t"]])
     gemm_ms = phases["rank_gemm"] / max(n_calls, 1)
     flops = 2.0 * (e_hi - e_lo) * W["d"] * Q                  # algorithmic, this rank's slice: 2*N*d per query
-    return {"queries": 2 * Q * reps, "ms": ms, "ms_e2e": ms_e2e, "kernel_ms": phases["rank"], "gemm_ms": gemm_ms,
-            "h2d_bytes_per_call": int(pos_host.numel() * 8 + q_host.numel() * 8), "d2h_bytes_per_call": 4 * Q,
+    return {"queries": 2 * Q * reps, "queries_e2e": 2 * Qe * reps, "ms": ms, "ms_e2e": ms_e2e, "kernel_ms": phases["rank"], "gemm_ms": gemm_ms,
+            "h2d_bytes_per_call": int(pos_host.numel() * 8 + q_host.numel() * 8), "d2h_bytes_per_call": 4 * Qe,
             "fix_ms": phases["rank_fix"] / max(n_calls, 1), "gemm_tflops": flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms else None,
             "gemm_flops": flops, "sharding": "entity shards + NCCL all-reduce of int32 counts" if world > 1 else "none",
             "mrr": float(np.mean(1 / both)), "hits10": float(np.mean(both <= 10)), "ranks": ranks, "queries_used": q_all}
@@ -798,11 +809,12 @@ def main():
                                    "TensorFlow reference not installable)"},
         "eval": {"metric": "filtered-eval queries/sec", "value": ev["queries"] / (ev["ms"] * 1e-3), "unit": "queries/s",
                  "value_note": "kernel-only: queries, filter index and ranges resident; kge_rank (+ all-reduce of counts at N > 1)",
-                 "e2e": {"value": ev["queries"] / (ev["ms_e2e"] * 1e-3), "unit": "queries/s",
+                 "e2e": {"value": ev["queries_e2e"] / (ev["ms_e2e"] * 1e-3), "unit": "queries/s", "queries": ev["queries_e2e"],
                          "h2d_bytes_per_call": ev["h2d_bytes_per_call"], "d2h_bytes_per_call": ev["d2h_bytes_per_call"],
-                         "what": "per evaluate() call and side: H2D of positive_X (483 142 triples) and of the queries, "
-                                 "kge_filter_index_build (one 64-bit radix sort), kge_filter_lookup, kge_rank, "
-                                 "all-reduce, D2H of the counts; host synchronised after both sides"},
+                         "what": "one evaluate() call per side over 59 071 queries (the FB15k test split): H2D of positive_X "
+                                 "(483 142 triples) and of the queries, kge_filter_index_build once (one 64-bit radix sort), then "
+                                 "per block of 16 384 queries kge_filter_lookup, kge_rank, all-reduce, D2H of the counts; host "
+                                 "synchronised after both sides; one untimed warm-up call per side, then 3 timed"},
                  "queries": ev["queries"], "sharding": ev["sharding"],
                  "kernel": "k_rank_dot_tc (tcgen05 kind::tf32) + k_rank_dot_fix/filter",
                  "mrr": ev["mrr"], "hits10": ev["hits10"],
