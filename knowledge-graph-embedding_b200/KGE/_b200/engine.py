@@ -35,6 +35,13 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def _refuse_empty(B):
+    """Before any step counter moves: kge_train_step refuses B == 0 (the reference's batch iterator never yields an
+    empty batch, data_utils.py:176-196), and a refused call must leave adam_t / lazy_t where they were."""
+    if B <= 0:
+        raise ValueError("empty batch")
+
+
 def _ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
 
@@ -287,6 +294,7 @@ class Engine:
         unchanged until the call that trains on it) / next_step: the following batch, whose gradient records are
         grouped while this step runs (kge_train_step_next); the results do not depend on it."""
         X = self._ids(triples)
+        _refuse_empty(X.shape[0])
         if not is_train:
             self.flush()                    # (also refuses stale data-parallel replicas)
         if next_triples is not None and is_train and neg_override is None and not want_negatives and not self.lazy:
@@ -330,6 +338,7 @@ class Engine:
         next_host: the following batch (pinned host tensor, same shape): copied and grouped under this step
         (kge_train_step_host_next); the call that trains on it copies nothing."""
         B = host_triples.shape[0]
+        _refuse_empty(B)
         if next_host is not None and is_train and not self.lazy and next_host.shape[0] == B:
             dt = torch.int64 if self.cfg.id_dtype == 1 else torch.int32
             if host_triples.dtype != dt or next_host.dtype != dt or not host_triples.is_contiguous() or not next_host.is_contiguous():

@@ -529,6 +529,8 @@ class KGEModel:
         assert corrupt_side in ("h", "t"), "corrupt_side can be 'h' or 't'"
         X = np.asarray(_plain(X)).reshape(-1, 3).astype(np.int64)
         side = _lib.SIDE_H if corrupt_side == "h" else _lib.SIDE_T
+        if len(X) == 0:                   # an empty split: the reference's loop (BaseModel.py:602-604) yields no ranks
+            return np.zeros(0, dtype=np.int64)
         # the known-positive index is built ONCE per call (one device sort of positive_X), every block of
         # queries then costs two binary searches per query (kge_filter_lookup)
         index = None if positive_X is None else eng.filter_index(np.asarray(_plain(positive_X)), corrupt_side)

@@ -39,7 +39,7 @@ def rel_err(a, b):
     return float((a - b).abs().max() / (b.abs().max() + 1e-12))
 
 
-def assert_weights_close(got, want, lr, steps, where=""):
+def assert_weights_close(got, want, lr, steps, where="", max_frac=0.01):
     """Adam divides by sqrt(v): where a summed gradient cancels to ~1e-6 the update
     lr*g/(|g|+eps') amplifies 1e-7 summation-order noise to a fraction of lr.  Observed over the 594 table
     comparisons of the GPU suite (round 2, gpurun_out/weights_obs.log): max |dW| = 0.069 of steps*lr (Adam's
@@ -52,7 +52,7 @@ def assert_weights_close(got, want, lr, steps, where=""):
     frac = float((diff > 1e-4 * scale).double().mean())
     print("weights %s: max|dW| %.3g (%.3g of scale, bound %.3g), outside 1e-4: %.5f" % (
         where, float(diff.max()), float(diff.max()) / scale, steps * lr, frac))
-    assert frac < 0.01, (where, frac, float(diff.max()))
+    assert frac < max_frac, (where, frac, float(diff.max()))
 
 
 class RankBand:
