@@ -109,6 +109,11 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 // the same butterflies over aligned groups of W lanes (W = 16: two independent rows per warp, step_narrow_kernels.cuh).
+// Programmatic dependent launch (sm_90+): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may
+// become resident while its predecessor on the stream still runs; pdl_wait() returns once that predecessor has
+// completed and its writes are visible (a no-op for an ordinary launch).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // With the upper half of a warp holding zeros, warp_sum and warp_sum_w<16> return the same bits in the lower half.
 template <int W> __device__ __forceinline__ float warp_sum_w(float v) {
 #pragma unroll

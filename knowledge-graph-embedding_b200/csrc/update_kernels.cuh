@@ -578,6 +578,7 @@ __global__ void __launch_bounds__(64, CPL <= 2 ? 18 : 1) k_update_fast(const Upd
   while (j < p.n_tabs - 1 && row >= p.tab[j].rows) { row -= p.tab[j].rows; ++j; }
   const UpdateTable& T = p.tab[j];
   if (row >= T.rows) return;                       // owner-partitioned apply: the last table may own no rows
+  pdl_wait();                                      // everything above is launch-parameter arithmetic
   if (MODE == 4 && p.scal[SCAL_ABORT] != 0.f) return;   // a peer never reached the barrier: leave the tables alone
   row += T.row_lo;
   const int nch = (T.cols + 3) >> 2;
@@ -630,6 +631,7 @@ __global__ void __launch_bounds__(64, 18) k_update_narrow(const UpdateParams p) 
   while (j < p.n_tabs - 1 && row >= p.tab[j].rows) { row -= p.tab[j].rows; ++j; }
   const UpdateTable& T = p.tab[j];
   const bool valid = in_range && row < T.rows;
+  pdl_wait();
   const int nch = (T.cols + 3) >> 2;
   const bool mine_l = hl < nch;
   const float4* wi = reinterpret_cast<const float4*>(T.w_in + row * (int64_t) T.ld);
@@ -736,15 +738,47 @@ inline int launch_update_heavy(const UpdateParams& up, int cpl, int64_t max_heav
   return KGE_OK;
 }
 
+// KGE_PDL=1 launches the row update with programmatic stream serialization behind the step kernel (its launch
+// latency then overlaps the step kernel's last CTAs).  Measured on C2 (round 2, scripts/gpu_pdl.sh): 80.9 vs 83.3 us
+// per step with L2 flushed, but 871 vs 883 M triples/s in the steady state and no change end to end; with an
+// explicit griddepcontrol.launch_dependents in k_step (at its start / after the negatives) 90.3 / 87.2 us — the
+// parked update CTAs take the slots the next batch's grouping chain runs in.  Off by default.
+inline bool pdl_enabled() {
+  static const int on = [] { const char* e = getenv("KGE_PDL"); return e ? atoi(e) : 0; }();
+  return on != 0;
+}
+template <class K, class P>
+inline cudaError_t launch_pdl(K kern, unsigned grid, unsigned block, cudaStream_t st, const P& prm) {
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = dim3(grid); lc.blockDim = dim3(block); lc.dynamicSmemBytes = 0; lc.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  lc.attrs = at; lc.numAttrs = 1;
+  return cudaLaunchKernelEx(&lc, kern, prm);
+}
+
 template <int MODE>
 inline int launch_update_fast(const UpdateParams& up, int cpl, cudaStream_t st) {
   if (MODE == 0 && update_narrow_ok(up, cpl)) {
-    k_update_narrow<<<(unsigned) ((up.total_rows + 3) / 4), 64, 0, st>>>(up);
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e;
+    if (pdl_enabled()) e = launch_pdl(k_update_narrow, (unsigned) ((up.total_rows + 3) / 4), 64, st, up);
+    else { k_update_narrow<<<(unsigned) ((up.total_rows + 3) / 4), 64, 0, st>>>(up); e = cudaGetLastError(); }
     if (e != cudaSuccess) { set_error("k_update_narrow launch failed: %s", cudaGetErrorString(e)); return KGE_ECUDA; }
     return KGE_OK;
   }
   const unsigned blocks = (unsigned) ((up.total_rows + 1) / 2);
+  if (MODE == 0 && pdl_enabled()) {
+    cudaError_t e;
+    switch (cpl) {
+      case 1: e = launch_pdl(k_update_fast<1, MODE>, blocks, 64, st, up); break;
+      case 2: e = launch_pdl(k_update_fast<2, MODE>, blocks, 64, st, up); break;
+      case 4: e = launch_pdl(k_update_fast<4, MODE>, blocks, 64, st, up); break;
+      default: e = launch_pdl(k_update_fast<8, MODE>, blocks, 64, st, up); break;
+    }
+    if (e != cudaSuccess) { set_error("k_update_fast launch failed: %s", cudaGetErrorString(e)); return KGE_ECUDA; }
+    return KGE_OK;
+  }
   switch (cpl) {
     case 1: k_update_fast<1, MODE><<<blocks, 64, 0, st>>>(up); break;
     case 2: k_update_fast<2, MODE><<<blocks, 64, 0, st>>>(up); break;
