@@ -433,13 +433,26 @@ def run_eval(eng, train, rank, world, device, reps=3):
     q_host = torch.from_numpy(q_e2e).pin_memory()
     out_host = {s: torch.zeros(Qe, dtype=torch.int32).pin_memory() for s in ("h", "t")}
 
-    def evaluate_call(s):
+    def evaluate_call(s, marks=None):
+        def mark(name):
+            if marks is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                marks.append((name, e))
+        mark("start")
         pos_dev = pos_host.to(device, non_blocking=True)
         q_dev = q_host.to(device, non_blocking=True)
+        mark("h2d")
         idx = eng.filter_index(pos_dev, s)
+        mark("index_build")
         for lo in range(0, Qe, blk):
             qb = q_dev[lo:lo + blk]
-            out_host[s][lo:lo + blk].copy_(counts(s, qb, idx.lookup(qb)), non_blocking=True)
+            f = idx.lookup(qb)
+            mark("lookup")
+            c = counts(s, qb, f)
+            mark("rank")
+            out_host[s][lo:lo + blk].copy_(c, non_blocking=True)
+            mark("d2h")
     for s in ("h", "t"):          # one untimed call per side (first cudaMalloc of the staging / index / ragged-block buffers)
         evaluate_call(s)
     if world > 1:
@@ -453,6 +466,12 @@ def run_eval(eng, train, rank, world, device, reps=3):
     ms_e2e = (time.perf_counter() - t0) * 1e3
     for s in ("h", "t"):
         assert torch.equal(out_host[s][:Q], cnts[s].cpu()), "e2e ranks differ from the resident-input ranks"
+    seg = {}                          # where one call's device time goes (an extra, untimed call with events between the stages)
+    marks = []
+    evaluate_call("t", marks)
+    torch.cuda.synchronize()
+    for (_, e0), (name, e1) in zip(marks[:-1], marks[1:]):
+        seg[name] = round(seg.get(name, 0.0) + e0.elapsed_time(e1), 4)
 
     t = torch.tensor([a.elapsed_time(b), ms_e2e], dtype=torch.float64, device=device)
     if world > 1:
@@ -462,7 +481,7 @@ def run_eval(eng, train, rank, world, device, reps=3):
     both = np.concatenate([ranks["h"], ranks["t"]])
     gemm_ms = phases["rank_gemm"] / max(n_calls, 1)
     flops = 2.0 * (e_hi - e_lo) * W["d"] * Q                  # algorithmic, this rank's slice: 2*N*d per query
-    return {"queries": 2 * Q * reps, "queries_e2e": 2 * Qe * reps, "ms": ms, "ms_e2e": ms_e2e, "kernel_ms": phases["rank"], "gemm_ms": gemm_ms,
+    return {"queries": 2 * Q * reps, "queries_e2e": 2 * Qe * reps, "e2e_segments_ms": seg, "ms": ms, "ms_e2e": ms_e2e, "kernel_ms": phases["rank"], "gemm_ms": gemm_ms,
             "h2d_bytes_per_call": int(pos_host.numel() * 8 + q_host.numel() * 8), "d2h_bytes_per_call": 4 * Qe,
             "fix_ms": phases["rank_fix"] / max(n_calls, 1), "gemm_tflops": flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms else None,
             "gemm_flops": flops, "sharding": "entity shards + NCCL all-reduce of int32 counts" if world > 1 else "none",
@@ -809,7 +828,7 @@ def main():
                                    "TensorFlow reference not installable)"},
         "eval": {"metric": "filtered-eval queries/sec", "value": ev["queries"] / (ev["ms"] * 1e-3), "unit": "queries/s",
                  "value_note": "kernel-only: queries, filter index and ranges resident; kge_rank (+ all-reduce of counts at N > 1)",
-                 "e2e": {"value": ev["queries_e2e"] / (ev["ms_e2e"] * 1e-3), "unit": "queries/s", "queries": ev["queries_e2e"],
+                 "e2e": {"value": ev["queries_e2e"] / (ev["ms_e2e"] * 1e-3), "unit": "queries/s", "queries": ev["queries_e2e"], "device_ms_per_call": ev["e2e_segments_ms"],
                          "h2d_bytes_per_call": ev["h2d_bytes_per_call"], "d2h_bytes_per_call": ev["d2h_bytes_per_call"],
                          "what": "one evaluate() call per side over 59 071 queries (the FB15k test split): H2D of positive_X "
                                  "(483 142 triples) and of the queries, kge_filter_index_build once (one 64-bit radix sort), then "

@@ -56,3 +56,37 @@ for rep in range(5):
     torch.cuda.synchronize()
     t1 = time.perf_counter()
     print("rep", rep, "wall_ms", round((t1 - t0) * 1e3, 2), "host marks ms", [round((m - t0) * 1e3, 2) for m in marks])
+
+# one evaluate()-shaped call (bench.py's end-to-end leg): 59 071 queries per side in blocks of 16 384, one index per call
+Qe, blk = 59071, 16384
+q_e = train[rng.integers(0, len(train), Qe)]
+qe_host = torch.from_numpy(q_e).pin_memory()
+oute = torch.zeros(Qe, dtype=torch.int32).pin_memory()
+for rep in range(5):
+    for s, sid in (("h", 0), ("t", 1)):
+        names, evs = [], []
+        def mark(n):
+            e = ev(); e.record(); names.append(n); evs.append(e)
+        t0 = time.perf_counter()
+        mark("start")
+        pos_dev = pos_host.to(dev, non_blocking=True); q_dev = qe_host.to(dev, non_blocking=True)
+        mark("h2d")
+        idx = eng.filter_index(pos_dev, s)
+        mark("index")
+        for lo in range(0, Qe, blk):
+            qb = q_dev[lo:lo + blk]
+            f = idx.lookup(qb)
+            mark("lookup")
+            c = eng.rank_counts(qb, sid, f[0], f[1])
+            mark("rank")
+            oute[lo:lo + blk].copy_(c, non_blocking=True)
+            mark("d2h")
+        t1 = time.perf_counter()
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        if rep == 4:
+            seg = {}
+            for n, a, b in zip(names[1:], evs[:-1], evs[1:]):
+                seg[n] = round(seg.get(n, 0) + a.elapsed_time(b), 3)
+            print("evaluate() call side", s, "device segments ms", seg, "sum", round(evs[0].elapsed_time(evs[-1]), 3),
+                  "host enqueue", round((t1 - t0) * 1e3, 3), "wall", round((t2 - t0) * 1e3, 3))
