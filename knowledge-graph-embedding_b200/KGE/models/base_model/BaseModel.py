@@ -89,6 +89,48 @@ class ShardedTableView:
         self._trainer.assign_table(self._slot, value)
 
 
+class _CheckpointWriter:
+    """Checkpoint files written off the training thread (one GPU, unsharded tables).  `snapshot` copies a device
+    tensor into a pinned host buffer in STREAM order — the snapshot is the state after the last enqueued step, and
+    the steps enqueued afterwards run while it drains; a worker thread waits for the copies and writes the files
+    (to a temporary name, then renamed) under the next epoch.  One write in flight: the next save, any load and
+    the end of train() join it first, so the pinned buffers are never overwritten under a writer."""
+
+    def __init__(self):
+        self.thread, self.buf, self.err = None, {}, None
+
+    def snapshot(self, key, t):
+        b = self.buf.get(key)
+        if b is None or b.shape != t.shape or b.dtype != t.dtype:
+            b = self.buf[key] = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        b.copy_(t, non_blocking=True)
+        return b
+
+    def submit(self, jobs):
+        import threading
+        done = torch.cuda.Event()
+        done.record()
+
+        def work():
+            try:
+                done.synchronize()
+                for obj, path in jobs:
+                    torch.save(obj, path + ".tmp")
+                    os.replace(path + ".tmp", path)
+            except Exception as e:          # surfaced by the next join()
+                self.err = e
+        self.thread = threading.Thread(target=work, name="kge-checkpoint")
+        self.thread.start()
+
+    def join(self):
+        if self.thread is not None:
+            self.thread.join()
+            self.thread = None
+        if self.err is not None:
+            e, self.err = self.err, None
+            raise e
+
+
 class KGEModel:
     """Base of all models.  Subclasses declare `MODEL` (kernel family name) and
     `_tables(n_ent, n_rel)` -> {key: (shape, init)} with init = limit | "eye"."""
@@ -411,6 +453,7 @@ class KGEModel:
             # the next step: every rank waits here
             if world_size > 1:
                 torch.distributed.barrier()
+        self._join_checkpoint()           # the last checkpoint's files are complete before train() returns
         if log_projector:
             writers.projector(self.model_weights, self.metadata)
         writers.close()
@@ -449,29 +492,49 @@ class KGEModel:
         owner-partitioned exchange; its shard under sharded tables) with the row-lazy stamps.  Under torchrun
         every rank must call this (reading a sharded table is a collective)."""
         rank, world = _dp.world()
-        weights = {k: v.tensor.detach().cpu() for k, v in self.model_weights.items()}       # collective when sharded
+        self._join_checkpoint()
+        # one GPU, unsharded: pinned snapshots in stream order + a writer thread (the files are complete when
+        # train() returns or the checkpoint is loaded); otherwise (collective reads) written here
+        bg = world == 1 and self._sharded is None and os.environ.get("KGE_B200_ASYNC_CKPT", "1") != "0"
+        if bg and getattr(self, "_ckpt_writer", None) is None:
+            self._ckpt_writer = _CheckpointWriter()
+        host = (lambda key, t: self._ckpt_writer.snapshot(key, t.detach())) if bg else (lambda key, t: t.detach().cpu())
         engines = self._train_engines()
-        prog = getattr(self, "_progress", {"epoch": -1, "step": 0})
-        if rank == 0:
-            torch.save({"weights": weights, "adam_t": engines[0].adam_t, "epoch": prog["epoch"], "step": prog["step"],
-                        "world": world, "sharded": self._sharded is not None, "n_engines": len(engines),
-                        "train_loss_history": list(getattr(self, "train_loss_history", [])),
-                        "val_loss_history": list(getattr(self, "val_loss_history", [])),
-                        "best_step": getattr(self, "best_step", None), "patience": int(patience)}, self._ckpt_path())
-        opt = []
         for e in engines:
             e.flush()
+        weights = {k: host("w." + k, v.tensor) for k, v in self.model_weights.items()}       # collective when sharded
+        prog = getattr(self, "_progress", {"epoch": -1, "step": 0})
+        jobs = []
+        if rank == 0:
+            jobs.append(({"weights": weights, "adam_t": engines[0].adam_t, "epoch": prog["epoch"], "step": prog["step"],
+                          "world": world, "sharded": self._sharded is not None, "n_engines": len(engines),
+                          "train_loss_history": list(getattr(self, "train_loss_history", [])),
+                          "val_loss_history": list(getattr(self, "val_loss_history", [])),
+                          "best_step": getattr(self, "best_step", None), "patience": int(patience)}, self._ckpt_path()))
+        opt = []
+        for i, e in enumerate(engines):
             opt.append({"adam_t": e.adam_t, "lazy_t": e.lazy_t,
-                        "m": {s: t.m.cpu() for s, t in e.tab.items() if t.m is not None},
-                        "v": {s: t.v.cpu() for s, t in e.tab.items() if t.v is not None},
-                        "last": {s: t.last.cpu() for s, t in e.tab.items() if t.last is not None}})
-        torch.save({"world": world, "sharded": self._sharded is not None, "engines": opt}, self._opt_path(rank))
+                        "m": {s: host("m.%d.%d" % (i, s), t.m) for s, t in e.tab.items() if t.m is not None},
+                        "v": {s: host("v.%d.%d" % (i, s), t.v) for s, t in e.tab.items() if t.v is not None},
+                        "last": {s: host("l.%d.%d" % (i, s), t.last) for s, t in e.tab.items() if t.last is not None}})
+        jobs.append(({"world": world, "sharded": self._sharded is not None, "engines": opt}, self._opt_path(rank)))
+        if bg:
+            self._ckpt_writer.submit(jobs)
+        else:
+            for obj, path in jobs:
+                torch.save(obj, path)
+
+    def _join_checkpoint(self):
+        w = getattr(self, "_ckpt_writer", None)
+        if w is not None:
+            w.join()
 
     def _load_checkpoint(self, with_optimizer=True):
         """Weights from `ckpt.pt`; with_optimizer: also this rank's optimizer slots, Adam step and lazy stamps
         (only when the file was written by the same world size / sharding, else the slots restart at zero with
         a warning).  Returns the checkpoint's bookkeeping dict."""
         rank, world = _dp.world()
+        self._join_checkpoint()
         if world > 1:
             torch.distributed.barrier()
         state = torch.load(self._ckpt_path())
@@ -600,11 +663,31 @@ class _Writers:
         if which in self.w:
             self.w[which].add_scalar("loss", value, step)
 
-    def histograms(self, weights, step):
-        if "root" in self.w:
-            for k, v in weights.items():
-                if v.tensor.numel() <= (1 << 22):
-                    self.w["root"].add_histogram(k, v.numpy(), step)
+    def histograms(self, weights, step, buckets=30):
+        """tf.summary.histogram's 30 equal-width buckets (BaseModel.py:463-483), counted on the device: only the
+        bucket counts and four moments cross to the host (the table itself stays where it is)."""
+        if "root" not in self.w:
+            return
+        for k, v in weights.items():
+            t = v.tensor.detach()
+            if t.numel() == 0 or t.numel() > (1 << 28):
+                continue
+            if not t.is_cuda:
+                self.w["root"].add_histogram(k, v.numpy(), step)
+                continue
+            t = t.float().reshape(-1)
+            lo, hi = torch.aminmax(t)
+            stats = torch.stack([lo.double(), hi.double(), t.sum(dtype=torch.float64), (t * t).sum(dtype=torch.float64)]).cpu()
+            lo_f, hi_f = float(stats[0]), float(stats[1])
+            if not (math.isfinite(lo_f) and math.isfinite(hi_f)):
+                continue
+            if hi_f <= lo_f:
+                hi_f = lo_f + 1e-12 + abs(lo_f) * 1e-6
+            counts = torch.histc(t, bins=buckets, min=lo_f, max=hi_f).cpu().numpy()
+            limits = np.linspace(lo_f, hi_f, buckets + 1)[1:]
+            self.w["root"].add_histogram_raw(k, min=lo_f, max=hi_f, num=int(t.numel()), sum=float(stats[2]),
+                                             sum_squares=float(stats[3]), bucket_limits=limits.tolist(),
+                                             bucket_counts=counts.tolist(), global_step=step)
 
     def projector(self, weights, metadata):
         """metadata + embedding tsv files and a projector_config.pbtxt in log_path."""

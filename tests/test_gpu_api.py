@@ -3,6 +3,7 @@ tests/test_ns_strategy.py and tests/test_integration.py (same invariants, same c
 matrix), plus golden parity of the API path itself (model classes -> C-ABI)."""
 import itertools
 import math
+import os
 
 import numpy as np
 import pytest
@@ -306,6 +307,54 @@ def test_resume_continues_bitwise(lazy, tmp_path, monkeypatch):
     assert ef.adam_t == ea.adam_t
     for s in ef.tab:
         assert torch.equal(ef.tab[s].m, ea.tab[s].m) and torch.equal(ef.tab[s].v, ea.tab[s].v), s
+
+
+def test_background_checkpoint_equals_the_synchronous_one(tmp_path, monkeypatch):
+    """One GPU: the checkpoint is a pinned snapshot in stream order written by a worker thread under the next epoch
+    (BaseModel._CheckpointWriter).  Its files are complete when train() returns and hold exactly what the
+    synchronous writer (KGE_B200_ASYNC_CKPT=0) saves — weights, Adam slots, counters."""
+    tr, va, md = _random_kg(n_ent=300, n_train=1500, n_val=100)
+    kw = dict(train_X=tr, val_X=None, metadata=md, batch_size=128, seed=9, epochs=3)
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("KGE_B200_ASYNC_CKPT", mode)
+        m = TransE(embedding_params={"embedding_size": 16}, negative_ratio=4, corrupt_side="h+t")
+        m.train(log_path=str(tmp_path / mode), **kw)
+        assert sorted(f for f in os.listdir(tmp_path / mode) if f.startswith("ckpt")) == ["ckpt.opt.rank0.pt", "ckpt.pt"]
+        out[mode] = (torch.load(tmp_path / mode / "ckpt.pt"), torch.load(tmp_path / mode / "ckpt.opt.rank0.pt"), m)
+    (ca, oa, ma), (cs, os_, ms) = out["1"], out["0"]
+    assert ca["adam_t"] == cs["adam_t"] and ca["epoch"] == cs["epoch"] == 2 and ca["step"] == cs["step"]
+    assert ca["train_loss_history"] == cs["train_loss_history"]
+    for k in cs["weights"]:
+        assert torch.equal(ca["weights"][k], cs["weights"][k]), k
+        assert np.array_equal(ca["weights"][k].numpy(), ma.model_weights[k].numpy()), k        # the state after the last step
+    for ea, es in zip(oa["engines"], os_["engines"]):
+        assert ea["adam_t"] == es["adam_t"]
+        for s2 in es["m"]:
+            assert torch.equal(ea["m"][s2], es["m"][s2]) and torch.equal(ea["v"][s2], es["v"][s2]), s2
+
+
+def test_device_histograms_match_numpy(tmp_path):
+    """_Writers.histograms counts tf.summary.histogram's 30 equal-width buckets on the device; the counts are those
+    of numpy on the same edges (values on an edge may fall either side: float32 edge arithmetic)."""
+    from KGE.models.base_model.BaseModel import _Writers, WeightView
+    from KGE._b200.engine import PaddedTable
+    pytest.importorskip("tensorboard")
+    g = torch.Generator().manual_seed(3)
+    table = PaddedTable(torch.randn(1000, 50, generator=g), torch.device("cuda:0"))
+    w = _Writers(str(tmp_path), with_val=False)
+    seen = {}
+    w.w["root"].add_histogram_raw = lambda tag, **kw2: seen.update({tag: kw2})
+    w.histograms({"ent_emb": WeightView("ent_emb", table)}, 0)
+    w.close()
+    h = seen["ent_emb"]
+    x = table.view.cpu().numpy().ravel()
+    assert h["num"] == x.size and abs(h["min"] - x.min()) < 1e-6 and abs(h["max"] - x.max()) < 1e-6
+    assert abs(h["sum"] - x.astype(np.float64).sum()) < 1e-3 and abs(h["sum_squares"] - (x.astype(np.float64) ** 2).sum()) < 1e-2
+    want, _ = np.histogram(x, bins=30, range=(h["min"], h["max"]))
+    got = np.asarray(h["bucket_counts"])
+    assert got.sum() == x.size and len(h["bucket_limits"]) == 30 and np.abs(got - want).max() <= 3
+    assert np.abs(np.cumsum(got) - np.cumsum(want)).max() <= 3
 
 
 def test_device_batch_stream_on_the_gpu():
