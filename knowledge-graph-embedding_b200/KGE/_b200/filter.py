@@ -29,7 +29,8 @@ class FilterIndex:
         self.ctx, self.cfg, self.side, self.device = ctx, cfg, _side(side), torch.device(device)
         dt = torch.int64 if cfg.id_dtype == 1 else torch.int32
         P = positive_X if torch.is_tensor(positive_X) else torch.as_tensor(np.ascontiguousarray(np.asarray(positive_X)))
-        P = P.to(device=self.device, dtype=dt).reshape(-1, 3).contiguous()
+        from . import engine as _engine
+        P = _engine.upload(P, self.device, dt).reshape(-1, 3).contiguous()
         self.n_pos = int(P.shape[0])
         if self.n_pos == 0:
             raise ValueError("positive_X is empty: pass positive_X=None for unfiltered ranks")

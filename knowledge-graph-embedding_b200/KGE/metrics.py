@@ -16,7 +16,17 @@ def mean_rank(ranks):
 
 
 def median_rank(ranks):
-    return float(np.median(_r(ranks)))
+    """np.median's value (middle element, or the mean of the two middle ones) by one partition of the ranks,
+    without its NaN scan: ranks are integers >= 1."""
+    r = _r(ranks)
+    n = r.size
+    if n == 0:
+        return float("nan")
+    k = n // 2
+    if n % 2:
+        return float(np.partition(r, k)[k])
+    p = np.partition(r, [k - 1, k])
+    return float(0.5 * (p[k - 1] + p[k]))
 
 
 def geometric_mean_rank(ranks):
@@ -35,3 +45,25 @@ def std_rank(ranks):
 def hits_at_k(ranks, k):
     assert k >= 1, "k needs >= 1"
     return float(np.mean(_r(ranks) <= k))
+
+
+def summary(ranks):
+    """The nine metrics of KGEModel.evaluate (BaseModel.py:606-618 of the reference) in its key order, from one
+    float64 copy of the ranks and one reciprocal — the same expressions as the functions above, so the same values."""
+    r = _r(ranks)
+    if r.size == 0:
+        nan = float("nan")
+        return {k: nan for k in ("mean_rank", "mean_reciprocal_rank", "median_rank", "geometric_mean_rank",
+                                 "harmonic_mean_rank", "std_rank", "hit@1", "hit@3", "hit@10")}
+    inv = 1.0 / r
+    return {
+        "mean_rank": float(np.mean(r)),
+        "mean_reciprocal_rank": float(np.mean(inv)),
+        "median_rank": median_rank(r),
+        "geometric_mean_rank": float(np.exp(np.mean(np.log(r)))),
+        "harmonic_mean_rank": float(r.size / np.sum(inv)),
+        "std_rank": float(np.std(r)),
+        "hit@1": float(np.mean(r <= 1)),
+        "hit@3": float(np.mean(r <= 3)),
+        "hit@10": float(np.mean(r <= 10)),
+    }

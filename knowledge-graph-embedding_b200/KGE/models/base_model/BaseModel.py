@@ -597,17 +597,18 @@ class KGEModel:
         # the known-positive index is built ONCE per call (one device sort of positive_X), every block of
         # queries then costs two binary searches per query (kge_filter_lookup)
         index = None if positive_X is None else eng.filter_index(np.asarray(_plain(positive_X)), corrupt_side)
-        ranks = []
+        counts = []
         # multi-GPU: each rank counts over its slice of the entity table, counts are summed
         e_lo, e_hi = _dp.entity_shard(n_ent)
+        Xd = eng._ids(X)                  # one upload of the queries; the blocks are views of it
         for lo in range(0, len(X), 16384):
-            blk = eng._ids(X[lo:lo + 16384])
+            blk = Xd[lo:lo + 16384]
             off = ids = None
             if index is not None:
                 off, ids = index.lookup(blk)
-            cnt = _dp.allreduce_counts(eng.rank_counts(blk, side, off, ids, ent_lo=e_lo, ent_hi=e_hi))
-            ranks.append(cnt.cpu().numpy().astype(np.int64) + 1)
-        return np.concatenate(ranks)
+            counts.append(_dp.allreduce_counts(eng.rank_counts(blk, side, off, ids, ent_lo=e_lo, ent_hi=e_hi)))
+        # the host waits once, after the last block is enqueued
+        return torch.cat(counts).cpu().numpy().astype(np.int64) + 1
 
     def get_rank(self, x, positive_X, corrupt_side):
         """rank = 1 + #{candidates scoring strictly higher}, known positives excluded
@@ -617,17 +618,7 @@ class KGEModel:
     def evaluate(self, eval_X, corrupt_side, positive_X=None):
         ranks = self._rank_block(load_triples(eval_X), corrupt_side, positive_X)
         self.last_ranks = ranks
-        return {
-            "mean_rank": _metrics.mean_rank(ranks),
-            "mean_reciprocal_rank": _metrics.mean_reciprocal_rank(ranks),
-            "median_rank": _metrics.median_rank(ranks),
-            "geometric_mean_rank": _metrics.geometric_mean_rank(ranks),
-            "harmonic_mean_rank": _metrics.harmonic_mean_rank(ranks),
-            "std_rank": _metrics.std_rank(ranks),
-            "hit@1": _metrics.hits_at_k(ranks, k=1),
-            "hit@3": _metrics.hits_at_k(ranks, k=3),
-            "hit@10": _metrics.hits_at_k(ranks, k=10),
-        }
+        return _metrics.summary(ranks)
 
 
 def _plain(x):

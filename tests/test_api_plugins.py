@@ -83,6 +83,14 @@ def test_metrics_ranges_and_golden():
     close(mine, g["eval_vals"], 1e-9)
     with pytest.raises(AssertionError):
         metrics.hits_at_k(r, 0)
+    # evaluate()'s one-pass summary: the same nine values in the reference's key order (BaseModel.py:606-618)
+    s = metrics.summary(r)
+    assert list(s) == ["mean_rank", "mean_reciprocal_rank", "median_rank", "geometric_mean_rank", "harmonic_mean_rank",
+                       "std_rank", "hit@1", "hit@3", "hit@10"] and list(s.values()) == mine
+    for n in (1, 2, 3, 10, 11, 1000, 1001):                     # the partition median is np.median's value
+        x = rng.integers(1, 50, n)
+        assert metrics.median_rank(x) == float(np.median(x))
+    assert all(np.isnan(v) for v in metrics.summary(np.zeros(0, dtype=np.int64)).values())
 
 
 def test_index_and_split(tmp_path):
