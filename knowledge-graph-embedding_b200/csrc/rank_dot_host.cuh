@@ -1,5 +1,6 @@
 // rank_dot_host.cuh — host side of the tensor-core ranking path (included by rank.cu).
 #pragma once
+#include <stdlib.h>
 #include <cudaTypedefs.h>
 #include "host_common.cuh"
 #include "rank_dot_tc.cuh"
@@ -93,6 +94,16 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
     attr_set = true;
   }
   const int passes = ctx->opt_tc_passes == 2 ? 2 : 3;
+  // Two chains in front of the GEMM: the caller's stream takes the query side (max norm, query vectors and their
+  // hi/lo split, thresholds), the context's side stream the candidate side (hi/lo split of the table, once per call,
+  // and each block's known-positive bitmask); they meet in front of the GEMM.  KGE_RANK_SERIAL=1: one stream.
+  static const bool serial = [] { const char* e = getenv("KGE_RANK_SERIAL"); return e && atoi(e) != 0; }();
+  const bool fork = ctx->aux != nullptr && !serial;
+  cudaStream_t ts = fork ? ctx->aux : st;
+  if (fork) {                                  // the side stream starts behind everything already enqueued on st
+    KGE_CUDA_OK(cudaEventRecord(ctx->ev_fork, st));
+    KGE_CUDA_OK(cudaStreamWaitEvent(ts, ctx->ev_fork, 0));
+  }
   unsigned* maxn = reinterpret_cast<unsigned*>(wsb + L.off_maxn);
   KGE_CUDA_OK(cudaMemsetAsync(maxn, 0, 256, st));
   {
@@ -106,12 +117,12 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
   float* Ehi = reinterpret_cast<float*>(wsb + L.off_ehi);
   float* Elo = passes == 3 ? reinterpret_cast<float*>(wsb + L.off_elo) : nullptr;
   float* nlo = reinterpret_cast<float*>(wsb + L.off_nlo);
-  KGE_CUDA_OK(cudaMemsetAsync(nlo, 0, sizeof(float) * (size_t) L.n_etiles * TC_BN, st));
+  KGE_CUDA_OK(cudaMemsetAsync(nlo, 0, sizeof(float) * (size_t) L.n_etiles * TC_BN, ts));
   KGE_REQUIRE(E.ld == L.ldE, KGE_EUNSUPPORTED, "tensor-core ranking needs ld == round4(cols) (got %d)", E.ld);
   {
     int64_t blocks = (span + 7) / 8;
     if (blocks > (int64_t) ctx->sm_count * 32) blocks = (int64_t) ctx->sm_count * 32;
-    k_rank_split_table<<<(unsigned) blocks, 256, 0, st>>>(E.w, E.ld, E.cols, ent_lo, ent_hi, Ehi, Elo, nlo);
+    k_rank_split_table<<<(unsigned) blocks, 256, 0, ts>>>(E.w, E.ld, E.cols, ent_lo, ent_hi, Ehi, Elo, nlo);
     KGE_CUDA_OK(cudaGetLastError());
   }
   CUtensorMap map_ah, map_al, map_bh, map_bl;
@@ -143,8 +154,8 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
     uint32_t* filt = nullptr;
     if (filtered) {
       filt = reinterpret_cast<uint32_t*>(wsb + L.off_filt);
-      KGE_CUDA_OK(cudaMemsetAsync(filt, 0, sizeof(uint32_t) * (size_t) qn * L.words_per_q, st));
-      k_rank_filter_bits<<<(unsigned) ((qn + 7) / 8), 256, 0, st>>>(filter->off + q0, (filter->end ? filter->end : filter->off + 1) + q0,
+      KGE_CUDA_OK(cudaMemsetAsync(filt, 0, sizeof(uint32_t) * (size_t) qn * L.words_per_q, ts));
+      k_rank_filter_bits<<<(unsigned) ((qn + 7) / 8), 256, 0, ts>>>(filter->off + q0, (filter->end ? filter->end : filter->off + 1) + q0,
                                                                     filter->ids, qn, ent_lo, ent_hi, filt, L.words_per_q);
       KGE_CUDA_OK(cudaGetLastError());
     }
@@ -161,6 +172,10 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
     tp.words_per_q = L.words_per_q;
     KGE_CUDA_OK(cudaMemsetAsync(wsb + L.off_wins, 0, (L.off_ulist - L.off_wins), st));
     tp.filt = filt;
+    if (fork) {                                // candidate side ready
+      KGE_CUDA_OK(cudaEventRecord(ctx->ev_join, ts));
+      KGE_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
+    }
     int grid = tp.n_qblocks * split;
     if (grid > ctx->sm_count) grid = ctx->sm_count;
     const bool timed = (q0 == 0);           // phase slots hold one interval per call: time the first query block
@@ -180,6 +195,10 @@ inline int rank_dot_tensor(kge_ctx_impl* ctx, const kge_cfg* cfg, const kge_tabl
     k_rank_dot_final<<<(unsigned) ((qn + FIX_WARPS * 32 - 1) / (FIX_WARPS * 32)), FIX_WARPS * 32, 0, st>>>(fp);
     KGE_CUDA_OK(cudaGetLastError());
     if (timed) pt->end(7);
+    if (fork && q0 + L.qblk < Q) {             // the next block's bitmask may overwrite this one's only now
+      KGE_CUDA_OK(cudaEventRecord(ctx->ev_fork, st));
+      KGE_CUDA_OK(cudaStreamWaitEvent(ts, ctx->ev_fork, 0));
+    }
   }
   return KGE_OK;
 }

@@ -374,18 +374,52 @@ struct DotFixParams {
   int32_t* count;
 };
 
-// uncertain pairs -> exact fp32 score, one warp per pair (grid-stride over the list): hits join the query's wins
+// uncertain pairs -> exact fp32 score, hits join the query's wins.  A warp takes FIX_U consecutive pairs per round
+// and keeps their row loads in flight together (one pair per round left the kernel waiting on two dependent L2 round
+// trips per pair); each pair's score is warp_dot_exact's arithmetic — the same fmaf chain per lane in ascending
+// chunk order, the same butterfly — so the counts are unchanged.
+constexpr int FIX_U = 4;
 __global__ void __launch_bounds__(256) k_rank_dot_fix(const DotFixParams p) {
   const int lane = threadIdx.x & 31;
   const uint32_t n = *p.ucnt;
   if (n > p.ucap) return;                                   // overflow: k_rank_dot_final re-ranks the block exactly
   const int nch = (p.cols + 3) >> 2;
   const uint32_t nw = (gridDim.x * blockDim.x) >> 5;
-  for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += nw) {
-    const uint2 qe = p.ulist[i];
-    if (qe.x == 0xffffffffu) continue;                       // unused tail of a segment
-    const float s = warp_dot_exact(p.Qm + qe.x * (int64_t) p.kpad, p.E + qe.y * (int64_t) p.ldE, nch, lane) + p.bias[qe.x];
-    if (lane == 0 && s > p.pos[qe.x]) atomicAdd(p.wins + qe.x, 1);
+  // (measured and dropped: a CTA walking a contiguous run of the list so that its segment's 32 query rows come from
+  // L1 — 24.9 vs 25.2 M queries/s: the sentinel tails of the segments unbalance the CTAs)
+  for (uint32_t i0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * FIX_U; i0 < n; i0 += nw * FIX_U) {
+    uint32_t q[FIX_U];
+    bool ok[FIX_U];
+    const float4* a[FIX_U];
+    const float4* b[FIX_U];
+    float s[FIX_U];
+#pragma unroll
+    for (int u = 0; u < FIX_U; ++u) {
+      const bool in = i0 + u < n;
+      const uint2 qe = in ? p.ulist[i0 + u] : make_uint2(0xffffffffu, 0u);
+      ok[u] = qe.x != 0xffffffffu;                           // unused tail of a segment / past the end
+      q[u] = ok[u] ? qe.x : 0u;
+      a[u] = reinterpret_cast<const float4*>(p.Qm + q[u] * (int64_t) p.kpad);
+      b[u] = reinterpret_cast<const float4*>(p.E + (ok[u] ? (int64_t) qe.y : p.ent_lo) * (int64_t) p.ldE);
+      s[u] = 0.f;
+    }
+    for (int c = lane; c < nch; c += WARP) {
+      float4 x[FIX_U], y[FIX_U];
+#pragma unroll
+      for (int u = 0; u < FIX_U; ++u) { x[u] = a[u][c]; y[u] = __ldg(b[u] + c); }
+#pragma unroll
+      for (int u = 0; u < FIX_U; ++u) {
+        s[u] = fmaf(x[u].x, y[u].x, s[u]); s[u] = fmaf(x[u].y, y[u].y, s[u]);
+        s[u] = fmaf(x[u].z, y[u].z, s[u]); s[u] = fmaf(x[u].w, y[u].w, s[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < FIX_U; ++u) s[u] = warp_sum(s[u]);
+    if (lane == 0) {
+#pragma unroll
+      for (int u = 0; u < FIX_U; ++u)
+        if (ok[u] && s[u] + p.bias[q[u]] > p.pos[q[u]]) atomicAdd(p.wins + q[u], 1);
+    }
   }
 }
 // count_out += wins; or, when the list overflowed (degenerate score distributions: e.g. an all-equal table), the
