@@ -50,7 +50,8 @@ def upload(t_cpu, device, dtype=None):
     enough to go through the staging buffer."""
     device = torch.device(device)
     nbytes = t_cpu.numel() * t_cpu.element_size()
-    if t_cpu.is_cuda or device.type != "cuda" or nbytes < (1 << 20) or t_cpu.is_pinned() or not t_cpu.is_contiguous():
+    if (t_cpu.is_cuda or device.type != "cuda" or nbytes < (1 << 20) or nbytes > (1 << 30) or t_cpu.is_pinned()
+            or not t_cpu.is_contiguous()):
         out = t_cpu.to(device=device, non_blocking=True)
     else:
         st = _Staging.by_device.setdefault(device, _Staging())

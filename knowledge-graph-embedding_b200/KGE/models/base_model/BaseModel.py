@@ -496,6 +496,9 @@ class KGEModel:
         # one GPU, unsharded: pinned snapshots in stream order + a writer thread (the files are complete when
         # train() returns or the checkpoint is loaded); otherwise (collective reads) written here
         bg = world == 1 and self._sharded is None and os.environ.get("KGE_B200_ASYNC_CKPT", "1") != "0"
+        if bg:        # the snapshot lives in pinned host memory (weights + two optimizer slots): bounded
+            nbytes = 3 * sum(int(np.prod(v.shape)) * 4 for v in self.model_weights.values())
+            bg = nbytes <= int(os.environ.get("KGE_B200_ASYNC_CKPT_MAX_MB", "1024")) << 20
         if bg and getattr(self, "_ckpt_writer", None) is None:
             self._ckpt_writer = _CheckpointWriter()
         host = (lambda key, t: self._ckpt_writer.snapshot(key, t.detach())) if bg else (lambda key, t: t.detach().cpu())
