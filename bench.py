@@ -15,6 +15,7 @@ installable here) on a bounded sample of the same workload.
 """
 import argparse
 import json
+import math
 import os
 import statistics
 import subprocess
@@ -309,6 +310,7 @@ def run_ours(args, rank, world, device):
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
     stage = torch.empty((B, 3), dtype=torch.int64, device=device)
     barrier()
+    seen_e2e = 0.0
     t0 = time.perf_counter()
     for i in range(args.steps):
         if graph is None and world > 1:
@@ -317,12 +319,17 @@ def run_ours(args, rank, world, device):
             loss_host.copy_(loss_dev, non_blocking=True)
         elif graph is not None:   # host buffers through the captured graph: H2D of this (first step) / the next batch,
             graph_step(host_batches[i % n_batches], host_batches[(i + 1) % n_batches], loss_host)   # step, D2H of the loss
+            graph.wait_loss()     # the host has THIS step's loss before it issues the next one (the reference reads
+            seen_e2e += float(loss_host[0])                                    # loss.numpy() per batch); one GPU: the
+            continue              # graph stores it into the pinned word as soon as it is final (kge_step_graph_wait_loss)
         else:           # host buffers straight through the C-ABI: H2D + step + D2H enqueued by kge_train_step_host
             eng.train_step_host(host_batches[i % n_batches], seed, step_no[0], loss_host)
             step_no[0] += 1
         torch.cuda.current_stream().synchronize()      # the reference reads loss.numpy() per batch
-    barrier()
+        seen_e2e += float(loss_host[0])
+    barrier()                     # every step's kernels have finished inside the timed region
     ms_e2e = (time.perf_counter() - t0) * 1e3
+    assert math.isfinite(seen_e2e), "a loss read in the end-to-end loop was not finite"
     ms_e2e_plain = None
     if graph is not None and world == 1:       # the same through kge_train_step_host (no graph, no look-ahead), for comparison
         barrier()
@@ -806,11 +813,16 @@ def main():
         "e2e_plain_calls": (r["triples"] / (r["ms_e2e_plain"] * 1e-3)) if r["ms_e2e_plain"] else None,
         "e2e": {"value": r["triples"] / (r["ms_e2e"] * 1e-3), "unit": "triples/s",
                 "h2d_bytes_per_step": W["B"] * 3 * 8, "d2h_bytes_per_step": 4,
-                "sync": "stream synchronised and the loss read on the host after every step"},
+                "sync": ("the host waits for and reads every step's loss before it issues the next step "
+                         "(kge_step_graph_wait_loss: one GPU — the graph reads the pinned batch and stores the loss "
+                         "into the pinned word itself, the wait ends when the loss is final, the update kernels of "
+                         "step i overlap the launch of step i+1; N > 1 — stream synchronised); all kernels of all "
+                         "steps complete inside the timed region") if r["graph"] else
+                        "stream synchronised and the loss read on the host after every step"},
         "e2e_loss_one_step_late": {"value": r["triples"] / (r["ms_e2e_lag"] * 1e-3), "unit": "triples/s",
                                    "note": "same H2D / step / D2H per step, loss of step i read while step i+1 runs "
                                            "(KGEModel.train reads losses once per epoch)"},
-        "gpu_launches": args.steps * (8 if world == 1 else 12),      # single GPU: k_set_dyn, k_step, k_keys, k_scan, k_scatter, k_canon, k_update_heavy, k_update_fast
+        "gpu_launches": args.steps * (9 if world == 1 else 13),      # single GPU: k_set_dyn, k_stage_next, k_step, k_keys, k_scan, k_scatter, k_canon, k_update_heavy, k_update_fast
         "gpu_launches_note": "own kernels per step: k_constrain, k_step (loss/clip reduction folded into its last warp), "
         "k_update_fast on the caller's stream; k_keys, k_scan, k_scatter, k_canon, k_update_heavy on the side stream "
         "(+ one memset there); data-parallel runs split the update pair into k_update_fast/heavy<3> (row sums stored "

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define KGE_ABI_VERSION 11
+#define KGE_ABI_VERSION 12
 #define KGE_MAX_TABLES 4
 
 typedef enum { KGE_OK = 0, KGE_EINVAL = -1, KGE_EUNSUPPORTED = -2, KGE_ECUDA = -3,
@@ -217,9 +217,11 @@ int kge_train_step_host_next(kge_ctx*, const kge_cfg*, kge_tables*, const kge_sa
  * become one graph launch, and the kernels of a step are released by the GPU's own dependency tracking instead of
  * the host's enqueue order.  What changes from step to step — the Philox step, lr_t of the Adam step, the
  * look-ahead step — lives in a device block written by the graph's first node, whose arguments are patched per
- * launch (cudaGraphExecKernelNodeSetParams).  Per launch the host issues: the copy of the batch into the staging
- * buffer (from host or device memory), one node update, one graph launch, and (host_loss_out != NULL) the copy of
- * the loss — no host synchronisation.
+ * launch (cudaGraphExecKernelNodeSetParams).  Per launch the host issues one node update and one graph launch — no
+ * host synchronisation.  The look-ahead batch and the loss cross the host boundary INSIDE the graph when the caller's
+ * buffers are visible to the device (pinned / registered host memory, or device memory): a staging kernel on the
+ * look-ahead chain reads next_triples, and the kernel that makes the loss final stores it into host_loss_out; with
+ * pageable host memory the same transfers are copies queued in front of / behind the graph (ABI v12; before, always).
  *   kge_step_graph_create : fixes cfg, table pointers, sampler, batch size B, seed, loss word and workspace.
  *                           dev_triples / dev_triples_next: (B, 3) device staging buffers of cfg->id_dtype the
  *                           graph's kernels read (the second one is for the look-ahead batch, NULL = none).
@@ -239,6 +241,12 @@ int kge_step_graph_create(kge_ctx*, const kge_cfg*, const kge_tables*, const kge
 int kge_step_graph_launch(kge_step_graph*, kge_tables*, const void* triples, uint64_t step, uint64_t adam_t,
                           const void* next_triples, uint64_t next_step, float* host_loss_out, void* stream);
 int kge_step_graph_destroy(kge_step_graph*);
+/* Blocks the host until the loss of the LAST launch is in its host_loss_out.  When the graph stored it there itself
+ * (pinned buffer, single-GPU graph) this returns as soon as the loss is final — before the update kernels of the
+ * step have run — so a loop that reads every step's loss (the reference's loss.numpy() per batch,
+ * BaseModel.py:139-145) enqueues the next step under them; stream order keeps the steps in sequence.  Otherwise
+ * it is cudaStreamSynchronize on the launch's stream.  (ABI v12) */
+int kge_step_graph_wait_loss(kge_step_graph*);
 /* Phase times of the LAST launch of a graph created while KGE_OPT_GRAPH_PROFILE was 1 (the graph then records
  * its own phase-boundary events: measuring, not for production): phase_ms[KGE_N_PHASES] as kge_profile_end,
  * *total_ms = first to last node.  Synchronises the device. */

@@ -175,6 +175,11 @@ class StepGraph:
         eng._sync_shadow(T)
         return self.loss
 
+    def wait_loss(self):
+        """Host waits until the last launch's loss is in its `host_loss` buffer (kge_step_graph_wait_loss): with a
+        pinned buffer on one GPU that is before the step's update kernels have finished."""
+        L.check(L.load().kge_step_graph_wait_loss(self.h))
+
     def phases(self):
         """-> ({phase: ms}, total ms) of the last launch (graph created under set_option(OPT_GRAPH_PROFILE, 1))."""
         ms = (C.c_float * L.N_PHASES)()

@@ -3,7 +3,7 @@ library or a failing call raises."""
 import ctypes as C
 import os
 
-KGE_ABI_VERSION = 11
+KGE_ABI_VERSION = 12
 KGE_MAX_TABLES = 4
 (UM, SE, TRANSE, TRANSH, TRANSR, TRANSD, ROTATE, DISTMULT, RESCAL) = range(9)
 SCORE_LP, SCORE_LP_POW, SCORE_DOT = 0, 1, 2
@@ -93,7 +93,7 @@ SYMBOLS = ["kge_abi_version", "kge_last_error", "kge_ctx_create", "kge_ctx_destr
            "kge_filter_index_bytes", "kge_filter_index_build", "kge_filter_lookup",
            "kge_train_step_next", "kge_train_step_host_next",
            "kge_step_graph_create", "kge_step_graph_launch", "kge_step_graph_destroy",
-           "kge_train_step_dp_next", "kge_step_graph_create_dp", "kge_step_graph_launch_dp", "kge_step_graph_phases",
+           "kge_train_step_dp_next", "kge_step_graph_create_dp", "kge_step_graph_launch_dp", "kge_step_graph_phases", "kge_step_graph_wait_loss",
            "kge_epoch_perm_bytes", "kge_epoch_perm", "kge_batch_gather"]
 RANK_STATIC_BYTES = 4 << 20
 
@@ -138,6 +138,7 @@ def load():
     L.kge_step_graph_launch.argtypes = [vp, C.POINTER(Tables), vp, u64, u64, vp, u64, vp, vp]
     L.kge_step_graph_destroy.argtypes = [vp]
     L.kge_step_graph_phases.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    L.kge_step_graph_wait_loss.argtypes = [vp]
     L.kge_train_grad.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Sampler), C.POINTER(Dp), vp, i64,
                                  u64, u64, vp, C.POINTER(Grads), vp, vp, vp, C.c_size_t, vp]
     L.kge_train_apply.argtypes = [vp, C.POINTER(Cfg), C.POINTER(Tables), C.POINTER(Grads), vp, i64, u64, vp, vp,

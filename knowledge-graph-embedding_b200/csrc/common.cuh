@@ -34,6 +34,12 @@ struct DynScal {
   unsigned long long step_next; // ... of the batch grouped ahead (kge_train_step_next)
   float lr_t;                   // Adam: lr * sqrt(1 - b2^t) / (1 - b1^t); SGD / Adagrad: lr
   uint32_t epoch;               // cross-GPU barrier epoch of the data-parallel step
+  // host-side ends of a captured step (kge_step_graph_launch with pinned host buffers): read / written by the
+  // graph's own kernels through mapped host memory instead of by copies queued around the graph
+  const void* next_src;         // the look-ahead batch (pinned host or device memory; NULL: already staged by a copy)
+  float* host_loss;             // the loss goes here as soon as it is final (NULL: not wanted)
+  unsigned long long* host_seq; // ... followed by `seq`: what kge_step_graph_wait_loss spins on
+  unsigned long long seq;
 };
 // a batch whose gradient records were grouped ahead of its step (kge_train_step_next)
 struct Prefetched {

@@ -17,7 +17,17 @@ struct ReduceParams {
   float* loss_out;
   float* stage;          // k_reduce: [N_PART_MAX][RED_CTAS] per-CTA sums (behind the partials in the workspace)
   unsigned* done;        // k_reduce: self-resetting ticket counter
+  const DynScal* dyn;    // captured step graph: where the host wants the loss (DynScal.host_loss / host_seq), else NULL
 };
+// the loss is final: hand it to a host that waits for it (kge_step_graph_wait_loss) before the update kernels run
+__device__ __forceinline__ void publish_loss_to_host(const DynScal* dyn, float loss) {
+  if (dyn == nullptr) return;
+  float* hl = dyn->host_loss;
+  if (hl == nullptr) return;
+  *reinterpret_cast<volatile float*>(hl) = loss;
+  __threadfence_system();
+  *reinterpret_cast<volatile unsigned long long*>(dyn->host_seq) = dyn->seq;
+}
 constexpr int RED_CTAS = 64;      // k_reduce: CTAs of the first level (one SM's L2 bandwidth was the single-CTA kernel's limit)
 
 // The same reduction folded into the step kernel (saves a launch when B is small), in two levels so that
@@ -48,7 +58,7 @@ __device__ __forceinline__ void tail_reduce_ctas(const ReduceParams& p, int n_ct
   for (int q = 0; q < 5; ++q) {
     const float a = warp_sum(acc[q]);
     if (lane == 0 && q < p.n_part) {
-      if (q == 0) { p.scal[8] = a; *p.loss_out = a; }
+      if (q == 0) { p.scal[8] = a; *p.loss_out = a; publish_loss_to_host(p.dyn, a); }
       else { p.scal[4 + q - 1] = a; p.scal[q - 1] = p.clip_norm / fmaxf(sqrtf(a), p.clip_norm); }
     }
   }

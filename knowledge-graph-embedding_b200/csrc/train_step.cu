@@ -370,6 +370,18 @@ extern "C" int kge_workspace_bytes(const kge_cfg* cfg, int64_t B, int64_t Q, siz
   return KGE_OK;
 }
 
+namespace kge {
+// Captured step graph, look-ahead chain: the next batch is fetched by the graph itself from wherever the launch says
+// (DynScal.next_src: pinned host memory read over PCIe, or device memory) into its staging buffer — a copy queued in
+// front of the graph launch would sit on the step's critical path (5 us per step on C2).
+__global__ void __launch_bounds__(256) k_stage_next(uint32_t* __restrict__ dst, const DynScal* d, size_t words) {
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(d->next_src);
+  if (src == nullptr) return;
+  for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (size_t) gridDim.x * blockDim.x)
+    dst[i] = src[i];
+}
+}  // namespace kge
+
 // dp / grads_out / scal_out non-NULL = the gradient half of a data-parallel step (kge_train_grad)
 static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, const kge_sampler* smp,
                       const kge_dp* dp, const void* triples, int64_t B, uint64_t seed, uint64_t step, uint64_t adam_t,
@@ -561,6 +573,9 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   p.rp.loss_out = grad_only ? p.rp.scal + 9 : loss_out;
   p.rp.stage = p.part + N_PART * (size_t) B;
   p.rp.done = ctx->ticket + 1;
+  // captured step graph on one GPU: the kernel that makes the loss final also hands it to the host (DynScal.host_loss)
+  const bool dense_reg_loss = has_dense_reg(cfg);
+  p.rp.dyn = (dyn && !grad_only && !dense_reg_loss) ? dyn : nullptr;
 
   // side stream: sort keys depend on ids only, so key generation, the stable radix sort and the
   // segment table run concurrently with the step kernel and join before the update kernels
@@ -642,6 +657,11 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
     if (next_host)          // the next batch comes from host memory: its copy rides the same stream, ahead of the chain
       KGE_CUDA_OK(cudaMemcpyAsync(const_cast<void*>(next_triples), next_host, (size_t) B * 3 * (cfg->id_dtype ? 8 : 4),
                                   cudaMemcpyHostToDevice, px));
+    if (dyn) {              // captured: the graph stages the batch itself (no-op when the launch copied it)
+      k_stage_next<<<8, 256, 0, px>>>(reinterpret_cast<uint32_t*>(const_cast<void*>(next_triples)), dyn,
+                                      (size_t) B * 3 * (cfg->id_dtype ? 2 : 1));
+      KGE_CUDA_OK(cudaGetLastError());
+    }
     StepParams kp = p;
     kp.triples = next_triples;
     kp.sd.step = next_step;
@@ -856,6 +876,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
   up.n_tabs = 0;
   up.total_rows = 0;
   ReduceDenseParams rd;
+  rd.dyn = nullptr;
   rd.row_begin[0] = 0;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
     if (!cols[s] || is_matrix_slot(cfg, s)) continue;
@@ -1001,6 +1022,7 @@ static int train_impl(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* tables, con
       rd.matpart = mu.part; rd.n_mat = L.n_mat_cta; rd.mat_loss_coef = cfg->constraint_weight / (float) cfg->n_rel;
     }
     rd.clip_norm = cfg->clip_norm; rd.write_scales = is_train != 0; rd.scal = rp.scal; rd.loss_out = loss_out;
+    rd.dyn = (dyn && !grad_only) ? dyn : nullptr;
     k_reduce_dense<<<1, 1024, 0, st>>>(rd);
     KGE_CUDA_OK(cudaGetLastError());
     if (!is_train) { pt.end(4); return KGE_OK; }
@@ -1146,6 +1168,7 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
   up.n_tabs = 0;
   up.total_rows = 0;
   ReduceDenseParams rd;
+  rd.dyn = nullptr;
   rd.row_begin[0] = 0;
   int max_ch = 1;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
@@ -1468,8 +1491,10 @@ extern "C" int kge_train_step_dp(kge_ctx* ctx, const kge_cfg* cfg, kge_tables* t
 namespace kge {
 // first node of every captured step: the launch's scalars, patched per launch with
 // cudaGraphExecKernelNodeSetParams, land in the device block the other kernels read
-__global__ void k_set_dyn(DynScal* d, unsigned long long step, unsigned long long step_next, float lr_t, uint32_t epoch) {
+__global__ void k_set_dyn(DynScal* d, unsigned long long step, unsigned long long step_next, float lr_t, uint32_t epoch,
+                          const void* next_src, float* host_loss, unsigned long long* host_seq, unsigned long long seq) {
   d->step = step; d->step_next = step_next; d->lr_t = lr_t; d->epoch = epoch;
+  d->next_src = next_src; d->host_loss = host_loss; d->host_seq = host_seq; d->seq = seq;
 }
 struct GraphVariant {
   unsigned ev_mask = 0;          // phases whose events this variant records (KGE_OPT_GRAPH_PROFILE)
@@ -1501,6 +1526,10 @@ struct kge_step_graph {
   kge_dp dp;
   kge_grads push[2], slots[2];   // by staging parity of the exchange (bit 4 of the variant key)
   kge_peer_flags pf;
+  // the host's end of the loss (kge_step_graph_wait_loss): a mapped word the graph writes `seq` to behind the loss
+  unsigned long long* host_seq; unsigned long long* host_seq_dev; unsigned long long seq;
+  bool loss_direct;          // the last launch wrote the loss into the caller's pinned buffer itself
+  cudaStream_t last_stream;
   int parity;                // staging buffer the NEXT ungrouped batch goes to
   bool next_grouped;         // the previous launch grouped a batch (into stage[parity])
   uint64_t next_step;
@@ -1532,7 +1561,7 @@ static int graph_capture(kge_step_graph* g, int key) {
   ctx->capturing = 1;
   ctx->gev = g->prof ? g->gev : nullptr;
   ctx->gev_mask = 0;
-  k_set_dyn<<<1, 1, 0, g->cap>>>(ctx->dyn, 0ull, 0ull, 0.f, 0u);
+  k_set_dyn<<<1, 1, 0, g->cap>>>(ctx->dyn, 0ull, 0ull, 0.f, 0u, nullptr, nullptr, nullptr, 0ull);
   if (g->prof) cudaEventRecordWithFlags(g->gev[2 * KGE_N_PHASES], g->cap, cudaEventRecordExternal);
   int rc;
   if (g->dp_mode) {
@@ -1578,6 +1607,12 @@ extern "C" int kge_step_graph_create(kge_ctx* ctx_, const kge_cfg* cfg, const kg
   g->stage[0] = dev_triples; g->stage[1] = dev_triples_next;
   g->B = B; g->seed = seed; g->dev_loss = dev_loss; g->ws = ws; g->ws_bytes = ws_bytes;
   g->parity = 0; g->next_grouped = false; g->next_step = 0; g->dp_mode = false;
+  g->host_seq = nullptr; g->host_seq_dev = nullptr; g->seq = 0; g->loss_direct = false; g->last_stream = nullptr;
+  if (cudaHostAlloc(reinterpret_cast<void**>(&g->host_seq), 64, cudaHostAllocMapped) != cudaSuccess ||
+      cudaHostGetDevicePointer(reinterpret_cast<void**>(&g->host_seq_dev), g->host_seq, 0) != cudaSuccess) {
+    delete g; set_error("pinned word for the loss hand-off could not be allocated"); return KGE_ECUDA;
+  }
+  *g->host_seq = 0;
   if (cudaStreamCreateWithFlags(&g->cap, cudaStreamNonBlocking) != cudaSuccess) { delete g; set_error("stream create failed"); return KGE_ECUDA; }
   for (int j = 0; j < 6; ++j)
     if (cudaEventCreateWithFlags(&g->ev[j], cudaEventDisableTiming) != cudaSuccess) { set_error("event create failed"); return KGE_ECUDA; }
@@ -1629,26 +1664,71 @@ static int graph_launch(kge_step_graph* g, kge_tables* tables, const void* tripl
     KGE_REQUIRE(triples, KGE_EINVAL, "triples is NULL and the batch was not staged by the previous launch");
     KGE_CUDA_OK(cudaMemcpyAsync(g->stage[par], triples, bytes, cudaMemcpyDefault, st));
   }
-  if (next_triples) KGE_CUDA_OK(cudaMemcpyAsync(g->stage[1 - par], next_triples, bytes, cudaMemcpyDefault, st));
+  // The look-ahead batch and the loss cross the host boundary INSIDE the graph when the caller's buffers are visible
+  // to the device (pinned / registered host memory, or device memory): k_stage_next reads the batch on the side
+  // chain, the kernel that makes the loss final stores it into the host buffer followed by a sequence word.
+  // Pageable host memory keeps the copies queued around the graph.
+  auto device_view = [](const void* ptr) -> void* {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) return at.devicePointer;
+    return nullptr;
+  };
+  static const bool direct_off = [] { const char* e = getenv("KGE_GRAPH_DIRECT_IO"); return e && atoi(e) == 0; }();
+  const void* next_src = nullptr;
+  if (next_triples) {
+    next_src = direct_off ? nullptr : device_view(next_triples);
+    if (!next_src) KGE_CUDA_OK(cudaMemcpyAsync(g->stage[1 - par], next_triples, bytes, cudaMemcpyDefault, st));
+  }
+  float* loss_direct = nullptr;
+  if (host_loss_out && !g->dp_mode && !direct_off) loss_direct = reinterpret_cast<float*>(device_view(host_loss_out));
   const int key = (tables->wn_valid[KGE_T_ENT] ? 1 : 0) | (grouped ? 2 : 0) | (next_triples ? 4 : 0) | (par << 3) | (staging_parity << 4);
   kge::GraphVariant& V = g->var[key];
   if (!V.exec) { if (int rc = graph_capture(g, key)) return rc; }
   unsigned long long a0 = step, a1 = next_step;
   float lr_t = g->cfg.optimizer == KGE_OPTIM_ADAM ? adam_lr(g->cfg.lr, g->cfg.beta1, g->cfg.beta2, adam_t) : g->cfg.lr;
   DynScal* dptr = g->ctx->dyn;
-  void* args[5] = {&dptr, &a0, &a1, &lr_t, &epoch};
+  unsigned long long seq = loss_direct ? ++g->seq : g->seq;
+  unsigned long long* seq_dev = g->host_seq_dev;
+  void* args[9] = {&dptr, &a0, &a1, &lr_t, &epoch, &next_src, &loss_direct, &seq_dev, &seq};
   cudaKernelNodeParams np = {};
   np.func = (void*) kge::k_set_dyn;
   np.gridDim = dim3(1, 1, 1); np.blockDim = dim3(1, 1, 1); np.sharedMemBytes = 0; np.kernelParams = args; np.extra = nullptr;
   KGE_CUDA_OK(cudaGraphExecKernelNodeSetParams(V.exec, V.set_node, &np));
   KGE_CUDA_OK(cudaGraphLaunch(V.exec, st));
-  if (host_loss_out) KGE_CUDA_OK(cudaMemcpyAsync(host_loss_out, g->dev_loss, sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (host_loss_out && !loss_direct) KGE_CUDA_OK(cudaMemcpyAsync(host_loss_out, g->dev_loss, sizeof(float), cudaMemcpyDeviceToHost, st));
+  g->loss_direct = loss_direct != nullptr;
+  g->last_stream = st;
   tables->wn_valid[KGE_T_ENT] = V.wn_valid_after;
   g->last_mask = V.ev_mask;
   g->next_grouped = next_triples != nullptr;
   g->next_step = next_step;
   if (next_triples) g->parity = 1 - par;         // the grouped batch sits in the other buffer / set
   return KGE_OK;
+}
+
+// Returns once the loss of the last launch is in the caller's host buffer.  When the graph stored it there itself
+// (pinned buffer, one GPU) that is BEFORE the update kernels have run: the host may read the loss and enqueue the
+// next step while they finish (stream order keeps the steps in sequence).  Otherwise: a stream synchronisation.
+extern "C" int kge_step_graph_wait_loss(kge_step_graph* g) {
+  KGE_REQUIRE(g, KGE_EINVAL, "graph is NULL");
+  if (!g->loss_direct) {
+    KGE_CUDA_OK(cudaStreamSynchronize(g->last_stream));
+    return KGE_OK;
+  }
+  const unsigned long long want = g->seq;
+  volatile unsigned long long* w = g->host_seq;
+  for (unsigned long long spin = 0;; ++spin) {
+    if (*w >= want) return KGE_OK;
+    if ((spin & 0xfffff) == 0xfffff) {           // every ~1M polls: has the stream died or finished without the store?
+      cudaError_t e = cudaStreamQuery(g->last_stream);
+      if (e == cudaSuccess) { KGE_REQUIRE(*w >= want, KGE_ECUDA, "the step finished without publishing its loss"); return KGE_OK; }
+      KGE_REQUIRE(e == cudaErrorNotReady, KGE_ECUDA, "stream error while waiting for the loss: %s", cudaGetErrorString(e));
+    }
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+  }
 }
 
 extern "C" int kge_step_graph_phases(kge_step_graph* g, float* phase_ms, float* total_ms) {
@@ -1670,6 +1750,7 @@ extern "C" int kge_step_graph_destroy(kge_step_graph* g) {
     if (V.graph) cudaGraphDestroy(V.graph);
   }
   if (g->cap) cudaStreamDestroy(g->cap);
+  if (g->host_seq) cudaFreeHost(g->host_seq);
   for (int j = 0; j < 6; ++j) if (g->ev[j]) cudaEventDestroy(g->ev[j]);
   for (int j = 0; j < 2 * KGE_N_PHASES + 2; ++j) if (g->gev[j]) cudaEventDestroy(g->gev[j]);
   delete g;

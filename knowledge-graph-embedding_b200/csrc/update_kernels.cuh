@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(1024) k_reduce(const ReduceParams p) {
     float b = 0.f;
     for (int c = 0; c < (int) gridDim.x; ++c) b += __ldcg(p.stage + q * RED_CTAS + c);      // CTA order (warp-uniform)
     if (lane == 0) {
-      if (q == 0) { p.scal[8] = b; *p.loss_out = b; }
+      if (q == 0) { p.scal[8] = b; *p.loss_out = b; publish_loss_to_host(p.dyn, b); }
       else {
         p.scal[4 + q - 1] = b;
         // tf.clip_by_norm: g * clip / max(||g||, clip)      (BaseModel.py:327)
@@ -842,6 +842,7 @@ struct ReduceDenseParams {
   int write_scales;
   float* scal;
   float* loss_out;
+  const DynScal* dyn;        // see ReduceParams.dyn: with a dense regulariser THIS kernel makes the loss final
 };
 __device__ __forceinline__ float block_sum_1024(float a, float* sm) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -886,7 +887,7 @@ __global__ void __launch_bounds__(1024) k_reduce_dense(const ReduceDenseParams p
       }
     }
   }
-  if (threadIdx.x == 0) { p.scal[8] += loss_add; *p.loss_out = p.scal[8]; }
+  if (threadIdx.x == 0) { p.scal[8] += loss_add; *p.loss_out = p.scal[8]; publish_loss_to_host(p.dyn, p.scal[8]); }
 }
 
 }  // namespace kge

@@ -108,6 +108,30 @@ def test_step_graph_equals_plain_bitwise(case, lookahead):
     _assert_same(_state(plain), _state(gr), "mixed")
 
 
+@pytest.mark.parametrize("case", [CASES[1], CASES[3], CASES[6], CASES[7]], ids=["DistMult-200", "TransE-50", "TransR-24", "RESCAL-16"])
+@pytest.mark.parametrize("pinned", [True, False])
+def test_step_graph_wait_loss_reads_every_step(case, pinned):
+    """kge_step_graph_wait_loss: the host has each step's loss before it issues the next step, without a stream
+    synchronisation.  Pinned buffers: the graph reads the look-ahead batch from host memory itself and the kernel
+    that makes the loss final stores it into the host word (for RESCAL that is the dense-regulariser reduction);
+    pageable buffers: the same call falls back to copies around the graph + a stream synchronisation.  Either way
+    the losses and the final state are those of plain kge_train_step calls, bit for bit."""
+    B, steps = 96, 9
+    Xh = [x.pin_memory() if pinned else x.clone() for x in _batches(steps, B)]
+    plain, gr = _engine(case), _engine(case)
+    G = gr.step_graph(B, 7, lookahead=True)
+    lh = torch.full((1,), float("nan"))
+    lh = lh.pin_memory() if pinned else lh
+    for i in range(steps):
+        want = float(plain.train_step(Xh[i].cuda(), 7, i).item())
+        nxt = Xh[i + 1] if i + 1 < steps and i != 4 else None              # step 5 is staged by its own launch
+        G.launch(Xh[i], i, next_triples=nxt, host_loss=lh)
+        G.wait_loss()
+        assert float(lh[0]) == want, (i, float(lh[0]), want)
+    torch.cuda.synchronize()
+    _assert_same(_state(plain), _state(gr), (case, pinned))
+
+
 def test_step_graph_device_batches_and_sgd():
     from KGE._b200 import lib as L
     case = ("TransE", 50, "l1", "hinge", 4, "h+t")
