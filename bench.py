@@ -817,7 +817,8 @@ def main():
                          "(kge_step_graph_wait_loss: one GPU — the graph reads the pinned batch and stores the loss "
                          "into the pinned word itself, the wait ends when the loss is final, the update kernels of "
                          "step i overlap the launch of step i+1; N > 1 — stream synchronised); all kernels of all "
-                         "steps complete inside the timed region") if r["graph"] else
+                         "steps complete inside the timed region; L2 is NOT flushed between these steps (a flush kernel would sit "
+                         "inside the wall-clock region): compare with value_steady_state_l2_warm, not with the cold-L2 value") if r["graph"] else
                         "stream synchronised and the loss read on the host after every step"},
         "e2e_loss_one_step_late": {"value": r["triples"] / (r["ms_e2e_lag"] * 1e-3), "unit": "triples/s",
                                    "note": "same H2D / step / D2H per step, loss of step i read while step i+1 runs "

@@ -1159,16 +1159,18 @@ extern "C" int kge_train_apply(kge_ctx* ctx_, const kge_cfg* cfg, kge_tables* ta
     ss.n = g->n_peers;
     for (int j = 0; j < ss.n; ++j) { KGE_REQUIRE(g->peer_scal[j], KGE_EINVAL, "grads.peer_scal[%d] is NULL", j); ss.s[j] = g->peer_scal[j]; }
   } else { KGE_REQUIRE(scal_summed, KGE_EINVAL, "scal_summed is NULL"); ss.n = 1; ss.s[0] = scal_summed; }
-  k_dp_scales<<<1, 32, 0, st>>>(ss, cfg->clip_norm, scal, loss_out, g->abort_word);
+  const bool dense = has_dense_reg(cfg);
+  // captured step graph: the kernel that makes the loss final hands it to the host (DynScal.host_loss)
+  const DynScal* dyn_pub = ctx->capturing ? ctx->dyn : nullptr;
+  k_dp_scales<<<1, 32, 0, st>>>(ss, cfg->clip_norm, scal, loss_out, g->abort_word, dense ? nullptr : dyn_pub);
   KGE_CUDA_OK(cudaGetLastError());
 
-  const bool dense = has_dense_reg(cfg);
   const bool shadow_ok = shadow_capable(ctx, cfg, tables);
   UpdateParams up;
   up.n_tabs = 0;
   up.total_rows = 0;
   ReduceDenseParams rd;
-  rd.dyn = nullptr;
+  rd.dyn = dense ? dyn_pub : nullptr;
   rd.row_begin[0] = 0;
   int max_ch = 1;
   for (int s = 0; s < KGE_MAX_TABLES; ++s) {
@@ -1681,7 +1683,7 @@ static int graph_launch(kge_step_graph* g, kge_tables* tables, const void* tripl
     if (!next_src) KGE_CUDA_OK(cudaMemcpyAsync(g->stage[1 - par], next_triples, bytes, cudaMemcpyDefault, st));
   }
   float* loss_direct = nullptr;
-  if (host_loss_out && !g->dp_mode && !direct_off) loss_direct = reinterpret_cast<float*>(device_view(host_loss_out));
+  if (host_loss_out && !direct_off) loss_direct = reinterpret_cast<float*>(device_view(host_loss_out));
   const int key = (tables->wn_valid[KGE_T_ENT] ? 1 : 0) | (grouped ? 2 : 0) | (next_triples ? 4 : 0) | (par << 3) | (staging_parity << 4);
   kge::GraphVariant& V = g->var[key];
   if (!V.exec) { if (int rc = graph_capture(g, key)) return rc; }

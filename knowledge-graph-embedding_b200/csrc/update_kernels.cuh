@@ -808,7 +808,8 @@ inline int launch_update(const UpdateParams& up, int cpl, int64_t blocks, cudaSt
 struct ScalSlots { const float* s[KGE_MAX_PEERS]; int n; };
 // abort (nullable): the error word of kge_peer_barrier.  KGE_PEER_DEAD => scal[SCAL_ABORT] = 1: the update
 // kernels of the apply half return before touching a row, and the loss is NaN.
-__global__ void k_dp_scales(const ScalSlots in, float clip_norm, float* scal, float* loss_out, const uint32_t* abort) {
+__global__ void k_dp_scales(const ScalSlots in, float clip_norm, float* scal, float* loss_out, const uint32_t* abort,
+                            const DynScal* dyn = nullptr) {
   const int t = threadIdx.x;
   if (t > KGE_MAX_TABLES) return;
   const bool dead = abort != nullptr && *reinterpret_cast<const volatile uint32_t*>(abort) == KGE_PEER_DEAD;
@@ -818,7 +819,12 @@ __global__ void k_dp_scales(const ScalSlots in, float clip_norm, float* scal, fl
     scal[4 + t] = a;
     scal[t] = clip_norm / fmaxf(sqrtf(a), clip_norm);
     if (t == 0) scal[SCAL_ABORT] = dead ? 1.f : 0.f;
-  } else { scal[8] = a; *loss_out = dead ? __int_as_float(0x7fc00000) : a; }
+  } else {
+    scal[8] = a;
+    const float loss = dead ? __int_as_float(0x7fc00000) : a;
+    *loss_out = loss;
+    publish_loss_to_host(dyn, loss);         // captured data-parallel step: the host may wait for exactly this
+  }
 }
 // data-parallel gradient half with peer staging: this rank's [norm^2 x4, loss] block to every rank
 __global__ void k_push_scal(const float* __restrict__ src, ScalSlots out) {
