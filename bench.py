@@ -330,6 +330,8 @@ def run_ours(args, rank, world, device):
     barrier()                     # every step's kernels have finished inside the timed region
     ms_e2e = (time.perf_counter() - t0) * 1e3
     assert math.isfinite(seen_e2e), "a loss read in the end-to-end loop was not finite"
+    if graph is not None:         # what the host read last is the last step's loss, bit for bit
+        assert float(loss_host[0]) == float(graph.loss.item()), "host loss differs from the device loss of the last step"
     ms_e2e_plain = None
     if graph is not None and world == 1:       # the same through kge_train_step_host (no graph, no look-ahead), for comparison
         barrier()
