@@ -107,6 +107,32 @@ def test_tensor_core_rank_equals_generic(model, score, d, n_ent, side):
     assert np.array_equal(parts, tc_flt)
 
 
+@pytest.mark.parametrize("model,score,d", [("DistMult", "dot", 32), ("TransE", "dot", 20)])
+def test_tensor_core_rank_one_call_over_several_query_blocks(model, score, d):
+    """kge_rank takes any number of queries: beyond 16 384 the tensor-core path walks query blocks inside ONE call
+    (table split once, the known-positive bitmask of block i+1 built on the side stream only after block i has
+    finished with the buffer).  40 000 queries in one call == the same queries in calls of at most 16 384, exactly."""
+    from KGE._b200.filter import build_filter
+    n_ent, Q = 600, 40000
+    rng = np.random.default_rng(31)
+    _, _, eng = make_pair(model, n_ent, R, d, None, score=_score_for(model, score), loss=LOSSES["hinge"])
+    pos = rand_triples(rng, 30000, n_ent, R)
+    Xq = pos[rng.integers(0, len(pos), Q)].copy()
+    Xq[::5] = rand_triples(rng, len(Xq[::5]), n_ent, R)
+    for side, s in (("h", 0), ("t", 1)):
+        off, ids = build_filter(pos, Xq, side, n_ent, eng.device)
+        whole = eng.rank_counts(Xq, s, off, ids).cpu().numpy()
+        whole_raw = eng.rank_counts(Xq, s).cpu().numpy()
+        parts, parts_raw = [], []
+        for lo in range(0, Q, 16384):
+            o2, i2 = build_filter(pos, Xq[lo:lo + 16384], side, n_ent, eng.device)
+            parts.append(eng.rank_counts(Xq[lo:lo + 16384], s, o2, i2).cpu().numpy())
+            parts_raw.append(eng.rank_counts(Xq[lo:lo + 16384], s).cpu().numpy())
+        assert np.array_equal(whole, np.concatenate(parts)), side
+        assert np.array_equal(whole_raw, np.concatenate(parts_raw)), side
+        assert (whole <= whole_raw).all() and (whole < whole_raw).any()
+
+
 @pytest.mark.parametrize("n_proto", [2, 5])
 def test_tensor_core_rank_with_mass_ties_falls_back_exactly(n_proto):
     """A table of only a few distinct rows: hundreds of candidates tie with the true score EXACTLY and every one of
