@@ -23,6 +23,25 @@ def test_library_exports_every_declared_symbol():
     assert L.kge_abi_version() == lib.KGE_ABI_VERSION
 
 
+def test_binding_argument_counts_match_header():
+    """Every entry point's ctypes argtypes has as many entries as the header's declaration has parameters (a
+    parameter added on one side only would otherwise read garbage off the stack instead of failing)."""
+    from KGE._b200 import lib
+    L = lib.load()
+    src = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "kge_abi.h")).read(), flags=re.S)
+    seen = 0
+    for m in re.finditer(r"^(?:int|const char\*) (kge_[a-z_]+)\((.*?)\);", src, re.M | re.S):
+        name, args = m.group(1), " ".join(m.group(2).split())
+        n = 0 if args in ("", "void") else args.count(",") + 1
+        at = getattr(L, name).argtypes
+        if n == 0:
+            assert not at, name
+        else:
+            assert at is not None and len(at) == n, (name, n, None if at is None else len(at))
+        seen += 1
+    assert seen == len(lib.SYMBOLS)
+
+
 def test_struct_sizes_match_header():
     from KGE._b200 import lib
     assert C.sizeof(lib.Table) == 56 and C.sizeof(lib.Tables) == 4 * 56 + 16 + 8
