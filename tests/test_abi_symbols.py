@@ -51,6 +51,32 @@ def test_struct_sizes_match_header():
     assert C.sizeof(lib.Grads) == 760   # kge_grads (gcc sizeof): dense, n_peers, peer slots, owner fields, abort_word, multicast
 
 
+def test_struct_layouts_match_the_header_as_gcc_sees_it(tmp_path):
+    """sizeof and the offset of every field of the nine ABI structs, from a C program compiled against
+    include/kge_abi.h, against the ctypes mirrors (same names, same order)."""
+    import subprocess
+    from KGE._b200 import lib
+    pairs = [("kge_table", lib.Table), ("kge_tables", lib.Tables), ("kge_cfg", lib.Cfg), ("kge_sampler", lib.Sampler),
+             ("kge_filter", lib.Filter), ("kge_dp", lib.Dp), ("kge_grads", lib.Grads), ("kge_peer_flags", lib.PeerFlags),
+             ("kge_shard", lib.Shard)]
+    lines = ["#include <stdio.h>", "#include <stddef.h>", '#include "kge_abi.h"', "int main(void) {"]
+    for cname, cls in pairs:
+        lines.append('  printf("%s %%zu", sizeof(%s));' % (cname, cname))
+        for f in cls._fields_:
+            lines.append('  printf(" %%zu", offsetof(%s, %s));' % (cname, f[0]))
+        lines.append('  printf("\\n");')
+    lines += ["  return 0;", "}"]
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.strip().splitlines()
+    for (cname, cls), line in zip(pairs, out):
+        got = [int(x) for x in line.split()[1:]]
+        want = [C.sizeof(cls)] + [getattr(cls, f[0]).offset for f in cls._fields_]
+        assert got == want, (cname, got, want)
+
+
 def test_no_cpu_fallback():
     import torch
     if torch.cuda.is_available():
