@@ -86,3 +86,35 @@ def test_typed_pools_as_csr():
     ent_type, off, members, pos = _type_csr(["a", "b", "a", "b"], t2i)
     assert members.tolist() == [0, 2, 3, 1, 3] and off.tolist() == [0, 3, 5]
     assert pos.tolist() == [0, 0, 1, 1]                            # entity 3 is of type b: its position in b's pool
+
+
+def test_optimizer_descriptors_map_to_cfg_fields():
+    """'Adam' / 'SGD' / 'Adagrad', the KGE.optimizers objects and any Keras-style object (attributes that may be
+    tf.Variables: `.numpy()`) -> kge_cfg fields; what has no kernel raises (BaseModel.py:243-246 accepts any optimizer)."""
+    from KGE import optimizers as O
+
+    assert O.adam_fields(None) == O.adam_fields("Adam") == {"optimizer": L.OPTIM_ADAM, "lr": 0.001, "beta1": 0.9, "beta2": 0.999, "eps": 1e-7}
+    assert O.adam_fields(O.Adam(learning_rate=0.01, beta_1=0.8, beta_2=0.99, epsilon=1e-6)) == {
+        "optimizer": L.OPTIM_ADAM, "lr": 0.01, "beta1": 0.8, "beta2": 0.99, "eps": 1e-6}
+    assert O.adam_fields("sgd") == {"optimizer": L.OPTIM_SGD, "lr": 0.01}
+    assert O.adam_fields(O.Adagrad(learning_rate=0.05, initial_accumulator_value=0.2)) == {
+        "optimizer": L.OPTIM_ADAGRAD, "lr": 0.05, "eps": 1e-7, "acc_init": 0.2}
+
+    class Var:                       # a tf.Variable-like hyper-parameter
+        def __init__(self, v):
+            self.v = v
+
+        def numpy(self):
+            return self.v
+
+    class KerasAdam:                 # name contains "adam": picked up by its attributes
+        learning_rate, beta_1, beta_2, epsilon = Var(0.002), 0.85, 0.995, 1e-8
+    got = O.adam_fields(KerasAdam())
+    assert got == {"optimizer": L.OPTIM_ADAM, "lr": 0.002, "beta1": 0.85, "beta2": 0.995, "eps": 1e-8}
+
+    class SGD:
+        learning_rate, momentum = 0.1, 0.9
+    for bad in (lambda: O.adam_fields("RMSprop"), lambda: O.adam_fields(SGD()), lambda: O.SGD(momentum=0.5),
+                lambda: O.Adam(amsgrad=True), lambda: O.adam_fields(type("Nadam", (), {})())):
+        with pytest.raises(NotImplementedError):
+            bad()
