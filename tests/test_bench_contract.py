@@ -38,3 +38,32 @@ def test_product_arm_needs_a_cuda_device():
         pytest.skip("GPU present")
     r = _run("--steps", "1", "--warmup", "1")
     assert r.returncode != 0 and "CUDA device" in (r.stderr + r.stdout) and "{" not in r.stdout
+
+
+def test_product_code_never_reaches_into_the_oracle():
+    """oracle/ is test infrastructure: only tests/, __graft_entry__.smoke() and bench.py's CPU legs may use it.  No
+    module of the shipped package imports it (statically), and importing the package leaves it unloaded."""
+    import ast
+    pkg = os.path.join(ROOT, "knowledge-graph-embedding_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if not f.endswith(".py"):
+                continue
+            tree = ast.parse(open(os.path.join(dirpath, f)).read())
+            for node in ast.walk(tree):
+                names = []
+                if isinstance(node, ast.Import):
+                    names = [a.name for a in node.names]
+                elif isinstance(node, ast.ImportFrom):
+                    names = [node.module or ""]
+                assert not any(n == "oracle" or n.startswith("oracle.") for n in names), (f, names)
+    code = ("import sys; sys.path[:0] = [%r, %r]; import KGE, KGE.models.base_model.BaseModel, KGE._b200.engine, KGE._b200.shard; "
+            "assert not any(m == 'oracle' or m.startswith('oracle.') for m in sys.modules), 'oracle loaded'") % (ROOT, pkg)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-1500:]
+    # and bench.py touches it only inside its CPU legs (function bodies), never at import time
+    tree = ast.parse(open(os.path.join(ROOT, "bench.py")).read())
+    for node in tree.body:
+        if isinstance(node, (ast.Import, ast.ImportFrom)):
+            names = [a.name for a in node.names] if isinstance(node, ast.Import) else [node.module or ""]
+            assert not any(n.startswith("oracle") for n in names)
