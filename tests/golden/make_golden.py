@@ -22,6 +22,7 @@ import warnings
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
+OUT = os.environ.get("KGE_GOLDEN_OUT", HERE)        # tests/test_golden_oracle.py regenerates into a scratch directory
 sys.path.insert(0, os.path.join(ROOT, "oracle", "tf_shim"))
 sys.path.insert(0, "/root/reference")
 sys.path.insert(0, ROOT)
@@ -91,7 +92,7 @@ def gen_ops():
     out["soft_p2"] = npy(Cn.soft_constraint(tf.constant(X), p=2, value=1.0, axis=-1))
     out["lpreg_p2"] = npy(Cn.Lp_regularization(tf.constant(X), p=2, axis=-1))
     out["lpreg_p3"] = npy(Cn.Lp_regularization(tf.constant(X), p=3, axis=-1))
-    np.savez_compressed(os.path.join(HERE, "ops.npz"), **out)
+    np.savez_compressed(os.path.join(OUT, "ops.npz"), **out)
     return len(out)
 
 
@@ -283,7 +284,7 @@ def gen_case(name, spec, opt=None):
     out["spec"] = np.asarray([str(x) for x in spec])
     if opt is not None:
         out["opt"] = np.asarray([str(opt[0]), repr(float(opt[1]))])
-    np.savez_compressed(os.path.join(HERE, "case_%s.npz" % name), **out)
+    np.savez_compressed(os.path.join(OUT, "case_%s.npz" % name), **out)
     return rec["loss"]
 
 
@@ -300,7 +301,7 @@ def gen_typed():
     out = {"ind2type": np.asarray(ind2type), "X": X}
     for side in ("h", "t"):
         out["neg_" + side] = npy(strat(tf.constant(X), negative_ratio=5, side=side))
-    np.savez_compressed(os.path.join(HERE, "typed.npz"), **out)
+    np.savez_compressed(os.path.join(OUT, "typed.npz"), **out)
 
 
 # ---------------------------------------------------------------------------------
@@ -351,7 +352,7 @@ def gen_train_loop():
     out["eval_keys"] = np.asarray(list(res.keys()))
     out["eval_vals"] = np.asarray([float(v) for v in res.values()])
     out["cfg"] = np.asarray([d, k, bs, epochs, SEED])
-    np.savez_compressed(os.path.join(HERE, "train_loop_transh.npz"), **out)
+    np.savez_compressed(os.path.join(OUT, "train_loop_transh.npz"), **out)
     return len(smp.batches)
 
 

@@ -213,3 +213,24 @@ def test_full_train_loop_matches_reference():
         close(W.data[kk], v)
     res, _ = RS.evaluate(m, W, g["val"], "h", np.concatenate([g["train"], g["val"]]))
     close(list(res.values()), g["eval_vals"], 1e-9)
+
+
+def test_committed_fixtures_are_what_the_reference_source_produces_today(tmp_path):
+    """The pin itself: tests/golden/make_golden.py executes the UNMODIFIED reference package (over the tf shim) on
+    the seeded inputs; what it writes now must equal the committed fixtures array for array.  Needs
+    /root/reference (the build container; the GPU box has no reference: skipped there)."""
+    import subprocess
+    import sys
+    if not os.path.isdir("/root/reference/KGE"):
+        pytest.skip("the reference checkout is not on this machine")
+    env = dict(os.environ, KGE_GOLDEN_OUT=str(tmp_path))
+    r = subprocess.run([sys.executable, os.path.join(GOLD, "make_golden.py")], env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    made = sorted(f for f in os.listdir(tmp_path) if f.endswith(".npz"))
+    assert len(made) >= 20, made
+    for f in made:
+        new, old = np.load(os.path.join(tmp_path, f)), np.load(os.path.join(GOLD, f))
+        assert sorted(new.files) == sorted(old.files), f
+        for k in new.files:
+            assert new[k].dtype == old[k].dtype and new[k].shape == old[k].shape, (f, k)
+            assert np.array_equal(new[k], old[k], equal_nan=new[k].dtype.kind in "fc"), (f, k)
