@@ -234,3 +234,19 @@ def test_committed_fixtures_are_what_the_reference_source_produces_today(tmp_pat
         for k in new.files:
             assert new[k].dtype == old[k].dtype and new[k].shape == old[k].shape, (f, k)
             assert np.array_equal(new[k], old[k], equal_nan=new[k].dtype.kind in "fc"), (f, k)
+
+
+def test_bundled_dataset_fixture_equals_the_reference_files():
+    """tests/golden/data_bundled.npz (the real FB15k-237 train / valid and FB15k valid triples the GPU tests train
+    and rank on) against the reference's bundled CSV files, triple for triple (build container only)."""
+    ref = "/root/reference/data"
+    if not os.path.isdir(ref):
+        pytest.skip("the reference checkout is not on this machine")
+    files = {"fb15k237_train": "fb15k_237/train_indexed/train.csv", "fb15k237_valid": "fb15k_237/valid_indexed/valid.csv",
+             "fb15k_valid": "fb15k/valid_indexed/valid.csv"}
+    g = np.load(os.path.join(GOLD, "data_bundled.npz"))
+    assert sorted(g.files) == sorted(files)
+    for name, rel in files.items():
+        a = np.loadtxt(os.path.join(ref, rel), delimiter=",", dtype=np.int64)
+        assert np.array_equal(g[name].astype(np.int64), a), name
+    assert g["fb15k237_train"].shape == (272115, 3) and g["fb15k237_valid"].shape == (17526, 3) and g["fb15k_valid"].shape == (50000, 3)
