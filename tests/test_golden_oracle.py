@@ -250,3 +250,38 @@ def test_bundled_dataset_fixture_equals_the_reference_files():
         a = np.loadtxt(os.path.join(ref, rel), delimiter=",", dtype=np.int64)
         assert np.array_equal(g[name].astype(np.int64), a), name
     assert g["fb15k237_train"].shape == (272115, 3) and g["fb15k237_valid"].shape == (17526, 3) and g["fb15k_valid"].shape == (50000, 3)
+
+
+FRESH = {          # specs, sizes and seeds (from the names) that no committed fixture has
+    "fresh_transe": ("TransE", "l1", "logistic", 3, "t", True, 1.0, 12, 12),
+    "fresh_distmult": ("DistMult", None, "hinge", 5, "h+t", True, 0.5, 10, 10),
+    "fresh_transr": ("TransR", "l2", "hinge", 2, "h", True, 1.0, 6, 9),
+    "fresh_rotate": ("RotatE", "l2", "selfadv", 4, "h+t", True, 1.0, 10, 10),
+    "fresh_transh": ("TransH", "l2pow", "bce", 3, "h+t", True, 0.25, 8, 8),
+    "fresh_transd": ("TransD", "l1", "square", 2, "t", False, 1.0, 7, 11),
+    "fresh_rescal": ("RESCAL", None, "logistic", 2, "h+t", True, 1.0, 6, 6),
+    "fresh_se": ("SE", "l2", "hinge", 3, "h+t", True, 1.0, 5, 5),
+    "fresh_um": ("UM", "l1", "hinge", 2, "h", True, 1.0, 9, 9),
+}
+
+
+def test_oracle_against_the_live_reference_on_unseen_cases(tmp_path, monkeypatch):
+    """Beyond the committed vectors: in the build container the generator runs the reference's source on nine cases
+    no fixture holds (other sizes, seeds, score / loss / side combinations), and the oracle has to reproduce their
+    scores, step sequences (losses, weights after every step, negatives' layout), ranks and metrics."""
+    import subprocess
+    import sys
+    if not os.path.isdir("/root/reference/KGE"):
+        pytest.skip("the reference checkout is not on this machine")
+    code = ("import runpy, sys\n"
+            "ns = runpy.run_path(%r, run_name='golden')\n"
+            "for name, spec in %r.items():\n"
+            "    ns['gen_case'](name, spec)\n") % (os.path.join(GOLD, "make_golden.py"), FRESH)
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, KGE_GOLDEN_OUT=str(tmp_path)), capture_output=True,
+                       text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-3000:]
+    monkeypatch.setattr(sys.modules[__name__], "GOLD", str(tmp_path))
+    for name in FRESH:
+        test_score_hrt(name)
+        test_run_single_batch_sequence(name)
+        test_ranks_and_metrics(name)
