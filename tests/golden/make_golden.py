@@ -189,6 +189,16 @@ CASES = {
     "distmult_hinge_nocon": ("DistMult", None, "hinge", 2, "h", False, 1.0, 8, 8),
     "rescal": ("RESCAL", None, "square", 4, "h+t", True, 1.0, 6, 6),
     "rescal_logistic_nocon": ("RESCAL", None, "logistic", 2, "t", False, 1.0, 6, 6),
+    # round 2: one more per model, other sizes (rectangular TransR / TransD both ways), sides and score / loss pairings
+    "extra_transe": ("TransE", "l1", "logistic", 3, "t", True, 1.0, 12, 12),
+    "extra_distmult": ("DistMult", None, "hinge", 5, "h+t", True, 0.5, 10, 10),
+    "extra_transr": ("TransR", "l2", "hinge", 2, "h", True, 1.0, 6, 9),
+    "extra_rotate": ("RotatE", "l2", "selfadv", 4, "h+t", True, 1.0, 10, 10),
+    "extra_transh": ("TransH", "l2pow", "bce", 3, "h+t", True, 0.25, 8, 8),
+    "extra_transd": ("TransD", "l1", "square", 2, "t", False, 1.0, 7, 11),
+    "extra_rescal": ("RESCAL", None, "logistic", 2, "h+t", True, 1.0, 6, 6),
+    "extra_se": ("SE", "l2", "hinge", 3, "h+t", True, 1.0, 5, 5),
+    "extra_um": ("UM", "l1", "hinge", 2, "h", True, 1.0, 9, 9),
 }
 # user-supplied Keras optimizers (BaseModel.py:243-246).  name: (case spec, optimizer, lr)
 OPT_CASES = {
