@@ -265,6 +265,14 @@ FRESH = {          # specs, sizes and seeds (from the names) that no committed f
 }
 
 
+FRESH_OPT = {      # user-supplied Keras optimizers (BaseModel.py:243-246) on models the committed optimizer cases do not pair them with
+    "fresh_opt_um_sgd": (("UM", "l2pow", "hinge", 3, "h+t", True, 1.0, 9, 9), "sgd", 0.02),
+    "fresh_opt_se_adagrad": (("SE", "l1", "hinge", 2, "t", True, 1.0, 5, 5), "adagrad", 0.03),
+    "fresh_opt_rescal_sgd": (("RESCAL", None, "square", 2, "h+t", True, 1.0, 6, 6), "sgd", 0.01),
+    "fresh_opt_rotate_sgd": (("RotatE", "l1", "selfadv", 4, "h+t", True, 1.0, 8, 8), "sgd", 0.05),
+}
+
+
 def test_oracle_against_the_live_reference_on_unseen_cases(tmp_path, monkeypatch):
     """Beyond the committed vectors: in the build container the generator runs the reference's source on nine cases
     no fixture holds (other sizes, seeds, score / loss / side combinations), and the oracle has to reproduce their
@@ -276,12 +284,14 @@ def test_oracle_against_the_live_reference_on_unseen_cases(tmp_path, monkeypatch
     code = ("import runpy, sys\n"
             "ns = runpy.run_path(%r, run_name='golden')\n"
             "for name, spec in %r.items():\n"
-            "    ns['gen_case'](name, spec)\n") % (os.path.join(GOLD, "make_golden.py"), FRESH)
+            "    ns['gen_case'](name, spec)\n"
+            "for name, (spec, kind, lr) in %r.items():\n"
+            "    ns['gen_case'](name, spec, (kind, lr))\n") % (os.path.join(GOLD, "make_golden.py"), FRESH, FRESH_OPT)
     r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, KGE_GOLDEN_OUT=str(tmp_path)), capture_output=True,
                        text=True, timeout=900)
     assert r.returncode == 0, r.stderr[-3000:]
     monkeypatch.setattr(sys.modules[__name__], "GOLD", str(tmp_path))
-    for name in FRESH:
+    for name in list(FRESH) + list(FRESH_OPT):
         test_score_hrt(name)
         test_run_single_batch_sequence(name)
         test_ranks_and_metrics(name)
